@@ -1,0 +1,161 @@
+/* qcb200.h -- C ABI of the B200-native collocation evaluator.
+ *
+ * Drop-in for the evaluator behind QuantumCollocation.jl's bilinear integrators
+ * (reference seam: the `integrator=` keyword of the problem templates,
+ * src/problem_templates/smooth_pulse_problem.jl:57,103-127; the objects built by
+ * src/quantum_integrators.jl:28-134).  Julia reaches these entry points with `ccall`
+ * (see INTEGRATION.md and julia/QCB200.jl); Python reaches them with ctypes.
+ *
+ * Conventions
+ *  - every matrix is column-major FP64; every index array handed across the ABI is 1-based
+ *    int64 (what Julia's Int arrays hold);
+ *  - the caller owns all host arrays; the library owns device memory, streams and pinned
+ *    staging; no host pointer is retained after a call returns; no callbacks;
+ *  - every function returns a qcb_status; the text of the last error on a handle is
+ *    available through qcb_last_error();
+ *  - a handle is not thread-safe (Ipopt's callbacks are sequential on one host thread,
+ *    src/quantum_control_problem.jl:163-164);
+ *  - there is no CPU fallback: if no CUDA device is usable, qcb_create fails.
+ */
+#ifndef QCB200_H
+#define QCB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct qcb_handle_s *qcb_handle;
+typedef struct qcb_fidelity_s *qcb_fidelity;
+
+typedef enum {
+    QCB_OK = 0,
+    QCB_ERR_ARG = 1,        /* bad argument / descriptor */
+    QCB_ERR_CUDA = 2,       /* CUDA runtime error (message has the detail) */
+    QCB_ERR_RANGE = 3,      /* non-finite input or ||dt*G(u)||_1 beyond the supported range:
+                               map to Ipopt's "evaluation failed" in the shim */
+    QCB_ERR_STRUCTURE = 4,  /* a caller-supplied sparsity structure could not be mapped */
+    QCB_ERR_NOMEM = 5
+} qcb_status;
+
+/* x-block layout of the defect Jacobian */
+#define QCB_JAC_DENSE_X 0      /* d(delta)/d(x_k) as a dense x_dim^2 block (explicit zeros) */
+#define QCB_JAC_BLOCK_DIAG 1   /* c diagonal d x d blocks */
+
+/* What to evaluate */
+#define QCB_WANT_DEFECT 0
+#define QCB_WANT_JACOBIAN 1
+#define QCB_WANT_HESSIAN 2
+
+/* Problem descriptor.  Replaces the arguments of
+ *   DirectTrajOpt.BilinearIntegrator(G_hat, x_sym, u_sym, traj)
+ * as called at src/quantum_integrators.jl:32,44,55,71,112,123,133: the closure G_hat(u) =
+ * G_drift + sum_j u_j G_j is passed as its matrices, the symbols as offsets into a knot. */
+typedef struct {
+    int32_t struct_bytes;   /* sizeof(qcb_desc), for ABI evolution */
+    int32_t d;              /* rows of the generator (2n for kets / vectorised unitaries) */
+    int32_t c;              /* columns of the state panel: n for I_n (x) G (unitary), 1 for a ket */
+    int32_t m;              /* number of drives */
+    int32_t N;              /* knots of the trajectory; K = N-1 intervals */
+    int32_t S;              /* systems sharing the controls (SamplingTrajectory), else 1 */
+    int32_t z_dim;          /* doubles per knot in Z */
+    int32_t u_off;          /* 0-based offset of u inside a knot */
+    int32_t dt_off;         /* 0-based offset of the timestep inside a knot */
+    int32_t jac_mode;       /* QCB_JAC_* */
+    int32_t device;         /* CUDA device ordinal */
+    int32_t k_begin;        /* this handle evaluates intervals [k_begin, k_end), 0-based; */
+    int32_t k_end;          /*   k_end = 0 means K (the multi-GPU time-slab partition)      */
+    int32_t force_path;     /* 0 auto, 1 small-d kernel, 2 large-d DMMA path (testing) */
+    const int32_t *x_off;   /* [S] 0-based offset of each system's state inside a knot */
+    const double *G_drift;  /* [S][d*d]    */
+    const double *G_drives; /* [S][m][d*d] */
+} qcb_desc;
+
+/* ---- life cycle -------------------------------------------------------------------- */
+qcb_status qcb_create(qcb_handle *out, const qcb_desc *desc);
+void qcb_destroy(qcb_handle h);
+const char *qcb_last_error(qcb_handle h);   /* h may be NULL: error of the last failed qcb_create */
+const char *qcb_version(void);
+
+/* ---- sizes ---------------------------------------------------------------------------
+ * integrator.dim in the reference = x_dim*(N-1) per integrator
+ * (src/problem_templates/smooth_pulse_problem.jl:513); here summed over the S systems and
+ * restricted to the handle's slab. */
+int64_t qcb_defect_dim(qcb_handle h);
+int64_t qcb_jacobian_nnz(qcb_handle h);
+int64_t qcb_hessian_nnz(qcb_handle h);
+
+/* ---- sparsity structure ---------------------------------------------------------------
+ * Native structure, order [system][interval][entries sorted by (column,row)].  rows of the
+ * Jacobian are 1-based positions in this handle's defect vector plus row_base; columns are
+ * 1-based positions in Z.  Replaces the jacobian_structure / hessian_structure queries the
+ * MOI evaluator of DirectTrajOpt makes of an AbstractIntegrator. */
+qcb_status qcb_jacobian_structure(qcb_handle h, int64_t row_base, int64_t *rows, int64_t *cols);
+qcb_status qcb_hessian_structure(qcb_handle h, int64_t *rows, int64_t *cols);
+/* Adopt the reference's own COO order instead: pass the (rows, cols) the Julia integrator
+ * reports for its Jacobian block (rows relative to row_base) and its Hessian block.  Entries
+ * must be grouped [system][interval] with the same pattern in every interval; entries the
+ * model makes structurally zero are accepted and filled with 0.  Either pair may be NULL
+ * (nnz 0) to keep the native order for it. */
+qcb_status qcb_set_structure(qcb_handle h, int64_t row_base,
+                             const int64_t *jac_rows, const int64_t *jac_cols, int64_t jac_nnz,
+                             const int64_t *hess_rows, const int64_t *hess_cols, int64_t hess_nnz);
+
+/* ---- evaluation, host buffers (what the Julia shim calls from Ipopt's callbacks) -------
+ * Z: N*z_dim doubles.  mu: multipliers of this integrator set, [S][K][x_dim] with K = N-1
+ * (full-trajectory indexing even for a slab handle).  Outputs cover the handle's slab.
+ *   qcb_eval_defect   <- DirectTrajOpt.evaluate!(delta, integrator, traj)
+ *                        (src/problem_templates/smooth_pulse_problem.jl:512-515)
+ *   qcb_eval_jacobian <- the integrator's Jacobian-values callback (eval_jac_g)
+ *   qcb_eval_hessian  <- the integrator's Hessian-of-Lagrangian-values callback (eval_h)
+ *   qcb_eval_all      <- all three from one pass over the trajectory
+ * Any output pointer of qcb_eval_all may be NULL. */
+qcb_status qcb_eval_defect(qcb_handle h, const double *Z, double *delta);
+qcb_status qcb_eval_jacobian(qcb_handle h, const double *Z, double *jac_vals);
+qcb_status qcb_eval_hessian(qcb_handle h, const double *Z, const double *mu, double *hess_vals);
+qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu,
+                        double *delta, double *jac_vals, double *hess_vals);
+
+/* ---- evaluation, device buffers (inputs/outputs already resident in HBM) ---------------
+ * Same semantics; all pointers are device pointers on the handle's device; the work is
+ * ordered on the handle's stream and the call returns after it has completed. */
+qcb_status qcb_eval_all_device(qcb_handle h, const double *dZ, const double *dmu,
+                               double *d_delta, double *d_jac_vals, double *d_hess_vals);
+
+/* Pinned host memory for callers that want full PCIe bandwidth on the host-buffer calls. */
+qcb_status qcb_host_alloc(void **ptr, size_t bytes);
+void qcb_host_free(void *ptr);
+
+/* Number of kernels this handle has launched since creation, and per-phase timings of the
+ * last host-buffer call in milliseconds: [0] H2D, [1] kernels, [2] D2H, [3] total. */
+int64_t qcb_kernel_launches(qcb_handle h);
+qcb_status qcb_get_timings(qcb_handle h, double ms[4]);
+/* The CUDA stream (cudaStream_t) the handle launches on, for callers that time with events. */
+void *qcb_stream(qcb_handle h);
+
+/* ---- terminal fidelities ---------------------------------------------------------------
+ * F(x_N) for the losses of src/quantum_objectives.jl and the constraints of
+ * src/quantum_constraints.jl.  goal: complex entries as interleaved (re, im) pairs,
+ * column-major.  All of them are quadratic forms F = w * sum_r (g_r . x)^2. */
+#define QCB_FID_UNITARY 0           /* unitary_fidelity_loss, quantum_objectives.jl:173-180 */
+#define QCB_FID_KET 1               /* ket_fidelity_loss, :21-27 */
+#define QCB_FID_COHERENT_KET 2      /* coherent_ket_fidelity, :88-103 (x = concatenated kets) */
+#define QCB_FID_UNITARY_SUBSPACE 3  /* EmbeddedOperator variant, :182-191 */
+
+/* n: Hilbert dimension; count: number of kets (COHERENT_KET) else 1; subspace: 0-based level
+ * indices (UNITARY_SUBSPACE; goal is then n_sub x n_sub), NULL otherwise. */
+qcb_status qcb_fidelity_create(qcb_fidelity *out, int32_t kind, int32_t n, int32_t count,
+                               const double *goal_re_im, const int32_t *subspace, int32_t n_sub,
+                               int32_t device);
+void qcb_fidelity_destroy(qcb_fidelity f);
+int64_t qcb_fidelity_x_dim(qcb_fidelity f);
+/* x: x_dim doubles (host).  F, grad (x_dim) and hess (x_dim*x_dim, dense column-major) may be
+ * NULL.  The infidelity objective Q*|1-F| (quantum_objectives.jl:199) and the constraint
+ * F_min - F (quantum_constraints.jl:112) follow by the chain rule in the shim. */
+qcb_status qcb_fidelity_eval(qcb_fidelity f, const double *x, double *F, double *grad, double *hess);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QCB200_H */

@@ -1,0 +1,446 @@
+"""CPU oracle for the per-knot collocation evaluation (TEST INFRASTRUCTURE ONLY).
+
+This file restates, with numpy/scipy, the mathematics of the hot path that
+QuantumCollocation.jl delegates to DirectTrajOpt.jl's ``BilinearIntegrator``:
+
+    defect      delta_k = x_{k+1} - exp(dt_k * G(u_k)) x_k     (docs/src/index.md:99-105,
+                                                                 src/quantum_integrators.jl:28-45)
+    generator   G(u) = G_drift + sum_j u_j G_j                   (src/quantum_integrators.jl:31,43)
+    Jacobian    d delta / d(x_k, u_k, dt_k, x_{k+1})
+    Hessian     d^2 (mu_k . delta_k) / d z_k^2
+    fidelities  src/quantum_objectives.jl:21-27, 88-103, 173-191
+    constraints src/quantum_constraints.jl:20-35, 65-100, 106-121
+
+PARITY UNPINNED: the arithmetic of this path lives in un-vendored Julia
+dependencies (DirectTrajOpt.jl 0.8, ExponentialAction.jl 0.2,
+PiccoloQuantumObjects.jl 0.10 -- compat bounds in Project.toml:21-34) and no
+Julia toolchain exists in this image, so this oracle cannot be checked against
+outputs of the reference evaluator itself.  It is pinned only against what the
+reference tree does hold: the iso-vec layout fixture (test/test_utils.jl:52-103),
+the CoherentKetInfidelityObjective known answers (src/quantum_objectives.jl:315-394),
+the structure cardinalities printed in the docs' Ipopt logs
+(docs/literate/examples/multilevel_transmon.jl:105-113, two_qubit_gates.jl:135-143)
+and finite-difference self-consistency (the reference's own ``test_integrator``
+criterion, src/quantum_integrators.jl:194).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may import
+this module.  The product path (the CUDA library) never does.
+
+The oracle is deliberately *independent* of the algorithm the CUDA kernels use
+(truncated Taylor + scaling-and-squaring with adjoint second-order sweeps): it
+uses scipy's Pade expm, scipy's expm_frechet, and block-triangular
+exponentials for the second-order Frechet terms.
+"""
+from __future__ import annotations
+
+import numpy as np
+from scipy.linalg import expm, expm_frechet
+
+# --------------------------------------------------------------------------- #
+# Isomorphisms (PiccoloQuantumObjects conventions as used by the reference:
+# src/quantum_objectives.jl:25,177; test/test_utils.jl:88-92)
+# --------------------------------------------------------------------------- #
+
+
+def iso(Z: np.ndarray) -> np.ndarray:
+    """Real representation of a complex matrix: [[Re, -Im], [Im, Re]]."""
+    Z = np.asarray(Z, dtype=complex)
+    return np.block([[Z.real, -Z.imag], [Z.imag, Z.real]])
+
+
+def G_of_H(H: np.ndarray) -> np.ndarray:
+    """Generator G(H) = iso(-iH) = [[Im H, Re H], [-Re H, Im H]] (skew for Hermitian H)."""
+    H = np.asarray(H, dtype=complex)
+    return np.block([[H.imag, H.real], [-H.real, H.imag]])
+
+
+def ket_to_iso(psi: np.ndarray) -> np.ndarray:
+    psi = np.asarray(psi, dtype=complex)
+    return np.concatenate([psi.real, psi.imag])
+
+
+def iso_to_ket(x: np.ndarray) -> np.ndarray:
+    n = x.shape[0] // 2
+    return x[:n] + 1j * x[n:]
+
+
+def operator_to_iso_vec(U: np.ndarray) -> np.ndarray:
+    """vec([Re U; Im U]): per column j the 2n numbers [Re U[:,j]; Im U[:,j]]."""
+    U = np.asarray(U, dtype=complex)
+    return np.concatenate([np.concatenate([U[:, j].real, U[:, j].imag]) for j in range(U.shape[1])])
+
+
+def iso_vec_to_operator(x: np.ndarray) -> np.ndarray:
+    n = int(round(np.sqrt(x.shape[0] / 2)))
+    P = x.reshape(n, 2 * n).T  # column-major reshape to (2n, n)
+    return P[:n, :] + 1j * P[n:, :]
+
+
+# --------------------------------------------------------------------------- #
+# Per-unit evaluation (one knot k of one integrator)
+# --------------------------------------------------------------------------- #
+
+
+def second_frechet(A: np.ndarray, B: np.ndarray, C: np.ndarray) -> np.ndarray:
+    """D^2 exp(A)[B, C] via exp of a 3x3 block upper-triangular matrix (both orderings)."""
+    d = A.shape[0]
+    Zr = np.zeros((d, d))
+
+    def ordered(P, Q):
+        T = np.block([[A, P, Zr], [Zr, A, Q], [Zr, Zr, A]])
+        return expm(T)[:d, 2 * d:]
+
+    return ordered(B, C) + ordered(C, B)
+
+
+def unit_eval(G0, Gd, X, Xn, M, u, dt, want_hessian=True):
+    """All canonical blocks for one unit.
+
+    G0 (d,d), Gd (m,d,d); X, Xn, M are (d,c) panels (column-major reshape of the
+    x_dim-vectors); u (m,), dt scalar.  Signs are those of delta = Xn - E X.
+    Returns dict: E, delta (d,c), J_u (m,d,c), J_dt (d,c), and (if want_hessian)
+    H_xu (m,d,c), H_xdt (d,c), H_uu (m,m), H_udt (m,), H_dtdt (scalar).
+    """
+    m = Gd.shape[0]
+    G = G0 + np.tensordot(u, Gd, axes=1) if m else G0.copy()
+    A = dt * G
+    E = expm(A)
+    out = {"E": E, "delta": Xn - E @ X}
+    L = [expm_frechet(A, dt * Gd[j], compute_expm=False) for j in range(m)]
+    GE = G @ E
+    out["J_u"] = np.array([-(L[j] @ X) for j in range(m)]).reshape(m, *X.shape)
+    out["J_dt"] = -(GE @ X)
+    if want_hessian:
+        W = M @ X.T
+        out["H_xu"] = np.array([-(L[j].T @ M) for j in range(m)]).reshape(m, *X.shape)
+        out["H_xdt"] = -(GE.T @ M)
+        Huu = np.zeros((m, m))
+        for i in range(m):
+            for j in range(i, m):
+                Q = second_frechet(A, dt * Gd[i], dt * Gd[j])
+                Huu[i, j] = Huu[j, i] = -np.sum(W * Q)
+        out["H_uu"] = Huu
+        out["H_udt"] = np.array([-np.sum(W * (Gd[j] @ E + G @ L[j])) for j in range(m)])
+        out["H_dtdt"] = -np.sum(W * (G @ GE))
+    return out
+
+
+# --------------------------------------------------------------------------- #
+# Problem layout + native sparsity structure
+# --------------------------------------------------------------------------- #
+
+
+class Layout:
+    """Knot-major flat Z layout for one (possibly sampled) bilinear integrator set.
+
+    d: generator dim, c: state columns (x_dim = d*c), m: drives, N: knots,
+    S: systems; x_off[s], u_off, dt_off: 0-based offsets inside a knot of width z_dim.
+    jac_mode: 0 = dense x-block (x_dim^2 per knot, the structure the docs-era Ipopt
+    logs imply), 1 = block-diagonal (c blocks of d^2).
+    """
+
+    def __init__(self, d, c, m, N, S, z_dim, x_off, u_off, dt_off, jac_mode=0):
+        self.d, self.c, self.m, self.N, self.S = d, c, m, N, S
+        self.z_dim, self.x_off, self.u_off, self.dt_off = z_dim, list(x_off), u_off, dt_off
+        self.jac_mode = jac_mode
+        self.x_dim = d * c
+        self.K = N - 1
+
+    @property
+    def jac_nnz_unit(self):
+        xb = self.x_dim ** 2 if self.jac_mode == 0 else self.c * self.d ** 2
+        return xb + self.x_dim * (self.m + 2)
+
+    @property
+    def hess_nnz_unit(self):
+        m = self.m
+        return self.x_dim * (m + 1) + m * (m + 1) // 2 + m + 1
+
+    def unit_inputs(self, Z, mu, s, k):
+        d, c, zd = self.d, self.c, self.z_dim
+        zk = Z[k * zd:(k + 1) * zd]
+        zn = Z[(k + 1) * zd:(k + 2) * zd]
+        X = zk[self.x_off[s]:self.x_off[s] + self.x_dim].reshape(c, d).T
+        Xn = zn[self.x_off[s]:self.x_off[s] + self.x_dim].reshape(c, d).T
+        u = zk[self.u_off:self.u_off + self.m]
+        dt = zk[self.dt_off]
+        M = None
+        if mu is not None:
+            M = mu[(s * self.K + k) * self.x_dim:(s * self.K + k + 1) * self.x_dim].reshape(c, d).T
+        return X, Xn, M, u, dt
+
+    # ---- native structure: per unit, entries sorted by (column, row) like Julia's findnz ----
+    def jac_unit_pattern(self, s):
+        """List of (local_row, local_col_in_[z_k;z_{k+1}], source) sorted by (col,row).
+
+        source = ('E', r, q) -> -E[r,q]; ('Z',) -> 0; ('U', j, i) -> J_u[j] flat i;
+        ('T', i) -> J_dt flat i; ('I',) -> +1.
+        """
+        d, c, m, xd, zd = self.d, self.c, self.m, self.x_dim, self.z_dim
+        ent = []
+        for q in range(xd):
+            b, qq = divmod(q, d)
+            col = self.x_off[s] + q
+            if self.jac_mode == 0:
+                for r in range(xd):
+                    a, rr = divmod(r, d)
+                    ent.append((r, col, ("E", rr, qq) if a == b else ("Z",)))
+            else:
+                for rr in range(d):
+                    ent.append((b * d + rr, col, ("E", rr, qq)))
+        for j in range(m):
+            for r in range(xd):
+                ent.append((r, self.u_off + j, ("U", j, r)))
+        for r in range(xd):
+            ent.append((r, self.dt_off, ("T", r)))
+        for r in range(xd):
+            ent.append((r, zd + self.x_off[s] + r, ("I",)))
+        ent.sort(key=lambda e: (e[1], e[0]))
+        return ent
+
+    def hess_unit_pattern(self, s):
+        """Upper-triangular (row<=col in z_k indices) entries sorted by (col,row).
+
+        source = ('XU', j, i), ('XT', i), ('UU', i, j), ('UT', j), ('TT',).
+        """
+        m, xd = self.m, self.x_dim
+        ent = []
+
+        def add(a, b, src):
+            ent.append((min(a, b), max(a, b), src))
+
+        for j in range(m):
+            for i in range(xd):
+                add(self.x_off[s] + i, self.u_off + j, ("XU", j, i))
+        for i in range(xd):
+            add(self.x_off[s] + i, self.dt_off, ("XT", i))
+        for i in range(m):
+            for j in range(i, m):
+                add(self.u_off + i, self.u_off + j, ("UU", i, j))
+        for j in range(m):
+            add(self.u_off + j, self.dt_off, ("UT", j))
+        add(self.dt_off, self.dt_off, ("TT",))
+        ent.sort(key=lambda e: (e[1], e[0]))
+        return ent
+
+    def jacobian_structure(self, row_base=0):
+        """1-based (rows, cols) of the whole integrator set, order [s][k][unit pattern]."""
+        rows, cols = [], []
+        for s in range(self.S):
+            pat = self.jac_unit_pattern(s)
+            lr = np.array([e[0] for e in pat], dtype=np.int64)
+            lc = np.array([e[1] for e in pat], dtype=np.int64)
+            for k in range(self.K):
+                rows.append(row_base + (s * self.K + k) * self.x_dim + lr + 1)
+                cols.append(k * self.z_dim + lc + 1)
+        return np.concatenate(rows), np.concatenate(cols)
+
+    def hessian_structure(self):
+        rows, cols = [], []
+        for s in range(self.S):
+            pat = self.hess_unit_pattern(s)
+            lr = np.array([e[0] for e in pat], dtype=np.int64)
+            lc = np.array([e[1] for e in pat], dtype=np.int64)
+            for k in range(self.K):
+                rows.append(k * self.z_dim + lr + 1)
+                cols.append(k * self.z_dim + lc + 1)
+        return np.concatenate(rows), np.concatenate(cols)
+
+
+def _jac_value(src, ev):
+    t = src[0]
+    if t == "E":
+        return -ev["E"][src[1], src[2]]
+    if t == "Z":
+        return 0.0
+    if t == "U":
+        return ev["J_u"][src[1]].T.reshape(-1)[src[2]]
+    if t == "T":
+        return ev["J_dt"].T.reshape(-1)[src[1]]
+    return 1.0
+
+
+def _hess_value(src, ev):
+    t = src[0]
+    if t == "XU":
+        return ev["H_xu"][src[1]].T.reshape(-1)[src[2]]
+    if t == "XT":
+        return ev["H_xdt"].T.reshape(-1)[src[1]]
+    if t == "UU":
+        return ev["H_uu"][src[1], src[2]]
+    if t == "UT":
+        return ev["H_udt"][src[1]]
+    return ev["H_dtdt"]
+
+
+def evaluate(layout: Layout, G0, Gd, Z, mu=None, want_jac=True, want_hess=True,
+             k_range=None):
+    """Whole-trajectory oracle evaluation in the native structure order.
+
+    G0: (S,d,d), Gd: (S,m,d,d).  Returns (delta, jac_vals, hess_vals); delta is
+    ordered [s][k][x_dim] (src/problem_templates/smooth_pulse_problem.jl:513 --
+    ``integrator.dim`` = x_dim*(N-1) per integrator).
+    """
+    L = layout
+    ks = range(L.K) if k_range is None else range(*k_range)
+    nk = len(ks)
+    delta = np.zeros(L.S * nk * L.x_dim)
+    jac = np.zeros(L.S * nk * L.jac_nnz_unit) if want_jac else None
+    hess = np.zeros(L.S * nk * L.hess_nnz_unit) if (want_hess and mu is not None) else None
+    for s in range(L.S):
+        jp = L.jac_unit_pattern(s) if want_jac else None
+        hp = L.hess_unit_pattern(s) if hess is not None else None
+        for ik, k in enumerate(ks):
+            X, Xn, M, u, dt = L.unit_inputs(Z, mu, s, k)
+            ev = unit_eval(G0[s], Gd[s], X, Xn, M, u, dt, want_hessian=hess is not None)
+            o = (s * nk + ik)
+            delta[o * L.x_dim:(o + 1) * L.x_dim] = ev["delta"].T.reshape(-1)
+            if want_jac:
+                jac[o * L.jac_nnz_unit:(o + 1) * L.jac_nnz_unit] = [_jac_value(e[2], ev) for e in jp]
+            if hess is not None:
+                hess[o * L.hess_nnz_unit:(o + 1) * L.hess_nnz_unit] = [_hess_value(e[2], ev) for e in hp]
+    return delta, jac, hess
+
+
+def defect_only(layout: Layout, G0, Gd, Z):
+    L = layout
+    delta = np.zeros(L.S * L.K * L.x_dim)
+    for s in range(L.S):
+        for k in range(L.K):
+            X, Xn, _, u, dt = L.unit_inputs(Z, None, s, k)
+            G = G0[s] + np.tensordot(u, Gd[s], axes=1)
+            o = s * L.K + k
+            delta[o * L.x_dim:(o + 1) * L.x_dim] = (Xn - expm(dt * G) @ X).T.reshape(-1)
+    return delta
+
+
+# --------------------------------------------------------------------------- #
+# Terminal fidelities (src/quantum_objectives.jl) -- value, gradient, Hessian
+# --------------------------------------------------------------------------- #
+
+KIND_UNITARY = 0        # unitary_fidelity_loss, src/quantum_objectives.jl:173-180
+KIND_KET = 1            # ket_fidelity_loss, :21-27
+KIND_COHERENT_KET = 2   # coherent_ket_fidelity, :88-103
+KIND_UNITARY_SUBSPACE = 3  # EmbeddedOperator variant, :182-191
+
+
+def unitary_fidelity(x, U_goal):
+    U = iso_vec_to_operator(x)
+    n = U.shape[0]
+    return abs(np.trace(U_goal.conj().T @ U)) ** 2 / n ** 2
+
+
+def unitary_subspace_fidelity(x, U_goal_sub, subspace):
+    U = iso_vec_to_operator(x)[np.ix_(subspace, subspace)]
+    n = len(subspace)
+    Mm = U_goal_sub.conj().T @ U
+    return (abs(np.trace(Mm.conj().T @ Mm)) + abs(np.trace(Mm)) ** 2) / (n * (n + 1))
+
+
+def ket_fidelity(x, psi_goal):
+    return abs(np.vdot(psi_goal, iso_to_ket(x))) ** 2
+
+
+def coherent_ket_fidelity(xs, goals):
+    n = len(xs)
+    return abs(sum(np.vdot(goals[i], iso_to_ket(xs[i])) for i in range(n)) / n) ** 2
+
+
+def fidelity_quadratic_form(kind, n_or_dim, goal, subspace=None):
+    """Every fidelity above is F(x) = sum_r (g_r . x)^2 * w for fixed real vectors g_r.
+
+    Returns (Gmat [R, x_dim], w).  unitary/ket/coherent: R = 2 (a, b); subspace: many rows.
+    """
+    if kind == KIND_UNITARY:
+        U_goal = np.asarray(goal, dtype=complex)
+        n = U_goal.shape[0]
+        ga = operator_to_iso_vec(U_goal)                       # Re tr(Ug^† U)
+        gb = operator_to_iso_vec(1j * U_goal)                  # Im tr(Ug^† U) = Re tr((iUg)^† U)
+        return np.array([ga, gb]), 1.0 / n ** 2
+    if kind == KIND_KET:
+        psi = np.asarray(goal, dtype=complex)
+        return np.array([ket_to_iso(psi), ket_to_iso(1j * psi)]), 1.0
+    if kind == KIND_COHERENT_KET:
+        goals = [np.asarray(g, dtype=complex) for g in goal]
+        n = len(goals)
+        ga = np.concatenate([ket_to_iso(g) for g in goals])
+        gb = np.concatenate([ket_to_iso(1j * g) for g in goals])
+        return np.array([ga, gb]), 1.0 / n ** 2
+    if kind == KIND_UNITARY_SUBSPACE:
+        Ug = np.asarray(goal, dtype=complex)
+        n_full = n_or_dim
+        ns = len(subspace)
+        rows = []
+        # |tr M|^2 with M = Ug^† U_sub: two rows; tr(M^†M) = ||U_sub||_F^2 for unitary Ug:
+        # in general ||Ug^† U_sub||_F^2 = sum over entries (Re^2 + Im^2) of M.
+        def embed(Vsub):
+            V = np.zeros((n_full, n_full), dtype=complex)
+            V[np.ix_(subspace, subspace)] = Vsub
+            return operator_to_iso_vec(V)
+        rows.append(embed(Ug))
+        rows.append(embed(1j * Ug))
+        # M[a,b] = sum_r conj(Ug[r,a]) U_sub[r,b]  -> Re and Im parts as linear forms
+        for a in range(ns):
+            for b in range(ns):
+                V = np.zeros((ns, ns), dtype=complex)
+                V[:, b] = Ug[:, a]
+                rows.append(embed(V))
+                rows.append(embed(1j * V))
+        return np.array(rows), 1.0 / (ns * (ns + 1))
+    raise ValueError(kind)
+
+
+def fidelity_vgh(kind, x, goal, n_full=None, subspace=None):
+    """F, grad F, Hess F (dense) from the quadratic form."""
+    Gm, w = fidelity_quadratic_form(kind, n_full, goal, subspace)
+    p = Gm @ x
+    F = w * float(p @ p)
+    g = 2 * w * (Gm.T @ p)
+    H = 2 * w * (Gm.T @ Gm)
+    return F, g, H
+
+
+# --------------------------------------------------------------------------- #
+# Finite-difference self-consistency (the reference's test_integrator criterion,
+# src/quantum_integrators.jl:194)
+# --------------------------------------------------------------------------- #
+
+
+def fd_check_unit(G0, Gd, X, Xn, M, u, dt, h=1e-6):
+    """max abs error of analytic Jacobian / Hessian blocks vs central differences."""
+    ev = unit_eval(G0, Gd, X, Xn, M, u, dt)
+    m = len(u)
+
+    def defect(uu, tt, XX):
+        G = G0 + np.tensordot(uu, Gd, axes=1)
+        return Xn - expm(tt * G) @ XX
+
+    errs = {}
+    ju = []
+    for j in range(m):
+        e = np.zeros(m); e[j] = h
+        ju.append((defect(u + e, dt, X) - defect(u - e, dt, X)) / (2 * h))
+    errs["J_u"] = max((np.abs(np.array(ju) - ev["J_u"]).max(),)) if m else 0.0
+    jt = (defect(u, dt + h, X) - defect(u, dt - h, X)) / (2 * h)
+    errs["J_dt"] = np.abs(jt - ev["J_dt"]).max()
+
+    def lag(uu, tt):
+        return np.sum(M * defect(uu, tt, X))
+
+    hh = 1e-4
+    Huu = np.zeros((m, m))
+    for i in range(m):
+        for j in range(m):
+            ei = np.zeros(m); ei[i] = hh
+            ej = np.zeros(m); ej[j] = hh
+            Huu[i, j] = (lag(u + ei + ej, dt) - lag(u + ei - ej, dt) - lag(u - ei + ej, dt) + lag(u - ei - ej, dt)) / (4 * hh * hh)
+    errs["H_uu"] = np.abs(Huu - ev["H_uu"]).max() if m else 0.0
+    Hut = np.zeros(m)
+    for j in range(m):
+        ej = np.zeros(m); ej[j] = hh
+        Hut[j] = (lag(u + ej, dt + hh) - lag(u + ej, dt - hh) - lag(u - ej, dt + hh) + lag(u - ej, dt - hh)) / (4 * hh * hh)
+    errs["H_udt"] = np.abs(Hut - ev["H_udt"]).max() if m else 0.0
+    Htt = (lag(u, dt + hh) - 2 * lag(u, dt) + lag(u, dt - hh)) / (hh * hh)
+    errs["H_dtdt"] = abs(Htt - ev["H_dtdt"])
+    # d/dX of (mu . J_u[j]) = H_xu[j]
+    return errs

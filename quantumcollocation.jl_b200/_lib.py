@@ -1,0 +1,81 @@
+"""ctypes loader of the product library ``csrc/libqcb200.so`` (the C ABI of include/qcb200.h).
+
+There is no fallback: if the library is missing or no CUDA device is usable, every
+evaluation entry point raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libqcb200.so")
+
+c_dp = ctypes.POINTER(ctypes.c_double)
+c_ip = ctypes.POINTER(ctypes.c_int32)
+c_lp = ctypes.POINTER(ctypes.c_int64)
+c_vp = ctypes.c_void_p
+
+
+class QcbDesc(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in (
+        "struct_bytes", "d", "c", "m", "N", "S", "z_dim", "u_off", "dt_off", "jac_mode", "device",
+        "k_begin", "k_end", "force_path")] + [
+        ("x_off", c_ip), ("G_drift", c_dp), ("G_drives", c_dp)]
+
+
+STATUS = {0: "QCB_OK", 1: "QCB_ERR_ARG", 2: "QCB_ERR_CUDA", 3: "QCB_ERR_RANGE", 4: "QCB_ERR_STRUCTURE", 5: "QCB_ERR_NOMEM"}
+
+# every symbol include/qcb200.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "qcb_create": (ctypes.c_int, [ctypes.POINTER(c_vp), ctypes.POINTER(QcbDesc)]),
+    "qcb_destroy": (None, [c_vp]),
+    "qcb_last_error": (ctypes.c_char_p, [c_vp]),
+    "qcb_version": (ctypes.c_char_p, []),
+    "qcb_defect_dim": (ctypes.c_int64, [c_vp]),
+    "qcb_jacobian_nnz": (ctypes.c_int64, [c_vp]),
+    "qcb_hessian_nnz": (ctypes.c_int64, [c_vp]),
+    "qcb_jacobian_structure": (ctypes.c_int, [c_vp, ctypes.c_int64, c_lp, c_lp]),
+    "qcb_hessian_structure": (ctypes.c_int, [c_vp, c_lp, c_lp]),
+    "qcb_set_structure": (ctypes.c_int, [c_vp, ctypes.c_int64, c_lp, c_lp, ctypes.c_int64, c_lp, c_lp, ctypes.c_int64]),
+    "qcb_eval_defect": (ctypes.c_int, [c_vp, c_vp, c_vp]),
+    "qcb_eval_jacobian": (ctypes.c_int, [c_vp, c_vp, c_vp]),
+    "qcb_eval_hessian": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp]),
+    "qcb_eval_all": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "qcb_eval_all_device": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "qcb_host_alloc": (ctypes.c_int, [ctypes.POINTER(c_vp), ctypes.c_size_t]),
+    "qcb_host_free": (None, [c_vp]),
+    "qcb_kernel_launches": (ctypes.c_int64, [c_vp]),
+    "qcb_get_timings": (ctypes.c_int, [c_vp, c_dp]),
+    "qcb_stream": (c_vp, [c_vp]),
+    "qcb_fidelity_create": (ctypes.c_int, [ctypes.POINTER(c_vp), ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                           c_dp, c_ip, ctypes.c_int32, ctypes.c_int32]),
+    "qcb_fidelity_destroy": (None, [c_vp]),
+    "qcb_fidelity_x_dim": (ctypes.c_int64, [c_vp]),
+    "qcb_fidelity_eval": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp]),
+}
+
+_lib = None
+
+
+class QcbError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__(f"{STATUS.get(status, status)}: {message}")
+        self.status = status
+
+
+def load():
+    """Load libqcb200.so and bind every declared symbol.  Raises if the library is absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `make -C {os.path.dirname(LIB_PATH)}` "
+                "(or __graft_entry__.build()).  There is no CPU fallback.")
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(lib, name)   # AttributeError if the symbol is not exported
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib

@@ -1,0 +1,215 @@
+"""Thin object layer over the C ABI: one ``Evaluator`` per integrator set (handle)."""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import numpy as np
+
+from . import _lib
+from .layout import KnotLayout
+
+
+def _ptr(a):
+    """Raw address of a numpy array / torch tensor / int / None."""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return a
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    return a.data_ptr()   # torch tensor
+
+
+def _colmajor(M):
+    """[..., d, d] row-major numpy (M[r, c]) -> contiguous buffer holding column-major matrices."""
+    return np.ascontiguousarray(np.swapaxes(np.asarray(M, dtype=np.float64), -1, -2))
+
+
+class Evaluator:
+    """Owns a ``qcb_handle``: defect / Jacobian / Hessian-of-Lagrangian values of a bilinear
+    integrator set on one GPU, for the interval slab ``[k_begin, k_end)``."""
+
+    def __init__(self, layout: KnotLayout, G_drift, G_drives, device: int = 0,
+                 k_begin: int = 0, k_end: int = 0, force_path: int = 0):
+        self.lib = _lib.load()
+        self.layout = L = layout
+        G_drift = np.asarray(G_drift, dtype=np.float64).reshape(L.S, L.d, L.d)
+        G_drives = np.asarray(G_drives, dtype=np.float64).reshape(L.S, L.m, L.d, L.d)
+        self._g0 = _colmajor(G_drift)
+        self._gd = _colmajor(G_drives) if L.m else np.zeros(1)
+        self._xo = np.asarray(L.x_off, dtype=np.int32)
+        desc = _lib.QcbDesc(
+            struct_bytes=ctypes.sizeof(_lib.QcbDesc), d=L.d, c=L.c, m=L.m, N=L.N, S=L.S, z_dim=L.z_dim,
+            u_off=L.u_off, dt_off=L.dt_off, jac_mode=L.jac_mode, device=device, k_begin=k_begin, k_end=k_end,
+            force_path=force_path,
+            x_off=self._xo.ctypes.data_as(_lib.c_ip), G_drift=self._g0.ctypes.data_as(_lib.c_dp),
+            G_drives=self._gd.ctypes.data_as(_lib.c_dp))
+        h = ctypes.c_void_p()
+        st = self.lib.qcb_create(ctypes.byref(h), ctypes.byref(desc))
+        if st != 0:
+            raise _lib.QcbError(st, self.lib.qcb_last_error(None).decode())
+        self.h = h
+        self.k_begin = k_begin
+        self.k_end = k_end or L.K
+
+    # -- sizes --
+    @property
+    def defect_dim(self) -> int:
+        return self.lib.qcb_defect_dim(self.h)
+
+    @property
+    def jacobian_nnz(self) -> int:
+        return self.lib.qcb_jacobian_nnz(self.h)
+
+    @property
+    def hessian_nnz(self) -> int:
+        return self.lib.qcb_hessian_nnz(self.h)
+
+    @property
+    def kernel_launches(self) -> int:
+        return self.lib.qcb_kernel_launches(self.h)
+
+    @property
+    def stream(self) -> int:
+        return self.lib.qcb_stream(self.h) or 0
+
+    def _check(self, st):
+        if st != 0:
+            raise _lib.QcbError(st, self.lib.qcb_last_error(self.h).decode())
+
+    # -- structure --
+    def jacobian_structure(self, row_base: int = 0):
+        n = self.jacobian_nnz
+        rows, cols = np.empty(n, dtype=np.int64), np.empty(n, dtype=np.int64)
+        self._check(self.lib.qcb_jacobian_structure(self.h, row_base, rows.ctypes.data_as(_lib.c_lp), cols.ctypes.data_as(_lib.c_lp)))
+        return rows, cols
+
+    def hessian_structure(self):
+        n = self.hessian_nnz
+        rows, cols = np.empty(n, dtype=np.int64), np.empty(n, dtype=np.int64)
+        self._check(self.lib.qcb_hessian_structure(self.h, rows.ctypes.data_as(_lib.c_lp), cols.ctypes.data_as(_lib.c_lp)))
+        return rows, cols
+
+    def set_structure(self, jac=None, hess=None, row_base: int = 0):
+        def pr(t):
+            if t is None:
+                return None, None, 0
+            r = np.ascontiguousarray(t[0], dtype=np.int64)
+            c = np.ascontiguousarray(t[1], dtype=np.int64)
+            return r, c, len(r)
+        jr, jc, jn = pr(jac)
+        hr, hc, hn = pr(hess)
+        p = lambda a: None if a is None else a.ctypes.data_as(_lib.c_lp)
+        self._check(self.lib.qcb_set_structure(self.h, row_base, p(jr), p(jc), jn, p(hr), p(hc), hn))
+
+    # -- evaluation with host buffers --
+    def eval_all(self, Z, mu=None, delta=None, jac=None, hess=None, want_jac=True, want_hess=True):
+        """Returns (delta, jac_vals, hess_vals) numpy arrays (caller may pass preallocated ones)."""
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        if mu is not None:
+            mu = np.ascontiguousarray(mu, dtype=np.float64)
+        if delta is None:
+            delta = np.empty(self.defect_dim)
+        if jac is None and want_jac:
+            jac = np.empty(self.jacobian_nnz)
+        if hess is None and want_hess and mu is not None:
+            hess = np.empty(self.hessian_nnz)
+        self._check(self.lib.qcb_eval_all(self.h, _ptr(Z), _ptr(mu), _ptr(delta), _ptr(jac), _ptr(hess)))
+        return delta, jac, hess
+
+    def eval_all_raw(self, Z, mu, delta, jac, hess):
+        """Pointer-level call (numpy arrays, pinned torch tensors or raw addresses)."""
+        self._check(self.lib.qcb_eval_all(self.h, _ptr(Z), _ptr(mu), _ptr(delta), _ptr(jac), _ptr(hess)))
+
+    def eval_defect(self, Z, delta=None):
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        delta = np.empty(self.defect_dim) if delta is None else delta
+        self._check(self.lib.qcb_eval_defect(self.h, _ptr(Z), _ptr(delta)))
+        return delta
+
+    def eval_jacobian(self, Z, jac=None):
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        jac = np.empty(self.jacobian_nnz) if jac is None else jac
+        self._check(self.lib.qcb_eval_jacobian(self.h, _ptr(Z), _ptr(jac)))
+        return jac
+
+    def eval_hessian(self, Z, mu, hess=None):
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        mu = np.ascontiguousarray(mu, dtype=np.float64)
+        hess = np.empty(self.hessian_nnz) if hess is None else hess
+        self._check(self.lib.qcb_eval_hessian(self.h, _ptr(Z), _ptr(mu), _ptr(hess)))
+        return hess
+
+    # -- evaluation with device buffers (torch CUDA tensors or raw device addresses) --
+    def eval_all_device(self, dZ, dmu, d_delta, d_jac, d_hess):
+        self._check(self.lib.qcb_eval_all_device(self.h, _ptr(dZ), _ptr(dmu), _ptr(d_delta), _ptr(d_jac), _ptr(d_hess)))
+
+    def timings(self):
+        ms = (ctypes.c_double * 4)()
+        self.lib.qcb_get_timings(self.h, ms)
+        return {"h2d_ms": ms[0], "kernels_ms": ms[1], "d2h_ms": ms[2], "total_ms": ms[3]}
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.qcb_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Fidelity:
+    """Terminal fidelity F(x_N) and its derivatives on the GPU (include/qcb200.h, qcb_fidelity_*)."""
+    UNITARY, KET, COHERENT_KET, UNITARY_SUBSPACE = 0, 1, 2, 3
+
+    def __init__(self, kind: int, goal, n: Optional[int] = None, subspace=None, device: int = 0):
+        self.lib = _lib.load()
+        goal = np.asarray(goal, dtype=complex)
+        if kind == self.UNITARY:
+            n = goal.shape[0]; count = 1
+            flat = goal.T.reshape(-1)
+        elif kind == self.KET:
+            n = goal.shape[0]; count = 1
+            flat = goal.reshape(-1)
+        elif kind == self.COHERENT_KET:
+            count, n = goal.shape
+            flat = goal.reshape(-1)
+        else:
+            count = 1
+            flat = goal.T.reshape(-1)
+        gi = np.ascontiguousarray(np.stack([flat.real, flat.imag], axis=-1).reshape(-1))
+        sub = None if subspace is None else np.asarray(subspace, dtype=np.int32)
+        h = ctypes.c_void_p()
+        st = self.lib.qcb_fidelity_create(ctypes.byref(h), kind, n, count, gi.ctypes.data_as(_lib.c_dp),
+                                          None if sub is None else sub.ctypes.data_as(_lib.c_ip),
+                                          0 if sub is None else len(sub), device)
+        if st != 0:
+            raise _lib.QcbError(st, self.lib.qcb_last_error(None).decode())
+        self.h = h
+        self.x_dim = self.lib.qcb_fidelity_x_dim(h)
+
+    def eval(self, x, want_grad=True, want_hess=False):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        assert x.shape == (self.x_dim,)
+        F = np.zeros(1)
+        g = np.empty(self.x_dim) if want_grad else None
+        H = np.empty((self.x_dim, self.x_dim)) if want_hess else None
+        st = self.lib.qcb_fidelity_eval(self.h, _ptr(x), _ptr(F), _ptr(g), _ptr(H))
+        if st != 0:
+            raise _lib.QcbError(st, "fidelity evaluation failed")
+        return float(F[0]), g, H
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.qcb_fidelity_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

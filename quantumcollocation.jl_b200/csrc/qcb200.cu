@@ -1,0 +1,859 @@
+// qcb200.cu -- C ABI + host executor of the B200-native collocation evaluator.
+// See include/qcb200.h for the contract and DESIGN.md for the architecture.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/qcb200.h"
+#include "qcb_program.h"
+#include "qcb_large.cuh"
+#include "qcb_small.cuh"
+
+using namespace qcb;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct CudaFail { cudaError_t e; const char *what; int line; };
+#define CK(call)                                                         \
+    do {                                                                 \
+        cudaError_t e_ = (call);                                         \
+        if (e_ != cudaSuccess) throw CudaFail{e_, #call, __LINE__};      \
+    } while (0)
+
+struct Entry { int64_t row, col; uint32_t code; };
+
+inline int round_up(int v, int q) { return (v + q - 1) / q * q; }
+
+}  // namespace
+
+struct qcb_handle_s {
+    // geometry
+    int d = 0, c = 0, m = 0, N = 0, S = 1, K = 0, z_dim = 0, u_off = 0, dt_off = 0, jac_mode = 0;
+    int k0 = 0, k1 = 0, nk = 0, units = 0, xdim = 0;
+    int dp = 0, cp = 0;            // padded dims of the device matrices / panels
+    bool large = false;
+    int device = 0, n_sm = 148;
+    std::vector<int> x_off;
+    std::string err;
+    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    std::vector<cudaEvent_t> chunk_events;
+    int64_t launches = 0;
+    double ms[4] = {0, 0, 0, 0};
+
+    // device constants
+    double *dG0 = nullptr, *dGd = nullptr;
+    int *d_xoff = nullptr;
+    uint32_t *d_jcode = nullptr, *d_hcode = nullptr;   // [S][nnz]
+    int64_t jnnz_unit = 0, hnnz_unit = 0;
+    int64_t JA = 0, HA = 0;                            // arena strides (doubles)
+    bool custom_j = false, custom_h = false;
+    unsigned long long *d_norm = nullptr;
+    int *d_bad = nullptr;
+
+    // staging for the host-buffer API
+    double *dZ = nullptr, *dmu = nullptr;
+    double *d_delta = nullptr, *d_jac = nullptr, *d_hess = nullptr;
+
+    // large-path scratch
+    int chunk_units = 0, s_cap = -1;
+    double *sc_fixed = nullptr, *sc_E = nullptr, *sc_W = nullptr, *sc_dslot = nullptr, *sc_L[2] = {nullptr, nullptr};
+    double *sc_XP = nullptr, *sc_MP = nullptr, *sc_EX = nullptr, *sc_ja = nullptr, *sc_ha = nullptr;
+    double *sc_H = nullptr, *sc_c1 = nullptr, *sc_c2 = nullptr, *sc_c3 = nullptr, *sc_tau = nullptr, *sc_ntau = nullptr;
+    int small_threads = 0;
+
+    UnitGeom geom() const {
+        UnitGeom q;
+        q.d = d; q.c = c; q.m = m; q.dp = dp; q.cp = cp; q.z_dim = z_dim; q.u_off = u_off; q.dt_off = dt_off;
+        q.K = K; q.nk = nk; q.k_begin = k0; q.S = S; q.x_off = d_xoff; q.G0 = dG0; q.Gd = dGd;
+        return q;
+    }
+};
+
+namespace {
+
+// ---------------------------------------------------------------------------------------
+// Native structure patterns and slot codes
+// ---------------------------------------------------------------------------------------
+struct Codes {
+    qcb_handle_s *h;
+    int64_t dd() const { return (int64_t)h->dp * h->dp; }
+    int64_t pan() const { return (int64_t)h->dp * h->cp; }
+    uint32_t jE(int rr, int qq) const { return (uint32_t)(rr + (int64_t)qq * h->dp) | QCB_CODE_NEG; }
+    uint32_t jU(int j, int i) const { return (uint32_t)(dd() + j * pan() + (i % h->d) + (int64_t)(i / h->d) * h->dp); }
+    uint32_t jT(int i) const { return jU(h->m, i); }
+    uint32_t jZero() const { return (uint32_t)(dd() + (h->m + 1) * pan()); }
+    uint32_t jOne() const { return jZero() + 1; }
+    uint32_t hXU(int j, int i) const { return (uint32_t)(j * pan() + (i % h->d) + (int64_t)(i / h->d) * h->dp); }
+    uint32_t hXT(int i) const { return hXU(h->m, i); }
+    uint32_t hUU(int i, int j) const { return (uint32_t)((h->m + 1) * pan() + i * h->m + j); }
+    uint32_t hUT(int j) const { return (uint32_t)((h->m + 1) * pan() + h->m * h->m + j); }
+    uint32_t hTT() const { return hUT(h->m); }
+    uint32_t hZero() const { return hTT() + 1; }
+};
+
+// per-unit native Jacobian pattern of system s: local row, local col in [z_k; z_{k+1}], code;
+// sorted by (col, row) -- the order Julia's findnz gives for a sparse block.
+std::vector<Entry> jac_pattern(qcb_handle_s *h, int s) {
+    Codes cd{h};
+    const int d = h->d, xd = h->xdim, m = h->m;
+    std::vector<Entry> v;
+    v.reserve((size_t)h->jnnz_unit);
+    for (int q = 0; q < xd; ++q) {
+        const int b = q / d, qq = q % d;
+        const int64_t col = h->x_off[s] + q;
+        if (h->jac_mode == QCB_JAC_DENSE_X) {
+            for (int r = 0; r < xd; ++r)
+                v.push_back({r, col, (r / d == b) ? cd.jE(r % d, qq) : cd.jZero()});
+        } else {
+            for (int rr = 0; rr < d; ++rr) v.push_back({(int64_t)b * d + rr, col, cd.jE(rr, qq)});
+        }
+    }
+    for (int j = 0; j < m; ++j)
+        for (int r = 0; r < xd; ++r) v.push_back({r, (int64_t)h->u_off + j, cd.jU(j, r)});
+    for (int r = 0; r < xd; ++r) v.push_back({r, (int64_t)h->dt_off, cd.jT(r)});
+    for (int r = 0; r < xd; ++r) v.push_back({r, (int64_t)h->z_dim + h->x_off[s] + r, cd.jOne()});
+    std::stable_sort(v.begin(), v.end(), [](const Entry &a, const Entry &b) {
+        return a.col != b.col ? a.col < b.col : a.row < b.row;
+    });
+    return v;
+}
+
+std::vector<Entry> hess_pattern(qcb_handle_s *h, int s) {
+    Codes cd{h};
+    const int xd = h->xdim, m = h->m;
+    std::vector<Entry> v;
+    v.reserve((size_t)h->hnnz_unit);
+    auto add = [&](int64_t a, int64_t b, uint32_t code) { v.push_back({std::min(a, b), std::max(a, b), code}); };
+    for (int j = 0; j < m; ++j)
+        for (int i = 0; i < xd; ++i) add(h->x_off[s] + i, h->u_off + j, cd.hXU(j, i));
+    for (int i = 0; i < xd; ++i) add(h->x_off[s] + i, h->dt_off, cd.hXT(i));
+    for (int i = 0; i < m; ++i)
+        for (int j = i; j < m; ++j) add(h->u_off + i, h->u_off + j, cd.hUU(i, j));
+    for (int j = 0; j < m; ++j) add(h->u_off + j, h->dt_off, cd.hUT(j));
+    add(h->dt_off, h->dt_off, cd.hTT());
+    std::stable_sort(v.begin(), v.end(), [](const Entry &a, const Entry &b) {
+        return a.col != b.col ? a.col < b.col : a.row < b.row;
+    });
+    return v;
+}
+
+void upload_codes(qcb_handle_s *h, uint32_t **dptr, const std::vector<uint32_t> &codes) {
+    if (*dptr) { CK(cudaFree(*dptr)); *dptr = nullptr; }
+    CK(cudaMalloc(dptr, codes.size() * sizeof(uint32_t)));
+    CK(cudaMemcpy(*dptr, codes.data(), codes.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+}
+
+void build_native_codes(qcb_handle_s *h, bool jac, bool hess) {
+    if (jac) {
+        std::vector<uint32_t> codes;
+        for (int s = 0; s < h->S; ++s)
+            for (auto &e : jac_pattern(h, s)) codes.push_back(e.code);
+        upload_codes(h, &h->d_jcode, codes);
+        h->custom_j = false;
+    }
+    if (hess) {
+        std::vector<uint32_t> codes;
+        for (int s = 0; s < h->S; ++s)
+            for (auto &e : hess_pattern(h, s)) codes.push_back(e.code);
+        upload_codes(h, &h->d_hcode, codes);
+        h->custom_h = false;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Launch helpers
+// ---------------------------------------------------------------------------------------
+template <int BM, int BN, int WM, int WN, int STAGES>
+void launch_gemm_cfg(qcb_handle_s *h, const GemmArgs &g, int batch) {
+    static bool attr_set[64] = {false};
+    auto kern = bgemm_kernel<BM, BN, WM, WN, STAGES>;
+    const size_t smem = GemmSmem<BM, BN>::bytes(STAGES);
+    if (!attr_set[h->device]) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set[h->device] = true;
+    }
+    const int tiles = (g.M / BM) * (g.N / BN);
+    const int threads = (BM / WM) * (BN / WN) * 32;
+    kern<<<(unsigned)(batch * tiles), threads, smem, h->stream>>>(g);
+    ++h->launches;
+}
+
+void launch_gemm(qcb_handle_s *h, GemmArgs &g, int units) {
+    const int batch = units * g.ndir;
+    const bool big_ok = (g.M % 128 == 0) && (g.N % 128 == 0);
+    if (big_ok && (long long)batch * (g.M / 128) * (g.N / 128) >= 2LL * h->n_sm)
+        launch_gemm_cfg<128, 128, 64, 32, 4>(h, g, batch);
+    else
+        launch_gemm_cfg<64, 64, 32, 32, 4>(h, g, batch);
+    CK(cudaGetLastError());
+}
+
+struct LargeExec {
+    qcb_handle_s *h;
+    int nu;        // units in this chunk
+    int u0;        // slab-local index of the chunk's first unit
+    int s;         // squarings (uniform)
+    int level = 0;
+    int cur = 0;   // which L buffer holds the current level
+    long long dd, pan;
+
+    Opnd mat(double *base, long long su, long long sd = 0, long long ss = 0) const {
+        Opnd o; o.p = base; o.su = su; o.sd = sd; o.ss = ss; o.ld = h->dp; o.pad_ = 0; return o;
+    }
+    Opnd E(int lvl) const {
+        if (lvl == s) return mat(h->sc_ja, h->JA);
+        return mat(h->sc_E + (long long)lvl * h->chunk_units * dd, dd);
+    }
+    Opnd W(int lvl) const { return mat(h->sc_W + (long long)lvl * h->chunk_units * dd, dd); }
+    Opnd fixed(int r) const { return mat(h->sc_fixed + (long long)r * h->chunk_units * dd, dd); }
+    Opnd reg(int r) const {
+        if (r < QR_NUM_FIXED) return fixed(r);
+        switch (r) {
+        case QR_EL: return E(level);
+        case QR_EL1: return E(level + 1);
+        case QR_WL: return W(level);
+        case QR_WL1: return W(level + 1);
+        case QR_E0: return E(0);
+        case QR_W0: return W(0);
+        case QR_GJ: return mat(h->dGd, 0, dd, (long long)h->m * dd);
+        case QR_L: return mat(h->sc_L[cur], (long long)h->m * dd, dd);
+        case QR_LN: return mat(h->sc_L[cur ^ 1], (long long)h->m * dd, dd);
+        default: return mat(h->sc_dslot + (long long)qcb_dslot(r) * h->chunk_units * h->m * dd, (long long)h->m * dd, dd);
+        }
+    }
+    GemmArgs base_args(int ndir) const {
+        GemmArgs g;
+        memset(&g, 0, sizeof(g));
+        g.M = g.N = g.K = h->dp;
+        g.d_ident = h->d;
+        g.alpha = 1.0;
+        g.ndir = ndir;
+        g.unit0_global = u0;
+        g.nk = h->nk;
+        return g;
+    }
+    void run(const qcb_op &op, int ndir) {
+        GemmArgs g = base_args(ndir);
+        g.nterm = op.nterm;
+        g.nlin = op.nlin;
+        for (int t = 0; t < op.nterm; ++t) {
+            g.term[t].a = reg(op.term[t].a);
+            g.term[t].b = reg(op.term[t].b);
+            g.term[t].ta = op.term[t].ta;
+            g.term[t].tb = op.term[t].tb;
+        }
+        for (int l = 0; l < op.nlin; ++l) {
+            g.lin[l] = reg(op.lin[l].reg);
+            g.lin_coef[l] = QCB_TAYLOR[op.lin[l].coef];
+        }
+        g.ident = op.ident >= 0 ? QCB_TAYLOR[op.ident] : 0.0;
+        g.dst = reg(op.dst);
+        launch_gemm(h, g, nu);
+    }
+    // dst = alpha * [scale] * op(a) * op(b), general shapes
+    void product(Opnd dst, Opnd a, int ta, Opnd b, int tb, int M, int N, int Kd, int ndir, double alpha,
+                 const double *unit_scale) {
+        GemmArgs g = base_args(ndir);
+        g.M = M; g.N = N; g.K = Kd;
+        g.d_ident = 0;
+        g.nterm = 1;
+        g.term[0].a = a; g.term[0].b = b; g.term[0].ta = ta; g.term[0].tb = tb;
+        g.alpha = alpha;
+        g.unit_scale = unit_scale;
+        g.dst = dst;
+        launch_gemm(h, g, nu);
+    }
+    void contract(Opnd P, int nj, Opnd Q, int ni, double *out, int accumulate) {
+        ContractArgs a;
+        a.P = P; a.Q = Q; a.nj = nj; a.ni = ni; a.nelem = dd; a.out = out; a.accumulate = accumulate;
+        a.unit0_global = u0; a.nk = h->nk;
+        contract_kernel<<<(unsigned)(nu * nj), 256, 0, h->stream>>>(a);
+        ++h->launches;
+        CK(cudaGetLastError());
+    }
+};
+
+void free_scratch(qcb_handle_s *h) {
+    double **ptrs[] = {&h->sc_fixed, &h->sc_E, &h->sc_W, &h->sc_dslot, &h->sc_L[0], &h->sc_L[1], &h->sc_XP, &h->sc_MP,
+                       &h->sc_EX, &h->sc_ja, &h->sc_ha, &h->sc_H, &h->sc_c1, &h->sc_c2, &h->sc_c3, &h->sc_tau, &h->sc_ntau};
+    for (auto p : ptrs)
+        if (*p) { cudaFree(*p); *p = nullptr; }
+    h->s_cap = -1;
+}
+
+size_t scratch_bytes_per_unit(const qcb_handle_s *h, int s_cap) {
+    const size_t dd = (size_t)h->dp * h->dp, pan = (size_t)h->dp * h->cp;
+    size_t n = (QR_NUM_FIXED + 2 * (size_t)(s_cap + 1) + (size_t)(QCB_NUM_DSLOTS + 2) * h->m) * dd;
+    n += 3 * pan + h->JA + h->HA + (size_t)h->m * h->m + 2 * h->m + 3;
+    return n * sizeof(double);
+}
+
+void ensure_scratch(qcb_handle_s *h, int s_need) {
+    if (h->s_cap >= s_need && h->sc_fixed) return;
+    free_scratch(h);
+    const int s_cap = std::max(s_need, 2);
+    size_t budget_mb = 6144;
+    if (const char *e = getenv("QCB_SCRATCH_MB")) budget_mb = (size_t)std::max(64L, atol(e));
+    const size_t per = scratch_bytes_per_unit(h, s_cap);
+    long long cu = (long long)((budget_mb << 20) / per);
+    cu = std::max(1LL, std::min<long long>(cu, h->units));
+    if (cu < h->units && cu * h->m > 2LL * h->n_sm) {
+        // pick the chunk size near the budget whose (unit x direction) batch fills whole waves best
+        long long best = cu;
+        double best_eff = 0;
+        for (long long t = cu; t > cu * 3 / 4 && t > 0; --t) {
+            long long ctas = t * std::max(1, h->m);
+            double eff = (double)ctas / (double)(((ctas + h->n_sm - 1) / h->n_sm) * h->n_sm);
+            if (eff > best_eff + 1e-9) { best_eff = eff; best = t; }
+        }
+        cu = best;
+    }
+    h->chunk_units = (int)cu;
+    const size_t dd = (size_t)h->dp * h->dp, pan = (size_t)h->dp * h->cp, n = (size_t)cu;
+    const size_t mm = std::max(1, h->m);
+    CK(cudaMalloc(&h->sc_fixed, QR_NUM_FIXED * n * dd * 8));
+    CK(cudaMalloc(&h->sc_E, (size_t)(s_cap + 1) * n * dd * 8));
+    CK(cudaMalloc(&h->sc_W, (size_t)(s_cap + 1) * n * dd * 8));
+    CK(cudaMalloc(&h->sc_dslot, (size_t)QCB_NUM_DSLOTS * n * mm * dd * 8));
+    CK(cudaMalloc(&h->sc_L[0], n * mm * dd * 8));
+    CK(cudaMalloc(&h->sc_L[1], n * mm * dd * 8));
+    CK(cudaMalloc(&h->sc_XP, n * pan * 8));
+    CK(cudaMalloc(&h->sc_MP, n * pan * 8));
+    CK(cudaMalloc(&h->sc_EX, n * pan * 8));
+    CK(cudaMalloc(&h->sc_ja, n * (size_t)h->JA * 8));
+    CK(cudaMalloc(&h->sc_ha, n * (size_t)h->HA * 8));
+    CK(cudaMalloc(&h->sc_H, n * mm * mm * 8));
+    CK(cudaMalloc(&h->sc_c1, n * mm * 8));
+    CK(cudaMalloc(&h->sc_c2, n * mm * 8));
+    CK(cudaMalloc(&h->sc_c3, n * 8));
+    CK(cudaMalloc(&h->sc_tau, n * 8));
+    CK(cudaMalloc(&h->sc_ntau, n * 8));
+    h->s_cap = s_cap;
+}
+
+struct HostOut { double *delta, *jac, *hess; };
+
+// norm pre-pass over the whole slab -> uniform number of squarings (or -1)
+int slab_squarings(qcb_handle_s *h, const double *dZ) {
+    CK(cudaMemsetAsync(h->d_norm, 0, sizeof(unsigned long long), h->stream));
+    CK(cudaMemsetAsync(h->d_bad, 0, sizeof(int), h->stream));
+    build_G_kernel<<<h->units, 256, 0, h->stream>>>(h->geom(), dZ, 0, nullptr, 0, h->d_norm, h->d_bad);
+    ++h->launches;
+    CK(cudaGetLastError());
+    unsigned long long bits = 0;
+    int bad = 0;
+    CK(cudaMemcpyAsync(&bits, h->d_norm, sizeof(bits), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(&bad, h->d_bad, sizeof(bad), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (bad) return -1;
+    double nrm;
+    memcpy(&nrm, &bits, sizeof(nrm));
+    return qcb_squarings(nrm);
+}
+
+void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_delta, double *d_jac,
+                double *d_hess, int want, const HostOut *host, int s) {
+    ensure_scratch(h, s);
+    const bool wj = want & 1, wh = (want & 2) && dmu;
+    const long long dd = (long long)h->dp * h->dp, pan = (long long)h->dp * h->cp;
+    const int m = h->m;
+    UnitGeom q = h->geom();
+    size_t chunk_idx = 0;
+    for (int u0 = 0; u0 < h->units; u0 += h->chunk_units, ++chunk_idx) {
+        const int nu = std::min(h->chunk_units, h->units - u0);
+        LargeExec X{h, nu, u0, s};
+        X.dd = dd; X.pan = pan;
+        Opnd G = X.fixed(QR_G), A = X.fixed(QR_A);
+        build_G_kernel<<<nu, 256, 0, h->stream>>>(q, dZ, u0, const_cast<double *>(G.p), dd, h->d_norm, h->d_bad);
+        ++h->launches;
+        prep_unit_kernel<<<nu, 256, 0, h->stream>>>(q, dZ, wh ? dmu : nullptr, u0, s, G.p, const_cast<double *>(A.p), dd,
+                                                     h->sc_XP, wh ? h->sc_MP : nullptr, pan, h->sc_tau, h->sc_ntau);
+        ++h->launches;
+        CK(cudaGetLastError());
+        Opnd XP = X.mat(h->sc_XP, pan), MP = X.mat(h->sc_MP, pan), EXp = X.mat(h->sc_EX, pan);
+        // polynomial + squarings
+        X.level = 0;
+        for (int i = 0; i < QCB_NOPS(QCB_P1); ++i) X.run(QCB_P1[i], 1);
+        for (int l = 0; l < s; ++l) { X.level = l; X.run(QCB_P2[0], 1); }
+        Opnd Ef = X.E(s);
+        // defect
+        X.product(EXp, Ef, 0, XP, 0, h->dp, h->cp, h->dp, 1, 1.0, nullptr);
+        delta_kernel<<<nu, 256, 0, h->stream>>>(q, dZ, h->sc_EX, pan, d_delta, u0);
+        ++h->launches;
+        if (wj || wh) {
+            if (wh) {
+                X.product(X.W(s), MP, 0, XP, 1, h->dp, h->dp, h->cp, 1, 1.0, nullptr);   // W = M X^T
+                for (int l = s - 1; l >= 0; --l) { X.level = l; X.run(QCB_P3[0], 1); }
+                X.level = 0;
+                for (int i = 0; i < QCB_NOPS(QCB_P4); ++i) X.run(QCB_P4[i], 1);
+            }
+            X.level = 0; X.cur = 0;
+            if (m > 0) {
+                for (int i = 0; i < QCB_NOPS(QCB_P5); ++i) X.run(QCB_P5[i], m);
+                if (wh) {
+                    for (int i = 0; i < QCB_NOPS(QCB_P6); ++i) X.run(QCB_P6[i], m);
+                    X.contract(X.reg(QR_DAB), m, X.reg(QR_GJ), m, h->sc_H, 0);
+                }
+                for (int l = 0; l < s; ++l) {
+                    X.level = l;
+                    if (wh) {
+                        X.run(QCB_P7S[0], m);
+                        X.contract(X.reg(QR_S), m, X.reg(QR_L), m, h->sc_H, 1);
+                    }
+                    X.run(QCB_P7L[0], m);
+                    X.cur ^= 1;
+                }
+            }
+            // final blocks
+            Opnd GE = X.fixed(QR_A2), WE = X.fixed(QR_A3), GW = X.fixed(QR_A4), L = X.reg(QR_L);
+            X.product(GE, G, 0, Ef, 0, h->dp, h->dp, h->dp, 1, 1.0, nullptr);
+            Opnd JU = X.mat(h->sc_ja + dd, h->JA, pan), JT = X.mat(h->sc_ja + dd + m * pan, h->JA);
+            if (m > 0) X.product(JU, L, 0, XP, 0, h->dp, h->cp, h->dp, m, 1.0, h->sc_ntau);
+            X.product(JT, GE, 0, XP, 0, h->dp, h->cp, h->dp, 1, -1.0, nullptr);
+            arena_consts_kernel<<<(nu + 127) / 128, 128, 0, h->stream>>>(h->sc_ja, h->JA, dd + (m + 1) * pan, nu);
+            ++h->launches;
+            if (wh) {
+                Opnd Wt = X.W(s);
+                Opnd HXU = X.mat(h->sc_ha, h->HA, pan), HXT = X.mat(h->sc_ha + m * pan, h->HA);
+                if (m > 0) X.product(HXU, L, 1, MP, 0, h->dp, h->cp, h->dp, m, 1.0, h->sc_ntau);
+                X.product(HXT, GE, 1, MP, 0, h->dp, h->cp, h->dp, 1, -1.0, nullptr);
+                X.product(WE, Wt, 0, Ef, 1, h->dp, h->dp, h->dp, 1, 1.0, nullptr);
+                X.product(GW, G, 1, Wt, 0, h->dp, h->dp, h->dp, 1, 1.0, nullptr);
+                if (m > 0) {
+                    X.contract(WE, 1, X.reg(QR_GJ), m, h->sc_c1, 0);
+                    X.contract(GW, 1, L, m, h->sc_c2, 0);
+                }
+                X.contract(GW, 1, GE, 1, h->sc_c3, 0);
+                finalize_scalars_kernel<<<nu, 64, 0, h->stream>>>(m, h->sc_tau, h->sc_H, h->sc_c1, h->sc_c2, h->sc_c3,
+                                                                  h->sc_ha, h->HA, (m + 1) * pan);
+                ++h->launches;
+            }
+            if (wj && d_jac) {
+                int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->jnnz_unit / 4096));
+                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(h->sc_ja, h->JA, h->d_jcode, h->jnnz_unit, d_jac, u0, h->nk, cpu);
+                ++h->launches;
+            }
+            if (wh && d_hess) {
+                int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->hnnz_unit / 4096));
+                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(h->sc_ha, h->HA, h->d_hcode, h->hnnz_unit, d_hess, u0, h->nk, cpu);
+                ++h->launches;
+            }
+        }
+        CK(cudaGetLastError());
+        if (host) {   // stream this chunk's results to the host while the next chunk computes
+            if (h->chunk_events.size() <= chunk_idx) {
+                cudaEvent_t e;
+                CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                h->chunk_events.push_back(e);
+            }
+            CK(cudaEventRecord(h->chunk_events[chunk_idx], h->stream));
+            CK(cudaStreamWaitEvent(h->copy_stream, h->chunk_events[chunk_idx], 0));
+            if (host->delta)
+                CK(cudaMemcpyAsync(host->delta + (size_t)u0 * h->xdim, d_delta + (size_t)u0 * h->xdim,
+                                   (size_t)nu * h->xdim * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+            if (wj && host->jac)
+                CK(cudaMemcpyAsync(host->jac + (size_t)u0 * h->jnnz_unit, d_jac + (size_t)u0 * h->jnnz_unit,
+                                   (size_t)nu * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+            if (wh && host->hess)
+                CK(cudaMemcpyAsync(host->hess + (size_t)u0 * h->hnnz_unit, d_hess + (size_t)u0 * h->hnnz_unit,
+                                   (size_t)nu * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+        }
+    }
+}
+
+void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_delta, double *d_jac,
+                double *d_hess, int want, int s) {
+    SmallParams p;
+    p.d = h->d; p.c = h->c; p.m = h->m; p.z_dim = h->z_dim; p.u_off = h->u_off; p.dt_off = h->dt_off;
+    p.K = h->K; p.nk = h->nk; p.k_begin = h->k0; p.S = h->S;
+    p.x_off = h->d_xoff; p.G0 = h->dG0; p.Gd = h->dGd; p.Z = dZ; p.mu = dmu;
+    p.delta = d_delta; p.jac = d_jac; p.hess = d_hess;
+    p.jcode = h->d_jcode; p.hcode = h->d_hcode; p.jnnz = h->jnnz_unit; p.hnnz = h->hnnz_unit;
+    p.want = want; p.smax = s; p.bad_flag = h->d_bad;
+    const size_t smem = small_smem_doubles(h->d, h->c, h->m, s) * sizeof(double);
+    if (smem > 227 * 1024) throw CudaFail{cudaErrorInvalidValue, "small-path shared memory exceeds 227 KB", __LINE__};
+    CK(cudaFuncSetAttribute(small_unit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    small_unit_kernel<<<h->units, h->small_threads, smem, h->stream>>>(p);
+    ++h->launches;
+    CK(cudaGetLastError());
+}
+
+// common driver: device inputs -> device outputs (+ optional streamed host outputs)
+qcb_status eval_device(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_delta, double *d_jac,
+                       double *d_hess, int want, const HostOut *host) {
+    const int s = slab_squarings(h, dZ);
+    if (s < 0) {
+        h->err = "non-finite input or ||dt*G(u)||_1 beyond the supported range";
+        return QCB_ERR_RANGE;
+    }
+    if (h->large) {
+        eval_large(h, dZ, dmu, d_delta, d_jac, d_hess, want, host, s);
+    } else {
+        eval_small(h, dZ, dmu, d_delta, d_jac, d_hess, want, s);
+        if (host) {
+            CK(cudaEventRecord(h->ev[4], h->stream));
+            CK(cudaStreamWaitEvent(h->copy_stream, h->ev[4], 0));
+            if (host->delta)
+                CK(cudaMemcpyAsync(host->delta, d_delta, (size_t)h->units * h->xdim * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+            if ((want & 1) && host->jac)
+                CK(cudaMemcpyAsync(host->jac, d_jac, (size_t)h->units * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+            if ((want & 2) && host->hess)
+                CK(cudaMemcpyAsync(host->hess, d_hess, (size_t)h->units * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+        }
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    if (host) CK(cudaStreamSynchronize(h->copy_stream));
+    int bad = 0;
+    CK(cudaMemcpy(&bad, h->d_bad, sizeof(int), cudaMemcpyDeviceToHost));
+    if (bad) {
+        h->err = "non-finite input or ||dt*G(u)||_1 beyond the supported range";
+        return QCB_ERR_RANGE;
+    }
+    return QCB_OK;
+}
+
+qcb_status fail(qcb_handle_s *h, qcb_status st, const std::string &msg) {
+    if (h) h->err = msg; else g_create_error = msg;
+    return st;
+}
+qcb_status fail_cuda(qcb_handle_s *h, const CudaFail &f) {
+    char buf[512];
+    snprintf(buf, sizeof buf, "CUDA error '%s' in %s (qcb200.cu:%d)", cudaGetErrorString(f.e), f.what, f.line);
+    cudaGetLastError();
+    return fail(h, f.e == cudaErrorMemoryAllocation ? QCB_ERR_NOMEM : QCB_ERR_CUDA, buf);
+}
+
+void init_constants() {
+    CK(cudaMemcpyToSymbol(c_P1, QCB_P1, sizeof(QCB_P1)));
+    CK(cudaMemcpyToSymbol(c_P2, QCB_P2, sizeof(QCB_P2)));
+    CK(cudaMemcpyToSymbol(c_P3, QCB_P3, sizeof(QCB_P3)));
+    CK(cudaMemcpyToSymbol(c_P4, QCB_P4, sizeof(QCB_P4)));
+    CK(cudaMemcpyToSymbol(c_P5, QCB_P5, sizeof(QCB_P5)));
+    CK(cudaMemcpyToSymbol(c_P6, QCB_P6, sizeof(QCB_P6)));
+    CK(cudaMemcpyToSymbol(c_P7S, QCB_P7S, sizeof(QCB_P7S)));
+    CK(cudaMemcpyToSymbol(c_P7L, QCB_P7L, sizeof(QCB_P7L)));
+    CK(cudaMemcpyToSymbol(c_taylor, QCB_TAYLOR, sizeof(QCB_TAYLOR)));
+}
+
+void ensure_out(qcb_handle_s *h, double **p, size_t n) {
+    if (!*p) CK(cudaMalloc(p, std::max<size_t>(n, 1) * sizeof(double)));
+}
+
+}  // namespace
+
+// =========================================================================================
+// C ABI
+// =========================================================================================
+extern "C" {
+
+const char *qcb_version(void) { return "qcb200 0.1.0 (sm_100a)"; }
+
+const char *qcb_last_error(qcb_handle h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+qcb_status qcb_create(qcb_handle *out, const qcb_desc *desc) {
+    if (!out || !desc) return fail(nullptr, QCB_ERR_ARG, "null argument");
+    *out = nullptr;
+    if (desc->struct_bytes != (int32_t)sizeof(qcb_desc)) return fail(nullptr, QCB_ERR_ARG, "qcb_desc.struct_bytes mismatch");
+    if (desc->d < 1 || desc->c < 1 || desc->m < 0 || desc->N < 2 || desc->S < 1 || desc->z_dim < 1)
+        return fail(nullptr, QCB_ERR_ARG, "bad dimensions in qcb_desc");
+    if (desc->m > CONTRACT_MAXI) return fail(nullptr, QCB_ERR_ARG, "more than 32 drives are not supported");
+    if (!desc->x_off || !desc->G_drift || (desc->m > 0 && !desc->G_drives))
+        return fail(nullptr, QCB_ERR_ARG, "null array in qcb_desc");
+    if (desc->jac_mode != QCB_JAC_DENSE_X && desc->jac_mode != QCB_JAC_BLOCK_DIAG)
+        return fail(nullptr, QCB_ERR_ARG, "bad jac_mode");
+    const int xdim = desc->d * desc->c;
+    for (int s = 0; s < desc->S; ++s)
+        if (desc->x_off[s] < 0 || desc->x_off[s] + xdim > desc->z_dim) return fail(nullptr, QCB_ERR_ARG, "x_off out of the knot");
+    if (desc->u_off < 0 || desc->u_off + desc->m > desc->z_dim || desc->dt_off < 0 || desc->dt_off >= desc->z_dim)
+        return fail(nullptr, QCB_ERR_ARG, "u_off / dt_off out of the knot");
+    const int K = desc->N - 1;
+    const int k0 = desc->k_begin, k1 = desc->k_end == 0 ? K : desc->k_end;
+    if (k0 < 0 || k1 > K || k0 >= k1) return fail(nullptr, QCB_ERR_ARG, "bad interval slab [k_begin, k_end)");
+
+    qcb_handle_s *h = new qcb_handle_s();
+    try {
+        int ndev = 0;
+        if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+            cudaGetLastError();
+            delete h;
+            return fail(nullptr, QCB_ERR_CUDA, "no usable CUDA device: this library has no CPU fallback");
+        }
+        if (desc->device < 0 || desc->device >= ndev) { delete h; return fail(nullptr, QCB_ERR_ARG, "bad device ordinal"); }
+        h->device = desc->device;
+        CK(cudaSetDevice(h->device));
+        cudaDeviceProp prop;
+        CK(cudaGetDeviceProperties(&prop, h->device));
+        h->n_sm = prop.multiProcessorCount;
+        h->d = desc->d; h->c = desc->c; h->m = desc->m; h->N = desc->N; h->S = desc->S; h->K = K;
+        h->z_dim = desc->z_dim; h->u_off = desc->u_off; h->dt_off = desc->dt_off; h->jac_mode = desc->jac_mode;
+        h->k0 = k0; h->k1 = k1; h->nk = k1 - k0; h->units = h->S * h->nk; h->xdim = xdim;
+        h->x_off.assign(desc->x_off, desc->x_off + desc->S);
+        // path selection: the fused kernel needs every register of a unit in shared memory
+        const size_t small_need = small_smem_doubles(h->d, h->c, h->m, 3) * sizeof(double);
+        h->large = small_need > 200 * 1024;
+        if (desc->force_path == 1) h->large = false;
+        if (desc->force_path == 2) h->large = true;
+        if (h->large) { h->dp = round_up(h->d, 64); h->cp = round_up(h->c, 64); }
+        else { h->dp = h->d; h->cp = h->c; }
+        h->small_threads = std::min(512, std::max(32, round_up(h->d * h->d, 32)));
+        const int64_t xb = h->jac_mode == QCB_JAC_DENSE_X ? (int64_t)xdim * xdim : (int64_t)h->c * h->d * h->d;
+        h->jnnz_unit = xb + (int64_t)xdim * (h->m + 2);
+        h->hnnz_unit = (int64_t)xdim * (h->m + 1) + (int64_t)h->m * (h->m + 1) / 2 + h->m + 1;
+        const int64_t dd = (int64_t)h->dp * h->dp, pan = (int64_t)h->dp * h->cp;
+        h->JA = dd + (h->m + 1) * pan + 2;
+        h->HA = (h->m + 1) * pan + (int64_t)h->m * h->m + h->m + 2;
+        h->HA += h->HA & 1;
+        if (h->JA >= (1LL << 31) || h->HA >= (1LL << 31)) { delete h; return fail(nullptr, QCB_ERR_ARG, "unit too large for 31-bit slot codes"); }
+
+        CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        for (auto &e : h->ev) CK(cudaEventCreate(&e));
+        init_constants();
+        // generators, padded to dp x dp
+        {
+            std::vector<double> g0((size_t)h->S * dd, 0.0), gd((size_t)h->S * std::max(1, h->m) * dd, 0.0);
+            for (int s = 0; s < h->S; ++s) {
+                for (int q = 0; q < h->d; ++q)
+                    for (int r = 0; r < h->d; ++r)
+                        g0[(size_t)s * dd + r + (size_t)q * h->dp] = desc->G_drift[(size_t)s * h->d * h->d + r + (size_t)q * h->d];
+                for (int j = 0; j < h->m; ++j)
+                    for (int q = 0; q < h->d; ++q)
+                        for (int r = 0; r < h->d; ++r)
+                            gd[((size_t)s * h->m + j) * dd + r + (size_t)q * h->dp] =
+                                desc->G_drives[((size_t)s * h->m + j) * h->d * h->d + r + (size_t)q * h->d];
+            }
+            CK(cudaMalloc(&h->dG0, g0.size() * 8));
+            CK(cudaMalloc(&h->dGd, gd.size() * 8));
+            CK(cudaMemcpy(h->dG0, g0.data(), g0.size() * 8, cudaMemcpyHostToDevice));
+            CK(cudaMemcpy(h->dGd, gd.data(), gd.size() * 8, cudaMemcpyHostToDevice));
+        }
+        CK(cudaMalloc(&h->d_xoff, h->S * sizeof(int)));
+        CK(cudaMemcpy(h->d_xoff, h->x_off.data(), h->S * sizeof(int), cudaMemcpyHostToDevice));
+        CK(cudaMalloc(&h->d_norm, sizeof(unsigned long long)));
+        CK(cudaMalloc(&h->d_bad, sizeof(int)));
+        CK(cudaMemset(h->d_bad, 0, sizeof(int)));
+        build_native_codes(h, true, true);
+    } catch (const CudaFail &f) {
+        qcb_status st = fail_cuda(nullptr, f);
+        qcb_destroy(h);
+        return st;
+    }
+    *out = h;
+    return QCB_OK;
+}
+
+void qcb_destroy(qcb_handle h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    free_scratch(h);
+    void *ptrs[] = {h->dG0, h->dGd, h->d_xoff, h->d_jcode, h->d_hcode, h->d_norm, h->d_bad, h->dZ, h->dmu, h->d_delta, h->d_jac, h->d_hess};
+    for (void *p : ptrs)
+        if (p) cudaFree(p);
+    for (auto &e : h->ev)
+        if (e) cudaEventDestroy(e);
+    for (auto &e : h->chunk_events) cudaEventDestroy(e);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    delete h;
+}
+
+int64_t qcb_defect_dim(qcb_handle h) { return h ? (int64_t)h->units * h->xdim : 0; }
+int64_t qcb_jacobian_nnz(qcb_handle h) { return h ? (int64_t)h->units * h->jnnz_unit : 0; }
+int64_t qcb_hessian_nnz(qcb_handle h) { return h ? (int64_t)h->units * h->hnnz_unit : 0; }
+int64_t qcb_kernel_launches(qcb_handle h) { return h ? h->launches : 0; }
+void *qcb_stream(qcb_handle h) { return h ? (void *)h->stream : nullptr; }
+
+qcb_status qcb_get_timings(qcb_handle h, double ms[4]) {
+    if (!h || !ms) return QCB_ERR_ARG;
+    for (int i = 0; i < 4; ++i) ms[i] = h->ms[i];
+    return QCB_OK;
+}
+
+qcb_status qcb_jacobian_structure(qcb_handle h, int64_t row_base, int64_t *rows, int64_t *cols) {
+    if (!h || !rows || !cols) return fail(h, QCB_ERR_ARG, "null argument");
+    if (h->custom_j) return fail(h, QCB_ERR_STRUCTURE, "a caller-supplied Jacobian structure is in force");
+    int64_t p = 0;
+    for (int s = 0; s < h->S; ++s) {
+        std::vector<Entry> pat = jac_pattern(h, s);
+        for (int kl = 0; kl < h->nk; ++kl) {
+            const int64_t rb = row_base + ((int64_t)s * h->nk + kl) * h->xdim, cb = (int64_t)(h->k0 + kl) * h->z_dim;
+            for (auto &e : pat) { rows[p] = rb + e.row + 1; cols[p] = cb + e.col + 1; ++p; }
+        }
+    }
+    return QCB_OK;
+}
+
+qcb_status qcb_hessian_structure(qcb_handle h, int64_t *rows, int64_t *cols) {
+    if (!h || !rows || !cols) return fail(h, QCB_ERR_ARG, "null argument");
+    if (h->custom_h) return fail(h, QCB_ERR_STRUCTURE, "a caller-supplied Hessian structure is in force");
+    int64_t p = 0;
+    for (int s = 0; s < h->S; ++s) {
+        std::vector<Entry> pat = hess_pattern(h, s);
+        for (int kl = 0; kl < h->nk; ++kl) {
+            const int64_t cb = (int64_t)(h->k0 + kl) * h->z_dim;
+            for (auto &e : pat) { rows[p] = cb + e.row + 1; cols[p] = cb + e.col + 1; ++p; }
+        }
+    }
+    return QCB_OK;
+}
+
+qcb_status qcb_set_structure(qcb_handle h, int64_t row_base, const int64_t *jr, const int64_t *jc, int64_t jn,
+                             const int64_t *hr, const int64_t *hc, int64_t hn) {
+    if (!h) return QCB_ERR_ARG;
+    Codes cd{h};
+    const int d = h->d, xd = h->xdim, m = h->m;
+    try {
+        CK(cudaSetDevice(h->device));
+        if (jr && jc && jn > 0) {
+            if (jn % h->units) return fail(h, QCB_ERR_STRUCTURE, "Jacobian nnz is not a multiple of the number of units");
+            const int64_t per = jn / h->units;
+            std::vector<uint32_t> codes((size_t)h->S * per);
+            for (int64_t p = 0; p < jn; ++p) {
+                const int64_t un = p / per, e = p % per;
+                const int s = (int)(un / h->nk), kl = (int)(un % h->nk), k = h->k0 + kl;
+                const int64_t r = jr[p] - 1 - row_base - un * xd;
+                const int64_t col = jc[p] - 1 - (int64_t)k * h->z_dim;
+                if (r < 0 || r >= xd) return fail(h, QCB_ERR_STRUCTURE, "Jacobian row outside its unit: entries must be grouped [system][interval]");
+                if (col < 0 || col >= 2 * (int64_t)h->z_dim) return fail(h, QCB_ERR_STRUCTURE, "Jacobian column outside knots k, k+1 of its unit");
+                uint32_t code = cd.jZero();
+                if (col >= h->x_off[s] && col < h->x_off[s] + xd) {
+                    const int qx = (int)(col - h->x_off[s]);
+                    if (qx / d == r / d) code = cd.jE((int)(r % d), qx % d);
+                } else if (col >= h->u_off && col < h->u_off + m) code = cd.jU((int)(col - h->u_off), (int)r);
+                else if (col == h->dt_off) code = cd.jT((int)r);
+                else if (col >= h->z_dim + h->x_off[s] && col < h->z_dim + h->x_off[s] + xd) {
+                    if (col - h->z_dim - h->x_off[s] == r) code = cd.jOne();
+                }
+                uint32_t &slot = codes[(size_t)s * per + e];
+                if (kl == 0) slot = code;
+                else if (slot != code) return fail(h, QCB_ERR_STRUCTURE, "Jacobian pattern differs between intervals");
+            }
+            upload_codes(h, &h->d_jcode, codes);
+            h->jnnz_unit = per;
+            h->custom_j = true;
+            if (h->d_jac) { CK(cudaFree(h->d_jac)); h->d_jac = nullptr; }
+        }
+        if (hr && hc && hn > 0) {
+            if (hn % h->units) return fail(h, QCB_ERR_STRUCTURE, "Hessian nnz is not a multiple of the number of units");
+            const int64_t per = hn / h->units;
+            std::vector<uint32_t> codes((size_t)h->S * per);
+            auto classify = [&](int s, int64_t v, int &kind, int &idx) {   // 0 x, 1 u, 2 dt, 3 other
+                if (v >= h->x_off[s] && v < h->x_off[s] + xd) { kind = 0; idx = (int)(v - h->x_off[s]); }
+                else if (v >= h->u_off && v < h->u_off + m) { kind = 1; idx = (int)(v - h->u_off); }
+                else if (v == h->dt_off) { kind = 2; idx = 0; }
+                else { kind = 3; idx = 0; }
+            };
+            for (int64_t p = 0; p < hn; ++p) {
+                const int64_t un = p / per, e = p % per;
+                const int s = (int)(un / h->nk), kl = (int)(un % h->nk), k = h->k0 + kl;
+                const int64_t a = hr[p] - 1 - (int64_t)k * h->z_dim, b = hc[p] - 1 - (int64_t)k * h->z_dim;
+                if (a < 0 || a >= h->z_dim || b < 0 || b >= h->z_dim)
+                    return fail(h, QCB_ERR_STRUCTURE, "Hessian entry outside the knot of its unit: entries must be grouped [system][interval]");
+                int ka, ia, kb, ib;
+                classify(s, a, ka, ia);
+                classify(s, b, kb, ib);
+                if (ka > kb) { std::swap(ka, kb); std::swap(ia, ib); }
+                uint32_t code = cd.hZero();
+                if (ka == 0 && kb == 1) code = cd.hXU(ib, ia);
+                else if (ka == 0 && kb == 2) code = cd.hXT(ia);
+                else if (ka == 1 && kb == 1) code = cd.hUU(std::min(ia, ib), std::max(ia, ib));
+                else if (ka == 1 && kb == 2) code = cd.hUT(ia);
+                else if (ka == 2 && kb == 2) code = cd.hTT();
+                uint32_t &slot = codes[(size_t)s * per + e];
+                if (kl == 0) slot = code;
+                else if (slot != code) return fail(h, QCB_ERR_STRUCTURE, "Hessian pattern differs between intervals");
+            }
+            upload_codes(h, &h->d_hcode, codes);
+            h->hnnz_unit = per;
+            h->custom_h = true;
+            if (h->d_hess) { CK(cudaFree(h->d_hess)); h->d_hess = nullptr; }
+        }
+    } catch (const CudaFail &f) {
+        return fail_cuda(h, f);
+    }
+    return QCB_OK;
+}
+
+qcb_status qcb_eval_all_device(qcb_handle h, const double *dZ, const double *dmu, double *d_delta,
+                               double *d_jac, double *d_hess) {
+    if (!h || !dZ) return fail(h, QCB_ERR_ARG, "null argument");
+    try {
+        CK(cudaSetDevice(h->device));
+        int want = (d_jac ? 1 : 0) | ((d_hess && dmu) ? 2 : 0);
+        if (!d_delta) { ensure_out(h, &h->d_delta, (size_t)h->units * h->xdim); d_delta = h->d_delta; }
+        return eval_device(h, dZ, dmu, d_delta, d_jac, d_hess, want, nullptr);
+    } catch (const CudaFail &f) {
+        return fail_cuda(h, f);
+    }
+}
+
+qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu, double *delta, double *jac, double *hess) {
+    if (!h || !Z) return fail(h, QCB_ERR_ARG, "null argument");
+    if (hess && !mu) return fail(h, QCB_ERR_ARG, "Hessian values need the multipliers");
+    try {
+        CK(cudaSetDevice(h->device));
+        const size_t nz = (size_t)h->N * h->z_dim, nmu = (size_t)h->S * h->K * h->xdim;
+        ensure_out(h, &h->dZ, nz);
+        ensure_out(h, &h->d_delta, (size_t)h->units * h->xdim);
+        if (jac) ensure_out(h, &h->d_jac, (size_t)h->units * h->jnnz_unit);
+        if (hess) { ensure_out(h, &h->dmu, nmu); ensure_out(h, &h->d_hess, (size_t)h->units * h->hnnz_unit); }
+        CK(cudaEventRecord(h->ev[0], h->stream));
+        // only the knots of this slab (plus the halo knot k_end) are needed on the device
+        CK(cudaMemcpyAsync(h->dZ + (size_t)h->k0 * h->z_dim, Z + (size_t)h->k0 * h->z_dim,
+                           (size_t)(h->nk + 1) * h->z_dim * 8, cudaMemcpyHostToDevice, h->stream));
+        if (hess) {
+            for (int s = 0; s < h->S; ++s) {
+                const size_t off = ((size_t)s * h->K + h->k0) * h->xdim;
+                CK(cudaMemcpyAsync(h->dmu + off, mu + off, (size_t)h->nk * h->xdim * 8, cudaMemcpyHostToDevice, h->stream));
+            }
+        }
+        CK(cudaEventRecord(h->ev[1], h->stream));
+        HostOut ho{delta, jac, hess};
+        int want = (jac ? 1 : 0) | (hess ? 2 : 0);
+        qcb_status st = eval_device(h, h->dZ, hess ? h->dmu : nullptr, h->d_delta, jac ? h->d_jac : nullptr,
+                                    hess ? h->d_hess : nullptr, want, &ho);
+        CK(cudaEventRecord(h->ev[2], h->stream));
+        CK(cudaEventSynchronize(h->ev[2]));
+        float a = 0, b = 0;
+        cudaEventElapsedTime(&a, h->ev[0], h->ev[1]);
+        cudaEventElapsedTime(&b, h->ev[1], h->ev[2]);
+        h->ms[0] = a; h->ms[1] = b; h->ms[2] = 0; h->ms[3] = a + b;
+        return st;
+    } catch (const CudaFail &f) {
+        return fail_cuda(h, f);
+    }
+}
+
+qcb_status qcb_eval_defect(qcb_handle h, const double *Z, double *delta) {
+    if (!delta) return fail(h, QCB_ERR_ARG, "null output");
+    return qcb_eval_all(h, Z, nullptr, delta, nullptr, nullptr);
+}
+qcb_status qcb_eval_jacobian(qcb_handle h, const double *Z, double *jac) {
+    if (!jac) return fail(h, QCB_ERR_ARG, "null output");
+    return qcb_eval_all(h, Z, nullptr, nullptr, jac, nullptr);
+}
+qcb_status qcb_eval_hessian(qcb_handle h, const double *Z, const double *mu, double *hess) {
+    if (!hess) return fail(h, QCB_ERR_ARG, "null output");
+    return qcb_eval_all(h, Z, mu, nullptr, nullptr, hess);
+}
+
+qcb_status qcb_host_alloc(void **ptr, size_t bytes) {
+    if (!ptr) return QCB_ERR_ARG;
+    cudaError_t e = cudaMallocHost(ptr, bytes);
+    if (e != cudaSuccess) { cudaGetLastError(); *ptr = nullptr; return QCB_ERR_NOMEM; }
+    return QCB_OK;
+}
+void qcb_host_free(void *ptr) { if (ptr) cudaFreeHost(ptr); }
+
+}  // extern "C"
+
+#include "qcb_fidelity.cuh"

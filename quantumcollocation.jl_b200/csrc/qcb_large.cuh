@@ -1,0 +1,357 @@
+// qcb_large.cuh -- large-d path: every op of qcb_program.h becomes one batched FP64 DMMA GEMM
+// launch over (unit x direction), registers in HBM scratch.
+//
+// tcgen05 has no FP64 kind, so the tensor-core route for this path is mma.sync DMMA
+// (SASS DMMA.8x8x4 on sm_100a; measured 37.1 TFLOP/s on B200, scratch/dmma_probe.cu).
+// Operand slabs are staged global -> shared with 16-byte cp.async (LDGSTS) in a
+// multi-stage ring; fragments are read from padded shared tiles without bank conflicts;
+// the epilogue fuses the linear terms / identity / per-unit scale of the matrix op.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace qcb {
+
+struct Opnd {
+    const double *p;
+    long long su, sd, ss;   // strides (doubles) per local unit, per direction, per system
+    int ld;
+    int pad_;
+};
+struct GemmTerm { Opnd a, b; int ta, tb; };
+struct GemmArgs {
+    int M, N, K;            // padded: M % BM == 0, N % BN == 0, K % 16 == 0
+    int d_ident;            // identity is added on the first d_ident diagonal entries
+    int nterm, nlin;
+    GemmTerm term[6];
+    Opnd lin[4];
+    double lin_coef[4];
+    double ident;
+    double alpha;           // scale on the product sum
+    const double *unit_scale;  // optional per-local-unit scale on the product sum
+    Opnd dst;
+    int ndir;               // batch = units * ndir, direction fastest
+    int unit0_global, nk;   // system of a unit = (unit0_global + unit) / nk
+};
+
+__device__ __forceinline__ void cp_async16(double *smem_dst, const double *gsrc) {
+    unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+__device__ __forceinline__ void dmma_16x8x4(double (&c)[4], double a0, double a1, double b) {
+    asm volatile("mma.sync.aligned.m16n8k4.row.col.f64.f64.f64.f64 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};\n"
+                 : "+d"(c[0]), "+d"(c[1]), "+d"(c[2]), "+d"(c[3])
+                 : "d"(a0), "d"(a1), "d"(b));
+}
+
+constexpr int GEMM_BK = 16;
+template <int BM, int BN> struct GemmSmem {
+    static constexpr int A_ST = (GEMM_BK * (BM + 4) > BM * (GEMM_BK + 4)) ? GEMM_BK * (BM + 4) : BM * (GEMM_BK + 4);
+    static constexpr int B_ST = (GEMM_BK * (BN + 4) > BN * (GEMM_BK + 4)) ? GEMM_BK * (BN + 4) : BN * (GEMM_BK + 4);
+    static constexpr size_t bytes(int stages) { return (size_t)stages * (A_ST + B_ST) * sizeof(double); }
+};
+
+template <int BM, int BN, int WM, int WN, int STAGES>
+__global__ void __launch_bounds__((BM / WM) * (BN / WN) * 32)
+bgemm_kernel(const __grid_constant__ GemmArgs g) {
+    constexpr int BK = GEMM_BK;
+    constexpr int NTHR = (BM / WM) * (BN / WN) * 32;
+    constexpr int MT = WM / 16, NT = WN / 8;
+    constexpr int A_ST = GemmSmem<BM, BN>::A_ST, B_ST = GemmSmem<BM, BN>::B_ST;
+    extern __shared__ __align__(16) double smem[];
+    double *As = smem, *Bs = smem + STAGES * A_ST;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int gid = lane >> 2, tig = lane & 3;
+    const int wm = warp % (BM / WM), wn = warp / (BM / WM);
+    const int tiles_n = g.N / BN, tiles = (g.M / BM) * tiles_n;
+    const int batch = blockIdx.x / tiles, tile = blockIdx.x % tiles;
+    const int m0 = (tile / tiles_n) * BM, n0 = (tile % tiles_n) * BN;
+    const int unit = batch / g.ndir, dir = batch % g.ndir;
+    const int sys = (g.unit0_global + unit) / g.nk;
+    const long long ou = unit, od = dir, os = sys;
+
+    double acc[MT][NT][4];
+#pragma unroll
+    for (int i = 0; i < MT; ++i)
+#pragma unroll
+        for (int j = 0; j < NT; ++j)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[i][j][q] = 0.0;
+
+    const int kslabs = g.K / BK;
+    const int nit = g.nterm * kslabs;
+
+    auto load_stage = [&](int it, int stage) {
+        const GemmTerm &t = g.term[it / kslabs];
+        const int k0 = (it % kslabs) * BK;
+        const double *pa = t.a.p + ou * t.a.su + od * t.a.sd + os * t.a.ss;
+        const double *pb = t.b.p + ou * t.b.su + od * t.b.sd + os * t.b.ss;
+        double *as = As + stage * A_ST, *bs = Bs + stage * B_ST;
+        if (!t.ta) {
+            for (int ch = tid; ch < BK * (BM / 2); ch += NTHR) {
+                int kc = ch / (BM / 2), r2 = ch % (BM / 2);
+                cp_async16(as + kc * (BM + 4) + 2 * r2, pa + (m0 + 2 * r2) + (long long)(k0 + kc) * t.a.ld);
+            }
+        } else {
+            for (int ch = tid; ch < BM * (BK / 2); ch += NTHR) {
+                int r = ch / (BK / 2), k2 = ch % (BK / 2);
+                cp_async16(as + r * (BK + 4) + 2 * k2, pa + (k0 + 2 * k2) + (long long)(m0 + r) * t.a.ld);
+            }
+        }
+        if (!t.tb) {
+            for (int ch = tid; ch < BN * (BK / 2); ch += NTHR) {
+                int n = ch / (BK / 2), k2 = ch % (BK / 2);
+                cp_async16(bs + n * (BK + 4) + 2 * k2, pb + (k0 + 2 * k2) + (long long)(n0 + n) * t.b.ld);
+            }
+        } else {
+            for (int ch = tid; ch < BK * (BN / 2); ch += NTHR) {
+                int kc = ch / (BN / 2), n2 = ch % (BN / 2);
+                cp_async16(bs + kc * (BN + 4) + 2 * n2, pb + (n0 + 2 * n2) + (long long)(k0 + kc) * t.b.ld);
+            }
+        }
+    };
+
+#pragma unroll
+    for (int s = 0; s < STAGES - 1; ++s) {
+        if (s < nit) load_stage(s, s);
+        cp_async_commit();
+    }
+    for (int it = 0; it < nit; ++it) {
+        cp_async_wait<STAGES - 2>();
+        __syncthreads();
+        {
+            int nx = it + STAGES - 1;
+            if (nx < nit) load_stage(nx, nx % STAGES);
+            cp_async_commit();
+        }
+        const GemmTerm &t = g.term[it / kslabs];
+        const int a_rs = t.ta ? (BK + 4) : 1, a_ks = t.ta ? 1 : (BM + 4);
+        const int b_ks = t.tb ? (BN + 4) : 1, b_ns = t.tb ? 1 : (BK + 4);
+        const double *as = As + (it % STAGES) * A_ST + (wm * WM + gid) * a_rs + tig * a_ks;
+        const double *bs = Bs + (it % STAGES) * B_ST + (wn * WN + gid) * b_ns + tig * b_ks;
+#pragma unroll
+        for (int kk = 0; kk < BK; kk += 4) {
+            double a0[MT], a1[MT], b[NT];
+#pragma unroll
+            for (int i = 0; i < MT; ++i) {
+                a0[i] = as[(i * 16) * a_rs + kk * a_ks];
+                a1[i] = as[(i * 16 + 8) * a_rs + kk * a_ks];
+            }
+#pragma unroll
+            for (int j = 0; j < NT; ++j) b[j] = bs[(j * 8) * b_ns + kk * b_ks];
+#pragma unroll
+            for (int i = 0; i < MT; ++i)
+#pragma unroll
+                for (int j = 0; j < NT; ++j) dmma_16x8x4(acc[i][j], a0[i], a1[i], b[j]);
+        }
+    }
+    cp_async_wait<0>();
+
+    // ---- epilogue: alpha*scale*acc + sum lin + ident*I -> dst ----
+    double sc = g.alpha;
+    if (g.unit_scale) sc *= g.unit_scale[unit];
+    double *pd = const_cast<double *>(g.dst.p) + ou * g.dst.su + od * g.dst.sd + os * g.dst.ss;
+    const double *pl[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+        pl[r] = (r < g.nlin) ? g.lin[r].p + ou * g.lin[r].su + od * g.lin[r].sd + os * g.lin[r].ss : nullptr;
+#pragma unroll
+    for (int i = 0; i < MT; ++i)
+#pragma unroll
+        for (int j = 0; j < NT; ++j)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                int r = m0 + wm * WM + i * 16 + gid + (q >> 1) * 8;
+                int c = n0 + wn * WN + j * 8 + tig * 2 + (q & 1);
+                double v = sc * acc[i][j][q];
+                for (int l = 0; l < g.nlin; ++l) v += g.lin_coef[l] * pl[l][r + (long long)c * g.lin[l].ld];
+                if (r == c && r < g.d_ident) v += g.ident;
+                pd[r + (long long)c * g.dst.ld] = v;
+            }
+}
+
+// ---------------------------------------------------------------------------------------
+// Frobenius contractions  out[unit][j*ni + i] (+)= < P(unit, j), Q(unit|sys, i) >
+// ---------------------------------------------------------------------------------------
+constexpr int CONTRACT_MAXI = 32;
+struct ContractArgs {
+    Opnd P, Q;        // P: sd = stride per j;  Q: sd = stride per i
+    int nj, ni;
+    long long nelem;  // dp*dp (contiguous, ld == dp)
+    double *out;      // [units][nj*ni]
+    int accumulate;
+    int unit0_global, nk;
+};
+__global__ void __launch_bounds__(256) contract_kernel(const __grid_constant__ ContractArgs g) {
+    const int unit = blockIdx.x / g.nj, j = blockIdx.x % g.nj;
+    const int sys = (g.unit0_global + unit) / g.nk;
+    const double *P = g.P.p + (long long)unit * g.P.su + (long long)j * g.P.sd + (long long)sys * g.P.ss;
+    const double *Q = g.Q.p + (long long)unit * g.Q.su + (long long)sys * g.Q.ss;
+    double acc[CONTRACT_MAXI];
+#pragma unroll
+    for (int i = 0; i < CONTRACT_MAXI; ++i) acc[i] = 0.0;
+    for (long long e = threadIdx.x; e < g.nelem; e += blockDim.x) {
+        double p = P[e];
+#pragma unroll
+        for (int i = 0; i < CONTRACT_MAXI; ++i)
+            if (i < g.ni) acc[i] = fma(p, Q[(long long)i * g.Q.sd + e], acc[i]);
+    }
+    __shared__ double red[8][CONTRACT_MAXI];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < CONTRACT_MAXI; ++i) {
+        if (i < g.ni) {
+            double v = acc[i];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0) red[warp][i] = v;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < g.ni) {
+        double v = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) v += red[w][threadIdx.x];
+        double *o = g.out + ((long long)unit * g.nj + j) * g.ni + threadIdx.x;
+        *o = g.accumulate ? (*o + v) : v;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Set-up kernels
+// ---------------------------------------------------------------------------------------
+struct UnitGeom {
+    int d, c, m, dp, cp, z_dim, u_off, dt_off, K, nk, k_begin, S;
+    const int *x_off;        // device [S]
+    const double *G0, *Gd;   // device, padded: [S][dp*dp], [S][m][dp*dp]
+};
+
+// G = G0 + sum u_j G_j for every local unit in [u0, u0+nu) (padded dp x dp), plus ||dt*G||_1
+// folded into a global max (norm as ordered-uint64 bits; NaN/Inf raise the flag).
+__global__ void __launch_bounds__(256)
+build_G_kernel(UnitGeom q, const double *Z, int u0_global, double *Gout, long long g_stride,
+               unsigned long long *norm_max_bits, int *bad_flag) {
+    const int unit = blockIdx.x, ug = u0_global + unit;
+    const int sys = ug / q.nk, k = q.k_begin + ug % q.nk;
+    const double *zk = Z + (long long)k * q.z_dim;
+    const long long dd = (long long)q.dp * q.dp;
+    const double *G0 = q.G0 + sys * dd, *Gd = q.Gd + (long long)sys * q.m * dd;
+    double *G = Gout ? Gout + (long long)unit * g_stride : nullptr;
+    const double dt = zk[q.dt_off];
+    __shared__ double colsum[8];
+    double worst = 0.0;
+    int bad = !isfinite(dt);
+    for (int col = 0; col < q.dp; ++col) {
+        double part = 0.0;
+        for (int r = threadIdx.x; r < q.dp; r += blockDim.x) {
+            long long e = r + (long long)col * q.dp;
+            double v = G0[e];
+            for (int j = 0; j < q.m; ++j) v = fma(zk[q.u_off + j], Gd[j * dd + e], v);
+            if (G) G[e] = v;
+            part += fabs(dt * v);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+        if ((threadIdx.x & 31) == 0) colsum[threadIdx.x >> 5] = part;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double s = 0;
+            for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += colsum[w];
+            if (!isfinite(s)) bad = 1;
+            worst = fmax(worst, s);
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        if (bad) atomicExch(bad_flag, 1);
+        else atomicMax(norm_max_bits, (unsigned long long)__double_as_longlong(worst));
+    }
+}
+
+// A = tau*G, padded panels XP / MP from Z / mu, per-unit scales.
+__global__ void __launch_bounds__(256)
+prep_unit_kernel(UnitGeom q, const double *Z, const double *mu, int u0_global, int s_levels,
+                 const double *G, double *A, long long mat_stride,
+                 double *XP, double *MP, long long pan_stride,
+                 double *tau_out, double *neg_tau_out) {
+    const int unit = blockIdx.x, ug = u0_global + unit;
+    const int sys = ug / q.nk, kl = ug % q.nk, k = q.k_begin + kl;
+    const double *zk = Z + (long long)k * q.z_dim;
+    const double tau = ldexp(zk[q.dt_off], -s_levels);
+    const long long dd = (long long)q.dp * q.dp;
+    const double *Gu = G + (long long)unit * mat_stride;
+    double *Au = A + (long long)unit * mat_stride;
+    for (long long e = threadIdx.x; e < dd; e += blockDim.x) Au[e] = tau * Gu[e];
+    const double *x = zk + q.x_off[sys];
+    const double *mk = mu ? mu + ((long long)sys * q.K + k) * ((long long)q.d * q.c) : nullptr;
+    double *xp = XP + (long long)unit * pan_stride, *mp = MP ? MP + (long long)unit * pan_stride : nullptr;
+    for (int e = threadIdx.x; e < q.dp * q.cp; e += blockDim.x) {
+        int r = e % q.dp, b = e / q.dp;
+        bool in = (r < q.d) && (b < q.c);
+        xp[e] = in ? x[r + b * q.d] : 0.0;
+        if (mp) mp[e] = (in && mk) ? mk[r + b * q.d] : 0.0;
+    }
+    if (threadIdx.x == 0) { tau_out[unit] = tau; neg_tau_out[unit] = -tau; }
+}
+
+// Hessian scalar blocks of one unit: HUU = -tau^2/2 (H + H^T), HUT_j = -(c1_j + tau c2_j), HTT = -c3
+__global__ void finalize_scalars_kernel(int m, const double *tau, const double *H, const double *c1,
+                                        const double *c2, const double *c3, double *harena,
+                                        long long harena_stride, long long off_huu) {
+    const int unit = blockIdx.x;
+    const double t = tau[unit];
+    double *out = harena + (long long)unit * harena_stride + off_huu;
+    const double *Hu = H + (long long)unit * m * m;
+    for (int e = threadIdx.x; e < m * m; e += blockDim.x) {
+        int i = e / m, j = e % m;
+        out[e] = -0.5 * t * t * (Hu[i * m + j] + Hu[j * m + i]);
+    }
+    for (int j = threadIdx.x; j < m; j += blockDim.x)
+        out[m * m + j] = -(c1[(long long)unit * m + j] + t * c2[(long long)unit * m + j]);
+    if (threadIdx.x == 0) { out[m * m + m] = -c3[unit]; out[m * m + m + 1] = 0.0; }
+}
+
+// constants 0.0 / 1.0 at the tail of the Jacobian arena
+__global__ void arena_consts_kernel(double *jarena, long long stride, long long off, int units) {
+    int u = blockIdx.x * blockDim.x + threadIdx.x;
+    if (u < units) { jarena[u * stride + off] = 0.0; jarena[u * stride + off + 1] = 1.0; }
+}
+
+// ---------------------------------------------------------------------------------------
+// Output assembly: COO values in the caller's order, coalesced stores, gathers from the arena
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+assemble_kernel(const double *arena, long long arena_stride, const uint32_t *code, long long nnz,
+                double *out, int u0_global, int nk, int chunks_per_unit) {
+    const int unit = blockIdx.x / chunks_per_unit, chunk = blockIdx.x % chunks_per_unit;
+    const int sys = (u0_global + unit) / nk;
+    const uint32_t *cd = code + (long long)sys * nnz;
+    const double *ar = arena + (long long)unit * arena_stride;
+    double *o = out + (long long)(u0_global + unit) * nnz;
+    const long long per = (nnz + chunks_per_unit - 1) / chunks_per_unit;
+    const long long e1 = (chunk + 1) * per < nnz ? (chunk + 1) * per : nnz;
+    for (long long e = chunk * per + threadIdx.x; e < e1; e += blockDim.x) {
+        uint32_t cc = cd[e];
+        double v = ar[cc & 0x7fffffffu];
+        o[e] = (cc >> 31) ? -v : v;
+    }
+}
+
+// delta = x_{k+1} - (E X)  with EX in a padded panel
+__global__ void __launch_bounds__(256)
+delta_kernel(UnitGeom q, const double *Z, const double *EX, long long pan_stride, double *delta, int u0_global) {
+    const int unit = blockIdx.x, ug = u0_global + unit;
+    const int sys = ug / q.nk, k = q.k_begin + ug % q.nk;
+    const double *xn = Z + (long long)(k + 1) * q.z_dim + q.x_off[sys];
+    const double *ex = EX + (long long)unit * pan_stride;
+    double *o = delta + (long long)ug * q.d * q.c;
+    for (int e = threadIdx.x; e < q.d * q.c; e += blockDim.x) {
+        int r = e % q.d, b = e / q.d;
+        o[e] = xn[e] - ex[r + b * q.dp];
+    }
+}
+
+}  // namespace qcb

@@ -1,0 +1,157 @@
+/* qcb_program.h -- the matrix program evaluated for every unit (knot x system).
+ *
+ * One unit = one interval k of one bilinear integrator
+ * (reference: src/quantum_integrators.jl:28-45, DirectTrajOpt.BilinearIntegrator call sites).
+ * Everything the evaluator needs from exp(dt*G(u)) -- the exponential itself, its first
+ * Frechet derivatives along every drive generator, and the W-contracted second
+ * derivatives -- is written here ONCE as a list of "matrix ops"
+ *
+ *     dst = sum_t op(a_t) * op(b_t)  +  sum_r c[coef_r] * reg_r  +  c[ident] * I
+ *
+ * over virtual d x d registers.  c[k] = 1/k! (degree-12 truncated Taylor, evaluated
+ * Paterson-Stockmeyer style in blocks of 4), followed by s squarings.  The small-d CUDA
+ * kernel interprets the table inside one launch with registers in shared memory; the
+ * large-d path turns every op into one batched FP64 DMMA GEMM launch with registers in
+ * HBM scratch; the CPU port under oracle/ interprets the same table on the host.
+ *
+ * Plain C so that all three translation units can include it.
+ */
+#ifndef QCB_PROGRAM_H
+#define QCB_PROGRAM_H
+#include <stdint.h>
+#ifdef __CUDACC__
+#define QCB_HD __host__ __device__
+#else
+#define QCB_HD
+#endif
+
+#define QCB_TAYLOR_DEGREE 12
+#define QCB_THETA 0.25          /* ||A/2^s||_1 <= theta before the polynomial is applied */
+#define QCB_MAX_SQUARINGS 10    /* ||dt*G(u)||_1 <= theta * 2^10 = 256; beyond: QCB_ERR_RANGE */
+#define QCB_MAX_TERMS 6
+#define QCB_MAX_LIN 4
+
+/* ---- virtual registers ---- */
+enum {
+    /* per unit (shared by all drive directions) */
+    QR_G = 0, QR_A, QR_A2, QR_A3, QR_A4, QR_Z1, QR_Z2,
+    QR_ZB1, QR_ZB2, QR_AB4, QR_AB3, QR_AB2,
+    QR_NUM_FIXED,                 /* = 12 */
+    /* level-relative chain registers (resolved with the current squaring level l) */
+    QR_EL = 16,                   /* E[l]   */
+    QR_EL1,                       /* E[l+1] */
+    QR_WL,                        /* Wlev[l]   */
+    QR_WL1,                       /* Wlev[l+1] */
+    QR_E0,                        /* E[0]   */
+    QR_W0,                        /* Wlev[0] */
+    /* system constant: generator of the current drive direction j */
+    QR_GJ = 24,
+    /* per (unit, direction) temporaries; several share a physical slot (see qcb_dslot) */
+    QR_DA2 = 32, QR_DA3, QR_DA4, QR_DZ1, QR_DZ2,
+    QR_DZB1, QR_DZB2, QR_DAB4, QR_DAB3, QR_DAB2,
+    QR_DAB,                       /* aliases DA3 */
+    QR_S,                         /* aliases DA2 */
+    QR_L = 48,                    /* L_j at the current level */
+    QR_LN                         /* L_j at the next level */
+};
+#define QCB_NUM_DSLOTS 10
+
+QCB_HD static inline int qcb_is_dreg(int r) { return r >= QR_DA2 && r <= QR_S; }
+QCB_HD static inline int qcb_dslot(int r) {
+    if (r == QR_DAB) return QR_DA3 - QR_DA2;
+    if (r == QR_S) return QR_DA2 - QR_DA2;
+    return r - QR_DA2;
+}
+
+typedef struct { uint8_t a, b, ta, tb; } qcb_term;
+typedef struct { uint8_t reg, coef; } qcb_lin;
+typedef struct {
+    uint8_t dst, nterm, nlin;
+    int8_t ident;                 /* Taylor coefficient index multiplying I, or -1 */
+    qcb_term term[QCB_MAX_TERMS];
+    qcb_lin lin[QCB_MAX_LIN];
+} qcb_op;
+
+#define T_(a, b, ta, tb) { a, b, ta, tb }
+#define NOT_ { 0, 0, 0, 0 }
+#define NOL_ { 0, 0 }
+
+/* Phase 1: polynomial, forward (per unit).  A = tau*G is prepared by the set-up step. */
+static const qcb_op QCB_P1[] = {
+    { QR_A2, 1, 0, -1, { T_(QR_A, QR_A, 0, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+    { QR_A3, 1, 0, -1, { T_(QR_A, QR_A2, 0, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+    { QR_A4, 1, 0, -1, { T_(QR_A2, QR_A2, 0, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+    { QR_Z2, 0, 4, 8, { NOT_, NOT_, NOT_, NOT_, NOT_, NOT_ }, { { QR_A, 9 }, { QR_A2, 10 }, { QR_A3, 11 }, { QR_A4, 12 } } },
+    { QR_Z1, 1, 3, 4, { T_(QR_A4, QR_Z2, 0, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { { QR_A, 5 }, { QR_A2, 6 }, { QR_A3, 7 }, NOL_ } },
+    { QR_E0, 1, 3, 0, { T_(QR_A4, QR_Z1, 0, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { { QR_A, 1 }, { QR_A2, 2 }, { QR_A3, 3 }, NOL_ } },
+};
+/* Phase 2: squaring, level l = 0..s-1:  E[l+1] = E[l]^2 */
+static const qcb_op QCB_P2[] = {
+    { QR_EL1, 1, 0, -1, { T_(QR_EL, QR_EL, 0, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+};
+/* Phase 3: adjoint weight chain, level l = s-1..0:  W[l] = W[l+1] E[l]^T + E[l]^T W[l+1] */
+static const qcb_op QCB_P3[] = {
+    { QR_WL, 2, 0, -1, { T_(QR_WL1, QR_EL, 0, 1), T_(QR_EL, QR_WL1, 1, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+};
+/* Phase 4: polynomial, reverse sweep seeded with W[0] (per unit) */
+static const qcb_op QCB_P4[] = {
+    { QR_ZB1, 1, 0, -1, { T_(QR_A4, QR_W0, 1, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+    { QR_ZB2, 1, 0, -1, { T_(QR_A4, QR_ZB1, 1, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+    { QR_AB4, 2, 1, -1, { T_(QR_W0, QR_Z1, 0, 1), T_(QR_ZB1, QR_Z2, 0, 1), NOT_, NOT_, NOT_, NOT_ }, { { QR_ZB2, 12 }, NOL_, NOL_, NOL_ } },
+    { QR_AB3, 0, 3, -1, { NOT_, NOT_, NOT_, NOT_, NOT_, NOT_ }, { { QR_W0, 3 }, { QR_ZB1, 7 }, { QR_ZB2, 11 }, NOL_ } },
+    { QR_AB2, 3, 3, -1, { T_(QR_AB4, QR_A2, 0, 1), T_(QR_A2, QR_AB4, 1, 0), T_(QR_A, QR_AB3, 1, 0), NOT_, NOT_, NOT_ }, { { QR_W0, 2 }, { QR_ZB1, 6 }, { QR_ZB2, 10 }, NOL_ } },
+};
+/* Phase 5: polynomial, forward tangent along G_j (per unit x direction) */
+static const qcb_op QCB_P5[] = {
+    { QR_DA2, 2, 0, -1, { T_(QR_GJ, QR_A, 0, 0), T_(QR_A, QR_GJ, 0, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+    { QR_DA3, 2, 0, -1, { T_(QR_GJ, QR_A2, 0, 0), T_(QR_A, QR_DA2, 0, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+    { QR_DA4, 2, 0, -1, { T_(QR_DA2, QR_A2, 0, 0), T_(QR_A2, QR_DA2, 0, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+    { QR_DZ2, 0, 4, -1, { NOT_, NOT_, NOT_, NOT_, NOT_, NOT_ }, { { QR_GJ, 9 }, { QR_DA2, 10 }, { QR_DA3, 11 }, { QR_DA4, 12 } } },
+    { QR_DZ1, 2, 3, -1, { T_(QR_DA4, QR_Z2, 0, 0), T_(QR_A4, QR_DZ2, 0, 0), NOT_, NOT_, NOT_, NOT_ }, { { QR_GJ, 5 }, { QR_DA2, 6 }, { QR_DA3, 7 }, NOL_ } },
+    { QR_L, 2, 3, -1, { T_(QR_DA4, QR_Z1, 0, 0), T_(QR_A4, QR_DZ1, 0, 0), NOT_, NOT_, NOT_, NOT_ }, { { QR_GJ, 1 }, { QR_DA2, 2 }, { QR_DA3, 3 }, NOL_ } },
+};
+/* Phase 6: tangent of the reverse sweep along G_j (per unit x direction) */
+static const qcb_op QCB_P6[] = {
+    { QR_DZB1, 1, 0, -1, { T_(QR_DA4, QR_W0, 1, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+    { QR_DZB2, 2, 0, -1, { T_(QR_DA4, QR_ZB1, 1, 0), T_(QR_A4, QR_DZB1, 1, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+    { QR_DAB4, 3, 1, -1, { T_(QR_W0, QR_DZ1, 0, 1), T_(QR_DZB1, QR_Z2, 0, 1), T_(QR_ZB1, QR_DZ2, 0, 1), NOT_, NOT_, NOT_ }, { { QR_DZB2, 12 }, NOL_, NOL_, NOL_ } },
+    { QR_DAB3, 0, 2, -1, { NOT_, NOT_, NOT_, NOT_, NOT_, NOT_ }, { { QR_DZB1, 7 }, { QR_DZB2, 11 }, NOL_, NOL_ } },
+    { QR_DAB2, 6, 2, -1, { T_(QR_DAB4, QR_A2, 0, 1), T_(QR_AB4, QR_DA2, 0, 1), T_(QR_DA2, QR_AB4, 1, 0), T_(QR_A2, QR_DAB4, 1, 0), T_(QR_GJ, QR_AB3, 1, 0), T_(QR_A, QR_DAB3, 1, 0) }, { { QR_DZB1, 6 }, { QR_DZB2, 10 }, NOL_, NOL_ } },
+    { QR_DAB, 6, 2, -1, { T_(QR_DAB3, QR_A2, 0, 1), T_(QR_AB3, QR_DA2, 0, 1), T_(QR_DAB2, QR_A, 0, 1), T_(QR_AB2, QR_GJ, 0, 1), T_(QR_GJ, QR_AB2, 1, 0), T_(QR_A, QR_DAB2, 1, 0) }, { { QR_DZB1, 5 }, { QR_DZB2, 9 }, NOL_, NOL_ } },
+};
+/* Phase 7 (per level l = 0..s-1, per direction):
+ *   S_j = L_j^T W[l+1] + W[l+1] L_j^T ;  H[j][i] += <S_j, L_i> ;  L_j <- E[l] L_j + L_j E[l] */
+static const qcb_op QCB_P7S[] = {
+    { QR_S, 2, 0, -1, { T_(QR_L, QR_WL1, 1, 0), T_(QR_WL1, QR_L, 0, 1), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+};
+static const qcb_op QCB_P7L[] = {
+    { QR_LN, 2, 0, -1, { T_(QR_EL, QR_L, 0, 0), T_(QR_L, QR_EL, 0, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+};
+#undef T_
+#undef NOT_
+#undef NOL_
+
+#define QCB_NOPS(t) ((int)(sizeof(t) / sizeof((t)[0])))
+
+static const double QCB_TAYLOR[QCB_TAYLOR_DEGREE + 1] = {
+    1.0, 1.0, 1.0 / 2, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040, 1.0 / 40320,
+    1.0 / 362880, 1.0 / 3628800, 1.0 / 39916800, 1.0 / 479001600 };
+
+/* number of squarings for a given 1-norm of dt*G(u); -1 if out of range / non-finite */
+QCB_HD static inline int qcb_squarings(double norm1) {
+    if (!(norm1 == norm1) || norm1 > QCB_THETA * (double)(1 << QCB_MAX_SQUARINGS)) return -1;
+    int s = 0;
+    double t = QCB_THETA;
+    while (norm1 > t) { t *= 2.0; ++s; }
+    return s;
+}
+
+/* ---- canonical per-unit value arenas (sources of the COO value vectors) ----
+ * Jacobian arena : [ E (dp*dp) | JU_0..JU_{m-1} (dp*cp each) | JT (dp*cp) | 0.0 | 1.0 ]
+ * Hessian arena  : [ HXU_0..HXU_{m-1} (dp*cp each) | HXT (dp*cp) | HUU (m*m) | HUT (m) | HTT (1) | 0.0 ]
+ * E is stored with its own sign (the x_k block of the Jacobian is -E: the slot code carries
+ * the sign); every other entry is stored with the sign of the derivative of delta.
+ * Slot code: bit 31 = negate, bits 0..30 = offset into the unit's arena. */
+#define QCB_CODE_NEG 0x80000000u
+
+#endif /* QCB_PROGRAM_H */
