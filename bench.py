@@ -1,0 +1,384 @@
+#!/usr/bin/env python
+"""bench.py -- knot-point evaluations per second (defect + Jacobian + Hessian-of-Lagrangian).
+
+One "step" = one full evaluation pass of the hot path over the synthetic trajectory of the
+named workload (default: BASELINE.json's headline, cfg5 = 6-qubit coupled-transmon unitary,
+d = 128, 12 drives, T = 2000 -> 1999 units), i.e. what Ipopt triggers with one eval_g +
+eval_jac_g + eval_h round.
+
+  python bench.py --gpus 1 --steps K --warmup W                 # the CUDA library
+  python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+  python bench.py --impl reference ...                          # CPU port on the host cores
+
+`value`  : device-resident throughput (inputs and outputs in HBM), CUDA events on the library's
+           stream, max over ranks.  N > 1: the T = 2000 trajectory is cut into N contiguous time
+           slabs, one per GPU ("strong" scaling), no data-path collective.
+`e2e`    : same metric through the public host-buffer call (Evaluator.eval_all ->
+           qcb_eval_all): pinned host Z / mu in, H2D, kernels, D2H of delta / Jacobian /
+           Hessian values into pinned host buffers, every step.  N > 1: every rank copies its
+           slab over its own PCIe link into one shared pinned host buffer.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOAD_DESC = {
+    "cfg1": "single-qubit Hadamard, X/Y drives, T=50 (README example)",
+    "cfg2": "3-level transmon X gate, T=200",
+    "cfg3": "two transmon qutrits CZ (d=18) unitary, T=500",
+    "cfg3_ket": "two transmon qutrits (d=18) ket, T=500",
+    "cfg4": "robust single-qubit gate, 256 samples, T=400 (knot x sample batching)",
+    "cfg5": "6-qubit coupled-transmon unitary (dim 64, real-iso 128), 12 drives, T=2000",
+}
+
+
+def algorithmic_bytes_per_unit(L):
+    """8 * [(3 x_dim + m + 1) inputs + x_dim defect + Jacobian nnz + Hessian nnz]."""
+    return 8 * (3 * L.x_dim + L.m + 1 + L.x_dim + L.jac_nnz_unit + L.hess_nnz_unit)
+
+
+def survey_flops_per_unit(L):
+    """SURVEY.md 8d convention: 2 d^3 * 10 * (1 + 6m) + 2 d^2 c (2m + 4)."""
+    return 2 * L.d ** 3 * 10 * (1 + 6 * L.m) + 2 * L.d ** 2 * L.c * (2 * L.m + 4)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.tmp = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.proc = None
+        self.gpu_index = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu_index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=self.tmp, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.tmp.flush()
+        rows = [r.strip().split(",") for r in open(self.tmp.name) if r.strip()]
+        os.unlink(self.tmp.name)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for nm, v in zip(names, r[5:9]):
+                    if v.strip().lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_port_throughput(w, sample_units, threads, repeats=1):
+    """Oracle port (oracle/qc_port.c, built -march=native on this box) on the host cores."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import qc_port
+    import qc_oracle
+    L = w.layout
+    OL = qc_oracle.Layout(L.d, L.c, L.m, L.N, L.S, L.z_dim, L.x_off, L.u_off, L.dt_off, L.jac_mode)
+    try:
+        qc_port.build(native=True)
+        native = True
+    except Exception:
+        native = False
+    nk = max(1, min(L.K, sample_units // L.S))
+    best = None
+    for _ in range(repeats):
+        t = time.perf_counter()
+        qc_port.evaluate_arenas(OL, w.G_drift, w.G_drives, w.Z, w.mu, True, True, (0, nk), threads, native)
+        dt = time.perf_counter() - t
+        best = dt if best is None else min(best, dt)
+    return nk * L.S / best, nk * L.S, native
+
+
+def run_reference(args):
+    """--impl reference: the CPU port of the path on the box's host cores (the reference's own
+    Julia evaluator cannot run in this image: no Julia, un-vendored deps -- see DESIGN.md)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import qcb200
+    from qcb200 import workloads
+    cores = os.cpu_count() or 1
+    w = workloads.make(args.workload, N=args.knots)
+    L = w.layout
+    per_step = max(cores, min(L.S * L.K, args.ref_units or (4 * cores if L.d >= 64 else 4096 * cores)))
+    rates = []
+    for i in range(args.warmup + args.steps):
+        r, n_units, native = cpu_port_throughput(w, per_step, cores)
+        if i >= args.warmup:
+            rates.append(r)
+    v = float(np.mean(rates))
+    line = {
+        "impl": "reference", "metric": "knot-pt evals/sec (defect+Jac+Hess)", "value": v, "unit": "knot-evals/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * n_units / v,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {WORKLOAD_DESC.get(args.workload, '')}", "units_per_step_sample": n_units,
+                   "d": L.d, "c": L.c, "m": L.m, "N": L.N, "S": L.S},
+        "cpu_baseline": {"value": v, "unit": "knot-evals/s", "cores": cores, "kind": "port",
+                         "sample": f"first {n_units} of {L.S * L.K} units per step, OpenMP over units, "
+                                   f"{'-march=native' if native else '-march=x86-64-v3'}"},
+        "e2e": {"value": v, "unit": "knot-evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--workload", default="cfg5", choices=sorted(WORKLOAD_DESC))
+    ap.add_argument("--knots", type=int, default=None, help="override the number of knots (testing)")
+    ap.add_argument("--ref-units", type=int, default=None)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    import qcb200
+    from qcb200 import workloads, Evaluator
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU port")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    w = workloads.make(args.workload, N=args.knots)
+    L = w.layout
+    K = L.K
+    k0, k1 = (K * rank) // world, (K * (rank + 1)) // world
+    ev = Evaluator(L, w.G_drift, w.G_drives, device=local, k_begin=k0, k_end=k1)
+    units_total = L.S * K
+
+    # ---------------- device-resident throughput (`value`) ----------------
+    dZ = torch.from_numpy(w.Z).to(dev)
+    dmu = torch.from_numpy(w.mu).to(dev)
+    d_delta = torch.empty(ev.defect_dim, dtype=torch.float64, device=dev)
+    d_jac = torch.empty(ev.jacobian_nnz, dtype=torch.float64, device=dev)
+    d_hess = torch.empty(ev.hessian_nnz, dtype=torch.float64, device=dev)
+    st = torch.cuda.ExternalStream(ev.stream, device=dev)
+    for _ in range(max(args.warmup, 3)):
+        ev.eval_all_device(dZ, dmu, d_delta, d_jac, d_hess)
+    # live FP64 GEMM peak (MEASURED_PEAKS.json has no FP64 figure)
+    dgemm_tflops = None
+    if rank == 0:
+        a = torch.randn(8192, 8192, dtype=torch.float64, device=dev)
+        b = torch.randn(8192, 8192, dtype=torch.float64, device=dev)
+        for _ in range(2):
+            torch.matmul(a, b)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            torch.matmul(a, b)
+        e1.record(); e1.synchronize()
+        dgemm_tflops = 3 * 2 * 8192 ** 3 / (e0.elapsed_time(e1) * 1e-3) / 1e12
+        del a, b
+    ev.profile(True)
+    launches0 = ev.kernel_launches
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    step_bytes = algorithmic_bytes_per_unit(L) * L.S * (k1 - k0)
+    flush = None
+    if step_bytes < 2 * 126e6:      # working set could sit in the 126 MB L2: flush it between steps
+        flush = torch.empty(64 * 1024 * 1024, dtype=torch.float64, device=dev)   # 512 MB
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ms_sum = 0.0
+    for _ in range(args.steps):
+        if flush is not None:
+            flush.add_(1.0)
+            torch.cuda.synchronize()
+        e0.record(st)
+        ev.eval_all_device(dZ, dmu, d_delta, d_jac, d_hess)
+        e1.record(st)
+        e1.synchronize()
+        ms_sum += e0.elapsed_time(e1)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms_dev = max_over_ranks(ms_sum) / args.steps
+    launches = ev.kernel_launches - launches0
+    prof = ev.profile_read()
+    ev.profile(False)
+    value = units_total / (ms_dev * 1e-3)
+
+    # ---------------- end-to-end through the host-buffer API (`e2e`) ----------------
+    e2e = None
+    if not args.no_e2e:
+        n_delta, n_jac, n_hess = units_total * L.x_dim, units_total * L.jac_nnz_unit, units_total * L.hess_nnz_unit
+        if world == 1:
+            hZ = torch.from_numpy(w.Z).pin_memory()
+            hmu = torch.from_numpy(w.mu).pin_memory()
+            h_delta = torch.empty(n_delta, dtype=torch.float64, pin_memory=True)
+            h_jac = torch.empty(n_jac, dtype=torch.float64, pin_memory=True)
+            h_hess = torch.empty(n_hess, dtype=torch.float64, pin_memory=True)
+            ptr = lambda t, off=0: t.data_ptr() + 8 * off
+            pZ, pmu = ptr(hZ), ptr(hmu)
+            p_delta, p_jac, p_hess = ptr(h_delta), ptr(h_jac), ptr(h_hess)
+        else:
+            # one shared pinned host buffer; every rank writes its slab over its own PCIe link
+            from multiprocessing import shared_memory
+            sizes = [len(w.Z), len(w.mu), n_delta, n_jac, n_hess]
+            offs = np.concatenate([[0], np.cumsum(sizes)])
+            name = f"qcb200_bench_{os.environ.get('MASTER_PORT', '0')}"
+            if rank == 0:
+                shm = shared_memory.SharedMemory(create=True, size=int(offs[-1]) * 8, name=name)
+            dist.barrier()
+            if rank != 0:
+                shm = shared_memory.SharedMemory(name=name)
+            buf = np.ndarray((int(offs[-1]),), dtype=np.float64, buffer=shm.buf)
+            if rank == 0:
+                buf[offs[0]:offs[1]] = w.Z
+                buf[offs[1]:offs[2]] = w.mu
+            base = buf.ctypes.data
+            rc = torch.cuda.cudart().cudaHostRegister(base, int(offs[-1]) * 8, 0)
+            assert int(rc) == 0, f"cudaHostRegister failed: {rc}"
+            dist.barrier()
+            pZ, pmu = base + 8 * int(offs[0]), base + 8 * int(offs[1])
+            # S == 1 for the sharded workloads: a slab is one contiguous range of every output
+            assert L.S == 1 or world == 1
+            p_delta = base + 8 * (int(offs[2]) + k0 * L.x_dim)
+            p_jac = base + 8 * (int(offs[3]) + k0 * L.jac_nnz_unit)
+            p_hess = base + 8 * (int(offs[4]) + k0 * L.hess_nnz_unit)
+        for _ in range(1):
+            ev.eval_all_raw(pZ, pmu, p_delta, p_jac, p_hess)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            ev.eval_all_raw(pZ, pmu, p_delta, p_jac, p_hess)
+        torch.cuda.synchronize()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        barrier()
+        tm = ev.timings()
+        h2d = 8 * ((k1 - k0 + 1) * L.z_dim + L.S * (k1 - k0) * L.x_dim)
+        d2h = 8 * (ev.defect_dim + ev.jacobian_nnz + ev.hessian_nnz)
+        if world > 1:
+            t_h2d = torch.tensor([h2d, d2h], dtype=torch.float64, device=dev)
+            dist.all_reduce(t_h2d)
+            h2d, d2h = int(t_h2d[0].item()), int(t_h2d[1].item())
+            # spot check: the shared buffer holds every rank's slab
+            if rank == 0:
+                chk = float(np.abs(buf[offs[2]:offs[3]]).sum())
+                assert np.isfinite(chk) and chk > 0
+            torch.cuda.cudart().cudaHostUnregister(base)
+            del buf
+            dist.barrier()
+            shm.close()
+            if rank == 0:
+                shm.unlink()
+        e2e = {"value": units_total / (dt / args.steps), "unit": "knot-evals/s", "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * dt / args.steps,
+               "last_call_rank0_ms": tm}
+
+    # ---------------- CPU baseline (rank 0, N = 1 only) ----------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        sample = args.ref_units or (32 * cores if L.d >= 64 else 8192 * cores)
+        rate, n_units, native = cpu_port_throughput(w, sample, cores)
+        cpu = {"value": rate, "unit": "knot-evals/s", "cores": cores, "kind": "port",
+               "sample": f"first {n_units} of {units_total} units, one pass, OpenMP over units, "
+                         f"{'-march=native' if native else '-march=x86-64-v3'}"}
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        per_rank_units = L.S * (k1 - k0)
+        if prof["launches"] > 0 and L.d >= 25:
+            gemm_ms = prof["ms"] / prof["launches"]
+            achieved = prof["flops"] / (prof["ms"] * 1e-3) / 1e12
+            roofline = {
+                "bound": "tensor", "kernel": "bgemm_kernel (batched FP64 DMMA GEMM, mma.sync m16n8k4 -> SASS DMMA.8x8x4)",
+                "achieved": achieved, "peak": dgemm_tflops, "unit": "TFLOP/s", "frac": achieved / dgemm_tflops,
+                "peak_source": "cuBLAS DGEMM 8192^3 timed live in this run (MEASURED_PEAKS.json has no FP64 entry; "
+                               "raw DMMA issue peak measured 37.1 TFLOP/s, scratch/dmma_probe.cu)",
+                "traffic": None,
+                "launches_per_step": prof["launches"] / args.steps, "avg_launch_ms": gemm_ms,
+                "kernel_share_of_step": prof["ms"] / args.steps / ms_dev if world == 1 else None,
+                "flops_per_unit_executed": prof["flops"] / args.steps / per_rank_units,
+                "flops_per_unit_survey_convention": survey_flops_per_unit(L),
+                "hbm_algorithmic_gbs": algorithmic_bytes_per_unit(L) * units_total / (ms_dev * 1e-3) / 1e9,
+            }
+        else:
+            gbs = algorithmic_bytes_per_unit(L) * units_total / (ms_dev * 1e-3) / 1e9
+            pk = peaks.get("hbm_gbs", 6650.0)
+            roofline = {"bound": "hbm", "kernel": "small_unit_kernel (fused per-unit evaluator)", "achieved": gbs, "peak": pk,
+                        "unit": "GB/s", "frac": gbs / pk,
+                        "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6.65 TB/s",
+                        "traffic": None, "bytes_per_unit": algorithmic_bytes_per_unit(L)}
+        line = {
+            "metric": "knot-pt evals/sec (defect+Jac+Hess)", "value": value, "unit": "knot-evals/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {WORKLOAD_DESC[args.workload]}", "units": units_total, "d": L.d,
+                       "c": L.c, "m": L.m, "N": L.N, "S": L.S,
+                       "jac_structure": "block-diagonal" if L.jac_mode else "dense-x",
+                       "parallelism": f"time-slab x{world}" if world > 1 else "single GPU",
+                       "l2": "inputs+outputs per step exceed L2 (no flush needed)" if flush is None
+                             else "L2 flushed between timed steps (512 MB read-modify-write)"},
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

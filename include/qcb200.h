@@ -133,6 +133,12 @@ int64_t qcb_kernel_launches(qcb_handle h);
 qcb_status qcb_get_timings(qcb_handle h, double ms[4]);
 /* The CUDA stream (cudaStream_t) the handle launches on, for callers that time with events. */
 void *qcb_stream(qcb_handle h);
+/* Per-launch CUDA-event timing of the dominant kernel of the large-d path (the batched FP64
+ * DMMA GEMM).  After enabling, every evaluation accumulates into
+ * out[0] = launches, out[1] = total milliseconds, out[2] = total algorithmic flops, out[3] = 0.
+ * No counterpart in the reference (measurement only). */
+qcb_status qcb_profile_enable(qcb_handle h, int32_t on);
+qcb_status qcb_profile_read(qcb_handle h, double out[4]);
 
 /* ---- terminal fidelities ---------------------------------------------------------------
  * F(x_N) for the losses of src/quantum_objectives.jl and the constraints of

@@ -48,6 +48,8 @@ SYMBOLS = {
     "qcb_kernel_launches": (ctypes.c_int64, [c_vp]),
     "qcb_get_timings": (ctypes.c_int, [c_vp, c_dp]),
     "qcb_stream": (c_vp, [c_vp]),
+    "qcb_profile_enable": (ctypes.c_int, [c_vp, ctypes.c_int32]),
+    "qcb_profile_read": (ctypes.c_int, [c_vp, c_dp]),
     "qcb_fidelity_create": (ctypes.c_int, [ctypes.POINTER(c_vp), ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                            c_dp, c_ip, ctypes.c_int32, ctypes.c_int32]),
     "qcb_fidelity_destroy": (None, [c_vp]),

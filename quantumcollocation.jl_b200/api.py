@@ -150,6 +150,14 @@ class Evaluator:
         self.lib.qcb_get_timings(self.h, ms)
         return {"h2d_ms": ms[0], "kernels_ms": ms[1], "d2h_ms": ms[2], "total_ms": ms[3]}
 
+    def profile(self, on: bool):
+        self.lib.qcb_profile_enable(self.h, 1 if on else 0)
+
+    def profile_read(self):
+        out = (ctypes.c_double * 4)()
+        self.lib.qcb_profile_read(self.h, out)
+        return {"launches": out[0], "ms": out[1], "flops": out[2]}
+
     def close(self):
         if getattr(self, "h", None):
             self.lib.qcb_destroy(self.h)

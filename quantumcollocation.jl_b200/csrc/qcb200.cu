@@ -48,6 +48,12 @@ struct qcb_handle_s {
     std::vector<cudaEvent_t> chunk_events;
     int64_t launches = 0;
     double ms[4] = {0, 0, 0, 0};
+    // optional per-launch profiling of the batched DMMA GEMM (qcb_profile_*)
+    bool profiling = false;
+    std::vector<cudaEvent_t> prof_ev;     // pairs
+    std::vector<double> prof_flops;       // algorithmic flops of each recorded launch
+    size_t prof_used = 0;
+    double prof_acc[4] = {0, 0, 0, 0};    // launches, total ms, total flops, reserved
 
     // device constants
     double *dG0 = nullptr, *dGd = nullptr;
@@ -183,7 +189,19 @@ void launch_gemm_cfg(qcb_handle_s *h, const GemmArgs &g, int batch) {
     }
     const int tiles = (g.M / BM) * (g.N / BN);
     const int threads = (BM / WM) * (BN / WN) * 32;
+    const bool prof = h->profiling;
+    if (prof) {
+        if (h->prof_used + 2 > h->prof_ev.size()) {
+            for (int i = 0; i < 2; ++i) { cudaEvent_t e; CK(cudaEventCreate(&e)); h->prof_ev.push_back(e); }
+        }
+        CK(cudaEventRecord(h->prof_ev[h->prof_used], h->stream));
+    }
     kern<<<(unsigned)(batch * tiles), threads, smem, h->stream>>>(g);
+    if (prof) {
+        CK(cudaEventRecord(h->prof_ev[h->prof_used + 1], h->stream));
+        h->prof_flops.push_back(2.0 * g.M * g.N * g.K * g.nterm * batch);
+        h->prof_used += 2;
+    }
     ++h->launches;
 }
 
@@ -191,7 +209,7 @@ void launch_gemm(qcb_handle_s *h, GemmArgs &g, int units) {
     const int batch = units * g.ndir;
     const bool big_ok = (g.M % 128 == 0) && (g.N % 128 == 0);
     if (big_ok && (long long)batch * (g.M / 128) * (g.N / 128) >= 2LL * h->n_sm)
-        launch_gemm_cfg<128, 128, 64, 32, 4>(h, g, batch);
+        launch_gemm_cfg<128, 128, 32, 32, 4>(h, g, batch);
     else
         launch_gemm_cfg<64, 64, 32, 32, 4>(h, g, batch);
     CK(cudaGetLastError());
@@ -276,7 +294,10 @@ struct LargeExec {
         ContractArgs a;
         a.P = P; a.Q = Q; a.nj = nj; a.ni = ni; a.nelem = dd; a.out = out; a.accumulate = accumulate;
         a.unit0_global = u0; a.nk = h->nk;
-        contract_kernel<<<(unsigned)(nu * nj), 256, 0, h->stream>>>(a);
+        if (nj > 1 && nj <= 16 && ni <= 16 && (dd % 128) == 0)
+            contract_mma_kernel<<<(unsigned)nu, 256, 0, h->stream>>>(a);
+        else
+            contract_kernel<<<(unsigned)(nu * nj), 256, 0, h->stream>>>(a);
         ++h->launches;
         CK(cudaGetLastError());
     }
@@ -512,6 +533,15 @@ qcb_status eval_device(qcb_handle_s *h, const double *dZ, const double *dmu, dou
     }
     CK(cudaStreamSynchronize(h->stream));
     if (host) CK(cudaStreamSynchronize(h->copy_stream));
+    if (h->profiling) {
+        for (size_t i = 0; i + 1 < h->prof_used; i += 2) {
+            float t = 0;
+            cudaEventElapsedTime(&t, h->prof_ev[i], h->prof_ev[i + 1]);
+            h->prof_acc[0] += 1; h->prof_acc[1] += t; h->prof_acc[2] += h->prof_flops[i / 2];
+        }
+        h->prof_used = 0;
+        h->prof_flops.clear();
+    }
     int bad = 0;
     CK(cudaMemcpy(&bad, h->d_bad, sizeof(int), cudaMemcpyDeviceToHost));
     if (bad) {
@@ -661,6 +691,7 @@ void qcb_destroy(qcb_handle h) {
     for (auto &e : h->ev)
         if (e) cudaEventDestroy(e);
     for (auto &e : h->chunk_events) cudaEventDestroy(e);
+    for (auto &e : h->prof_ev) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     delete h;
@@ -671,6 +702,18 @@ int64_t qcb_jacobian_nnz(qcb_handle h) { return h ? (int64_t)h->units * h->jnnz_
 int64_t qcb_hessian_nnz(qcb_handle h) { return h ? (int64_t)h->units * h->hnnz_unit : 0; }
 int64_t qcb_kernel_launches(qcb_handle h) { return h ? h->launches : 0; }
 void *qcb_stream(qcb_handle h) { return h ? (void *)h->stream : nullptr; }
+
+qcb_status qcb_profile_enable(qcb_handle h, int32_t on) {
+    if (!h) return QCB_ERR_ARG;
+    h->profiling = on != 0;
+    for (double &v : h->prof_acc) v = 0;
+    return QCB_OK;
+}
+qcb_status qcb_profile_read(qcb_handle h, double out[4]) {
+    if (!h || !out) return QCB_ERR_ARG;
+    for (int i = 0; i < 4; ++i) out[i] = h->prof_acc[i];
+    return QCB_OK;
+}
 
 qcb_status qcb_get_timings(qcb_handle h, double ms[4]) {
     if (!h || !ms) return QCB_ERR_ARG;

@@ -51,7 +51,11 @@ constexpr int GEMM_BK = 16;
 template <int BM, int BN> struct GemmSmem {
     static constexpr int A_ST = (GEMM_BK * (BM + 4) > BM * (GEMM_BK + 4)) ? GEMM_BK * (BM + 4) : BM * (GEMM_BK + 4);
     static constexpr int B_ST = (GEMM_BK * (BN + 4) > BN * (GEMM_BK + 4)) ? GEMM_BK * (BN + 4) : BN * (GEMM_BK + 4);
-    static constexpr size_t bytes(int stages) { return (size_t)stages * (A_ST + B_ST) * sizeof(double); }
+    static constexpr size_t bytes(int stages) {
+        size_t pipe = (size_t)stages * (A_ST + B_ST) * sizeof(double);
+        size_t ctile = (size_t)BN * (BM + 2) * sizeof(double);
+        return pipe > ctile ? pipe : ctile;
+    }
 };
 
 template <int BM, int BN, int WM, int WN, int STAGES>
@@ -151,27 +155,50 @@ bgemm_kernel(const __grid_constant__ GemmArgs g) {
     }
     cp_async_wait<0>();
 
-    // ---- epilogue: alpha*scale*acc + sum lin + ident*I -> dst ----
-    double sc = g.alpha;
-    if (g.unit_scale) sc *= g.unit_scale[unit];
-    double *pd = const_cast<double *>(g.dst.p) + ou * g.dst.su + od * g.dst.sd + os * g.dst.ss;
-    const double *pl[4];
-#pragma unroll
-    for (int r = 0; r < 4; ++r)
-        pl[r] = (r < g.nlin) ? g.lin[r].p + ou * g.lin[r].su + od * g.lin[r].sd + os * g.lin[r].ss : nullptr;
+    // ---- epilogue: accumulators -> shared tile -> coalesced 16-byte pass that fuses
+    //      alpha*scale*acc + sum_l coef_l*lin_l + ident*I and stores dst ----
+    __syncthreads();                      // every warp is done with the operand stages
+    constexpr int LDC = BM + 2;           // == 2 (mod 16) words: conflict-free fragment stores
+    double *Cs = smem;
 #pragma unroll
     for (int i = 0; i < MT; ++i)
 #pragma unroll
         for (int j = 0; j < NT; ++j)
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                int r = m0 + wm * WM + i * 16 + gid + (q >> 1) * 8;
-                int c = n0 + wn * WN + j * 8 + tig * 2 + (q & 1);
-                double v = sc * acc[i][j][q];
-                for (int l = 0; l < g.nlin; ++l) v += g.lin_coef[l] * pl[l][r + (long long)c * g.lin[l].ld];
-                if (r == c && r < g.d_ident) v += g.ident;
-                pd[r + (long long)c * g.dst.ld] = v;
+                int r = wm * WM + i * 16 + gid + (q >> 1) * 8;
+                int c = wn * WN + j * 8 + tig * 2 + (q & 1);
+                Cs[c * LDC + r] = acc[i][j][q];
             }
+    __syncthreads();
+    double sc = g.alpha;
+    if (g.unit_scale) sc *= g.unit_scale[unit];
+    double *pd = const_cast<double *>(g.dst.p) + ou * g.dst.su + od * g.dst.sd + os * g.dst.ss;
+    const double *pl[4];
+    double cf[4];
+    long long ldl[4];
+#pragma unroll
+    for (int l = 0; l < 4; ++l) {
+        const bool on = l < g.nlin;
+        pl[l] = on ? g.lin[l].p + ou * g.lin[l].su + od * g.lin[l].sd + os * g.lin[l].ss : nullptr;
+        cf[l] = on ? g.lin_coef[l] : 0.0;
+        ldl[l] = on ? g.lin[l].ld : 0;
+    }
+    for (int idx = tid; idx < (BM / 2) * BN; idx += NTHR) {
+        const int r = 2 * (idx % (BM / 2)), c = idx / (BM / 2);
+        double2 v = *reinterpret_cast<const double2 *>(Cs + c * LDC + r);
+        v.x *= sc; v.y *= sc;
+#pragma unroll
+        for (int l = 0; l < 4; ++l)
+            if (pl[l]) {
+                const double2 t = *reinterpret_cast<const double2 *>(pl[l] + (m0 + r) + (long long)(n0 + c) * ldl[l]);
+                v.x = fma(cf[l], t.x, v.x); v.y = fma(cf[l], t.y, v.y);
+            }
+        const int gr = m0 + r, gc = n0 + c;
+        if (gc == gr && gr < g.d_ident) v.x += g.ident;
+        if (gc == gr + 1 && gc < g.d_ident) v.y += g.ident;
+        *reinterpret_cast<double2 *>(pd + gr + (long long)gc * g.dst.ld) = v;
+    }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -216,6 +243,49 @@ __global__ void __launch_bounds__(256) contract_kernel(const __grid_constant__ C
         double v = 0;
         for (int w = 0; w < (int)(blockDim.x >> 5); ++w) v += red[w][threadIdx.x];
         double *o = g.out + ((long long)unit * g.nj + j) * g.ni + threadIdx.x;
+        *o = g.accumulate ? (*o + v) : v;
+    }
+}
+
+// Tensor-core variant for nj, ni <= 16: H = P Q^T with K = nelem on DMMA, one CTA per unit, every
+// matrix read exactly once (32-byte sectors fully used).  The sum over elements is order-free, so
+// lane (gid, tig) feeds elements e0 + 4*tig + t of rows gid / gid+8 into step t of both operands.
+__global__ void __launch_bounds__(256) contract_mma_kernel(const __grid_constant__ ContractArgs g) {
+    const int unit = blockIdx.x;
+    const int sys = (g.unit0_global + unit) / g.nk;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, gid = lane >> 2, tig = lane & 3;
+    const double *P = g.P.p + (long long)unit * g.P.su + (long long)sys * g.P.ss;
+    const double *Q = g.Q.p + (long long)unit * g.Q.su + (long long)sys * g.Q.ss;
+    const bool pa0 = gid < g.nj, pa1 = gid + 8 < g.nj, pb0 = gid < g.ni, pb1 = gid + 8 < g.ni;
+    const double *A0 = P + (long long)gid * g.P.sd + 4 * tig, *A1 = P + (long long)(gid + 8) * g.P.sd + 4 * tig;
+    const double *B0 = Q + (long long)gid * g.Q.sd + 4 * tig, *B1 = Q + (long long)(gid + 8) * g.Q.sd + 4 * tig;
+    double c0[4] = {0, 0, 0, 0}, c1[4] = {0, 0, 0, 0};
+    const double2 z2 = make_double2(0.0, 0.0);
+    for (long long e = (long long)warp * 16; e < g.nelem; e += 8 * 16) {
+        double2 a0x = z2, a0y = z2, a1x = z2, a1y = z2, b0x = z2, b0y = z2, b1x = z2, b1y = z2;
+        if (pa0) { a0x = *reinterpret_cast<const double2 *>(A0 + e); a0y = *reinterpret_cast<const double2 *>(A0 + e + 2); }
+        if (pa1) { a1x = *reinterpret_cast<const double2 *>(A1 + e); a1y = *reinterpret_cast<const double2 *>(A1 + e + 2); }
+        if (pb0) { b0x = *reinterpret_cast<const double2 *>(B0 + e); b0y = *reinterpret_cast<const double2 *>(B0 + e + 2); }
+        if (pb1) { b1x = *reinterpret_cast<const double2 *>(B1 + e); b1y = *reinterpret_cast<const double2 *>(B1 + e + 2); }
+        dmma_16x8x4(c0, a0x.x, a1x.x, b0x.x); dmma_16x8x4(c1, a0x.x, a1x.x, b1x.x);
+        dmma_16x8x4(c0, a0x.y, a1x.y, b0x.y); dmma_16x8x4(c1, a0x.y, a1x.y, b1x.y);
+        dmma_16x8x4(c0, a0y.x, a1y.x, b0y.x); dmma_16x8x4(c1, a0y.x, a1y.x, b1y.x);
+        dmma_16x8x4(c0, a0y.y, a1y.y, b0y.y); dmma_16x8x4(c1, a0y.y, a1y.y, b1y.y);
+    }
+    __shared__ double red[8][16][17];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int r = gid + (q >> 1) * 8, cc = tig * 2 + (q & 1);
+        red[warp][r][cc] = c0[q];
+        red[warp][r][cc + 8] = c1[q];
+    }
+    __syncthreads();
+    const int j = threadIdx.x >> 4, i = threadIdx.x & 15;
+    if (j < g.nj && i < g.ni) {
+        double v = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) v += red[w][j][i];
+        double *o = g.out + ((long long)unit * g.nj + j) * g.ni + i;
         *o = g.accumulate ? (*o + v) : v;
     }
 }
