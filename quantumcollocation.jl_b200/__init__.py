@@ -5,7 +5,7 @@ The product is ``csrc/libqcb200.so`` (hand-written sm_100a CUDA behind the C ABI
 reference's integrator / objective / constraint objects, synthetic workloads and the
 multi-GPU time-slab driver.
 """
-from . import isomorphisms, layout, workloads  # noqa: F401
+from . import isomorphisms, layout, workloads, piccolo, distributed  # noqa: F401
 from .layout import KnotLayout, JAC_BLOCK_DIAG, JAC_DENSE_X  # noqa: F401
 from .api import Evaluator, Fidelity  # noqa: F401
 from ._lib import QcbError, load as load_library  # noqa: F401

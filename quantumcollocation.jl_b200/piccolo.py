@@ -1,0 +1,357 @@
+"""Host-side mirror of the reference's interface for the hot path (Python stand-in for the Julia
+host; the Julia shim with the same shape is julia/QCB200.jl).
+
+Names, argument meaning and error behaviour follow the reference:
+
+* ``BilinearIntegrator(qtraj, N)``            src/quantum_integrators.jl:28-134
+* ``evaluate_(delta, integrator, traj)``      DirectTrajOpt.evaluate! as called at
+                                              src/problem_templates/smooth_pulse_problem.jl:512-515
+* ``test_integrator(integrator, traj; atol)`` src/quantum_integrators.jl:194
+* ``UnitaryInfidelityObjective`` etc.         src/quantum_objectives.jl:34-42,60-68,134-166,193-201
+* ``objective_value`` / ``gradient_``         src/quantum_objectives.jl:348-354
+* ``Final*FidelityConstraint``                src/quantum_constraints.jl:20-35,65-100,106-121
+
+All numerical work goes through the CUDA library (api.Evaluator / api.Fidelity).
+"""
+from __future__ import annotations
+
+from collections import OrderedDict
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+
+from .api import Evaluator, Fidelity
+from .isomorphisms import G_of_H, ket_to_iso, operator_to_iso_vec
+from .layout import JAC_BLOCK_DIAG, JAC_DENSE_X, KnotLayout
+
+
+# --------------------------------------------------------------------------------------- #
+# Minimal stand-ins for PiccoloQuantumObjects / NamedTrajectories containers
+# --------------------------------------------------------------------------------------- #
+class QuantumSystem:
+    """``QuantumSystem(H_drift, H_drives)`` with ``.G(u) = G_drift + sum_j u_j G_j``."""
+
+    def __init__(self, H_drift, H_drives: Sequence):
+        self.H_drift = np.asarray(H_drift, dtype=complex)
+        self.H_drives = [np.asarray(h, dtype=complex) for h in H_drives]
+        self.levels = self.H_drift.shape[0]
+        self.n_drives = len(self.H_drives)
+        self.G_drift = G_of_H(self.H_drift)
+        self.G_drives = np.array([G_of_H(h) for h in self.H_drives]).reshape(self.n_drives, 2 * self.levels, 2 * self.levels)
+
+    def G(self, u, t: float = 0.0):
+        return self.G_drift + np.tensordot(np.asarray(u, dtype=float), self.G_drives, axes=1)
+
+
+class NamedTrajectory:
+    """Knot-major container: components are (dim_i, N) arrays stacked in insertion order;
+    ``datavec`` is the flat ``Z`` of length ``dim * N`` (src/quantum_objectives.jl:353)."""
+
+    def __init__(self, components: Dict[str, np.ndarray], timestep: str = "dt", controls=("u",),
+                 goal: Optional[dict] = None):
+        self.names = list(components)
+        comps = OrderedDict((k, np.atleast_2d(np.asarray(v, dtype=float))) for k, v in components.items())
+        self.N = next(iter(comps.values())).shape[1]
+        self.dims = {k: v.shape[0] for k, v in comps.items()}
+        self.components = {}
+        off = 0
+        for k, v in comps.items():
+            assert v.shape[1] == self.N, f"component {k} has {v.shape[1]} knots, expected {self.N}"
+            self.components[k] = np.arange(off, off + v.shape[0])
+            off += v.shape[0]
+        self.dim = off
+        self.data = np.vstack(list(comps.values()))          # (dim, N)
+        self.timestep = timestep
+        self.controls = tuple(controls)
+        self.goal = goal or {}
+        self.global_dim = 0
+
+    @property
+    def datavec(self) -> np.ndarray:
+        return np.ascontiguousarray(self.data.T).reshape(-1)
+
+    def __getitem__(self, name):
+        return self.data[self.components[name], :]
+
+    def update(self, name, value):
+        self.data[self.components[name], :] = value
+
+
+class UnitaryTrajectory:
+    def __init__(self, system: QuantumSystem, U_goal, state_name="U_iso", drive_name="u"):
+        self.system, self.goal = system, np.asarray(U_goal, dtype=complex)
+        self.state_name, self.drive_name = state_name, drive_name
+        self.columns = system.levels
+
+
+class KetTrajectory:
+    def __init__(self, system: QuantumSystem, psi_init, psi_goal, state_name="psi_iso", drive_name="u"):
+        self.system = system
+        self.init, self.goal = np.asarray(psi_init, dtype=complex), np.asarray(psi_goal, dtype=complex)
+        self.state_name, self.drive_name = state_name, drive_name
+        self.columns = 1
+
+
+class MultiKetTrajectory:
+    def __init__(self, system: QuantumSystem, psi_inits, psi_goals, drive_name="u"):
+        self.system = system
+        self.inits = [np.asarray(p, dtype=complex) for p in psi_inits]
+        self.goals = [np.asarray(p, dtype=complex) for p in psi_goals]
+        self.state_names = [f"psi_iso{i + 1}" for i in range(len(self.inits))]
+        self.drive_name = drive_name
+        self.columns = 1
+
+
+class SamplingTrajectory:
+    """One state per system, shared controls (src/problem_templates/sampling_problem.jl:125-136)."""
+
+    def __init__(self, base_trajectory, systems: Sequence[QuantumSystem]):
+        self.base_trajectory = base_trajectory
+        self.systems = list(systems)
+        stem = base_trajectory.state_name
+        self.state_names = [f"{stem}{i + 1}" for i in range(len(self.systems))]
+        self.drive_name = base_trajectory.drive_name
+        self.columns = base_trajectory.columns
+
+
+def _layout_from_traj(traj: NamedTrajectory, state_names: Sequence[str], drive_name: str, d: int, c: int,
+                      jac_mode: Optional[int]) -> KnotLayout:
+    x_off = []
+    for nm in state_names:
+        idx = traj.components[nm]
+        if len(idx) != d * c or not np.all(np.diff(idx) == 1):
+            raise ValueError(f"state component {nm} must be {d * c} contiguous entries of a knot")
+        x_off.append(int(idx[0]))
+    u_idx = traj.components[drive_name]
+    dt_idx = traj.components[traj.timestep]
+    if jac_mode is None:
+        jac_mode = JAC_BLOCK_DIAG if d * c > 512 else JAC_DENSE_X
+    return KnotLayout(d=d, c=c, m=len(u_idx), N=traj.N, S=len(state_names), z_dim=traj.dim, x_off=x_off,
+                      u_off=int(u_idx[0]), dt_off=int(dt_idx[0]), jac_mode=jac_mode)
+
+
+class Integrator:
+    """The drop-in for one ``DirectTrajOpt.BilinearIntegrator`` (or, fused, for the whole vector the
+    reference builds for MultiKet / Sampling trajectories).  ``dim`` = x_dim * (N - 1) [* S]."""
+
+    def __init__(self, layout: KnotLayout, G_drift, G_drives, device=0, k_begin=0, k_end=0, force_path=0):
+        self.layout = layout
+        self.evaluator = Evaluator(layout, G_drift, G_drives, device=device, k_begin=k_begin, k_end=k_end,
+                                   force_path=force_path)
+        self.dim = self.evaluator.defect_dim
+
+    def evaluate(self, delta: np.ndarray, traj: NamedTrajectory) -> np.ndarray:
+        if delta.shape != (self.dim,):
+            raise ValueError(f"delta has shape {delta.shape}, expected ({self.dim},)")
+        return self.evaluator.eval_defect(traj.datavec, delta)
+
+    def jacobian_structure(self, row_base=0):
+        return self.evaluator.jacobian_structure(row_base)
+
+    def hessian_structure(self):
+        return self.evaluator.hessian_structure()
+
+    def jacobian_values(self, traj: NamedTrajectory, out=None):
+        return self.evaluator.eval_jacobian(traj.datavec, out)
+
+    def hessian_of_lagrangian_values(self, traj: NamedTrajectory, mu: np.ndarray, out=None):
+        return self.evaluator.eval_hessian(traj.datavec, mu, out)
+
+
+def BilinearIntegrator(qtraj, traj: NamedTrajectory, fused: bool = False, device: int = 0,
+                       jac_mode: Optional[int] = None, force_path: int = 0):
+    """Dispatch on the trajectory type exactly like src/quantum_integrators.jl:28-134.
+
+    Unitary / Ket -> one ``Integrator``; MultiKet / Sampling -> a list with one integrator per
+    state (the reference's return type) or, with ``fused=True``, a single integrator that
+    evaluates every state of a knot in one launch (knot x sample batching).
+    """
+    kw = dict(device=device, force_path=force_path)
+    if isinstance(qtraj, (UnitaryTrajectory, KetTrajectory)):
+        sys_ = qtraj.system
+        d = 2 * sys_.levels
+        L = _layout_from_traj(traj, [qtraj.state_name], qtraj.drive_name, d, qtraj.columns, jac_mode)
+        return Integrator(L, sys_.G_drift[None], sys_.G_drives[None], **kw)
+    if isinstance(qtraj, MultiKetTrajectory):
+        systems = [qtraj.system] * len(qtraj.state_names)
+        names, cols = qtraj.state_names, 1
+    elif isinstance(qtraj, SamplingTrajectory):
+        systems, names, cols = qtraj.systems, qtraj.state_names, qtraj.columns
+    else:
+        raise TypeError(f"no BilinearIntegrator for {type(qtraj).__name__}")
+    d = 2 * systems[0].levels
+    if fused:
+        L = _layout_from_traj(traj, names, qtraj.drive_name, d, cols, jac_mode)
+        return Integrator(L, np.array([s.G_drift for s in systems]), np.array([s.G_drives for s in systems]), **kw)
+    out = []
+    for s, nm in zip(systems, names):
+        L = _layout_from_traj(traj, [nm], qtraj.drive_name, d, cols, jac_mode)
+        out.append(Integrator(L, s.G_drift[None], s.G_drives[None], **kw))
+    return out
+
+
+def evaluate_(delta: np.ndarray, integrator: Integrator, traj: NamedTrajectory) -> np.ndarray:
+    """``DirectTrajOpt.evaluate!(delta, integrator, traj)``."""
+    return integrator.evaluate(delta, traj)
+
+
+def test_integrator(integrator: Integrator, traj: NamedTrajectory, atol: float = 1e-3, h: float = 1e-6,
+                    rng=None, max_columns: int = 24) -> Dict[str, float]:
+    """Derivative self-consistency, the reference's own criterion (src/quantum_integrators.jl:194):
+    Jacobian values vs central differences of the defect, Hessian-of-Lagrangian values vs central
+    differences of mu^T Jacobian.  Every evaluation is a call into the CUDA library.  Checks a random
+    subset of ``max_columns`` variables.  Raises AssertionError beyond ``atol``."""
+    rng = rng or np.random.default_rng(0)
+    ev, L = integrator.evaluator, integrator.layout
+    Z = traj.datavec.copy()
+    rows, cols = ev.jacobian_structure()
+    jac = ev.eval_jacobian(Z)
+    mu = rng.normal(size=L.S * L.K * L.x_dim)
+    hr, hc = ev.hessian_structure()
+    hess = ev.eval_hessian(Z, mu)
+    # candidate variables: everything the integrator depends on
+    used = np.unique(cols) - 1
+    pick = rng.choice(used, size=min(max_columns, len(used)), replace=False)
+    err_j = err_h = 0.0
+    mu_slab = mu.reshape(L.S, L.K, L.x_dim)[:, ev.k_begin:ev.k_end].reshape(-1)
+    for v in pick:
+        Zp, Zm = Z.copy(), Z.copy()
+        Zp[v] += h
+        Zm[v] -= h
+        fd = (ev.eval_defect(Zp) - ev.eval_defect(Zm)) / (2 * h)
+        col = np.zeros(integrator.dim)
+        sel = cols == v + 1
+        np.add.at(col, rows[sel] - 1, jac[sel])
+        err_j = max(err_j, float(np.abs(fd - col).max()))
+        # d/dv (mu^T J)  vs  Hessian column v
+        gp = np.zeros(len(Z)); gm = np.zeros(len(Z))
+        np.add.at(gp, cols - 1, ev.eval_jacobian(Zp) * mu_slab[rows - 1])
+        np.add.at(gm, cols - 1, ev.eval_jacobian(Zm) * mu_slab[rows - 1])
+        fdh = (gp - gm) / (2 * h)
+        colh = np.zeros(len(Z))
+        a = hc == v + 1
+        np.add.at(colh, hr[a] - 1, hess[a])
+        b = (hr == v + 1) & (hc != v + 1)
+        np.add.at(colh, hc[b] - 1, hess[b])
+        err_h = max(err_h, float(np.abs(fdh - colh).max()))
+    assert err_j < atol, f"Jacobian inconsistent with finite differences: {err_j:.3e}"
+    assert err_h < atol, f"Hessian inconsistent with finite differences: {err_h:.3e}"
+    return {"jacobian": err_j, "hessian": err_h}
+
+
+test_integrator.__test__ = False   # not a pytest test
+
+
+# --------------------------------------------------------------------------------------- #
+# Objectives (src/quantum_objectives.jl) and constraints (src/quantum_constraints.jl)
+# --------------------------------------------------------------------------------------- #
+class TerminalObjective:
+    """``Q * |1 - F(x_N)|`` on one or several (concatenated) terminal components."""
+
+    def __init__(self, fidelity: Fidelity, names: Sequence[str], traj: NamedTrajectory, Q: float = 100.0):
+        self.fidelity, self.names, self.Q = fidelity, list(names), float(Q)
+        self.idx = np.concatenate([traj.components[n] for n in self.names])
+        if len(self.idx) != fidelity.x_dim:
+            raise ValueError("terminal components do not match the goal's dimension")
+
+    def _x(self, traj):
+        return np.ascontiguousarray(traj.data[self.idx, traj.N - 1])
+
+    def __call__(self, traj):
+        return objective_value(self, traj)
+
+
+def objective_value(obj: TerminalObjective, traj: NamedTrajectory) -> float:
+    F, _, _ = obj.fidelity.eval(obj._x(traj), want_grad=False)
+    return obj.Q * abs(1.0 - F)
+
+
+def gradient_(grad: np.ndarray, obj: TerminalObjective, traj: NamedTrajectory) -> np.ndarray:
+    """``gradient!(grad, obj, traj)`` with ``grad = zeros(traj.dim * traj.N + traj.global_dim)``."""
+    if grad.shape != (traj.dim * traj.N + traj.global_dim,):
+        raise ValueError("gradient buffer has the wrong length")
+    F, g, _ = obj.fidelity.eval(obj._x(traj))
+    grad[:] = 0.0
+    grad[(traj.N - 1) * traj.dim + obj.idx] = -np.sign(1.0 - F) * obj.Q * g
+    return grad
+
+
+def hessian_values(obj: TerminalObjective, traj: NamedTrajectory) -> np.ndarray:
+    """Dense Hessian block of the objective on its terminal components."""
+    F, _, H = obj.fidelity.eval(obj._x(traj), want_grad=False, want_hess=True)
+    return -np.sign(1.0 - F) * obj.Q * H
+
+
+def UnitaryInfidelityObjective(U_goal, name: str, traj: NamedTrajectory, Q: float = 100.0, subspace=None, device=0):
+    """src/quantum_objectives.jl:193-201; with ``subspace`` the EmbeddedOperator variant (:182-191)."""
+    U_goal = np.asarray(U_goal, dtype=complex)
+    if subspace is None:
+        f = Fidelity(Fidelity.UNITARY, U_goal, device=device)
+    else:
+        n = int(round(np.sqrt(traj.dims[name] / 2)))
+        f = Fidelity(Fidelity.UNITARY_SUBSPACE, U_goal, n=n, subspace=subspace, device=device)
+    return TerminalObjective(f, [name], traj, Q)
+
+
+def KetInfidelityObjective(psi_goal, name: str, traj: NamedTrajectory, Q: float = 100.0, device=0):
+    """src/quantum_objectives.jl:60-68 (explicit goal); :34-42 reads the goal from ``traj.goal``."""
+    if psi_goal is None:
+        g = np.asarray(traj.goal[name])
+        psi_goal = g[:len(g) // 2] + 1j * g[len(g) // 2:]
+    return TerminalObjective(Fidelity(Fidelity.KET, psi_goal, device=device), [name], traj, Q)
+
+
+def CoherentKetInfidelityObjective(psi_goals, names: Sequence[str], traj: NamedTrajectory, Q: float = 100.0, device=0):
+    """src/quantum_objectives.jl:134-166."""
+    if len(psi_goals) != len(names):
+        raise AssertionError("Number of names must match number of goals")
+    return TerminalObjective(Fidelity(Fidelity.COHERENT_KET, np.array(psi_goals), device=device), names, traj, Q)
+
+
+class FinalFidelityConstraint:
+    """``[final_fidelity - F(x_N)] <= 0`` at knot N (equality=false, times=[traj.N])."""
+
+    def __init__(self, fidelity: Fidelity, names: Sequence[str], final_fidelity: float, traj: NamedTrajectory):
+        self.fidelity, self.names, self.final_fidelity = fidelity, list(names), float(final_fidelity)
+        self.idx = np.concatenate([traj.components[n] for n in self.names])
+        self.equality, self.times = False, [traj.N]
+
+    def value(self, traj):
+        F, _, _ = self.fidelity.eval(np.ascontiguousarray(traj.data[self.idx, traj.N - 1]), want_grad=False)
+        return np.array([self.final_fidelity - F])
+
+    def jacobian(self, traj):
+        """(cols [1-based into Z], values) of the single row."""
+        _, g, _ = self.fidelity.eval(np.ascontiguousarray(traj.data[self.idx, traj.N - 1]))
+        return (traj.N - 1) * traj.dim + self.idx + 1, -g
+
+    def hessian_of_lagrangian(self, traj, mu: float):
+        _, _, H = self.fidelity.eval(np.ascontiguousarray(traj.data[self.idx, traj.N - 1]), want_grad=False, want_hess=True)
+        return -mu * H
+
+
+def FinalUnitaryFidelityConstraint(U_goal, name, final_fidelity, traj, subspace=None, device=0):
+    """src/quantum_constraints.jl:106-121."""
+    U_goal = np.asarray(U_goal, dtype=complex)
+    if subspace is None:
+        f = Fidelity(Fidelity.UNITARY, U_goal, device=device)
+    else:
+        n = int(round(np.sqrt(traj.dims[name] / 2)))
+        f = Fidelity(Fidelity.UNITARY_SUBSPACE, U_goal, n=n, subspace=subspace, device=device)
+    return FinalFidelityConstraint(f, [name], final_fidelity, traj)
+
+
+def FinalKetFidelityConstraint(psi_goal, name, final_fidelity, traj, device=0):
+    """src/quantum_constraints.jl:20-35."""
+    return FinalFidelityConstraint(Fidelity(Fidelity.KET, psi_goal, device=device), [name], final_fidelity, traj)
+
+
+def FinalCoherentKetFidelityConstraint(psi_goals, names, final_fidelity, traj, device=0):
+    """src/quantum_constraints.jl:65-100."""
+    if len(psi_goals) != len(names):
+        raise AssertionError("Number of names must match number of goals")
+    return FinalFidelityConstraint(Fidelity(Fidelity.COHERENT_KET, np.array(psi_goals), device=device), names, final_fidelity, traj)
+
+
+# aliases for the old (docs / BASELINE.json) names, SURVEY.md Appendix A
+UnitaryIntegrator = KetIntegrator = BilinearIntegrator

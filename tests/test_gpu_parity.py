@@ -1,0 +1,320 @@
+"""GPU parity tests: the CUDA library, called through the C ABI, against the oracle on the same
+seeded inputs.  Tolerance: 1e-10 relative, block-normwise (BASELINE.json north_star; SURVEY
+Appendix B), FP64.  Structures must be bit-exact."""
+import os
+
+import numpy as np
+import pytest
+
+import qcb200
+from qcb200 import Evaluator, KnotLayout, workloads, piccolo, _lib
+import qc_oracle as O
+import qc_port as P
+from conftest import ROOT, oracle_layout, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def check_all(ev, OL, w, Z=None, mu=None, ref=None, tol=TOL):
+    Z = w.Z if Z is None else Z
+    mu = w.mu if mu is None else mu
+    d0, j0, h0 = ref or O.evaluate(OL, w.G_drift, w.G_drives, Z, mu)
+    d1, j1, h1 = ev.eval_all(Z, mu)
+    assert rel_err(d1, d0) < tol, ("defect", rel_err(d1, d0))
+    assert rel_err(j1, j0) < tol, ("jacobian", rel_err(j1, j0))
+    assert rel_err(h1, h0) < tol, ("hessian", rel_err(h1, h0))
+    return d1, j1, h1
+
+
+# ---- every BASELINE config at oracle-sized N, both kernels paths where they apply ----------------
+CASES = [("cfg1", 8, None, 0), ("cfg1_drift", 12, None, 0), ("cfg2", 9, None, 0), ("cfg3", 5, None, 0),
+         ("cfg3_ket", 6, None, 0), ("cfg4", 6, 5, 0),
+         ("cfg1_drift", 9, None, 2), ("cfg2", 5, None, 2), ("cfg3", 4, None, 2), ("cfg3_ket", 5, None, 2), ("cfg4", 5, 3, 2)]
+
+
+@pytest.mark.parametrize("name,N,S,path", CASES)
+def test_cuda_matches_scipy_oracle(name, N, S, path, built_libs):
+    w = workloads.make(name, N=N, S=S)
+    OL = oracle_layout(w.layout)
+    ev = Evaluator(w.layout, w.G_drift, w.G_drives, force_path=path)
+    check_all(ev, OL, w)
+    # structures bit-exact against the oracle's generator
+    r, c = ev.jacobian_structure(row_base=7)
+    ro, co = OL.jacobian_structure(row_base=7)
+    assert np.array_equal(r, ro) and np.array_equal(c, co)
+    r, c = ev.hessian_structure()
+    ro, co = OL.hessian_structure()
+    assert np.array_equal(r, ro) and np.array_equal(c, co)
+    assert ev.kernel_launches > 0
+    ev.close()
+
+
+@pytest.mark.parametrize("name,N,S", [("cfg1_drift", 5, None), ("cfg2", 4, None), ("cfg3_ket", 4, None),
+                                      ("cfg3", 3, None), ("cfg4", 4, 3)])
+def test_cuda_matches_committed_golden_vectors(name, N, S, built_libs):
+    g = np.load(os.path.join(GOLD, "oracle_small.npz"))
+    w = workloads.make(name, N=N, S=S, seed=7)
+    ev = Evaluator(w.layout, w.G_drift, w.G_drives)
+    d1, j1, h1 = ev.eval_all(g[f"{name}.Z"], g[f"{name}.mu"])
+    assert rel_err(d1, g[f"{name}.delta"]) < TOL and rel_err(j1, g[f"{name}.jac"]) < TOL
+    assert rel_err(h1, g[f"{name}.hess"]) < TOL
+    r, c = ev.jacobian_structure()
+    assert np.array_equal(r, g[f"{name}.jac_rows"]) and np.array_equal(c, g[f"{name}.jac_cols"])
+
+
+def test_cfg5_d128_against_port_and_scipy_spot(built_libs):
+    """cfg5 shape (d = 128, c = 64, m = 12, DMMA path): all values of 6 units against the CPU port
+    (itself pinned to scipy by tests/test_oracle.py), plus a direct scipy check of E."""
+    from scipy.linalg import expm
+    w = workloads.make("cfg5", N=7)
+    L = w.layout
+    OL = oracle_layout(L)
+    ev = Evaluator(L, w.G_drift, w.G_drives)
+    ref = P.evaluate(OL, w.G_drift, w.G_drives, w.Z, w.mu)
+    d1, j1, h1 = check_all(ev, OL, w, ref=ref)
+    X, Xn, M, u, dt = OL.unit_inputs(w.Z, w.mu, 0, 3)
+    E = expm(dt * (w.G_drift[0] + np.tensordot(u, w.G_drives[0], axes=1)))
+    assert rel_err(d1[3 * L.x_dim:4 * L.x_dim], (Xn - E @ X).T.reshape(-1)) < TOL
+    # block-diagonal structure: the first d*d Jacobian entries of a unit are -E, column-major
+    assert rel_err(j1[3 * L.jac_nnz_unit:3 * L.jac_nnz_unit + L.d ** 2], -E.T.reshape(-1)) < TOL
+    ev.close()
+
+
+# ---- call variants of the ABI ----------------------------------------------------------------------
+def test_separate_callbacks_equal_fused_call(built_libs):
+    w = workloads.make("cfg2", N=7)
+    ev = Evaluator(w.layout, w.G_drift, w.G_drives)
+    d, j, h = ev.eval_all(w.Z, w.mu)
+    assert np.array_equal(ev.eval_defect(w.Z), d)
+    assert np.array_equal(ev.eval_jacobian(w.Z), j)
+    assert np.array_equal(ev.eval_hessian(w.Z, w.mu), h)
+    with pytest.raises(_lib.QcbError):
+        ev.eval_all_raw(w.Z, None, None, None, np.empty(ev.hessian_nnz))   # Hessian needs mu
+    ev.close()
+
+
+@pytest.mark.parametrize("name,N,path", [("cfg2", 6, 0), ("cfg3", 4, 2)])
+def test_device_buffer_entry_point(name, N, path, built_libs):
+    import torch
+    w = workloads.make(name, N=N)
+    ev = Evaluator(w.layout, w.G_drift, w.G_drives, force_path=path)
+    d, j, h = ev.eval_all(w.Z, w.mu)
+    dZ, dmu = torch.from_numpy(w.Z).cuda(), torch.from_numpy(w.mu).cuda()
+    dd = torch.empty(ev.defect_dim, dtype=torch.float64, device="cuda")
+    dj = torch.empty(ev.jacobian_nnz, dtype=torch.float64, device="cuda")
+    dh = torch.empty(ev.hessian_nnz, dtype=torch.float64, device="cuda")
+    ev.eval_all_device(dZ, dmu, dd, dj, dh)
+    assert np.array_equal(dd.cpu().numpy(), d) and np.array_equal(dj.cpu().numpy(), j)
+    assert np.array_equal(dh.cpu().numpy(), h)
+    ev.close()
+
+
+@pytest.mark.parametrize("name,N,S,path", [("cfg2", 11, None, 0), ("cfg4", 9, 3, 0), ("cfg3", 7, None, 2)])
+def test_time_slab_handles_tile_the_trajectory(name, N, S, path, built_libs):
+    w = workloads.make(name, N=N, S=S)
+    L = w.layout
+    full = Evaluator(L, w.G_drift, w.G_drives, force_path=path)
+    d, j, h = full.eval_all(w.Z, w.mu)
+    d = d.reshape(L.S, L.K, -1); j = j.reshape(L.S, L.K, -1); h = h.reshape(L.S, L.K, -1)
+    for k0, k1 in [(0, 3), (3, L.K - 1), (L.K - 1, L.K)]:
+        ev = Evaluator(L, w.G_drift, w.G_drives, k_begin=k0, k_end=k1, force_path=path)
+        ds, js, hs = ev.eval_all(w.Z, w.mu)
+        # the fused small-d kernel picks the squaring count per unit: slabs are bit-identical to the
+        # full pass; the large-d path uses one count per slab (its maximum), so only to rounding
+        same = np.array_equal if path != 2 else (lambda a, b: rel_err(a, b) < 1e-13)
+        assert same(ds.reshape(L.S, k1 - k0, -1), d[:, k0:k1])
+        assert same(js.reshape(L.S, k1 - k0, -1), j[:, k0:k1])
+        assert same(hs.reshape(L.S, k1 - k0, -1), h[:, k0:k1])
+        r, c = ev.jacobian_structure()
+        assert c.min() >= k0 * L.z_dim + 1 and c.max() <= (k1 + 1) * L.z_dim
+        ev.close()
+    full.close()
+
+
+# ---- caller-supplied (reference-side) sparsity order ----------------------------------------------
+@pytest.mark.parametrize("path", [0, 2])
+def test_custom_structure_permutation_and_structural_zeros(path, built_libs):
+    w = workloads.make("cfg2", N=6)
+    L = w.layout
+    ev = Evaluator(L, w.G_drift, w.G_drives, force_path=path)
+    d, j, h = ev.eval_all(w.Z, w.mu)
+    jr, jc = ev.jacobian_structure()
+    hr, hc = ev.hessian_structure()
+    rng = np.random.default_rng(0)
+    nj, nh = L.jac_nnz_unit, L.hess_nnz_unit
+    pj, ph = rng.permutation(nj), rng.permutation(nh)
+    # same permutation inside every unit, plus one extra structurally-zero entry per unit
+    # (a (row, t-column) Jacobian entry; a (t, t) Hessian entry), lower-triangular Hessian order
+    t_col = L.dt_off - 1
+    jr2 = np.concatenate([np.append(jr[k * nj:(k + 1) * nj][pj], k * L.x_dim + 1) for k in range(L.K)])
+    jc2 = np.concatenate([np.append(jc[k * nj:(k + 1) * nj][pj], k * L.z_dim + t_col + 1) for k in range(L.K)])
+    hr2 = np.concatenate([np.append(hc[k * nh:(k + 1) * nh][ph], k * L.z_dim + t_col + 1) for k in range(L.K)])
+    hc2 = np.concatenate([np.append(hr[k * nh:(k + 1) * nh][ph], k * L.z_dim + t_col + 1) for k in range(L.K)])
+    ev.set_structure((jr2, jc2), (hr2, hc2))
+    assert ev.jacobian_nnz == L.K * (nj + 1) and ev.hessian_nnz == L.K * (nh + 1)
+    d2, j2, h2 = ev.eval_all(w.Z, w.mu)
+    assert np.array_equal(d2, d)
+    j2 = j2.reshape(L.K, nj + 1); h2 = h2.reshape(L.K, nh + 1)
+    assert np.array_equal(j2[:, :nj], j.reshape(L.K, nj)[:, pj]) and np.all(j2[:, nj] == 0)
+    assert np.array_equal(h2[:, :nh], h.reshape(L.K, nh)[:, ph]) and np.all(h2[:, nh] == 0)
+    # a structure that is not periodic / not grouped by unit is refused
+    with pytest.raises(_lib.QcbError) as ei:
+        ev.set_structure((jr2[::-1].copy(), jc2[::-1].copy()), None)
+    assert ei.value.status == 4
+    ev.close()
+
+
+# ---- edge cases -------------------------------------------------------------------------------------
+def test_minimal_trajectory_two_knots_and_zero_controls(built_libs):
+    w = workloads.make("cfg1_drift", N=2, u_scale=0.0)
+    ev = Evaluator(w.layout, w.G_drift, w.G_drives)
+    check_all(ev, oracle_layout(w.layout), w)
+    ev.close()
+
+
+def test_no_drives(built_libs):
+    """m = 0: only the x, dt blocks exist."""
+    rng = np.random.default_rng(2)
+    n, N = 3, 5
+    H = rng.normal(size=(n, n)) + 1j * rng.normal(size=(n, n)); H = H + H.conj().T
+    L = KnotLayout(d=2 * n, c=1, m=0, N=N, S=1, z_dim=2 * n + 1, x_off=[0], u_off=2 * n, dt_off=2 * n)
+    G0 = O.G_of_H(H)[None]
+    Gd = np.zeros((1, 0, 2 * n, 2 * n))
+    Z = rng.normal(size=(N, L.z_dim)); Z[:, L.dt_off] = 0.3
+    mu = rng.normal(size=L.K * L.x_dim)
+    ev = Evaluator(L, G0, Gd)
+    d0, j0, h0 = O.evaluate(oracle_layout(L), G0, Gd, Z.reshape(-1), mu)
+    d1, j1, h1 = ev.eval_all(Z.reshape(-1), mu)
+    assert rel_err(d1, d0) < TOL and rel_err(j1, j0) < TOL and rel_err(h1, h0) < TOL
+    ev.close()
+
+
+@pytest.mark.parametrize("path", [0, 2])
+def test_large_norm_many_squarings(path, built_libs):
+    w = workloads.make("cfg2", N=5)
+    L = w.layout
+    Z = w.Z.reshape(L.N, L.z_dim).copy()
+    Z[:, L.dt_off] = np.array([9.0, 0.01, 3.0, 0.5, 1.0])      # per-unit squarings differ: 6, 0, 4, 2, ...
+    ev = Evaluator(L, w.G_drift, w.G_drives, force_path=path)
+    check_all(ev, oracle_layout(L), w, Z=Z.reshape(-1))
+    ev.close()
+
+
+def test_non_skew_generator(built_libs):
+    """Lindblad-like / variational generators are not skew-symmetric: exp is not orthogonal."""
+    rng = np.random.default_rng(5)
+    d, m, N = 6, 2, 5
+    L = KnotLayout.smooth_pulse(d, 1, m, N)
+    G0 = 0.5 * rng.normal(size=(1, d, d))
+    Gd = 0.5 * rng.normal(size=(1, m, d, d))
+    Z = rng.normal(size=(N, L.z_dim)); Z[:, L.dt_off] = 0.4; Z[:, L.u_off:L.u_off + m] *= 0.3
+    mu = rng.normal(size=L.K * L.x_dim)
+    for path in (0, 2):
+        ev = Evaluator(L, G0, Gd, force_path=path)
+        d0, j0, h0 = O.evaluate(oracle_layout(L), G0, Gd, Z.reshape(-1), mu)
+        d1, j1, h1 = ev.eval_all(Z.reshape(-1), mu)
+        assert rel_err(d1, d0) < TOL and rel_err(j1, j0) < TOL and rel_err(h1, h0) < TOL
+        ev.close()
+
+
+@pytest.mark.parametrize("path", [0, 2])
+def test_non_finite_and_out_of_range_inputs_fail_loudly(path, built_libs):
+    w = workloads.make("cfg2", N=5)
+    L = w.layout
+    ev = Evaluator(L, w.G_drift, w.G_drives, force_path=path)
+    Z = w.Z.reshape(L.N, L.z_dim).copy()
+    Z[2, L.u_off] = np.nan
+    with pytest.raises(_lib.QcbError) as ei:
+        ev.eval_all(Z.reshape(-1), w.mu)
+    assert ei.value.status == 3
+    Z = w.Z.reshape(L.N, L.z_dim).copy()
+    Z[1, L.dt_off] = 1e6                      # ||dt G|| far beyond theta * 2^10
+    with pytest.raises(_lib.QcbError) as ei:
+        ev.eval_all(Z.reshape(-1), w.mu)
+    assert ei.value.status == 3
+    ev.eval_all(w.Z, w.mu)                    # the handle stays usable afterwards
+    ev.close()
+
+
+def test_knot_offsets_are_runtime_data(built_libs):
+    """Component order inside a knot is the caller's: put u first, dt in the middle, x last."""
+    rng = np.random.default_rng(9)
+    w = workloads.make("cfg2", N=6)
+    L0 = w.layout
+    L = KnotLayout(d=L0.d, c=L0.c, m=L0.m, N=L0.N, S=1, z_dim=L0.x_dim + 7, x_off=[7], u_off=1, dt_off=4)
+    Z0 = w.Z.reshape(L0.N, L0.z_dim)
+    Z = rng.normal(size=(L.N, L.z_dim))
+    Z[:, 7:] = Z0[:, :L0.x_dim]; Z[:, 1:3] = Z0[:, L0.u_off:L0.u_off + 2]; Z[:, 4] = Z0[:, L0.dt_off]
+    ev = Evaluator(L, w.G_drift, w.G_drives)
+    d0, j0, h0 = O.evaluate(oracle_layout(L), w.G_drift, w.G_drives, Z.reshape(-1), w.mu)
+    d1, j1, h1 = ev.eval_all(Z.reshape(-1), w.mu)
+    assert rel_err(d1, d0) < TOL and rel_err(j1, j0) < TOL and rel_err(h1, h0) < TOL
+    r, c = ev.hessian_structure()
+    ro, co = oracle_layout(L).hessian_structure()
+    assert np.array_equal(r, ro) and np.array_equal(c, co)
+    ev.close()
+
+
+# ---- the reference's own operator-level tests, restated (src/quantum_integrators.jl:175-329) ------
+def _test_system():
+    # QuantumSystem(GATES[:Z], [GATES[:X], GATES[:Y]], [1.0, 1.0]), N = 11, zero controls (:181-191)
+    return piccolo.QuantumSystem(workloads.Z2, [workloads.X2, workloads.Y2])
+
+
+def _traj(state: dict, N=11, m=2, rng=None):
+    rng = rng or np.random.default_rng(0)
+    comps = dict(state)
+    comps.update({"t": np.arange(N)[None] * 0.1, "dt": np.full((1, N), 0.1), "u": np.zeros((m, N))})
+    return piccolo.NamedTrajectory(comps, timestep="dt")
+
+
+def test_reference_test_integrator_unitary_and_ket(built_libs):
+    sys_ = _test_system()
+    rng = np.random.default_rng(1)
+    N = 11
+    U = np.stack([qcb200.isomorphisms.operator_to_iso_vec(workloads.haar_unitary(2, rng)) for _ in range(N)], axis=1)
+    traj = _traj({"U_iso": U})
+    integ = piccolo.BilinearIntegrator(piccolo.UnitaryTrajectory(sys_, workloads.H_GATE), traj)
+    assert integ.dim == 8 * (N - 1)
+    errs = piccolo.test_integrator(integ, traj, atol=1e-3)       # the reference's tolerance
+    assert errs["jacobian"] < 1e-6 and errs["hessian"] < 1e-5     # ours is far tighter
+    psi = rng.normal(size=(4, N))
+    trajk = _traj({"psi_iso": psi})
+    integ = piccolo.BilinearIntegrator(piccolo.KetTrajectory(sys_, [1, 0], [0, 1]), trajk)
+    piccolo.test_integrator(integ, trajk, atol=1e-3)
+    delta = np.zeros(integ.dim)
+    piccolo.evaluate_(delta, integ, trajk)
+    assert np.abs(delta).max() > 0
+    with pytest.raises(ValueError):
+        piccolo.evaluate_(np.zeros(3), integ, trajk)
+
+
+def test_reference_multiket_and_sampling_dispatch(built_libs):
+    sys_ = _test_system()
+    rng = np.random.default_rng(2)
+    N = 11
+    traj = _traj({"psi_iso1": rng.normal(size=(4, N)), "psi_iso2": rng.normal(size=(4, N))})
+    mk = piccolo.MultiKetTrajectory(sys_, [[1, 0], [0, 1]], [[0, 1], [1, 0]])
+    ints = piccolo.BilinearIntegrator(mk, traj)
+    assert isinstance(ints, list) and len(ints) == 2            # one integrator per ket (:63-74)
+    for it in ints:
+        piccolo.test_integrator(it, traj, atol=1e-3)
+    fused = piccolo.BilinearIntegrator(mk, traj, fused=True)
+    d_f = fused.evaluate(np.zeros(fused.dim), traj)
+    d_s = np.concatenate([it.evaluate(np.zeros(it.dim), traj) for it in ints])
+    assert np.array_equal(d_f, d_s)
+    # SamplingTrajectory: one integrator per system, shared controls (:91-101)
+    systems = [piccolo.QuantumSystem((1 + e) * workloads.Z2, [workloads.X2, workloads.Y2]) for e in (-0.1, 0.0, 0.1)]
+    base = piccolo.UnitaryTrajectory(systems[1], workloads.H_GATE)
+    st = piccolo.SamplingTrajectory(base, systems)
+    U = lambda: np.stack([qcb200.isomorphisms.operator_to_iso_vec(workloads.haar_unitary(2, rng)) for _ in range(N)], axis=1)
+    trajs = _traj({nm: U() for nm in st.state_names})
+    ints = piccolo.BilinearIntegrator(st, trajs)
+    assert len(ints) == 3
+    fused = piccolo.BilinearIntegrator(st, trajs, fused=True)
+    piccolo.test_integrator(fused, trajs, atol=1e-3)
+    d_f = fused.evaluate(np.zeros(fused.dim), trajs)
+    d_s = np.concatenate([it.evaluate(np.zeros(it.dim), trajs) for it in ints])
+    assert np.array_equal(d_f, d_s)
