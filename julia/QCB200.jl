@@ -1,0 +1,110 @@
+# QCB200.jl -- Julia shim: an AbstractIntegrator that forwards to libqcb200.so via ccall.
+#
+# NOT EXECUTED in this repository's CI (no Julia toolchain in the build image).  It shows the
+# reference-side binding a maintainer adds; the method names that DirectTrajOpt 0.8 dispatches on
+# for Jacobian / Hessian values must be checked against the installed package (SURVEY.md 8b marks
+# them [memory]); only the ccall signatures below are normative (include/qcb200.h).
+module QCB200
+
+using DirectTrajOpt
+using NamedTrajectories
+using PiccoloQuantumObjects
+import DirectTrajOpt: evaluate!
+
+const LIB = get(ENV, "QCB200_LIB", "libqcb200.so")
+
+struct QcbDesc                      # mirrors qcb_desc, include/qcb200.h
+    struct_bytes::Int32; d::Int32; c::Int32; m::Int32; N::Int32; S::Int32; z_dim::Int32
+    u_off::Int32; dt_off::Int32; jac_mode::Int32; device::Int32; k_begin::Int32; k_end::Int32
+    force_path::Int32
+    x_off::Ptr{Int32}; G_drift::Ptr{Float64}; G_drives::Ptr{Float64}
+end
+
+mutable struct B200BilinearIntegrator <: DirectTrajOpt.AbstractIntegrator
+    handle::Ptr{Cvoid}
+    dim::Int                        # x_dim * (N-1) [* S]: same meaning as BilinearIntegrator.dim
+    jac_nnz::Int
+    hess_nnz::Int
+end
+
+check(h, st) = st == 0 || error(unsafe_string(ccall((:qcb_last_error, LIB), Cstring, (Ptr{Cvoid},), h)))
+
+"""
+    B200BilinearIntegrator(qtraj, traj; device=0)
+
+Drop-in for `BilinearIntegrator(qtraj, N)` (src/quantum_integrators.jl:28-134).  Pass it through the
+templates' own seam:  `SmoothPulseProblem(qtraj, N; integrator = B200BilinearIntegrator(qtraj, traj))`
+(src/problem_templates/smooth_pulse_problem.jl:57,103-127); for `SamplingProblem`, which hard-codes
+its integrators (sampling_problem.jl:153), replace `prob.integrators[i]` after construction.
+"""
+function B200BilinearIntegrator(systems::Vector, state_names::Vector{Symbol}, drive::Symbol,
+                                traj::NamedTrajectory, columns::Int; device::Int = 0, jac_mode::Int = 0)
+    d = 2 * systems[1].levels
+    m = systems[1].n_drives
+    # matrices are dense column-major Float64: exactly what the C ABI wants
+    G0 = reduce(hcat, [vec(Matrix{Float64}(s.G(zeros(m), 0.0))) for s in systems])
+    Gd = reduce(hcat, [vec(Matrix{Float64}(s.G(Float64.(1:m .== j), 0.0)) .- reshape(G0[:, i], d, d))
+                       for (i, s) in enumerate(systems) for j in 1:m])
+    x_off = Int32[first(traj.components[n]) - 1 for n in state_names]
+    desc = QcbDesc(sizeof(QcbDesc), d, columns, m, traj.N, length(systems), traj.dim,
+                   first(traj.components[drive]) - 1, first(traj.components[traj.timestep]) - 1,
+                   jac_mode, device, 0, 0, 0, pointer(x_off), pointer(G0), pointer(Gd))
+    h = Ref{Ptr{Cvoid}}(C_NULL)
+    GC.@preserve x_off G0 Gd begin
+        st = ccall((:qcb_create, LIB), Cint, (Ref{Ptr{Cvoid}}, Ref{QcbDesc}), h, desc)
+    end
+    st == 0 || error(unsafe_string(ccall((:qcb_last_error, LIB), Cstring, (Ptr{Cvoid},), C_NULL)))
+    int = B200BilinearIntegrator(h[],
+        ccall((:qcb_defect_dim, LIB), Int64, (Ptr{Cvoid},), h[]),
+        ccall((:qcb_jacobian_nnz, LIB), Int64, (Ptr{Cvoid},), h[]),
+        ccall((:qcb_hessian_nnz, LIB), Int64, (Ptr{Cvoid},), h[]))
+    finalizer(i -> ccall((:qcb_destroy, LIB), Cvoid, (Ptr{Cvoid},), i.handle), int)
+    return int
+end
+
+# DirectTrajOpt.evaluate!(delta, integrator, traj)  (smooth_pulse_problem.jl:512-515)
+function evaluate!(δ::AbstractVector{Float64}, int::B200BilinearIntegrator, traj::NamedTrajectory)
+    Z = traj.datavec
+    GC.@preserve δ Z check(int.handle, ccall((:qcb_eval_defect, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}), int.handle, Z, δ))
+    return nothing
+end
+
+# Adopt the structure DirectTrajOpt itself reports for the stock integrator, so that values land
+# in exactly the reference's COO order (bit-exact sparsity).
+function adopt_structure!(int::B200BilinearIntegrator, jac_rows::Vector{Int}, jac_cols::Vector{Int},
+                          hess_rows::Vector{Int}, hess_cols::Vector{Int}; row_base::Int = 0)
+    GC.@preserve jac_rows jac_cols hess_rows hess_cols check(int.handle, ccall((:qcb_set_structure, LIB), Cint,
+        (Ptr{Cvoid}, Int64, Ptr{Int64}, Ptr{Int64}, Int64, Ptr{Int64}, Ptr{Int64}, Int64),
+        int.handle, row_base, jac_rows, jac_cols, length(jac_rows), hess_rows, hess_cols, length(hess_rows)))
+    int.jac_nnz = ccall((:qcb_jacobian_nnz, LIB), Int64, (Ptr{Cvoid},), int.handle)
+    int.hess_nnz = ccall((:qcb_hessian_nnz, LIB), Int64, (Ptr{Cvoid},), int.handle)
+end
+
+# eval_jac_g / eval_h value callbacks: write straight into Ipopt's value buffers
+function jacobian_values!(vals::AbstractVector{Float64}, int::B200BilinearIntegrator, Z::Vector{Float64})
+    GC.@preserve vals Z check(int.handle, ccall((:qcb_eval_jacobian, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}), int.handle, Z, vals))
+end
+function hessian_of_lagrangian_values!(vals::AbstractVector{Float64}, int::B200BilinearIntegrator,
+                                       Z::Vector{Float64}, μ::Vector{Float64})
+    GC.@preserve vals Z μ check(int.handle, ccall((:qcb_eval_hessian, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}), int.handle, Z, μ, vals))
+end
+
+# Dispatch mirroring src/quantum_integrators.jl:28-101
+B200BilinearIntegrator(q::UnitaryTrajectory, traj; kw...) =
+    B200BilinearIntegrator([get_system(q)], [state_name(q)], drive_name(q), traj, get_system(q).levels; kw...)
+B200BilinearIntegrator(q::KetTrajectory, traj; kw...) =
+    B200BilinearIntegrator([get_system(q)], [state_name(q)], drive_name(q), traj, 1; kw...)
+B200BilinearIntegrator(q::MultiKetTrajectory, traj; kw...) =
+    B200BilinearIntegrator(fill(get_system(q), length(state_names(q))), state_names(q), drive_name(q), traj, 1; kw...)
+B200BilinearIntegrator(q::SamplingTrajectory, traj; kw...) =
+    B200BilinearIntegrator(q.systems, state_names(q), drive_name(q), traj,
+                           q.base_trajectory isa UnitaryTrajectory ? q.systems[1].levels : 1; kw...)
+
+# Old (docs / BASELINE.json) names
+const UnitaryIntegrator = B200BilinearIntegrator
+const KetIntegrator = B200BilinearIntegrator
+
+end # module
