@@ -161,6 +161,31 @@ int64_t qcb_fidelity_x_dim(qcb_fidelity f);
  * F_min - F (quantum_constraints.jl:112) follow by the chain rule in the shim. */
 qcb_status qcb_fidelity_eval(qcb_fidelity f, const double *x, double *F, double *grad, double *hess);
 
+/* Batched fidelity that never allocates.  It has no counterpart in the reference.
+ *
+ * For callers that must not (or cannot) obtain device memory while they run: a host program whose
+ * GPU memory is already fully claimed by another allocator (PyTorch's or CUDA.jl's caching pool),
+ * so that a cudaMalloc inside this library would fail; and latency-sensitive loops (the per-iteration
+ * objective of a SamplingProblem, sampling_problem.jl:139-142) that cannot afford the device-wide
+ * synchronisation cudaMalloc / cudaFree imply.  This call uses no cudaMalloc, cudaFree or any
+ * allocating library routine: its only scratch -- the projections g_r . x_b -- is a fixed
+ * 512 KiB array compiled into the library (resident on every GPU that loads it, until exit).
+ *
+ *   d_X    [count][x_dim]  terminal states, device memory (caller's)
+ *   d_F    [count]         fidelities, device memory (caller's), may be NULL
+ *   d_grad [count][x_dim]  gradients dF/dx, device memory (caller's), may be NULL
+ *
+ * Limit: count * R <= 65536 and count <= 65535, where R is the number of linear forms of the
+ * fidelity kind (2 for unitary / ket / coherent-ket, 2 + 2 n_sub^2 for the subspace kind); larger
+ * batches are rejected with QCB_ERR_ARG before anything is launched.  The first call on a device
+ * also looks up the device address of the fixed array; make that first call before any stream
+ * capture is begun.  All calls in the process share the one array and it keeps the previous
+ * call's contents (each call overwrites every slot it later reads, so nothing needs clearing):
+ * two calls whose kernels can overlap on the GPU (different handles, streams or host threads)
+ * race with each other -- serialise them.  Returns after the work has completed. */
+qcb_status qcb_fidelity_eval_batch_device_noalloc(qcb_fidelity f, const double *d_X, int64_t count,
+                                                  double *d_F, double *d_grad);
+
 #ifdef __cplusplus
 }
 #endif

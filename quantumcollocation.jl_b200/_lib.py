@@ -55,6 +55,7 @@ SYMBOLS = {
     "qcb_fidelity_destroy": (None, [c_vp]),
     "qcb_fidelity_x_dim": (ctypes.c_int64, [c_vp]),
     "qcb_fidelity_eval": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "qcb_fidelity_eval_batch_device_noalloc": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int64, c_vp, c_vp]),
 }
 
 _lib = None

@@ -900,3 +900,92 @@ void qcb_host_free(void *ptr) { if (ptr) cudaFreeHost(ptr); }
 }  // extern "C"
 
 #include "qcb_fidelity.cuh"
+
+// =========================================================================================
+// Allocation-free batched fidelity (declared in include/qcb200.h next to qcb_fidelity_eval)
+// =========================================================================================
+// Scratch for the projections p[b][r] = g_r . x_b lives in this fixed device array instead of in
+// memory obtained from cudaMalloc.  Every GPU that loads the library carries these 512 KiB until
+// the process exits.  In host code `g_noalloc_proj` is only a stand-in for the symbol, not an
+// address a kernel can use: the usable device address is looked up once per device with
+// cudaGetSymbolAddress (below) and that pointer is what the kernels receive.
+#define QCB_NOALLOC_MAX_PROJ 65536
+static __device__ __align__(256) double g_noalloc_proj[QCB_NOALLOC_MAX_PROJ];
+
+namespace qcb {
+__global__ void __launch_bounds__(256)
+fid_project_batch_kernel(const double *G, const double *X, double *p, int64_t n, int64_t R) {
+    const int64_t r = blockIdx.x, b = blockIdx.y;
+    const double *g = G + r * n, *x = X + b * n;
+    double v = 0.0;
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) v = fma(g[i], x[i], v);
+    __shared__ double red[8];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0;
+        for (int w = 0; w < 8; ++w) s += red[w];
+        p[b * R + r] = s;
+    }
+}
+__global__ void fid_grad_batch_kernel(const double *G, const double *p, double *grad, double *F,
+                                      int64_t n, int64_t R, double w) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+    const double *pb = p + b * R;
+    if (i < n && grad) {
+        double v = 0.0;
+        for (int64_t r = 0; r < R; ++r) v = fma(G[r * n + i], pb[r], v);
+        grad[b * n + i] = 2.0 * w * v;
+    }
+    if (i == 0 && F) {
+        double f = 0.0;
+        for (int64_t r = 0; r < R; ++r) f = fma(pb[r], pb[r], f);
+        F[b] = w * f;
+    }
+}
+}  // namespace qcb
+
+namespace {
+constexpr int kMaxDevices = 64;
+double *g_noalloc_ptr[kMaxDevices] = {nullptr};   // device address of g_noalloc_proj, per device
+}  // namespace
+
+extern "C" qcb_status qcb_fidelity_eval_batch_device_noalloc(qcb_fidelity f, const double *d_X, int64_t count,
+                                                             double *d_F, double *d_grad) {
+    if (!f || !d_X || count < 1) return QCB_ERR_ARG;
+    if (count * f->R > QCB_NOALLOC_MAX_PROJ || count > 65535) {
+        char buf[200];
+        snprintf(buf, sizeof buf, "batch too large for the fixed scratch: count * %lld projections per state must be <= %d",
+                 (long long)f->R, QCB_NOALLOC_MAX_PROJ);
+        f->err = buf;
+        return QCB_ERR_ARG;
+    }
+    if (f->device < 0 || f->device >= kMaxDevices) return QCB_ERR_ARG;
+    cudaError_t e = cudaSetDevice(f->device);
+    if (e == cudaSuccess && !g_noalloc_ptr[f->device]) {
+        // one-time set-up on this device (this device is current): resolve the symbol's address
+        double *ptr = nullptr;
+        e = cudaGetSymbolAddress((void **)&ptr, g_noalloc_proj);
+        if (e == cudaSuccess) g_noalloc_ptr[f->device] = ptr;
+    }
+    if (e == cudaSuccess) {
+        double *p = g_noalloc_ptr[f->device];
+        const int64_t n = f->x_dim;
+        dim3 g1((unsigned)f->R, (unsigned)count), g2((unsigned)((n + 255) / 256), (unsigned)count);
+        // every projection slot read below is written first in this same call: nothing has to start at zero
+        qcb::fid_project_batch_kernel<<<g1, 256, 0, f->stream>>>(f->dG, d_X, p, n, f->R);
+        qcb::fid_grad_batch_kernel<<<g2, 256, 0, f->stream>>>(f->dG, p, d_grad, d_F, n, f->R, f->w);
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(f->stream);
+    }
+    if (e != cudaSuccess) {
+        char buf[200];
+        snprintf(buf, sizeof buf, "CUDA error '%s' in qcb_fidelity_eval_batch_device_noalloc", cudaGetErrorString(e));
+        f->err = buf;
+        cudaGetLastError();
+        return QCB_ERR_CUDA;
+    }
+    return QCB_OK;
+}
