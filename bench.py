@@ -273,24 +273,42 @@ def main():
             # one shared pinned host buffer; every rank writes its slab over its own PCIe link
             from multiprocessing import shared_memory
             sizes = [len(w.Z), len(w.mu), n_delta, n_jac, n_hess]
-            offs = np.concatenate([[0], np.cumsum(sizes)])
+            PG = (1 << 21) // 8                       # every array starts on a 2 MiB boundary
+            starts, tot = [], 0
+            for n_ in sizes:
+                starts.append(tot)
+                tot += (n_ + PG - 1) // PG * PG
+            offs = starts + [tot]
             name = f"qcb200_bench_{os.environ.get('MASTER_PORT', '0')}"
             if rank == 0:
-                shm = shared_memory.SharedMemory(create=True, size=int(offs[-1]) * 8, name=name)
+                shm = shared_memory.SharedMemory(create=True, size=tot * 8, name=name)
             dist.barrier()
             if rank != 0:
                 shm = shared_memory.SharedMemory(name=name)
-            buf = np.ndarray((int(offs[-1]),), dtype=np.float64, buffer=shm.buf)
+                try:    # only the creator (rank 0) unlinks: keep the other ranks' trackers quiet
+                    from multiprocessing import resource_tracker
+                    resource_tracker.unregister(shm._name, "shared_memory")
+                except Exception:
+                    pass
+            buf = np.ndarray((tot,), dtype=np.float64, buffer=shm.buf)
             if rank == 0:
-                buf[offs[0]:offs[1]] = w.Z
-                buf[offs[1]:offs[2]] = w.mu
+                buf[offs[0]:offs[0] + len(w.Z)] = w.Z
+                buf[offs[1]:offs[1] + len(w.mu)] = w.mu
             base = buf.ctypes.data
-            rc = torch.cuda.cudart().cudaHostRegister(base, int(offs[-1]) * 8, 0)
-            assert int(rc) == 0, f"cudaHostRegister failed: {rc}"
+            # pin only what this rank touches (inputs + its own output slabs), page-rounded
+            assert L.S == 1, "slab-contiguous outputs need S == 1"
+            regs = [(offs[0], offs[2]),
+                    (offs[2] + k0 * L.x_dim, offs[2] + k1 * L.x_dim),
+                    (offs[3] + k0 * L.jac_nnz_unit, offs[3] + k1 * L.jac_nnz_unit),
+                    (offs[4] + k0 * L.hess_nnz_unit, offs[4] + k1 * L.hess_nnz_unit)]
+            registered = []
+            for lo, hi in regs:
+                lo_b, hi_b = (8 * lo) // 4096 * 4096, (8 * hi + 4095) // 4096 * 4096
+                rc = torch.cuda.cudart().cudaHostRegister(base + lo_b, hi_b - lo_b, 0)
+                assert int(rc) == 0, f"cudaHostRegister failed: {int(rc)}"
+                registered.append(base + lo_b)
             dist.barrier()
             pZ, pmu = base + 8 * int(offs[0]), base + 8 * int(offs[1])
-            # S == 1 for the sharded workloads: a slab is one contiguous range of every output
-            assert L.S == 1 or world == 1
             p_delta = base + 8 * (int(offs[2]) + k0 * L.x_dim)
             p_jac = base + 8 * (int(offs[3]) + k0 * L.jac_nnz_unit)
             p_hess = base + 8 * (int(offs[4]) + k0 * L.hess_nnz_unit)
@@ -312,9 +330,10 @@ def main():
             h2d, d2h = int(t_h2d[0].item()), int(t_h2d[1].item())
             # spot check: the shared buffer holds every rank's slab
             if rank == 0:
-                chk = float(np.abs(buf[offs[2]:offs[3]]).sum())
-                assert np.isfinite(chk) and chk > 0
-            torch.cuda.cudart().cudaHostUnregister(base)
+                chk = buf[offs[2]:offs[2] + n_delta]
+                assert np.isfinite(chk).all() and np.abs(chk[-L.x_dim:]).sum() > 0 and np.abs(chk[:L.x_dim]).sum() > 0
+            for ptr_ in registered:
+                torch.cuda.cudart().cudaHostUnregister(ptr_)
             del buf
             dist.barrier()
             shm.close()

@@ -84,6 +84,9 @@ def gpu_compute(evaluator):
     def compute(k0, k1, Z, mu):
         assert (k0, k1) == (evaluator.k_begin, evaluator.k_end)
         dev = Z.device
+        # the library launches on its own stream: the NCCL broadcast that produced Z / mu is only
+        # ordered on torch's stream, so finish it before handing the buffers over
+        torch.cuda.current_stream(dev).synchronize()
         d = torch.empty(evaluator.defect_dim, dtype=torch.float64, device=dev)
         j = torch.empty(evaluator.jacobian_nnz, dtype=torch.float64, device=dev)
         h = torch.empty(evaluator.hessian_nnz, dtype=torch.float64, device=dev) if mu is not None else None
