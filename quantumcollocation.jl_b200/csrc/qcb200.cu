@@ -40,6 +40,9 @@ struct qcb_handle_s {
     int k0 = 0, k1 = 0, nk = 0, units = 0, xdim = 0;
     int dp = 0, cp = 0;            // padded dims of the device matrices / panels
     bool large = false;
+    bool iso = false;              // generators have the real-iso block form: half storage + half flops
+    int gcols = 0;                 // stored columns per matrix (dp, or dp/2 when iso)
+    int64_t msz = 0;               // doubles per stored matrix
     int device = 0, n_sm = 148;
     std::vector<int> x_off;
     std::string err;
@@ -80,6 +83,7 @@ struct qcb_handle_s {
         UnitGeom q;
         q.d = d; q.c = c; q.m = m; q.dp = dp; q.cp = cp; q.z_dim = z_dim; q.u_off = u_off; q.dt_off = dt_off;
         q.K = K; q.nk = nk; q.k_begin = k0; q.S = S; q.x_off = d_xoff; q.G0 = dG0; q.Gd = dGd;
+        q.gcols = gcols; q.gsz = msz;
         return q;
     }
 };
@@ -91,9 +95,17 @@ namespace {
 // ---------------------------------------------------------------------------------------
 struct Codes {
     qcb_handle_s *h;
-    int64_t dd() const { return (int64_t)h->dp * h->dp; }
+    int64_t dd() const { return h->msz; }
     int64_t pan() const { return (int64_t)h->dp * h->cp; }
-    uint32_t jE(int rr, int qq) const { return (uint32_t)(rr + (int64_t)qq * h->dp) | QCB_CODE_NEG; }
+    // value -E(rr, qq); in iso half storage only E_L = E(:, 0:n) is in the arena and
+    // E(i, j>=n) = -E_L(i+n, j-n) (i < n) or E_L(i-n, j-n) (i >= n)
+    uint32_t jE(int rr, int qq) const {
+        if (!h->iso) return (uint32_t)(rr + (int64_t)qq * h->dp) | QCB_CODE_NEG;
+        const int n = h->d / 2;
+        if (qq < n) return (uint32_t)(rr + (int64_t)qq * h->dp) | QCB_CODE_NEG;
+        if (rr < n) return (uint32_t)((rr + n) + (int64_t)(qq - n) * h->dp);
+        return (uint32_t)((rr - n) + (int64_t)(qq - n) * h->dp) | QCB_CODE_NEG;
+    }
     uint32_t jU(int j, int i) const { return (uint32_t)(dd() + j * pan() + (i % h->d) + (int64_t)(i / h->d) * h->dp); }
     uint32_t jT(int i) const { return jU(h->m, i); }
     uint32_t jZero() const { return (uint32_t)(dd() + (h->m + 1) * pan()); }
@@ -205,6 +217,33 @@ void launch_gemm_cfg(qcb_handle_s *h, const GemmArgs &g, int batch) {
     ++h->launches;
 }
 
+void launch_gemm_iso(qcb_handle_s *h, const GemmArgs &g, int units) {
+    static bool attr_set[64] = {false};
+    constexpr int ST = 3;
+    auto kern = bgemm_iso_kernel<ST>;
+    const size_t smem = GemmSmem<128, 64>::bytes(ST);
+    if (!attr_set[h->device]) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set[h->device] = true;
+    }
+    const int batch = units * g.ndir;
+    const int tiles = (g.M / 128) * (g.N / 64);
+    const bool prof = h->profiling;
+    if (prof) {
+        if (h->prof_used + 2 > h->prof_ev.size())
+            for (int i = 0; i < 2; ++i) { cudaEvent_t e; CK(cudaEventCreate(&e)); h->prof_ev.push_back(e); }
+        CK(cudaEventRecord(h->prof_ev[h->prof_used], h->stream));
+    }
+    kern<<<(unsigned)(batch * tiles), 256, smem, h->stream>>>(g);
+    if (prof) {
+        CK(cudaEventRecord(h->prof_ev[h->prof_used + 1], h->stream));
+        h->prof_flops.push_back(2.0 * g.M * g.N * g.K * g.nterm * batch);
+        h->prof_used += 2;
+    }
+    ++h->launches;
+    CK(cudaGetLastError());
+}
+
 void launch_gemm(qcb_handle_s *h, GemmArgs &g, int units) {
     const int batch = units * g.ndir;
     const bool big_ok = (g.M % 128 == 0) && (g.N % 128 == 0);
@@ -251,8 +290,9 @@ struct LargeExec {
     GemmArgs base_args(int ndir) const {
         GemmArgs g;
         memset(&g, 0, sizeof(g));
-        g.M = g.N = g.K = h->dp;
-        g.d_ident = h->d;
+        g.M = g.K = h->dp;
+        g.N = h->iso ? h->dp / 2 : h->dp;
+        g.d_ident = h->iso ? h->d / 2 : h->d;   // iso half storage: I_L = [I_n; 0]
         g.alpha = 1.0;
         g.ndir = ndir;
         g.unit0_global = u0;
@@ -275,11 +315,12 @@ struct LargeExec {
         }
         g.ident = op.ident >= 0 ? QCB_TAYLOR[op.ident] : 0.0;
         g.dst = reg(op.dst);
-        launch_gemm(h, g, nu);
+        if (h->iso) launch_gemm_iso(h, g, nu); else launch_gemm(h, g, nu);
     }
-    // dst = alpha * [scale] * op(a) * op(b), general shapes
+    // dst = alpha * [scale] * op(a) * op(b), general shapes.  In iso mode the left operand is a
+    // half-stored matrix (expanded on the fly) unless `plain` says both operands are ordinary.
     void product(Opnd dst, Opnd a, int ta, Opnd b, int tb, int M, int N, int Kd, int ndir, double alpha,
-                 const double *unit_scale) {
+                 const double *unit_scale, bool plain = false) {
         GemmArgs g = base_args(ndir);
         g.M = M; g.N = N; g.K = Kd;
         g.d_ident = 0;
@@ -288,7 +329,7 @@ struct LargeExec {
         g.alpha = alpha;
         g.unit_scale = unit_scale;
         g.dst = dst;
-        launch_gemm(h, g, nu);
+        if (h->iso && !plain) launch_gemm_iso(h, g, nu); else launch_gemm(h, g, nu);
     }
     void contract(Opnd P, int nj, Opnd Q, int ni, double *out, int accumulate) {
         ContractArgs a;
@@ -312,7 +353,7 @@ void free_scratch(qcb_handle_s *h) {
 }
 
 size_t scratch_bytes_per_unit(const qcb_handle_s *h, int s_cap) {
-    const size_t dd = (size_t)h->dp * h->dp, pan = (size_t)h->dp * h->cp;
+    const size_t dd = (size_t)h->msz, pan = (size_t)h->dp * h->cp;
     size_t n = (QR_NUM_FIXED + 2 * (size_t)(s_cap + 1) + (size_t)(QCB_NUM_DSLOTS + 2) * h->m) * dd;
     n += 3 * pan + h->JA + h->HA + (size_t)h->m * h->m + 2 * h->m + 3;
     return n * sizeof(double);
@@ -339,7 +380,7 @@ void ensure_scratch(qcb_handle_s *h, int s_need) {
         cu = best;
     }
     h->chunk_units = (int)cu;
-    const size_t dd = (size_t)h->dp * h->dp, pan = (size_t)h->dp * h->cp, n = (size_t)cu;
+    const size_t dd = (size_t)h->msz, pan = (size_t)h->dp * h->cp, n = (size_t)cu;
     const size_t mm = std::max(1, h->m);
     CK(cudaMalloc(&h->sc_fixed, QR_NUM_FIXED * n * dd * 8));
     CK(cudaMalloc(&h->sc_E, (size_t)(s_cap + 1) * n * dd * 8));
@@ -385,8 +426,9 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
                 double *d_hess, int want, const HostOut *host, int s) {
     ensure_scratch(h, s);
     const bool wj = want & 1, wh = (want & 2) && dmu;
-    const long long dd = (long long)h->dp * h->dp, pan = (long long)h->dp * h->cp;
+    const long long dd = h->msz, pan = (long long)h->dp * h->cp;
     const int m = h->m;
+    const int ncol = h->gcols;                       // columns of a stored matrix (dp, or dp/2 in iso mode)
     UnitGeom q = h->geom();
     size_t chunk_idx = 0;
     for (int u0 = 0; u0 < h->units; u0 += h->chunk_units, ++chunk_idx) {
@@ -412,7 +454,15 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         ++h->launches;
         if (wj || wh) {
             if (wh) {
-                X.product(X.W(s), MP, 0, XP, 1, h->dp, h->dp, h->cp, 1, 1.0, nullptr);   // W = M X^T
+                if (h->iso) {   // W = M X^T is a general matrix: project it onto the iso algebra (half storage)
+                    Opnd Wfull = X.mat(h->sc_dslot, (long long)h->dp * h->dp);
+                    X.product(Wfull, MP, 0, XP, 1, h->dp, h->dp, h->cp, 1, 1.0, nullptr, true);
+                    iso_project_kernel<<<nu, 256, 0, h->stream>>>(h->sc_dslot, (long long)h->dp * h->dp,
+                                                                  const_cast<double *>(X.W(s).p), dd, h->dp);
+                    ++h->launches;
+                } else {
+                    X.product(X.W(s), MP, 0, XP, 1, h->dp, h->dp, h->cp, 1, 1.0, nullptr);   // W = M X^T
+                }
                 for (int l = s - 1; l >= 0; --l) { X.level = l; X.run(QCB_P3[0], 1); }
                 X.level = 0;
                 for (int i = 0; i < QCB_NOPS(QCB_P4); ++i) X.run(QCB_P4[i], 1);
@@ -436,7 +486,7 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             }
             // final blocks
             Opnd GE = X.fixed(QR_A2), WE = X.fixed(QR_A3), GW = X.fixed(QR_A4), L = X.reg(QR_L);
-            X.product(GE, G, 0, Ef, 0, h->dp, h->dp, h->dp, 1, 1.0, nullptr);
+            X.product(GE, G, 0, Ef, 0, h->dp, ncol, h->dp, 1, 1.0, nullptr);
             Opnd JU = X.mat(h->sc_ja + dd, h->JA, pan), JT = X.mat(h->sc_ja + dd + m * pan, h->JA);
             if (m > 0) X.product(JU, L, 0, XP, 0, h->dp, h->cp, h->dp, m, 1.0, h->sc_ntau);
             X.product(JT, GE, 0, XP, 0, h->dp, h->cp, h->dp, 1, -1.0, nullptr);
@@ -447,15 +497,15 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
                 Opnd HXU = X.mat(h->sc_ha, h->HA, pan), HXT = X.mat(h->sc_ha + m * pan, h->HA);
                 if (m > 0) X.product(HXU, L, 1, MP, 0, h->dp, h->cp, h->dp, m, 1.0, h->sc_ntau);
                 X.product(HXT, GE, 1, MP, 0, h->dp, h->cp, h->dp, 1, -1.0, nullptr);
-                X.product(WE, Wt, 0, Ef, 1, h->dp, h->dp, h->dp, 1, 1.0, nullptr);
-                X.product(GW, G, 1, Wt, 0, h->dp, h->dp, h->dp, 1, 1.0, nullptr);
+                X.product(WE, Wt, 0, Ef, 1, h->dp, ncol, h->dp, 1, 1.0, nullptr);
+                X.product(GW, G, 1, Wt, 0, h->dp, ncol, h->dp, 1, 1.0, nullptr);
                 if (m > 0) {
                     X.contract(WE, 1, X.reg(QR_GJ), m, h->sc_c1, 0);
                     X.contract(GW, 1, L, m, h->sc_c2, 0);
                 }
                 X.contract(GW, 1, GE, 1, h->sc_c3, 0);
                 finalize_scalars_kernel<<<nu, 64, 0, h->stream>>>(m, h->sc_tau, h->sc_H, h->sc_c1, h->sc_c2, h->sc_c3,
-                                                                  h->sc_ha, h->HA, (m + 1) * pan);
+                                                                  h->sc_ha, h->HA, (m + 1) * pan, h->iso ? 2.0 : 1.0);
                 ++h->launches;
             }
             if (wj && d_jac) {
@@ -634,11 +684,32 @@ qcb_status qcb_create(qcb_handle *out, const qcb_desc *desc) {
         if (desc->force_path == 2) h->large = true;
         if (h->large) { h->dp = round_up(h->d, 64); h->cp = round_up(h->c, 64); }
         else { h->dp = h->d; h->cp = h->c; }
+        // real-iso block structure [[P,-Q],[Q,P]] of every generator -> half storage / half flops
+        h->iso = false;
+        if (h->large && h->d % 128 == 0 && !getenv("QCB_NO_ISO")) {
+            const int n = h->d / 2;
+            auto is_iso = [&](const double *M) {
+                for (int j = 0; j < n; ++j)
+                    for (int i = 0; i < n; ++i) {
+                        if (M[(i + n) + (size_t)(j + n) * h->d] != M[i + (size_t)j * h->d]) return false;
+                        if (M[i + (size_t)(j + n) * h->d] != -M[(i + n) + (size_t)j * h->d]) return false;
+                    }
+                return true;
+            };
+            bool ok = true;
+            for (int s = 0; s < h->S && ok; ++s) {
+                ok = is_iso(desc->G_drift + (size_t)s * h->d * h->d);
+                for (int j = 0; j < h->m && ok; ++j) ok = is_iso(desc->G_drives + ((size_t)s * h->m + j) * h->d * h->d);
+            }
+            h->iso = ok;
+        }
+        h->gcols = h->iso ? h->dp / 2 : h->dp;
+        h->msz = (int64_t)h->dp * h->gcols;
         h->small_threads = std::min(512, std::max(32, round_up(h->d * h->d, 32)));
         const int64_t xb = h->jac_mode == QCB_JAC_DENSE_X ? (int64_t)xdim * xdim : (int64_t)h->c * h->d * h->d;
         h->jnnz_unit = xb + (int64_t)xdim * (h->m + 2);
         h->hnnz_unit = (int64_t)xdim * (h->m + 1) + (int64_t)h->m * (h->m + 1) / 2 + h->m + 1;
-        const int64_t dd = (int64_t)h->dp * h->dp, pan = (int64_t)h->dp * h->cp;
+        const int64_t dd = h->msz, pan = (int64_t)h->dp * h->cp;
         h->JA = dd + (h->m + 1) * pan + 2;
         h->HA = (h->m + 1) * pan + (int64_t)h->m * h->m + h->m + 2;
         h->HA += h->HA & 1;
@@ -652,11 +723,12 @@ qcb_status qcb_create(qcb_handle *out, const qcb_desc *desc) {
         {
             std::vector<double> g0((size_t)h->S * dd, 0.0), gd((size_t)h->S * std::max(1, h->m) * dd, 0.0);
             for (int s = 0; s < h->S; ++s) {
-                for (int q = 0; q < h->d; ++q)
+                const int qmax = h->iso ? h->d / 2 : h->d;    // iso: only the left block column is kept
+                for (int q = 0; q < qmax; ++q)
                     for (int r = 0; r < h->d; ++r)
                         g0[(size_t)s * dd + r + (size_t)q * h->dp] = desc->G_drift[(size_t)s * h->d * h->d + r + (size_t)q * h->d];
                 for (int j = 0; j < h->m; ++j)
-                    for (int q = 0; q < h->d; ++q)
+                    for (int q = 0; q < qmax; ++q)
                         for (int r = 0; r < h->d; ++r)
                             gd[((size_t)s * h->m + j) * dd + r + (size_t)q * h->dp] =
                                 desc->G_drives[((size_t)s * h->m + j) * h->d * h->d + r + (size_t)q * h->d];

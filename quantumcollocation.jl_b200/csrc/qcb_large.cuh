@@ -202,6 +202,206 @@ bgemm_kernel(const __grid_constant__ GemmArgs g) {
 }
 
 // ---------------------------------------------------------------------------------------
+// Real-iso half-storage GEMM.
+//
+// Every matrix the program touches for a quantum generator G = iso(-iH) (closed or Lindblad)
+// has the block form  M = [[P, -Q], [Q, P]]  (n x n blocks, d = 2n), and so do products, sums and
+// transposes of such matrices.  Only the left block column M_L = [P; Q] (d x n, i.e. the first
+// d*n doubles of the column-major matrix) is stored and computed:
+//     [op(A) op(B)]_L = op(A)_full * op(B)_L          (d x d) * (d x n): half the flops of d^3.
+// The full left operand is reconstructed while loading tiles:
+//     X_full(i, j) = X_L(i, j)                      j <  n
+//                  = -X_L(i + n, j - n)             j >= n, i <  n
+//                  =  X_L(i - n, j - n)             j >= n, i >= n
+// (rows rotated by n, sign on the top half), and  (Y^T)_L(k, c) = Y_L(c, k) for k < n,
+// -Y_L(c + n, k - n) for k >= n.  The sign is uniform per (warp row-half, K slab) and is applied to
+// the A fragments with one integer XOR each.  The right operand may also be a plain d x N panel
+// (tb = 0 reads it as is), which is how E X, L_j X, L_j^T M are formed without expanding E, L_j.
+// Tile 128 x 64, 8 warps (32 x 32 each), 3-stage cp.async ring -> 2 CTAs per SM, so one CTA's
+// epilogue overlaps the other's DMMA main loop.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ double flip_sign(double v, unsigned mask) {
+    return __hiloint2double(__double2hiint(v) ^ (int)mask, __double2loint(v));
+}
+
+template <int STAGES>
+__global__ void __launch_bounds__(256, 2)
+bgemm_iso_kernel(const __grid_constant__ GemmArgs g) {
+    constexpr int BM = 128, BN = 64, WM = 32, WN = 32, BK = GEMM_BK, NTHR = 256;
+    constexpr int MT = WM / 16, NT = WN / 8;
+    constexpr int A_ST = GemmSmem<BM, BN>::A_ST, B_ST = GemmSmem<BM, BN>::B_ST;
+    extern __shared__ __align__(16) double smem[];
+    double *As = smem, *Bs = smem + STAGES * A_ST;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int gid = lane >> 2, tig = lane & 3;
+    const int wm = warp & 3, wn = warp >> 2;
+    const int tiles_n = g.N / BN, tiles = (g.M / BM) * tiles_n;
+    const int batch = blockIdx.x / tiles, tile = blockIdx.x % tiles;
+    const int m0 = (tile / tiles_n) * BM, n0 = (tile % tiles_n) * BN;
+    const int unit = batch / g.ndir, dir = batch % g.ndir;
+    const int sys = (g.unit0_global + unit) / g.nk;
+    const long long ou = unit, od = dir, os = sys;
+    const int dfull = g.K, nh = g.K >> 1;          // d and n = d/2 (K is always the full dimension)
+    const bool warp_top = (m0 + wm * WM) < nh;     // rows of this warp lie in the top half
+
+    double acc[MT][NT][4];
+#pragma unroll
+    for (int i = 0; i < MT; ++i)
+#pragma unroll
+        for (int j = 0; j < NT; ++j)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[i][j][q] = 0.0;
+
+    const int kslabs = g.K / BK;
+    const int nit = g.nterm * kslabs;
+
+    auto load_stage = [&](int it, int stage) {
+        const GemmTerm &t = g.term[it / kslabs];
+        const int k0 = (it % kslabs) * BK;
+        const bool khi = k0 >= nh;
+        const double *pa = t.a.p + ou * t.a.su + od * t.a.sd + os * t.a.ss;
+        const double *pb = t.b.p + ou * t.b.su + od * t.b.sd + os * t.b.ss;
+        double *as = As + stage * A_ST, *bs = Bs + stage * B_ST;
+        if (!t.ta) {
+            // X_full(i, k): column (k mod n), rows rotated by n when k >= n
+            const int ksrc = khi ? k0 - nh : k0;
+            for (int ch = tid; ch < BK * (BM / 2); ch += NTHR) {
+                const int kc = ch / (BM / 2), r = 2 * (ch % (BM / 2));
+                int i = m0 + r;
+                if (khi) i = (i < nh) ? i + nh : i - nh;
+                cp_async16(as + kc * (BM + 4) + r, pa + i + (long long)(ksrc + kc) * t.a.ld);
+            }
+        } else {
+            // X_full(k, i): i < n -> X_L(k, i);  i >= n -> +-X_L((k + n) mod d, i - n)
+            for (int ch = tid; ch < BM * (BK / 2); ch += NTHR) {
+                const int r = ch / (BK / 2), k2 = 2 * (ch % (BK / 2));
+                const int i = m0 + r;
+                const bool ihi = i >= nh;
+                int k = k0 + k2;
+                if (ihi) k = khi ? k - nh : k + nh;
+                cp_async16(as + r * (BK + 4) + k2, pa + k + (long long)(ihi ? i - nh : i) * t.a.ld);
+            }
+        }
+        if (!t.tb) {
+            for (int ch = tid; ch < BN * (BK / 2); ch += NTHR) {
+                const int n = ch / (BK / 2), k2 = 2 * (ch % (BK / 2));
+                cp_async16(bs + n * (BK + 4) + k2, pb + (k0 + k2) + (long long)(n0 + n) * t.b.ld);
+            }
+        } else {
+            // (Y^T)_L(k, c) = Y_L(c, k) (k < n) or -Y_L(c + n, k - n)
+            const int ksrc = khi ? k0 - nh : k0, roff = khi ? nh : 0;
+            for (int ch = tid; ch < BK * (BN / 2); ch += NTHR) {
+                const int kc = ch / (BN / 2), n2 = 2 * (ch % (BN / 2));
+                cp_async16(bs + kc * (BN + 4) + n2, pb + (roff + n0 + n2) + (long long)(ksrc + kc) * t.b.ld);
+            }
+        }
+    };
+
+#pragma unroll
+    for (int s = 0; s < STAGES - 1; ++s) {
+        if (s < nit) load_stage(s, s);
+        cp_async_commit();
+    }
+    for (int it = 0; it < nit; ++it) {
+        cp_async_wait<STAGES - 2>();
+        __syncthreads();
+        {
+            int nx = it + STAGES - 1;
+            if (nx < nit) load_stage(nx, nx % STAGES);
+            cp_async_commit();
+        }
+        const GemmTerm &t = g.term[it / kslabs];
+        const bool khi = ((it % kslabs) * BK) >= nh;
+        // sign of this (warp, slab):  left operand  ta=0: -(khi && top);  ta=1: -(bottom && !khi);
+        //                             right operand tb=1: -khi
+        bool neg = t.ta ? (!warp_top && !khi) : (warp_top && khi);
+        if (t.tb && khi) neg = !neg;
+        const unsigned smask = neg ? 0x80000000u : 0u;
+        const int a_rs = t.ta ? (BK + 4) : 1, a_ks = t.ta ? 1 : (BM + 4);
+        const int b_ks = t.tb ? (BN + 4) : 1, b_ns = t.tb ? 1 : (BK + 4);
+        const double *as = As + (it % STAGES) * A_ST + (wm * WM + gid) * a_rs + tig * a_ks;
+        const double *bs = Bs + (it % STAGES) * B_ST + (wn * WN + gid) * b_ns + tig * b_ks;
+#pragma unroll
+        for (int kk = 0; kk < BK; kk += 4) {
+            double a0[MT], a1[MT], b[NT];
+#pragma unroll
+            for (int i = 0; i < MT; ++i) {
+                a0[i] = flip_sign(as[(i * 16) * a_rs + kk * a_ks], smask);
+                a1[i] = flip_sign(as[(i * 16 + 8) * a_rs + kk * a_ks], smask);
+            }
+#pragma unroll
+            for (int j = 0; j < NT; ++j) b[j] = bs[(j * 8) * b_ns + kk * b_ks];
+#pragma unroll
+            for (int i = 0; i < MT; ++i)
+#pragma unroll
+                for (int j = 0; j < NT; ++j) dmma_16x8x4(acc[i][j], a0[i], a1[i], b[j]);
+        }
+    }
+    cp_async_wait<0>();
+    (void)dfull;
+
+    __syncthreads();
+    constexpr int LDC = BM + 2;
+    double *Cs = smem;
+#pragma unroll
+    for (int i = 0; i < MT; ++i)
+#pragma unroll
+        for (int j = 0; j < NT; ++j)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                int r = wm * WM + i * 16 + gid + (q >> 1) * 8;
+                int c = wn * WN + j * 8 + tig * 2 + (q & 1);
+                Cs[c * LDC + r] = acc[i][j][q];
+            }
+    __syncthreads();
+    double sc = g.alpha;
+    if (g.unit_scale) sc *= g.unit_scale[unit];
+    double *pd = const_cast<double *>(g.dst.p) + ou * g.dst.su + od * g.dst.sd + os * g.dst.ss;
+    const double *pl[4];
+    double cf[4];
+    long long ldl[4];
+#pragma unroll
+    for (int l = 0; l < 4; ++l) {
+        const bool on = l < g.nlin;
+        pl[l] = on ? g.lin[l].p + ou * g.lin[l].su + od * g.lin[l].sd + os * g.lin[l].ss : nullptr;
+        cf[l] = on ? g.lin_coef[l] : 0.0;
+        ldl[l] = on ? g.lin[l].ld : 0;
+    }
+    for (int idx = tid; idx < (BM / 2) * BN; idx += NTHR) {
+        const int r = 2 * (idx % (BM / 2)), c = idx / (BM / 2);
+        double2 v = *reinterpret_cast<const double2 *>(Cs + c * LDC + r);
+        v.x *= sc; v.y *= sc;
+#pragma unroll
+        for (int l = 0; l < 4; ++l)
+            if (pl[l]) {
+                const double2 t = *reinterpret_cast<const double2 *>(pl[l] + (m0 + r) + (long long)(n0 + c) * ldl[l]);
+                v.x = fma(cf[l], t.x, v.x); v.y = fma(cf[l], t.y, v.y);
+            }
+        const int gr = m0 + r, gc = n0 + c;
+        if (gc == gr && gr < g.d_ident) v.x += g.ident;
+        if (gc == gr + 1 && gc < g.d_ident) v.y += g.ident;
+        *reinterpret_cast<double2 *>(pd + gr + (long long)gc * g.dst.ld) = v;
+    }
+}
+
+// W_L = left block column of the projection of a general d x d matrix onto the iso algebra:
+//   P = (W11 + W22)/2,  Q = (W21 - W12)/2.   (<W, F> = <proj W, F> for every iso matrix F.)
+__global__ void __launch_bounds__(256)
+iso_project_kernel(const double *Wfull, long long w_stride, double *WL, long long wl_stride, int d) {
+    const int n = d >> 1;
+    const double *W = Wfull + (long long)blockIdx.x * w_stride;
+    double *o = WL + (long long)blockIdx.x * wl_stride;
+    for (int e = threadIdx.x; e < d * n; e += blockDim.x) {
+        const int i = e % d, j = e / d;
+        double v;
+        if (i < n) v = 0.5 * (W[i + (long long)j * d] + W[(i + n) + (long long)(j + n) * d]);
+        else v = 0.5 * (W[i + (long long)j * d] - W[(i - n) + (long long)(j + n) * d]);
+        o[e] = v;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
 // Frobenius contractions  out[unit][j*ni + i] (+)= < P(unit, j), Q(unit|sys, i) >
 // ---------------------------------------------------------------------------------------
 constexpr int CONTRACT_MAXI = 32;
@@ -295,6 +495,8 @@ __global__ void __launch_bounds__(256) contract_mma_kernel(const __grid_constant
 // ---------------------------------------------------------------------------------------
 struct UnitGeom {
     int d, c, m, dp, cp, z_dim, u_off, dt_off, K, nk, k_begin, S;
+    int gcols;               // stored columns of every generator-like matrix: dp, or dp/2 in iso half storage
+    long long gsz;           // doubles per stored matrix = dp * gcols
     const int *x_off;        // device [S]
     const double *G0, *Gd;   // device, padded: [S][dp*dp], [S][m][dp*dp]
 };
@@ -307,14 +509,14 @@ build_G_kernel(UnitGeom q, const double *Z, int u0_global, double *Gout, long lo
     const int unit = blockIdx.x, ug = u0_global + unit;
     const int sys = ug / q.nk, k = q.k_begin + ug % q.nk;
     const double *zk = Z + (long long)k * q.z_dim;
-    const long long dd = (long long)q.dp * q.dp;
+    const long long dd = q.gsz;
     const double *G0 = q.G0 + sys * dd, *Gd = q.Gd + (long long)sys * q.m * dd;
     double *G = Gout ? Gout + (long long)unit * g_stride : nullptr;
     const double dt = zk[q.dt_off];
     __shared__ double colsum[8];
     double worst = 0.0;
     int bad = !isfinite(dt);
-    for (int col = 0; col < q.dp; ++col) {
+    for (int col = 0; col < q.gcols; ++col) {   // iso half storage: the right half has the same column sums
         double part = 0.0;
         for (int r = threadIdx.x; r < q.dp; r += blockDim.x) {
             long long e = r + (long long)col * q.dp;
@@ -351,7 +553,7 @@ prep_unit_kernel(UnitGeom q, const double *Z, const double *mu, int u0_global, i
     const int sys = ug / q.nk, kl = ug % q.nk, k = q.k_begin + kl;
     const double *zk = Z + (long long)k * q.z_dim;
     const double tau = ldexp(zk[q.dt_off], -s_levels);
-    const long long dd = (long long)q.dp * q.dp;
+    const long long dd = q.gsz;
     const double *Gu = G + (long long)unit * mat_stride;
     double *Au = A + (long long)unit * mat_stride;
     for (long long e = threadIdx.x; e < dd; e += blockDim.x) Au[e] = tau * Gu[e];
@@ -370,18 +572,19 @@ prep_unit_kernel(UnitGeom q, const double *Z, const double *mu, int u0_global, i
 // Hessian scalar blocks of one unit: HUU = -tau^2/2 (H + H^T), HUT_j = -(c1_j + tau c2_j), HTT = -c3
 __global__ void finalize_scalars_kernel(int m, const double *tau, const double *H, const double *c1,
                                         const double *c2, const double *c3, double *harena,
-                                        long long harena_stride, long long off_huu) {
+                                        long long harena_stride, long long off_huu, double fac) {
+    // fac = 2 in iso half storage: <S, L>_full = 2 <S_L, L_L>
     const int unit = blockIdx.x;
     const double t = tau[unit];
     double *out = harena + (long long)unit * harena_stride + off_huu;
     const double *Hu = H + (long long)unit * m * m;
     for (int e = threadIdx.x; e < m * m; e += blockDim.x) {
         int i = e / m, j = e % m;
-        out[e] = -0.5 * t * t * (Hu[i * m + j] + Hu[j * m + i]);
+        out[e] = -0.5 * fac * t * t * (Hu[i * m + j] + Hu[j * m + i]);
     }
     for (int j = threadIdx.x; j < m; j += blockDim.x)
-        out[m * m + j] = -(c1[(long long)unit * m + j] + t * c2[(long long)unit * m + j]);
-    if (threadIdx.x == 0) { out[m * m + m] = -c3[unit]; out[m * m + m + 1] = 0.0; }
+        out[m * m + j] = -fac * (c1[(long long)unit * m + j] + t * c2[(long long)unit * m + j]);
+    if (threadIdx.x == 0) { out[m * m + m] = -fac * c3[unit]; out[m * m + m + 1] = 0.0; }
 }
 
 // constants 0.0 / 1.0 at the tail of the Jacobian arena
