@@ -322,12 +322,12 @@ def main():
         dt = max_over_ranks(time.perf_counter() - t0)
         barrier()
         tm = ev.timings()
-        h2d = 8 * ((k1 - k0 + 1) * L.z_dim + L.S * (k1 - k0) * L.x_dim)
-        d2h = 8 * (ev.defect_dim + ev.jacobian_nnz + ev.hessian_nnz)
+        h2d, d2h = ev.transfer_bytes()            # what the last call really moved over PCIe
+        host_written = 8 * (ev.defect_dim + ev.jacobian_nnz + ev.hessian_nnz)
         if world > 1:
-            t_h2d = torch.tensor([h2d, d2h], dtype=torch.float64, device=dev)
+            t_h2d = torch.tensor([h2d, d2h, host_written], dtype=torch.float64, device=dev)
             dist.all_reduce(t_h2d)
-            h2d, d2h = int(t_h2d[0].item()), int(t_h2d[1].item())
+            h2d, d2h, host_written = int(t_h2d[0].item()), int(t_h2d[1].item()), int(t_h2d[2].item())
             # spot check: the shared buffer holds every rank's slab
             if rank == 0:
                 chk = buf[offs[2]:offs[2] + n_delta]
@@ -340,7 +340,8 @@ def main():
             if rank == 0:
                 shm.unlink()
         e2e = {"value": units_total / (dt / args.steps), "unit": "knot-evals/s", "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * dt / args.steps,
+               "d2h_bytes_per_step": int(d2h), "host_result_bytes_per_step": int(host_written),
+               "ms_per_step": 1e3 * dt / args.steps,
                "last_call_rank0_ms": tm}
 
     # ---------------- CPU baseline (rank 0, N = 1 only) ----------------

@@ -131,6 +131,10 @@ void qcb_host_free(void *ptr);
  * last host-buffer call in milliseconds: [0] H2D, [1] kernels, [2] D2H, [3] total. */
 int64_t qcb_kernel_launches(qcb_handle h);
 qcb_status qcb_get_timings(qcb_handle h, double ms[4]);
+/* Bytes the last host-buffer call moved over PCIe: [0] host->device, [1] device->host.  On the
+ * large-d path the device->host figure is the compact value arenas (every distinct number once);
+ * the COO vectors are written from them by the host cores.  No counterpart in the reference. */
+qcb_status qcb_get_transfer_bytes(qcb_handle h, int64_t bytes[2]);
 /* The CUDA stream (cudaStream_t) the handle launches on, for callers that time with events. */
 void *qcb_stream(qcb_handle h);
 /* Per-launch CUDA-event timing of the dominant kernel of the large-d path (the batched FP64

@@ -47,6 +47,7 @@ SYMBOLS = {
     "qcb_host_free": (None, [c_vp]),
     "qcb_kernel_launches": (ctypes.c_int64, [c_vp]),
     "qcb_get_timings": (ctypes.c_int, [c_vp, c_dp]),
+    "qcb_get_transfer_bytes": (ctypes.c_int, [c_vp, c_lp]),
     "qcb_stream": (c_vp, [c_vp]),
     "qcb_profile_enable": (ctypes.c_int, [c_vp, ctypes.c_int32]),
     "qcb_profile_read": (ctypes.c_int, [c_vp, c_dp]),

@@ -150,6 +150,11 @@ class Evaluator:
         self.lib.qcb_get_timings(self.h, ms)
         return {"h2d_ms": ms[0], "kernels_ms": ms[1], "d2h_ms": ms[2], "total_ms": ms[3]}
 
+    def transfer_bytes(self):
+        b = (ctypes.c_int64 * 2)()
+        self.lib.qcb_get_transfer_bytes(self.h, b)
+        return int(b[0]), int(b[1])
+
     def profile(self, on: bool):
         self.lib.qcb_profile_enable(self.h, 1 if on else 0)
 

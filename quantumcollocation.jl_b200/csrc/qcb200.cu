@@ -5,8 +5,12 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
 #include <string>
+#include <thread>
 #include <vector>
+
+#include <immintrin.h>
 
 #include <cuda_runtime.h>
 
@@ -30,6 +34,11 @@ struct CudaFail { cudaError_t e; const char *what; int line; };
 
 struct Entry { int64_t row, col; uint32_t code; };
 
+// Run-length form of a unit's slot-code table, used by the host-side expansion of the compact
+// transfer (qcb_eval_all on the large-d path): copy / negated copy of `len` consecutive arena
+// entries, or `len` repeats of one entry.
+struct Seg { int64_t dst; uint32_t src; uint32_t len; uint32_t kind; };   // kind: bit0 negate, bit1 fill
+
 inline int round_up(int v, int q) { return (v + q - 1) / q * q; }
 
 }  // namespace
@@ -51,6 +60,7 @@ struct qcb_handle_s {
     std::vector<cudaEvent_t> chunk_events;
     int64_t launches = 0;
     double ms[4] = {0, 0, 0, 0};
+    int64_t xfer[2] = {0, 0};      // bytes moved host->device / device->host by the last host-buffer call
     // optional per-launch profiling of the batched DMMA GEMM (qcb_profile_*)
     bool profiling = false;
     std::vector<cudaEvent_t> prof_ev;     // pairs
@@ -78,6 +88,13 @@ struct qcb_handle_s {
     double *sc_XP = nullptr, *sc_MP = nullptr, *sc_EX = nullptr, *sc_ja = nullptr, *sc_ha = nullptr;
     double *sc_H = nullptr, *sc_c1 = nullptr, *sc_c2 = nullptr, *sc_c3 = nullptr, *sc_tau = nullptr, *sc_ntau = nullptr;
     int small_threads = 0;
+    // compact host transfer: arenas (not expanded COO vectors) cross PCIe, the host cores expand
+    std::vector<uint32_t> h_jcode, h_hcode;           // host copies of the code tables [S][nnz]
+    std::vector<std::vector<Seg>> jsegs, hsegs;       // per system
+    double *sc_ja2 = nullptr, *sc_ha2 = nullptr;      // second arena set (double buffering)
+    double *stage_j[2] = {nullptr, nullptr}, *stage_h[2] = {nullptr, nullptr};   // pinned
+    int stage_units = 0;
+    cudaEvent_t copied[2] = {nullptr, nullptr};
 
     UnitGeom geom() const {
         UnitGeom q;
@@ -164,6 +181,78 @@ std::vector<Entry> hess_pattern(qcb_handle_s *h, int s) {
     return v;
 }
 
+std::vector<Seg> build_segments(const uint32_t *code, int64_t nnz) {
+    std::vector<Seg> v;
+    int64_t e = 0;
+    while (e < nnz) {
+        const uint32_t c0 = code[e], off0 = c0 & 0x7fffffffu, neg = c0 >> 31;
+        int64_t len = 1;
+        uint32_t kind = neg;
+        if (e + 1 < nnz && code[e + 1] == c0) {                       // repeats of one entry
+            kind |= 2u;
+            while (e + len < nnz && code[e + len] == c0 && len < 0x7fffffff) ++len;
+        } else {
+            while (e + len < nnz && (code[e + len] >> 31) == neg &&
+                   (code[e + len] & 0x7fffffffu) == off0 + (uint32_t)len && len < 0x7fffffff) ++len;
+        }
+        v.push_back({e, off0, (uint32_t)len, kind});
+        e += len;
+    }
+    return v;
+}
+
+// dst[0..len) = +-src[0..len) with non-temporal 64-byte stores (the destination is written once
+// and never read by the library; streaming stores avoid the read-for-ownership traffic)
+__attribute__((target("avx512f"))) void copy_run_avx512(double *dst, const double *src, size_t len, bool neg) {
+    const __m512i sgn = neg ? _mm512_set1_epi64((long long)0x8000000000000000ull) : _mm512_setzero_si512();
+    size_t i = 0;
+    while (i < len && (reinterpret_cast<uintptr_t>(dst + i) & 63)) { dst[i] = neg ? -src[i] : src[i]; ++i; }
+    for (; i + 8 <= len; i += 8) _mm512_stream_pd(dst + i, _mm512_castsi512_pd(_mm512_xor_si512(_mm512_castpd_si512(_mm512_loadu_pd(src + i)), sgn)));
+    for (; i < len; ++i) dst[i] = neg ? -src[i] : src[i];
+}
+void copy_run_plain(double *dst, const double *src, size_t len, bool neg) {
+    if (neg) for (size_t i = 0; i < len; ++i) dst[i] = -src[i];
+    else memcpy(dst, src, len * sizeof(double));
+}
+__attribute__((target("avx512f"))) void fill_run_avx512(double *dst, double v, size_t len) {
+    const __m512d vv = _mm512_set1_pd(v);
+    size_t i = 0;
+    while (i < len && (reinterpret_cast<uintptr_t>(dst + i) & 63)) dst[i++] = v;
+    for (; i + 8 <= len; i += 8) _mm512_stream_pd(dst + i, vv);
+    for (; i < len; ++i) dst[i] = v;
+}
+
+// Expand `nu` units: out[(u0 + u) * nnz + seg.dst ...] from arena rows staged in host memory.
+void expand_units(const std::vector<std::vector<Seg>> &segs, int nk, int u0, int nu, const double *stage,
+                  int64_t arena_stride, double *out, int64_t nnz, int nthreads) {
+    static const bool has512 = __builtin_cpu_supports("avx512f");
+    std::atomic<int> next{0};
+    auto work = [&]() {
+        for (;;) {
+            const int u = next.fetch_add(1);
+            if (u >= nu) break;
+            const std::vector<Seg> &sg = segs[(size_t)((u0 + u) / nk)];
+            const double *ar = stage + (size_t)u * arena_stride;
+            double *o = out + (size_t)(u0 + u) * nnz;
+            for (const Seg &q : sg) {
+                const bool neg = q.kind & 1u;
+                if (q.kind & 2u) {
+                    const double v = neg ? -ar[q.src] : ar[q.src];
+                    if (has512) fill_run_avx512(o + q.dst, v, q.len);
+                    else for (uint32_t i = 0; i < q.len; ++i) o[q.dst + i] = v;
+                } else if (has512) copy_run_avx512(o + q.dst, ar + q.src, q.len, neg);
+                else copy_run_plain(o + q.dst, ar + q.src, q.len, neg);
+            }
+        }
+        if (has512) _mm_sfence();
+    };
+    const int nt = std::max(1, std::min(nthreads, nu));
+    std::vector<std::thread> th;
+    for (int t = 1; t < nt; ++t) th.emplace_back(work);
+    work();
+    for (auto &t : th) t.join();
+}
+
 void upload_codes(qcb_handle_s *h, uint32_t **dptr, const std::vector<uint32_t> &codes) {
     if (*dptr) { CK(cudaFree(*dptr)); *dptr = nullptr; }
     CK(cudaMalloc(dptr, codes.size() * sizeof(uint32_t)));
@@ -177,6 +266,7 @@ void build_native_codes(qcb_handle_s *h, bool jac, bool hess) {
             for (auto &e : jac_pattern(h, s)) codes.push_back(e.code);
         upload_codes(h, &h->d_jcode, codes);
         h->custom_j = false;
+        h->h_jcode = codes;
     }
     if (hess) {
         std::vector<uint32_t> codes;
@@ -184,6 +274,7 @@ void build_native_codes(qcb_handle_s *h, bool jac, bool hess) {
             for (auto &e : hess_pattern(h, s)) codes.push_back(e.code);
         upload_codes(h, &h->d_hcode, codes);
         h->custom_h = false;
+        h->h_hcode = codes;
     }
 }
 
@@ -262,12 +353,13 @@ struct LargeExec {
     int level = 0;
     int cur = 0;   // which L buffer holds the current level
     long long dd, pan;
+    double *ja = nullptr, *ha = nullptr;   // value arenas of this chunk
 
     Opnd mat(double *base, long long su, long long sd = 0, long long ss = 0) const {
         Opnd o; o.p = base; o.su = su; o.sd = sd; o.ss = ss; o.ld = h->dp; o.pad_ = 0; return o;
     }
     Opnd E(int lvl) const {
-        if (lvl == s) return mat(h->sc_ja, h->JA);
+        if (lvl == s) return mat(ja, h->JA);
         return mat(h->sc_E + (long long)lvl * h->chunk_units * dd, dd);
     }
     Opnd W(int lvl) const { return mat(h->sc_W + (long long)lvl * h->chunk_units * dd, dd); }
@@ -349,7 +441,37 @@ void free_scratch(qcb_handle_s *h) {
                        &h->sc_EX, &h->sc_ja, &h->sc_ha, &h->sc_H, &h->sc_c1, &h->sc_c2, &h->sc_c3, &h->sc_tau, &h->sc_ntau};
     for (auto p : ptrs)
         if (*p) { cudaFree(*p); *p = nullptr; }
+    if (h->sc_ja2) { cudaFree(h->sc_ja2); h->sc_ja2 = nullptr; }
+    if (h->sc_ha2) { cudaFree(h->sc_ha2); h->sc_ha2 = nullptr; }
+    for (int b = 0; b < 2; ++b) {
+        if (h->stage_j[b]) { cudaFreeHost(h->stage_j[b]); h->stage_j[b] = nullptr; }
+        if (h->stage_h[b]) { cudaFreeHost(h->stage_h[b]); h->stage_h[b] = nullptr; }
+    }
+    h->stage_units = 0;
     h->s_cap = -1;
+}
+
+// buffers of the compact host transfer (second arena set, pinned staging, run-length tables)
+void ensure_compact(qcb_handle_s *h) {
+    if (h->stage_units != h->chunk_units) {
+        const size_t n = (size_t)h->chunk_units;
+        CK(cudaMalloc(&h->sc_ja2, n * (size_t)h->JA * 8));
+        CK(cudaMalloc(&h->sc_ha2, n * (size_t)h->HA * 8));
+        for (int b = 0; b < 2; ++b) {
+            CK(cudaMallocHost(&h->stage_j[b], n * (size_t)h->JA * 8));
+            CK(cudaMallocHost(&h->stage_h[b], n * (size_t)h->HA * 8));
+            if (!h->copied[b]) CK(cudaEventCreateWithFlags(&h->copied[b], cudaEventDisableTiming));
+        }
+        h->stage_units = h->chunk_units;
+    }
+    if (h->jsegs.empty()) {
+        h->jsegs.resize(h->S);
+        for (int s = 0; s < h->S; ++s) h->jsegs[s] = build_segments(h->h_jcode.data() + (size_t)s * h->jnnz_unit, h->jnnz_unit);
+    }
+    if (h->hsegs.empty()) {
+        h->hsegs.resize(h->S);
+        for (int s = 0; s < h->S; ++s) h->hsegs[s] = build_segments(h->h_hcode.data() + (size_t)s * h->hnnz_unit, h->hnnz_unit);
+    }
 }
 
 size_t scratch_bytes_per_unit(const qcb_handle_s *h, int s_cap) {
@@ -402,7 +524,7 @@ void ensure_scratch(qcb_handle_s *h, int s_need) {
     h->s_cap = s_cap;
 }
 
-struct HostOut { double *delta, *jac, *hess; };
+struct HostOut { double *delta, *jac, *hess; bool compact; };
 
 // norm pre-pass over the whole slab -> uniform number of squarings (or -1)
 int slab_squarings(qcb_handle_s *h, const double *dZ) {
@@ -430,11 +552,30 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     const int m = h->m;
     const int ncol = h->gcols;                       // columns of a stored matrix (dp, or dp/2 in iso mode)
     UnitGeom q = h->geom();
+    const bool compact = host && host->compact && (wj || wh);
+    if (compact) ensure_compact(h);
+    const int nthreads = (int)std::max(1u, std::thread::hardware_concurrency());
+    int prev_u0 = -1, prev_nu = 0;           // chunk whose arenas are staged on the host, not yet expanded
+    auto expand_prev = [&](size_t idx_prev) {
+        if (prev_u0 < 0) return;
+        const int b = (int)(idx_prev & 1);
+        CK(cudaEventSynchronize(h->copied[b]));
+        if (wj && host->jac)
+            expand_units(h->jsegs, h->nk, prev_u0, prev_nu, h->stage_j[b], h->JA, host->jac, h->jnnz_unit, nthreads);
+        if (wh && host->hess)
+            expand_units(h->hsegs, h->nk, prev_u0, prev_nu, h->stage_h[b], h->HA, host->hess, h->hnnz_unit, nthreads);
+        prev_u0 = -1;
+    };
     size_t chunk_idx = 0;
     for (int u0 = 0; u0 < h->units; u0 += h->chunk_units, ++chunk_idx) {
         const int nu = std::min(h->chunk_units, h->units - u0);
         LargeExec X{h, nu, u0, s};
         X.dd = dd; X.pan = pan;
+        const int buf = compact ? (int)(chunk_idx & 1) : 0;
+        X.ja = buf ? h->sc_ja2 : h->sc_ja;
+        X.ha = buf ? h->sc_ha2 : h->sc_ha;
+        // the D2H of chunk idx-2 read this arena set: let it finish before overwriting
+        if (compact && chunk_idx >= 2) CK(cudaStreamWaitEvent(h->stream, h->copied[buf], 0));
         Opnd G = X.fixed(QR_G), A = X.fixed(QR_A);
         build_G_kernel<<<nu, 256, 0, h->stream>>>(q, dZ, u0, const_cast<double *>(G.p), dd, h->d_norm, h->d_bad);
         ++h->launches;
@@ -487,14 +628,14 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             // final blocks
             Opnd GE = X.fixed(QR_A2), WE = X.fixed(QR_A3), GW = X.fixed(QR_A4), L = X.reg(QR_L);
             X.product(GE, G, 0, Ef, 0, h->dp, ncol, h->dp, 1, 1.0, nullptr);
-            Opnd JU = X.mat(h->sc_ja + dd, h->JA, pan), JT = X.mat(h->sc_ja + dd + m * pan, h->JA);
+            Opnd JU = X.mat(X.ja + dd, h->JA, pan), JT = X.mat(X.ja + dd + m * pan, h->JA);
             if (m > 0) X.product(JU, L, 0, XP, 0, h->dp, h->cp, h->dp, m, 1.0, h->sc_ntau);
             X.product(JT, GE, 0, XP, 0, h->dp, h->cp, h->dp, 1, -1.0, nullptr);
-            arena_consts_kernel<<<(nu + 127) / 128, 128, 0, h->stream>>>(h->sc_ja, h->JA, dd + (m + 1) * pan, nu);
+            arena_consts_kernel<<<(nu + 127) / 128, 128, 0, h->stream>>>(X.ja, h->JA, dd + (m + 1) * pan, nu);
             ++h->launches;
             if (wh) {
                 Opnd Wt = X.W(s);
-                Opnd HXU = X.mat(h->sc_ha, h->HA, pan), HXT = X.mat(h->sc_ha + m * pan, h->HA);
+                Opnd HXU = X.mat(X.ha, h->HA, pan), HXT = X.mat(X.ha + m * pan, h->HA);
                 if (m > 0) X.product(HXU, L, 1, MP, 0, h->dp, h->cp, h->dp, m, 1.0, h->sc_ntau);
                 X.product(HXT, GE, 1, MP, 0, h->dp, h->cp, h->dp, 1, -1.0, nullptr);
                 X.product(WE, Wt, 0, Ef, 1, h->dp, ncol, h->dp, 1, 1.0, nullptr);
@@ -505,17 +646,17 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
                 }
                 X.contract(GW, 1, GE, 1, h->sc_c3, 0);
                 finalize_scalars_kernel<<<nu, 64, 0, h->stream>>>(m, h->sc_tau, h->sc_H, h->sc_c1, h->sc_c2, h->sc_c3,
-                                                                  h->sc_ha, h->HA, (m + 1) * pan, h->iso ? 2.0 : 1.0);
+                                                                  X.ha, h->HA, (m + 1) * pan, h->iso ? 2.0 : 1.0);
                 ++h->launches;
             }
-            if (wj && d_jac) {
+            if (wj && d_jac && !compact) {
                 int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->jnnz_unit / 4096));
-                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(h->sc_ja, h->JA, h->d_jcode, h->jnnz_unit, d_jac, u0, h->nk, cpu);
+                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ja, h->JA, h->d_jcode, h->jnnz_unit, d_jac, u0, h->nk, cpu);
                 ++h->launches;
             }
-            if (wh && d_hess) {
+            if (wh && d_hess && !compact) {
                 int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->hnnz_unit / 4096));
-                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(h->sc_ha, h->HA, h->d_hcode, h->hnnz_unit, d_hess, u0, h->nk, cpu);
+                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ha, h->HA, h->d_hcode, h->hnnz_unit, d_hess, u0, h->nk, cpu);
                 ++h->launches;
             }
         }
@@ -531,14 +672,27 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             if (host->delta)
                 CK(cudaMemcpyAsync(host->delta + (size_t)u0 * h->xdim, d_delta + (size_t)u0 * h->xdim,
                                    (size_t)nu * h->xdim * 8, cudaMemcpyDeviceToHost, h->copy_stream));
-            if (wj && host->jac)
-                CK(cudaMemcpyAsync(host->jac + (size_t)u0 * h->jnnz_unit, d_jac + (size_t)u0 * h->jnnz_unit,
-                                   (size_t)nu * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
-            if (wh && host->hess)
-                CK(cudaMemcpyAsync(host->hess + (size_t)u0 * h->hnnz_unit, d_hess + (size_t)u0 * h->hnnz_unit,
-                                   (size_t)nu * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+            if (compact) {
+                // compact transfer: the value arenas (every distinct number once) cross PCIe; the
+                // host cores write the COO vectors from them while the GPU works on the next chunk
+                if (wj && host->jac)
+                    CK(cudaMemcpyAsync(h->stage_j[buf], X.ja, (size_t)nu * h->JA * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                if (wh && host->hess)
+                    CK(cudaMemcpyAsync(h->stage_h[buf], X.ha, (size_t)nu * h->HA * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                CK(cudaEventRecord(h->copied[buf], h->copy_stream));
+                expand_prev(chunk_idx - 1);
+                prev_u0 = u0; prev_nu = nu;
+            } else {
+                if (wj && host->jac)
+                    CK(cudaMemcpyAsync(host->jac + (size_t)u0 * h->jnnz_unit, d_jac + (size_t)u0 * h->jnnz_unit,
+                                       (size_t)nu * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                if (wh && host->hess)
+                    CK(cudaMemcpyAsync(host->hess + (size_t)u0 * h->hnnz_unit, d_hess + (size_t)u0 * h->hnnz_unit,
+                                       (size_t)nu * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+            }
         }
     }
+    if (compact) expand_prev(chunk_idx - 1);
 }
 
 void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_delta, double *d_jac,
@@ -763,6 +917,7 @@ void qcb_destroy(qcb_handle h) {
     for (auto &e : h->ev)
         if (e) cudaEventDestroy(e);
     for (auto &e : h->chunk_events) cudaEventDestroy(e);
+    for (auto &e : h->copied) if (e) cudaEventDestroy(e);
     for (auto &e : h->prof_ev) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
@@ -774,6 +929,12 @@ int64_t qcb_jacobian_nnz(qcb_handle h) { return h ? (int64_t)h->units * h->jnnz_
 int64_t qcb_hessian_nnz(qcb_handle h) { return h ? (int64_t)h->units * h->hnnz_unit : 0; }
 int64_t qcb_kernel_launches(qcb_handle h) { return h ? h->launches : 0; }
 void *qcb_stream(qcb_handle h) { return h ? (void *)h->stream : nullptr; }
+
+qcb_status qcb_get_transfer_bytes(qcb_handle h, int64_t bytes[2]) {
+    if (!h || !bytes) return QCB_ERR_ARG;
+    bytes[0] = h->xfer[0]; bytes[1] = h->xfer[1];
+    return QCB_OK;
+}
 
 qcb_status qcb_profile_enable(qcb_handle h, int32_t on) {
     if (!h) return QCB_ERR_ARG;
@@ -855,6 +1016,8 @@ qcb_status qcb_set_structure(qcb_handle h, int64_t row_base, const int64_t *jr, 
             upload_codes(h, &h->d_jcode, codes);
             h->jnnz_unit = per;
             h->custom_j = true;
+            h->h_jcode = codes;
+            h->jsegs.clear();
             if (h->d_jac) { CK(cudaFree(h->d_jac)); h->d_jac = nullptr; }
         }
         if (hr && hc && hn > 0) {
@@ -890,6 +1053,8 @@ qcb_status qcb_set_structure(qcb_handle h, int64_t row_base, const int64_t *jr, 
             upload_codes(h, &h->d_hcode, codes);
             h->hnnz_unit = per;
             h->custom_h = true;
+            h->h_hcode = codes;
+            h->hsegs.clear();
             if (h->d_hess) { CK(cudaFree(h->d_hess)); h->d_hess = nullptr; }
         }
     } catch (const CudaFail &f) {
@@ -917,10 +1082,14 @@ qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu, double 
     try {
         CK(cudaSetDevice(h->device));
         const size_t nz = (size_t)h->N * h->z_dim, nmu = (size_t)h->S * h->K * h->xdim;
+        // large-d path: send the compact value arenas over PCIe and expand on the host cores
+        // (QCB_E2E_DIRECT=1 restores device-side assembly + full-size D2H)
+        const bool compact = h->large && (jac || hess) && !getenv("QCB_E2E_DIRECT");
         ensure_out(h, &h->dZ, nz);
         ensure_out(h, &h->d_delta, (size_t)h->units * h->xdim);
-        if (jac) ensure_out(h, &h->d_jac, (size_t)h->units * h->jnnz_unit);
-        if (hess) { ensure_out(h, &h->dmu, nmu); ensure_out(h, &h->d_hess, (size_t)h->units * h->hnnz_unit); }
+        if (jac && !compact) ensure_out(h, &h->d_jac, (size_t)h->units * h->jnnz_unit);
+        if (hess) ensure_out(h, &h->dmu, nmu);
+        if (hess && !compact) ensure_out(h, &h->d_hess, (size_t)h->units * h->hnnz_unit);
         CK(cudaEventRecord(h->ev[0], h->stream));
         // only the knots of this slab (plus the halo knot k_end) are needed on the device
         CK(cudaMemcpyAsync(h->dZ + (size_t)h->k0 * h->z_dim, Z + (size_t)h->k0 * h->z_dim,
@@ -931,11 +1100,18 @@ qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu, double 
                 CK(cudaMemcpyAsync(h->dmu + off, mu + off, (size_t)h->nk * h->xdim * 8, cudaMemcpyHostToDevice, h->stream));
             }
         }
+        h->xfer[0] = (int64_t)(h->nk + 1) * h->z_dim * 8 + (hess ? (int64_t)h->S * h->nk * h->xdim * 8 : 0);
+        h->xfer[1] = (delta ? (int64_t)h->units * h->xdim * 8 : 0)
+                   + (jac ? (int64_t)h->units * (compact ? h->JA : h->jnnz_unit) * 8 : 0)
+                   + (hess ? (int64_t)h->units * (compact ? h->HA : h->hnnz_unit) * 8 : 0);
         CK(cudaEventRecord(h->ev[1], h->stream));
-        HostOut ho{delta, jac, hess};
+        HostOut ho{delta, jac, hess, compact};
         int want = (jac ? 1 : 0) | (hess ? 2 : 0);
-        qcb_status st = eval_device(h, h->dZ, hess ? h->dmu : nullptr, h->d_delta, jac ? h->d_jac : nullptr,
-                                    hess ? h->d_hess : nullptr, want, &ho);
+        // in compact mode no device COO buffer exists: a non-null tag keeps the "wanted" logic uniform
+        double *tag = reinterpret_cast<double *>(uintptr_t(8));
+        qcb_status st = eval_device(h, h->dZ, hess ? h->dmu : nullptr, h->d_delta,
+                                    jac ? (compact ? tag : h->d_jac) : nullptr,
+                                    hess ? (compact ? tag : h->d_hess) : nullptr, want, &ho);
         CK(cudaEventRecord(h->ev[2], h->stream));
         CK(cudaEventSynchronize(h->ev[2]));
         float a = 0, b = 0;

@@ -318,3 +318,21 @@ def test_reference_multiket_and_sampling_dispatch(built_libs):
     d_f = fused.evaluate(np.zeros(fused.dim), trajs)
     d_s = np.concatenate([it.evaluate(np.zeros(it.dim), trajs) for it in ints])
     assert np.array_equal(d_f, d_s)
+
+
+@pytest.mark.parametrize("name,N,S", [("cfg3", 6, None), ("cfg4", 5, 3), ("cfg5", 4, None)])
+def test_large_path_compact_host_transfer_equals_direct(name, N, S, built_libs):
+    """qcb_eval_all on the large-d path ships the compact value arenas and expands them on the host
+    cores; QCB_E2E_DIRECT=1 selects device-side assembly + full-size D2H.  Same numbers either way."""
+    w = workloads.make(name, N=N, S=S)
+    ev = Evaluator(w.layout, w.G_drift, w.G_drives, force_path=2)
+    d1, j1, h1 = ev.eval_all(w.Z, w.mu)
+    os.environ["QCB_E2E_DIRECT"] = "1"
+    try:
+        d2, j2, h2 = ev.eval_all(w.Z, w.mu)
+    finally:
+        del os.environ["QCB_E2E_DIRECT"]
+    assert np.array_equal(d1, d2) and np.array_equal(j1, j2) and np.array_equal(h1, h2)
+    # Jacobian-only and Hessian-only callbacks through the compact route
+    assert np.array_equal(ev.eval_jacobian(w.Z), j1) and np.array_equal(ev.eval_hessian(w.Z, w.mu), h1)
+    ev.close()
