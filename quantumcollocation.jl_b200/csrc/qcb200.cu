@@ -695,19 +695,47 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     if (compact) expand_prev(chunk_idx - 1);
 }
 
+template <int D>
+void launch_small(qcb_handle_s *h, const SmallParams &p, size_t smem) {
+    auto kern = small_unit_kernel<D>;
+    CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int ctas = (p.units + p.upc - 1) / p.upc;
+    kern<<<ctas, p.upc * p.tpu, smem, h->stream>>>(p);
+}
+
 void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_delta, double *d_jac,
                 double *d_hess, int want, int s) {
     SmallParams p;
     p.d = h->d; p.c = h->c; p.m = h->m; p.z_dim = h->z_dim; p.u_off = h->u_off; p.dt_off = h->dt_off;
-    p.K = h->K; p.nk = h->nk; p.k_begin = h->k0; p.S = h->S;
+    p.K = h->K; p.nk = h->nk; p.k_begin = h->k0; p.S = h->S; p.units = h->units;
     p.x_off = h->d_xoff; p.G0 = h->dG0; p.Gd = h->dGd; p.Z = dZ; p.mu = dmu;
     p.delta = d_delta; p.jac = d_jac; p.hess = d_hess;
     p.jcode = h->d_jcode; p.hcode = h->d_hcode; p.jnnz = h->jnnz_unit; p.hnnz = h->hnnz_unit;
     p.want = want; p.smax = s; p.bad_flag = h->d_bad;
-    const size_t smem = small_smem_doubles(h->d, h->c, h->m, s) * sizeof(double);
-    if (smem > 227 * 1024) throw CudaFail{cudaErrorInvalidValue, "small-path shared memory exceeds 227 KB", __LINE__};
-    CK(cudaFuncSetAttribute(small_unit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    small_unit_kernel<<<h->units, h->small_threads, smem, h->stream>>>(p);
+    // threads per unit: one per matrix element, as a power of two <= 32 or a multiple of 32 (<= 512)
+    const int dd = h->d * h->d;
+    int tpu = 1;
+    if (dd <= 32) { while (tpu < dd) tpu <<= 1; } else tpu = std::min(512, round_up(dd, 32));
+    const size_t unit_d = small_unit_doubles(h->d, h->c, h->m, s);
+    if (small_smem_doubles(h->d, h->c, h->m, s, 1) * 8 > 227 * 1024)
+        throw CudaFail{cudaErrorInvalidValue, "small-path shared memory exceeds 227 KB", __LINE__};
+    // units per CTA: fill up to 512 threads / ~100 KB so that two CTAs share an SM
+    int upc = 1;
+    while (upc < 16 && (upc * 2) * tpu <= 256 && small_smem_doubles(h->d, h->c, h->m, s, upc * 2) * 8 <= 100 * 1024 &&
+           (long long)(upc * 2) * h->n_sm * 2 <= h->units)
+        upc *= 2;
+    p.tpu = tpu; p.upc = upc; p.unit_doubles = (int)unit_d;
+    const size_t smem = small_smem_doubles(h->d, h->c, h->m, s, upc) * sizeof(double);
+    switch (h->d) {
+    case 4: launch_small<4>(h, p, smem); break;
+    case 6: launch_small<6>(h, p, smem); break;
+    case 8: launch_small<8>(h, p, smem); break;
+    case 10: launch_small<10>(h, p, smem); break;
+    case 12: launch_small<12>(h, p, smem); break;
+    case 16: launch_small<16>(h, p, smem); break;
+    case 18: launch_small<18>(h, p, smem); break;
+    default: launch_small<0>(h, p, smem); break;
+    }
     ++h->launches;
     CK(cudaGetLastError());
 }

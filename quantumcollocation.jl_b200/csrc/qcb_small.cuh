@@ -1,8 +1,12 @@
-// qcb_small.cuh -- small-d path: one CTA per unit (interval k of system s), the whole matrix
-// program of qcb_program.h interpreted in a single launch with every virtual register in
-// shared memory.  G_drift / G_j are read through L1/L2 (they are shared by every unit of a
-// system); the unit's own state, multipliers and all intermediates never leave the SM; the
-// COO values are written once, coalesced, straight in the caller's sparsity order.
+// qcb_small.cuh -- small-d path: the whole matrix program of qcb_program.h for a unit (interval k
+// of system s) runs inside ONE launch with every virtual register in shared memory.  A CTA holds
+// `upc` units side by side, `tpu` threads each (one output element per thread and pass); the
+// squaring count is uniform per CTA (max over its units).  G_drift / G_j are read through L1/L2
+// (shared by every unit of a system); the unit's state, multipliers and all intermediates never
+// leave the SM; the COO values are written once, coalesced, in the caller's sparsity order.
+// The kernel is instantiated for the common compile-time dimensions (D = 4 ... 18) so that the
+// inner products unroll with immediate offsets; D = 0 is the run-time-d fallback.  The op
+// interpreter is kept out of line on purpose: one copy of its code stays hot in the I-cache.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -15,8 +19,11 @@ __constant__ double c_taylor[QCB_TAYLOR_DEGREE + 1];
 
 struct SmallParams {
     int d, c, m, z_dim, u_off, dt_off, K, nk, k_begin, S;
+    int units;                      // slab-local units = S * nk
+    int upc, tpu;                   // units per CTA, threads per unit
+    int unit_doubles;               // shared-memory doubles per unit
     const int *x_off;
-    const double *G0, *Gd;          // device, unpadded col-major [S][d*d], [S][m][d*d]
+    const double *G0, *Gd;          // device, col-major [S][d*d], [S][m][d*d]
     const double *Z, *mu;
     double *delta, *jac, *hess;     // outputs (slab-local unit indexing)
     const uint32_t *jcode, *hcode;  // [S][nnz]
@@ -28,12 +35,13 @@ struct SmallParams {
 
 struct SmallCtx {
     int d, dd, m, level, j;
+    int e0, tpu;     // this thread's first element and the element stride
     double *fixed;   // [QR_NUM_FIXED][dd]
     double *E, *W;   // [smax+1][dd]
     double *dslot;   // [QCB_NUM_DSLOTS][dd]
     double *L;       // [m+1][dd]
     const double *Gj;
-    int *Lidx;       // [m+1] in shared memory (slot of direction j; entry m = free slot)
+    const int *Lidx; // [m+1] shared by the CTA (slot of direction j; entry m = free slot)
 };
 
 __device__ __forceinline__ double *sm_resolve(const SmallCtx &x, int r) {
@@ -52,23 +60,46 @@ __device__ __forceinline__ double *sm_resolve(const SmallCtx &x, int r) {
     }
 }
 
-// dst = sum_t op(a)op(b) + sum_r c*reg + c*I ; whole CTA cooperates, one output element per
-// thread per pass.  Ends with a block barrier.
-__device__ void sm_run_op(const SmallCtx &x, const qcb_op &op) {
-    const int d = x.d, dd = x.dd;
+template <int D, int AS, int BS> __device__ __forceinline__ double dot_k(const double *a, const double *b, double acc, int d) {
+    // AS / BS: 1 = unit stride, 0 = stride d
+    if (D > 0) {
+        // four independent partial sums: the FP64 FMA latency chain would otherwise bound an op
+        double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0;
+#pragma unroll
+        for (int k = 0; k + 3 < D; k += 4) {
+            p0 = fma(a[(k + 0) * (AS ? 1 : D)], b[(k + 0) * (BS ? 1 : D)], p0);
+            p1 = fma(a[(k + 1) * (AS ? 1 : D)], b[(k + 1) * (BS ? 1 : D)], p1);
+            p2 = fma(a[(k + 2) * (AS ? 1 : D)], b[(k + 2) * (BS ? 1 : D)], p2);
+            p3 = fma(a[(k + 3) * (AS ? 1 : D)], b[(k + 3) * (BS ? 1 : D)], p3);
+        }
+#pragma unroll
+        for (int k = D & ~3; k < D; ++k) p0 = fma(a[k * (AS ? 1 : D)], b[k * (BS ? 1 : D)], p0);
+        acc += (p0 + p1) + (p2 + p3);
+    } else {
+        const int as = AS ? 1 : d, bs = BS ? 1 : d;
+        for (int k = 0; k < d; ++k) acc = fma(a[k * as], b[k * bs], acc);
+    }
+    return acc;
+}
+
+// dst = sum_t op(a)op(b) + sum_r c*reg + c*I for this thread's unit.  Ends with a CTA barrier.
+template <int D> __device__ __noinline__ void sm_run_op(const SmallCtx &x, const qcb_op &op) {
+    const int d = D > 0 ? D : x.d, dd = d * d;
     double *dst = sm_resolve(x, op.dst);
     const double *A[QCB_MAX_TERMS], *B[QCB_MAX_TERMS], *R[QCB_MAX_LIN];
     for (int t = 0; t < op.nterm; ++t) { A[t] = sm_resolve(x, op.term[t].a); B[t] = sm_resolve(x, op.term[t].b); }
     for (int r = 0; r < op.nlin; ++r) R[r] = sm_resolve(x, op.lin[r].reg);
-    for (int e = threadIdx.x; e < dd; e += blockDim.x) {
+    for (int e = x.e0; e < dd; e += x.tpu) {
         const int r = e % d, q = e / d;
         double acc = 0.0;
         for (int t = 0; t < op.nterm; ++t) {
-            const double *a = A[t] + (op.term[t].ta ? r * d : r);
-            const int as = op.term[t].ta ? 1 : d;
-            const double *b = B[t] + (op.term[t].tb ? q : q * d);
-            const int bs = op.term[t].tb ? d : 1;
-            for (int k = 0; k < d; ++k) acc = fma(a[k * as], b[k * bs], acc);
+            const int ta = op.term[t].ta, tb = op.term[t].tb;
+            const double *a = A[t] + (ta ? r * d : r);      // a(r,k): stride d (plain) or 1 (transposed)
+            const double *b = B[t] + (tb ? q : q * d);      // b(k,q): stride 1 (plain) or d (transposed)
+            if (!ta && !tb) acc = dot_k<D, 0, 1>(a, b, acc, d);
+            else if (ta && !tb) acc = dot_k<D, 1, 1>(a, b, acc, d);
+            else if (!ta && tb) acc = dot_k<D, 0, 0>(a, b, acc, d);
+            else acc = dot_k<D, 1, 0>(a, b, acc, d);
         }
         for (int l = 0; l < op.nlin; ++l) acc = fma(c_taylor[op.lin[l].coef], R[l][e], acc);
         if (op.ident >= 0 && r == q) acc += c_taylor[op.ident];
@@ -77,23 +108,48 @@ __device__ void sm_run_op(const SmallCtx &x, const qcb_op &op) {
     __syncthreads();
 }
 
-// block-wide Frobenius inner product, result broadcast to all threads
-__device__ double sm_dot(const double *a, const double *b, int n, double *red) {
-    double v = 0.0;
-    for (int e = threadIdx.x; e < n; e += blockDim.x) v = fma(a[e], b[e], v);
+// Sum over the threads of a unit, result in every thread of the unit.  tpu is a power of two <= 32
+// (aligned sub-warp groups) or a multiple of 32; `red` has room for 16 doubles per unit.
+__device__ __forceinline__ double unit_sum(double v, int tpu, double *red_unit, int lane_in_unit) {
+    if (tpu <= 32) {
+        for (int o = tpu >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        return v;
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    if ((lane_in_unit & 31) == 0) red_unit[lane_in_unit >> 5] = v;
     __syncthreads();
     double s = 0.0;
-    for (int w = 0; w < (int)((blockDim.x + 31) >> 5); ++w) s += red[w];
+    for (int w = 0; w < (tpu >> 5); ++w) s += red_unit[w];
+    __syncthreads();
+    return s;
+}
+__device__ __forceinline__ double unit_max(double v, int tpu, double *red_unit, int lane_in_unit) {
+    if (tpu <= 32) {
+        for (int o = tpu >> 1; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+        return v;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if ((lane_in_unit & 31) == 0) red_unit[lane_in_unit >> 5] = v;
+    __syncthreads();
+    double s = 0.0;
+    for (int w = 0; w < (tpu >> 5); ++w) s = fmax(s, red_unit[w]);
     __syncthreads();
     return s;
 }
 
-// C (d x c) = op(A) (d x d) * P (d x c), scaled
-__device__ void sm_panel(double *C, const double *A, int ta, const double *P, int d, int c, double scale) {
-    for (int e = threadIdx.x; e < d * c; e += blockDim.x) {
+// Frobenius inner product over a unit
+__device__ __noinline__ double sm_dot(const double *a, const double *b, int n, int e0, int tpu, double *red_unit) {
+    double v = 0.0;
+    for (int e = e0; e < n; e += tpu) v = fma(a[e], b[e], v);
+    return unit_sum(v, tpu, red_unit, e0);
+}
+
+// C (d x c) = scale * op(A) (d x d) * P (d x c)
+__device__ __noinline__ void sm_panel(double *C, const double *A, int ta, const double *P, int d, int c, double scale,
+                                      int e0, int tpu) {
+    for (int e = e0; e < d * c; e += tpu) {
         const int r = e % d, b = e / d;
         const double *a = A + (ta ? r * d : r);
         const int as = ta ? 1 : d;
@@ -103,28 +159,34 @@ __device__ void sm_panel(double *C, const double *A, int ta, const double *P, in
     }
 }
 
-static inline size_t small_smem_doubles(int d, int c, int m, int smax) {
+static inline size_t small_unit_doubles(int d, int c, int m, int smax) {
     size_t dd = (size_t)d * d, dc = (size_t)d * c;
     size_t n = (QR_NUM_FIXED + 2 * (size_t)(smax + 1) + QCB_NUM_DSLOTS + (m + 1)) * dd;
     n += 3 * dc;                                   // X, Xn, M panels
     n += dd + (m + 1) * dc + 2;                    // Jacobian arena
     n += (m + 1) * dc + (size_t)m * m + m + 2;     // Hessian arena
-    n += (size_t)m * m + 32;                       // H accumulator + reduction scratch
-    n += (m + 2) / 2 + 2;                          // Lidx (ints)
-    return n;
+    n += (size_t)m * m + 16;                       // H accumulator + reduction scratch
+    return (n + 1) & ~(size_t)1;                   // keep every unit 16-byte aligned
+}
+static inline size_t small_smem_doubles(int d, int c, int m, int smax, int upc = 1) {
+    return (size_t)upc * small_unit_doubles(d, c, m, smax) + (size_t)(m + 2) / 2 + 2 + (size_t)upc + 2;
 }
 
+template <int D>
 __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     extern __shared__ __align__(16) double sm[];
-    const int d = p.d, c = p.c, m = p.m, dd = d * d, dc = d * c;
-    const int ug = blockIdx.x;                       // slab-local unit index = sys*nk + kl
+    const int d = D > 0 ? D : p.d, c = p.c, m = p.m, dd = d * d, dc = d * c;
+    const int tpu = p.tpu, ul = threadIdx.x / tpu, e0 = threadIdx.x % tpu;
+    int ug = blockIdx.x * p.upc + ul;                 // slab-local unit index = sys*nk + kl
+    const bool live = ug < p.units;                   // tail CTA: spare slots shadow the last unit
+    if (!live) ug = p.units - 1;
     const int sys = ug / p.nk, k = p.k_begin + ug % p.nk;
     const double *zk = p.Z + (long long)k * p.z_dim, *zn = zk + p.z_dim;
     const double *G0 = p.G0 + (long long)sys * dd, *Gd = p.Gd + (long long)sys * m * dd;
 
     SmallCtx x;
-    x.d = d; x.dd = dd; x.m = m; x.level = 0; x.j = 0;
-    double *ptr = sm;
+    x.d = d; x.dd = dd; x.m = m; x.level = 0; x.j = 0; x.e0 = e0; x.tpu = tpu;
+    double *ptr = sm + (size_t)ul * p.unit_doubles;
     x.fixed = ptr; ptr += QR_NUM_FIXED * dd;
     x.E = ptr; ptr += (p.smax + 1) * dd;
     x.W = ptr; ptr += (p.smax + 1) * dd;
@@ -136,8 +198,11 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     double *JA = ptr; ptr += dd + (m + 1) * dc + 2;
     double *HA = ptr; ptr += (m + 1) * dc + m * m + m + 2;
     double *Hacc = ptr; ptr += m * m;
-    double *red = ptr; ptr += 32;
-    x.Lidx = reinterpret_cast<int *>(ptr);
+    double *red = ptr;
+    double *cta_tail = sm + (size_t)p.upc * p.unit_doubles;
+    int *Lidx = reinterpret_cast<int *>(cta_tail);                    // [m+1]
+    double *cta_nrm = cta_tail + (m + 2) / 2 + 2;                     // [upc]
+    x.Lidx = Lidx;
     x.Gj = Gd;
 
     const bool want_jac = p.want & 1, want_hess = (p.want & 2) && p.mu;
@@ -145,56 +210,54 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     const double dt = zk[p.dt_off];
 
     // ---- load unit inputs, G = G0 + sum u_j G_j ----
-    for (int e = threadIdx.x; e < dc; e += blockDim.x) {
+    for (int e = e0; e < dc; e += tpu) {
         X[e] = zk[p.x_off[sys] + e];
         Xn[e] = zn[p.x_off[sys] + e];
         Mu[e] = want_hess ? p.mu[((long long)sys * p.K + k) * dc + e] : 0.0;
     }
-    for (int e = threadIdx.x; e < dd; e += blockDim.x) {
+    for (int e = e0; e < dd; e += tpu) {
         double v = G0[e];
         for (int j = 0; j < m; ++j) v = fma(zk[p.u_off + j], Gd[j * dd + e], v);
         G[e] = v;
     }
-    if (threadIdx.x <= m) x.Lidx[threadIdx.x] = threadIdx.x;
-    for (int e = threadIdx.x; e < m * m; e += blockDim.x) Hacc[e] = 0.0;
+    if (threadIdx.x <= m) Lidx[threadIdx.x] = threadIdx.x;
+    for (int e = e0; e < m * m; e += tpu) Hacc[e] = 0.0;
     __syncthreads();
-    // ---- ||dt G||_1 -> number of squarings of this unit ----
-    double nrm = 0.0;
+    // ---- ||dt G||_1 per unit, then one squaring count for the CTA ----
     {
-        double mine = 0.0;   // thread q sums column q (d <= blockDim guaranteed by the host)
+        double mine = 0.0;
         bool bad = false;
-        for (int q = threadIdx.x; q < d; q += blockDim.x) {
+        for (int q = e0; q < d; q += tpu) {
             double cs = 0.0;
             for (int r = 0; r < d; ++r) cs += fabs(dt * G[r + q * d]);
             if (!isfinite(cs)) bad = true;
             mine = fmax(mine, cs);
         }
-        if (bad) mine = INFINITY;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) mine = fmax(mine, __shfl_xor_sync(0xffffffffu, mine, o));
-        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mine;
-        __syncthreads();
-        for (int w = 0; w < (int)((blockDim.x + 31) >> 5); ++w) nrm = fmax(nrm, red[w]);
+        if (bad || !isfinite(dt)) mine = INFINITY;
+        mine = unit_max(mine, tpu, red, e0);
+        if (e0 == 0) cta_nrm[ul] = mine;
         __syncthreads();
     }
-    int s = qcb_squarings(nrm);
+    double nrm = 0.0;
+    for (int u = 0; u < p.upc; ++u) nrm = fmax(nrm, cta_nrm[u]);
+    const int s = qcb_squarings(nrm);
     if (s < 0 || s > p.smax) {      // uniform across the CTA
         if (threadIdx.x == 0) atomicExch(p.bad_flag, 1);
         return;
     }
     const double tau = ldexp(dt, -s);
-    for (int e = threadIdx.x; e < dd; e += blockDim.x) A[e] = tau * G[e];
+    for (int e = e0; e < dd; e += tpu) A[e] = tau * G[e];
     __syncthreads();
 
     // ---- polynomial + squarings ----
-    for (int i = 0; i < 6; ++i) sm_run_op(x, c_P1[i]);
-    for (int l = 0; l < s; ++l) { x.level = l; sm_run_op(x, c_P2[0]); }
+    for (int i = 0; i < 6; ++i) sm_run_op<D>(x, c_P1[i]);
+    for (int l = 0; l < s; ++l) { x.level = l; sm_run_op<D>(x, c_P2[0]); }
     const double *E = x.E + s * dd;
 
     // ---- defect ----
-    {
+    if (live) {
         double *o = p.delta + (long long)ug * dc;
-        for (int e = threadIdx.x; e < dc; e += blockDim.x) {
+        for (int e = e0; e < dc; e += tpu) {
             const int r = e % d, b = e / d;
             double acc = 0.0;
             for (int q = 0; q < d; ++q) acc = fma(E[r + q * d], X[q + b * d], acc);
@@ -205,27 +268,27 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
 
     double *Wt = x.W + s * dd;
     if (want_hess) {
-        for (int e = threadIdx.x; e < dd; e += blockDim.x) {   // W = M X^T
+        for (int e = e0; e < dd; e += tpu) {   // W = M X^T
             const int r = e % d, q = e / d;
             double acc = 0.0;
             for (int b = 0; b < c; ++b) acc = fma(Mu[r + b * d], X[q + b * d], acc);
             Wt[e] = acc;
         }
         __syncthreads();
-        for (int l = s - 1; l >= 0; --l) { x.level = l; sm_run_op(x, c_P3[0]); }
+        for (int l = s - 1; l >= 0; --l) { x.level = l; sm_run_op<D>(x, c_P3[0]); }
         x.level = 0;
-        for (int i = 0; i < 5; ++i) sm_run_op(x, c_P4[i]);
+        for (int i = 0; i < 5; ++i) sm_run_op<D>(x, c_P4[i]);
     }
     // ---- per-direction tangents ----
     for (int j = 0; j < m; ++j) {
         x.j = j; x.Gj = Gd + (long long)j * dd; x.level = 0;
-        for (int i = 0; i < 6; ++i) sm_run_op(x, c_P5[i]);
+        for (int i = 0; i < 6; ++i) sm_run_op<D>(x, c_P5[i]);
         if (want_hess) {
-            for (int i = 0; i < 6; ++i) sm_run_op(x, c_P6[i]);
+            for (int i = 0; i < 6; ++i) sm_run_op<D>(x, c_P6[i]);
             const double *dAb = sm_resolve(x, QR_DAB);
             for (int i = 0; i < m; ++i) {
-                double v = sm_dot(dAb, Gd + (long long)i * dd, dd, red);
-                if (threadIdx.x == 0) Hacc[j * m + i] = v;
+                double v = sm_dot(dAb, Gd + (long long)i * dd, dd, e0, tpu, red);
+                if (e0 == 0) Hacc[j * m + i] = v;
             }
         }
     }
@@ -235,24 +298,24 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
         if (want_hess) {
             for (int j = 0; j < m; ++j) {
                 x.j = j;
-                sm_run_op(x, c_P7S[0]);
+                sm_run_op<D>(x, c_P7S[0]);
                 const double *Sj = sm_resolve(x, QR_S);
                 for (int i = 0; i < m; ++i) {
-                    double v = sm_dot(Sj, x.L + x.Lidx[i] * dd, dd, red);
-                    if (threadIdx.x == 0) Hacc[j * m + i] += v;
+                    double v = sm_dot(Sj, x.L + Lidx[i] * dd, dd, e0, tpu, red);
+                    if (e0 == 0) Hacc[j * m + i] += v;
                 }
             }
         }
         for (int j = 0; j < m; ++j) {
             x.j = j;
-            sm_run_op(x, c_P7L[0]);
-            if (threadIdx.x == 0) { int old = x.Lidx[j]; x.Lidx[j] = x.Lidx[m]; x.Lidx[m] = old; }
+            sm_run_op<D>(x, c_P7L[0]);
+            if (threadIdx.x == 0) { int old = Lidx[j]; Lidx[j] = Lidx[m]; Lidx[m] = old; }
             __syncthreads();
         }
     }
     // ---- final blocks ----
     double *GE = x.fixed + QR_A2 * dd, *WE = x.fixed + QR_A3 * dd, *GW = x.fixed + QR_A4 * dd;
-    for (int e = threadIdx.x; e < dd; e += blockDim.x) {
+    for (int e = e0; e < dd; e += tpu) {
         const int r = e % d, q = e / d;
         double g1 = 0.0, g2 = 0.0, g3 = 0.0;
         for (int kk = 0; kk < d; ++kk) {
@@ -267,31 +330,33 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     }
     __syncthreads();
     double *JU = JA + dd, *JT = JU + m * dc;
-    for (int j = 0; j < m; ++j) sm_panel(JU + j * dc, x.L + x.Lidx[j] * dd, 0, X, d, c, -tau);
-    sm_panel(JT, GE, 0, X, d, c, -1.0);
-    if (threadIdx.x == 0) { JT[dc] = 0.0; JT[dc + 1] = 1.0; }
+    for (int j = 0; j < m; ++j) sm_panel(JU + j * dc, x.L + Lidx[j] * dd, 0, X, d, c, -tau, e0, tpu);
+    sm_panel(JT, GE, 0, X, d, c, -1.0, e0, tpu);
+    if (e0 == 0) { JT[dc] = 0.0; JT[dc + 1] = 1.0; }
     if (want_hess) {
         double *HXU = HA, *HXT = HA + m * dc, *HUU = HXT + dc, *HUT = HUU + m * m, *HTT = HUT + m;
-        for (int j = 0; j < m; ++j) sm_panel(HXU + j * dc, x.L + x.Lidx[j] * dd, 1, Mu, d, c, -tau);
-        sm_panel(HXT, GE, 1, Mu, d, c, -1.0);
-        for (int e = threadIdx.x; e < m * m; e += blockDim.x) {
+        for (int j = 0; j < m; ++j) sm_panel(HXU + j * dc, x.L + Lidx[j] * dd, 1, Mu, d, c, -tau, e0, tpu);
+        sm_panel(HXT, GE, 1, Mu, d, c, -1.0, e0, tpu);
+        __syncthreads();                                  // Hacc complete (written by e0 == 0 lanes)
+        for (int e = e0; e < m * m; e += tpu) {
             const int i = e / m, j = e % m;
             HUU[e] = -0.5 * tau * tau * (Hacc[i * m + j] + Hacc[j * m + i]);
         }
         for (int j = 0; j < m; ++j) {
-            double c1 = sm_dot(WE, Gd + (long long)j * dd, dd, red);
-            double c2 = sm_dot(GW, x.L + x.Lidx[j] * dd, dd, red);
-            if (threadIdx.x == 0) HUT[j] = -(c1 + tau * c2);
+            double c1 = sm_dot(WE, Gd + (long long)j * dd, dd, e0, tpu, red);
+            double c2 = sm_dot(GW, x.L + Lidx[j] * dd, dd, e0, tpu, red);
+            if (e0 == 0) HUT[j] = -(c1 + tau * c2);
         }
-        double c3 = sm_dot(GW, GE, dd, red);
-        if (threadIdx.x == 0) { HTT[0] = -c3; HTT[1] = 0.0; }
+        double c3 = sm_dot(GW, GE, dd, e0, tpu, red);
+        if (e0 == 0) { HTT[0] = -c3; HTT[1] = 0.0; }
     }
     __syncthreads();
+    if (!live) return;
     // ---- coalesced COO stores in the caller's order ----
     if (want_jac && p.jac) {
         const uint32_t *cd = p.jcode + (long long)sys * p.jnnz;
         double *o = p.jac + (long long)ug * p.jnnz;
-        for (long long e = threadIdx.x; e < p.jnnz; e += blockDim.x) {
+        for (long long e = e0; e < p.jnnz; e += tpu) {
             uint32_t cc = cd[e];
             double v = JA[cc & 0x7fffffffu];
             o[e] = (cc >> 31) ? -v : v;
@@ -300,7 +365,7 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     if (want_hess && p.hess) {
         const uint32_t *cd = p.hcode + (long long)sys * p.hnnz;
         double *o = p.hess + (long long)ug * p.hnnz;
-        for (long long e = threadIdx.x; e < p.hnnz; e += blockDim.x) {
+        for (long long e = e0; e < p.hnnz; e += tpu) {
             uint32_t cc = cd[e];
             double v = HA[cc & 0x7fffffffu];
             o[e] = (cc >> 31) ? -v : v;
