@@ -60,6 +60,7 @@ struct qcb_handle_s {
     std::vector<cudaEvent_t> chunk_events;
     int64_t launches = 0;
     double ms[4] = {0, 0, 0, 0};
+    bool xfer_compact = false;
     int64_t xfer[2] = {0, 0};      // bytes moved host->device / device->host by the last host-buffer call
     // optional per-launch profiling of the batched DMMA GEMM (qcb_profile_*)
     bool profiling = false;
@@ -94,7 +95,13 @@ struct qcb_handle_s {
     double *sc_ja2 = nullptr, *sc_ha2 = nullptr;      // second arena set (double buffering)
     double *stage_j[2] = {nullptr, nullptr}, *stage_h[2] = {nullptr, nullptr};   // pinned
     int stage_units = 0;
-    cudaEvent_t copied[2] = {nullptr, nullptr};
+    double *part_j[2] = {nullptr, nullptr}, *part_h[2] = {nullptr, nullptr};   // device COO rows of the units sent directly
+    int part_units = 0;
+    // share of each chunk assembled on the device and DMA'd as full COO rows (QCB_DIRECT_FRACTION).
+    // Measured on the B200 box: 0 is best -- DMA writes and the cores' streaming stores share the same
+    // host DRAM write bandwidth (~107 GB/s), so splitting the work between them gains nothing.
+    double direct_fraction = 0.0;
+    cudaEvent_t copied[2] = {nullptr, nullptr}, part_done[2] = {nullptr, nullptr};
 
     UnitGeom geom() const {
         UnitGeom q;
@@ -407,6 +414,12 @@ struct LargeExec {
         }
         g.ident = op.ident >= 0 ? QCB_TAYLOR[op.ident] : 0.0;
         g.dst = reg(op.dst);
+        if (op.nterm == 0) {        // pure linear combination: no tensor work
+            lincomb_kernel<<<(unsigned)(nu * ndir * (g.N / 8)), 256, 0, h->stream>>>(g);
+            ++h->launches;
+            CK(cudaGetLastError());
+            return;
+        }
         if (h->iso) launch_gemm_iso(h, g, nu); else launch_gemm(h, g, nu);
     }
     // dst = alpha * [scale] * op(a) * op(b), general shapes.  In iso mode the left operand is a
@@ -447,6 +460,11 @@ void free_scratch(qcb_handle_s *h) {
         if (h->stage_j[b]) { cudaFreeHost(h->stage_j[b]); h->stage_j[b] = nullptr; }
         if (h->stage_h[b]) { cudaFreeHost(h->stage_h[b]); h->stage_h[b] = nullptr; }
     }
+    for (int b = 0; b < 2; ++b) {
+        if (h->part_j[b]) { cudaFree(h->part_j[b]); h->part_j[b] = nullptr; }
+        if (h->part_h[b]) { cudaFree(h->part_h[b]); h->part_h[b] = nullptr; }
+    }
+    h->part_units = 0;
     h->stage_units = 0;
     h->s_cap = -1;
 }
@@ -461,6 +479,13 @@ void ensure_compact(qcb_handle_s *h) {
             CK(cudaMallocHost(&h->stage_j[b], n * (size_t)h->JA * 8));
             CK(cudaMallocHost(&h->stage_h[b], n * (size_t)h->HA * 8));
             if (!h->copied[b]) CK(cudaEventCreateWithFlags(&h->copied[b], cudaEventDisableTiming));
+            if (!h->part_done[b]) CK(cudaEventCreateWithFlags(&h->part_done[b], cudaEventDisableTiming));
+        }
+        if (const char *e = getenv("QCB_DIRECT_FRACTION")) h->direct_fraction = std::min(1.0, std::max(0.0, atof(e)));
+        h->part_units = (int)(h->direct_fraction * h->chunk_units);
+        for (int b = 0; b < 2 && h->part_units > 0; ++b) {
+            CK(cudaMalloc(&h->part_j[b], (size_t)h->part_units * h->jnnz_unit * 8));
+            CK(cudaMalloc(&h->part_h[b], (size_t)h->part_units * h->hnnz_unit * 8));
         }
         h->stage_units = h->chunk_units;
     }
@@ -555,15 +580,19 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     const bool compact = host && host->compact && (wj || wh);
     if (compact) ensure_compact(h);
     const int nthreads = (int)std::max(1u, std::thread::hardware_concurrency());
-    int prev_u0 = -1, prev_nu = 0;           // chunk whose arenas are staged on the host, not yet expanded
+    // chunk whose arenas are staged on the host, not yet expanded; its first prev_nd units went
+    // the direct route (assembled on the device, full COO rows DMA'd) and need no expansion
+    int prev_u0 = -1, prev_nu = 0, prev_nd = 0;
     auto expand_prev = [&](size_t idx_prev) {
         if (prev_u0 < 0) return;
         const int b = (int)(idx_prev & 1);
         CK(cudaEventSynchronize(h->copied[b]));
         if (wj && host->jac)
-            expand_units(h->jsegs, h->nk, prev_u0, prev_nu, h->stage_j[b], h->JA, host->jac, h->jnnz_unit, nthreads);
+            expand_units(h->jsegs, h->nk, prev_u0 + prev_nd, prev_nu - prev_nd, h->stage_j[b] + (size_t)prev_nd * h->JA,
+                         h->JA, host->jac, h->jnnz_unit, nthreads);
         if (wh && host->hess)
-            expand_units(h->hsegs, h->nk, prev_u0, prev_nu, h->stage_h[b], h->HA, host->hess, h->hnnz_unit, nthreads);
+            expand_units(h->hsegs, h->nk, prev_u0 + prev_nd, prev_nu - prev_nd, h->stage_h[b] + (size_t)prev_nd * h->HA,
+                         h->HA, host->hess, h->hnnz_unit, nthreads);
         prev_u0 = -1;
     };
     size_t chunk_idx = 0;
@@ -575,7 +604,13 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         X.ja = buf ? h->sc_ja2 : h->sc_ja;
         X.ha = buf ? h->sc_ha2 : h->sc_ha;
         // the D2H of chunk idx-2 read this arena set: let it finish before overwriting
-        if (compact && chunk_idx >= 2) CK(cudaStreamWaitEvent(h->stream, h->copied[buf], 0));
+        if (compact && chunk_idx >= 2) {
+            CK(cudaStreamWaitEvent(h->stream, h->copied[buf], 0));
+            CK(cudaStreamWaitEvent(h->stream, h->part_done[buf], 0));
+        }
+        // hybrid: the PCIe link and the host cores both write COO rows -- the first nd units of the
+        // chunk are assembled on the device and DMA'd in full, the rest travel as compact arenas
+        const int nd = compact ? std::min(h->part_units, (int)(h->direct_fraction * nu)) : 0;
         Opnd G = X.fixed(QR_G), A = X.fixed(QR_A);
         build_G_kernel<<<nu, 256, 0, h->stream>>>(q, dZ, u0, const_cast<double *>(G.p), dd, h->d_norm, h->d_bad);
         ++h->launches;
@@ -651,13 +686,25 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             }
             if (wj && d_jac && !compact) {
                 int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->jnnz_unit / 4096));
-                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ja, h->JA, h->d_jcode, h->jnnz_unit, d_jac, u0, h->nk, cpu);
+                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ja, h->JA, h->d_jcode, h->jnnz_unit, d_jac, u0, h->nk, cpu, u0);
                 ++h->launches;
             }
             if (wh && d_hess && !compact) {
                 int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->hnnz_unit / 4096));
-                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ha, h->HA, h->d_hcode, h->hnnz_unit, d_hess, u0, h->nk, cpu);
+                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ha, h->HA, h->d_hcode, h->hnnz_unit, d_hess, u0, h->nk, cpu, u0);
                 ++h->launches;
+            }
+            if (compact && nd > 0) {
+                if (wj && host->jac) {
+                    int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->jnnz_unit / 4096));
+                    assemble_kernel<<<nd * cpu, 256, 0, h->stream>>>(X.ja, h->JA, h->d_jcode, h->jnnz_unit, h->part_j[buf], u0, h->nk, cpu, 0);
+                    ++h->launches;
+                }
+                if (wh && host->hess) {
+                    int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->hnnz_unit / 4096));
+                    assemble_kernel<<<nd * cpu, 256, 0, h->stream>>>(X.ha, h->HA, h->d_hcode, h->hnnz_unit, h->part_h[buf], u0, h->nk, cpu, 0);
+                    ++h->launches;
+                }
             }
         }
         CK(cudaGetLastError());
@@ -671,24 +718,35 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             CK(cudaStreamWaitEvent(h->copy_stream, h->chunk_events[chunk_idx], 0));
             if (host->delta)
                 CK(cudaMemcpyAsync(host->delta + (size_t)u0 * h->xdim, d_delta + (size_t)u0 * h->xdim,
-                                   (size_t)nu * h->xdim * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                                   (size_t)nu * h->xdim * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)nu * h->xdim * 8);
             if (compact) {
                 // compact transfer: the value arenas (every distinct number once) cross PCIe; the
                 // host cores write the COO vectors from them while the GPU works on the next chunk
-                if (wj && host->jac)
-                    CK(cudaMemcpyAsync(h->stage_j[buf], X.ja, (size_t)nu * h->JA * 8, cudaMemcpyDeviceToHost, h->copy_stream));
-                if (wh && host->hess)
-                    CK(cudaMemcpyAsync(h->stage_h[buf], X.ha, (size_t)nu * h->HA * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                if (wj && host->jac && nu > nd)
+                    CK(cudaMemcpyAsync(h->stage_j[buf] + (size_t)nd * h->JA, X.ja + (size_t)nd * h->JA,
+                                       (size_t)(nu - nd) * h->JA * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)(nu - nd) * h->JA * 8);
+                if (wh && host->hess && nu > nd)
+                    CK(cudaMemcpyAsync(h->stage_h[buf] + (size_t)nd * h->HA, X.ha + (size_t)nd * h->HA,
+                                       (size_t)(nu - nd) * h->HA * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)(nu - nd) * h->HA * 8);
                 CK(cudaEventRecord(h->copied[buf], h->copy_stream));
+                if (nd > 0) {
+                    if (wj && host->jac)
+                        CK(cudaMemcpyAsync(host->jac + (size_t)u0 * h->jnnz_unit, h->part_j[buf],
+                                           (size_t)nd * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)nd * h->jnnz_unit * 8);
+                    if (wh && host->hess)
+                        CK(cudaMemcpyAsync(host->hess + (size_t)u0 * h->hnnz_unit, h->part_h[buf],
+                                           (size_t)nd * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)nd * h->hnnz_unit * 8);
+                }
+                CK(cudaEventRecord(h->part_done[buf], h->copy_stream));
                 expand_prev(chunk_idx - 1);
-                prev_u0 = u0; prev_nu = nu;
+                prev_u0 = u0; prev_nu = nu; prev_nd = nd;
             } else {
                 if (wj && host->jac)
                     CK(cudaMemcpyAsync(host->jac + (size_t)u0 * h->jnnz_unit, d_jac + (size_t)u0 * h->jnnz_unit,
-                                       (size_t)nu * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                                       (size_t)nu * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)nu * h->jnnz_unit * 8);
                 if (wh && host->hess)
                     CK(cudaMemcpyAsync(host->hess + (size_t)u0 * h->hnnz_unit, d_hess + (size_t)u0 * h->hnnz_unit,
-                                       (size_t)nu * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                                       (size_t)nu * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)nu * h->hnnz_unit * 8);
             }
         }
     }
@@ -756,11 +814,11 @@ qcb_status eval_device(qcb_handle_s *h, const double *dZ, const double *dmu, dou
             CK(cudaEventRecord(h->ev[4], h->stream));
             CK(cudaStreamWaitEvent(h->copy_stream, h->ev[4], 0));
             if (host->delta)
-                CK(cudaMemcpyAsync(host->delta, d_delta, (size_t)h->units * h->xdim * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                CK(cudaMemcpyAsync(host->delta, d_delta, (size_t)h->units * h->xdim * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)h->units * h->xdim * 8);
             if ((want & 1) && host->jac)
-                CK(cudaMemcpyAsync(host->jac, d_jac, (size_t)h->units * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                CK(cudaMemcpyAsync(host->jac, d_jac, (size_t)h->units * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)h->units * h->jnnz_unit * 8);
             if ((want & 2) && host->hess)
-                CK(cudaMemcpyAsync(host->hess, d_hess, (size_t)h->units * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                CK(cudaMemcpyAsync(host->hess, d_hess, (size_t)h->units * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)h->units * h->hnnz_unit * 8);
         }
     }
     CK(cudaStreamSynchronize(h->stream));
@@ -946,6 +1004,7 @@ void qcb_destroy(qcb_handle h) {
         if (e) cudaEventDestroy(e);
     for (auto &e : h->chunk_events) cudaEventDestroy(e);
     for (auto &e : h->copied) if (e) cudaEventDestroy(e);
+    for (auto &e : h->part_done) if (e) cudaEventDestroy(e);
     for (auto &e : h->prof_ev) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
@@ -1129,9 +1188,8 @@ qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu, double 
             }
         }
         h->xfer[0] = (int64_t)(h->nk + 1) * h->z_dim * 8 + (hess ? (int64_t)h->S * h->nk * h->xdim * 8 : 0);
-        h->xfer[1] = (delta ? (int64_t)h->units * h->xdim * 8 : 0)
-                   + (jac ? (int64_t)h->units * (compact ? h->JA : h->jnnz_unit) * 8 : 0)
-                   + (hess ? (int64_t)h->units * (compact ? h->HA : h->hnnz_unit) * 8 : 0);
+        h->xfer[1] = 0;   // counted where the device->host copies are issued
+        h->xfer_compact = compact;
         CK(cudaEventRecord(h->ev[1], h->stream));
         HostOut ho{delta, jac, hess, compact};
         int want = (jac ? 1 : 0) | (hess ? 2 : 0);

@@ -184,20 +184,31 @@ bgemm_kernel(const __grid_constant__ GemmArgs g) {
         cf[l] = on ? g.lin_coef[l] : 0.0;
         ldl[l] = on ? g.lin[l].ld : 0;
     }
-    for (int idx = tid; idx < (BM / 2) * BN; idx += NTHR) {
-        const int r = 2 * (idx % (BM / 2)), c = idx / (BM / 2);
-        double2 v = *reinterpret_cast<const double2 *>(Cs + c * LDC + r);
-        v.x *= sc; v.y *= sc;
+    // four output vectors per pass: all linear-term loads of a pass are issued before any is used
+    constexpr int EPI_U = 4;
+    static_assert(((BM / 2) * BN) % (NTHR * EPI_U) == 0, "epilogue tiling");
+    for (int base = tid; base < (BM / 2) * BN; base += NTHR * EPI_U) {
+        double2 t[EPI_U][4];
 #pragma unroll
-        for (int l = 0; l < 4; ++l)
-            if (pl[l]) {
-                const double2 t = *reinterpret_cast<const double2 *>(pl[l] + (m0 + r) + (long long)(n0 + c) * ldl[l]);
-                v.x = fma(cf[l], t.x, v.x); v.y = fma(cf[l], t.y, v.y);
-            }
-        const int gr = m0 + r, gc = n0 + c;
-        if (gc == gr && gr < g.d_ident) v.x += g.ident;
-        if (gc == gr + 1 && gc < g.d_ident) v.y += g.ident;
-        *reinterpret_cast<double2 *>(pd + gr + (long long)gc * g.dst.ld) = v;
+        for (int u = 0; u < EPI_U; ++u) {
+            const int idx = base + u * NTHR, r = 2 * (idx % (BM / 2)), c = idx / (BM / 2);
+#pragma unroll
+            for (int l = 0; l < 4; ++l)
+                t[u][l] = pl[l] ? *reinterpret_cast<const double2 *>(pl[l] + (m0 + r) + (long long)(n0 + c) * ldl[l])
+                                : make_double2(0.0, 0.0);
+        }
+#pragma unroll
+        for (int u = 0; u < EPI_U; ++u) {
+            const int idx = base + u * NTHR, r = 2 * (idx % (BM / 2)), c = idx / (BM / 2);
+            double2 v = *reinterpret_cast<const double2 *>(Cs + c * LDC + r);
+            v.x *= sc; v.y *= sc;
+#pragma unroll
+            for (int l = 0; l < 4; ++l) { v.x = fma(cf[l], t[u][l].x, v.x); v.y = fma(cf[l], t[u][l].y, v.y); }
+            const int gr = m0 + r, gc = n0 + c;
+            if (gc == gr && gr < g.d_ident) v.x += g.ident;
+            if (gc == gr + 1 && gc < g.d_ident) v.y += g.ident;
+            *reinterpret_cast<double2 *>(pd + gr + (long long)gc * g.dst.ld) = v;
+        }
     }
 }
 
@@ -368,20 +379,31 @@ bgemm_iso_kernel(const __grid_constant__ GemmArgs g) {
         cf[l] = on ? g.lin_coef[l] : 0.0;
         ldl[l] = on ? g.lin[l].ld : 0;
     }
-    for (int idx = tid; idx < (BM / 2) * BN; idx += NTHR) {
-        const int r = 2 * (idx % (BM / 2)), c = idx / (BM / 2);
-        double2 v = *reinterpret_cast<const double2 *>(Cs + c * LDC + r);
-        v.x *= sc; v.y *= sc;
+    // four output vectors per pass: all linear-term loads of a pass are issued before any is used
+    constexpr int EPI_U = 4;
+    static_assert(((BM / 2) * BN) % (NTHR * EPI_U) == 0, "epilogue tiling");
+    for (int base = tid; base < (BM / 2) * BN; base += NTHR * EPI_U) {
+        double2 t[EPI_U][4];
 #pragma unroll
-        for (int l = 0; l < 4; ++l)
-            if (pl[l]) {
-                const double2 t = *reinterpret_cast<const double2 *>(pl[l] + (m0 + r) + (long long)(n0 + c) * ldl[l]);
-                v.x = fma(cf[l], t.x, v.x); v.y = fma(cf[l], t.y, v.y);
-            }
-        const int gr = m0 + r, gc = n0 + c;
-        if (gc == gr && gr < g.d_ident) v.x += g.ident;
-        if (gc == gr + 1 && gc < g.d_ident) v.y += g.ident;
-        *reinterpret_cast<double2 *>(pd + gr + (long long)gc * g.dst.ld) = v;
+        for (int u = 0; u < EPI_U; ++u) {
+            const int idx = base + u * NTHR, r = 2 * (idx % (BM / 2)), c = idx / (BM / 2);
+#pragma unroll
+            for (int l = 0; l < 4; ++l)
+                t[u][l] = pl[l] ? *reinterpret_cast<const double2 *>(pl[l] + (m0 + r) + (long long)(n0 + c) * ldl[l])
+                                : make_double2(0.0, 0.0);
+        }
+#pragma unroll
+        for (int u = 0; u < EPI_U; ++u) {
+            const int idx = base + u * NTHR, r = 2 * (idx % (BM / 2)), c = idx / (BM / 2);
+            double2 v = *reinterpret_cast<const double2 *>(Cs + c * LDC + r);
+            v.x *= sc; v.y *= sc;
+#pragma unroll
+            for (int l = 0; l < 4; ++l) { v.x = fma(cf[l], t[u][l].x, v.x); v.y = fma(cf[l], t[u][l].y, v.y); }
+            const int gr = m0 + r, gc = n0 + c;
+            if (gc == gr && gr < g.d_ident) v.x += g.ident;
+            if (gc == gr + 1 && gc < g.d_ident) v.y += g.ident;
+            *reinterpret_cast<double2 *>(pd + gr + (long long)gc * g.dst.ld) = v;
+        }
     }
 }
 
@@ -398,6 +420,40 @@ iso_project_kernel(const double *Wfull, long long w_stride, double *WL, long lon
         if (i < n) v = 0.5 * (W[i + (long long)j * d] + W[(i + n) + (long long)(j + n) * d]);
         else v = 0.5 * (W[i + (long long)j * d] - W[(i - n) + (long long)(j + n) * d]);
         o[e] = v;
+    }
+}
+
+// dst = sum_l coef_l * R_l + ident * I for ops without products (no tensor work): plain streaming
+// kernel, 16-byte accesses, one CTA per (batch item, column block).
+__global__ void __launch_bounds__(256) lincomb_kernel(const __grid_constant__ GemmArgs g) {
+    const int cols_per_cta = 8;
+    const int cblocks = g.N / cols_per_cta;
+    const int batch = blockIdx.x / cblocks, c0 = (blockIdx.x % cblocks) * cols_per_cta;
+    const int unit = batch / g.ndir, dir = batch % g.ndir;
+    const int sys = (g.unit0_global + unit) / g.nk;
+    const long long ou = unit, od = dir, os = sys;
+    double *pd = const_cast<double *>(g.dst.p) + ou * g.dst.su + od * g.dst.sd + os * g.dst.ss;
+    const double *pl[4];
+    double cf[4];
+#pragma unroll
+    for (int l = 0; l < 4; ++l) {
+        const bool on = l < g.nlin;
+        pl[l] = on ? g.lin[l].p + ou * g.lin[l].su + od * g.lin[l].sd + os * g.lin[l].ss : nullptr;
+        cf[l] = on ? g.lin_coef[l] : 0.0;
+    }
+    const int half_rows = g.M / 2;
+    for (int idx = threadIdx.x; idx < half_rows * cols_per_cta; idx += blockDim.x) {
+        const int r = 2 * (idx % half_rows), c = c0 + idx / half_rows;
+        double2 v = make_double2(0.0, 0.0);
+#pragma unroll
+        for (int l = 0; l < 4; ++l)
+            if (pl[l]) {
+                const double2 t = *reinterpret_cast<const double2 *>(pl[l] + r + (long long)c * g.lin[l].ld);
+                v.x = fma(cf[l], t.x, v.x); v.y = fma(cf[l], t.y, v.y);
+            }
+        if (c == r && r < g.d_ident) v.x += g.ident;
+        if (c == r + 1 && c < g.d_ident) v.y += g.ident;
+        *reinterpret_cast<double2 *>(pd + r + (long long)c * g.dst.ld) = v;
     }
 }
 
@@ -598,12 +654,12 @@ __global__ void arena_consts_kernel(double *jarena, long long stride, long long 
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 assemble_kernel(const double *arena, long long arena_stride, const uint32_t *code, long long nnz,
-                double *out, int u0_global, int nk, int chunks_per_unit) {
+                double *out, int u0_global, int nk, int chunks_per_unit, int out_u0) {
     const int unit = blockIdx.x / chunks_per_unit, chunk = blockIdx.x % chunks_per_unit;
     const int sys = (u0_global + unit) / nk;
     const uint32_t *cd = code + (long long)sys * nnz;
     const double *ar = arena + (long long)unit * arena_stride;
-    double *o = out + (long long)(u0_global + unit) * nnz;
+    double *o = out + (long long)(out_u0 + unit) * nnz;   // out_u0: unit index of `out`'s first row
     const long long per = (nnz + chunks_per_unit - 1) / chunks_per_unit;
     const long long e1 = (chunk + 1) * per < nnz ? (chunk + 1) * per : nnz;
     for (long long e = chunk * per + threadIdx.x; e < e1; e += blockDim.x) {
