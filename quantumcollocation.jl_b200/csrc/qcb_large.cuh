@@ -264,82 +264,119 @@ bgemm_iso_kernel(const __grid_constant__ GemmArgs g) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) acc[i][j][q] = 0.0;
 
-    const int kslabs = g.K / BK;
+    const int kslabs = g.K / BK, half = kslabs >> 1;
     const int nit = g.nterm * kslabs;
 
-    auto load_stage = [&](int it, int stage) {
-        const GemmTerm &t = g.term[it / kslabs];
-        const int k0 = (it % kslabs) * BK;
-        const bool khi = k0 >= nh;
-        const double *pa = t.a.p + ou * t.a.su + od * t.a.sd + os * t.a.ss;
-        const double *pb = t.b.p + ou * t.b.su + od * t.b.sd + os * t.b.ss;
-        double *as = As + stage * A_ST, *bs = Bs + stage * B_ST;
-        if (!t.ta) {
-            // X_full(i, k): column (k mod n), rows rotated by n when k >= n
-            const int ksrc = khi ? k0 - nh : k0;
-            for (int ch = tid; ch < BK * (BM / 2); ch += NTHR) {
-                const int kc = ch / (BM / 2), r = 2 * (ch % (BM / 2));
-                int i = m0 + r;
-                if (khi) i = (i < nh) ? i + nh : i - nh;
-                cp_async16(as + kc * (BM + 4) + r, pa + i + (long long)(ksrc + kc) * t.a.ld);
+    // ---- loader state: element offsets of this thread's 4 + 2 sixteen-byte chunks inside the two
+    //      operands of the current term; advanced by a constant per slab, corrected once when the
+    //      slab crosses k = n (the rotated half of the virtual full operand) ----
+    const double *l_pa = nullptr, *l_pb = nullptr;
+    int offA[4], adjA[4], offB[2], stepA = 0, stepB = 0, adjB = 0;
+    int sA = 0, sAstep = 0, sB = 0, sBstep = 0;     // shared-memory offsets of chunk 0 and the chunk stride
+    int l_term = 0, l_slab = 0, l_stage = 0;
+    auto loader_init = [&](int term) {
+        const GemmTerm &t = g.term[term];
+        l_pa = t.a.p + ou * t.a.su + od * t.a.sd + os * t.a.ss;
+        l_pb = t.b.p + ou * t.b.su + od * t.b.sd + os * t.b.ss;
+        const int lda = t.a.ld, ldb = t.b.ld;
+        if (!t.ta) {        // X_full(i, k): column k mod n, rows rotated by n for k >= n
+            const int r = m0 + 2 * (tid & 63), kc = tid >> 6;
+            const int rrot = (r < nh) ? r + nh : r - nh;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { offA[i] = r + (kc + 4 * i) * lda; adjA[i] = (rrot - r) - nh * lda; }
+            stepA = BK * lda;
+            sA = kc * (BM + 4) + 2 * (tid & 63); sAstep = 4 * (BM + 4);
+        } else {            // X_full(k, i): i < n -> X_L(k, i);  i >= n -> +-X_L((k + n) mod d, i - n)
+            const int k2 = 2 * (tid & 7);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int irow = m0 + (tid >> 3) + 32 * i;
+                const bool ihi = irow >= nh;
+                offA[i] = (ihi ? k2 + nh : k2) + (ihi ? irow - nh : irow) * lda;
+                adjA[i] = ihi ? -dfull : 0;
             }
-        } else {
-            // X_full(k, i): i < n -> X_L(k, i);  i >= n -> +-X_L((k + n) mod d, i - n)
-            for (int ch = tid; ch < BM * (BK / 2); ch += NTHR) {
-                const int r = ch / (BK / 2), k2 = 2 * (ch % (BK / 2));
-                const int i = m0 + r;
-                const bool ihi = i >= nh;
-                int k = k0 + k2;
-                if (ihi) k = khi ? k - nh : k + nh;
-                cp_async16(as + r * (BK + 4) + k2, pa + k + (long long)(ihi ? i - nh : i) * t.a.ld);
-            }
+            stepA = BK;
+            sA = (tid >> 3) * (BK + 4) + k2; sAstep = 32 * (BK + 4);
         }
-        if (!t.tb) {
-            for (int ch = tid; ch < BN * (BK / 2); ch += NTHR) {
-                const int n = ch / (BK / 2), k2 = 2 * (ch % (BK / 2));
-                cp_async16(bs + n * (BK + 4) + k2, pb + (k0 + k2) + (long long)(n0 + n) * t.b.ld);
-            }
+        if (!t.tb) {        // plain K x N right operand
+            const int k2 = 2 * (tid & 7);
+#pragma unroll
+            for (int i = 0; i < 2; ++i) offB[i] = k2 + (n0 + (tid >> 3) + 32 * i) * ldb;
+            stepB = BK; adjB = 0;
+            sB = (tid >> 3) * (BK + 4) + k2; sBstep = 32 * (BK + 4);
+        } else {            // (Y^T)_L(k, c) = Y_L(c, k) (k < n) or -Y_L(c + n, k - n)
+            const int n2 = 2 * (tid & 31), kc = tid >> 5;
+#pragma unroll
+            for (int i = 0; i < 2; ++i) offB[i] = (n0 + n2) + (kc + 8 * i) * ldb;
+            stepB = BK * ldb; adjB = nh - nh * ldb;
+            sB = kc * (BN + 4) + n2; sBstep = 8 * (BN + 4);
+        }
+    };
+    auto loader_issue = [&]() {
+        double *as = As + l_stage * A_ST + sA, *bs = Bs + l_stage * B_ST + sB;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) cp_async16(as + i * sAstep, l_pa + offA[i]);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) cp_async16(bs + i * sBstep, l_pb + offB[i]);
+        l_stage = (l_stage + 1 == STAGES) ? 0 : l_stage + 1;
+        if (++l_slab == kslabs) {
+            l_slab = 0;
+            if (++l_term < g.nterm) loader_init(l_term);
         } else {
-            // (Y^T)_L(k, c) = Y_L(c, k) (k < n) or -Y_L(c + n, k - n)
-            const int ksrc = khi ? k0 - nh : k0, roff = khi ? nh : 0;
-            for (int ch = tid; ch < BK * (BN / 2); ch += NTHR) {
-                const int kc = ch / (BN / 2), n2 = 2 * (ch % (BN / 2));
-                cp_async16(bs + kc * (BN + 4) + n2, pb + (roff + n0 + n2) + (long long)(ksrc + kc) * t.b.ld);
-            }
+            const bool cross = (l_slab == half);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) offA[i] += stepA + (cross ? adjA[i] : 0);
+#pragma unroll
+            for (int i = 0; i < 2; ++i) offB[i] += stepB + (cross ? adjB : 0);
         }
     };
 
+    if (nit > 0) loader_init(0);
 #pragma unroll
     for (int s = 0; s < STAGES - 1; ++s) {
-        if (s < nit) load_stage(s, s);
+        if (s < nit) loader_issue();
         cp_async_commit();
     }
+    // ---- consumer state ----
+    int c_term = 0, c_slab = 0, c_stage = 0;
+    int a_rs = 1, a_ks = BM + 4, b_ks = 1, b_ns = BK + 4, c_ta = 0, c_tb = 0;
+    bool cur_neg = false;      // accumulators currently hold minus the running sum
+    auto consumer_term = [&](int term) {
+        const GemmTerm &t = g.term[term];
+        c_ta = t.ta; c_tb = t.tb;
+        a_rs = t.ta ? (BK + 4) : 1; a_ks = t.ta ? 1 : (BM + 4);
+        b_ks = t.tb ? (BN + 4) : 1; b_ns = t.tb ? 1 : (BK + 4);
+    };
+    if (nit > 0) consumer_term(0);
     for (int it = 0; it < nit; ++it) {
         cp_async_wait<STAGES - 2>();
         __syncthreads();
-        {
-            int nx = it + STAGES - 1;
-            if (nx < nit) load_stage(nx, nx % STAGES);
-            cp_async_commit();
+        if (it + STAGES - 1 < nit) loader_issue();
+        cp_async_commit();
+        // sign of this (warp, slab): left operand ta=0: -(khi && top); ta=1: -(bottom && !khi);
+        // right operand tb=1: -khi.  Instead of negating fragments, the accumulators are negated
+        // whenever the sign changes (at most twice per term): acc -= a*b  ==  -( (-acc) + a*b ).
+        const bool khi = c_slab >= half;
+        bool neg = c_ta ? (!warp_top && !khi) : (warp_top && khi);
+        if (c_tb && khi) neg = !neg;
+        if (neg != cur_neg) {
+#pragma unroll
+            for (int i = 0; i < MT; ++i)
+#pragma unroll
+                for (int j = 0; j < NT; ++j)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) acc[i][j][q] = -acc[i][j][q];
+            cur_neg = neg;
         }
-        const GemmTerm &t = g.term[it / kslabs];
-        const bool khi = ((it % kslabs) * BK) >= nh;
-        // sign of this (warp, slab):  left operand  ta=0: -(khi && top);  ta=1: -(bottom && !khi);
-        //                             right operand tb=1: -khi
-        bool neg = t.ta ? (!warp_top && !khi) : (warp_top && khi);
-        if (t.tb && khi) neg = !neg;
-        const unsigned smask = neg ? 0x80000000u : 0u;
-        const int a_rs = t.ta ? (BK + 4) : 1, a_ks = t.ta ? 1 : (BM + 4);
-        const int b_ks = t.tb ? (BN + 4) : 1, b_ns = t.tb ? 1 : (BK + 4);
-        const double *as = As + (it % STAGES) * A_ST + (wm * WM + gid) * a_rs + tig * a_ks;
-        const double *bs = Bs + (it % STAGES) * B_ST + (wn * WN + gid) * b_ns + tig * b_ks;
+        const double *as = As + c_stage * A_ST + (wm * WM + gid) * a_rs + tig * a_ks;
+        const double *bs = Bs + c_stage * B_ST + (wn * WN + gid) * b_ns + tig * b_ks;
 #pragma unroll
         for (int kk = 0; kk < BK; kk += 4) {
             double a0[MT], a1[MT], b[NT];
 #pragma unroll
             for (int i = 0; i < MT; ++i) {
-                a0[i] = flip_sign(as[(i * 16) * a_rs + kk * a_ks], smask);
-                a1[i] = flip_sign(as[(i * 16 + 8) * a_rs + kk * a_ks], smask);
+                a0[i] = as[(i * 16) * a_rs + kk * a_ks];
+                a1[i] = as[(i * 16 + 8) * a_rs + kk * a_ks];
             }
 #pragma unroll
             for (int j = 0; j < NT; ++j) b[j] = bs[(j * 8) * b_ns + kk * b_ks];
@@ -348,6 +385,19 @@ bgemm_iso_kernel(const __grid_constant__ GemmArgs g) {
 #pragma unroll
                 for (int j = 0; j < NT; ++j) dmma_16x8x4(acc[i][j], a0[i], a1[i], b[j]);
         }
+        c_stage = (c_stage + 1 == STAGES) ? 0 : c_stage + 1;
+        if (++c_slab == kslabs) {
+            c_slab = 0;
+            if (++c_term < g.nterm) consumer_term(c_term);
+        }
+    }
+    if (cur_neg) {
+#pragma unroll
+        for (int i = 0; i < MT; ++i)
+#pragma unroll
+            for (int j = 0; j < NT; ++j)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[i][j][q] = -acc[i][j][q];
     }
     cp_async_wait<0>();
     (void)dfull;
