@@ -440,7 +440,7 @@ struct LargeExec {
         ContractArgs a;
         a.P = P; a.Q = Q; a.nj = nj; a.ni = ni; a.nelem = dd; a.out = out; a.accumulate = accumulate;
         a.unit0_global = u0; a.nk = h->nk;
-        if (nj > 1 && nj <= 16 && ni <= 16 && (dd % 128) == 0)
+        if (nj <= 16 && ni <= 16 && (dd % 128) == 0)
             contract_mma_kernel<<<(unsigned)nu, 256, 0, h->stream>>>(a);
         else
             contract_kernel<<<(unsigned)(nu * nj), 256, 0, h->stream>>>(a);

@@ -235,6 +235,32 @@ __device__ __forceinline__ double flip_sign(double v, unsigned mask) {
     return __hiloint2double(__double2hiint(v) ^ (int)mask, __double2loint(v));
 }
 
+// one staged K slab (16 deep) of the 128 x 64 tile: fragments from shared memory, 64 DMMA per warp
+template <int TA, int TB, int MT, int NT>
+__device__ __forceinline__ void iso_slab_mma(double (&acc)[MT][NT][4], const double *as0, const double *bs0,
+                                             int arow, int bcol, int tig) {
+    constexpr int BM = 128, BN = 64, BK = GEMM_BK;
+    constexpr int a_rs = TA ? (BK + 4) : 1, a_ks = TA ? 1 : (BM + 4);
+    constexpr int b_ks = TB ? (BN + 4) : 1, b_ns = TB ? 1 : (BK + 4);
+    const double *as = as0 + arow * a_rs + tig * a_ks;
+    const double *bs = bs0 + bcol * b_ns + tig * b_ks;
+#pragma unroll
+    for (int kk = 0; kk < BK; kk += 4) {
+        double a0[MT], a1[MT], b[NT];
+#pragma unroll
+        for (int i = 0; i < MT; ++i) {
+            a0[i] = as[(i * 16) * a_rs + kk * a_ks];
+            a1[i] = as[(i * 16 + 8) * a_rs + kk * a_ks];
+        }
+#pragma unroll
+        for (int j = 0; j < NT; ++j) b[j] = bs[(j * 8) * b_ns + kk * b_ks];
+#pragma unroll
+        for (int i = 0; i < MT; ++i)
+#pragma unroll
+            for (int j = 0; j < NT; ++j) dmma_16x8x4(acc[i][j], a0[i], a1[i], b[j]);
+    }
+}
+
 template <int STAGES>
 __global__ void __launch_bounds__(256, 2)
 bgemm_iso_kernel(const __grid_constant__ GemmArgs g) {
@@ -368,23 +394,12 @@ bgemm_iso_kernel(const __grid_constant__ GemmArgs g) {
                     for (int q = 0; q < 4; ++q) acc[i][j][q] = -acc[i][j][q];
             cur_neg = neg;
         }
-        const double *as = As + c_stage * A_ST + (wm * WM + gid) * a_rs + tig * a_ks;
-        const double *bs = Bs + c_stage * B_ST + (wn * WN + gid) * b_ns + tig * b_ks;
-#pragma unroll
-        for (int kk = 0; kk < BK; kk += 4) {
-            double a0[MT], a1[MT], b[NT];
-#pragma unroll
-            for (int i = 0; i < MT; ++i) {
-                a0[i] = as[(i * 16) * a_rs + kk * a_ks];
-                a1[i] = as[(i * 16 + 8) * a_rs + kk * a_ks];
-            }
-#pragma unroll
-            for (int j = 0; j < NT; ++j) b[j] = bs[(j * 8) * b_ns + kk * b_ks];
-#pragma unroll
-            for (int i = 0; i < MT; ++i)
-#pragma unroll
-                for (int j = 0; j < NT; ++j) dmma_16x8x4(acc[i][j], a0[i], a1[i], b[j]);
-        }
+        // four compile-time layouts of the staged tiles -> LDS with immediate offsets
+        const double *as0 = As + c_stage * A_ST, *bs0 = Bs + c_stage * B_ST;
+        if (!c_ta && !c_tb) iso_slab_mma<0, 0, MT, NT>(acc, as0, bs0, wm * WM + gid, wn * WN + gid, tig);
+        else if (c_ta && !c_tb) iso_slab_mma<1, 0, MT, NT>(acc, as0, bs0, wm * WM + gid, wn * WN + gid, tig);
+        else if (!c_ta && c_tb) iso_slab_mma<0, 1, MT, NT>(acc, as0, bs0, wm * WM + gid, wn * WN + gid, tig);
+        else iso_slab_mma<1, 1, MT, NT>(acc, as0, bs0, wm * WM + gid, wn * WN + gid, tig);
         c_stage = (c_stage + 1 == STAGES) ? 0 : c_stage + 1;
         if (++c_slab == kslabs) {
             c_slab = 0;
@@ -619,33 +634,37 @@ build_G_kernel(UnitGeom q, const double *Z, int u0_global, double *Gout, long lo
     const double *G0 = q.G0 + sys * dd, *Gd = q.Gd + (long long)sys * q.m * dd;
     double *G = Gout ? Gout + (long long)unit * g_stride : nullptr;
     const double dt = zk[q.dt_off];
-    __shared__ double colsum[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+    __shared__ double wmax[8];
+    __shared__ double su[CONTRACT_MAXI];
+    if (threadIdx.x < q.m) su[threadIdx.x] = zk[q.u_off + threadIdx.x];
+    __syncthreads();
+    // one warp per column: lanes stride the rows, a shuffle reduction gives the column's 1-norm
+    // (iso half storage: the right half has the same column sums)
     double worst = 0.0;
-    int bad = !isfinite(dt);
-    for (int col = 0; col < q.gcols; ++col) {   // iso half storage: the right half has the same column sums
+    bool bad = !isfinite(dt);
+    for (int col = warp; col < q.gcols; col += nwarp) {
         double part = 0.0;
-        for (int r = threadIdx.x; r < q.dp; r += blockDim.x) {
-            long long e = r + (long long)col * q.dp;
+        for (int r = lane; r < q.dp; r += 32) {
+            const long long e = r + (long long)col * q.dp;
             double v = G0[e];
-            for (int j = 0; j < q.m; ++j) v = fma(zk[q.u_off + j], Gd[j * dd + e], v);
+            for (int j = 0; j < q.m; ++j) v = fma(su[j], Gd[j * dd + e], v);
             if (G) G[e] = v;
             part += fabs(dt * v);
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-        if ((threadIdx.x & 31) == 0) colsum[threadIdx.x >> 5] = part;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            double s = 0;
-            for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += colsum[w];
-            if (!isfinite(s)) bad = 1;
-            worst = fmax(worst, s);
-        }
-        __syncthreads();
+        if (!isfinite(part)) bad = true;
+        worst = fmax(worst, part);
     }
+    if (bad) worst = INFINITY;
+    if (lane == 0) wmax[warp] = worst;
+    __syncthreads();
     if (threadIdx.x == 0) {
-        if (bad) atomicExch(bad_flag, 1);
-        else atomicMax(norm_max_bits, (unsigned long long)__double_as_longlong(worst));
+        double w = 0.0;
+        for (int i = 0; i < nwarp; ++i) w = fmax(w, wmax[i]);
+        if (!isfinite(w)) atomicExch(bad_flag, 1);
+        else atomicMax(norm_max_bits, (unsigned long long)__double_as_longlong(w));
     }
 }
 
