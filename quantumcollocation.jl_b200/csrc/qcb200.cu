@@ -515,14 +515,20 @@ void ensure_scratch(qcb_handle_s *h, int s_need) {
     const size_t per = scratch_bytes_per_unit(h, s_cap);
     long long cu = (long long)((budget_mb << 20) / per);
     cu = std::max(1LL, std::min<long long>(cu, h->units));
-    if (cu < h->units && cu * h->m > 2LL * h->n_sm) {
-        // pick the chunk size near the budget whose (unit x direction) batch fills whole waves best
-        long long best = cu;
-        double best_eff = 0;
-        for (long long t = cu; t > cu * 3 / 4 && t > 0; --t) {
-            long long ctas = t * std::max(1, h->m);
-            double eff = (double)ctas / (double)(((ctas + h->n_sm - 1) / h->n_sm) * h->n_sm);
-            if (eff > best_eff + 1e-9) { best_eff = eff; best = t; }
+    if (cu < h->units && h->m > 0) {
+        // choose the chunk size (<= the budget) that wastes the fewest CTA waves over the whole slab:
+        // the per-direction launches dominate, each has chunk*m CTAs on n_sm*ctas_per_sm slots
+        const long long slots = (long long)h->n_sm * (h->iso ? 2 : 1);
+        const long long tiles = h->iso ? (h->dp / 128) : ((h->dp % 128 == 0) ? (long long)(h->dp / 128) * (h->dp / 128)
+                                                                              : (long long)(h->dp / 64) * (h->dp / 64));
+        long long best = cu, best_waves = -1;
+        for (long long t = cu; t >= std::max(1LL, cu * 2 / 3); --t) {
+            long long waves = 0;
+            for (long long done = 0; done < h->units; done += t) {
+                const long long n_ = std::min<long long>(t, h->units - done);
+                waves += (n_ * h->m * tiles + slots - 1) / slots;
+            }
+            if (best_waves < 0 || waves < best_waves) { best_waves = waves; best = t; }
         }
         cu = best;
     }
