@@ -29,7 +29,8 @@ typedef struct {
     double *fixed[QR_NUM_FIXED];
     double *E[QCB_MAX_SQUARINGS + 1];
     double *W[QCB_MAX_SQUARINGS + 1];
-    double *dslot[QCB_NUM_DSLOTS];
+    double **dpersist;   /* [QCB_NUM_DPERSIST * m] : DA2, DA4, DZ1, DZ2 of every direction */
+    double *dtemp[QCB_NUM_DTEMP];
     double **L;      /* m + 1 rotating slots */
     int *Lidx;       /* L slot of direction j */
     int Lfree;
@@ -83,7 +84,9 @@ static double *resolve(ws_t *w, int r) {
     case QR_GJ: return (double *)w->Gj;
     case QR_L: return w->L[w->Lidx[w->j]];
     case QR_LN: return w->L[w->Lfree];
-    default: return w->dslot[qcb_dslot(r)];
+    default:
+        if (qcb_dpersist(r) >= 0) return w->dpersist[qcb_dpersist(r) * w->m + w->j];
+        return w->dtemp[qcb_dtemp(r)];
     }
 }
 
@@ -124,7 +127,9 @@ static ws_t *ws_new(int d, int m) {
         w->E[i] = (double *)malloc(dd * sizeof(double));
         w->W[i] = (double *)malloc(dd * sizeof(double));
     }
-    for (int i = 0; i < QCB_NUM_DSLOTS; ++i) w->dslot[i] = (double *)malloc(dd * sizeof(double));
+    w->dpersist = (double **)malloc((size_t)QCB_NUM_DPERSIST * (m + 1) * sizeof(double *));
+    for (int i = 0; i < QCB_NUM_DPERSIST * m; ++i) w->dpersist[i] = (double *)malloc(dd * sizeof(double));
+    for (int i = 0; i < QCB_NUM_DTEMP; ++i) w->dtemp[i] = (double *)malloc(dd * sizeof(double));
     w->L = (double **)malloc((m + 1) * sizeof(double *));
     for (int i = 0; i <= m; ++i) w->L[i] = (double *)malloc(dd * sizeof(double));
     w->Lidx = (int *)malloc((m + 1) * sizeof(int));
@@ -135,7 +140,9 @@ static ws_t *ws_new(int d, int m) {
 static void ws_free(ws_t *w) {
     for (int i = 0; i < QR_NUM_FIXED; ++i) free(w->fixed[i]);
     for (int i = 0; i <= QCB_MAX_SQUARINGS; ++i) { free(w->E[i]); free(w->W[i]); }
-    for (int i = 0; i < QCB_NUM_DSLOTS; ++i) free(w->dslot[i]);
+    for (int i = 0; i < QCB_NUM_DPERSIST * w->m; ++i) free(w->dpersist[i]);
+    free(w->dpersist);
+    for (int i = 0; i < QCB_NUM_DTEMP; ++i) free(w->dtemp[i]);
     for (int i = 0; i <= w->m; ++i) free(w->L[i]);
     free(w->L); free(w->Lidx); free(w->tA); free(w->tB); free(w);
 }
@@ -191,20 +198,27 @@ static int unit(ws_t *w, int d, int c, int m, const double *G0, const double *Gd
     for (int j = 0; j < m; ++j) {
         w->j = j; w->Gj = Gd + (size_t)j * dd; w->level = 0;
         for (int i = 0; i < QCB_NOPS(QCB_P5); ++i) run_op(w, &QCB_P5[i]);
-        if (hess) {
-            for (int i = 0; i < QCB_NOPS(QCB_P6); ++i) run_op(w, &QCB_P6[i]);
-            const double *dAb = resolve(w, QR_DAB);
-            for (int i = 0; i < m; ++i) H[j * m + i] = dot(dAb, Gd + (size_t)i * dd, dd);
-        }
+    }
+    if (hess) {     /* second order at the polynomial level: one product per node and direction */
+        for (int o = 0; o < QCB_NOPS(QCB_P6); ++o)
+            for (int j = 0; j < m; ++j) {
+                w->j = j; w->Gj = Gd + (size_t)j * dd; w->level = 0;
+                run_op(w, &QCB_P6[o]);
+                const double *U = resolve(w, QR_U);
+                for (int i = 0; i < m; ++i) {
+                    w->j = i; w->Gj = Gd + (size_t)i * dd;
+                    H[j * m + i] += dot(U, resolve(w, QCB_P6_PARTNER[o]), dd);
+                }
+            }
     }
     for (int l = 0; l < s; ++l) {
         w->level = l;
         if (hess)
             for (int j = 0; j < m; ++j) {
                 w->j = j;
-                run_op(w, &QCB_P7S[0]);
-                const double *Sj = resolve(w, QR_S);
-                for (int i = 0; i < m; ++i) H[j * m + i] += dot(Sj, w->L[w->Lidx[i]], dd);
+                run_op(w, &QCB_P7U[0]);
+                const double *U = resolve(w, QR_U);
+                for (int i = 0; i < m; ++i) H[j * m + i] += dot(U, w->L[w->Lidx[i]], dd);
             }
         for (int j = 0; j < m; ++j) {
             w->j = j;
@@ -249,7 +263,7 @@ static int unit(ws_t *w, int d, int c, int m, const double *G0, const double *Gd
         transpose(w->tA, G, d);
         gemm_nn_acc(GW, w->tA, Wt, d, d, d, d, d, d);
         for (int i = 0; i < m; ++i)
-            for (int j = 0; j < m; ++j) HUU[i * m + j] = -0.5 * tau * tau * (H[i * m + j] + H[j * m + i]);
+            for (int j = 0; j < m; ++j) HUU[i * m + j] = -tau * tau * (H[i * m + j] + H[j * m + i]);
         for (int j = 0; j < m; ++j)
             HUT[j] = -(dot(WE, Gd + (size_t)j * dd, dd) + tau * dot(GW, w->L[w->Lidx[j]], dd));
         HTT[0] = -dot(GW, GE, dd);

@@ -652,15 +652,17 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             X.level = 0; X.cur = 0;
             if (m > 0) {
                 for (int i = 0; i < QCB_NOPS(QCB_P5); ++i) X.run(QCB_P5[i], m);
-                if (wh) {
-                    for (int i = 0; i < QCB_NOPS(QCB_P6); ++i) X.run(QCB_P6[i], m);
-                    X.contract(X.reg(QR_DAB), m, X.reg(QR_GJ), m, h->sc_H, 0);
+                if (wh) {   // second order: one product per node and direction, then m x m contractions
+                    for (int i = 0; i < QCB_NOPS(QCB_P6); ++i) {
+                        X.run(QCB_P6[i], m);
+                        X.contract(X.reg(QR_U), m, X.reg(QCB_P6_PARTNER[i]), m, h->sc_H, i > 0);
+                    }
                 }
                 for (int l = 0; l < s; ++l) {
                     X.level = l;
                     if (wh) {
-                        X.run(QCB_P7S[0], m);
-                        X.contract(X.reg(QR_S), m, X.reg(QR_L), m, h->sc_H, 1);
+                        X.run(QCB_P7U[0], m);
+                        X.contract(X.reg(QR_U), m, X.reg(QR_L), m, h->sc_H, 1);
                     }
                     X.run(QCB_P7L[0], m);
                     X.cur ^= 1;
@@ -865,7 +867,8 @@ void init_constants() {
     CK(cudaMemcpyToSymbol(c_P4, QCB_P4, sizeof(QCB_P4)));
     CK(cudaMemcpyToSymbol(c_P5, QCB_P5, sizeof(QCB_P5)));
     CK(cudaMemcpyToSymbol(c_P6, QCB_P6, sizeof(QCB_P6)));
-    CK(cudaMemcpyToSymbol(c_P7S, QCB_P7S, sizeof(QCB_P7S)));
+    CK(cudaMemcpyToSymbol(c_P6_partner, QCB_P6_PARTNER, sizeof(QCB_P6_PARTNER)));
+    CK(cudaMemcpyToSymbol(c_P7U, QCB_P7U, sizeof(QCB_P7U)));
     CK(cudaMemcpyToSymbol(c_P7L, QCB_P7L, sizeof(QCB_P7L)));
     CK(cudaMemcpyToSymbol(c_taylor, QCB_TAYLOR, sizeof(QCB_TAYLOR)));
 }

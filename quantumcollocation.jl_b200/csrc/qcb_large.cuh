@@ -705,7 +705,7 @@ __global__ void finalize_scalars_kernel(int m, const double *tau, const double *
     const double *Hu = H + (long long)unit * m * m;
     for (int e = threadIdx.x; e < m * m; e += blockDim.x) {
         int i = e / m, j = e % m;
-        out[e] = -0.5 * fac * t * t * (Hu[i * m + j] + Hu[j * m + i]);
+        out[e] = -fac * t * t * (Hu[i * m + j] + Hu[j * m + i]);   // H = C + C^T (node contractions)
     }
     for (int j = threadIdx.x; j < m; j += blockDim.x)
         out[m * m + j] = -fac * (c1[(long long)unit * m + j] + t * c2[(long long)unit * m + j]);

@@ -46,22 +46,23 @@ enum {
     QR_W0,                        /* Wlev[0] */
     /* system constant: generator of the current drive direction j */
     QR_GJ = 24,
-    /* per (unit, direction) temporaries; several share a physical slot (see qcb_dslot) */
+    /* per (unit, direction) registers (see qcb_dslot / qcb_dpersist) */
     QR_DA2 = 32, QR_DA3, QR_DA4, QR_DZ1, QR_DZ2,
-    QR_DZB1, QR_DZB2, QR_DAB4, QR_DAB3, QR_DAB2,
-    QR_DAB,                       /* aliases DA3 */
-    QR_S,                         /* aliases DA2 */
+    QR_U,                         /* X_dot^T * N_bar of the current product node */
     QR_L = 48,                    /* L_j at the current level */
     QR_LN                         /* L_j at the next level */
 };
-#define QCB_NUM_DSLOTS 10
+#define QCB_NUM_DSLOTS 6          /* one slot per register when every direction has its own set */
+#define QCB_NUM_DPERSIST 4        /* DA2, DA4, DZ1, DZ2: read again by the contractions of every direction */
+#define QCB_NUM_DTEMP 2           /* DA3, U: dead once the direction's op sequence is over */
 
-QCB_HD static inline int qcb_is_dreg(int r) { return r >= QR_DA2 && r <= QR_S; }
-QCB_HD static inline int qcb_dslot(int r) {
-    if (r == QR_DAB) return QR_DA3 - QR_DA2;
-    if (r == QR_S) return QR_DA2 - QR_DA2;
-    return r - QR_DA2;
+QCB_HD static inline int qcb_is_dreg(int r) { return r >= QR_DA2 && r <= QR_U; }
+QCB_HD static inline int qcb_dslot(int r) { return r - QR_DA2; }
+/* index among the persistent per-direction registers, or -1 */
+QCB_HD static inline int qcb_dpersist(int r) {
+    return r == QR_DA2 ? 0 : r == QR_DA4 ? 1 : r == QR_DZ1 ? 2 : r == QR_DZ2 ? 3 : -1;
 }
+QCB_HD static inline int qcb_dtemp(int r) { return r == QR_DA3 ? 0 : 1; }
 
 typedef struct { uint8_t a, b, ta, tb; } qcb_term;
 typedef struct { uint8_t reg, coef; } qcb_lin;
@@ -110,19 +111,25 @@ static const qcb_op QCB_P5[] = {
     { QR_DZ1, 2, 3, -1, { T_(QR_DA4, QR_Z2, 0, 0), T_(QR_A4, QR_DZ2, 0, 0), NOT_, NOT_, NOT_, NOT_ }, { { QR_GJ, 5 }, { QR_DA2, 6 }, { QR_DA3, 7 }, NOL_ } },
     { QR_L, 2, 3, -1, { T_(QR_DA4, QR_Z1, 0, 0), T_(QR_A4, QR_DZ1, 0, 0), NOT_, NOT_, NOT_, NOT_ }, { { QR_GJ, 1 }, { QR_DA2, 2 }, { QR_DA3, 3 }, NOL_ } },
 };
-/* Phase 6: tangent of the reverse sweep along G_j (per unit x direction) */
+/* Phase 6: second-order terms at the polynomial level.  For a computation made of products
+ * N = X*Y and linear combinations, d^2 <W, T> / du_i du_j = sum over product nodes of
+ * <N_bar, X_dot_i Y_dot_j + X_dot_j Y_dot_i>, with N_bar the first-order adjoint of the node (phase
+ * 4) and X_dot, Y_dot the forward tangents (phase 5).  Per node and direction j one product
+ * U_j = X_dot_j^T N_bar, then C[j][i] += <U_j, Y_dot_i> for every i; H = C + C^T.  The nodes of
+ * phase 1: A2 = A*A, A3 = A*A2, A4 = A2*A2, Y2 = A4*Z2, Y1 = A4*Z1 (the two that share the partner
+ * dA2 are merged). */
 static const qcb_op QCB_P6[] = {
-    { QR_DZB1, 1, 0, -1, { T_(QR_DA4, QR_W0, 1, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
-    { QR_DZB2, 2, 0, -1, { T_(QR_DA4, QR_ZB1, 1, 0), T_(QR_A4, QR_DZB1, 1, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
-    { QR_DAB4, 3, 1, -1, { T_(QR_W0, QR_DZ1, 0, 1), T_(QR_DZB1, QR_Z2, 0, 1), T_(QR_ZB1, QR_DZ2, 0, 1), NOT_, NOT_, NOT_ }, { { QR_DZB2, 12 }, NOL_, NOL_, NOL_ } },
-    { QR_DAB3, 0, 2, -1, { NOT_, NOT_, NOT_, NOT_, NOT_, NOT_ }, { { QR_DZB1, 7 }, { QR_DZB2, 11 }, NOL_, NOL_ } },
-    { QR_DAB2, 6, 2, -1, { T_(QR_DAB4, QR_A2, 0, 1), T_(QR_AB4, QR_DA2, 0, 1), T_(QR_DA2, QR_AB4, 1, 0), T_(QR_A2, QR_DAB4, 1, 0), T_(QR_GJ, QR_AB3, 1, 0), T_(QR_A, QR_DAB3, 1, 0) }, { { QR_DZB1, 6 }, { QR_DZB2, 10 }, NOL_, NOL_ } },
-    { QR_DAB, 6, 2, -1, { T_(QR_DAB3, QR_A2, 0, 1), T_(QR_AB3, QR_DA2, 0, 1), T_(QR_DAB2, QR_A, 0, 1), T_(QR_AB2, QR_GJ, 0, 1), T_(QR_GJ, QR_AB2, 1, 0), T_(QR_A, QR_DAB2, 1, 0) }, { { QR_DZB1, 5 }, { QR_DZB2, 9 }, NOL_, NOL_ } },
+    { QR_U, 1, 0, -1, { T_(QR_GJ, QR_AB2, 1, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+    { QR_U, 2, 0, -1, { T_(QR_GJ, QR_AB3, 1, 0), T_(QR_DA2, QR_AB4, 1, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+    { QR_U, 1, 0, -1, { T_(QR_DA4, QR_ZB1, 1, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+    { QR_U, 1, 0, -1, { T_(QR_DA4, QR_W0, 1, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
 };
-/* Phase 7 (per level l = 0..s-1, per direction):
- *   S_j = L_j^T W[l+1] + W[l+1] L_j^T ;  H[j][i] += <S_j, L_i> ;  L_j <- E[l] L_j + L_j E[l] */
-static const qcb_op QCB_P7S[] = {
-    { QR_S, 2, 0, -1, { T_(QR_L, QR_WL1, 1, 0), T_(QR_WL1, QR_L, 0, 1), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
+/* the register whose direction-i instance is contracted with U_j after each op of phase 6 */
+static const uint8_t QCB_P6_PARTNER[] = { QR_GJ, QR_DA2, QR_DZ2, QR_DZ1 };
+/* Phase 7 (per level l = 0..s-1, per direction): the squaring E[l+1] = E[l]*E[l] is a product node
+ * with adjoint W[l+1]:  U_j = L_j^T W[l+1] ;  C[j][i] += <U_j, L_i> ;  L_j <- E[l] L_j + L_j E[l] */
+static const qcb_op QCB_P7U[] = {
+    { QR_U, 1, 0, -1, { T_(QR_L, QR_WL1, 1, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
 };
 static const qcb_op QCB_P7L[] = {
     { QR_LN, 2, 0, -1, { T_(QR_EL, QR_L, 0, 0), T_(QR_L, QR_EL, 0, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
@@ -149,6 +156,7 @@ QCB_HD static inline int qcb_squarings(double norm1) {
 /* ---- canonical per-unit value arenas (sources of the COO value vectors) ----
  * Jacobian arena : [ E (dp*dp) | JU_0..JU_{m-1} (dp*cp each) | JT (dp*cp) | 0.0 | 1.0 ]
  * Hessian arena  : [ HXU_0..HXU_{m-1} (dp*cp each) | HXT (dp*cp) | HUU (m*m) | HUT (m) | HTT (1) | 0.0 ]
+ * (HUU = -tau^2 (C + C^T) with C the accumulated node contractions of phases 6 and 7)
  * E is stored with its own sign (the x_k block of the Jacobian is -E: the slot code carries
  * the sign); every other entry is stored with the sign of the derivative of delta.
  * Slot code: bit 31 = negate, bits 0..30 = offset into the unit's arena. */

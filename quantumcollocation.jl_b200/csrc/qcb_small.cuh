@@ -14,7 +14,8 @@
 
 namespace qcb {
 
-__constant__ qcb_op c_P1[6], c_P2[1], c_P3[1], c_P4[5], c_P5[6], c_P6[6], c_P7S[1], c_P7L[1];
+__constant__ qcb_op c_P1[6], c_P2[1], c_P3[1], c_P4[5], c_P5[6], c_P6[4], c_P7U[1], c_P7L[1];
+__constant__ uint8_t c_P6_partner[4];
 __constant__ double c_taylor[QCB_TAYLOR_DEGREE + 1];
 
 struct SmallParams {
@@ -38,7 +39,8 @@ struct SmallCtx {
     int e0, tpu;     // this thread's first element and the element stride
     double *fixed;   // [QR_NUM_FIXED][dd]
     double *E, *W;   // [smax+1][dd]
-    double *dslot;   // [QCB_NUM_DSLOTS][dd]
+    double *dpersist;  // [QCB_NUM_DPERSIST][m][dd]: DA2, DA4, DZ1, DZ2 of every direction
+    double *dtemp;     // [QCB_NUM_DTEMP][dd]: DA3, U
     double *L;       // [m+1][dd]
     const double *Gj;
     const int *Lidx; // [m+1] shared by the CTA (slot of direction j; entry m = free slot)
@@ -56,7 +58,9 @@ __device__ __forceinline__ double *sm_resolve(const SmallCtx &x, int r) {
     case QR_GJ: return const_cast<double *>(x.Gj);
     case QR_L: return x.L + x.Lidx[x.j] * x.dd;
     case QR_LN: return x.L + x.Lidx[x.m] * x.dd;
-    default: return x.dslot + qcb_dslot(r) * x.dd;
+    default:
+        if (qcb_dpersist(r) >= 0) return x.dpersist + (qcb_dpersist(r) * x.m + x.j) * x.dd;
+        return x.dtemp + qcb_dtemp(r) * x.dd;
     }
 }
 
@@ -161,7 +165,7 @@ __device__ __noinline__ void sm_panel(double *C, const double *A, int ta, const 
 
 static inline size_t small_unit_doubles(int d, int c, int m, int smax) {
     size_t dd = (size_t)d * d, dc = (size_t)d * c;
-    size_t n = (QR_NUM_FIXED + 2 * (size_t)(smax + 1) + QCB_NUM_DSLOTS + (m + 1)) * dd;
+    size_t n = (QR_NUM_FIXED + 2 * (size_t)(smax + 1) + (size_t)QCB_NUM_DPERSIST * m + QCB_NUM_DTEMP + (m + 1)) * dd;
     n += 3 * dc;                                   // X, Xn, M panels
     n += dd + (m + 1) * dc + 2;                    // Jacobian arena
     n += (m + 1) * dc + (size_t)m * m + m + 2;     // Hessian arena
@@ -190,7 +194,8 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     x.fixed = ptr; ptr += QR_NUM_FIXED * dd;
     x.E = ptr; ptr += (p.smax + 1) * dd;
     x.W = ptr; ptr += (p.smax + 1) * dd;
-    x.dslot = ptr; ptr += QCB_NUM_DSLOTS * dd;
+    x.dpersist = ptr; ptr += QCB_NUM_DPERSIST * m * dd;
+    x.dtemp = ptr; ptr += QCB_NUM_DTEMP * dd;
     x.L = ptr; ptr += (m + 1) * dd;
     double *X = ptr; ptr += dc;
     double *Xn = ptr; ptr += dc;
@@ -279,18 +284,25 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
         x.level = 0;
         for (int i = 0; i < 5; ++i) sm_run_op<D>(x, c_P4[i]);
     }
-    // ---- per-direction tangents ----
+    // ---- per-direction first-order tangents ----
     for (int j = 0; j < m; ++j) {
         x.j = j; x.Gj = Gd + (long long)j * dd; x.level = 0;
         for (int i = 0; i < 6; ++i) sm_run_op<D>(x, c_P5[i]);
-        if (want_hess) {
-            for (int i = 0; i < 6; ++i) sm_run_op<D>(x, c_P6[i]);
-            const double *dAb = sm_resolve(x, QR_DAB);
-            for (int i = 0; i < m; ++i) {
-                double v = sm_dot(dAb, Gd + (long long)i * dd, dd, e0, tpu, red);
-                if (e0 == 0) Hacc[j * m + i] = v;
+    }
+    // ---- second order at the polynomial level: U_j = Xdot_j^T Nbar per product node, then
+    //      C[j][i] += <U_j, Ydot_i> ----
+    if (want_hess) {
+        for (int o = 0; o < 4; ++o)
+            for (int j = 0; j < m; ++j) {
+                x.j = j; x.Gj = Gd + (long long)j * dd; x.level = 0;
+                sm_run_op<D>(x, c_P6[o]);
+                const double *U = x.dtemp + qcb_dtemp(QR_U) * dd;
+                for (int i = 0; i < m; ++i) {
+                    x.j = i; x.Gj = Gd + (long long)i * dd;
+                    double v = sm_dot(U, sm_resolve(x, c_P6_partner[o]), dd, e0, tpu, red);
+                    if (e0 == 0) Hacc[j * m + i] += v;
+                }
             }
-        }
     }
     // ---- squaring levels ----
     for (int l = 0; l < s; ++l) {
@@ -298,10 +310,10 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
         if (want_hess) {
             for (int j = 0; j < m; ++j) {
                 x.j = j;
-                sm_run_op<D>(x, c_P7S[0]);
-                const double *Sj = sm_resolve(x, QR_S);
+                sm_run_op<D>(x, c_P7U[0]);
+                const double *U = x.dtemp + qcb_dtemp(QR_U) * dd;
                 for (int i = 0; i < m; ++i) {
-                    double v = sm_dot(Sj, x.L + Lidx[i] * dd, dd, e0, tpu, red);
+                    double v = sm_dot(U, x.L + Lidx[i] * dd, dd, e0, tpu, red);
                     if (e0 == 0) Hacc[j * m + i] += v;
                 }
             }
@@ -340,7 +352,7 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
         __syncthreads();                                  // Hacc complete (written by e0 == 0 lanes)
         for (int e = e0; e < m * m; e += tpu) {
             const int i = e / m, j = e % m;
-            HUU[e] = -0.5 * tau * tau * (Hacc[i * m + j] + Hacc[j * m + i]);
+            HUU[e] = -tau * tau * (Hacc[i * m + j] + Hacc[j * m + i]);
         }
         for (int j = 0; j < m; ++j) {
             double c1 = sm_dot(WE, Gd + (long long)j * dd, dd, e0, tpu, red);
