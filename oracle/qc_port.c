@@ -310,3 +310,54 @@ int qc_port_eval(int d, int c, int m, int N, int S, int z_dim, const int *x_off,
     }
     return fails;
 }
+
+/* Same evaluation, but delivering what the reference's evaluator must deliver to Ipopt: the COO value
+ * vectors in the caller's sparsity order.  jcode / hcode: [S][jnnz] / [S][hnnz] slot codes (bit 31 =
+ * negate, bits 0..30 = arena offset) as built by oracle/qc_port.py:arena_codes.  Outputs are indexed
+ * [s][k - k_begin][entry]. */
+int qc_port_eval_coo(int d, int c, int m, int N, int S, int z_dim, const int *x_off, int u_off, int dt_off,
+                     const double *G0, const double *Gd, const double *Z, const double *mu,
+                     int k_begin, int k_end, const unsigned *jcode, long long jnnz, const unsigned *hcode,
+                     long long hnnz, double *delta, double *jac, double *hess, int nthreads) {
+    int K = N - 1, nk = k_end - k_begin, xd = d * c;
+    size_t dd = (size_t)d * d, JA = qc_port_jac_arena(d, c, m), HA = qc_port_hess_arena(d, c, m);
+    int fails = 0;
+    int want = (jac ? 1 : 0) | ((hess && mu) ? 2 : 0);
+#ifdef _OPENMP
+    if (nthreads > 0) omp_set_num_threads(nthreads);
+#endif
+#pragma omp parallel reduction(+ : fails)
+    {
+        ws_t *w = ws_new(d, m);
+        double *jtmp = (double *)malloc(JA * sizeof(double));
+        double *htmp = (double *)malloc(HA * sizeof(double));
+#pragma omp for schedule(dynamic, 1)
+        for (int un = 0; un < S * nk; ++un) {
+            int s = un / nk, kl = un % nk, k = k_begin + kl;
+            const double *zk = Z + (size_t)k * z_dim, *zn = zk + z_dim;
+            const double *mk = mu ? mu + ((size_t)s * K + k) * xd : NULL;
+            int rc = unit(w, d, c, m, G0 + (size_t)s * dd, Gd + (size_t)s * m * dd, zk + x_off[s], zn + x_off[s],
+                          mk, zk + u_off, zk[dt_off], want, delta + (size_t)un * xd, jtmp, htmp);
+            if (rc) { ++fails; continue; }
+            if (want & 1) {
+                const unsigned *cd = jcode + (size_t)s * jnnz;
+                double *o = jac + (size_t)un * jnnz;
+                for (long long e = 0; e < jnnz; ++e) {
+                    double v = jtmp[cd[e] & 0x7fffffffu];
+                    o[e] = (cd[e] >> 31) ? -v : v;
+                }
+            }
+            if (want & 2) {
+                const unsigned *cd = hcode + (size_t)s * hnnz;
+                double *o = hess + (size_t)un * hnnz;
+                for (long long e = 0; e < hnnz; ++e) {
+                    double v = htmp[cd[e] & 0x7fffffffu];
+                    o[e] = (cd[e] >> 31) ? -v : v;
+                }
+            }
+        }
+        free(jtmp); free(htmp);
+        ws_free(w);
+    }
+    return fails;
+}

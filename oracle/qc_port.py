@@ -35,6 +35,11 @@ def lib(native: bool = False):
         L.qc_port_eval.argtypes = [ctypes.c_int] * 6 + [_ip, ctypes.c_int, ctypes.c_int,
                                    _dp, _dp, _dp, _dp, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                    _dp, _dp, _dp, ctypes.c_int]
+        L.qc_port_eval_coo.restype = ctypes.c_int
+        _up = ctypes.POINTER(ctypes.c_uint32)
+        L.qc_port_eval_coo.argtypes = [ctypes.c_int] * 6 + [_ip, ctypes.c_int, ctypes.c_int, _dp, _dp, _dp, _dp,
+                                       ctypes.c_int, ctypes.c_int, _up, ctypes.c_longlong, _up, ctypes.c_longlong,
+                                       _dp, _dp, _dp, ctypes.c_int]
         _libs[native] = L
     return _libs[native]
 
@@ -120,4 +125,46 @@ def evaluate(layout, G0, Gd, Z, mu=None, want_jac=True, want_hess=True, k_range=
             _, _, hi = arena_codes(L, s)
             hess[s] = ha[s * nk:(s + 1) * nk][:, hi]
         hess = hess.reshape(-1)
+    return delta, jac, hess
+
+
+_code_cache = {}
+
+
+def slot_codes(layout):
+    """uint32 slot codes [S, nnz] (bit 31 = negate) of the native structure, cached per layout."""
+    L = layout
+    key = (L.d, L.c, L.m, L.S, L.z_dim, tuple(L.x_off), L.u_off, L.dt_off, L.jac_mode)
+    if key not in _code_cache:
+        jc, hc = [], []
+        for s in range(L.S):
+            ji, js, hi = arena_codes(L, s)
+            jc.append(ji.astype(np.uint32) | np.where(js < 0, np.uint32(0x80000000), np.uint32(0)).astype(np.uint32))
+            hc.append(hi.astype(np.uint32))
+        _code_cache[key] = (np.ascontiguousarray(np.stack(jc)), np.ascontiguousarray(np.stack(hc)))
+    return _code_cache[key]
+
+
+def evaluate_coo(layout, G0, Gd, Z, mu, k_range=None, nthreads=0, native=False, out=None):
+    """CPU evaluator delivering the COO value vectors (what the reference hands to Ipopt), assembled
+    inside the C port.  Returns (delta, jac_vals, hess_vals)."""
+    L = layout
+    k0, k1 = (0, L.K) if k_range is None else k_range
+    nk = k1 - k0
+    lb = lib(native)
+    jc, hc = slot_codes(L)
+    G0 = np.ascontiguousarray(np.transpose(G0, (0, 2, 1)), dtype=np.float64)
+    Gd = np.ascontiguousarray(np.transpose(Gd, (0, 1, 3, 2)), dtype=np.float64)
+    Z = np.ascontiguousarray(Z, dtype=np.float64)
+    mu = np.ascontiguousarray(mu, dtype=np.float64)
+    if out is None:
+        out = (np.empty(L.S * nk * L.x_dim), np.empty(L.S * nk * L.jac_nnz_unit), np.empty(L.S * nk * L.hess_nnz_unit))
+    delta, jac, hess = out
+    xo = np.asarray(L.x_off, dtype=np.int32)
+    _up = ctypes.POINTER(ctypes.c_uint32)
+    fails = lb.qc_port_eval_coo(L.d, L.c, L.m, L.N, L.S, L.z_dim, xo.ctypes.data_as(_ip), L.u_off, L.dt_off,
+                                _p(G0), _p(Gd), _p(Z), _p(mu), k0, k1, jc.ctypes.data_as(_up), L.jac_nnz_unit,
+                                hc.ctypes.data_as(_up), L.hess_nnz_unit, _p(delta), _p(jac), _p(hess), nthreads)
+    if fails:
+        raise FloatingPointError(f"{fails} units had ||dt*G(u)||_1 out of range or non-finite")
     return delta, jac, hess

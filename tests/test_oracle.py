@@ -201,3 +201,14 @@ def test_golden_vectors(name, N, S, built_libs):
     assert rel_err(d1, g[f"{name}.delta"]) < 1e-13
     assert rel_err(j1, g[f"{name}.jac"]) < 1e-13
     assert rel_err(h1, g[f"{name}.hess"]) < 1e-12
+
+
+def test_port_coo_delivery_matches_arena_route(built_libs):
+    """The timed CPU baseline (qc_port_eval_coo: COO value vectors assembled inside the C port)
+    gives exactly what the arena route + numpy indexing gives."""
+    for name, N, S in (("cfg2", 5, None), ("cfg4", 4, 3), ("cfg3_ket", 4, None)):
+        w = workloads.make(name, N=N, S=S)
+        OL = oracle_layout(w.layout)
+        a = P.evaluate(OL, w.G_drift, w.G_drives, w.Z, w.mu)
+        b = P.evaluate_coo(OL, w.G_drift, w.G_drives, w.Z, w.mu)
+        assert all(np.array_equal(x, y) for x, y in zip(a, b))
