@@ -169,6 +169,7 @@ def main():
     ap.add_argument("--ref-units", type=int, default=None)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--out-mem", default="auto", choices=["auto", "pinned", "pageable"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
 
@@ -268,9 +269,18 @@ def main():
         if world == 1:
             hZ = torch.from_numpy(w.Z).pin_memory()
             hmu = torch.from_numpy(w.mu).pin_memory()
-            h_delta = torch.empty(n_delta, dtype=torch.float64, pin_memory=True)
-            h_jac = torch.empty(n_jac, dtype=torch.float64, pin_memory=True)
-            h_hess = torch.empty(n_hess, dtype=torch.float64, pin_memory=True)
+            # result buffers: pinned for the direct-DMA route (small-d path); ordinary (pageable,
+            # huge-page eligible) memory when the library writes them with the host cores
+            # (large-d path, compact transfer) -- which is also what Ipopt's own arrays are
+            out_pinned = args.out_mem != "pageable"      # measured: pinned is faster on both routes
+            if out_pinned:
+                h_delta = torch.empty(n_delta, dtype=torch.float64, pin_memory=True)
+                h_jac = torch.empty(n_jac, dtype=torch.float64, pin_memory=True)
+                h_hess = torch.empty(n_hess, dtype=torch.float64, pin_memory=True)
+            else:
+                h_delta = torch.from_numpy(np.zeros(n_delta))
+                h_jac = torch.from_numpy(np.zeros(n_jac))
+                h_hess = torch.from_numpy(np.zeros(n_hess))
             ptr = lambda t, off=0: t.data_ptr() + 8 * off
             pZ, pmu = ptr(hZ), ptr(hmu)
             p_delta, p_jac, p_hess = ptr(h_delta), ptr(h_jac), ptr(h_hess)
@@ -346,6 +356,7 @@ def main():
                 shm.unlink()
         e2e = {"value": units_total / (dt / args.steps), "unit": "knot-evals/s", "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "host_result_bytes_per_step": int(host_written),
+               "result_buffers": ("shared pinned" if world > 1 else ("pinned" if out_pinned else "pageable")),
                "ms_per_step": 1e3 * dt / args.steps,
                "last_call_rank0_ms": tm}
 

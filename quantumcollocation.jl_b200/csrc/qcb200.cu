@@ -119,17 +119,9 @@ namespace {
 // ---------------------------------------------------------------------------------------
 struct Codes {
     qcb_handle_s *h;
-    int64_t dd() const { return h->msz; }
+    int64_t dd() const { return (int64_t)h->dp * h->dp; }      // E slot of the Jacobian arena (always full)
     int64_t pan() const { return (int64_t)h->dp * h->cp; }
-    // value -E(rr, qq); in iso half storage only E_L = E(:, 0:n) is in the arena and
-    // E(i, j>=n) = -E_L(i+n, j-n) (i < n) or E_L(i-n, j-n) (i >= n)
-    uint32_t jE(int rr, int qq) const {
-        if (!h->iso) return (uint32_t)(rr + (int64_t)qq * h->dp) | QCB_CODE_NEG;
-        const int n = h->d / 2;
-        if (qq < n) return (uint32_t)(rr + (int64_t)qq * h->dp) | QCB_CODE_NEG;
-        if (rr < n) return (uint32_t)((rr + n) + (int64_t)(qq - n) * h->dp);
-        return (uint32_t)((rr - n) + (int64_t)(qq - n) * h->dp) | QCB_CODE_NEG;
-    }
+    uint32_t jE(int rr, int qq) const { return (uint32_t)(rr + (int64_t)qq * h->dp) | QCB_CODE_NEG; }   // -E(rr, qq)
     uint32_t jU(int j, int i) const { return (uint32_t)(dd() + j * pan() + (i % h->d) + (int64_t)(i / h->d) * h->dp); }
     uint32_t jT(int i) const { return jU(h->m, i); }
     uint32_t jZero() const { return (uint32_t)(dd() + (h->m + 1) * pan()); }
@@ -671,10 +663,16 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             // final blocks
             Opnd GE = X.fixed(QR_A2), WE = X.fixed(QR_A3), GW = X.fixed(QR_A4), L = X.reg(QR_L);
             X.product(GE, G, 0, Ef, 0, h->dp, ncol, h->dp, 1, 1.0, nullptr);
-            Opnd JU = X.mat(X.ja + dd, h->JA, pan), JT = X.mat(X.ja + dd + m * pan, h->JA);
+            const long long esz = (long long)h->dp * h->dp;   // the arena always holds the full E
+            Opnd JU = X.mat(X.ja + esz, h->JA, pan), JT = X.mat(X.ja + esz + m * pan, h->JA);
             if (m > 0) X.product(JU, L, 0, XP, 0, h->dp, h->cp, h->dp, m, 1.0, h->sc_ntau);
             X.product(JT, GE, 0, XP, 0, h->dp, h->cp, h->dp, 1, -1.0, nullptr);
-            arena_consts_kernel<<<(nu + 127) / 128, 128, 0, h->stream>>>(X.ja, h->JA, dd + (m + 1) * pan, nu);
+            arena_consts_kernel<<<(nu + 127) / 128, 128, 0, h->stream>>>(X.ja, h->JA, esz + (m + 1) * pan, nu);
+            if (h->iso) {   // right block column of E from the computed left one: the COO x-block is then c
+                            // contiguous copies of -E (long runs for the device gather and the host expansion)
+                iso_expand_kernel<<<nu, 256, 0, h->stream>>>(X.ja, h->JA, h->dp);
+                ++h->launches;
+            }
             ++h->launches;
             if (wh) {
                 Opnd Wt = X.W(s);
@@ -959,7 +957,7 @@ qcb_status qcb_create(qcb_handle *out, const qcb_desc *desc) {
         h->jnnz_unit = xb + (int64_t)xdim * (h->m + 2);
         h->hnnz_unit = (int64_t)xdim * (h->m + 1) + (int64_t)h->m * (h->m + 1) / 2 + h->m + 1;
         const int64_t dd = h->msz, pan = (int64_t)h->dp * h->cp;
-        h->JA = dd + (h->m + 1) * pan + 2;
+        h->JA = (int64_t)h->dp * h->dp + (h->m + 1) * pan + 2;
         h->HA = (h->m + 1) * pan + (int64_t)h->m * h->m + h->m + 2;
         h->HA += h->HA & 1;
         if (h->JA >= (1LL << 31) || h->HA >= (1LL << 31)) { delete h; return fail(nullptr, QCB_ERR_ARG, "unit too large for 31-bit slot codes"); }

@@ -472,6 +472,17 @@ bgemm_iso_kernel(const __grid_constant__ GemmArgs g) {
     }
 }
 
+// E(:, n:d) from E_L = E(:, 0:n) of an iso matrix stored at the head of each unit's arena
+__global__ void __launch_bounds__(256) iso_expand_kernel(double *arena, long long stride, int d) {
+    const int n = d >> 1;
+    double *E = arena + (long long)blockIdx.x * stride;
+    for (int e = threadIdx.x; e < d * n; e += blockDim.x) {
+        const int i = e % d, j = e / d;            // target (i, j + n)
+        const double v = (i < n) ? -E[(i + n) + (long long)j * d] : E[(i - n) + (long long)j * d];
+        E[i + (long long)(j + n) * d] = v;
+    }
+}
+
 // W_L = left block column of the projection of a general d x d matrix onto the iso algebra:
 //   P = (W11 + W22)/2,  Q = (W21 - W12)/2.   (<W, F> = <proj W, F> for every iso matrix F.)
 __global__ void __launch_bounds__(256)
