@@ -34,53 +34,58 @@ struct SmallParams {
     int *bad_flag;
 };
 
+// Matrices live in shared memory with an odd leading dimension (ld = d + 1 for even d): column and
+// row (transposed) walks are then both free of bank conflicts.
+QCB_HD static inline int small_ld(int d) { return (d & 1) ? d : d + 1; }
+
 struct SmallCtx {
-    int d, dd, m, level, j;
+    int d, ld, msz, m, level, j;
     int e0, tpu;     // this thread's first element and the element stride
-    double *fixed;   // [QR_NUM_FIXED][dd]
-    double *E, *W;   // [smax+1][dd]
-    double *dpersist;  // [QCB_NUM_DPERSIST][m][dd]: DA2, DA4, DZ1, DZ2 of every direction
-    double *dtemp;     // [QCB_NUM_DTEMP][dd]: DA3, U
-    double *L;       // [m+1][dd]
-    const double *Gj;
+    double *fixed;   // [QR_NUM_FIXED][msz]
+    double *E, *W;   // [smax+1][msz]
+    double *dpersist;  // [QCB_NUM_DPERSIST][m][msz]: DA2, DA4, DZ1, DZ2 of every direction
+    double *dtemp;     // [QCB_NUM_DTEMP][msz]: DA3, U
+    double *L;       // [m+1][msz]
+    const double *Gs;  // [m][msz] the unit's drive generators, staged in shared memory
     const int *Lidx; // [m+1] shared by the CTA (slot of direction j; entry m = free slot)
 };
 
 __device__ __forceinline__ double *sm_resolve(const SmallCtx &x, int r) {
-    if (r < QR_NUM_FIXED) return x.fixed + r * x.dd;
+    if (r < QR_NUM_FIXED) return x.fixed + r * x.msz;
     switch (r) {
-    case QR_EL: return x.E + x.level * x.dd;
-    case QR_EL1: return x.E + (x.level + 1) * x.dd;
-    case QR_WL: return x.W + x.level * x.dd;
-    case QR_WL1: return x.W + (x.level + 1) * x.dd;
+    case QR_EL: return x.E + x.level * x.msz;
+    case QR_EL1: return x.E + (x.level + 1) * x.msz;
+    case QR_WL: return x.W + x.level * x.msz;
+    case QR_WL1: return x.W + (x.level + 1) * x.msz;
     case QR_E0: return x.E;
     case QR_W0: return x.W;
-    case QR_GJ: return const_cast<double *>(x.Gj);
-    case QR_L: return x.L + x.Lidx[x.j] * x.dd;
-    case QR_LN: return x.L + x.Lidx[x.m] * x.dd;
+    case QR_GJ: return const_cast<double *>(x.Gs) + x.j * x.msz;
+    case QR_L: return x.L + x.Lidx[x.j] * x.msz;
+    case QR_LN: return x.L + x.Lidx[x.m] * x.msz;
     default:
-        if (qcb_dpersist(r) >= 0) return x.dpersist + (qcb_dpersist(r) * x.m + x.j) * x.dd;
-        return x.dtemp + qcb_dtemp(r) * x.dd;
+        if (qcb_dpersist(r) >= 0) return x.dpersist + (qcb_dpersist(r) * x.m + x.j) * x.msz;
+        return x.dtemp + qcb_dtemp(r) * x.msz;
     }
 }
 
-template <int D, int AS, int BS> __device__ __forceinline__ double dot_k(const double *a, const double *b, double acc, int d) {
-    // AS / BS: 1 = unit stride, 0 = stride d
+template <int D, int AS, int BS> __device__ __forceinline__ double dot_k(const double *a, const double *b, double acc, int d, int ld) {
+    // AS / BS: 1 = unit stride, 0 = stride ld
     if (D > 0) {
+        constexpr int LD = (D & 1) ? D : D + 1;
         // four independent partial sums: the FP64 FMA latency chain would otherwise bound an op
         double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0;
 #pragma unroll
         for (int k = 0; k + 3 < D; k += 4) {
-            p0 = fma(a[(k + 0) * (AS ? 1 : D)], b[(k + 0) * (BS ? 1 : D)], p0);
-            p1 = fma(a[(k + 1) * (AS ? 1 : D)], b[(k + 1) * (BS ? 1 : D)], p1);
-            p2 = fma(a[(k + 2) * (AS ? 1 : D)], b[(k + 2) * (BS ? 1 : D)], p2);
-            p3 = fma(a[(k + 3) * (AS ? 1 : D)], b[(k + 3) * (BS ? 1 : D)], p3);
+            p0 = fma(a[(k + 0) * (AS ? 1 : LD)], b[(k + 0) * (BS ? 1 : LD)], p0);
+            p1 = fma(a[(k + 1) * (AS ? 1 : LD)], b[(k + 1) * (BS ? 1 : LD)], p1);
+            p2 = fma(a[(k + 2) * (AS ? 1 : LD)], b[(k + 2) * (BS ? 1 : LD)], p2);
+            p3 = fma(a[(k + 3) * (AS ? 1 : LD)], b[(k + 3) * (BS ? 1 : LD)], p3);
         }
 #pragma unroll
-        for (int k = D & ~3; k < D; ++k) p0 = fma(a[k * (AS ? 1 : D)], b[k * (BS ? 1 : D)], p0);
+        for (int k = D & ~3; k < D; ++k) p0 = fma(a[k * (AS ? 1 : LD)], b[k * (BS ? 1 : LD)], p0);
         acc += (p0 + p1) + (p2 + p3);
     } else {
-        const int as = AS ? 1 : d, bs = BS ? 1 : d;
+        const int as = AS ? 1 : ld, bs = BS ? 1 : ld;
         for (int k = 0; k < d; ++k) acc = fma(a[k * as], b[k * bs], acc);
     }
     return acc;
@@ -88,26 +93,24 @@ template <int D, int AS, int BS> __device__ __forceinline__ double dot_k(const d
 
 // dst = sum_t op(a)op(b) + sum_r c*reg + c*I for this thread's unit.  Ends with a CTA barrier.
 template <int D> __device__ __noinline__ void sm_run_op(const SmallCtx &x, const qcb_op &op) {
-    const int d = D > 0 ? D : x.d, dd = d * d;
+    const int d = D > 0 ? D : x.d, ld = D > 0 ? ((D & 1) ? D : D + 1) : x.ld, dd = d * d;
     double *dst = sm_resolve(x, op.dst);
-    const double *A[QCB_MAX_TERMS], *B[QCB_MAX_TERMS], *R[QCB_MAX_LIN];
-    for (int t = 0; t < op.nterm; ++t) { A[t] = sm_resolve(x, op.term[t].a); B[t] = sm_resolve(x, op.term[t].b); }
-    for (int r = 0; r < op.nlin; ++r) R[r] = sm_resolve(x, op.lin[r].reg);
     for (int e = x.e0; e < dd; e += x.tpu) {
         const int r = e % d, q = e / d;
         double acc = 0.0;
         for (int t = 0; t < op.nterm; ++t) {
             const int ta = op.term[t].ta, tb = op.term[t].tb;
-            const double *a = A[t] + (ta ? r * d : r);      // a(r,k): stride d (plain) or 1 (transposed)
-            const double *b = B[t] + (tb ? q : q * d);      // b(k,q): stride 1 (plain) or d (transposed)
-            if (!ta && !tb) acc = dot_k<D, 0, 1>(a, b, acc, d);
-            else if (ta && !tb) acc = dot_k<D, 1, 1>(a, b, acc, d);
-            else if (!ta && tb) acc = dot_k<D, 0, 0>(a, b, acc, d);
-            else acc = dot_k<D, 1, 0>(a, b, acc, d);
+            const double *a = sm_resolve(x, op.term[t].a) + (ta ? r * ld : r);   // a(r,k): stride ld, or 1 if transposed
+            const double *b = sm_resolve(x, op.term[t].b) + (tb ? q : q * ld);   // b(k,q): stride 1, or ld if transposed
+            if (!ta && !tb) acc = dot_k<D, 0, 1>(a, b, acc, d, ld);
+            else if (ta && !tb) acc = dot_k<D, 1, 1>(a, b, acc, d, ld);
+            else if (!ta && tb) acc = dot_k<D, 0, 0>(a, b, acc, d, ld);
+            else acc = dot_k<D, 1, 0>(a, b, acc, d, ld);
         }
-        for (int l = 0; l < op.nlin; ++l) acc = fma(c_taylor[op.lin[l].coef], R[l][e], acc);
+        const int off = r + q * ld;
+        for (int l = 0; l < op.nlin; ++l) acc = fma(c_taylor[op.lin[l].coef], sm_resolve(x, op.lin[l].reg)[off], acc);
         if (op.ident >= 0 && r == q) acc += c_taylor[op.ident];
-        dst[e] = acc;
+        dst[off] = acc;
     }
     __syncthreads();
 }
@@ -143,20 +146,23 @@ __device__ __forceinline__ double unit_max(double v, int tpu, double *red_unit, 
     return s;
 }
 
-// Frobenius inner product over a unit
-__device__ __noinline__ double sm_dot(const double *a, const double *b, int n, int e0, int tpu, double *red_unit) {
+// Frobenius inner product of two d x d matrices (leading dimension ld) over a unit
+__device__ __noinline__ double sm_dot(const double *a, const double *b, int d, int ld, int e0, int tpu, double *red_unit) {
     double v = 0.0;
-    for (int e = e0; e < n; e += tpu) v = fma(a[e], b[e], v);
+    for (int e = e0; e < d * d; e += tpu) {
+        const int off = (e % d) + (e / d) * ld;
+        v = fma(a[off], b[off], v);
+    }
     return unit_sum(v, tpu, red_unit, e0);
 }
 
-// C (d x c) = scale * op(A) (d x d) * P (d x c)
-__device__ __noinline__ void sm_panel(double *C, const double *A, int ta, const double *P, int d, int c, double scale,
-                                      int e0, int tpu) {
+// C (d x c, packed) = scale * op(A) (d x d, ld) * P (d x c, packed)
+__device__ __noinline__ void sm_panel(double *C, const double *A, int ta, const double *P, int d, int ld, int c,
+                                      double scale, int e0, int tpu) {
     for (int e = e0; e < d * c; e += tpu) {
         const int r = e % d, b = e / d;
-        const double *a = A + (ta ? r * d : r);
-        const int as = ta ? 1 : d;
+        const double *a = A + (ta ? r * ld : r);
+        const int as = ta ? 1 : ld;
         double acc = 0.0;
         for (int k = 0; k < d; ++k) acc = fma(a[k * as], P[k + b * d], acc);
         C[e] = scale * acc;
@@ -164,8 +170,8 @@ __device__ __noinline__ void sm_panel(double *C, const double *A, int ta, const 
 }
 
 static inline size_t small_unit_doubles(int d, int c, int m, int smax) {
-    size_t dd = (size_t)d * d, dc = (size_t)d * c;
-    size_t n = (QR_NUM_FIXED + 2 * (size_t)(smax + 1) + (size_t)QCB_NUM_DPERSIST * m + QCB_NUM_DTEMP + (m + 1)) * dd;
+    size_t msz = (size_t)small_ld(d) * d, dd = (size_t)d * d, dc = (size_t)d * c;
+    size_t n = (QR_NUM_FIXED + 2 * (size_t)(smax + 1) + (size_t)QCB_NUM_DPERSIST * m + QCB_NUM_DTEMP + (m + 1) + m) * msz;
     n += 3 * dc;                                   // X, Xn, M panels
     n += dd + (m + 1) * dc + 2;                    // Jacobian arena
     n += (m + 1) * dc + (size_t)m * m + m + 2;     // Hessian arena
@@ -180,6 +186,7 @@ template <int D>
 __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     extern __shared__ __align__(16) double sm[];
     const int d = D > 0 ? D : p.d, c = p.c, m = p.m, dd = d * d, dc = d * c;
+    const int ld = D > 0 ? ((D & 1) ? D : D + 1) : small_ld(d), msz = ld * d;
     const int tpu = p.tpu, ul = threadIdx.x / tpu, e0 = threadIdx.x % tpu;
     int ug = blockIdx.x * p.upc + ul;                 // slab-local unit index = sys*nk + kl
     const bool live = ug < p.units;                   // tail CTA: spare slots shadow the last unit
@@ -189,14 +196,15 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     const double *G0 = p.G0 + (long long)sys * dd, *Gd = p.Gd + (long long)sys * m * dd;
 
     SmallCtx x;
-    x.d = d; x.dd = dd; x.m = m; x.level = 0; x.j = 0; x.e0 = e0; x.tpu = tpu;
+    x.d = d; x.ld = ld; x.msz = msz; x.m = m; x.level = 0; x.j = 0; x.e0 = e0; x.tpu = tpu;
     double *ptr = sm + (size_t)ul * p.unit_doubles;
-    x.fixed = ptr; ptr += QR_NUM_FIXED * dd;
-    x.E = ptr; ptr += (p.smax + 1) * dd;
-    x.W = ptr; ptr += (p.smax + 1) * dd;
-    x.dpersist = ptr; ptr += QCB_NUM_DPERSIST * m * dd;
-    x.dtemp = ptr; ptr += QCB_NUM_DTEMP * dd;
-    x.L = ptr; ptr += (m + 1) * dd;
+    x.fixed = ptr; ptr += QR_NUM_FIXED * msz;
+    x.E = ptr; ptr += (p.smax + 1) * msz;
+    x.W = ptr; ptr += (p.smax + 1) * msz;
+    x.dpersist = ptr; ptr += QCB_NUM_DPERSIST * m * msz;
+    x.dtemp = ptr; ptr += QCB_NUM_DTEMP * msz;
+    x.L = ptr; ptr += (m + 1) * msz;
+    double *Gs = ptr; ptr += m * msz;
     double *X = ptr; ptr += dc;
     double *Xn = ptr; ptr += dc;
     double *Mu = ptr; ptr += dc;
@@ -208,22 +216,27 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     int *Lidx = reinterpret_cast<int *>(cta_tail);                    // [m+1]
     double *cta_nrm = cta_tail + (m + 2) / 2 + 2;                     // [upc]
     x.Lidx = Lidx;
-    x.Gj = Gd;
+    x.Gs = Gs;
 
     const bool want_jac = p.want & 1, want_hess = (p.want & 2) && p.mu;
-    double *G = x.fixed + QR_G * dd, *A = x.fixed + QR_A * dd;
+    double *G = x.fixed + QR_G * msz, *A = x.fixed + QR_A * msz;
     const double dt = zk[p.dt_off];
 
-    // ---- load unit inputs, G = G0 + sum u_j G_j ----
+    // ---- load unit inputs; stage G_j in shared memory; G = G0 + sum u_j G_j ----
     for (int e = e0; e < dc; e += tpu) {
         X[e] = zk[p.x_off[sys] + e];
         Xn[e] = zn[p.x_off[sys] + e];
         Mu[e] = want_hess ? p.mu[((long long)sys * p.K + k) * dc + e] : 0.0;
     }
     for (int e = e0; e < dd; e += tpu) {
+        const int off = (e % d) + (e / d) * ld;
         double v = G0[e];
-        for (int j = 0; j < m; ++j) v = fma(zk[p.u_off + j], Gd[j * dd + e], v);
-        G[e] = v;
+        for (int j = 0; j < m; ++j) {
+            const double gj = Gd[j * dd + e];
+            Gs[j * msz + off] = gj;
+            v = fma(zk[p.u_off + j], gj, v);
+        }
+        G[off] = v;
     }
     if (threadIdx.x <= m) Lidx[threadIdx.x] = threadIdx.x;
     for (int e = e0; e < m * m; e += tpu) Hacc[e] = 0.0;
@@ -234,7 +247,7 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
         bool bad = false;
         for (int q = e0; q < d; q += tpu) {
             double cs = 0.0;
-            for (int r = 0; r < d; ++r) cs += fabs(dt * G[r + q * d]);
+            for (int r = 0; r < d; ++r) cs += fabs(dt * G[r + q * ld]);
             if (!isfinite(cs)) bad = true;
             mine = fmax(mine, cs);
         }
@@ -251,13 +264,13 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
         return;
     }
     const double tau = ldexp(dt, -s);
-    for (int e = e0; e < dd; e += tpu) A[e] = tau * G[e];
+    for (int e = e0; e < dd; e += tpu) { const int off = (e % d) + (e / d) * ld; A[off] = tau * G[off]; }
     __syncthreads();
 
     // ---- polynomial + squarings ----
     for (int i = 0; i < 6; ++i) sm_run_op<D>(x, c_P1[i]);
     for (int l = 0; l < s; ++l) { x.level = l; sm_run_op<D>(x, c_P2[0]); }
-    const double *E = x.E + s * dd;
+    const double *E = x.E + s * msz;
 
     // ---- defect ----
     if (live) {
@@ -265,19 +278,19 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
         for (int e = e0; e < dc; e += tpu) {
             const int r = e % d, b = e / d;
             double acc = 0.0;
-            for (int q = 0; q < d; ++q) acc = fma(E[r + q * d], X[q + b * d], acc);
+            for (int q = 0; q < d; ++q) acc = fma(E[r + q * ld], X[q + b * d], acc);
             o[e] = Xn[e] - acc;
         }
     }
     if (!want_jac && !want_hess) return;
 
-    double *Wt = x.W + s * dd;
+    double *Wt = x.W + s * msz;
     if (want_hess) {
         for (int e = e0; e < dd; e += tpu) {   // W = M X^T
             const int r = e % d, q = e / d;
             double acc = 0.0;
             for (int b = 0; b < c; ++b) acc = fma(Mu[r + b * d], X[q + b * d], acc);
-            Wt[e] = acc;
+            Wt[r + q * ld] = acc;
         }
         __syncthreads();
         for (int l = s - 1; l >= 0; --l) { x.level = l; sm_run_op<D>(x, c_P3[0]); }
@@ -286,7 +299,7 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     }
     // ---- per-direction first-order tangents ----
     for (int j = 0; j < m; ++j) {
-        x.j = j; x.Gj = Gd + (long long)j * dd; x.level = 0;
+        x.j = j; x.level = 0;
         for (int i = 0; i < 6; ++i) sm_run_op<D>(x, c_P5[i]);
     }
     // ---- second order at the polynomial level: U_j = Xdot_j^T Nbar per product node, then
@@ -294,12 +307,12 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     if (want_hess) {
         for (int o = 0; o < 4; ++o)
             for (int j = 0; j < m; ++j) {
-                x.j = j; x.Gj = Gd + (long long)j * dd; x.level = 0;
+                x.j = j; x.level = 0;
                 sm_run_op<D>(x, c_P6[o]);
-                const double *U = x.dtemp + qcb_dtemp(QR_U) * dd;
+                const double *U = x.dtemp + qcb_dtemp(QR_U) * msz;
                 for (int i = 0; i < m; ++i) {
-                    x.j = i; x.Gj = Gd + (long long)i * dd;
-                    double v = sm_dot(U, sm_resolve(x, c_P6_partner[o]), dd, e0, tpu, red);
+                    x.j = i;
+                    double v = sm_dot(U, sm_resolve(x, c_P6_partner[o]), d, ld, e0, tpu, red);
                     if (e0 == 0) Hacc[j * m + i] += v;
                 }
             }
@@ -311,9 +324,9 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
             for (int j = 0; j < m; ++j) {
                 x.j = j;
                 sm_run_op<D>(x, c_P7U[0]);
-                const double *U = x.dtemp + qcb_dtemp(QR_U) * dd;
+                const double *U = x.dtemp + qcb_dtemp(QR_U) * msz;
                 for (int i = 0; i < m; ++i) {
-                    double v = sm_dot(U, x.L + Lidx[i] * dd, dd, e0, tpu, red);
+                    double v = sm_dot(U, x.L + Lidx[i] * msz, d, ld, e0, tpu, red);
                     if (e0 == 0) Hacc[j * m + i] += v;
                 }
             }
@@ -326,40 +339,41 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
         }
     }
     // ---- final blocks ----
-    double *GE = x.fixed + QR_A2 * dd, *WE = x.fixed + QR_A3 * dd, *GW = x.fixed + QR_A4 * dd;
+    double *GE = x.fixed + QR_A2 * msz, *WE = x.fixed + QR_A3 * msz, *GW = x.fixed + QR_A4 * msz;
     for (int e = e0; e < dd; e += tpu) {
         const int r = e % d, q = e / d;
         double g1 = 0.0, g2 = 0.0, g3 = 0.0;
         for (int kk = 0; kk < d; ++kk) {
-            g1 = fma(G[r + kk * d], E[kk + q * d], g1);            // G E
+            g1 = fma(G[r + kk * ld], E[kk + q * ld], g1);            // G E
             if (want_hess) {
-                g2 = fma(Wt[r + kk * d], E[q + kk * d], g2);       // W E^T
-                g3 = fma(G[kk + r * d], Wt[kk + q * d], g3);       // G^T W
+                g2 = fma(Wt[r + kk * ld], E[q + kk * ld], g2);       // W E^T
+                g3 = fma(G[kk + r * ld], Wt[kk + q * ld], g3);       // G^T W
             }
         }
-        GE[e] = g1; WE[e] = g2; GW[e] = g3;
-        JA[e] = E[e];
+        const int off = r + q * ld;
+        GE[off] = g1; WE[off] = g2; GW[off] = g3;
+        JA[e] = E[off];
     }
     __syncthreads();
     double *JU = JA + dd, *JT = JU + m * dc;
-    for (int j = 0; j < m; ++j) sm_panel(JU + j * dc, x.L + Lidx[j] * dd, 0, X, d, c, -tau, e0, tpu);
-    sm_panel(JT, GE, 0, X, d, c, -1.0, e0, tpu);
+    for (int j = 0; j < m; ++j) sm_panel(JU + j * dc, x.L + Lidx[j] * msz, 0, X, d, ld, c, -tau, e0, tpu);
+    sm_panel(JT, GE, 0, X, d, ld, c, -1.0, e0, tpu);
     if (e0 == 0) { JT[dc] = 0.0; JT[dc + 1] = 1.0; }
     if (want_hess) {
         double *HXU = HA, *HXT = HA + m * dc, *HUU = HXT + dc, *HUT = HUU + m * m, *HTT = HUT + m;
-        for (int j = 0; j < m; ++j) sm_panel(HXU + j * dc, x.L + Lidx[j] * dd, 1, Mu, d, c, -tau, e0, tpu);
-        sm_panel(HXT, GE, 1, Mu, d, c, -1.0, e0, tpu);
+        for (int j = 0; j < m; ++j) sm_panel(HXU + j * dc, x.L + Lidx[j] * msz, 1, Mu, d, ld, c, -tau, e0, tpu);
+        sm_panel(HXT, GE, 1, Mu, d, ld, c, -1.0, e0, tpu);
         __syncthreads();                                  // Hacc complete (written by e0 == 0 lanes)
         for (int e = e0; e < m * m; e += tpu) {
             const int i = e / m, j = e % m;
             HUU[e] = -tau * tau * (Hacc[i * m + j] + Hacc[j * m + i]);
         }
         for (int j = 0; j < m; ++j) {
-            double c1 = sm_dot(WE, Gd + (long long)j * dd, dd, e0, tpu, red);
-            double c2 = sm_dot(GW, x.L + Lidx[j] * dd, dd, e0, tpu, red);
+            double c1 = sm_dot(WE, Gs + j * msz, d, ld, e0, tpu, red);
+            double c2 = sm_dot(GW, x.L + Lidx[j] * msz, d, ld, e0, tpu, red);
             if (e0 == 0) HUT[j] = -(c1 + tau * c2);
         }
-        double c3 = sm_dot(GW, GE, dd, e0, tpu, red);
+        double c3 = sm_dot(GW, GE, d, ld, e0, tpu, red);
         if (e0 == 0) { HTT[0] = -c3; HTT[1] = 0.0; }
     }
     __syncthreads();
