@@ -156,6 +156,54 @@ __device__ __noinline__ double sm_dot(const double *a, const double *b, int d, i
     return unit_sum(v, tpu, red_unit, e0);
 }
 
+// out[i] += <U, P_i> for i < m in one pass and one reduction (P_i = base + slot(i) * msz with
+// slot(i) = idx ? idx[i] : i).  `red_unit` needs 4 doubles per warp of the unit.
+__device__ __noinline__ void sm_dot_multi(const double *U, const double *base, int msz, const int *idx, int m,
+                                          int d, int ld, int e0, int tpu, double *red_unit, double *out) {
+    for (int i0 = 0; i0 < m; i0 += 4) {
+        const int nn = min(4, m - i0);
+        const double *P[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) P[q] = base + (long long)((q < nn) ? (idx ? idx[i0 + q] : i0 + q) : (idx ? idx[i0] : i0)) * msz;
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+        for (int e = e0; e < d * d; e += tpu) {
+            const int off = (e % d) + (e / d) * ld;
+            const double u = U[off];
+            a0 = fma(u, P[0][off], a0); a1 = fma(u, P[1][off], a1);
+            a2 = fma(u, P[2][off], a2); a3 = fma(u, P[3][off], a3);
+        }
+        if (tpu <= 32) {
+            for (int o = tpu >> 1; o > 0; o >>= 1) {
+                a0 += __shfl_xor_sync(0xffffffffu, a0, o); a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+                a2 += __shfl_xor_sync(0xffffffffu, a2, o); a3 += __shfl_xor_sync(0xffffffffu, a3, o);
+            }
+            if (e0 == 0) {
+                out[i0] += a0;
+                if (nn > 1) out[i0 + 1] += a1;
+                if (nn > 2) out[i0 + 2] += a2;
+                if (nn > 3) out[i0 + 3] += a3;
+            }
+        } else {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                a0 += __shfl_xor_sync(0xffffffffu, a0, o); a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+                a2 += __shfl_xor_sync(0xffffffffu, a2, o); a3 += __shfl_xor_sync(0xffffffffu, a3, o);
+            }
+            if ((e0 & 31) == 0) {
+                double *r = red_unit + (e0 >> 5) * 4;
+                r[0] = a0; r[1] = a1; r[2] = a2; r[3] = a3;
+            }
+            __syncthreads();
+            if (e0 < nn) {
+                double v = 0.0;
+                for (int w = 0; w < (tpu >> 5); ++w) v += red_unit[w * 4 + e0];
+                out[i0 + e0] += v;
+            }
+            __syncthreads();
+        }
+    }
+}
+
 // C (d x c, packed) = scale * op(A) (d x d, ld) * P (d x c, packed)
 __device__ __noinline__ void sm_panel(double *C, const double *A, int ta, const double *P, int d, int ld, int c,
                                       double scale, int e0, int tpu) {
@@ -175,7 +223,7 @@ static inline size_t small_unit_doubles(int d, int c, int m, int smax) {
     n += 3 * dc;                                   // X, Xn, M panels
     n += dd + (m + 1) * dc + 2;                    // Jacobian arena
     n += (m + 1) * dc + (size_t)m * m + m + 2;     // Hessian arena
-    n += (size_t)m * m + 16;                       // H accumulator + reduction scratch
+    n += (size_t)m * m + 64;                       // H accumulator + reduction scratch (4 per warp)
     return (n + 1) & ~(size_t)1;                   // keep every unit 16-byte aligned
 }
 static inline size_t small_smem_doubles(int d, int c, int m, int smax, int upc = 1) {
@@ -310,11 +358,8 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
                 x.j = j; x.level = 0;
                 sm_run_op<D>(x, c_P6[o]);
                 const double *U = x.dtemp + qcb_dtemp(QR_U) * msz;
-                for (int i = 0; i < m; ++i) {
-                    x.j = i;
-                    double v = sm_dot(U, sm_resolve(x, c_P6_partner[o]), d, ld, e0, tpu, red);
-                    if (e0 == 0) Hacc[j * m + i] += v;
-                }
+                x.j = 0;     // partner of direction i = partner of direction 0 + i * msz
+                sm_dot_multi(U, sm_resolve(x, c_P6_partner[o]), msz, nullptr, m, d, ld, e0, tpu, red, Hacc + j * m);
             }
     }
     // ---- squaring levels ----
@@ -325,10 +370,7 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
                 x.j = j;
                 sm_run_op<D>(x, c_P7U[0]);
                 const double *U = x.dtemp + qcb_dtemp(QR_U) * msz;
-                for (int i = 0; i < m; ++i) {
-                    double v = sm_dot(U, x.L + Lidx[i] * msz, d, ld, e0, tpu, red);
-                    if (e0 == 0) Hacc[j * m + i] += v;
-                }
+                sm_dot_multi(U, x.L, msz, Lidx, m, d, ld, e0, tpu, red, Hacc + j * m);
             }
         }
         for (int j = 0; j < m; ++j) {
