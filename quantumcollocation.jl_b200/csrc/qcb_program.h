@@ -25,6 +25,14 @@
 #define QCB_HD
 #endif
 
+/* tables are compile-time constants for the C++ / CUDA translation units (the small-d kernel
+ * instantiates one specialised routine per op), plain const data for the C port */
+#ifdef __cplusplus
+#define QCB_TABLE static constexpr
+#else
+#define QCB_TABLE static const
+#endif
+
 #define QCB_TAYLOR_DEGREE 12
 #define QCB_THETA 0.25          /* ||A/2^s||_1 <= theta before the polynomial is applied */
 #define QCB_MAX_SQUARINGS 10    /* ||dt*G(u)||_1 <= theta * 2^10 = 256; beyond: QCB_ERR_RANGE */
@@ -78,7 +86,7 @@ typedef struct {
 #define NOL_ { 0, 0 }
 
 /* Phase 1: polynomial, forward (per unit).  A = tau*G is prepared by the set-up step. */
-static const qcb_op QCB_P1[] = {
+QCB_TABLE qcb_op QCB_P1[] = {
     { QR_A2, 1, 0, -1, { T_(QR_A, QR_A, 0, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
     { QR_A3, 1, 0, -1, { T_(QR_A, QR_A2, 0, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
     { QR_A4, 1, 0, -1, { T_(QR_A2, QR_A2, 0, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
@@ -87,15 +95,15 @@ static const qcb_op QCB_P1[] = {
     { QR_E0, 1, 3, 0, { T_(QR_A4, QR_Z1, 0, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { { QR_A, 1 }, { QR_A2, 2 }, { QR_A3, 3 }, NOL_ } },
 };
 /* Phase 2: squaring, level l = 0..s-1:  E[l+1] = E[l]^2 */
-static const qcb_op QCB_P2[] = {
+QCB_TABLE qcb_op QCB_P2[] = {
     { QR_EL1, 1, 0, -1, { T_(QR_EL, QR_EL, 0, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
 };
 /* Phase 3: adjoint weight chain, level l = s-1..0:  W[l] = W[l+1] E[l]^T + E[l]^T W[l+1] */
-static const qcb_op QCB_P3[] = {
+QCB_TABLE qcb_op QCB_P3[] = {
     { QR_WL, 2, 0, -1, { T_(QR_WL1, QR_EL, 0, 1), T_(QR_EL, QR_WL1, 1, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
 };
 /* Phase 4: polynomial, reverse sweep seeded with W[0] (per unit) */
-static const qcb_op QCB_P4[] = {
+QCB_TABLE qcb_op QCB_P4[] = {
     { QR_ZB1, 1, 0, -1, { T_(QR_A4, QR_W0, 1, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
     { QR_ZB2, 1, 0, -1, { T_(QR_A4, QR_ZB1, 1, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
     { QR_AB4, 2, 1, -1, { T_(QR_W0, QR_Z1, 0, 1), T_(QR_ZB1, QR_Z2, 0, 1), NOT_, NOT_, NOT_, NOT_ }, { { QR_ZB2, 12 }, NOL_, NOL_, NOL_ } },
@@ -103,7 +111,7 @@ static const qcb_op QCB_P4[] = {
     { QR_AB2, 3, 3, -1, { T_(QR_AB4, QR_A2, 0, 1), T_(QR_A2, QR_AB4, 1, 0), T_(QR_A, QR_AB3, 1, 0), NOT_, NOT_, NOT_ }, { { QR_W0, 2 }, { QR_ZB1, 6 }, { QR_ZB2, 10 }, NOL_ } },
 };
 /* Phase 5: polynomial, forward tangent along G_j (per unit x direction) */
-static const qcb_op QCB_P5[] = {
+QCB_TABLE qcb_op QCB_P5[] = {
     { QR_DA2, 2, 0, -1, { T_(QR_GJ, QR_A, 0, 0), T_(QR_A, QR_GJ, 0, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
     { QR_DA3, 2, 0, -1, { T_(QR_GJ, QR_A2, 0, 0), T_(QR_A, QR_DA2, 0, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
     { QR_DA4, 2, 0, -1, { T_(QR_DA2, QR_A2, 0, 0), T_(QR_A2, QR_DA2, 0, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
@@ -118,20 +126,20 @@ static const qcb_op QCB_P5[] = {
  * U_j = X_dot_j^T N_bar, then C[j][i] += <U_j, Y_dot_i> for every i; H = C + C^T.  The nodes of
  * phase 1: A2 = A*A, A3 = A*A2, A4 = A2*A2, Y2 = A4*Z2, Y1 = A4*Z1 (the two that share the partner
  * dA2 are merged). */
-static const qcb_op QCB_P6[] = {
+QCB_TABLE qcb_op QCB_P6[] = {
     { QR_U, 1, 0, -1, { T_(QR_GJ, QR_AB2, 1, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
     { QR_U, 2, 0, -1, { T_(QR_GJ, QR_AB3, 1, 0), T_(QR_DA2, QR_AB4, 1, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
     { QR_U, 1, 0, -1, { T_(QR_DA4, QR_ZB1, 1, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
     { QR_U, 1, 0, -1, { T_(QR_DA4, QR_W0, 1, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
 };
 /* the register whose direction-i instance is contracted with U_j after each op of phase 6 */
-static const uint8_t QCB_P6_PARTNER[] = { QR_GJ, QR_DA2, QR_DZ2, QR_DZ1 };
+QCB_TABLE uint8_t QCB_P6_PARTNER[] = { QR_GJ, QR_DA2, QR_DZ2, QR_DZ1 };
 /* Phase 7 (per level l = 0..s-1, per direction): the squaring E[l+1] = E[l]*E[l] is a product node
  * with adjoint W[l+1]:  U_j = L_j^T W[l+1] ;  C[j][i] += <U_j, L_i> ;  L_j <- E[l] L_j + L_j E[l] */
-static const qcb_op QCB_P7U[] = {
+QCB_TABLE qcb_op QCB_P7U[] = {
     { QR_U, 1, 0, -1, { T_(QR_L, QR_WL1, 1, 0), NOT_, NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
 };
-static const qcb_op QCB_P7L[] = {
+QCB_TABLE qcb_op QCB_P7L[] = {
     { QR_LN, 2, 0, -1, { T_(QR_EL, QR_L, 0, 0), T_(QR_L, QR_EL, 0, 0), NOT_, NOT_, NOT_, NOT_ }, { NOL_, NOL_, NOL_, NOL_ } },
 };
 #undef T_
@@ -140,7 +148,7 @@ static const qcb_op QCB_P7L[] = {
 
 #define QCB_NOPS(t) ((int)(sizeof(t) / sizeof((t)[0])))
 
-static const double QCB_TAYLOR[QCB_TAYLOR_DEGREE + 1] = {
+QCB_TABLE double QCB_TAYLOR[QCB_TAYLOR_DEGREE + 1] = {
     1.0, 1.0, 1.0 / 2, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040, 1.0 / 40320,
     1.0 / 362880, 1.0 / 3628800, 1.0 / 39916800, 1.0 / 479001600 };
 

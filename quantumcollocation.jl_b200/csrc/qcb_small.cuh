@@ -10,6 +10,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <utility>
 #include "qcb_program.h"
 
 namespace qcb {
@@ -113,6 +114,78 @@ template <int D> __device__ __noinline__ void sm_run_op(const SmallCtx &x, const
         dst[off] = acc;
     }
     __syncthreads();
+}
+
+// ---- compile-time ops (D > 0): one specialised routine per table entry -- register bases are
+//      constants, the k loops unroll with immediate offsets, Taylor coefficients are immediates ----
+template <int D> struct SmDims {
+    static constexpr int ld = (D & 1) ? D : D + 1;
+    static constexpr int msz = ld * D;
+};
+template <int D, int R> __device__ __forceinline__ double *sm_resolve_s(const SmallCtx &x) {
+    constexpr int MSZ = SmDims<D>::msz;
+    if constexpr (R < QR_NUM_FIXED) return x.fixed + R * MSZ;
+    else if constexpr (R == QR_EL) return x.E + x.level * MSZ;
+    else if constexpr (R == QR_EL1) return x.E + (x.level + 1) * MSZ;
+    else if constexpr (R == QR_WL) return x.W + x.level * MSZ;
+    else if constexpr (R == QR_WL1) return x.W + (x.level + 1) * MSZ;
+    else if constexpr (R == QR_E0) return x.E;
+    else if constexpr (R == QR_W0) return x.W;
+    else if constexpr (R == QR_GJ) return const_cast<double *>(x.Gs) + x.j * MSZ;
+    else if constexpr (R == QR_L) return x.L + x.Lidx[x.j] * MSZ;
+    else if constexpr (R == QR_LN) return x.L + x.Lidx[x.m] * MSZ;
+    else if constexpr (R == QR_DA2 || R == QR_DA4 || R == QR_DZ1 || R == QR_DZ2)
+        return x.dpersist + ((R == QR_DA2 ? 0 : R == QR_DA4 ? 1 : R == QR_DZ1 ? 2 : 3) * x.m + x.j) * MSZ;
+    else return x.dtemp + (R == QR_DA3 ? 0 : 1) * MSZ;
+}
+template <int D, const qcb_op *TAB, int I, int T>
+__device__ __forceinline__ double sm_term_s(const SmallCtx &x, int r, int q) {
+    constexpr qcb_term tm = TAB[I].term[T];
+    constexpr int LD = SmDims<D>::ld;
+    const double *a = sm_resolve_s<D, tm.a>(x) + (tm.ta ? r * LD : r);
+    const double *b = sm_resolve_s<D, tm.b>(x) + (tm.tb ? q : q * LD);
+    return dot_k<D, (tm.ta ? 1 : 0), (tm.tb ? 0 : 1)>(a, b, 0.0, D, LD);
+}
+template <int D, const qcb_op *TAB, int I, int L>
+__device__ __forceinline__ double sm_lin_s(const SmallCtx &x, int off) {
+    constexpr qcb_lin ln = TAB[I].lin[L];
+    constexpr double cf = QCB_TAYLOR[ln.coef];
+    return cf * sm_resolve_s<D, ln.reg>(x)[off];
+}
+template <int D, const qcb_op *TAB, int I, int... T, int... L>
+__device__ __forceinline__ void sm_run_static_impl(const SmallCtx &x, std::integer_sequence<int, T...>,
+                                                   std::integer_sequence<int, L...>) {
+    constexpr qcb_op op = TAB[I];
+    constexpr int LD = SmDims<D>::ld;
+    double *dst = sm_resolve_s<D, op.dst>(x);
+    for (int e = x.e0; e < D * D; e += x.tpu) {
+        const int r = e % D, q = e / D, off = r + q * LD;
+        double acc = (0.0 + ... + sm_term_s<D, TAB, I, T>(x, r, q));
+        acc += (0.0 + ... + sm_lin_s<D, TAB, I, L>(x, off));
+        if constexpr (op.ident >= 0) {
+            constexpr double ci = QCB_TAYLOR[op.ident >= 0 ? op.ident : 0];
+            if (r == q) acc += ci;
+        }
+        dst[off] = acc;
+    }
+    __syncthreads();
+}
+template <int D, const qcb_op *TAB, int I> __device__ __forceinline__ void sm_run_static(const SmallCtx &x) {
+    sm_run_static_impl<D, TAB, I>(x, std::make_integer_sequence<int, TAB[I].nterm>{},
+                                  std::make_integer_sequence<int, TAB[I].nlin>{});
+}
+template <int D, const qcb_op *TAB, int... I>
+__device__ __forceinline__ void sm_run_table_impl(const SmallCtx &x, std::integer_sequence<int, I...>) {
+    (sm_run_static<D, TAB, I>(x), ...);
+}
+// run ops 0..N-1 of a table: specialised code for D > 0, the interpreter otherwise
+template <int D, const qcb_op *TAB, int N> __device__ __forceinline__ void sm_run_table(const SmallCtx &x, const qcb_op *ctab) {
+    if constexpr (D > 0) sm_run_table_impl<D, TAB>(x, std::make_integer_sequence<int, N>{});
+    else for (int i = 0; i < N; ++i) sm_run_op<0>(x, ctab[i]);
+}
+template <int D, const qcb_op *TAB, int I> __device__ __forceinline__ void sm_run_one(const SmallCtx &x, const qcb_op *ctab) {
+    if constexpr (D > 0) sm_run_static<D, TAB, I>(x);
+    else sm_run_op<0>(x, ctab[I]);
 }
 
 // Sum over the threads of a unit, result in every thread of the unit.  tpu is a power of two <= 32
@@ -316,8 +389,8 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     __syncthreads();
 
     // ---- polynomial + squarings ----
-    for (int i = 0; i < 6; ++i) sm_run_op<D>(x, c_P1[i]);
-    for (int l = 0; l < s; ++l) { x.level = l; sm_run_op<D>(x, c_P2[0]); }
+    sm_run_table<D, QCB_P1, 6>(x, c_P1);
+    for (int l = 0; l < s; ++l) { x.level = l; sm_run_one<D, QCB_P2, 0>(x, c_P2); }
     const double *E = x.E + s * msz;
 
     // ---- defect ----
@@ -341,26 +414,33 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
             Wt[r + q * ld] = acc;
         }
         __syncthreads();
-        for (int l = s - 1; l >= 0; --l) { x.level = l; sm_run_op<D>(x, c_P3[0]); }
+        for (int l = s - 1; l >= 0; --l) { x.level = l; sm_run_one<D, QCB_P3, 0>(x, c_P3); }
         x.level = 0;
-        for (int i = 0; i < 5; ++i) sm_run_op<D>(x, c_P4[i]);
+        sm_run_table<D, QCB_P4, 5>(x, c_P4);
     }
     // ---- per-direction first-order tangents ----
     for (int j = 0; j < m; ++j) {
         x.j = j; x.level = 0;
-        for (int i = 0; i < 6; ++i) sm_run_op<D>(x, c_P5[i]);
+        sm_run_table<D, QCB_P5, 6>(x, c_P5);
     }
     // ---- second order at the polynomial level: U_j = Xdot_j^T Nbar per product node, then
     //      C[j][i] += <U_j, Ydot_i> ----
     if (want_hess) {
-        for (int o = 0; o < 4; ++o)
+        auto node = [&](auto O) {
+            constexpr int o = decltype(O)::value;
             for (int j = 0; j < m; ++j) {
                 x.j = j; x.level = 0;
-                sm_run_op<D>(x, c_P6[o]);
+                sm_run_one<D, QCB_P6, o>(x, c_P6);
                 const double *U = x.dtemp + qcb_dtemp(QR_U) * msz;
                 x.j = 0;     // partner of direction i = partner of direction 0 + i * msz
-                sm_dot_multi(U, sm_resolve(x, c_P6_partner[o]), msz, nullptr, m, d, ld, e0, tpu, red, Hacc + j * m);
+                constexpr int partner = QCB_P6_PARTNER[o];
+                sm_dot_multi(U, sm_resolve(x, partner), msz, nullptr, m, d, ld, e0, tpu, red, Hacc + j * m);
             }
+        };
+        node(std::integral_constant<int, 0>{});
+        node(std::integral_constant<int, 1>{});
+        node(std::integral_constant<int, 2>{});
+        node(std::integral_constant<int, 3>{});
     }
     // ---- squaring levels ----
     for (int l = 0; l < s; ++l) {
@@ -368,14 +448,14 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
         if (want_hess) {
             for (int j = 0; j < m; ++j) {
                 x.j = j;
-                sm_run_op<D>(x, c_P7U[0]);
+                sm_run_one<D, QCB_P7U, 0>(x, c_P7U);
                 const double *U = x.dtemp + qcb_dtemp(QR_U) * msz;
                 sm_dot_multi(U, x.L, msz, Lidx, m, d, ld, e0, tpu, red, Hacc + j * m);
             }
         }
         for (int j = 0; j < m; ++j) {
             x.j = j;
-            sm_run_op<D>(x, c_P7L[0]);
+            sm_run_one<D, QCB_P7L, 0>(x, c_P7L);
             if (threadIdx.x == 0) { int old = Lidx[j]; Lidx[j] = Lidx[m]; Lidx[m] = old; }
             __syncthreads();
         }
