@@ -77,7 +77,9 @@ struct qcb_handle_s {
     int64_t JA = 0, HA = 0;                            // arena strides (doubles)
     bool custom_j = false, custom_h = false;
     unsigned long long *d_norm = nullptr;
-    int *d_bad = nullptr;
+    int *d_bad = nullptr;          // [0] flags (bit0 non-finite / out of range, bit1 chain capacity), [1] max squarings seen
+    int *h_flags = nullptr;        // pinned host mirror of d_bad[0..1]
+    int s_hint = 2;                // small-d path: chain capacity tried first (squarings of the last call)
 
     // staging for the host-buffer API
     double *dZ = nullptr, *dmu = nullptr;
@@ -552,7 +554,7 @@ struct HostOut { double *delta, *jac, *hess; bool compact; };
 // norm pre-pass over the whole slab -> uniform number of squarings (or -1)
 int slab_squarings(qcb_handle_s *h, const double *dZ) {
     CK(cudaMemsetAsync(h->d_norm, 0, sizeof(unsigned long long), h->stream));
-    CK(cudaMemsetAsync(h->d_bad, 0, sizeof(int), h->stream));
+    CK(cudaMemsetAsync(h->d_bad, 0, 2 * sizeof(int), h->stream));
     build_G_kernel<<<h->units, 256, 0, h->stream>>>(h->geom(), dZ, 0, nullptr, 0, h->d_norm, h->d_bad);
     ++h->launches;
     CK(cudaGetLastError());
@@ -807,25 +809,37 @@ void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
 // common driver: device inputs -> device outputs (+ optional streamed host outputs)
 qcb_status eval_device(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_delta, double *d_jac,
                        double *d_hess, int want, const HostOut *host) {
-    const int s = slab_squarings(h, dZ);
-    if (s < 0) {
-        h->err = "non-finite input or ||dt*G(u)||_1 beyond the supported range";
-        return QCB_ERR_RANGE;
-    }
+    const char *range_msg = "non-finite input or ||dt*G(u)||_1 beyond the supported range";
     if (h->large) {
+        const int s = slab_squarings(h, dZ);
+        if (s < 0) { h->err = range_msg; return QCB_ERR_RANGE; }
         eval_large(h, dZ, dmu, d_delta, d_jac, d_hess, want, host, s);
     } else {
-        eval_small(h, dZ, dmu, d_delta, d_jac, d_hess, want, s);
+        // No norm pre-pass on the small-d path: the kernel sizes its squaring chains for the count
+        // seen by the previous call, reports the count it needs, and is re-run once if that was
+        // not enough (rare: the count only changes when ||dt*G(u)||_1 crosses a power of two).
+        int cap = std::min(h->s_hint, QCB_MAX_SQUARINGS);
+        for (int attempt = 0;; ++attempt) {
+            CK(cudaMemsetAsync(h->d_bad, 0, 2 * sizeof(int), h->stream));
+            eval_small(h, dZ, dmu, d_delta, d_jac, d_hess, want, cap);
+            CK(cudaMemcpyAsync(h->h_flags, h->d_bad, 2 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+            CK(cudaStreamSynchronize(h->stream));
+            if (h->h_flags[0] & 1) { h->err = range_msg; return QCB_ERR_RANGE; }
+            if (!(h->h_flags[0] & 2)) break;
+            cap = h->h_flags[1];
+            if (attempt > 1 || cap > QCB_MAX_SQUARINGS) { h->err = range_msg; return QCB_ERR_RANGE; }
+        }
+        h->s_hint = std::max(h->h_flags[1], 0);
         if (host) {
-            CK(cudaEventRecord(h->ev[4], h->stream));
-            CK(cudaStreamWaitEvent(h->copy_stream, h->ev[4], 0));
             if (host->delta)
                 CK(cudaMemcpyAsync(host->delta, d_delta, (size_t)h->units * h->xdim * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)h->units * h->xdim * 8);
             if ((want & 1) && host->jac)
                 CK(cudaMemcpyAsync(host->jac, d_jac, (size_t)h->units * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)h->units * h->jnnz_unit * 8);
             if ((want & 2) && host->hess)
                 CK(cudaMemcpyAsync(host->hess, d_hess, (size_t)h->units * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)h->units * h->hnnz_unit * 8);
+            CK(cudaStreamSynchronize(h->copy_stream));
         }
+        return QCB_OK;
     }
     CK(cudaStreamSynchronize(h->stream));
     if (host) CK(cudaStreamSynchronize(h->copy_stream));
@@ -840,10 +854,7 @@ qcb_status eval_device(qcb_handle_s *h, const double *dZ, const double *dmu, dou
     }
     int bad = 0;
     CK(cudaMemcpy(&bad, h->d_bad, sizeof(int), cudaMemcpyDeviceToHost));
-    if (bad) {
-        h->err = "non-finite input or ||dt*G(u)||_1 beyond the supported range";
-        return QCB_ERR_RANGE;
-    }
+    if (bad) { h->err = range_msg; return QCB_ERR_RANGE; }
     return QCB_OK;
 }
 
@@ -988,8 +999,9 @@ qcb_status qcb_create(qcb_handle *out, const qcb_desc *desc) {
         CK(cudaMalloc(&h->d_xoff, h->S * sizeof(int)));
         CK(cudaMemcpy(h->d_xoff, h->x_off.data(), h->S * sizeof(int), cudaMemcpyHostToDevice));
         CK(cudaMalloc(&h->d_norm, sizeof(unsigned long long)));
-        CK(cudaMalloc(&h->d_bad, sizeof(int)));
-        CK(cudaMemset(h->d_bad, 0, sizeof(int)));
+        CK(cudaMalloc(&h->d_bad, 2 * sizeof(int)));
+        CK(cudaMemset(h->d_bad, 0, 2 * sizeof(int)));
+        CK(cudaMallocHost(&h->h_flags, 2 * sizeof(int)));
         build_native_codes(h, true, true);
     } catch (const CudaFail &f) {
         qcb_status st = fail_cuda(nullptr, f);
@@ -1007,6 +1019,7 @@ void qcb_destroy(qcb_handle h) {
     void *ptrs[] = {h->dG0, h->dGd, h->d_xoff, h->d_jcode, h->d_hcode, h->d_norm, h->d_bad, h->dZ, h->dmu, h->d_delta, h->d_jac, h->d_hess};
     for (void *p : ptrs)
         if (p) cudaFree(p);
+    if (h->h_flags) cudaFreeHost(h->h_flags);
     for (auto &e : h->ev)
         if (e) cudaEventDestroy(e);
     for (auto &e : h->chunk_events) cudaEventDestroy(e);

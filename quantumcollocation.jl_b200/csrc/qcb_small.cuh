@@ -381,9 +381,15 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     for (int u = 0; u < p.upc; ++u) nrm = fmax(nrm, cta_nrm[u]);
     const int s = qcb_squarings(nrm);
     if (s < 0 || s > p.smax) {      // uniform across the CTA
-        if (threadIdx.x == 0) atomicExch(p.bad_flag, 1);
+        // bad_flag[0]: bit0 = non-finite / out of range, bit1 = the chains of this launch are too
+        // short; bad_flag[1] = squarings needed (the host re-launches with that capacity)
+        if (threadIdx.x == 0) {
+            atomicOr(p.bad_flag, s < 0 ? 1 : 2);
+            if (s >= 0) atomicMax(p.bad_flag + 1, s);
+        }
         return;
     }
+    if (threadIdx.x == 0 && s > 0) atomicMax(p.bad_flag + 1, s);
     const double tau = ldexp(dt, -s);
     for (int e = e0; e < dd; e += tpu) { const int off = (e % d) + (e / d) * ld; A[off] = tau * G[off]; }
     __syncthreads();
