@@ -740,12 +740,24 @@ assemble_kernel(const double *arena, long long arena_stride, const uint32_t *cod
     const uint32_t *cd = code + (long long)sys * nnz;
     const double *ar = arena + (long long)unit * arena_stride;
     double *o = out + (long long)(out_u0 + unit) * nnz;   // out_u0: unit index of `out`'s first row
-    const long long per = (nnz + chunks_per_unit - 1) / chunks_per_unit;
-    const long long e1 = (chunk + 1) * per < nnz ? (chunk + 1) * per : nnz;
-    for (long long e = chunk * per + threadIdx.x; e < e1; e += blockDim.x) {
-        uint32_t cc = cd[e];
-        double v = ar[cc & 0x7fffffffu];
-        o[e] = (cc >> 31) ? -v : v;
+    long long per = (nnz + chunks_per_unit - 1) / chunks_per_unit;
+    per += per & 1;                                   // even chunk starts keep 16-byte alignment
+    const long long b0 = chunk * per, e1 = (b0 + per < nnz) ? b0 + per : nnz;
+    if ((nnz & 1) == 0 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+        // two entries per thread, one 16-byte store (rows of `out` are then all 16-byte aligned)
+        for (long long e = b0 + 2 * threadIdx.x; e < e1; e += 2 * blockDim.x) {
+            const uint2 cc = *reinterpret_cast<const uint2 *>(cd + e);
+            double v0 = ar[cc.x & 0x7fffffffu], v1 = ar[cc.y & 0x7fffffffu];
+            if (cc.x >> 31) v0 = -v0;
+            if (cc.y >> 31) v1 = -v1;
+            *reinterpret_cast<double2 *>(o + e) = make_double2(v0, v1);
+        }
+    } else {
+        for (long long e = b0 + threadIdx.x; e < e1; e += blockDim.x) {
+            uint32_t cc = cd[e];
+            double v = ar[cc & 0x7fffffffu];
+            o[e] = (cc >> 31) ? -v : v;
+        }
     }
 }
 
