@@ -262,6 +262,23 @@ def main():
     ev.profile(False)
     value = units_total / (ms_dev * 1e-3)
 
+    # ---- evaluator time per Ipopt iteration with the callback mix the reference's logs show
+    #      (55 eval_g : 51 eval_jac_g : 50 eval_h per 50 iterations, multilevel_transmon.jl:147-153) ----
+    def timed(fn, reps=2):
+        fn()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(st)
+        for _ in range(reps):
+            fn()
+        b.record(st); b.synchronize()
+        return max_over_ranks(a.elapsed_time(b)) / reps
+    t_g = timed(lambda: ev.eval_all_device(dZ, None, d_delta, None, None))
+    t_j = timed(lambda: ev.eval_all_device(dZ, None, d_delta, d_jac, None))
+    t_h = timed(lambda: ev.eval_all_device(dZ, dmu, d_delta, None, d_hess))
+    callback_mix = {"eval_g_ms": t_g, "eval_jac_g_ms": t_j, "eval_h_ms": t_h,
+                    "evaluator_ms_per_ipopt_iteration": (55 * t_g + 51 * t_j + 50 * t_h) / 50.0,
+                    "mix": "55 g : 51 jac : 50 hess per 50 iterations (docs/literate/examples/multilevel_transmon.jl:147-153)"}
+
     # ---------------- end-to-end through the host-buffer API (`e2e`) ----------------
     e2e = None
     if not args.no_e2e:
@@ -380,12 +397,20 @@ def main():
         if prof["launches"] > 0 and L.d >= 25:
             gemm_ms = prof["ms"] / prof["launches"]
             achieved = prof["flops"] / (prof["ms"] * 1e-3) / 1e12
+            traffic, traffic_src = None, None
+            try:    # DRAM bytes per tensor flop of this kernel from the committed ncu --set full capture
+                tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic_bgemm_iso.json")))
+                traffic = tj["dram_bytes_per_flop_per_drive_launches"] * prof["flops"] / prof["launches"]
+                traffic_src = "profiles/r01_traffic_bgemm_iso.json: (dram__bytes_read.sum + dram__bytes_write.sum) per tensor flop x flops of the average launch"
+            except Exception:
+                pass
             roofline = {
-                "bound": "tensor", "kernel": "bgemm_kernel (batched FP64 DMMA GEMM, mma.sync m16n8k4 -> SASS DMMA.8x8x4)",
+                "bound": "tensor", "kernel": "bgemm_iso_kernel / bgemm_kernel (batched FP64 DMMA GEMM, mma.sync m16n8k4 -> SASS DMMA.8x8x4)",
                 "achieved": achieved, "peak": dgemm_tflops, "unit": "TFLOP/s", "frac": achieved / dgemm_tflops,
                 "peak_source": "cuBLAS DGEMM 8192^3 timed live in this run (MEASURED_PEAKS.json has no FP64 entry; "
                                "raw DMMA issue peak measured 37.1 TFLOP/s, scratch/dmma_probe.cu)",
-                "traffic": None,
+                "traffic": traffic, "traffic_source": traffic_src,
+                "algorithmic_bytes_per_launch": 8.0 * (prof["flops"] / prof["launches"]) / (2.0 * L.d) * 2.5,
                 "launches_per_step": prof["launches"] / args.steps, "avg_launch_ms": gemm_ms,
                 "kernel_share_of_step": prof["ms"] / args.steps / ms_dev if world == 1 else None,
                 "flops_per_unit_executed": prof["flops"] / args.steps / per_rank_units,
@@ -410,6 +435,7 @@ def main():
                        "l2": "inputs+outputs per step exceed L2 (no flush needed)" if flush is None
                              else "L2 flushed between timed steps (512 MB read-modify-write)"},
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "callback_mix": callback_mix,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
