@@ -190,6 +190,46 @@ qcb_status qcb_fidelity_eval(qcb_fidelity f, const double *x, double *F, double 
 qcb_status qcb_fidelity_eval_batch_device_noalloc(qcb_fidelity f, const double *d_X, int64_t count,
                                                   double *d_F, double *d_grad);
 
+/* ---- auxiliary knot-point terms ------------------------------------------
+ * The cheap terms every problem template adds around the bilinear integrator:
+ *   derivative integrators  delta_k = x_{k+1} - x_k - dt_k * dx_k   (DirectTrajOpt.DerivativeIntegrator as
+ *       used at src/problem_templates/smooth_pulse_problem.jl:150-152; "du[k] = (u[k+1] - u[k]) / dt",
+ *       spline_pulse_problem.jl:176), 4 Jacobian entries and 1 Hessian entry per row;
+ *   leakage objective  sum_t Q_t * sum_{i in idx} x_t[i]^2 / |idx|   (src/quantum_objectives.jl:291-307);
+ *   leakage constraint x_t[i]^2 - value <= 0                          (src/quantum_constraints.jl:156-172).
+ * Orders: derivative rows [k][integrator][component]; Jacobian values per row in the order
+ * (x_k, dx_k, dt_k, x_{k+1}); leakage arrays [t][i] over all N knots. */
+typedef struct qcb_aux_s *qcb_aux;
+typedef struct {
+    int32_t struct_bytes;       /* sizeof(qcb_aux_desc) */
+    int32_t N, z_dim, dt_off, device;
+    int32_t n_deriv;            /* number of derivative integrators */
+    int32_t leak_x_off;         /* 0-based offset of the state the leakage indices refer to */
+    int32_t n_leak;             /* number of leakage indices (0: none) */
+    const int32_t *deriv_x_off;  /* [n_deriv] offset of x  (e.g. u,  du)  */
+    const int32_t *deriv_dx_off; /* [n_deriv] offset of dx (e.g. du, ddu) */
+    const int32_t *deriv_dim;    /* [n_deriv] */
+    const int32_t *leak_idx;     /* [n_leak] 0-based indices inside the state component */
+} qcb_aux_desc;
+qcb_status qcb_aux_create(qcb_aux *out, const qcb_aux_desc *desc);
+void qcb_aux_destroy(qcb_aux a);
+int64_t qcb_aux_derivative_dim(qcb_aux a);      /* (N-1) * sum of dims */
+int64_t qcb_aux_leakage_dim(qcb_aux a);         /* N * n_leak */
+/* 1-based COO structure of the derivative rows: 4 Jacobian entries per row, 1 Hessian entry per row
+ * (upper triangle).  Any pointer pair may be NULL. */
+qcb_status qcb_aux_derivative_structure(qcb_aux a, int64_t row_base, int64_t *jac_rows, int64_t *jac_cols,
+                                        int64_t *hess_rows, int64_t *hess_cols);
+/* Host buffers; outputs may be NULL.  mu: multipliers of the derivative rows. */
+qcb_status qcb_aux_derivative_eval(qcb_aux a, const double *Z, const double *mu, double *delta,
+                                   double *jac_vals, double *hess_vals);
+/* Qs: [N] knot weights (NULL = 1).  objective: scalar; grad_vals / con_vals / con_jac_vals /
+ * con_hess_vals: [N][n_leak] (gradient entries dJ/dx_t[idx_i]; constraint values; their derivatives
+ * 2 x; Hessian-of-Lagrangian diagonal 2 mu).  The objective's own Hessian is the constant diagonal
+ * 2 Q_t / n_leak. */
+qcb_status qcb_aux_leakage_eval(qcb_aux a, const double *Z, const double *Qs, double value, const double *mu,
+                                double *objective, double *grad_vals, double *con_vals, double *con_jac_vals,
+                                double *con_hess_vals);
+
 #ifdef __cplusplus
 }
 #endif

@@ -444,3 +444,36 @@ def fd_check_unit(G0, Gd, X, Xn, M, u, dt, h=1e-6):
     errs["H_dtdt"] = abs(Htt - ev["H_dtdt"])
     # d/dX of (mu . J_u[j]) = H_xu[j]
     return errs
+
+
+# --------------------------------------------------------------------------- #
+# Auxiliary knot-point terms
+# --------------------------------------------------------------------------- #
+
+
+def derivative_integrator(Z, N, z_dim, dt_off, pairs, mu=None):
+    """delta_k = x_{k+1} - x_k - dt_k dx_k for every (x_off, dx_off, dim) pair
+    (src/problem_templates/smooth_pulse_problem.jl:150-152, spline_pulse_problem.jl:176).
+    Returns delta [K, rows], jac [K, rows, 4] in the order (x_k, dx_k, dt_k, x_{k+1}), hess [K, rows]."""
+    Zm = np.asarray(Z).reshape(N, z_dim)
+    rx = np.concatenate([np.arange(p[0], p[0] + p[2]) for p in pairs])
+    rdx = np.concatenate([np.arange(p[1], p[1] + p[2]) for p in pairs])
+    dt = Zm[:-1, dt_off][:, None]
+    delta = Zm[1:, rx] - Zm[:-1, rx] - dt * Zm[:-1, rdx]
+    jac = np.stack([-np.ones_like(delta), -dt * np.ones_like(delta), -Zm[:-1, rdx], np.ones_like(delta)], axis=-1)
+    hess = None if mu is None else -np.asarray(mu).reshape(delta.shape)
+    return delta, jac, hess
+
+
+def leakage(Z, N, z_dim, x_off, idx, Qs=None, value=0.0, mu=None):
+    """Objective sum_t Q_t sum(abs2, x_t[idx]) / len(idx) (src/quantum_objectives.jl:298) and constraint
+    abs2.(x_t[idx]) .- value (src/quantum_constraints.jl:163) with their derivatives."""
+    Zm = np.asarray(Z).reshape(N, z_dim)
+    v = Zm[:, x_off + np.asarray(idx)]
+    Q = np.ones(N) if Qs is None else np.asarray(Qs)
+    obj = float(np.sum(Q * np.sum(v * v, axis=1) / len(idx)))
+    grad = 2 * Q[:, None] * v / len(idx)
+    con = v * v - value
+    cjac = 2 * v
+    chess = None if mu is None else 2 * np.asarray(mu).reshape(v.shape)
+    return obj, grad, con, cjac, chess

@@ -24,6 +24,12 @@ class QcbDesc(ctypes.Structure):
         ("x_off", c_ip), ("G_drift", c_dp), ("G_drives", c_dp)]
 
 
+class QcbAuxDesc(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in (
+        "struct_bytes", "N", "z_dim", "dt_off", "device", "n_deriv", "leak_x_off", "n_leak")] + [
+        ("deriv_x_off", c_ip), ("deriv_dx_off", c_ip), ("deriv_dim", c_ip), ("leak_idx", c_ip)]
+
+
 STATUS = {0: "QCB_OK", 1: "QCB_ERR_ARG", 2: "QCB_ERR_CUDA", 3: "QCB_ERR_RANGE", 4: "QCB_ERR_STRUCTURE", 5: "QCB_ERR_NOMEM"}
 
 # every symbol include/qcb200.h declares: name -> (restype, argtypes)
@@ -56,6 +62,13 @@ SYMBOLS = {
     "qcb_fidelity_destroy": (None, [c_vp]),
     "qcb_fidelity_x_dim": (ctypes.c_int64, [c_vp]),
     "qcb_fidelity_eval": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "qcb_aux_create": (ctypes.c_int, [ctypes.POINTER(c_vp), ctypes.POINTER(QcbAuxDesc)]),
+    "qcb_aux_destroy": (None, [c_vp]),
+    "qcb_aux_derivative_dim": (ctypes.c_int64, [c_vp]),
+    "qcb_aux_leakage_dim": (ctypes.c_int64, [c_vp]),
+    "qcb_aux_derivative_structure": (ctypes.c_int, [c_vp, ctypes.c_int64, c_lp, c_lp, c_lp, c_lp]),
+    "qcb_aux_derivative_eval": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "qcb_aux_leakage_eval": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_double, c_vp, c_dp, c_vp, c_vp, c_vp, c_vp]),
     "qcb_fidelity_eval_batch_device_noalloc": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int64, c_vp, c_vp]),
 }
 

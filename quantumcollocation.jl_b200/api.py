@@ -226,3 +226,71 @@ class Fidelity:
             self.close()
         except Exception:
             pass
+
+
+class Aux:
+    """Derivative integrators and leakage terms on the GPU (include/qcb200.h, qcb_aux_*)."""
+
+    def __init__(self, N: int, z_dim: int, dt_off: int, derivatives=(), leak_x_off: int = 0, leak_idx=(), device: int = 0):
+        self.lib = _lib.load()
+        self.N, self.z_dim = N, z_dim
+        self._dx = np.asarray([d[0] for d in derivatives], dtype=np.int32)
+        self._ddx = np.asarray([d[1] for d in derivatives], dtype=np.int32)
+        self._dim = np.asarray([d[2] for d in derivatives], dtype=np.int32)
+        self._leak = np.asarray(leak_idx, dtype=np.int32)
+        p = lambda arr: arr.ctypes.data_as(_lib.c_ip) if len(arr) else None
+        desc = _lib.QcbAuxDesc(struct_bytes=ctypes.sizeof(_lib.QcbAuxDesc), N=N, z_dim=z_dim, dt_off=dt_off, device=device,
+                               n_deriv=len(self._dim), leak_x_off=leak_x_off, n_leak=len(self._leak),
+                               deriv_x_off=p(self._dx), deriv_dx_off=p(self._ddx), deriv_dim=p(self._dim), leak_idx=p(self._leak))
+        h = ctypes.c_void_p()
+        st = self.lib.qcb_aux_create(ctypes.byref(h), ctypes.byref(desc))
+        if st != 0:
+            raise _lib.QcbError(st, self.lib.qcb_last_error(None).decode())
+        self.h = h
+        self.derivative_dim = self.lib.qcb_aux_derivative_dim(h)
+        self.leakage_dim = self.lib.qcb_aux_leakage_dim(h)
+
+    def derivative_structure(self, row_base=0):
+        n = self.derivative_dim
+        jr, jc = np.empty(4 * n, dtype=np.int64), np.empty(4 * n, dtype=np.int64)
+        hr, hc = np.empty(n, dtype=np.int64), np.empty(n, dtype=np.int64)
+        P = lambda x: x.ctypes.data_as(_lib.c_lp)
+        st = self.lib.qcb_aux_derivative_structure(self.h, row_base, P(jr), P(jc), P(hr), P(hc))
+        assert st == 0
+        return (jr, jc), (hr, hc)
+
+    def derivative_eval(self, Z, mu=None):
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        n = self.derivative_dim
+        delta, jac = np.empty(n), np.empty(4 * n)
+        hess = np.empty(n) if mu is not None else None
+        mu = None if mu is None else np.ascontiguousarray(mu, dtype=np.float64)
+        st = self.lib.qcb_aux_derivative_eval(self.h, _ptr(Z), _ptr(mu), _ptr(delta), _ptr(jac), _ptr(hess))
+        if st != 0:
+            raise _lib.QcbError(st, "derivative integrator evaluation failed")
+        return delta, jac, hess
+
+    def leakage_eval(self, Z, Qs=None, value=0.0, mu=None):
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        n = self.leakage_dim
+        obj = ctypes.c_double(0.0)
+        grad, con, cjac = np.empty(n), np.empty(n), np.empty(n)
+        chess = np.empty(n) if mu is not None else None
+        Qs = None if Qs is None else np.ascontiguousarray(Qs, dtype=np.float64)
+        mu = None if mu is None else np.ascontiguousarray(mu, dtype=np.float64)
+        st = self.lib.qcb_aux_leakage_eval(self.h, _ptr(Z), _ptr(Qs), float(value), _ptr(mu), ctypes.byref(obj),
+                                           _ptr(grad), _ptr(con), _ptr(cjac), _ptr(chess))
+        if st != 0:
+            raise _lib.QcbError(st, "leakage evaluation failed")
+        return obj.value, grad, con, cjac, chess
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.qcb_aux_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

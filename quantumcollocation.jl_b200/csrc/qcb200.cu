@@ -1254,6 +1254,7 @@ void qcb_host_free(void *ptr) { if (ptr) cudaFreeHost(ptr); }
 }  // extern "C"
 
 #include "qcb_fidelity.cuh"
+#include "qcb_aux.cuh"
 
 // =========================================================================================
 // Allocation-free batched fidelity (declared in include/qcb200.h next to qcb_fidelity_eval)

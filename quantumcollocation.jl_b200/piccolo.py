@@ -20,7 +20,7 @@ from typing import Dict, List, Optional, Sequence
 
 import numpy as np
 
-from .api import Evaluator, Fidelity
+from .api import Aux, Evaluator, Fidelity
 from .isomorphisms import G_of_H, ket_to_iso, operator_to_iso_vec
 from .layout import JAC_BLOCK_DIAG, JAC_DENSE_X, KnotLayout
 
@@ -351,6 +351,64 @@ def FinalCoherentKetFidelityConstraint(psi_goals, names, final_fidelity, traj, d
     if len(psi_goals) != len(names):
         raise AssertionError("Number of names must match number of goals")
     return FinalFidelityConstraint(Fidelity(Fidelity.COHERENT_KET, np.array(psi_goals), device=device), names, final_fidelity, traj)
+
+
+# --------------------------------------------------------------------------------------- #
+# Auxiliary terms of the templates
+# --------------------------------------------------------------------------------------- #
+class DerivativeIntegrator:
+    """``DerivativeIntegrator(x_name, dx_name, traj)``: x_{k+1} - x_k - dt_k dx_k = 0
+    (src/problem_templates/smooth_pulse_problem.jl:150-152; spline_pulse_problem.jl:176)."""
+
+    def __init__(self, x_name: str, dx_name: str, traj: NamedTrajectory, device: int = 0):
+        xi, dxi = traj.components[x_name], traj.components[dx_name]
+        if len(xi) != len(dxi):
+            raise ValueError("x and dx must have the same dimension")
+        self.aux = Aux(traj.N, traj.dim, int(traj.components[traj.timestep][0]),
+                       derivatives=[(int(xi[0]), int(dxi[0]), len(xi))], device=device)
+        self.dim = self.aux.derivative_dim
+
+    def evaluate(self, delta: np.ndarray, traj: NamedTrajectory) -> np.ndarray:
+        if delta.shape != (self.dim,):
+            raise ValueError(f"delta has shape {delta.shape}, expected ({self.dim},)")
+        delta[:] = self.aux.derivative_eval(traj.datavec)[0]
+        return delta
+
+
+class LeakageObjective:
+    """``LeakageObjective(indices, name, traj; times, Qs)`` (src/quantum_objectives.jl:291-307):
+    sum over the knots of Q_t * sum(abs2, x_t[indices]) / length(indices).  indices are 0-based here."""
+
+    def __init__(self, indices, name: str, traj: NamedTrajectory, Qs=None, device: int = 0):
+        self.aux = Aux(traj.N, traj.dim, int(traj.components[traj.timestep][0]),
+                       leak_x_off=int(traj.components[name][0]), leak_idx=list(indices), device=device)
+        self.Qs = np.ones(traj.N) if Qs is None else np.asarray(Qs, dtype=float)
+        self.cols = (np.arange(traj.N)[:, None] * traj.dim + traj.components[name][0] + np.asarray(indices)[None, :]).reshape(-1)
+
+    def __call__(self, traj):
+        return self.aux.leakage_eval(traj.datavec, self.Qs)[0]
+
+    def gradient(self, grad: np.ndarray, traj) -> np.ndarray:
+        grad[:] = 0.0
+        np.add.at(grad, self.cols, self.aux.leakage_eval(traj.datavec, self.Qs)[1])
+        return grad
+
+
+class LeakageConstraint:
+    """``LeakageConstraint(value, indices, name, traj)`` (src/quantum_constraints.jl:156-172):
+    abs2.(x_t[indices]) .- value <= 0 at every knot."""
+
+    def __init__(self, value: float, indices, name: str, traj: NamedTrajectory, device: int = 0):
+        self.value = float(value)
+        self.aux = Aux(traj.N, traj.dim, int(traj.components[traj.timestep][0]),
+                       leak_x_off=int(traj.components[name][0]), leak_idx=list(indices), device=device)
+        self.equality = False
+
+    def values(self, traj):
+        return self.aux.leakage_eval(traj.datavec, None, self.value)[2]
+
+    def jacobian_values(self, traj):
+        return self.aux.leakage_eval(traj.datavec, None, self.value)[3]
 
 
 # aliases for the old (docs / BASELINE.json) names, SURVEY.md Appendix A

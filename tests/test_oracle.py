@@ -212,3 +212,27 @@ def test_port_coo_delivery_matches_arena_route(built_libs):
         a = P.evaluate(OL, w.G_drift, w.G_drives, w.Z, w.mu)
         b = P.evaluate_coo(OL, w.G_drift, w.G_drives, w.Z, w.mu)
         assert all(np.array_equal(x, y) for x, y in zip(a, b))
+
+
+def test_aux_oracle_definitions():
+    """Derivative integrator and leakage restatements: definitions from the reference tree
+    (spline_pulse_problem.jl:176 'du[k] = (u[k+1] - u[k]) / dt'; quantum_objectives.jl:298;
+    quantum_constraints.jl:163) and finite-difference consistency."""
+    rng = np.random.default_rng(0)
+    N, zd, dt_off = 6, 9, 2
+    Z = rng.normal(size=N * zd)
+    pairs = [(3, 5, 2), (5, 7, 2)]
+    mu = rng.normal(size=(N - 1) * 4)
+    d0, j0, h0 = O.derivative_integrator(Z, N, zd, dt_off, pairs, mu)
+    Zm = Z.reshape(N, zd)
+    k, r = 2, 1
+    assert abs(d0[k, r] - (Zm[k + 1, 4] - Zm[k, 4] - Zm[k, dt_off] * Zm[k, 6])) < 1e-15
+    lag = lambda z: float(np.sum(mu * O.derivative_integrator(z, N, zd, dt_off, pairs)[0].reshape(-1)))
+    h = 1e-5
+    ei = np.zeros(N * zd); ei[k * zd + 6] = h          # dx component
+    ej = np.zeros(N * zd); ej[k * zd + dt_off] = h     # dt
+    fd = (lag(Z + ei + ej) - lag(Z + ei - ej) - lag(Z - ei + ej) + lag(Z - ei - ej)) / (4 * h * h)
+    assert abs(fd - h0[k, r]) < 1e-6
+    obj, grad, con, cjac, chess = O.leakage(Z, N, zd, 3, [0, 2, 3], Qs=np.full(N, 2.0), value=0.1, mu=np.ones(N * 3))
+    assert abs(obj - 2.0 * np.sum(Zm[:, [3, 5, 6]] ** 2) / 3) < 1e-13
+    assert np.allclose(con, Zm[:, [3, 5, 6]] ** 2 - 0.1) and np.allclose(cjac, 2 * Zm[:, [3, 5, 6]])
