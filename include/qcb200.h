@@ -123,6 +123,19 @@ qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu,
 qcb_status qcb_eval_all_device(qcb_handle h, const double *dZ, const double *dmu,
                                double *d_delta, double *d_jac_vals, double *d_hess_vals);
 
+/* Peer delivery for the multi-GPU time-slab partition (no counterpart in the
+ * single-process reference).  The rank that hosts Ipopt allocates the full value buffers with
+ * qcb_device_alloc and exports them (64-byte CUDA IPC handles, to be sent to the other ranks by any
+ * means); every other rank maps them with qcb_ipc_open and passes `mapped + slab offset` as the
+ * output pointers of qcb_eval_all_device: its kernels then store the slab straight into the host
+ * rank's HBM over NVLink while they compute -- the gather is fused into the producing kernels. */
+qcb_status qcb_device_alloc(int32_t device, void **ptr, size_t bytes);
+void qcb_device_free(int32_t device, void *ptr);
+qcb_status qcb_ipc_export(int32_t device, void *ptr, unsigned char handle[64]);
+qcb_status qcb_ipc_open(int32_t device, const unsigned char handle[64], void **ptr);
+void qcb_ipc_close(int32_t device, void *ptr);
+qcb_status qcb_device_to_host(int32_t device, void *dst_host, const void *src_device, size_t bytes);
+
 /* Pinned host memory for callers that want full PCIe bandwidth on the host-buffer calls. */
 qcb_status qcb_host_alloc(void **ptr, size_t bytes);
 void qcb_host_free(void *ptr);

@@ -49,6 +49,12 @@ SYMBOLS = {
     "qcb_eval_hessian": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp]),
     "qcb_eval_all": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "qcb_eval_all_device": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "qcb_device_alloc": (ctypes.c_int, [ctypes.c_int32, ctypes.POINTER(c_vp), ctypes.c_size_t]),
+    "qcb_device_free": (None, [ctypes.c_int32, c_vp]),
+    "qcb_ipc_export": (ctypes.c_int, [ctypes.c_int32, c_vp, ctypes.c_char_p]),
+    "qcb_ipc_open": (ctypes.c_int, [ctypes.c_int32, ctypes.c_char_p, ctypes.POINTER(c_vp)]),
+    "qcb_ipc_close": (None, [ctypes.c_int32, c_vp]),
+    "qcb_device_to_host": (ctypes.c_int, [ctypes.c_int32, c_vp, c_vp, ctypes.c_size_t]),
     "qcb_host_alloc": (ctypes.c_int, [ctypes.POINTER(c_vp), ctypes.c_size_t]),
     "qcb_host_free": (None, [c_vp]),
     "qcb_kernel_launches": (ctypes.c_int64, [c_vp]),

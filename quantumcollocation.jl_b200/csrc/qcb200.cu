@@ -1344,3 +1344,46 @@ extern "C" qcb_status qcb_fidelity_eval_batch_device_noalloc(qcb_fidelity f, con
     }
     return QCB_OK;
 }
+
+// =========================================================================================
+// Device memory + CUDA IPC helpers for the multi-GPU time-slab driver
+// =========================================================================================
+extern "C" {
+
+qcb_status qcb_device_alloc(int32_t device, void **ptr, size_t bytes) {
+    if (!ptr) return QCB_ERR_ARG;
+    *ptr = nullptr;
+    if (cudaSetDevice(device) != cudaSuccess || cudaMalloc(ptr, bytes) != cudaSuccess) { cudaGetLastError(); return QCB_ERR_NOMEM; }
+    return QCB_OK;
+}
+void qcb_device_free(int32_t device, void *ptr) {
+    if (ptr && cudaSetDevice(device) == cudaSuccess) cudaFree(ptr);
+}
+qcb_status qcb_ipc_export(int32_t device, void *ptr, unsigned char handle[64]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+    if (!ptr || !handle) return QCB_ERR_ARG;
+    cudaIpcMemHandle_t hdl;
+    if (cudaSetDevice(device) != cudaSuccess || cudaIpcGetMemHandle(&hdl, ptr) != cudaSuccess) { cudaGetLastError(); return QCB_ERR_CUDA; }
+    memcpy(handle, &hdl, 64);
+    return QCB_OK;
+}
+qcb_status qcb_ipc_open(int32_t device, const unsigned char handle[64], void **ptr) {
+    if (!ptr || !handle) return QCB_ERR_ARG;
+    cudaIpcMemHandle_t hdl;
+    memcpy(&hdl, handle, 64);
+    if (cudaSetDevice(device) != cudaSuccess ||
+        cudaIpcOpenMemHandle(ptr, hdl, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); *ptr = nullptr; return QCB_ERR_CUDA; }
+    return QCB_OK;
+}
+void qcb_ipc_close(int32_t device, void *ptr) {
+    if (ptr && cudaSetDevice(device) == cudaSuccess) cudaIpcCloseMemHandle(ptr);
+}
+qcb_status qcb_device_to_host(int32_t device, void *dst_host, const void *src_device, size_t bytes) {
+    if (cudaSetDevice(device) != cudaSuccess || cudaMemcpy(dst_host, src_device, bytes, cudaMemcpyDeviceToHost) != cudaSuccess) {
+        cudaGetLastError();
+        return QCB_ERR_CUDA;
+    }
+    return QCB_OK;
+}
+
+}  // extern "C"

@@ -94,3 +94,75 @@ def gpu_compute(evaluator):
         return d, j, h
 
     return compute
+
+
+class PeerDelivery:
+    """Fused gather: every rank's kernels store their slab of the value vectors directly into buffers
+    that live in the root GPU's HBM, mapped into each process with CUDA IPC (NVLink peer stores);
+    no collective follows the evaluation -- a barrier is all that is left.
+
+    Only layouts with S == 1 (a slab is one contiguous range of every output) are supported.
+    """
+
+    def __init__(self, evaluator, layout, device_index: int, root: int = 0, group=None):
+        import ctypes
+        import torch
+        import torch.distributed as dist
+        from . import _lib
+        if layout.S != 1:
+            raise ValueError("peer delivery needs S == 1")
+        self.lib, self.dist, self.group = _lib.load(), dist, group
+        self.ev, self.L, self.dev, self.root = evaluator, layout, device_index, root
+        self.rank = dist.get_rank(group)
+        L = layout
+        self.sizes = (L.K * L.x_dim, L.K * L.jac_nnz_unit, L.K * L.hess_nnz_unit)
+        handles = torch.zeros(3, 64, dtype=torch.uint8)
+        self.base = []
+        if self.rank == root:
+            for i, n in enumerate(self.sizes):
+                p = ctypes.c_void_p()
+                st = self.lib.qcb_device_alloc(device_index, ctypes.byref(p), n * 8)
+                if st != 0:
+                    raise MemoryError("qcb_device_alloc failed")
+                buf = ctypes.create_string_buffer(64)
+                assert self.lib.qcb_ipc_export(device_index, p, buf) == 0
+                handles[i] = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8)
+                self.base.append(p.value)
+        obj = [handles.numpy().tobytes() if self.rank == root else None]
+        dist.broadcast_object_list(obj, src=root, group=group)
+        if self.rank != root:
+            raw = obj[0]
+            for i in range(3):
+                p = ctypes.c_void_p()
+                st = self.lib.qcb_ipc_open(device_index, raw[64 * i:64 * (i + 1)], ctypes.byref(p))
+                if st != 0:
+                    raise RuntimeError("qcb_ipc_open failed (no peer access between the GPUs?)")
+                self.base.append(p.value)
+        k0 = evaluator.k_begin
+        self.out = (self.base[0] + 8 * k0 * L.x_dim, self.base[1] + 8 * k0 * L.jac_nnz_unit,
+                    self.base[2] + 8 * k0 * L.hess_nnz_unit)
+
+    def evaluate(self, dZ, dmu):
+        """Evaluate this rank's slab with the outputs landing in the root's buffers; returns after
+        every rank is done (barrier)."""
+        self.ev.eval_all_device(dZ, dmu, self.out[0], self.out[1], self.out[2])
+        self.dist.barrier(group=self.group)
+
+    def fetch(self):
+        """Root only: copy the gathered vectors to host numpy arrays (verification)."""
+        import numpy as np
+        assert self.rank == self.root
+        outs = []
+        for p, n in zip(self.base, self.sizes):
+            a = np.empty(n)
+            assert self.lib.qcb_device_to_host(self.dev, a.ctypes.data, p, n * 8) == 0
+            outs.append(a)
+        return outs
+
+    def close(self):
+        for p in self.base:
+            if self.rank == self.root:
+                self.lib.qcb_device_free(self.dev, p)
+            else:
+                self.lib.qcb_ipc_close(self.dev, p)
+        self.base = []

@@ -21,4 +21,21 @@ for name, N, S in [("cfg2", 41, None), ("cfg4", 13, 5), ("cfg5", 33, None)]:
     else:
         co.evaluate()
     dist.barrier()
+
+# ---- peer delivery (CUDA IPC): slabs stored straight into rank 0's HBM by the producing kernels ----
+for name, N in [("cfg2", 41), ("cfg5", 33)]:
+    w = workloads.make(name, N=N); L = w.layout
+    k0, k1 = distributed.slab_bounds(L.K, rank, world)
+    ev = Evaluator(L, w.G_drift, w.G_drives, device=local, k_begin=k0, k_end=k1)
+    pd = distributed.PeerDelivery(ev, L, local)
+    dZ, dmu = torch.from_numpy(w.Z).to(dev), torch.from_numpy(w.mu).to(dev)
+    pd.evaluate(dZ, dmu)
+    if rank == 0:
+        got = pd.fetch()
+        full = Evaluator(L, w.G_drift, w.G_drives, device=local)
+        ref = full.eval_all(w.Z, w.mu)
+        print(name, "peer delivery world", world, [float(np.abs(a - b).max() / np.abs(b).max()) for a, b in zip(got, ref)], flush=True)
+        assert all(np.abs(a - b).max() <= 1e-12 * np.abs(b).max() for a, b in zip(got, ref))
+    dist.barrier()
+    pd.close()
 dist.destroy_process_group()
