@@ -504,7 +504,7 @@ void ensure_scratch(qcb_handle_s *h, int s_need) {
     if (h->s_cap >= s_need && h->sc_fixed) return;
     free_scratch(h);
     const int s_cap = std::max(s_need, 2);
-    size_t budget_mb = 6144;
+    size_t budget_mb = 8192;
     if (const char *e = getenv("QCB_SCRATCH_MB")) budget_mb = (size_t)std::max(64L, atol(e));
     const size_t per = scratch_bytes_per_unit(h, s_cap);
     long long cu = (long long)((budget_mb << 20) / per);
@@ -517,10 +517,11 @@ void ensure_scratch(qcb_handle_s *h, int s_need) {
                                                                               : (long long)(h->dp / 64) * (h->dp / 64));
         long long best = cu, best_waves = -1;
         for (long long t = cu; t >= std::max(1LL, cu * 2 / 3); --t) {
+            // ~13 per-drive launches and ~20 per-unit launches per chunk, all of similar tile cost
             long long waves = 0;
             for (long long done = 0; done < h->units; done += t) {
                 const long long n_ = std::min<long long>(t, h->units - done);
-                waves += (n_ * h->m * tiles + slots - 1) / slots;
+                waves += 13 * ((n_ * h->m * tiles + slots - 1) / slots) + 20 * ((n_ * tiles + slots - 1) / slots);
             }
             if (best_waves < 0 || waves < best_waves) { best_waves = waves; best = t; }
         }
