@@ -596,9 +596,20 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
                          h->HA, host->hess, h->hnnz_unit, nthreads);
         prev_u0 = -1;
     };
+    // Host-complete calls are bound by the host cores' expansion, not by the GPU: use small chunks
+    // (six full waves of per-drive CTAs) so that the first arenas reach the host early and the
+    // expansion pipeline starts after a few milliseconds instead of a third of the evaluation.
+    int chunk_step = h->chunk_units;
+    if (compact && !getenv("QCB_E2E_BIG_CHUNKS")) {
+        const long long slots = (long long)h->n_sm * (h->iso ? 2 : 1);
+        const long long tiles = h->iso ? (h->dp / 128) : ((h->dp % 128 == 0) ? (long long)(h->dp / 128) * (h->dp / 128)
+                                                                              : (long long)(h->dp / 64) * (h->dp / 64));
+        const long long small = std::max(1LL, 6 * slots / std::max<long long>(1, (long long)std::max(1, h->m) * tiles));
+        chunk_step = (int)std::min<long long>(h->chunk_units, small);
+    }
     size_t chunk_idx = 0;
-    for (int u0 = 0; u0 < h->units; u0 += h->chunk_units, ++chunk_idx) {
-        const int nu = std::min(h->chunk_units, h->units - u0);
+    for (int u0 = 0; u0 < h->units; u0 += chunk_step, ++chunk_idx) {
+        const int nu = std::min(chunk_step, h->units - u0);
         LargeExec X{h, nu, u0, s};
         X.dd = dd; X.pan = pan;
         const int buf = compact ? (int)(chunk_idx & 1) : 0;
