@@ -6,6 +6,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -223,18 +226,80 @@ __attribute__((target("avx512f"))) void fill_run_avx512(double *dst, double v, s
     for (; i < len; ++i) dst[i] = v;
 }
 
-// Expand `nu` units: out[(u0 + u) * nnz + seg.dst ...] from arena rows staged in host memory.
-void expand_units(const std::vector<std::vector<Seg>> &segs, int nk, int u0, int nu, const double *stage,
-                  int64_t arena_stride, double *out, int64_t nnz, int nthreads) {
+// Persistent worker threads for the host-side expansion (created once per process, shared by all
+// handles): run(fn) executes fn() on every worker and on the caller, returns when all are done.
+class HostPool {
+public:
+    static HostPool &get() { static HostPool p; return p; }
+    int size() const { return (int)workers_.size() + 1; }
+    void run(const std::function<void()> &fn) {
+        {
+            std::lock_guard<std::mutex> lk(m_);
+            fn_ = &fn; pending_ = (int)workers_.size(); ++epoch_;
+        }
+        cv_.notify_all();
+        fn();
+        std::unique_lock<std::mutex> lk(m_);
+        done_.wait(lk, [&] { return pending_ == 0; });
+        fn_ = nullptr;
+    }
+private:
+    HostPool() {
+        const int n = (int)std::max(1u, std::thread::hardware_concurrency());
+        for (int i = 1; i < n; ++i) workers_.emplace_back([this] { loop(); });
+    }
+    ~HostPool() {
+        { std::lock_guard<std::mutex> lk(m_); stop_ = true; ++epoch_; }
+        cv_.notify_all();
+        for (auto &w : workers_) w.join();
+    }
+    void loop() {
+        unsigned long long seen = 0;
+        for (;;) {
+            const std::function<void()> *fn;
+            {
+                std::unique_lock<std::mutex> lk(m_);
+                cv_.wait(lk, [&] { return epoch_ != seen; });
+                seen = epoch_;
+                if (stop_) return;
+                fn = fn_;
+            }
+            (*fn)();
+            { std::lock_guard<std::mutex> lk(m_); if (--pending_ == 0) done_.notify_one(); }
+        }
+    }
+    std::vector<std::thread> workers_;
+    std::mutex m_;
+    std::condition_variable cv_, done_;
+    const std::function<void()> *fn_ = nullptr;
+    int pending_ = 0;
+    unsigned long long epoch_ = 0;
+    bool stop_ = false;
+};
+
+// One expansion job: `nu` units of one COO vector from arena rows staged in host memory.
+struct ExpandJob {
+    const std::vector<std::vector<Seg>> *segs;
+    const double *stage;
+    int64_t arena_stride;
+    double *out;
+    int64_t nnz;
+};
+
+// Expand units [u0, u0 + nu) of every job: out[(u0 + u) * nnz + seg.dst ...] = +-arena[seg.src ...].
+void expand_units(const ExpandJob *jobs, int njobs, int nk, int u0, int nu) {
     static const bool has512 = __builtin_cpu_supports("avx512f");
     std::atomic<int> next{0};
-    auto work = [&]() {
+    const int total = nu * njobs;
+    std::function<void()> work = [&]() {
         for (;;) {
-            const int u = next.fetch_add(1);
-            if (u >= nu) break;
-            const std::vector<Seg> &sg = segs[(size_t)((u0 + u) / nk)];
-            const double *ar = stage + (size_t)u * arena_stride;
-            double *o = out + (size_t)(u0 + u) * nnz;
+            const int w = next.fetch_add(1);
+            if (w >= total) break;
+            const ExpandJob &jb = jobs[w / nu];
+            const int u = w % nu;
+            const std::vector<Seg> &sg = (*jb.segs)[(size_t)((u0 + u) / nk)];
+            const double *ar = jb.stage + (size_t)u * jb.arena_stride;
+            double *o = jb.out + (size_t)(u0 + u) * jb.nnz;
             for (const Seg &q : sg) {
                 const bool neg = q.kind & 1u;
                 if (q.kind & 2u) {
@@ -247,11 +312,7 @@ void expand_units(const std::vector<std::vector<Seg>> &segs, int nk, int u0, int
         }
         if (has512) _mm_sfence();
     };
-    const int nt = std::max(1, std::min(nthreads, nu));
-    std::vector<std::thread> th;
-    for (int t = 1; t < nt; ++t) th.emplace_back(work);
-    work();
-    for (auto &t : th) t.join();
+    HostPool::get().run(work);
 }
 
 void upload_codes(qcb_handle_s *h, uint32_t **dptr, const std::vector<uint32_t> &codes) {
@@ -580,7 +641,6 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     UnitGeom q = h->geom();
     const bool compact = host && host->compact && (wj || wh);
     if (compact) ensure_compact(h);
-    const int nthreads = (int)std::max(1u, std::thread::hardware_concurrency());
     // chunk whose arenas are staged on the host, not yet expanded; its first prev_nd units went
     // the direct route (assembled on the device, full COO rows DMA'd) and need no expansion
     int prev_u0 = -1, prev_nu = 0, prev_nd = 0;
@@ -588,12 +648,11 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         if (prev_u0 < 0) return;
         const int b = (int)(idx_prev & 1);
         CK(cudaEventSynchronize(h->copied[b]));
-        if (wj && host->jac)
-            expand_units(h->jsegs, h->nk, prev_u0 + prev_nd, prev_nu - prev_nd, h->stage_j[b] + (size_t)prev_nd * h->JA,
-                         h->JA, host->jac, h->jnnz_unit, nthreads);
-        if (wh && host->hess)
-            expand_units(h->hsegs, h->nk, prev_u0 + prev_nd, prev_nu - prev_nd, h->stage_h[b] + (size_t)prev_nd * h->HA,
-                         h->HA, host->hess, h->hnnz_unit, nthreads);
+        ExpandJob jobs[2];
+        int nj = 0;
+        if (wj && host->jac) jobs[nj++] = {&h->jsegs, h->stage_j[b] + (size_t)prev_nd * h->JA, h->JA, host->jac, h->jnnz_unit};
+        if (wh && host->hess) jobs[nj++] = {&h->hsegs, h->stage_h[b] + (size_t)prev_nd * h->HA, h->HA, host->hess, h->hnnz_unit};
+        if (nj > 0 && prev_nu > prev_nd) expand_units(jobs, nj, h->nk, prev_u0 + prev_nd, prev_nu - prev_nd);
         prev_u0 = -1;
     };
     // Host-complete calls are bound by the host cores' expansion, not by the GPU: use small chunks
