@@ -123,6 +123,16 @@ qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu,
 qcb_status qcb_eval_all_device(qcb_handle h, const double *dZ, const double *dmu,
                                double *d_delta, double *d_jac_vals, double *d_hess_vals);
 
+/* ---- rollout --------------------------------------------------------------
+ * x_{k+1} = exp(dt_k G(u_k)) x_k for k = 1..N-1 with the controls and timesteps of Z held constant
+ * over each interval -- the propagation behind sync_trajectory! / rollout fidelity
+ * (src/quantum_control_problem.jl:137-150; piccolo_options.jl:30 `rollout_integrator = expv`).
+ * x_init: [S][x_dim] initial states, or NULL to start from the states stored at knot 1 of Z.
+ * states: [S][N][x_dim] (host).  All propagators are computed in parallel by the evaluator's
+ * kernels; only the chain of N-1 panel products is sequential.  The handle must own the whole
+ * trajectory (k_begin = 0, k_end = K). */
+qcb_status qcb_rollout(qcb_handle h, const double *Z, const double *x_init, double *states);
+
 /* Peer delivery for the multi-GPU time-slab partition (no counterpart in the
  * single-process reference).  The rank that hosts Ipopt allocates the full value buffers with
  * qcb_device_alloc and exports them (64-byte CUDA IPC handles, to be sent to the other ranks by any

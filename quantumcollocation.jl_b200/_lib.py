@@ -49,6 +49,7 @@ SYMBOLS = {
     "qcb_eval_hessian": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp]),
     "qcb_eval_all": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "qcb_eval_all_device": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "qcb_rollout": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp]),
     "qcb_device_alloc": (ctypes.c_int, [ctypes.c_int32, ctypes.POINTER(c_vp), ctypes.c_size_t]),
     "qcb_device_free": (None, [ctypes.c_int32, c_vp]),
     "qcb_ipc_export": (ctypes.c_int, [ctypes.c_int32, c_vp, ctypes.c_char_p]),

@@ -145,6 +145,16 @@ class Evaluator:
     def eval_all_device(self, dZ, dmu, d_delta, d_jac, d_hess):
         self._check(self.lib.qcb_eval_all_device(self.h, _ptr(dZ), _ptr(dmu), _ptr(d_delta), _ptr(d_jac), _ptr(d_hess)))
 
+    def rollout(self, Z, x_init=None):
+        """States [S, N, x_dim] of x_{k+1} = exp(dt_k G(u_k)) x_k (x_init [S, x_dim] or knot 1 of Z)."""
+        L = self.layout
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        if x_init is not None:
+            x_init = np.ascontiguousarray(x_init, dtype=np.float64).reshape(L.S, L.x_dim)
+        states = np.empty((L.S, L.N, L.x_dim))
+        self._check(self.lib.qcb_rollout(self.h, _ptr(Z), _ptr(x_init), _ptr(states)))
+        return states
+
     def timings(self):
         ms = (ctypes.c_double * 4)()
         self.lib.qcb_get_timings(self.h, ms)

@@ -94,6 +94,7 @@ struct qcb_handle_s {
     double *sc_XP = nullptr, *sc_MP = nullptr, *sc_EX = nullptr, *sc_ja = nullptr, *sc_ha = nullptr;
     double *sc_H = nullptr, *sc_c1 = nullptr, *sc_c2 = nullptr, *sc_c3 = nullptr, *sc_tau = nullptr, *sc_ntau = nullptr;
     int small_threads = 0;
+    double *d_Eall = nullptr, *d_states = nullptr, *d_xinit = nullptr;   // rollout buffers
     // compact host transfer: arenas (not expanded COO vectors) cross PCIe, the host cores expand
     std::vector<uint32_t> h_jcode, h_hcode;           // host copies of the code tables [S][nnz]
     std::vector<std::vector<Seg>> jsegs, hsegs;       // per system
@@ -632,7 +633,7 @@ int slab_squarings(qcb_handle_s *h, const double *dZ) {
 }
 
 void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_delta, double *d_jac,
-                double *d_hess, int want, const HostOut *host, int s) {
+                double *d_hess, int want, const HostOut *host, int s, double *E_out = nullptr) {
     ensure_scratch(h, s);
     const bool wj = want & 1, wh = (want & 2) && dmu;
     const long long dd = h->msz, pan = (long long)h->dp * h->cp;
@@ -699,6 +700,11 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         X.product(EXp, Ef, 0, XP, 0, h->dp, h->cp, h->dp, 1, 1.0, nullptr);
         delta_kernel<<<nu, 256, 0, h->stream>>>(q, dZ, h->sc_EX, pan, d_delta, u0);
         ++h->launches;
+        if (E_out) {      // rollouts: keep the (unpadded, full) propagator of every unit
+            if (h->iso) { iso_expand_kernel<<<nu, 256, 0, h->stream>>>(X.ja, h->JA, h->dp); ++h->launches; }
+            extract_E_kernel<<<nu, 256, 0, h->stream>>>(X.ja, h->JA, h->dp, h->d, E_out + (size_t)u0 * h->d * h->d);
+            ++h->launches;
+        }
         if (wj || wh) {
             if (wh) {
                 if (h->iso) {   // W = M X^T is a general matrix: project it onto the iso algebra (half storage)
@@ -841,8 +847,9 @@ void launch_small(qcb_handle_s *h, const SmallParams &p, size_t smem) {
 }
 
 void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_delta, double *d_jac,
-                double *d_hess, int want, int s) {
+                double *d_hess, int want, int s, double *E_out = nullptr) {
     SmallParams p;
+    p.E_out = E_out;
     p.d = h->d; p.c = h->c; p.m = h->m; p.z_dim = h->z_dim; p.u_off = h->u_off; p.dt_off = h->dt_off;
     p.K = h->K; p.nk = h->nk; p.k_begin = h->k0; p.S = h->S; p.units = h->units;
     p.x_off = h->d_xoff; p.G0 = h->dG0; p.Gd = h->dGd; p.Z = dZ; p.mu = dmu;
@@ -879,12 +886,12 @@ void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
 
 // common driver: device inputs -> device outputs (+ optional streamed host outputs)
 qcb_status eval_device(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_delta, double *d_jac,
-                       double *d_hess, int want, const HostOut *host) {
+                       double *d_hess, int want, const HostOut *host, double *E_out = nullptr) {
     const char *range_msg = "non-finite input or ||dt*G(u)||_1 beyond the supported range";
     if (h->large) {
         const int s = slab_squarings(h, dZ);
         if (s < 0) { h->err = range_msg; return QCB_ERR_RANGE; }
-        eval_large(h, dZ, dmu, d_delta, d_jac, d_hess, want, host, s);
+        eval_large(h, dZ, dmu, d_delta, d_jac, d_hess, want, host, s, E_out);
     } else {
         // No norm pre-pass on the small-d path: the kernel sizes its squaring chains for the count
         // seen by the previous call, reports the count it needs, and is re-run once if that was
@@ -892,7 +899,7 @@ qcb_status eval_device(qcb_handle_s *h, const double *dZ, const double *dmu, dou
         int cap = std::min(h->s_hint, QCB_MAX_SQUARINGS);
         for (int attempt = 0;; ++attempt) {
             CK(cudaMemsetAsync(h->d_bad, 0, 2 * sizeof(int), h->stream));
-            eval_small(h, dZ, dmu, d_delta, d_jac, d_hess, want, cap);
+            eval_small(h, dZ, dmu, d_delta, d_jac, d_hess, want, cap, E_out);
             CK(cudaMemcpyAsync(h->h_flags, h->d_bad, 2 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
             CK(cudaStreamSynchronize(h->stream));
             if (h->h_flags[0] & 1) { h->err = range_msg; return QCB_ERR_RANGE; }
@@ -1087,7 +1094,8 @@ void qcb_destroy(qcb_handle h) {
     if (!h) return;
     cudaSetDevice(h->device);
     free_scratch(h);
-    void *ptrs[] = {h->dG0, h->dGd, h->d_xoff, h->d_jcode, h->d_hcode, h->d_norm, h->d_bad, h->dZ, h->dmu, h->d_delta, h->d_jac, h->d_hess};
+    void *ptrs[] = {h->dG0, h->dGd, h->d_xoff, h->d_jcode, h->d_hcode, h->d_norm, h->d_bad, h->dZ, h->dmu, h->d_delta, h->d_jac, h->d_hess,
+                    h->d_Eall, h->d_states, h->d_xinit};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (h->h_flags) cudaFreeHost(h->h_flags);
@@ -1312,6 +1320,39 @@ qcb_status qcb_eval_jacobian(qcb_handle h, const double *Z, double *jac) {
 qcb_status qcb_eval_hessian(qcb_handle h, const double *Z, const double *mu, double *hess) {
     if (!hess) return fail(h, QCB_ERR_ARG, "null output");
     return qcb_eval_all(h, Z, mu, nullptr, nullptr, hess);
+}
+
+qcb_status qcb_rollout(qcb_handle h, const double *Z, const double *x_init, double *states) {
+    if (!h || !Z || !states) return fail(h, QCB_ERR_ARG, "null argument");
+    if (h->k0 != 0 || h->k1 != h->K) return fail(h, QCB_ERR_ARG, "a rollout needs a handle that owns the whole trajectory");
+    try {
+        CK(cudaSetDevice(h->device));
+        const size_t nz = (size_t)h->N * h->z_dim, dd = (size_t)h->d * h->d, ns = (size_t)h->S * h->N * h->xdim;
+        ensure_out(h, &h->dZ, nz);
+        ensure_out(h, &h->d_delta, (size_t)h->units * h->xdim);
+        ensure_out(h, &h->d_Eall, (size_t)h->units * dd);
+        ensure_out(h, &h->d_states, ns);
+        CK(cudaMemcpyAsync(h->dZ, Z, nz * 8, cudaMemcpyHostToDevice, h->stream));
+        if (x_init) {
+            ensure_out(h, &h->d_xinit, (size_t)h->S * h->xdim);
+            CK(cudaMemcpyAsync(h->d_xinit, x_init, (size_t)h->S * h->xdim * 8, cudaMemcpyHostToDevice, h->stream));
+        }
+        // every propagator E_k in parallel (polynomial + squarings only), then the sequential chain
+        qcb_status st = eval_device(h, h->dZ, nullptr, h->d_delta, nullptr, nullptr, 0, nullptr, h->d_Eall);
+        if (st != QCB_OK) return st;
+        const size_t smem = 2 * (size_t)h->xdim * sizeof(double);
+        if (smem > 200 * 1024) return fail(h, QCB_ERR_ARG, "state panel too large for the rollout kernel");
+        CK(cudaFuncSetAttribute(rollout_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        rollout_chain_kernel<<<h->S, 256, smem, h->stream>>>(h->d_Eall, x_init ? h->d_xinit : nullptr, h->dZ, h->z_dim,
+                                                             h->d_xoff, h->d, h->c, h->K, h->d_states);
+        ++h->launches;
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(states, h->d_states, ns * 8, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        return QCB_OK;
+    } catch (const CudaFail &f) {
+        return fail_cuda(h, f);
+    }
 }
 
 qcb_status qcb_host_alloc(void **ptr, size_t bytes) {

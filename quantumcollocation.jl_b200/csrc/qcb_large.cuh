@@ -775,4 +775,42 @@ delta_kernel(UnitGeom q, const double *Z, const double *EX, long long pan_stride
     }
 }
 
+
+// out[u][r + q*d] = arena[u*stride + r + q*dp]: the unpadded propagator of every unit of a chunk
+__global__ void __launch_bounds__(256)
+extract_E_kernel(const double *arena, long long stride, int dp, int d, double *out) {
+    const double *E = arena + (long long)blockIdx.x * stride;
+    double *o = out + (long long)blockIdx.x * d * d;
+    for (int e = threadIdx.x; e < d * d; e += blockDim.x) o[e] = E[(e % d) + (long long)(e / d) * dp];
+}
+
+// Rollout: x_{k+1} = E_k x_k along the trajectory, one CTA per system, the state panel (d x c) in
+// shared memory, E_k streamed from global memory (computed for all k beforehand, in parallel).
+// states: [S][N][x_dim].  Thread t owns row r = t % d for the columns b = t / d, t / d + nb, ...
+__global__ void __launch_bounds__(256)
+rollout_chain_kernel(const double *E, const double *x_init, const double *Z, int z_dim, const int *x_off,
+                     int d, int c, int K, double *states) {
+    extern __shared__ double xs[];          // two panels of d*c
+    const int s = blockIdx.x, dc = d * c;
+    double *cur = xs, *nxt = xs + dc;
+    double *out = states + (long long)s * (K + 1) * dc;
+    for (int e = threadIdx.x; e < dc; e += blockDim.x) {
+        const double v = x_init ? x_init[(long long)s * dc + e] : Z[x_off[s] + e];
+        cur[e] = v; out[e] = v;
+    }
+    __syncthreads();
+    for (int k = 0; k < K; ++k) {
+        const double *Ek = E + ((long long)s * K + k) * d * d;
+        for (int e = threadIdx.x; e < dc; e += blockDim.x) {
+            const int r = e % d, b = e / d;
+            double acc = 0.0;
+            for (int q = 0; q < d; ++q) acc = fma(Ek[r + (long long)q * d], cur[q + b * d], acc);
+            nxt[e] = acc;
+            out[(long long)(k + 1) * dc + e] = acc;
+        }
+        __syncthreads();
+        double *t = cur; cur = nxt; nxt = t;
+    }
+}
+
 }  // namespace qcb

@@ -31,6 +31,7 @@ struct SmallParams {
     const uint32_t *jcode, *hcode;  // [S][nnz]
     long long jnnz, hnnz;
     int want;                       // bit0 jac, bit1 hess
+    double *E_out;                  // optional [units][d*d]: the propagator of every unit (rollouts)
     int smax;                       // chain capacity allocated in shared memory
     int *bad_flag;
 };
@@ -408,6 +409,10 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
             for (int q = 0; q < d; ++q) acc = fma(E[r + q * ld], X[q + b * d], acc);
             o[e] = Xn[e] - acc;
         }
+    }
+    if (p.E_out && live) {
+        double *o = p.E_out + (long long)ug * dd;
+        for (int e = e0; e < dd; e += tpu) o[e] = E[(e % d) + (e / d) * ld];
     }
     if (!want_jac && !want_hess) return;
 

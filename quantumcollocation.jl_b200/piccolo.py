@@ -190,6 +190,13 @@ def BilinearIntegrator(qtraj, traj: NamedTrajectory, fused: bool = False, device
     return out
 
 
+def rollout(integrator: Integrator, traj: NamedTrajectory, x_init=None) -> np.ndarray:
+    """States [S, N, x_dim] obtained by propagating ``x_init`` (default: the states at knot 1) with the
+    trajectory's controls and timesteps -- what ``sync_trajectory!`` re-computes after a solve
+    (src/quantum_control_problem.jl:137-150), for controls held constant over each interval."""
+    return integrator.evaluator.rollout(traj.datavec, x_init)
+
+
 def evaluate_(delta: np.ndarray, integrator: Integrator, traj: NamedTrajectory) -> np.ndarray:
     """``DirectTrajOpt.evaluate!(delta, integrator, traj)``."""
     return integrator.evaluate(delta, traj)
