@@ -336,3 +336,60 @@ def test_large_path_compact_host_transfer_equals_direct(name, N, S, built_libs):
     # Jacobian-only and Hessian-only callbacks through the compact route
     assert np.array_equal(ev.eval_jacobian(w.Z), j1) and np.array_equal(ev.eval_hessian(w.Z, w.mu), h1)
     ev.close()
+
+
+def _random_system(n, m, rng, scale=0.05):
+    rh = lambda: (lambda A: (A + A.conj().T) / 2)(rng.normal(size=(n, n)) + 1j * rng.normal(size=(n, n)))
+    return scale * O.G_of_H(rh())[None], scale * np.array([O.G_of_H(rh()) for _ in range(m)])[None]
+
+
+def test_large_path_d256_two_row_tiles(built_libs):
+    """d = 256 (7 qubits): the iso half-storage GEMM runs two 128-row tiles per matrix, so the
+    row-rotation / sign logic is exercised with m0 > 0.  Ket panel, 2 drives, against the CPU port."""
+    rng = np.random.default_rng(3)
+    n, m, N = 128, 2, 3
+    G0, Gd = _random_system(n, m, rng, scale=0.02)
+    L = KnotLayout.smooth_pulse(2 * n, 1, m, N, jac_mode=1)
+    Z = rng.normal(size=(N, L.z_dim)); Z[:, L.dt_off] = 0.3; Z[:, L.u_off:L.u_off + m] *= 0.2
+    mu = rng.normal(size=L.K * L.x_dim)
+    ev = Evaluator(L, G0, Gd)
+    d1, j1, h1 = ev.eval_all(Z.reshape(-1), mu)
+    d0, j0, h0 = P.evaluate(oracle_layout(L), G0, Gd, Z.reshape(-1), mu)
+    assert rel_err(d1, d0) < TOL and rel_err(j1, j0) < TOL and rel_err(h1, h0) < TOL
+    ev.close()
+
+
+def test_large_path_full_storage_d128_without_iso_structure(built_libs):
+    """A d = 128 generator WITHOUT the real-iso block form (e.g. a variational / block-triangular
+    generator): the full-storage 128 x 128-tile DMMA kernel is used instead of the half-storage one."""
+    rng = np.random.default_rng(4)
+    d, m, N = 128, 2, 3
+    G0 = 0.01 * rng.normal(size=(1, d, d))
+    Gd = 0.01 * rng.normal(size=(1, m, d, d))
+    L = KnotLayout.smooth_pulse(d, 2, m, N, jac_mode=1)
+    Z = rng.normal(size=(N, L.z_dim)); Z[:, L.dt_off] = 0.25; Z[:, L.u_off:L.u_off + m] *= 0.3
+    mu = rng.normal(size=L.K * L.x_dim)
+    ev = Evaluator(L, G0, Gd)
+    d1, j1, h1 = ev.eval_all(Z.reshape(-1), mu)
+    d0, j0, h0 = P.evaluate(oracle_layout(L), G0, Gd, Z.reshape(-1), mu)
+    assert rel_err(d1, d0) < TOL and rel_err(j1, j0) < TOL and rel_err(h1, h0) < TOL
+    ev.close()
+
+
+@pytest.mark.parametrize("d,c,m,S", [(2, 1, 1, 1), (5, 2, 3, 2), (7, 1, 2, 1), (9, 3, 1, 2), (14, 2, 2, 1), (20, 1, 5, 1), (40, 3, 2, 1)])
+def test_odd_shapes_and_general_generators(d, c, m, S, built_libs):
+    """Dimensions without a specialised instance (run-time-d interpreter), odd d, several systems,
+    non-skew generators, and d = 40 (large-d path padded to 64)."""
+    rng = np.random.default_rng(d * 100 + c * 10 + m)
+    N = 4
+    G0 = 0.3 * rng.normal(size=(S, d, d)) / np.sqrt(d)
+    Gd = 0.3 * rng.normal(size=(S, m, d, d)) / np.sqrt(d)
+    L = KnotLayout.smooth_pulse(d, c, m, N, S=S, with_derivatives=False)
+    Z = rng.normal(size=(N, L.z_dim)); Z[:, L.dt_off] = rng.uniform(0.1, 1.5, N); Z[:, L.u_off:L.u_off + m] *= 0.5
+    mu = rng.normal(size=S * L.K * L.x_dim)
+    ev = Evaluator(L, G0, Gd)
+    d1, j1, h1 = ev.eval_all(Z.reshape(-1), mu)
+    ref = O.evaluate if d <= 14 else P.evaluate
+    d0, j0, h0 = ref(oracle_layout(L), G0, Gd, Z.reshape(-1), mu)
+    assert rel_err(d1, d0) < TOL and rel_err(j1, j0) < TOL and rel_err(h1, h0) < TOL
+    ev.close()
