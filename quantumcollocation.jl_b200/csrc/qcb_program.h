@@ -61,16 +61,16 @@ enum {
     QR_LN                         /* L_j at the next level */
 };
 #define QCB_NUM_DSLOTS 6          /* one slot per register when every direction has its own set */
-#define QCB_NUM_DPERSIST 4        /* DA2, DA4, DZ1, DZ2: read again by the contractions of every direction */
-#define QCB_NUM_DTEMP 2           /* DA3, U: dead once the direction's op sequence is over */
+#define QCB_NUM_DPERSIST 5        /* DA2, DA3, DA4, DZ1, DZ2: kept per direction (all directions advance together) */
+#define QCB_NUM_DTEMP 1           /* U: dead once its contraction is done */
 
 QCB_HD static inline int qcb_is_dreg(int r) { return r >= QR_DA2 && r <= QR_U; }
 QCB_HD static inline int qcb_dslot(int r) { return r - QR_DA2; }
 /* index among the persistent per-direction registers, or -1 */
 QCB_HD static inline int qcb_dpersist(int r) {
-    return r == QR_DA2 ? 0 : r == QR_DA4 ? 1 : r == QR_DZ1 ? 2 : r == QR_DZ2 ? 3 : -1;
+    return (r >= QR_DA2 && r <= QR_DZ2) ? r - QR_DA2 : -1;
 }
-QCB_HD static inline int qcb_dtemp(int r) { return r == QR_DA3 ? 0 : 1; }
+QCB_HD static inline int qcb_dtemp(int r) { (void)r; return 0; }
 
 typedef struct { uint8_t a, b, ta, tb; } qcb_term;
 typedef struct { uint8_t reg, coef; } qcb_lin;

@@ -45,11 +45,10 @@ struct SmallCtx {
     int e0, tpu;     // this thread's first element and the element stride
     double *fixed;   // [QR_NUM_FIXED][msz]
     double *E, *W;   // [smax+1][msz]
-    double *dpersist;  // [QCB_NUM_DPERSIST][m][msz]: DA2, DA4, DZ1, DZ2 of every direction
-    double *dtemp;     // [QCB_NUM_DTEMP][msz]: DA3, U
-    double *L;       // [m+1][msz]
+    double *dpersist;  // [QCB_NUM_DPERSIST][m][msz]: DA2, DA3, DA4, DZ1, DZ2 of every direction
+    double *L;       // [2][m][msz]: L_j at the current / next squaring level
+    int lcur;        // which half of L holds the current level
     const double *Gs;  // [m][msz] the unit's drive generators, staged in shared memory
-    const int *Lidx; // [m+1] shared by the CTA (slot of direction j; entry m = free slot)
 };
 
 __device__ __forceinline__ double *sm_resolve(const SmallCtx &x, int r) {
@@ -62,11 +61,9 @@ __device__ __forceinline__ double *sm_resolve(const SmallCtx &x, int r) {
     case QR_E0: return x.E;
     case QR_W0: return x.W;
     case QR_GJ: return const_cast<double *>(x.Gs) + x.j * x.msz;
-    case QR_L: return x.L + x.Lidx[x.j] * x.msz;
-    case QR_LN: return x.L + x.Lidx[x.m] * x.msz;
-    default:
-        if (qcb_dpersist(r) >= 0) return x.dpersist + (qcb_dpersist(r) * x.m + x.j) * x.msz;
-        return x.dtemp + qcb_dtemp(r) * x.msz;
+    case QR_L: return x.L + (x.lcur * x.m + x.j) * x.msz;
+    case QR_LN: return x.L + ((x.lcur ^ 1) * x.m + x.j) * x.msz;
+    default: return x.dpersist + (qcb_dpersist(r) * x.m + x.j) * x.msz;   // QR_U is never stored here
     }
 }
 
@@ -94,7 +91,7 @@ template <int D, int AS, int BS> __device__ __forceinline__ double dot_k(const d
 }
 
 // dst = sum_t op(a)op(b) + sum_r c*reg + c*I for this thread's unit.  Ends with a CTA barrier.
-template <int D> __device__ __noinline__ void sm_run_op(const SmallCtx &x, const qcb_op &op) {
+template <int D, bool SYNC = true> __device__ __noinline__ void sm_run_op(const SmallCtx &x, const qcb_op &op) {
     const int d = D > 0 ? D : x.d, ld = D > 0 ? ((D & 1) ? D : D + 1) : x.ld, dd = d * d;
     double *dst = sm_resolve(x, op.dst);
     for (int e = x.e0; e < dd; e += x.tpu) {
@@ -114,7 +111,7 @@ template <int D> __device__ __noinline__ void sm_run_op(const SmallCtx &x, const
         if (op.ident >= 0 && r == q) acc += c_taylor[op.ident];
         dst[off] = acc;
     }
-    __syncthreads();
+    if (SYNC) __syncthreads();
 }
 
 // ---- compile-time ops (D > 0): one specialised routine per table entry -- register bases are
@@ -133,11 +130,9 @@ template <int D, int R> __device__ __forceinline__ double *sm_resolve_s(const Sm
     else if constexpr (R == QR_E0) return x.E;
     else if constexpr (R == QR_W0) return x.W;
     else if constexpr (R == QR_GJ) return const_cast<double *>(x.Gs) + x.j * MSZ;
-    else if constexpr (R == QR_L) return x.L + x.Lidx[x.j] * MSZ;
-    else if constexpr (R == QR_LN) return x.L + x.Lidx[x.m] * MSZ;
-    else if constexpr (R == QR_DA2 || R == QR_DA4 || R == QR_DZ1 || R == QR_DZ2)
-        return x.dpersist + ((R == QR_DA2 ? 0 : R == QR_DA4 ? 1 : R == QR_DZ1 ? 2 : 3) * x.m + x.j) * MSZ;
-    else return x.dtemp + (R == QR_DA3 ? 0 : 1) * MSZ;
+    else if constexpr (R == QR_L) return x.L + (x.lcur * x.m + x.j) * MSZ;
+    else if constexpr (R == QR_LN) return x.L + ((x.lcur ^ 1) * x.m + x.j) * MSZ;
+    else return x.dpersist + ((R - QR_DA2) * x.m + x.j) * MSZ;
 }
 template <int D, const qcb_op *TAB, int I, int T>
 __device__ __forceinline__ double sm_term_s(const SmallCtx &x, int r, int q) {
@@ -153,7 +148,7 @@ __device__ __forceinline__ double sm_lin_s(const SmallCtx &x, int off) {
     constexpr double cf = QCB_TAYLOR[ln.coef];
     return cf * sm_resolve_s<D, ln.reg>(x)[off];
 }
-template <int D, const qcb_op *TAB, int I, int... T, int... L>
+template <int D, const qcb_op *TAB, int I, bool SYNC, int... T, int... L>
 __device__ __forceinline__ void sm_run_static_impl(const SmallCtx &x, std::integer_sequence<int, T...>,
                                                    std::integer_sequence<int, L...>) {
     constexpr qcb_op op = TAB[I];
@@ -169,10 +164,10 @@ __device__ __forceinline__ void sm_run_static_impl(const SmallCtx &x, std::integ
         }
         dst[off] = acc;
     }
-    __syncthreads();
+    if (SYNC) __syncthreads();
 }
-template <int D, const qcb_op *TAB, int I> __device__ __forceinline__ void sm_run_static(const SmallCtx &x) {
-    sm_run_static_impl<D, TAB, I>(x, std::make_integer_sequence<int, TAB[I].nterm>{},
+template <int D, const qcb_op *TAB, int I, bool SYNC = true> __device__ __forceinline__ void sm_run_static(const SmallCtx &x) {
+    sm_run_static_impl<D, TAB, I, SYNC>(x, std::make_integer_sequence<int, TAB[I].nterm>{},
                                   std::make_integer_sequence<int, TAB[I].nlin>{});
 }
 template <int D, const qcb_op *TAB, int... I>
@@ -184,9 +179,33 @@ template <int D, const qcb_op *TAB, int N> __device__ __forceinline__ void sm_ru
     if constexpr (D > 0) sm_run_table_impl<D, TAB>(x, std::make_integer_sequence<int, N>{});
     else for (int i = 0; i < N; ++i) sm_run_op<0>(x, ctab[i]);
 }
-template <int D, const qcb_op *TAB, int I> __device__ __forceinline__ void sm_run_one(const SmallCtx &x, const qcb_op *ctab) {
-    if constexpr (D > 0) sm_run_static<D, TAB, I>(x);
-    else sm_run_op<0>(x, ctab[I]);
+template <int D, const qcb_op *TAB, int I, bool SYNC = true> __device__ __forceinline__ void sm_run_one(const SmallCtx &x, const qcb_op *ctab) {
+    if constexpr (D > 0) sm_run_static<D, TAB, I, SYNC>(x);
+    else sm_run_op<0, SYNC>(x, ctab[I]);
+}
+
+// value of the product terms of op I at element (r, q) -- no store (fused contractions)
+template <int D, const qcb_op *TAB, int I, int... T>
+__device__ __forceinline__ double sm_products_s(const SmallCtx &x, int r, int q, std::integer_sequence<int, T...>) {
+    return (0.0 + ... + sm_term_s<D, TAB, I, T>(x, r, q));
+}
+template <int D, const qcb_op *TAB, int I>
+__device__ __forceinline__ double sm_products(const SmallCtx &x, const qcb_op *ctab, int r, int q) {
+    if constexpr (D > 0) {
+        return sm_products_s<D, TAB, I>(x, r, q, std::make_integer_sequence<int, TAB[I].nterm>{});
+    } else {
+        const qcb_op &op = ctab[I];
+        const int d = x.d, ld = x.ld;
+        double acc = 0.0;
+        for (int t = 0; t < op.nterm; ++t) {
+            const int ta = op.term[t].ta, tb = op.term[t].tb;
+            const double *a = sm_resolve(x, op.term[t].a) + (ta ? r * ld : r);
+            const double *b = sm_resolve(x, op.term[t].b) + (tb ? q : q * ld);
+            const int as = ta ? 1 : ld, bs = tb ? ld : 1;
+            for (int k = 0; k < d; ++k) acc = fma(a[k * as], b[k * bs], acc);
+        }
+        return acc;
+    }
 }
 
 // Sum over the threads of a unit, result in every thread of the unit.  tpu is a power of two <= 32
@@ -291,17 +310,91 @@ __device__ __noinline__ void sm_panel(double *C, const double *A, int ta, const 
     }
 }
 
+// Add the unit-wide sums of a[0..nn) to out[0..nn).  red_unit: 8 doubles per warp of the unit.
+__device__ __forceinline__ void unit_reduce_add8(double (&a)[8], int nn, int tpu, int e0, double *red_unit, double *out) {
+    if (tpu <= 32) {
+#pragma unroll
+        for (int t = 0; t < 8; ++t)
+            for (int o = tpu >> 1; o > 0; o >>= 1) a[t] += __shfl_xor_sync(0xffffffffu, a[t], o);
+        if (e0 == 0)
+#pragma unroll
+            for (int t = 0; t < 8; ++t) if (t < nn) out[t] += a[t];
+    } else {
+#pragma unroll
+        for (int t = 0; t < 8; ++t)
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) a[t] += __shfl_xor_sync(0xffffffffu, a[t], o);
+        if ((e0 & 31) == 0)
+#pragma unroll
+            for (int t = 0; t < 8; ++t) red_unit[(e0 >> 5) * 8 + t] = a[t];
+        __syncthreads();
+        if (e0 < nn) {
+            double v = 0.0;
+            for (int w = 0; w < (tpu >> 5); ++w) v += red_unit[w * 8 + e0];
+            out[e0] += v;
+        }
+        __syncthreads();
+    }
+}
+
+// Second order at the polynomial level for direction j, all product nodes at once and nothing
+// stored:  Hrow[i] += sum_nodes sum_e (Xdot_j^T Nbar)[e] * Ydot_i[e].
+template <int D> __device__ __noinline__ void sm_p6_pass(SmallCtx &x, int j, const qcb_op *ctab, double *red_unit, double *Hrow) {
+    const int d = D > 0 ? D : x.d, ld = D > 0 ? ((D & 1) ? D : D + 1) : x.ld, msz = ld * d, m = x.m;
+    constexpr int pr0 = QCB_P6_PARTNER[0], pr1 = QCB_P6_PARTNER[1], pr2 = QCB_P6_PARTNER[2], pr3 = QCB_P6_PARTNER[3];
+    auto partner_base = [&](int reg) {
+        return (reg == QR_GJ) ? x.Gs : x.dpersist + (long long)qcb_dpersist(reg) * m * msz;
+    };
+    const double *part[4] = {partner_base(pr0), partner_base(pr1), partner_base(pr2), partner_base(pr3)};
+    x.j = j; x.level = 0;
+    for (int i0 = 0; i0 < m; i0 += 8) {
+        const int nn = min(8, m - i0);
+        double a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int e = x.e0; e < d * d; e += x.tpu) {
+            const int r = e % d, q = e / d, off = r + q * ld;
+            const double u0 = sm_products<D, QCB_P6, 0>(x, ctab, r, q), u1 = sm_products<D, QCB_P6, 1>(x, ctab, r, q);
+            const double u2 = sm_products<D, QCB_P6, 2>(x, ctab, r, q), u3 = sm_products<D, QCB_P6, 3>(x, ctab, r, q);
+#pragma unroll
+            for (int t = 0; t < 8; ++t)
+                if (t < nn) {
+                    const long long po = (long long)(i0 + t) * msz + off;
+                    a[t] = fma(u0, part[0][po], fma(u1, part[1][po], fma(u2, part[2][po], fma(u3, part[3][po], a[t]))));
+                }
+        }
+        unit_reduce_add8(a, nn, x.tpu, x.e0, red_unit, Hrow + i0);
+    }
+}
+
+// One squaring level for direction j:  Hrow[i] += sum_e (L_j^T W[l+1])[e] * L_i[e]
+template <int D> __device__ __noinline__ void sm_level_pass(SmallCtx &x, int j, int level, const qcb_op *ctab, double *red_unit, double *Hrow) {
+    const int d = D > 0 ? D : x.d, ld = D > 0 ? ((D & 1) ? D : D + 1) : x.ld, msz = ld * d, m = x.m;
+    const double *Lbase = x.L + (long long)x.lcur * m * msz;
+    x.j = j; x.level = level;
+    for (int i0 = 0; i0 < m; i0 += 8) {
+        const int nn = min(8, m - i0);
+        double a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int e = x.e0; e < d * d; e += x.tpu) {
+            const int r = e % d, q = e / d, off = r + q * ld;
+            const double u = sm_products<D, QCB_P7U, 0>(x, ctab, r, q);
+#pragma unroll
+            for (int t = 0; t < 8; ++t)
+                if (t < nn) a[t] = fma(u, Lbase[(long long)(i0 + t) * msz + off], a[t]);
+        }
+        unit_reduce_add8(a, nn, x.tpu, x.e0, red_unit, Hrow + i0);
+    }
+}
+
 static inline size_t small_unit_doubles(int d, int c, int m, int smax) {
     size_t msz = (size_t)small_ld(d) * d, dd = (size_t)d * d, dc = (size_t)d * c;
-    size_t n = (QR_NUM_FIXED + 2 * (size_t)(smax + 1) + (size_t)QCB_NUM_DPERSIST * m + QCB_NUM_DTEMP + (m + 1) + m) * msz;
+    size_t n = (QR_NUM_FIXED + 2 * (size_t)(smax + 1) + (size_t)QCB_NUM_DPERSIST * m + 2 * (size_t)m + m) * msz;
     n += 3 * dc;                                   // X, Xn, M panels
     n += dd + (m + 1) * dc + 2;                    // Jacobian arena
     n += (m + 1) * dc + (size_t)m * m + m + 2;     // Hessian arena
-    n += (size_t)m * m + 64;                       // H accumulator + reduction scratch (4 per warp)
+    n += (size_t)m * m + 128;                      // H accumulator + reduction scratch (8 per warp)
     return (n + 1) & ~(size_t)1;                   // keep every unit 16-byte aligned
 }
 static inline size_t small_smem_doubles(int d, int c, int m, int smax, int upc = 1) {
-    return (size_t)upc * small_unit_doubles(d, c, m, smax) + (size_t)(m + 2) / 2 + 2 + (size_t)upc + 2;
+    return (size_t)upc * small_unit_doubles(d, c, m, smax) + (size_t)upc + 2;
 }
 
 template <int D>
@@ -324,8 +417,8 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     x.E = ptr; ptr += (p.smax + 1) * msz;
     x.W = ptr; ptr += (p.smax + 1) * msz;
     x.dpersist = ptr; ptr += QCB_NUM_DPERSIST * m * msz;
-    x.dtemp = ptr; ptr += QCB_NUM_DTEMP * msz;
-    x.L = ptr; ptr += (m + 1) * msz;
+    x.L = ptr; ptr += 2 * m * msz;
+    x.lcur = 0;
     double *Gs = ptr; ptr += m * msz;
     double *X = ptr; ptr += dc;
     double *Xn = ptr; ptr += dc;
@@ -335,9 +428,7 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     double *Hacc = ptr; ptr += m * m;
     double *red = ptr;
     double *cta_tail = sm + (size_t)p.upc * p.unit_doubles;
-    int *Lidx = reinterpret_cast<int *>(cta_tail);                    // [m+1]
-    double *cta_nrm = cta_tail + (m + 2) / 2 + 2;                     // [upc]
-    x.Lidx = Lidx;
+    double *cta_nrm = cta_tail;                                       // [upc]
     x.Gs = Gs;
 
     const bool want_jac = p.want & 1, want_hess = (p.want & 2) && p.mu;
@@ -360,7 +451,6 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
         }
         G[off] = v;
     }
-    if (threadIdx.x <= m) Lidx[threadIdx.x] = threadIdx.x;
     for (int e = e0; e < m * m; e += tpu) Hacc[e] = 0.0;
     __syncthreads();
     // ---- ||dt G||_1 per unit, then one squaring count for the CTA ----
@@ -395,9 +485,47 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     for (int e = e0; e < dd; e += tpu) { const int off = (e % d) + (e / d) * ld; A[off] = tau * G[off]; }
     __syncthreads();
 
-    // ---- polynomial + squarings ----
-    sm_run_table<D, QCB_P1, 6>(x, c_P1);
-    for (int l = 0; l < s; ++l) { x.level = l; sm_run_one<D, QCB_P2, 0>(x, c_P2); }
+    const bool tang = want_jac || want_hess;
+    double *Wt = x.W + s * msz;
+    if (want_hess) {
+        for (int e = e0; e < dd; e += tpu) {   // W = M X^T (independent of E: ready before it is needed)
+            const int r = e % d, q = e / d;
+            double acc = 0.0;
+            for (int b = 0; b < c; ++b) acc = fma(Mu[r + b * d], X[q + b * d], acc);
+            Wt[r + q * ld] = acc;
+        }
+    }
+    // ---- polynomial: the five dependency levels of the Paterson-Stockmeyer scheme; the forward
+    //      tangents of ALL drive directions advance in the same barrier steps ----
+    x.level = 0;
+    sm_run_one<D, QCB_P1, 0, false>(x, c_P1);                                           // A2
+    if (tang) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P5, 0, false>(x, c_P5); }   // dA2_j
+    __syncthreads();
+    sm_run_one<D, QCB_P1, 1, false>(x, c_P1);                                           // A3
+    sm_run_one<D, QCB_P1, 2, false>(x, c_P1);                                           // A4
+    if (tang) for (int j = 0; j < m; ++j) {
+        x.j = j;
+        sm_run_one<D, QCB_P5, 1, false>(x, c_P5);                                       // dA3_j
+        sm_run_one<D, QCB_P5, 2, false>(x, c_P5);                                       // dA4_j
+    }
+    __syncthreads();
+    sm_run_one<D, QCB_P1, 3, false>(x, c_P1);                                           // Z2
+    if (tang) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P5, 3, false>(x, c_P5); }   // dZ2_j
+    __syncthreads();
+    sm_run_one<D, QCB_P1, 4, false>(x, c_P1);                                           // Z1
+    if (tang) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P5, 4, false>(x, c_P5); }   // dZ1_j
+    __syncthreads();
+    sm_run_one<D, QCB_P1, 5, false>(x, c_P1);                                           // E[0]
+    if (tang) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P5, 5, false>(x, c_P5); }   // L_j
+    __syncthreads();
+    // ---- squarings (Jacobian-only calls advance L_j in the same steps) ----
+    for (int l = 0; l < s; ++l) {
+        x.level = l;
+        sm_run_one<D, QCB_P2, 0, false>(x, c_P2);
+        if (tang && !want_hess) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P7L, 0, false>(x, c_P7L); }
+        __syncthreads();
+        if (tang && !want_hess) x.lcur ^= 1;
+    }
     const double *E = x.E + s * msz;
 
     // ---- defect ----
@@ -414,63 +542,29 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
         double *o = p.E_out + (long long)ug * dd;
         for (int e = e0; e < dd; e += tpu) o[e] = E[(e % d) + (e / d) * ld];
     }
-    if (!want_jac && !want_hess) return;
+    if (!tang) return;
 
-    double *Wt = x.W + s * msz;
     if (want_hess) {
-        for (int e = e0; e < dd; e += tpu) {   // W = M X^T
-            const int r = e % d, q = e / d;
-            double acc = 0.0;
-            for (int b = 0; b < c; ++b) acc = fma(Mu[r + b * d], X[q + b * d], acc);
-            Wt[r + q * ld] = acc;
-        }
-        __syncthreads();
+        // adjoint weight chain, reverse sweep of the polynomial (AB4 and AB3 share a step)
         for (int l = s - 1; l >= 0; --l) { x.level = l; sm_run_one<D, QCB_P3, 0>(x, c_P3); }
         x.level = 0;
-        sm_run_table<D, QCB_P4, 5>(x, c_P4);
-    }
-    // ---- per-direction first-order tangents ----
-    for (int j = 0; j < m; ++j) {
-        x.j = j; x.level = 0;
-        sm_run_table<D, QCB_P5, 6>(x, c_P5);
-    }
-    // ---- second order at the polynomial level: U_j = Xdot_j^T Nbar per product node, then
-    //      C[j][i] += <U_j, Ydot_i> ----
-    if (want_hess) {
-        auto node = [&](auto O) {
-            constexpr int o = decltype(O)::value;
-            for (int j = 0; j < m; ++j) {
-                x.j = j; x.level = 0;
-                sm_run_one<D, QCB_P6, o>(x, c_P6);
-                const double *U = x.dtemp + qcb_dtemp(QR_U) * msz;
-                x.j = 0;     // partner of direction i = partner of direction 0 + i * msz
-                constexpr int partner = QCB_P6_PARTNER[o];
-                sm_dot_multi(U, sm_resolve(x, partner), msz, nullptr, m, d, ld, e0, tpu, red, Hacc + j * m);
-            }
-        };
-        node(std::integral_constant<int, 0>{});
-        node(std::integral_constant<int, 1>{});
-        node(std::integral_constant<int, 2>{});
-        node(std::integral_constant<int, 3>{});
-    }
-    // ---- squaring levels ----
-    for (int l = 0; l < s; ++l) {
-        x.level = l;
-        if (want_hess) {
-            for (int j = 0; j < m; ++j) {
-                x.j = j;
-                sm_run_one<D, QCB_P7U, 0>(x, c_P7U);
-                const double *U = x.dtemp + qcb_dtemp(QR_U) * msz;
-                sm_dot_multi(U, x.L, msz, Lidx, m, d, ld, e0, tpu, red, Hacc + j * m);
-            }
-        }
-        for (int j = 0; j < m; ++j) {
-            x.j = j;
-            sm_run_one<D, QCB_P7L, 0>(x, c_P7L);
-            if (threadIdx.x == 0) { int old = Lidx[j]; Lidx[j] = Lidx[m]; Lidx[m] = old; }
+        sm_run_one<D, QCB_P4, 0>(x, c_P4);                                              // ZB1
+        sm_run_one<D, QCB_P4, 1>(x, c_P4);                                              // ZB2
+        sm_run_one<D, QCB_P4, 2, false>(x, c_P4);                                       // AB4
+        sm_run_one<D, QCB_P4, 3>(x, c_P4);                                              // AB3
+        sm_run_one<D, QCB_P4, 4>(x, c_P4);                                              // AB2
+        // second order at the polynomial level: fused product + contraction, nothing stored
+        for (int j = 0; j < m; ++j) sm_p6_pass<D>(x, j, c_P6, red, Hacc + j * m);
+        // squaring levels: contraction against W[l+1], then all L_j advance in one step
+        for (int l = 0; l < s; ++l) {
+            for (int j = 0; j < m; ++j) sm_level_pass<D>(x, j, l, c_P7U, red, Hacc + j * m);
+            x.level = l;
+            for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P7L, 0, false>(x, c_P7L); }
             __syncthreads();
+            x.lcur ^= 1;
         }
     }
+    const double *Lfin = x.L + (long long)x.lcur * m * msz;     // L_j of the last level, j-major
     // ---- final blocks ----
     double *GE = x.fixed + QR_A2 * msz, *WE = x.fixed + QR_A3 * msz, *GW = x.fixed + QR_A4 * msz;
     for (int e = e0; e < dd; e += tpu) {
@@ -489,12 +583,12 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     }
     __syncthreads();
     double *JU = JA + dd, *JT = JU + m * dc;
-    for (int j = 0; j < m; ++j) sm_panel(JU + j * dc, x.L + Lidx[j] * msz, 0, X, d, ld, c, -tau, e0, tpu);
+    for (int j = 0; j < m; ++j) sm_panel(JU + j * dc, Lfin + j * msz, 0, X, d, ld, c, -tau, e0, tpu);
     sm_panel(JT, GE, 0, X, d, ld, c, -1.0, e0, tpu);
     if (e0 == 0) { JT[dc] = 0.0; JT[dc + 1] = 1.0; }
     if (want_hess) {
         double *HXU = HA, *HXT = HA + m * dc, *HUU = HXT + dc, *HUT = HUU + m * m, *HTT = HUT + m;
-        for (int j = 0; j < m; ++j) sm_panel(HXU + j * dc, x.L + Lidx[j] * msz, 1, Mu, d, ld, c, -tau, e0, tpu);
+        for (int j = 0; j < m; ++j) sm_panel(HXU + j * dc, Lfin + j * msz, 1, Mu, d, ld, c, -tau, e0, tpu);
         sm_panel(HXT, GE, 1, Mu, d, ld, c, -1.0, e0, tpu);
         __syncthreads();                                  // Hacc complete (written by e0 == 0 lanes)
         for (int e = e0; e < m * m; e += tpu) {
@@ -503,7 +597,7 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
         }
         for (int j = 0; j < m; ++j) {
             double c1 = sm_dot(WE, Gs + j * msz, d, ld, e0, tpu, red);
-            double c2 = sm_dot(GW, x.L + Lidx[j] * msz, d, ld, e0, tpu, red);
+            double c2 = sm_dot(GW, Lfin + j * msz, d, ld, e0, tpu, red);
             if (e0 == 0) HUT[j] = -(c1 + tau * c2);
         }
         double c3 = sm_dot(GW, GE, d, ld, e0, tpu, red);
