@@ -1292,11 +1292,11 @@ qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu, double 
         CK(cudaEventRecord(h->ev[1], h->stream));
         HostOut ho{delta, jac, hess, compact};
         int want = (jac ? 1 : 0) | (hess ? 2 : 0);
-        // in compact mode no device COO buffer exists: a non-null tag keeps the "wanted" logic uniform
-        double *tag = reinterpret_cast<double *>(uintptr_t(8));
+        // in compact mode no device COO buffer exists (the arenas travel instead): `want` alone says
+        // what is evaluated
         qcb_status st = eval_device(h, h->dZ, hess ? h->dmu : nullptr, h->d_delta,
-                                    jac ? (compact ? tag : h->d_jac) : nullptr,
-                                    hess ? (compact ? tag : h->d_hess) : nullptr, want, &ho);
+                                    (jac && !compact) ? h->d_jac : nullptr, (hess && !compact) ? h->d_hess : nullptr,
+                                    want, &ho);
         CK(cudaEventRecord(h->ev[2], h->stream));
         CK(cudaEventSynchronize(h->ev[2]));
         float a = 0, b = 0;
