@@ -393,3 +393,24 @@ def test_odd_shapes_and_general_generators(d, c, m, S, built_libs):
     d0, j0, h0 = ref(oracle_layout(L), G0, Gd, Z.reshape(-1), mu)
     assert rel_err(d1, d0) < TOL and rel_err(j1, j0) < TOL and rel_err(h1, h0) < TOL
     ev.close()
+
+
+@pytest.mark.parametrize("d,m", [(6, 17), (40, 17), (128, 18)])
+def test_many_drives(d, m, built_libs):
+    """More than 16 drives: the small-d kernel loops its contraction chunks, the large-d path falls
+    back from the 16 x 16 DMMA contraction to the generic one."""
+    rng = np.random.default_rng(d + m)
+    N = 3
+    if d == 128:
+        G0, Gd = _random_system(64, m, rng, scale=0.02)      # iso structure -> half-storage path
+    else:
+        G0 = 0.2 * rng.normal(size=(1, d, d)) / np.sqrt(d)
+        Gd = 0.2 * rng.normal(size=(1, m, d, d)) / np.sqrt(d)
+    L = KnotLayout.smooth_pulse(d, 1, m, N, with_derivatives=False)
+    Z = rng.normal(size=(N, L.z_dim)); Z[:, L.dt_off] = 0.4; Z[:, L.u_off:L.u_off + m] *= 0.2
+    mu = rng.normal(size=L.K * L.x_dim)
+    ev = Evaluator(L, G0, Gd)
+    d1, j1, h1 = ev.eval_all(Z.reshape(-1), mu)
+    d0, j0, h0 = P.evaluate(oracle_layout(L), G0, Gd, Z.reshape(-1), mu)
+    assert rel_err(d1, d0) < TOL and rel_err(j1, j0) < TOL and rel_err(h1, h0) < TOL
+    ev.close()
