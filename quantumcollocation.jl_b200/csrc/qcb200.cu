@@ -95,6 +95,7 @@ struct qcb_handle_s {
     double *sc_H = nullptr, *sc_c1 = nullptr, *sc_c2 = nullptr, *sc_c3 = nullptr, *sc_tau = nullptr, *sc_ntau = nullptr;
     int small_threads = 0;
     double *d_Eall = nullptr, *d_states = nullptr, *d_xinit = nullptr;   // rollout buffers
+    double *d_ja_all = nullptr, *d_ha_all = nullptr, *hs_ja = nullptr, *hs_ha = nullptr;   // small-d compact host route
     // compact host transfer: arenas (not expanded COO vectors) cross PCIe, the host cores expand
     std::vector<uint32_t> h_jcode, h_hcode;           // host copies of the code tables [S][nnz]
     std::vector<std::vector<Seg>> jsegs, hsegs;       // per system
@@ -613,6 +614,7 @@ void ensure_scratch(qcb_handle_s *h, int s_need) {
 }
 
 struct HostOut { double *delta, *jac, *hess; bool compact; };
+void ensure_out(qcb_handle_s *h, double **p, size_t n);
 
 // norm pre-pass over the whole slab -> uniform number of squarings (or -1)
 int slab_squarings(qcb_handle_s *h, const double *dZ) {
@@ -847,9 +849,11 @@ void launch_small(qcb_handle_s *h, const SmallParams &p, size_t smem) {
 }
 
 void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_delta, double *d_jac,
-                double *d_hess, int want, int s, double *E_out = nullptr) {
+                double *d_hess, int want, int s, double *E_out = nullptr, bool arenas = false) {
     SmallParams p;
     p.E_out = E_out;
+    p.ja_out = arenas ? h->d_ja_all : nullptr; p.ha_out = arenas ? h->d_ha_all : nullptr;
+    p.ja_stride = h->JA; p.ha_stride = h->HA;
     p.d = h->d; p.c = h->c; p.m = h->m; p.z_dim = h->z_dim; p.u_off = h->u_off; p.dt_off = h->dt_off;
     p.K = h->K; p.nk = h->nk; p.k_begin = h->k0; p.S = h->S; p.units = h->units;
     p.x_off = h->d_xoff; p.G0 = h->dG0; p.Gd = h->dGd; p.Z = dZ; p.mu = dmu;
@@ -896,10 +900,27 @@ qcb_status eval_device(qcb_handle_s *h, const double *dZ, const double *dmu, dou
         // No norm pre-pass on the small-d path: the kernel sizes its squaring chains for the count
         // seen by the previous call, reports the count it needs, and is re-run once if that was
         // not enough (rare: the count only changes when ||dt*G(u)||_1 crosses a power of two).
+        // compact host route when the COO vectors are much larger than the distinct values
+        // (dense-x Jacobians): the arenas cross PCIe, the host cores expand them
+        const bool compact = host && host->compact;
+        if (compact) {
+            ensure_out(h, &h->d_ja_all, (size_t)h->units * h->JA);
+            ensure_out(h, &h->d_ha_all, (size_t)h->units * h->HA);
+            if (!h->hs_ja) CK(cudaMallocHost(&h->hs_ja, (size_t)h->units * h->JA * 8));
+            if (!h->hs_ha) CK(cudaMallocHost(&h->hs_ha, (size_t)h->units * h->HA * 8));
+            if (h->jsegs.empty()) {
+                h->jsegs.resize(h->S);
+                for (int s2 = 0; s2 < h->S; ++s2) h->jsegs[s2] = build_segments(h->h_jcode.data() + (size_t)s2 * h->jnnz_unit, h->jnnz_unit);
+            }
+            if (h->hsegs.empty()) {
+                h->hsegs.resize(h->S);
+                for (int s2 = 0; s2 < h->S; ++s2) h->hsegs[s2] = build_segments(h->h_hcode.data() + (size_t)s2 * h->hnnz_unit, h->hnnz_unit);
+            }
+        }
         int cap = std::min(h->s_hint, QCB_MAX_SQUARINGS);
         for (int attempt = 0;; ++attempt) {
             CK(cudaMemsetAsync(h->d_bad, 0, 2 * sizeof(int), h->stream));
-            eval_small(h, dZ, dmu, d_delta, d_jac, d_hess, want, cap, E_out);
+            eval_small(h, dZ, dmu, d_delta, compact ? nullptr : d_jac, compact ? nullptr : d_hess, want, cap, E_out, compact);
             CK(cudaMemcpyAsync(h->h_flags, h->d_bad, 2 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
             CK(cudaStreamSynchronize(h->stream));
             if (h->h_flags[0] & 1) { h->err = range_msg; return QCB_ERR_RANGE; }
@@ -909,13 +930,25 @@ qcb_status eval_device(qcb_handle_s *h, const double *dZ, const double *dmu, dou
         }
         h->s_hint = std::max(h->h_flags[1], 0);
         if (host) {
+            const bool wj = (want & 1) && host->jac, wh = (want & 2) && host->hess;
             if (host->delta)
                 CK(cudaMemcpyAsync(host->delta, d_delta, (size_t)h->units * h->xdim * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)h->units * h->xdim * 8);
-            if ((want & 1) && host->jac)
-                CK(cudaMemcpyAsync(host->jac, d_jac, (size_t)h->units * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)h->units * h->jnnz_unit * 8);
-            if ((want & 2) && host->hess)
-                CK(cudaMemcpyAsync(host->hess, d_hess, (size_t)h->units * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)h->units * h->hnnz_unit * 8);
-            CK(cudaStreamSynchronize(h->copy_stream));
+            if (compact) {
+                if (wj) { CK(cudaMemcpyAsync(h->hs_ja, h->d_ja_all, (size_t)h->units * h->JA * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)h->units * h->JA * 8; }
+                if (wh) { CK(cudaMemcpyAsync(h->hs_ha, h->d_ha_all, (size_t)h->units * h->HA * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)h->units * h->HA * 8; }
+                CK(cudaStreamSynchronize(h->copy_stream));
+                ExpandJob jobs[2];
+                int nj = 0;
+                if (wj) jobs[nj++] = {&h->jsegs, h->hs_ja, h->JA, host->jac, h->jnnz_unit};
+                if (wh) jobs[nj++] = {&h->hsegs, h->hs_ha, h->HA, host->hess, h->hnnz_unit};
+                if (nj > 0) expand_units(jobs, nj, h->nk, 0, h->units);
+            } else {
+                if (wj)
+                    CK(cudaMemcpyAsync(host->jac, d_jac, (size_t)h->units * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)h->units * h->jnnz_unit * 8);
+                if (wh)
+                    CK(cudaMemcpyAsync(host->hess, d_hess, (size_t)h->units * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)h->units * h->hnnz_unit * 8);
+                CK(cudaStreamSynchronize(h->copy_stream));
+            }
         }
         return QCB_OK;
     }
@@ -1095,10 +1128,12 @@ void qcb_destroy(qcb_handle h) {
     cudaSetDevice(h->device);
     free_scratch(h);
     void *ptrs[] = {h->dG0, h->dGd, h->d_xoff, h->d_jcode, h->d_hcode, h->d_norm, h->d_bad, h->dZ, h->dmu, h->d_delta, h->d_jac, h->d_hess,
-                    h->d_Eall, h->d_states, h->d_xinit};
+                    h->d_Eall, h->d_states, h->d_xinit, h->d_ja_all, h->d_ha_all};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (h->h_flags) cudaFreeHost(h->h_flags);
+    if (h->hs_ja) cudaFreeHost(h->hs_ja);
+    if (h->hs_ha) cudaFreeHost(h->hs_ha);
     for (auto &e : h->ev)
         if (e) cudaEventDestroy(e);
     for (auto &e : h->chunk_events) cudaEventDestroy(e);
@@ -1270,7 +1305,9 @@ qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu, double 
         const size_t nz = (size_t)h->N * h->z_dim, nmu = (size_t)h->S * h->K * h->xdim;
         // large-d path: send the compact value arenas over PCIe and expand on the host cores
         // (QCB_E2E_DIRECT=1 restores device-side assembly + full-size D2H)
-        const bool compact = h->large && (jac || hess) && !getenv("QCB_E2E_DIRECT");
+        // (small-d path: only when the COO vectors are >= 4x larger than the arenas, e.g. dense-x Jacobians)
+        const bool compact = (jac || hess) && !getenv("QCB_E2E_DIRECT") &&
+                             (h->large || (h->jnnz_unit + h->hnnz_unit) >= 4 * (h->JA + h->HA));
         ensure_out(h, &h->dZ, nz);
         ensure_out(h, &h->d_delta, (size_t)h->units * h->xdim);
         if (jac && !compact) ensure_out(h, &h->d_jac, (size_t)h->units * h->jnnz_unit);

@@ -32,6 +32,8 @@ struct SmallParams {
     long long jnnz, hnnz;
     int want;                       // bit0 jac, bit1 hess
     double *E_out;                  // optional [units][d*d]: the propagator of every unit (rollouts)
+    double *ja_out, *ha_out;        // optional [units][ja_stride / ha_stride]: the value arenas instead of the COO vectors
+    long long ja_stride, ha_stride; //   (compact host transfer: the host cores expand them)
     int smax;                       // chain capacity allocated in shared memory
     int *bad_flag;
 };
@@ -605,6 +607,15 @@ __global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
     }
     __syncthreads();
     if (!live) return;
+    // ---- compact host transfer: hand over the arenas themselves ----
+    if (want_jac && p.ja_out) {
+        double *o = p.ja_out + (long long)ug * p.ja_stride;
+        for (int e = e0; e < dd + (m + 1) * dc + 2; e += tpu) o[e] = JA[e];
+    }
+    if (want_hess && p.ha_out) {
+        double *o = p.ha_out + (long long)ug * p.ha_stride;
+        for (int e = e0; e < (m + 1) * dc + m * m + m + 2; e += tpu) o[e] = HA[e];
+    }
     // ---- coalesced COO stores in the caller's order ----
     if (want_jac && p.jac) {
         const uint32_t *cd = p.jcode + (long long)sys * p.jnnz;
