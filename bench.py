@@ -168,6 +168,7 @@ def main():
     ap.add_argument("--ref-units", type=int, default=None)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-mix", action="store_true", help="skip the per-callback timings (profiling runs)")
     ap.add_argument("--out-mem", default="auto", choices=["auto", "pinned", "pageable"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
@@ -271,12 +272,14 @@ def main():
             fn()
         b.record(st); b.synchronize()
         return max_over_ranks(a.elapsed_time(b)) / reps
-    t_g = timed(lambda: ev.eval_all_device(dZ, None, d_delta, None, None))
-    t_j = timed(lambda: ev.eval_all_device(dZ, None, d_delta, d_jac, None))
-    t_h = timed(lambda: ev.eval_all_device(dZ, dmu, d_delta, None, d_hess))
-    callback_mix = {"eval_g_ms": t_g, "eval_jac_g_ms": t_j, "eval_h_ms": t_h,
-                    "evaluator_ms_per_ipopt_iteration": (55 * t_g + 51 * t_j + 50 * t_h) / 50.0,
-                    "mix": "55 g : 51 jac : 50 hess per 50 iterations (docs/literate/examples/multilevel_transmon.jl:147-153)"}
+    callback_mix = None
+    if not args.no_mix:
+        t_g = timed(lambda: ev.eval_all_device(dZ, None, d_delta, None, None))
+        t_j = timed(lambda: ev.eval_all_device(dZ, None, d_delta, d_jac, None))
+        t_h = timed(lambda: ev.eval_all_device(dZ, dmu, d_delta, None, d_hess))
+        callback_mix = {"eval_g_ms": t_g, "eval_jac_g_ms": t_j, "eval_h_ms": t_h,
+                        "evaluator_ms_per_ipopt_iteration": (55 * t_g + 51 * t_j + 50 * t_h) / 50.0,
+                        "mix": "55 g : 51 jac : 50 hess per 50 iterations (docs/literate/examples/multilevel_transmon.jl:147-153)"}
 
     # ---- N > 1: device-complete on the rank that hosts Ipopt -- every rank's kernels store their
     #      slab straight into rank 0's HBM (CUDA IPC peer mapping, NVLink): the gather is fused ----
