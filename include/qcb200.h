@@ -253,6 +253,27 @@ qcb_status qcb_aux_leakage_eval(qcb_aux a, const double *Z, const double *Qs, do
                                 double *objective, double *grad_vals, double *con_vals, double *con_jac_vals,
                                 double *con_hess_vals);
 
+/* Objective terms around the integrator: quadratic regularisers and the minimum-time
+ * term.  Replaces DirectTrajOpt.QuadraticRegularizer (call sites smooth_pulse_problem.jl:139-152) and
+ * MinimumTimeObjective (minimum_time_problem.jl:84-131):
+ *     J = sum_terms 1/2 sum_{t=1..N} sum_i R_i (dt_t v_{t,i})^2  +  D sum_{t=1..N-1} dt_t
+ * This form reproduces the objective values printed in the reference's solver logs to 1e-14
+ * (docs/literate/examples/multilevel_transmon.jl:139, two_qubit_gates.jl:261) on the solved
+ * trajectories the reference ships (docs/data), see tests/test_reference_fixtures.py.
+ * Terms: component offsets off[i] / sizes dim[i] inside a knot, weights R concatenated.  grad_Z:
+ * [N * z_dim] dense gradient (overwritten).  hess_vals: per knot, {(v,v), (v,dt)} for every regularised
+ * entry then one (dt,dt) value: N * (2 rows + 1) numbers in the order of qcb_aux_regularizer_structure. */
+qcb_status qcb_aux_regularizer_structure(qcb_aux a, int32_t n_terms, const int32_t *off, const int32_t *dim,
+                                         int64_t *hess_rows, int64_t *hess_cols);
+qcb_status qcb_aux_regularizer_eval(qcb_aux a, const double *Z, int32_t n_terms, const int32_t *off,
+                                    const int32_t *dim, const double *R, double min_time_D, double *objective,
+                                    double *grad_Z, double *hess_vals);
+/* TimeStepsAllEqualConstraint (applied by every template, "timesteps all equal constraint" in the
+ * logs; 2 nnz per row = the 98 / 198 of SURVEY.md 8a-a5): rows t = 1..N-1: dt_t - dt_N = 0.
+ * delta [N-1]; Jacobian COO (1-based) and values (+1, -1) [2 (N-1)].  Any output may be NULL. */
+qcb_status qcb_aux_timesteps_equal(qcb_aux a, const double *Z, int64_t row_base, double *delta, int64_t *jac_rows,
+                                   int64_t *jac_cols, double *jac_vals);
+
 #ifdef __cplusplus
 }
 #endif

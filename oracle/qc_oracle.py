@@ -11,17 +11,30 @@ QuantumCollocation.jl delegates to DirectTrajOpt.jl's ``BilinearIntegrator``:
     fidelities  src/quantum_objectives.jl:21-27, 88-103, 173-191
     constraints src/quantum_constraints.jl:20-35, 65-100, 106-121
 
-PARITY UNPINNED: the arithmetic of this path lives in un-vendored Julia
+PARITY STATUS.  The arithmetic of this path lives in un-vendored Julia
 dependencies (DirectTrajOpt.jl 0.8, ExponentialAction.jl 0.2,
 PiccoloQuantumObjects.jl 0.10 -- compat bounds in Project.toml:21-34) and no
-Julia toolchain exists in this image, so this oracle cannot be checked against
-outputs of the reference evaluator itself.  It is pinned only against what the
-reference tree does hold: the iso-vec layout fixture (test/test_utils.jl:52-103),
-the CoherentKetInfidelityObjective known answers (src/quantum_objectives.jl:315-394),
-the structure cardinalities printed in the docs' Ipopt logs
-(docs/literate/examples/multilevel_transmon.jl:105-113, two_qubit_gates.jl:135-143)
-and finite-difference self-consistency (the reference's own ``test_integrator``
-criterion, src/quantum_integrators.jl:194).
+Julia toolchain exists in this image, so the reference evaluator cannot be run
+here.  What the reference tree does hold are OUTPUTS of that evaluator: solved
+trajectories (docs/data/*.jld2) and the Ipopt summaries of the runs that made
+them (docs/literate/examples/multilevel_transmon.jl:139-141,241-243;
+two_qubit_gates.jl:261-263).  tests/test_reference_fixtures.py replays them:
+
+  PINNED against the reference's own output
+    * defect: max|delta| on three solved trajectories equals the logged
+      "Constraint violation" to 6e-12, 2e-12 and 0 (last digit) relative;
+    * objective terms: (subspace) unitary infidelity, quadratic regularisers,
+      minimum-time term and leakage objective reproduce the three logged
+      "Objective" values to <= 1e-14;
+    * iso-vec / knot layout (test/test_utils.jl:52-103), CoherentKet known answers
+      (src/quantum_objectives.jl:315-394), structure cardinalities of the Ipopt logs
+      (multilevel_transmon.jl:105-113, two_qubit_gates.jl:135-143).
+  PARITY UNPINNED (no reference output exists in the tree to compare with)
+    * Jacobian and Hessian-of-Lagrangian VALUES and the DirectTrajOpt 0.8 COO
+      ORDER.  They are derivatives of the pinned defect function and are checked
+      by central differences (the reference's own ``test_integrator`` criterion,
+      src/quantum_integrators.jl:194) and against scipy's expm_frechet; the order
+      is taken from the reference at run time (qcb_set_structure).
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may import
 this module.  The product path (the CUDA library) never does.
@@ -477,3 +490,53 @@ def leakage(Z, N, z_dim, x_off, idx, Qs=None, value=0.0, mu=None):
     cjac = 2 * v
     chess = None if mu is None else 2 * np.asarray(mu).reshape(v.shape)
     return obj, grad, con, cjac, chess
+
+
+def quadratic_regularizer(Z, N, z_dim, dt_off, terms, min_time_D=0.0):
+    """Objective terms around the integrator, in the form the reference's solver logs pin
+    (tests/test_reference_fixtures.py; call sites src/problem_templates/smooth_pulse_problem.jl:139-152,
+    minimum_time_problem.jl:84-131):
+        J = sum_terms 1/2 sum_{t=1..N} sum_i R_i (dt_t v_{t,i})^2 + D sum_{t=1..N-1} dt_t
+    terms: [(offset, dim, R)].  Returns (J, dense gradient [N, z_dim], dense Hessian [N, z_dim, z_dim])."""
+    Zm = np.asarray(Z, dtype=np.float64).reshape(N, z_dim)
+    dt = Zm[:, dt_off]
+    J = float(min_time_D * dt[:-1].sum())
+    grad = np.zeros((N, z_dim))
+    hess = np.zeros((N, z_dim, z_dim))
+    grad[:-1, dt_off] += min_time_D
+    for off, dim, R in terms:
+        R = np.broadcast_to(np.asarray(R, dtype=np.float64), (dim,))
+        for i in range(dim):
+            c = off + i
+            v = Zm[:, c]
+            J += float(0.5 * np.sum(R[i] * (dt * v) ** 2))
+            grad[:, c] += R[i] * dt ** 2 * v
+            grad[:, dt_off] += R[i] * dt * v ** 2
+            hess[:, c, c] += R[i] * dt ** 2
+            hess[:, c, dt_off] += 2 * R[i] * dt * v
+            hess[:, dt_off, c] += 2 * R[i] * dt * v
+            hess[:, dt_off, dt_off] += R[i] * v ** 2
+    return J, grad, hess
+
+
+def timesteps_all_equal(Z, N, z_dim, dt_off):
+    """TimeStepsAllEqualConstraint ("timesteps all equal constraint" in the reference's logs, 2 nnz per
+    row): rows dt_t - dt_N for t < N."""
+    Zm = np.asarray(Z, dtype=np.float64).reshape(N, z_dim)
+    return Zm[:-1, dt_off] - Zm[-1, dt_off]
+
+
+def leakage_indices(subspace, levels):
+    """0-based iso-vec indices of the operator entries that connect the subspace with its complement
+    (row outside & column inside, and row inside & column outside; real and imaginary parts).  This
+    set reproduces the logged objective of the reference's leakage example to 1e-18
+    (docs/literate/examples/multilevel_transmon.jl:241, tests/test_reference_fixtures.py)."""
+    n = levels
+    sub = set(int(s) for s in subspace)
+    idx = []
+    for j in range(n):
+        for part in (0, n):
+            for i in range(n):
+                if (i in sub) != (j in sub):
+                    idx.append(j * 2 * n + part + i)
+    return np.asarray(idx, dtype=np.int64)

@@ -294,6 +294,51 @@ class Aux:
             raise _lib.QcbError(st, "leakage evaluation failed")
         return obj.value, grad, con, cjac, chess
 
+    @staticmethod
+    def _terms(terms):
+        off = np.asarray([t[0] for t in terms], dtype=np.int32)
+        dim = np.asarray([t[1] for t in terms], dtype=np.int32)
+        R = np.concatenate([np.broadcast_to(np.asarray(t[2], dtype=np.float64), (t[1],)) for t in terms]) if terms else np.zeros(0)
+        return off, dim, np.ascontiguousarray(R)
+
+    def regularizer_structure(self, terms):
+        """1-based upper-triangle COO of the objective Hessian of `regularizer_eval` (same order)."""
+        off, dim, _ = self._terms(terms)
+        n = self.N * (2 * int(dim.sum()) + 1)
+        hr, hc = np.empty(n, dtype=np.int64), np.empty(n, dtype=np.int64)
+        ip = lambda a: a.ctypes.data_as(_lib.c_ip) if len(a) else None
+        st = self.lib.qcb_aux_regularizer_structure(self.h, len(dim), ip(off), ip(dim), hr.ctypes.data_as(_lib.c_lp), hc.ctypes.data_as(_lib.c_lp))
+        if st != 0:
+            raise _lib.QcbError(st, "regulariser structure failed")
+        return hr, hc
+
+    def regularizer_eval(self, Z, terms, min_time_D=0.0, want_hessian=True):
+        """terms: [(offset in knot, dim, R scalar or [dim])].  J = sum 1/2 R (dt v)^2 + D sum_{t<N} dt.
+        Returns (J, dense gradient [N*z_dim], Hessian values)."""
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        off, dim, R = self._terms(terms)
+        obj = ctypes.c_double(0.0)
+        grad = np.empty(self.N * self.z_dim)
+        hess = np.empty(self.N * (2 * int(dim.sum()) + 1)) if want_hessian else None
+        ip = lambda a: a.ctypes.data_as(_lib.c_ip) if len(a) else None
+        st = self.lib.qcb_aux_regularizer_eval(self.h, _ptr(Z), len(dim), ip(off), ip(dim), _ptr(R) if len(R) else None,
+                                               float(min_time_D), ctypes.byref(obj), _ptr(grad), _ptr(hess))
+        if st != 0:
+            raise _lib.QcbError(st, "regulariser evaluation failed")
+        return obj.value, grad, hess
+
+    def timesteps_equal(self, Z, row_base=0):
+        """Rows dt_t - dt_N (t < N): (delta, (rows, cols), values)."""
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        K = self.N - 1
+        delta, vals = np.empty(K), np.empty(2 * K)
+        jr, jc = np.empty(2 * K, dtype=np.int64), np.empty(2 * K, dtype=np.int64)
+        st = self.lib.qcb_aux_timesteps_equal(self.h, _ptr(Z), row_base, _ptr(delta), jr.ctypes.data_as(_lib.c_lp),
+                                              jc.ctypes.data_as(_lib.c_lp), _ptr(vals))
+        if st != 0:
+            raise _lib.QcbError(st, "timestep constraint evaluation failed")
+        return delta, (jr, jc), vals
+
     def close(self):
         if getattr(self, "h", None):
             self.lib.qcb_aux_destroy(self.h)

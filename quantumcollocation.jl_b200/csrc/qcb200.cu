@@ -95,6 +95,11 @@ struct qcb_handle_s {
     double *sc_H = nullptr, *sc_c1 = nullptr, *sc_c2 = nullptr, *sc_c3 = nullptr, *sc_tau = nullptr, *sc_ntau = nullptr;
     int small_threads = 0;
     double *d_Eall = nullptr, *d_states = nullptr, *d_xinit = nullptr;   // rollout buffers
+    // sparse drive generators (ELL): products with G_j become gathers
+    bool sparse_drives = false;
+    int ell_w = 0;
+    int *d_ell_idx = nullptr, *d_ellT_idx = nullptr;
+    double *d_ell_val = nullptr, *d_ellT_val = nullptr;
     double *d_ja_all = nullptr, *d_ha_all = nullptr, *hs_ja = nullptr, *hs_ha = nullptr;   // small-d compact host route
     // compact host transfer: arenas (not expanded COO vectors) cross PCIe, the host cores expand
     std::vector<uint32_t> h_jcode, h_hcode;           // host copies of the code tables [S][nnz]
@@ -471,7 +476,46 @@ struct LargeExec {
         }
         g.ident = op.ident >= 0 ? QCB_TAYLOR[op.ident] : 0.0;
         g.dst = reg(op.dst);
-        if (op.nterm == 0) {        // pure linear combination: no tensor work
+        if (h->sparse_drives && op.nterm > 0) {
+            // terms with the drive generator as a factor are gathers (sparse_drive_kernel -> dst);
+            // the remaining dense terms are added by the GEMM through a linear term reading dst back
+            SparseArgs sa;
+            memset(&sa, 0, sizeof(sa));
+            int nd = 0;
+            for (int t = 0; t < op.nterm; ++t) {
+                const bool ga = op.term[t].a == QR_GJ, gb = op.term[t].b == QR_GJ;
+                if ((ga && !op.term[t].tb) || (gb && !op.term[t].ta && !op.term[t].tb)) {
+                    sa.x[sa.nterm] = ga ? g.term[t].b : g.term[t].a;
+                    sa.kind[sa.nterm] = ga ? (op.term[t].ta ? 1 : 0) : 2;
+                    ++sa.nterm;
+                } else {
+                    g.term[nd++] = g.term[t];
+                }
+            }
+            if (sa.nterm > 0 && op.nlin + (nd > 0 ? 1 : 0) <= QCB_MAX_LIN) {
+                sa.dst = g.dst; sa.d = h->dp; sa.ncols = g.N; sa.iso = h->iso ? 1 : 0; sa.W = h->ell_w; sa.m = h->m;
+                sa.ell_idx = h->d_ell_idx; sa.ellT_idx = h->d_ellT_idx; sa.ell_val = h->d_ell_val; sa.ellT_val = h->d_ellT_val;
+                sa.ndir = ndir; sa.unit0_global = u0; sa.nk = h->nk;
+                const dim3 sgrid((unsigned)(nu * ndir)), sblock(128, 2);
+                switch (h->ell_w) {
+                case 1: sparse_drive_kernel<1><<<sgrid, sblock, 0, h->stream>>>(sa); break;
+                case 2: sparse_drive_kernel<2><<<sgrid, sblock, 0, h->stream>>>(sa); break;
+                case 4: sparse_drive_kernel<4><<<sgrid, sblock, 0, h->stream>>>(sa); break;
+                default: sparse_drive_kernel<8><<<sgrid, sblock, 0, h->stream>>>(sa); break;
+                }
+                ++h->launches;
+                CK(cudaGetLastError());
+                if (nd == 0 && op.nlin == 0 && op.ident < 0) return;     // the op was sparse only
+                g.lin[g.nlin] = g.dst; g.lin_coef[g.nlin] = 1.0; ++g.nlin;
+                g.nterm = nd;
+            } else {
+                for (int t = 0; t < op.nterm; ++t) {      // not applicable: restore the dense form
+                    g.term[t].a = reg(op.term[t].a); g.term[t].b = reg(op.term[t].b);
+                    g.term[t].ta = op.term[t].ta; g.term[t].tb = op.term[t].tb;
+                }
+            }
+        }
+        if (g.nterm == 0) {        // pure linear combination: no tensor work
             lincomb_kernel<<<(unsigned)(nu * ndir * (g.N / 8)), 256, 0, h->stream>>>(g);
             ++h->launches;
             CK(cudaGetLastError());
@@ -1107,6 +1151,49 @@ qcb_status qcb_create(qcb_handle *out, const qcb_desc *desc) {
             CK(cudaMemcpy(h->dG0, g0.data(), g0.size() * 8, cudaMemcpyHostToDevice));
             CK(cudaMemcpy(h->dGd, gd.data(), gd.size() * 8, cudaMemcpyHostToDevice));
         }
+        // sparse drive generators -> ELL (large-d path only; unpadded systems)
+        if (h->large && h->dp == h->d && h->m > 0 && !getenv("QCB_DENSE_DRIVES")) {
+            const int d = h->d;
+            int W = 0;
+            for (int s = 0; s < h->S; ++s)
+                for (int j = 0; j < h->m; ++j) {
+                    const double *Gj = desc->G_drives + ((size_t)s * h->m + j) * d * d;
+                    std::vector<int> rown(d, 0), coln(d, 0);
+                    for (int q = 0; q < d; ++q)
+                        for (int r = 0; r < d; ++r)
+                            if (Gj[r + (size_t)q * d] != 0.0) { ++rown[r]; ++coln[q]; }
+                    for (int i = 0; i < d; ++i) W = std::max(W, std::max(rown[i], coln[i]));
+                }
+            if (W >= 1 && W <= 8) {
+                W = W <= 2 ? W : (W <= 4 ? 4 : 8);     // kernel instantiations: 1, 2, 4, 8
+                const size_t tot = (size_t)h->S * h->m * d * W;
+                std::vector<int> idx(tot, 0), idxT(tot, 0);
+                std::vector<double> val(tot, 0.0), valT(tot, 0.0);
+                for (int s = 0; s < h->S; ++s)
+                    for (int j = 0; j < h->m; ++j) {
+                        const double *Gj = desc->G_drives + ((size_t)s * h->m + j) * d * d;
+                        const size_t base = ((size_t)s * h->m + j) * d * W;
+                        std::vector<int> rown(d, 0), coln(d, 0);
+                        for (int q = 0; q < d; ++q)
+                            for (int r = 0; r < d; ++r) {
+                                const double v = Gj[r + (size_t)q * d];
+                                if (v == 0.0) continue;
+                                idx[base + (size_t)r * W + rown[r]] = q; val[base + (size_t)r * W + rown[r]] = v; ++rown[r];
+                                idxT[base + (size_t)q * W + coln[q]] = r; valT[base + (size_t)q * W + coln[q]] = v; ++coln[q];
+                            }
+                    }
+                CK(cudaMalloc(&h->d_ell_idx, tot * sizeof(int)));
+                CK(cudaMalloc(&h->d_ellT_idx, tot * sizeof(int)));
+                CK(cudaMalloc(&h->d_ell_val, tot * 8));
+                CK(cudaMalloc(&h->d_ellT_val, tot * 8));
+                CK(cudaMemcpy(h->d_ell_idx, idx.data(), tot * sizeof(int), cudaMemcpyHostToDevice));
+                CK(cudaMemcpy(h->d_ellT_idx, idxT.data(), tot * sizeof(int), cudaMemcpyHostToDevice));
+                CK(cudaMemcpy(h->d_ell_val, val.data(), tot * 8, cudaMemcpyHostToDevice));
+                CK(cudaMemcpy(h->d_ellT_val, valT.data(), tot * 8, cudaMemcpyHostToDevice));
+                h->ell_w = W;
+                h->sparse_drives = true;
+            }
+        }
         CK(cudaMalloc(&h->d_xoff, h->S * sizeof(int)));
         CK(cudaMemcpy(h->d_xoff, h->x_off.data(), h->S * sizeof(int), cudaMemcpyHostToDevice));
         CK(cudaMalloc(&h->d_norm, sizeof(unsigned long long)));
@@ -1128,7 +1215,8 @@ void qcb_destroy(qcb_handle h) {
     cudaSetDevice(h->device);
     free_scratch(h);
     void *ptrs[] = {h->dG0, h->dGd, h->d_xoff, h->d_jcode, h->d_hcode, h->d_norm, h->d_bad, h->dZ, h->dmu, h->d_delta, h->d_jac, h->d_hess,
-                    h->d_Eall, h->d_states, h->d_xinit, h->d_ja_all, h->d_ha_all};
+                    h->d_Eall, h->d_states, h->d_xinit, h->d_ja_all, h->d_ha_all,
+                    h->d_ell_idx, h->d_ellT_idx, h->d_ell_val, h->d_ellT_val};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (h->h_flags) cudaFreeHost(h->h_flags);

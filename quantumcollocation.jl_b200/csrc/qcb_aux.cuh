@@ -11,6 +11,9 @@ struct qcb_aux_s {
     int *d_leak = nullptr;                         // [n_leak] knot offsets of the leakage entries
     std::vector<int> row_x, row_dx, leak;
     double *dZ = nullptr, *dmu = nullptr, *dQ = nullptr, *dout = nullptr;
+    int *d_reg_off = nullptr;                      // [z_dim-capped rows] regulariser rows of the last call
+    double *d_reg_R = nullptr;
+    size_t reg_cap = 0;
     size_t out_cap = 0;
     cudaStream_t stream = nullptr;
     int64_t launches = 0;
@@ -62,6 +65,60 @@ __global__ void aux_leakage_kernel(const double *Z, const double *Q, const doubl
         for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += red[w];
         obj_terms[t] = q * s / n_leak;
     }
+}
+
+// Quadratic regularisers and the minimum-time term of the objective, one CTA per knot t:
+//   J = sum_rows 1/2 R_r (dt_t v_{t,r})^2  (all N knots)  +  D sum_{t<N} dt_t
+// (the form the reference's solver logs pin: tests/test_reference_fixtures.py).  Per knot:
+//   obj_terms[t]; grad[t][z_dim] (dense, zeroed here first); hess[t][2 rows + 1] =
+//   {(v_r,v_r) = R dt^2, (v_r,dt) = 2 R dt v_r} per row, then (dt,dt) = sum_r R v_r^2.
+__global__ void aux_regularizer_kernel(const double *Z, int N, int z_dim, int dt_off, int rows, const int *row_off,
+                                       const double *row_R, double D, double *obj_terms, double *grad, double *hess) {
+    const int t = blockIdx.x;
+    const double *z = Z + (long long)t * z_dim;
+    const double dt = z[dt_off];
+    double *g = grad ? grad + (long long)t * z_dim : nullptr;
+    if (g) {
+        for (int i = threadIdx.x; i < z_dim; i += blockDim.x) g[i] = 0.0;
+        __syncthreads();
+    }
+    double part = 0.0, gdt = 0.0, hdt = 0.0;
+    for (int r = threadIdx.x; r < rows; r += blockDim.x) {
+        const double v = z[row_off[r]], R = row_R[r];
+        part = fma(0.5 * R * dt * dt, v * v, part);
+        gdt = fma(R * dt, v * v, gdt);
+        hdt = fma(R, v * v, hdt);
+        if (g) atomicAdd(g + row_off[r], R * dt * dt * v);      // two terms may regularise one component
+        if (hess) {
+            double *h = hess + (long long)t * (2 * rows + 1) + 2 * r;
+            h[0] = R * dt * dt; h[1] = 2.0 * R * dt * v;
+        }
+    }
+    __shared__ double red[3][8];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        part += __shfl_xor_sync(0xffffffffu, part, o);
+        gdt += __shfl_xor_sync(0xffffffffu, gdt, o);
+        hdt += __shfl_xor_sync(0xffffffffu, hdt, o);
+    }
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = part; red[1][threadIdx.x >> 5] = gdt; red[2][threadIdx.x >> 5] = hdt; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s0 = 0, s1 = 0, s2 = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { s0 += red[0][w]; s1 += red[1][w]; s2 += red[2][w]; }
+        const bool timed = t < N - 1;
+        if (obj_terms) obj_terms[t] = s0 + (timed ? D * dt : 0.0);
+        if (g) atomicAdd(g + dt_off, s1 + (timed ? D : 0.0));
+        if (hess) hess[(long long)t * (2 * rows + 1) + 2 * rows] = s2;
+    }
+}
+
+// all timesteps equal: rows t = 0..N-2:  dt_t - dt_{N-1} = 0, constant Jacobian (+1, -1)
+__global__ void aux_dt_equal_kernel(const double *Z, int N, int z_dim, int dt_off, double *delta, double *jac) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= N - 1) return;
+    if (delta) delta[t] = Z[(long long)t * z_dim + dt_off] - Z[(long long)(N - 1) * z_dim + dt_off];
+    if (jac) { jac[2 * t] = 1.0; jac[2 * t + 1] = -1.0; }
 }
 
 }  // namespace qcb
@@ -130,7 +187,7 @@ qcb_status qcb_aux_create(qcb_aux *out, const qcb_aux_desc *d) {
 void qcb_aux_destroy(qcb_aux a) {
     if (!a) return;
     cudaSetDevice(a->device);
-    void *ptrs[] = {a->d_row_x, a->d_row_dx, a->d_leak, a->dZ, a->dmu, a->dQ, a->dout};
+    void *ptrs[] = {a->d_row_x, a->d_row_dx, a->d_leak, a->dZ, a->dmu, a->dQ, a->dout, a->d_reg_off, a->d_reg_R};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (a->stream) cudaStreamDestroy(a->stream);
     delete a;
@@ -216,6 +273,114 @@ qcb_status qcb_aux_leakage_eval(qcb_aux a, const double *Z, const double *Qs, do
         if (con_hess_vals) CK(cudaMemcpyAsync(con_hess_vals, dch, n * 8, cudaMemcpyDeviceToHost, a->stream));
         CK(cudaStreamSynchronize(a->stream));
         if (objective) { double s = 0; for (double v : terms) s += v; *objective = s; }   // N knot terms computed on the GPU
+    } catch (const CudaFail &f) {
+        char buf[256];
+        snprintf(buf, sizeof buf, "CUDA error '%s' in %s", cudaGetErrorString(f.e), f.what);
+        a->err = buf; cudaGetLastError();
+        return QCB_ERR_CUDA;
+    }
+    return QCB_OK;
+}
+
+namespace {
+// flattens (off, dim, R) terms into per-row knot offsets and weights; false if a term leaves the knot
+bool aux_reg_rows(qcb_aux a, int32_t n_terms, const int32_t *off, const int32_t *dim, const double *R,
+                  std::vector<int> &ro, std::vector<double> &rr) {
+    size_t w = 0;
+    for (int i = 0; i < n_terms; ++i) {
+        if (dim[i] < 1 || off[i] < 0 || off[i] + dim[i] > a->z_dim) return false;
+        for (int r = 0; r < dim[i]; ++r) { ro.push_back(off[i] + r); rr.push_back(R ? R[w] : 1.0); ++w; }
+    }
+    return true;
+}
+}  // namespace
+
+qcb_status qcb_aux_regularizer_structure(qcb_aux a, int32_t n_terms, const int32_t *off, const int32_t *dim,
+                                         int64_t *hess_rows, int64_t *hess_cols) {
+    if (!a || n_terms < 0 || (n_terms > 0 && (!off || !dim)) || !hess_rows || !hess_cols) return QCB_ERR_ARG;
+    std::vector<int> ro; std::vector<double> rr;
+    if (!aux_reg_rows(a, n_terms, off, dim, nullptr, ro, rr)) { a->err = "regulariser component outside the knot"; return QCB_ERR_ARG; }
+    const int64_t rows = (int64_t)ro.size(), per = 2 * rows + 1;
+    for (int t = 0; t < a->N; ++t) {
+        const int64_t zb = (int64_t)t * a->z_dim, dtc = zb + a->dt_off;
+        for (int64_t r = 0; r < rows; ++r) {
+            const int64_t v = zb + ro[r], e = t * per + 2 * r;
+            hess_rows[e] = v + 1; hess_cols[e] = v + 1;
+            hess_rows[e + 1] = std::min(v, dtc) + 1; hess_cols[e + 1] = std::max(v, dtc) + 1;
+        }
+        hess_rows[t * per + 2 * rows] = dtc + 1; hess_cols[t * per + 2 * rows] = dtc + 1;
+    }
+    return QCB_OK;
+}
+
+qcb_status qcb_aux_regularizer_eval(qcb_aux a, const double *Z, int32_t n_terms, const int32_t *off, const int32_t *dim,
+                                    const double *R, double min_time_D, double *objective, double *grad_Z,
+                                    double *hess_vals) {
+    if (!a || !Z || n_terms < 0 || (n_terms > 0 && (!off || !dim || !R))) return QCB_ERR_ARG;
+    std::vector<int> ro; std::vector<double> rr;
+    if (!aux_reg_rows(a, n_terms, off, dim, R, ro, rr)) { a->err = "regulariser component outside the knot"; return QCB_ERR_ARG; }
+    try {
+        CK(cudaSetDevice(a->device));
+        const size_t rows = ro.size(), N = (size_t)a->N, zd = (size_t)a->z_dim, per = 2 * rows + 1;
+        if (a->reg_cap < std::max<size_t>(rows, 1)) {
+            if (a->d_reg_off) CK(cudaFree(a->d_reg_off));
+            if (a->d_reg_R) CK(cudaFree(a->d_reg_R));
+            a->reg_cap = std::max<size_t>(rows, 1);
+            CK(cudaMalloc(&a->d_reg_off, a->reg_cap * sizeof(int)));
+            CK(cudaMalloc(&a->d_reg_R, a->reg_cap * 8));
+        }
+        if (rows) {
+            CK(cudaMemcpyAsync(a->d_reg_off, ro.data(), rows * sizeof(int), cudaMemcpyHostToDevice, a->stream));
+            CK(cudaMemcpyAsync(a->d_reg_R, rr.data(), rows * 8, cudaMemcpyHostToDevice, a->stream));
+        }
+        CK(cudaMemcpyAsync(a->dZ, Z, N * zd * 8, cudaMemcpyHostToDevice, a->stream));
+        aux_out(a, std::max(N + N * zd + N * per, std::max(4 * (size_t)qcb_aux_leakage_dim(a) + N, 6 * (size_t)qcb_aux_derivative_dim(a))));
+        double *dobj = a->dout, *dg = dobj + N, *dh = dg + N * zd;
+        qcb::aux_regularizer_kernel<<<(unsigned)N, 128, 0, a->stream>>>(a->dZ, a->N, a->z_dim, a->dt_off, (int)rows, a->d_reg_off,
+                                                                       a->d_reg_R, min_time_D, dobj, grad_Z ? dg : nullptr,
+                                                                       hess_vals ? dh : nullptr);
+        ++a->launches;
+        CK(cudaGetLastError());
+        std::vector<double> terms(N);
+        CK(cudaMemcpyAsync(terms.data(), dobj, N * 8, cudaMemcpyDeviceToHost, a->stream));
+        if (grad_Z) CK(cudaMemcpyAsync(grad_Z, dg, N * zd * 8, cudaMemcpyDeviceToHost, a->stream));
+        if (hess_vals) CK(cudaMemcpyAsync(hess_vals, dh, N * per * 8, cudaMemcpyDeviceToHost, a->stream));
+        CK(cudaStreamSynchronize(a->stream));
+        if (objective) { double s = 0; for (double v : terms) s += v; *objective = s; }   // N knot terms computed on the GPU
+    } catch (const CudaFail &f) {
+        char buf[256];
+        snprintf(buf, sizeof buf, "CUDA error '%s' in %s", cudaGetErrorString(f.e), f.what);
+        a->err = buf; cudaGetLastError();
+        return QCB_ERR_CUDA;
+    }
+    return QCB_OK;
+}
+
+qcb_status qcb_aux_timesteps_equal(qcb_aux a, const double *Z, int64_t row_base, double *delta, int64_t *jac_rows,
+                                   int64_t *jac_cols, double *jac_vals) {
+    if (!a) return QCB_ERR_ARG;
+    const int K = a->N - 1;
+    if (jac_rows && jac_cols)
+        for (int t = 0; t < K; ++t) {
+            jac_rows[2 * t] = jac_rows[2 * t + 1] = row_base + t + 1;
+            jac_cols[2 * t] = (int64_t)t * a->z_dim + a->dt_off + 1;
+            jac_cols[2 * t + 1] = (int64_t)K * a->z_dim + a->dt_off + 1;
+        }
+    if (!delta && !jac_vals) return QCB_OK;
+    if (!Z) return QCB_ERR_ARG;
+    try {
+        CK(cudaSetDevice(a->device));
+        const size_t N = (size_t)a->N;
+        CK(cudaMemcpyAsync(a->dZ, Z, N * a->z_dim * 8, cudaMemcpyHostToDevice, a->stream));
+        aux_out(a, 3 * N);
+        double *dd = a->dout, *dj = a->dout + N;
+        qcb::aux_dt_equal_kernel<<<(unsigned)((K + 127) / 128), 128, 0, a->stream>>>(a->dZ, a->N, a->z_dim, a->dt_off,
+                                                                                    delta ? dd : nullptr, jac_vals ? dj : nullptr);
+        ++a->launches;
+        CK(cudaGetLastError());
+        if (delta) CK(cudaMemcpyAsync(delta, dd, (size_t)K * 8, cudaMemcpyDeviceToHost, a->stream));
+        if (jac_vals) CK(cudaMemcpyAsync(jac_vals, dj, (size_t)2 * K * 8, cudaMemcpyDeviceToHost, a->stream));
+        CK(cudaStreamSynchronize(a->stream));
     } catch (const CudaFail &f) {
         char buf[256];
         snprintf(buf, sizeof buf, "CUDA error '%s' in %s", cudaGetErrorString(f.e), f.what);

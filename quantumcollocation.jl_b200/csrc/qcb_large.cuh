@@ -555,6 +555,93 @@ __global__ void __launch_bounds__(256) lincomb_kernel(const __grid_constant__ Ge
 }
 
 // ---------------------------------------------------------------------------------------
+// Products with a sparse drive generator.  The drive Hamiltonians of real devices are Paulis /
+// ladder operators: G_j has a handful of nonzeros per row (the reference itself keeps them as
+// SparseArrays), so G_j*X, G_j^T*X and X*G_j are O(d^2) gathers, not O(d^3) GEMMs.  ELL format:
+// ell_idx / ell_val [S][m][d][W] hold the nonzeros of every row of G_j, ellT_* those of every
+// column (= rows of G_j^T); unused slots have value 0 and index 0.
+// dst = sum of up to two such terms (iso half storage or full storage); a following GEMM adds the
+// op's dense terms on top through a linear term that reads dst back.
+// ---------------------------------------------------------------------------------------
+struct SparseArgs {
+    Opnd dst, x[2];
+    int kind[2];            // 0: G_j * X   1: G_j^T * X   2: X * G_j
+    int nterm;
+    int d, ncols, iso;      // rows, stored columns (d or d/2), iso half storage?
+    int W, m;
+    const int *ell_idx, *ellT_idx;
+    const double *ell_val, *ellT_val;
+    int ndir, unit0_global, nk;
+};
+// Block (128, 2): x walks the rows, y the columns, so no index is ever divided; the row's ELL entries
+// are loaded once, and eight columns per pass keep eight independent gathers in flight.
+template <int W>
+__global__ void __launch_bounds__(256) sparse_drive_kernel(const __grid_constant__ SparseArgs g) {
+    const int unit = blockIdx.x / g.ndir, dir = blockIdx.x % g.ndir;
+    const int sys = (g.unit0_global + unit) / g.nk;
+    const long long ou = unit, od = dir, os = sys;
+    double *__restrict__ dst = const_cast<double *>(g.dst.p) + ou * g.dst.su + od * g.dst.sd + os * g.dst.ss;
+    const long long ell_base = ((long long)sys * g.m + dir) * g.d * W;
+    const int d = g.d, n = d >> 1, ncols = g.ncols, ldd = g.dst.ld;
+    const bool two = g.nterm > 1;
+    const double *__restrict__ X0 = g.x[0].p + ou * g.x[0].su + od * g.x[0].sd + os * g.x[0].ss;
+    const double *__restrict__ X1 = two ? g.x[1].p + ou * g.x[1].su + od * g.x[1].sd + os * g.x[1].ss : X0;
+    const int ld0 = g.x[0].ld, ld1 = g.x[1].ld, k0 = g.kind[0], k1 = two ? g.kind[1] : -1;
+    constexpr int UNR = 8;
+    for (int r = threadIdx.x; r < d; r += blockDim.x) {
+        int li0[W], li1[W];
+        double lv0[W], lv1[W];
+#pragma unroll
+        for (int w = 0; w < W; ++w) {
+            li0[w] = li1[w] = 0; lv0[w] = lv1[w] = 0.0;
+            if (k0 < 2) {
+                li0[w] = __ldg((k0 == 0 ? g.ell_idx : g.ellT_idx) + ell_base + r * W + w);
+                lv0[w] = __ldg((k0 == 0 ? g.ell_val : g.ellT_val) + ell_base + r * W + w);
+            }
+            if (k1 >= 0 && k1 < 2) {
+                li1[w] = __ldg((k1 == 0 ? g.ell_idx : g.ellT_idx) + ell_base + r * W + w);
+                lv1[w] = __ldg((k1 == 0 ? g.ell_val : g.ellT_val) + ell_base + r * W + w);
+            }
+        }
+        for (int c0 = threadIdx.y; c0 < ncols; c0 += UNR * blockDim.y) {
+            double acc[UNR];
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) {
+                const int c = c0 + u * blockDim.y;
+                acc[u] = 0.0;
+                if (c >= ncols) continue;
+                if (k0 < 2) {
+#pragma unroll
+                    for (int w = 0; w < W; ++w) acc[u] = fma(lv0[w], X0[li0[w] + c * ld0], acc[u]);
+                }
+                if (k1 >= 0 && k1 < 2) {
+#pragma unroll
+                    for (int w = 0; w < W; ++w) acc[u] = fma(lv1[w], X1[li1[w] + c * ld1], acc[u]);
+                }
+                if (k0 == 2 || k1 == 2) {       // row r of X_full against column c of G_j
+                    const double *__restrict__ X = (k0 == 2) ? X0 : X1;
+                    const int ldx = (k0 == 2) ? ld0 : ld1;
+#pragma unroll
+                    for (int w = 0; w < W; ++w) {
+                        const int k = __ldg(g.ellT_idx + ell_base + c * W + w);
+                        const double v = __ldg(g.ellT_val + ell_base + c * W + w);
+                        double xv;
+                        if (!g.iso || k < n) xv = X[r + k * ldx];
+                        else xv = (r < n) ? -X[(r + n) + (k - n) * ldx] : X[(r - n) + (k - n) * ldx];
+                        acc[u] = fma(v, xv, acc[u]);
+                    }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) {
+                const int c = c0 + u * blockDim.y;
+                if (c < ncols) dst[r + c * ldd] = acc[u];
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
 // Frobenius contractions  out[unit][j*ni + i] (+)= < P(unit, j), Q(unit|sys, i) >
 // ---------------------------------------------------------------------------------------
 constexpr int CONTRACT_MAXI = 32;

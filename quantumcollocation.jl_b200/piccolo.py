@@ -66,6 +66,21 @@ class NamedTrajectory:
         self.goal = goal or {}
         self.global_dim = 0
 
+    @classmethod
+    def from_jld2(cls, path: str, key: str = "traj") -> "NamedTrajectory":
+        """A trajectory saved by the reference (`save(path, "traj", prob.trajectory)`; the solved
+        examples under docs/data), decoded by quantumcollocation.jl_b200/jld2.py."""
+        from . import jld2
+        t = jld2.named_trajectory(jld2.load(path)[key])
+        order = sorted(t["components"], key=lambda k: t["components"][k][0])
+        traj = cls({k: t["data"][t["components"][k], :] for k in order}, timestep=t["timestep"],
+                   controls=tuple(t["raw"].get("control_names", {}).values()),
+                   goal={k: np.asarray(v) for k, v in t["raw"].get("goal", {}).items()})
+        traj.bounds = t["raw"].get("bounds", {})
+        traj.initial = {k: np.asarray(v) for k, v in t["raw"].get("initial", {}).items()}
+        traj.final = {k: np.asarray(v) for k, v in t["raw"].get("final", {}).items()}
+        return traj
+
     @property
     def datavec(self) -> np.ndarray:
         return np.ascontiguousarray(self.data.T).reshape(-1)
@@ -416,6 +431,71 @@ class LeakageConstraint:
 
     def jacobian_values(self, traj):
         return self.aux.leakage_eval(traj.datavec, None, self.value)[3]
+
+
+def get_iso_vec_leakage_indices(subspace, levels: int) -> np.ndarray:
+    """0-based iso-vec operator indices coupling `subspace` to its complement (both directions, real
+    and imaginary parts) -- the set PiccoloQuantumObjects' helper of this name yields: with it the
+    leakage example's logged objective is reproduced to 1e-18 (tests/test_reference_fixtures.py)."""
+    n = int(levels)
+    sub = set(int(s) for s in subspace)
+    return np.asarray([j * 2 * n + part + i for j in range(n) for part in (0, n) for i in range(n)
+                       if (i in sub) != (j in sub)], dtype=np.int64)
+
+
+class QuadraticRegularizer:
+    """``QuadraticRegularizer(name, traj, R)`` (src/problem_templates/smooth_pulse_problem.jl:139-152):
+    J = 1/2 sum_t (dt_t v_t)' diag(R) (dt_t v_t) over all N knots; R scalar or one weight per entry."""
+
+    def __init__(self, name: str, traj: NamedTrajectory, R, device: int = 0):
+        idx = traj.components[name]
+        self.term = (int(idx[0]), len(idx), R)
+        self.aux = Aux(traj.N, traj.dim, int(traj.components[traj.timestep][0]), device=device)
+
+    def __call__(self, traj):
+        return self.aux.regularizer_eval(traj.datavec, [self.term], want_hessian=False)[0]
+
+    def gradient(self, grad: np.ndarray, traj) -> np.ndarray:
+        grad[:] = self.aux.regularizer_eval(traj.datavec, [self.term], want_hessian=False)[1]
+        return grad
+
+    def hessian_structure(self):
+        return self.aux.regularizer_structure([self.term])
+
+    def hessian_values(self, traj):
+        return self.aux.regularizer_eval(traj.datavec, [self.term])[2]
+
+
+class MinimumTimeObjective:
+    """``MinimumTimeObjective(traj; D)`` (src/problem_templates/minimum_time_problem.jl:84-131):
+    J = D * sum of the first N-1 timesteps."""
+
+    def __init__(self, traj: NamedTrajectory, D: float = 100.0, device: int = 0):
+        self.D = float(D)
+        self.aux = Aux(traj.N, traj.dim, int(traj.components[traj.timestep][0]), device=device)
+
+    def __call__(self, traj):
+        return self.aux.regularizer_eval(traj.datavec, [], self.D, want_hessian=False)[0]
+
+    def gradient(self, grad: np.ndarray, traj) -> np.ndarray:
+        grad[:] = self.aux.regularizer_eval(traj.datavec, [], self.D, want_hessian=False)[1]
+        return grad
+
+
+class TimeStepsAllEqualConstraint:
+    """dt_t - dt_N = 0 for t < N ("timesteps all equal constraint" in the reference's solver logs)."""
+
+    def __init__(self, traj: NamedTrajectory, device: int = 0):
+        self.aux = Aux(traj.N, traj.dim, int(traj.components[traj.timestep][0]), device=device)
+        self.dim = traj.N - 1
+        self.equality = True
+
+    def values(self, traj):
+        return self.aux.timesteps_equal(traj.datavec)[0]
+
+    def jacobian(self, traj, row_base: int = 0):
+        _, rc, vals = self.aux.timesteps_equal(traj.datavec, row_base)
+        return rc, vals
 
 
 # aliases for the old (docs / BASELINE.json) names, SURVEY.md Appendix A

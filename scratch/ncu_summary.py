@@ -3,7 +3,7 @@ import csv, re, subprocess, sys, collections
 def launches(path):
     lines=[l for l in open(path) if not l.startswith('==')]
     rows=[(r['Kernel Name'],float(r['Metric Value'].replace(',',''))) for r in csv.DictReader(lines)]
-    ours=[(n,v) for n,v in rows if any(k in n for k in ['bgemm','contract','build_G','prep_unit','finalize','arena','assemble','delta_kernel','iso_project','iso_expand','lincomb','extract_E','rollout','small_unit','fid_'])]
+    ours=[(n,v) for n,v in rows if any(k in n for k in ['bgemm','contract','build_G','prep_unit','finalize','arena','assemble','delta_kernel','iso_project','iso_expand','lincomb','extract_E','rollout','small_unit','fid_','sparse_drive','aux_'])]
     idx=[i for i,(n,v) in enumerate(ours) if 'build_G' in n and True]
     # last evaluation = from the last norm pre-pass (first build_G of an eval) to the end
     pre=[i for i in idx if i+1 < len(ours) and 'build_G' in ours[i+1][0]]

@@ -82,6 +82,28 @@ def test_cfg5_d128_against_port_and_scipy_spot(built_libs):
     ev.close()
 
 
+@pytest.mark.parametrize("mix,iso", [(1, False), (2, True), (3, True), (3, False), (12, True)])
+def test_d128_drive_sparsity_classes(mix, iso, built_libs):
+    """Large-d path with drive generators of 2, 3 (ELL width 2 / 4: gather products) and 12 nonzeros
+    per row (beyond the ELL limit of 8: dense DMMA products) against the CPU port; iso=False breaks
+    the real-iso block structure of the drift so that the full-storage kernels run."""
+    w = workloads.make("cfg5", N=4)
+    L = w.layout
+    OL = oracle_layout(L)
+    Gd = np.array(w.G_drives)
+    m = Gd.shape[1]
+    mixed = np.stack([sum((0.5 + 0.1 * t) * Gd[0, (j + t) % m] for t in range(mix)) for j in range(m)])[None]
+    assert max(int((g != 0).sum(axis=0).max()) for g in mixed[0]) == mix
+    G0 = np.array(w.G_drift)
+    if not iso:
+        G0[0, 0, 1] += 0.05
+    ev = Evaluator(L, G0, mixed)
+    ref = P.evaluate(OL, G0, mixed, w.Z, w.mu)
+    d1, j1, h1 = ev.eval_all(w.Z, w.mu)
+    assert rel_err(d1, ref[0]) < TOL and rel_err(j1, ref[1]) < TOL and rel_err(h1, ref[2]) < TOL
+    ev.close()
+
+
 # ---- call variants of the ABI ----------------------------------------------------------------------
 def test_separate_callbacks_equal_fused_call(built_libs):
     w = workloads.make("cfg2", N=7)

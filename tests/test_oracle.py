@@ -1,5 +1,6 @@
 """CPU tests: pin the oracle against everything the reference tree holds for this path, and the
-C port against the oracle.  (The reference's evaluator itself cannot run here: parity unpinned.)"""
+C port against the oracle.  (The reference's evaluator itself cannot run here; its logged outputs are replayed in
+tests/test_reference_fixtures.py.)"""
 import json
 import os
 
