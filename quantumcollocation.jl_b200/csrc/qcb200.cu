@@ -100,6 +100,8 @@ struct qcb_handle_s {
     int ell_w = 0;
     int *d_ell_idx = nullptr, *d_ellT_idx = nullptr;
     double *d_ell_val = nullptr, *d_ellT_val = nullptr;
+    double *d_unit_norm = nullptr;            // [units] ||dt G(u)||_1 of the last norm pre-pass
+    std::vector<double> h_unit_norm;
     double *d_ja_all = nullptr, *d_ha_all = nullptr, *hs_ja = nullptr, *hs_ha = nullptr;   // small-d compact host route
     // compact host transfer: arenas (not expanded COO vectors) cross PCIe, the host cores expand
     std::vector<uint32_t> h_jcode, h_hcode;           // host copies of the code tables [S][nnz]
@@ -664,11 +666,17 @@ void ensure_out(qcb_handle_s *h, double **p, size_t n);
 int slab_squarings(qcb_handle_s *h, const double *dZ) {
     CK(cudaMemsetAsync(h->d_norm, 0, sizeof(unsigned long long), h->stream));
     CK(cudaMemsetAsync(h->d_bad, 0, 2 * sizeof(int), h->stream));
-    build_G_kernel<<<h->units, 256, 0, h->stream>>>(h->geom(), dZ, 0, nullptr, 0, h->d_norm, h->d_bad);
+    if (!h->d_unit_norm) {
+        CK(cudaMalloc(&h->d_unit_norm, (size_t)h->units * 8));
+        h->h_unit_norm.resize(h->units);
+    }
+    build_G_kernel<<<h->units, 256, 0, h->stream>>>(h->geom(), dZ, 0, nullptr, 0, h->d_norm, h->d_bad, h->d_unit_norm);
     ++h->launches;
     CK(cudaGetLastError());
     unsigned long long bits = 0;
     int bad = 0;
+    // per-unit norms: every chunk of units takes the squaring count its own members need
+    CK(cudaMemcpyAsync(h->h_unit_norm.data(), h->d_unit_norm, (size_t)h->units * 8, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaMemcpyAsync(&bits, h->d_norm, sizeof(bits), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaMemcpyAsync(&bad, h->d_bad, sizeof(bad), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
@@ -679,8 +687,8 @@ int slab_squarings(qcb_handle_s *h, const double *dZ) {
 }
 
 void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_delta, double *d_jac,
-                double *d_hess, int want, const HostOut *host, int s, double *E_out = nullptr) {
-    ensure_scratch(h, s);
+                double *d_hess, int want, const HostOut *host, int s_slab, double *E_out = nullptr) {
+    ensure_scratch(h, s_slab);
     const bool wj = want & 1, wh = (want & 2) && dmu;
     const long long dd = h->msz, pan = (long long)h->dp * h->cp;
     const int m = h->m;
@@ -716,6 +724,14 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     size_t chunk_idx = 0;
     for (int u0 = 0; u0 < h->units; u0 += chunk_step, ++chunk_idx) {
         const int nu = std::min(chunk_step, h->units - u0);
+        // squarings of this chunk: what the largest ||dt G(u)||_1 among its units needs (smooth pulses
+        // have slowly varying norms, so quiet stretches of the trajectory skip levels the peaks need)
+        int s = s_slab;
+        if ((int)h->h_unit_norm.size() == h->units && !getenv("QCB_UNIFORM_SQUARINGS")) {
+            double mx = 0.0;
+            for (int u = u0; u < u0 + nu; ++u) mx = std::max(mx, h->h_unit_norm[u]);
+            s = std::min(s_slab, std::max(0, qcb_squarings(mx)));
+        }
         LargeExec X{h, nu, u0, s};
         X.dd = dd; X.pan = pan;
         const int buf = compact ? (int)(chunk_idx & 1) : 0;
@@ -1216,7 +1232,7 @@ void qcb_destroy(qcb_handle h) {
     free_scratch(h);
     void *ptrs[] = {h->dG0, h->dGd, h->d_xoff, h->d_jcode, h->d_hcode, h->d_norm, h->d_bad, h->dZ, h->dmu, h->d_delta, h->d_jac, h->d_hess,
                     h->d_Eall, h->d_states, h->d_xinit, h->d_ja_all, h->d_ha_all,
-                    h->d_ell_idx, h->d_ellT_idx, h->d_ell_val, h->d_ellT_val};
+                    h->d_ell_idx, h->d_ellT_idx, h->d_ell_val, h->d_ellT_val, h->d_unit_norm};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (h->h_flags) cudaFreeHost(h->h_flags);

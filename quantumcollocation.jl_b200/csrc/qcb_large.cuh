@@ -745,7 +745,7 @@ struct UnitGeom {
 // folded into a global max (norm as ordered-uint64 bits; NaN/Inf raise the flag).
 __global__ void __launch_bounds__(256)
 build_G_kernel(UnitGeom q, const double *Z, int u0_global, double *Gout, long long g_stride,
-               unsigned long long *norm_max_bits, int *bad_flag) {
+               unsigned long long *norm_max_bits, int *bad_flag, double *unit_norm = nullptr) {
     const int unit = blockIdx.x, ug = u0_global + unit;
     const int sys = ug / q.nk, k = q.k_begin + ug % q.nk;
     const double *zk = Z + (long long)k * q.z_dim;
@@ -784,6 +784,7 @@ build_G_kernel(UnitGeom q, const double *Z, int u0_global, double *Gout, long lo
         for (int i = 0; i < nwarp; ++i) w = fmax(w, wmax[i]);
         if (!isfinite(w)) atomicExch(bad_flag, 1);
         else atomicMax(norm_max_bits, (unsigned long long)__double_as_longlong(w));
+        if (unit_norm) unit_norm[unit] = w;
     }
 }
 

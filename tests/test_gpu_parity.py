@@ -104,6 +104,28 @@ def test_d128_drive_sparsity_classes(mix, iso, built_libs):
     ev.close()
 
 
+def test_d128_chunks_take_their_own_squaring_count(built_libs, monkeypatch):
+    """Large-d path: with a scratch budget of a few units per chunk and timesteps that grow along the
+    trajectory, successive chunks run 0, 1, 2, ... squaring levels; every unit must still match the port."""
+    monkeypatch.setenv("QCB_SCRATCH_MB", "64")      # the minimum: about 7 units of d = 128 per chunk
+    w = workloads.make("cfg5", N=17)
+    L = w.layout
+    OL = oracle_layout(L)
+    Z = w.Z.reshape(L.N, L.z_dim).copy()
+    Z[:, L.dt_off] *= np.linspace(0.3, 6.0, L.N)
+    Z = Z.reshape(-1)
+    ev = Evaluator(L, w.G_drift, w.G_drives)
+    ref = P.evaluate(OL, w.G_drift, w.G_drives, Z, w.mu)
+    d1, j1, h1 = ev.eval_all(Z, w.mu)
+    assert rel_err(d1, ref[0]) < TOL and rel_err(j1, ref[1]) < TOL and rel_err(h1, ref[2]) < TOL
+    # per unit, not only in the block norm: late units have much larger entries than early ones
+    nj, nh = L.jac_nnz_unit, L.hess_nnz_unit
+    for k in range(L.N - 1):
+        assert rel_err(j1[k * nj:(k + 1) * nj], ref[1][k * nj:(k + 1) * nj]) < TOL
+        assert rel_err(h1[k * nh:(k + 1) * nh], ref[2][k * nh:(k + 1) * nh]) < TOL
+    ev.close()
+
+
 # ---- call variants of the ABI ----------------------------------------------------------------------
 def test_separate_callbacks_equal_fused_call(built_libs):
     w = workloads.make("cfg2", N=7)
