@@ -102,6 +102,8 @@ struct qcb_handle_s {
     double *d_ell_val = nullptr, *d_ellT_val = nullptr;
     double *d_unit_norm = nullptr;            // [units] ||dt G(u)||_1 of the last norm pre-pass
     std::vector<double> h_unit_norm;
+    int *d_perm = nullptr;                    // units sorted by squaring count (device-resident calls, S = 1)
+    std::vector<int> h_perm, h_class_end;
     double *d_ja_all = nullptr, *d_ha_all = nullptr, *hs_ja = nullptr, *hs_ha = nullptr;   // small-d compact host route
     // compact host transfer: arenas (not expanded COO vectors) cross PCIe, the host cores expand
     std::vector<uint32_t> h_jcode, h_hcode;           // host copies of the code tables [S][nnz]
@@ -721,15 +723,48 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         const long long small = std::max(1LL, 6 * slots / std::max<long long>(1, (long long)std::max(1, h->m) * tiles));
         chunk_step = (int)std::min<long long>(h->chunk_units, small);
     }
-    size_t chunk_idx = 0;
-    for (int u0 = 0; u0 < h->units; u0 += chunk_step, ++chunk_idx) {
-        const int nu = std::min(chunk_step, h->units - u0);
+    // Device-resident calls on one system: visit the units in the order of their squaring count, so
+    // that a chunk never runs levels only a few of its members need (random pulses: most units sit
+    // one level below the largest).  perm maps position -> unit; the kernels that touch Z, mu and
+    // the outputs read it, everything in between works on chunk-local scratch.  Host-complete calls
+    // are bound by the host cores and keep the natural order (contiguous D2H ranges).
+    const int *perm = nullptr;
+    h->h_class_end.clear();
+    if (!host && !E_out && h->S == 1 && (int)h->h_unit_norm.size() == h->units && !getenv("QCB_UNIFORM_SQUARINGS") &&
+        !getenv("QCB_NO_UNIT_SORT")) {
+        std::vector<int> cls(h->units);
+        int lo = QCB_MAX_SQUARINGS, hi = 0;
+        for (int u = 0; u < h->units; ++u) {
+            cls[u] = std::min(s_slab, std::max(0, qcb_squarings(h->h_unit_norm[u])));
+            lo = std::min(lo, cls[u]); hi = std::max(hi, cls[u]);
+        }
+        if (hi > lo) {
+            h->h_perm.resize(h->units);
+            int p = 0;
+            for (int c = lo; c <= hi; ++c) {
+                for (int u = 0; u < h->units; ++u) if (cls[u] == c) h->h_perm[p++] = u;
+                if (h->h_class_end.empty() || h->h_class_end.back() != p) h->h_class_end.push_back(p);
+            }
+            if (!h->d_perm) CK(cudaMalloc(&h->d_perm, (size_t)h->units * sizeof(int)));
+            CK(cudaMemcpyAsync(h->d_perm, h->h_perm.data(), (size_t)h->units * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+            perm = h->d_perm;
+        }
+    }
+    size_t chunk_idx = 0, class_idx = 0;
+    int nu_next = 0;
+    for (int u0 = 0; u0 < h->units; u0 += nu_next, ++chunk_idx) {
+        int nu = std::min(chunk_step, h->units - u0);
+        if (perm) {     // chunks do not straddle a class boundary
+            while (class_idx < h->h_class_end.size() && h->h_class_end[class_idx] <= u0) ++class_idx;
+            if (class_idx < h->h_class_end.size()) nu = std::min(nu, h->h_class_end[class_idx] - u0);
+        }
+        nu_next = nu;
         // squarings of this chunk: what the largest ||dt G(u)||_1 among its units needs (smooth pulses
         // have slowly varying norms, so quiet stretches of the trajectory skip levels the peaks need)
         int s = s_slab;
         if ((int)h->h_unit_norm.size() == h->units && !getenv("QCB_UNIFORM_SQUARINGS")) {
             double mx = 0.0;
-            for (int u = u0; u < u0 + nu; ++u) mx = std::max(mx, h->h_unit_norm[u]);
+            for (int u = u0; u < u0 + nu; ++u) mx = std::max(mx, h->h_unit_norm[perm ? h->h_perm[u] : u]);
             s = std::min(s_slab, std::max(0, qcb_squarings(mx)));
         }
         LargeExec X{h, nu, u0, s};
@@ -746,10 +781,10 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         // chunk are assembled on the device and DMA'd in full, the rest travel as compact arenas
         const int nd = compact ? std::min(h->part_units, (int)(h->direct_fraction * nu)) : 0;
         Opnd G = X.fixed(QR_G), A = X.fixed(QR_A);
-        build_G_kernel<<<nu, 256, 0, h->stream>>>(q, dZ, u0, const_cast<double *>(G.p), dd, h->d_norm, h->d_bad);
+        build_G_kernel<<<nu, 256, 0, h->stream>>>(q, dZ, u0, const_cast<double *>(G.p), dd, h->d_norm, h->d_bad, nullptr, perm);
         ++h->launches;
         prep_unit_kernel<<<nu, 256, 0, h->stream>>>(q, dZ, wh ? dmu : nullptr, u0, s, G.p, const_cast<double *>(A.p), dd,
-                                                     h->sc_XP, wh ? h->sc_MP : nullptr, pan, h->sc_tau, h->sc_ntau);
+                                                     h->sc_XP, wh ? h->sc_MP : nullptr, pan, h->sc_tau, h->sc_ntau, perm);
         ++h->launches;
         CK(cudaGetLastError());
         Opnd XP = X.mat(h->sc_XP, pan), MP = X.mat(h->sc_MP, pan), EXp = X.mat(h->sc_EX, pan);
@@ -760,7 +795,7 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         Opnd Ef = X.E(s);
         // defect
         X.product(EXp, Ef, 0, XP, 0, h->dp, h->cp, h->dp, 1, 1.0, nullptr);
-        delta_kernel<<<nu, 256, 0, h->stream>>>(q, dZ, h->sc_EX, pan, d_delta, u0);
+        delta_kernel<<<nu, 256, 0, h->stream>>>(q, dZ, h->sc_EX, pan, d_delta, u0, perm);
         ++h->launches;
         if (E_out) {      // rollouts: keep the (unpadded, full) propagator of every unit
             if (h->iso) { iso_expand_kernel<<<nu, 256, 0, h->stream>>>(X.ja, h->JA, h->dp); ++h->launches; }
@@ -833,12 +868,12 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             }
             if (wj && d_jac && !compact) {
                 int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->jnnz_unit / 4096));
-                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ja, h->JA, h->d_jcode, h->jnnz_unit, d_jac, u0, h->nk, cpu, u0);
+                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ja, h->JA, h->d_jcode, h->jnnz_unit, d_jac, u0, h->nk, cpu, u0, perm);
                 ++h->launches;
             }
             if (wh && d_hess && !compact) {
                 int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->hnnz_unit / 4096));
-                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ha, h->HA, h->d_hcode, h->hnnz_unit, d_hess, u0, h->nk, cpu, u0);
+                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ha, h->HA, h->d_hcode, h->hnnz_unit, d_hess, u0, h->nk, cpu, u0, perm);
                 ++h->launches;
             }
             if (compact && nd > 0) {
@@ -1232,7 +1267,7 @@ void qcb_destroy(qcb_handle h) {
     free_scratch(h);
     void *ptrs[] = {h->dG0, h->dGd, h->d_xoff, h->d_jcode, h->d_hcode, h->d_norm, h->d_bad, h->dZ, h->dmu, h->d_delta, h->d_jac, h->d_hess,
                     h->d_Eall, h->d_states, h->d_xinit, h->d_ja_all, h->d_ha_all,
-                    h->d_ell_idx, h->d_ellT_idx, h->d_ell_val, h->d_ellT_val, h->d_unit_norm};
+                    h->d_ell_idx, h->d_ellT_idx, h->d_ell_val, h->d_ellT_val, h->d_unit_norm, h->d_perm};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (h->h_flags) cudaFreeHost(h->h_flags);

@@ -745,8 +745,10 @@ struct UnitGeom {
 // folded into a global max (norm as ordered-uint64 bits; NaN/Inf raise the flag).
 __global__ void __launch_bounds__(256)
 build_G_kernel(UnitGeom q, const double *Z, int u0_global, double *Gout, long long g_stride,
-               unsigned long long *norm_max_bits, int *bad_flag, double *unit_norm = nullptr) {
-    const int unit = blockIdx.x, ug = u0_global + unit;
+               unsigned long long *norm_max_bits, int *bad_flag, double *unit_norm = nullptr,
+               const int *perm = nullptr) {
+    // perm: units sorted by squaring count (single system only); position -> slab-local unit
+    const int unit = blockIdx.x, ug = perm ? perm[u0_global + unit] : u0_global + unit;
     const int sys = ug / q.nk, k = q.k_begin + ug % q.nk;
     const double *zk = Z + (long long)k * q.z_dim;
     const long long dd = q.gsz;
@@ -793,8 +795,8 @@ __global__ void __launch_bounds__(256)
 prep_unit_kernel(UnitGeom q, const double *Z, const double *mu, int u0_global, int s_levels,
                  const double *G, double *A, long long mat_stride,
                  double *XP, double *MP, long long pan_stride,
-                 double *tau_out, double *neg_tau_out) {
-    const int unit = blockIdx.x, ug = u0_global + unit;
+                 double *tau_out, double *neg_tau_out, const int *perm = nullptr) {
+    const int unit = blockIdx.x, ug = perm ? perm[u0_global + unit] : u0_global + unit;
     const int sys = ug / q.nk, kl = ug % q.nk, k = q.k_begin + kl;
     const double *zk = Z + (long long)k * q.z_dim;
     const double tau = ldexp(zk[q.dt_off], -s_levels);
@@ -843,12 +845,13 @@ __global__ void arena_consts_kernel(double *jarena, long long stride, long long 
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 assemble_kernel(const double *arena, long long arena_stride, const uint32_t *code, long long nnz,
-                double *out, int u0_global, int nk, int chunks_per_unit, int out_u0) {
+                double *out, int u0_global, int nk, int chunks_per_unit, int out_u0, const int *perm = nullptr) {
     const int unit = blockIdx.x / chunks_per_unit, chunk = blockIdx.x % chunks_per_unit;
-    const int sys = (u0_global + unit) / nk;
+    const int sys = (perm ? perm[u0_global + unit] : u0_global + unit) / nk;
     const uint32_t *cd = code + (long long)sys * nnz;
     const double *ar = arena + (long long)unit * arena_stride;
-    double *o = out + (long long)(out_u0 + unit) * nnz;   // out_u0: unit index of `out`'s first row
+    // out_u0: unit index of `out`'s first row; with perm the row is the unit's own position
+    double *o = out + (long long)(perm ? perm[out_u0 + unit] : out_u0 + unit) * nnz;
     long long per = (nnz + chunks_per_unit - 1) / chunks_per_unit;
     per += per & 1;                                   // even chunk starts keep 16-byte alignment
     const long long b0 = chunk * per, e1 = (b0 + per < nnz) ? b0 + per : nnz;
@@ -872,8 +875,9 @@ assemble_kernel(const double *arena, long long arena_stride, const uint32_t *cod
 
 // delta = x_{k+1} - (E X)  with EX in a padded panel
 __global__ void __launch_bounds__(256)
-delta_kernel(UnitGeom q, const double *Z, const double *EX, long long pan_stride, double *delta, int u0_global) {
-    const int unit = blockIdx.x, ug = u0_global + unit;
+delta_kernel(UnitGeom q, const double *Z, const double *EX, long long pan_stride, double *delta, int u0_global,
+             const int *perm = nullptr) {
+    const int unit = blockIdx.x, ug = perm ? perm[u0_global + unit] : u0_global + unit;
     const int sys = ug / q.nk, k = q.k_begin + ug % q.nk;
     const double *xn = Z + (long long)(k + 1) * q.z_dim + q.x_off[sys];
     const double *ex = EX + (long long)unit * pan_stride;

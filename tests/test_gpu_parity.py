@@ -123,6 +123,23 @@ def test_d128_chunks_take_their_own_squaring_count(built_libs, monkeypatch):
     for k in range(L.N - 1):
         assert rel_err(j1[k * nj:(k + 1) * nj], ref[1][k * nj:(k + 1) * nj]) < TOL
         assert rel_err(h1[k * nh:(k + 1) * nh], ref[2][k * nh:(k + 1) * nh]) < TOL
+    # device-resident call: the units are visited sorted by squaring count (shuffle the timesteps so
+    # that the sorted order differs from the natural one) and written back to their own rows
+    import torch
+    Zs = Z.reshape(L.N, L.z_dim).copy()
+    Zs[:-1, L.dt_off] = Zs[np.random.default_rng(5).permutation(L.N - 1), L.dt_off]
+    Zs = Zs.reshape(-1)
+    ref = P.evaluate(OL, w.G_drift, w.G_drives, Zs, w.mu)
+    dZ, dmu = torch.from_numpy(Zs).cuda(), torch.from_numpy(w.mu).cuda()
+    dd = torch.empty(ev.defect_dim, dtype=torch.float64, device="cuda")
+    dj = torch.empty(ev.jacobian_nnz, dtype=torch.float64, device="cuda")
+    dh = torch.empty(ev.hessian_nnz, dtype=torch.float64, device="cuda")
+    ev.eval_all_device(dZ, dmu, dd, dj, dh)
+    dd, dj, dh = dd.cpu().numpy(), dj.cpu().numpy(), dh.cpu().numpy()
+    assert rel_err(dd, ref[0]) < TOL
+    for k in range(L.N - 1):
+        assert rel_err(dj[k * nj:(k + 1) * nj], ref[1][k * nj:(k + 1) * nj]) < TOL, k
+        assert rel_err(dh[k * nh:(k + 1) * nh], ref[2][k * nh:(k + 1) * nh]) < TOL, k
     ev.close()
 
 
