@@ -485,28 +485,37 @@ struct LargeExec {
             // the remaining dense terms are added by the GEMM through a linear term reading dst back
             SparseArgs sa;
             memset(&sa, 0, sizeof(sa));
-            int nd = 0;
+            int nd = 0, nleft = 0, nright = 0;
             for (int t = 0; t < op.nterm; ++t) {
                 const bool ga = op.term[t].a == QR_GJ, gb = op.term[t].b == QR_GJ;
-                if ((ga && !op.term[t].tb) || (gb && !op.term[t].ta && !op.term[t].tb)) {
-                    sa.x[sa.nterm] = ga ? g.term[t].b : g.term[t].a;
-                    sa.kind[sa.nterm] = ga ? (op.term[t].ta ? 1 : 0) : 2;
-                    ++sa.nterm;
+                if (ga && !op.term[t].tb && nleft == 0) {                    // G_j X  or  G_j^T X
+                    sa.xl = g.term[t].b;
+                    sa.l_idx = op.term[t].ta ? h->d_ellT_idx : h->d_ell_idx;
+                    sa.l_val = op.term[t].ta ? h->d_ellT_val : h->d_ell_val;
+                    ++nleft;
+                } else if (gb && !op.term[t].ta && !op.term[t].tb && nright == 0) {   // X G_j
+                    sa.xr = g.term[t].a;
+                    sa.r_idx = h->d_ellT_idx; sa.r_val = h->d_ellT_val;
+                    ++nright;
                 } else {
                     g.term[nd++] = g.term[t];
                 }
             }
-            if (sa.nterm > 0 && op.nlin + (nd > 0 ? 1 : 0) <= QCB_MAX_LIN) {
-                sa.dst = g.dst; sa.d = h->dp; sa.ncols = g.N; sa.iso = h->iso ? 1 : 0; sa.W = h->ell_w; sa.m = h->m;
-                sa.ell_idx = h->d_ell_idx; sa.ellT_idx = h->d_ellT_idx; sa.ell_val = h->d_ell_val; sa.ellT_val = h->d_ellT_val;
+            // forms of the program tables: one left term, optionally with the right term (dA2 = G A + A G)
+            if (nleft == 1 && op.nlin + (nd > 0 ? 1 : 0) <= QCB_MAX_LIN) {
+                sa.dst = g.dst; sa.d = h->dp; sa.ncols = g.N; sa.iso = h->iso ? 1 : 0; sa.m = h->m;
                 sa.ndir = ndir; sa.unit0_global = u0; sa.nk = h->nk;
-                const dim3 sgrid((unsigned)(nu * ndir)), sblock(128, 2);
+                const dim3 sgrid((unsigned)(nu * ndir)), sblock(64, 4);
+#define QCB_SPARSE_LAUNCH(W_)                                                                      \
+    if (nright) sparse_drive_kernel<W_, true><<<sgrid, sblock, 0, h->stream>>>(sa);              \
+    else sparse_drive_kernel<W_, false><<<sgrid, sblock, 0, h->stream>>>(sa)
                 switch (h->ell_w) {
-                case 1: sparse_drive_kernel<1><<<sgrid, sblock, 0, h->stream>>>(sa); break;
-                case 2: sparse_drive_kernel<2><<<sgrid, sblock, 0, h->stream>>>(sa); break;
-                case 4: sparse_drive_kernel<4><<<sgrid, sblock, 0, h->stream>>>(sa); break;
-                default: sparse_drive_kernel<8><<<sgrid, sblock, 0, h->stream>>>(sa); break;
+                case 1: QCB_SPARSE_LAUNCH(1); break;
+                case 2: QCB_SPARSE_LAUNCH(2); break;
+                case 4: QCB_SPARSE_LAUNCH(4); break;
+                default: QCB_SPARSE_LAUNCH(8); break;
                 }
+#undef QCB_SPARSE_LAUNCH
                 ++h->launches;
                 CK(cudaGetLastError());
                 if (nd == 0 && op.nlin == 0 && op.ident < 0) return;     // the op was sparse only

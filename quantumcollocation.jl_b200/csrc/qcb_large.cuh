@@ -564,78 +564,81 @@ __global__ void __launch_bounds__(256) lincomb_kernel(const __grid_constant__ Ge
 // op's dense terms on top through a linear term that reads dst back.
 // ---------------------------------------------------------------------------------------
 struct SparseArgs {
-    Opnd dst, x[2];
-    int kind[2];            // 0: G_j * X   1: G_j^T * X   2: X * G_j
-    int nterm;
+    Opnd dst;
+    Opnd xl;                // left term  T * X  : T = G_j (tables ell_*) or G_j^T (tables ellT_*), chosen by the host
+    Opnd xr;                // right term X * G_j (only sparse_drive_kernel<W, true>)
+    const int *l_idx;       // [S][m][d][W] rows of T
+    const double *l_val;
+    const int *r_idx;       // [S][m][d][W] columns of G_j
+    const double *r_val;
     int d, ncols, iso;      // rows, stored columns (d or d/2), iso half storage?
-    int W, m;
-    const int *ell_idx, *ellT_idx;
-    const double *ell_val, *ellT_val;
-    int ndir, unit0_global, nk;
+    int m, ndir, unit0_global, nk;
 };
-// Block (128, 2): x walks the rows, y the columns, so no index is ever divided; the row's ELL entries
-// are loaded once, and eight columns per pass keep eight independent gathers in flight.
-template <int W>
+// dst = T X (+ X G_j).  Block (64, 4): x walks row PAIRS (one 16-byte store per pair and column), y the
+// columns; the pair's ELL entries are loaded once, eight columns per pass keep the gathers in flight.
+// The term kinds are compile-time so that the loop body is a handful of instructions per element
+// (the first version spent ~60 and was issue bound at a third of the HBM write rate).
+template <int W, bool RIGHT>
 __global__ void __launch_bounds__(256) sparse_drive_kernel(const __grid_constant__ SparseArgs g) {
-    const int unit = blockIdx.x / g.ndir, dir = blockIdx.x % g.ndir;
+    const int unit = blockIdx.x / g.ndir, dir = blockIdx.x - unit * g.ndir;
     const int sys = (g.unit0_global + unit) / g.nk;
     const long long ou = unit, od = dir, os = sys;
     double *__restrict__ dst = const_cast<double *>(g.dst.p) + ou * g.dst.su + od * g.dst.sd + os * g.dst.ss;
-    const long long ell_base = ((long long)sys * g.m + dir) * g.d * W;
-    const int d = g.d, n = d >> 1, ncols = g.ncols, ldd = g.dst.ld;
-    const bool two = g.nterm > 1;
-    const double *__restrict__ X0 = g.x[0].p + ou * g.x[0].su + od * g.x[0].sd + os * g.x[0].ss;
-    const double *__restrict__ X1 = two ? g.x[1].p + ou * g.x[1].su + od * g.x[1].sd + os * g.x[1].ss : X0;
-    const int ld0 = g.x[0].ld, ld1 = g.x[1].ld, k0 = g.kind[0], k1 = two ? g.kind[1] : -1;
+    const double *__restrict__ XL = g.xl.p + ou * g.xl.su + od * g.xl.sd + os * g.xl.ss;
+    const double *__restrict__ XR = RIGHT ? g.xr.p + ou * g.xr.su + od * g.xr.sd + os * g.xr.ss : nullptr;
+    const int d = g.d, n = d >> 1, ncols = g.ncols, ldd = g.dst.ld, ldl = g.xl.ld, ldr = g.xr.ld;
+    const int ell_base = (sys * g.m + dir) * d * W;
+    const int *__restrict__ lidx = g.l_idx + ell_base;
+    const double *__restrict__ lval = g.l_val + ell_base;
+    const int *__restrict__ ridx = RIGHT ? g.r_idx + ell_base : nullptr;
+    const double *__restrict__ rval = RIGHT ? g.r_val + ell_base : nullptr;
+    const bool iso = g.iso != 0;
     constexpr int UNR = 8;
-    for (int r = threadIdx.x; r < d; r += blockDim.x) {
-        int li0[W], li1[W];
-        double lv0[W], lv1[W];
+    const int cstep = blockDim.y;
+    for (int r0 = 2 * threadIdx.x; r0 < d; r0 += 2 * blockDim.x) {
+        int ia[W], ib[W];
+        double va[W], vb[W];
 #pragma unroll
         for (int w = 0; w < W; ++w) {
-            li0[w] = li1[w] = 0; lv0[w] = lv1[w] = 0.0;
-            if (k0 < 2) {
-                li0[w] = __ldg((k0 == 0 ? g.ell_idx : g.ellT_idx) + ell_base + r * W + w);
-                lv0[w] = __ldg((k0 == 0 ? g.ell_val : g.ellT_val) + ell_base + r * W + w);
-            }
-            if (k1 >= 0 && k1 < 2) {
-                li1[w] = __ldg((k1 == 0 ? g.ell_idx : g.ellT_idx) + ell_base + r * W + w);
-                lv1[w] = __ldg((k1 == 0 ? g.ell_val : g.ellT_val) + ell_base + r * W + w);
-            }
+            ia[w] = __ldg(lidx + r0 * W + w); va[w] = __ldg(lval + r0 * W + w);
+            ib[w] = __ldg(lidx + (r0 + 1) * W + w); vb[w] = __ldg(lval + (r0 + 1) * W + w);
         }
-        for (int c0 = threadIdx.y; c0 < ncols; c0 += UNR * blockDim.y) {
-            double acc[UNR];
+        // right term, iso half storage: X_full[r, k] for k >= n is -X[r + n, k - n] (r < n) or X[r - n, k - n]
+        const int ra = (r0 < n) ? r0 + n : r0 - n, rb = (r0 + 1 < n) ? r0 + 1 + n : r0 + 1 - n;
+        const double sa = (r0 < n) ? -1.0 : 1.0, sb = (r0 + 1 < n) ? -1.0 : 1.0;
+        for (int c0 = threadIdx.y; c0 < ncols; c0 += UNR * cstep) {
+            double a0[UNR], a1[UNR];
 #pragma unroll
             for (int u = 0; u < UNR; ++u) {
-                const int c = c0 + u * blockDim.y;
-                acc[u] = 0.0;
-                if (c >= ncols) continue;
-                if (k0 < 2) {
-#pragma unroll
-                    for (int w = 0; w < W; ++w) acc[u] = fma(lv0[w], X0[li0[w] + c * ld0], acc[u]);
-                }
-                if (k1 >= 0 && k1 < 2) {
-#pragma unroll
-                    for (int w = 0; w < W; ++w) acc[u] = fma(lv1[w], X1[li1[w] + c * ld1], acc[u]);
-                }
-                if (k0 == 2 || k1 == 2) {       // row r of X_full against column c of G_j
-                    const double *__restrict__ X = (k0 == 2) ? X0 : X1;
-                    const int ldx = (k0 == 2) ? ld0 : ld1;
+                const int c = c0 + u * cstep;
+                a0[u] = a1[u] = 0.0;
+                if (c < ncols) {
+                    const double *__restrict__ xc = XL + c * ldl;
 #pragma unroll
                     for (int w = 0; w < W; ++w) {
-                        const int k = __ldg(g.ellT_idx + ell_base + c * W + w);
-                        const double v = __ldg(g.ellT_val + ell_base + c * W + w);
-                        double xv;
-                        if (!g.iso || k < n) xv = X[r + k * ldx];
-                        else xv = (r < n) ? -X[(r + n) + (k - n) * ldx] : X[(r - n) + (k - n) * ldx];
-                        acc[u] = fma(v, xv, acc[u]);
+                        a0[u] = fma(va[w], xc[ia[w]], a0[u]);
+                        a1[u] = fma(vb[w], xc[ib[w]], a1[u]);
+                    }
+                    if (RIGHT) {
+#pragma unroll
+                        for (int w = 0; w < W; ++w) {
+                            const int k = __ldg(ridx + c * W + w);
+                            const double v = __ldg(rval + c * W + w);
+                            if (!iso || k < n) {
+                                a0[u] = fma(v, XR[r0 + k * ldr], a0[u]);
+                                a1[u] = fma(v, XR[r0 + 1 + k * ldr], a1[u]);
+                            } else {
+                                a0[u] = fma(v * sa, XR[ra + (k - n) * ldr], a0[u]);
+                                a1[u] = fma(v * sb, XR[rb + (k - n) * ldr], a1[u]);
+                            }
+                        }
                     }
                 }
             }
 #pragma unroll
             for (int u = 0; u < UNR; ++u) {
-                const int c = c0 + u * blockDim.y;
-                if (c < ncols) dst[r + c * ldd] = acc[u];
+                const int c = c0 + u * cstep;
+                if (c < ncols) *reinterpret_cast<double2 *>(dst + r0 + c * ldd) = make_double2(a0[u], a1[u]);
             }
         }
     }
