@@ -96,6 +96,7 @@ struct qcb_handle_s {
     int small_threads = 0;
     double *d_Eall = nullptr, *d_states = nullptr, *d_xinit = nullptr;   // rollout buffers
     // sparse drive generators (ELL): products with G_j become gathers
+    bool run_assembly = true;                 // run-based device assembly (QCB_GATHER_ASSEMBLY=1: per-entry gather)
     bool sparse_drives = false;
     int ell_w = 0;
     int *d_ell_idx = nullptr, *d_ellT_idx = nullptr;
@@ -108,6 +109,8 @@ struct qcb_handle_s {
     // compact host transfer: arenas (not expanded COO vectors) cross PCIe, the host cores expand
     std::vector<uint32_t> h_jcode, h_hcode;           // host copies of the code tables [S][nnz]
     std::vector<std::vector<Seg>> jsegs, hsegs;       // per system
+    Piece *d_jpieces = nullptr, *d_hpieces = nullptr; // run-based device assembly: [S][n*pieces]
+    int n_jpieces = 0, n_hpieces = 0;
     double *sc_ja2 = nullptr, *sc_ha2 = nullptr;      // second arena set (double buffering)
     double *stage_j[2] = {nullptr, nullptr}, *stage_h[2] = {nullptr, nullptr};   // pinned
     int stage_units = 0;
@@ -214,6 +217,46 @@ std::vector<Seg> build_segments(const uint32_t *code, int64_t nnz) {
         e += len;
     }
     return v;
+}
+
+// Pieces of at most PIECE entries (QCB_PIECE, default 8192; flat between 4096 and 32768) for assemble_runs_kernel: runs of >= 256 consecutive arena entries
+// become COPY pieces, everything between them is covered by GATHER pieces (through the code table).
+std::vector<Piece> build_pieces(const uint32_t *code, int64_t nnz) {
+    int64_t PIECE = 8192;
+    const int64_t MIN_RUN = 256;
+    if (const char *e = getenv("QCB_PIECE")) PIECE = std::max(512L, atol(e));
+    std::vector<Piece> out;
+    int64_t gather_from = -1;
+    auto flush_gather = [&](int64_t upto) {
+        for (int64_t e = gather_from; gather_from >= 0 && e < upto; e += PIECE)
+            out.push_back({e, 0u, (unsigned)std::min(PIECE, upto - e), 0u, 0u});
+        gather_from = -1;
+    };
+    for (const Seg &sg : build_segments(code, nnz)) {
+        if (!(sg.kind & 2u) && sg.len >= MIN_RUN) {
+            flush_gather(sg.dst);
+            for (int64_t q = 0; q < sg.len; q += PIECE)
+                out.push_back({sg.dst + q, sg.src + (unsigned)q, (unsigned)std::min<int64_t>(PIECE, sg.len - q), (sg.kind & 1u) ? 2u : 1u, 0u});
+        } else if (gather_from < 0) {
+            gather_from = sg.dst;
+        }
+    }
+    flush_gather(nnz);
+    return out;
+}
+
+void upload_pieces(qcb_handle_s *h, const std::vector<uint32_t> &codes, int64_t nnz, Piece **dptr, int *count) {
+    std::vector<std::vector<Piece>> per(h->S);
+    size_t mx = 0;
+    for (int s = 0; s < h->S; ++s) { per[s] = build_pieces(codes.data() + (size_t)s * nnz, nnz); mx = std::max(mx, per[s].size()); }
+    std::vector<Piece> flat((size_t)h->S * mx, Piece{0, 0u, 0u, 0u, 0u});
+    for (int s = 0; s < h->S; ++s) std::copy(per[s].begin(), per[s].end(), flat.begin() + (size_t)s * mx);
+    if (*dptr) { CK(cudaFree(*dptr)); *dptr = nullptr; }
+    if (mx) {
+        CK(cudaMalloc(dptr, flat.size() * sizeof(Piece)));
+        CK(cudaMemcpy(*dptr, flat.data(), flat.size() * sizeof(Piece), cudaMemcpyHostToDevice));
+    }
+    *count = (int)mx;
 }
 
 // dst[0..len) = +-src[0..len) with non-temporal 64-byte stores (the destination is written once
@@ -876,13 +919,25 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
                 ++h->launches;
             }
             if (wj && d_jac && !compact) {
-                int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->jnnz_unit / 4096));
-                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ja, h->JA, h->d_jcode, h->jnnz_unit, d_jac, u0, h->nk, cpu, u0, perm);
+                if (h->run_assembly) {
+                    if (!h->d_jpieces) upload_pieces(h, h->h_jcode, h->jnnz_unit, &h->d_jpieces, &h->n_jpieces);
+                    assemble_runs_kernel<<<(unsigned)((size_t)nu * h->n_jpieces), 256, 0, h->stream>>>(
+                        X.ja, h->JA, h->d_jcode, h->jnnz_unit, h->d_jpieces, h->n_jpieces, d_jac, u0, h->nk, u0, perm);
+                } else {
+                    int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->jnnz_unit / 4096));
+                    assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ja, h->JA, h->d_jcode, h->jnnz_unit, d_jac, u0, h->nk, cpu, u0, perm);
+                }
                 ++h->launches;
             }
             if (wh && d_hess && !compact) {
-                int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->hnnz_unit / 4096));
-                assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ha, h->HA, h->d_hcode, h->hnnz_unit, d_hess, u0, h->nk, cpu, u0, perm);
+                if (h->run_assembly) {
+                    if (!h->d_hpieces) upload_pieces(h, h->h_hcode, h->hnnz_unit, &h->d_hpieces, &h->n_hpieces);
+                    assemble_runs_kernel<<<(unsigned)((size_t)nu * h->n_hpieces), 256, 0, h->stream>>>(
+                        X.ha, h->HA, h->d_hcode, h->hnnz_unit, h->d_hpieces, h->n_hpieces, d_hess, u0, h->nk, u0, perm);
+                } else {
+                    int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->hnnz_unit / 4096));
+                    assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ha, h->HA, h->d_hcode, h->hnnz_unit, d_hess, u0, h->nk, cpu, u0, perm);
+                }
                 ++h->launches;
             }
             if (compact && nd > 0) {
@@ -1133,6 +1188,7 @@ qcb_status qcb_create(qcb_handle *out, const qcb_desc *desc) {
     if (k0 < 0 || k1 > K || k0 >= k1) return fail(nullptr, QCB_ERR_ARG, "bad interval slab [k_begin, k_end)");
 
     qcb_handle_s *h = new qcb_handle_s();
+    h->run_assembly = !getenv("QCB_GATHER_ASSEMBLY");
     try {
         int ndev = 0;
         if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
@@ -1276,7 +1332,7 @@ void qcb_destroy(qcb_handle h) {
     free_scratch(h);
     void *ptrs[] = {h->dG0, h->dGd, h->d_xoff, h->d_jcode, h->d_hcode, h->d_norm, h->d_bad, h->dZ, h->dmu, h->d_delta, h->d_jac, h->d_hess,
                     h->d_Eall, h->d_states, h->d_xinit, h->d_ja_all, h->d_ha_all,
-                    h->d_ell_idx, h->d_ellT_idx, h->d_ell_val, h->d_ellT_val, h->d_unit_norm, h->d_perm};
+                    h->d_ell_idx, h->d_ellT_idx, h->d_ell_val, h->d_ellT_val, h->d_unit_norm, h->d_perm, h->d_jpieces, h->d_hpieces};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (h->h_flags) cudaFreeHost(h->h_flags);
@@ -1387,6 +1443,7 @@ qcb_status qcb_set_structure(qcb_handle h, int64_t row_base, const int64_t *jr, 
             h->custom_j = true;
             h->h_jcode = codes;
             h->jsegs.clear();
+            if (h->d_jpieces) { CK(cudaFree(h->d_jpieces)); h->d_jpieces = nullptr; }
             if (h->d_jac) { CK(cudaFree(h->d_jac)); h->d_jac = nullptr; }
         }
         if (hr && hc && hn > 0) {
@@ -1424,6 +1481,7 @@ qcb_status qcb_set_structure(qcb_handle h, int64_t row_base, const int64_t *jr, 
             h->custom_h = true;
             h->h_hcode = codes;
             h->hsegs.clear();
+            if (h->d_hpieces) { CK(cudaFree(h->d_hpieces)); h->d_hpieces = nullptr; }
             if (h->d_hess) { CK(cudaFree(h->d_hess)); h->d_hess = nullptr; }
         }
     } catch (const CudaFail &f) {
