@@ -627,9 +627,22 @@ void free_scratch(qcb_handle_s *h) {
 }
 
 // buffers of the compact host transfer (second arena set, pinned staging, run-length tables)
+// Units per chunk of a host-complete call.  Those are bound by the host cores' expansion, not by the
+// GPU: small chunks (six full waves of per-drive CTAs) let the first arenas reach the host early, so
+// the expansion pipeline starts after a few milliseconds instead of a third of the evaluation.
+int compact_step(const qcb_handle_s *h) {
+    if (getenv("QCB_E2E_BIG_CHUNKS")) return h->chunk_units;
+    const long long slots = (long long)h->n_sm * (h->iso ? 2 : 1);
+    const long long tiles = h->iso ? (h->dp / 128) : ((h->dp % 128 == 0) ? (long long)(h->dp / 128) * (h->dp / 128)
+                                                                          : (long long)(h->dp / 64) * (h->dp / 64));
+    const long long small = std::max(1LL, 6 * slots / std::max<long long>(1, (long long)std::max(1, h->m) * std::max(1LL, tiles)));
+    return (int)std::min<long long>(h->chunk_units, small);
+}
+
 void ensure_compact(qcb_handle_s *h) {
-    if (h->stage_units != h->chunk_units) {
-        const size_t n = (size_t)h->chunk_units;
+    const int step = compact_step(h);
+    if (h->stage_units != step) {
+        const size_t n = (size_t)step;
         CK(cudaMalloc(&h->sc_ja2, n * (size_t)h->JA * 8));
         CK(cudaMalloc(&h->sc_ha2, n * (size_t)h->HA * 8));
         for (int b = 0; b < 2; ++b) {
@@ -639,12 +652,12 @@ void ensure_compact(qcb_handle_s *h) {
             if (!h->part_done[b]) CK(cudaEventCreateWithFlags(&h->part_done[b], cudaEventDisableTiming));
         }
         if (const char *e = getenv("QCB_DIRECT_FRACTION")) h->direct_fraction = std::min(1.0, std::max(0.0, atof(e)));
-        h->part_units = (int)(h->direct_fraction * h->chunk_units);
+        h->part_units = (int)(h->direct_fraction * step);
         for (int b = 0; b < 2 && h->part_units > 0; ++b) {
             CK(cudaMalloc(&h->part_j[b], (size_t)h->part_units * h->jnnz_unit * 8));
             CK(cudaMalloc(&h->part_h[b], (size_t)h->part_units * h->hnnz_unit * 8));
         }
-        h->stage_units = h->chunk_units;
+        h->stage_units = step;
     }
     if (h->jsegs.empty()) {
         h->jsegs.resize(h->S);
@@ -667,7 +680,16 @@ void ensure_scratch(qcb_handle_s *h, int s_need) {
     if (h->s_cap >= s_need && h->sc_fixed) return;
     free_scratch(h);
     const int s_cap = std::max(s_need, 2);
+    // Scratch budget: a quarter of the free HBM, at most 24 GB (a cfg5 slab of 2000 knots then runs as
+    // one chunk per squaring class: fewer, longer launches -- 37.9 -> 36.2 ms against the former 8 GB).
     size_t budget_mb = 8192;
+    {
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess)
+            budget_mb = std::min<size_t>(24576, std::max<size_t>(512, (free_b >> 20) / 4));
+        else
+            cudaGetLastError();
+    }
     if (const char *e = getenv("QCB_SCRATCH_MB")) budget_mb = (size_t)std::max(64L, atol(e));
     const size_t per = scratch_bytes_per_unit(h, s_cap);
     long long cu = (long long)((budget_mb << 20) / per);
@@ -764,17 +786,7 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         if (nj > 0 && prev_nu > prev_nd) expand_units(jobs, nj, h->nk, prev_u0 + prev_nd, prev_nu - prev_nd);
         prev_u0 = -1;
     };
-    // Host-complete calls are bound by the host cores' expansion, not by the GPU: use small chunks
-    // (six full waves of per-drive CTAs) so that the first arenas reach the host early and the
-    // expansion pipeline starts after a few milliseconds instead of a third of the evaluation.
-    int chunk_step = h->chunk_units;
-    if (compact && !getenv("QCB_E2E_BIG_CHUNKS")) {
-        const long long slots = (long long)h->n_sm * (h->iso ? 2 : 1);
-        const long long tiles = h->iso ? (h->dp / 128) : ((h->dp % 128 == 0) ? (long long)(h->dp / 128) * (h->dp / 128)
-                                                                              : (long long)(h->dp / 64) * (h->dp / 64));
-        const long long small = std::max(1LL, 6 * slots / std::max<long long>(1, (long long)std::max(1, h->m) * tiles));
-        chunk_step = (int)std::min<long long>(h->chunk_units, small);
-    }
+    const int chunk_step = compact ? compact_step(h) : h->chunk_units;
     // Device-resident calls on one system: visit the units in the order of their squaring count, so
     // that a chunk never runs levels only a few of its members need (random pulses: most units sit
     // one level below the largest).  perm maps position -> unit; the kernels that touch Z, mu and
