@@ -103,6 +103,43 @@ B200BilinearIntegrator(q::SamplingTrajectory, traj; kw...) =
     B200BilinearIntegrator(q.systems, state_names(q), drive_name(q), traj,
                            q.base_trajectory isa UnitaryTrajectory ? q.systems[1].levels : 1; kw...)
 
+# Objective terms around the integrator (include/qcb200.h: qcb_aux_*): quadratic regularisers and the
+# minimum-time term in the form the reference's own solver logs pin (DESIGN.md section 6).
+struct QcbAuxDesc
+    struct_bytes::Int32; N::Int32; z_dim::Int32; dt_off::Int32; device::Int32
+    n_deriv::Int32; leak_x_off::Int32; n_leak::Int32
+    deriv_x_off::Ptr{Int32}; deriv_dx_off::Ptr{Int32}; deriv_dim::Ptr{Int32}; leak_idx::Ptr{Int32}
+end
+
+mutable struct B200ObjectiveTerms
+    handle::Ptr{Cvoid}
+    off::Vector{Int32}; dim::Vector{Int32}; R::Vector{Float64}; D::Float64
+end
+
+function B200ObjectiveTerms(traj::NamedTrajectory, names::Vector{Symbol}, Rs::Vector{Float64}; D::Float64=0.0, device::Int=0)
+    desc = QcbAuxDesc(Int32(sizeof(QcbAuxDesc)), traj.N, traj.dim, traj.components[traj.timestep][1] - 1, device,
+                      0, 0, 0, C_NULL, C_NULL, C_NULL, C_NULL)
+    h = Ref{Ptr{Cvoid}}(C_NULL)
+    st = ccall((:qcb_aux_create, LIB), Cint, (Ref{Ptr{Cvoid}}, Ref{QcbAuxDesc}), h, desc)
+    st == 0 || error(unsafe_string(ccall((:qcb_last_error, LIB), Cstring, (Ptr{Cvoid},), C_NULL)))
+    off = Int32[traj.components[n][1] - 1 for n in names]
+    dim = Int32[length(traj.components[n]) for n in names]
+    R = vcat([fill(Rs[i], dim[i]) for i in eachindex(names)]...)
+    obj = B200ObjectiveTerms(h[], off, dim, R, D)
+    finalizer(o -> ccall((:qcb_aux_destroy, LIB), Cvoid, (Ptr{Cvoid},), o.handle), obj)
+    return obj
+end
+
+# value and dense gradient over Z (what Ipopt's eval_f / eval_grad_f add to the terminal objective)
+function objective_and_gradient!(grad::Vector{Float64}, o::B200ObjectiveTerms, Z::Vector{Float64})
+    J = Ref{Float64}(0.0)
+    GC.@preserve grad Z o st = ccall((:qcb_aux_regularizer_eval, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Float64}, Int32, Ptr{Int32}, Ptr{Int32}, Ptr{Float64}, Float64, Ref{Float64}, Ptr{Float64}, Ptr{Float64}),
+        o.handle, Z, length(o.dim), o.off, o.dim, o.R, o.D, J, grad, C_NULL)
+    st == 0 || error("qcb_aux_regularizer_eval failed with status $st")
+    return J[]
+end
+
 # Old (docs / BASELINE.json) names
 const UnitaryIntegrator = B200BilinearIntegrator
 const KetIntegrator = B200BilinearIntegrator
