@@ -58,7 +58,8 @@ struct qcb_handle_s {
     int device = 0, n_sm = 148;
     std::vector<int> x_off;
     std::string err;
-    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    cudaStream_t stream = nullptr, copy_stream = nullptr, stream2 = nullptr;   // stream2: second lane of eval_large
+    cudaEvent_t lane_ev[2] = {nullptr, nullptr};
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     std::vector<cudaEvent_t> chunk_events;
     int64_t launches = 0;
@@ -398,7 +399,7 @@ void build_native_codes(qcb_handle_s *h, bool jac, bool hess) {
 // Launch helpers
 // ---------------------------------------------------------------------------------------
 template <int BM, int BN, int WM, int WN, int STAGES>
-void launch_gemm_cfg(qcb_handle_s *h, const GemmArgs &g, int batch) {
+void launch_gemm_cfg(qcb_handle_s *h, const GemmArgs &g, int batch, cudaStream_t st) {
     static bool attr_set[64] = {false};
     auto kern = bgemm_kernel<BM, BN, WM, WN, STAGES>;
     const size_t smem = GemmSmem<BM, BN>::bytes(STAGES);
@@ -413,18 +414,18 @@ void launch_gemm_cfg(qcb_handle_s *h, const GemmArgs &g, int batch) {
         if (h->prof_used + 2 > h->prof_ev.size()) {
             for (int i = 0; i < 2; ++i) { cudaEvent_t e; CK(cudaEventCreate(&e)); h->prof_ev.push_back(e); }
         }
-        CK(cudaEventRecord(h->prof_ev[h->prof_used], h->stream));
+        CK(cudaEventRecord(h->prof_ev[h->prof_used], st));
     }
-    kern<<<(unsigned)(batch * tiles), threads, smem, h->stream>>>(g);
+    kern<<<(unsigned)(batch * tiles), threads, smem, st>>>(g);
     if (prof) {
-        CK(cudaEventRecord(h->prof_ev[h->prof_used + 1], h->stream));
+        CK(cudaEventRecord(h->prof_ev[h->prof_used + 1], st));
         h->prof_flops.push_back(2.0 * g.M * g.N * g.K * g.nterm * batch);
         h->prof_used += 2;
     }
     ++h->launches;
 }
 
-void launch_gemm_iso(qcb_handle_s *h, const GemmArgs &g, int units) {
+void launch_gemm_iso(qcb_handle_s *h, const GemmArgs &g, int units, cudaStream_t st) {
     static bool attr_set[64] = {false};
     constexpr int ST = 3;
     auto kern = bgemm_iso_kernel<ST>;
@@ -439,11 +440,11 @@ void launch_gemm_iso(qcb_handle_s *h, const GemmArgs &g, int units) {
     if (prof) {
         if (h->prof_used + 2 > h->prof_ev.size())
             for (int i = 0; i < 2; ++i) { cudaEvent_t e; CK(cudaEventCreate(&e)); h->prof_ev.push_back(e); }
-        CK(cudaEventRecord(h->prof_ev[h->prof_used], h->stream));
+        CK(cudaEventRecord(h->prof_ev[h->prof_used], st));
     }
-    kern<<<(unsigned)(batch * tiles), 256, smem, h->stream>>>(g);
+    kern<<<(unsigned)(batch * tiles), 256, smem, st>>>(g);
     if (prof) {
-        CK(cudaEventRecord(h->prof_ev[h->prof_used + 1], h->stream));
+        CK(cudaEventRecord(h->prof_ev[h->prof_used + 1], st));
         h->prof_flops.push_back(2.0 * g.M * g.N * g.K * g.nterm * batch);
         h->prof_used += 2;
     }
@@ -451,13 +452,13 @@ void launch_gemm_iso(qcb_handle_s *h, const GemmArgs &g, int units) {
     CK(cudaGetLastError());
 }
 
-void launch_gemm(qcb_handle_s *h, GemmArgs &g, int units) {
+void launch_gemm(qcb_handle_s *h, GemmArgs &g, int units, cudaStream_t st) {
     const int batch = units * g.ndir;
     const bool big_ok = (g.M % 128 == 0) && (g.N % 128 == 0);
     if (big_ok && (long long)batch * (g.M / 128) * (g.N / 128) >= 2LL * h->n_sm)
-        launch_gemm_cfg<128, 128, 32, 32, 4>(h, g, batch);
+        launch_gemm_cfg<128, 128, 32, 32, 4>(h, g, batch, st);
     else
-        launch_gemm_cfg<64, 64, 32, 32, 4>(h, g, batch);
+        launch_gemm_cfg<64, 64, 32, 32, 4>(h, g, batch, st);
     CK(cudaGetLastError());
 }
 
@@ -469,11 +470,17 @@ struct LargeExec {
     int level = 0;
     int cur = 0;   // which L buffer holds the current level
     long long dd, pan;
-    double *ja = nullptr, *ha = nullptr;   // value arenas of this chunk
+    double *ja = nullptr, *ha = nullptr;   // value arenas (BASE pointers of the scratch arrays: see ubase)
+    // Lane support: squaring classes run concurrently on two streams, each on its own slice of the
+    // scratch arrays.  Every array has a per-unit stride, so a lane is just an offset of `ubase` units:
+    // mat() adds it for everything addressed through operands, raw kernel arguments use at().
+    int ubase = 0;
+    cudaStream_t st = nullptr;
 
     Opnd mat(double *base, long long su, long long sd = 0, long long ss = 0) const {
-        Opnd o; o.p = base; o.su = su; o.sd = sd; o.ss = ss; o.ld = h->dp; o.pad_ = 0; return o;
+        Opnd o; o.p = base + (long long)ubase * su; o.su = su; o.sd = sd; o.ss = ss; o.ld = h->dp; o.pad_ = 0; return o;
     }
+    double *at(double *base, long long su) const { return base + (long long)ubase * su; }
     Opnd E(int lvl) const {
         if (lvl == s) return mat(ja, h->JA);
         return mat(h->sc_E + (long long)lvl * h->chunk_units * dd, dd);
@@ -550,8 +557,8 @@ struct LargeExec {
                 sa.ndir = ndir; sa.unit0_global = u0; sa.nk = h->nk;
                 const dim3 sgrid((unsigned)(nu * ndir)), sblock(64, 4);
 #define QCB_SPARSE_LAUNCH(W_)                                                                      \
-    if (nright) sparse_drive_kernel<W_, true><<<sgrid, sblock, 0, h->stream>>>(sa);              \
-    else sparse_drive_kernel<W_, false><<<sgrid, sblock, 0, h->stream>>>(sa)
+    if (nright) sparse_drive_kernel<W_, true><<<sgrid, sblock, 0, st>>>(sa);              \
+    else sparse_drive_kernel<W_, false><<<sgrid, sblock, 0, st>>>(sa)
                 switch (h->ell_w) {
                 case 1: QCB_SPARSE_LAUNCH(1); break;
                 case 2: QCB_SPARSE_LAUNCH(2); break;
@@ -572,12 +579,12 @@ struct LargeExec {
             }
         }
         if (g.nterm == 0) {        // pure linear combination: no tensor work
-            lincomb_kernel<<<(unsigned)(nu * ndir * (g.N / 8)), 256, 0, h->stream>>>(g);
+            lincomb_kernel<<<(unsigned)(nu * ndir * (g.N / 8)), 256, 0, st>>>(g);
             ++h->launches;
             CK(cudaGetLastError());
             return;
         }
-        if (h->iso) launch_gemm_iso(h, g, nu); else launch_gemm(h, g, nu);
+        if (h->iso) launch_gemm_iso(h, g, nu, st); else launch_gemm(h, g, nu, st);
     }
     // dst = alpha * [scale] * op(a) * op(b), general shapes.  In iso mode the left operand is a
     // half-stored matrix (expanded on the fly) unless `plain` says both operands are ordinary.
@@ -591,16 +598,16 @@ struct LargeExec {
         g.alpha = alpha;
         g.unit_scale = unit_scale;
         g.dst = dst;
-        if (h->iso && !plain) launch_gemm_iso(h, g, nu); else launch_gemm(h, g, nu);
+        if (h->iso && !plain) launch_gemm_iso(h, g, nu, st); else launch_gemm(h, g, nu, st);
     }
     void contract(Opnd P, int nj, Opnd Q, int ni, double *out, int accumulate) {
         ContractArgs a;
         a.P = P; a.Q = Q; a.nj = nj; a.ni = ni; a.nelem = dd; a.out = out; a.accumulate = accumulate;
         a.unit0_global = u0; a.nk = h->nk;
         if (nj <= 16 && ni <= 16 && (dd % 128) == 0)
-            contract_mma_kernel<<<(unsigned)nu, 256, 0, h->stream>>>(a);
+            contract_mma_kernel<<<(unsigned)nu, 256, 0, st>>>(a);
         else
-            contract_kernel<<<(unsigned)(nu * nj), 256, 0, h->stream>>>(a);
+            contract_kernel<<<(unsigned)(nu * nj), 256, 0, st>>>(a);
         ++h->launches;
         CK(cudaGetLastError());
     }
@@ -814,6 +821,19 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             perm = h->d_perm;
         }
     }
+    // Lanes: when the scratch holds the whole slab, every squaring class is one chunk on its own
+    // slice of the scratch arrays (offset = its first position), and the classes alternate between two
+    // streams.  A small class (a few dozen units: launches of one or two CTA waves) then fills the
+    // SM slots the big class leaves idle in its wave tails instead of serialising ~50 under-filled
+    // launches behind it -- what strong scaling over 8 GPUs (250 units per GPU) otherwise pays for.
+    const bool lanes = perm && h->chunk_units >= h->units && (long long)h->m * dd >= (long long)h->dp * h->dp &&
+                       !h->profiling && !getenv("QCB_NO_LANES");   // per-launch timing needs kernels that run alone
+    if (lanes) {
+        if (!h->stream2) CK(cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking));
+        if (!h->lane_ev[0]) for (int i = 0; i < 2; ++i) CK(cudaEventCreateWithFlags(&h->lane_ev[i], cudaEventDisableTiming));
+        CK(cudaEventRecord(h->lane_ev[0], h->stream));          // inputs, norms and perm are ready
+        CK(cudaStreamWaitEvent(h->stream2, h->lane_ev[0], 0));
+    }
     size_t chunk_idx = 0, class_idx = 0;
     int nu_next = 0;
     for (int u0 = 0; u0 < h->units; u0 += nu_next, ++chunk_idx) {
@@ -823,6 +843,8 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             if (class_idx < h->h_class_end.size()) nu = std::min(nu, h->h_class_end[class_idx] - u0);
         }
         nu_next = nu;
+        const long long ub = lanes ? u0 : 0;                           // scratch slice of this chunk
+        cudaStream_t st = (lanes && (chunk_idx & 1)) ? h->stream2 : h->stream;
         // squarings of this chunk: what the largest ||dt G(u)||_1 among its units needs (smooth pulses
         // have slowly varying norms, so quiet stretches of the trajectory skip levels the peaks need)
         int s = s_slab;
@@ -832,23 +854,24 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             s = std::min(s_slab, std::max(0, qcb_squarings(mx)));
         }
         LargeExec X{h, nu, u0, s};
-        X.dd = dd; X.pan = pan;
+        X.dd = dd; X.pan = pan; X.ubase = (int)ub; X.st = st;
         const int buf = compact ? (int)(chunk_idx & 1) : 0;
         X.ja = buf ? h->sc_ja2 : h->sc_ja;
         X.ha = buf ? h->sc_ha2 : h->sc_ha;
         // the D2H of chunk idx-2 read this arena set: let it finish before overwriting
         if (compact && chunk_idx >= 2) {
-            CK(cudaStreamWaitEvent(h->stream, h->copied[buf], 0));
-            CK(cudaStreamWaitEvent(h->stream, h->part_done[buf], 0));
+            CK(cudaStreamWaitEvent(st, h->copied[buf], 0));
+            CK(cudaStreamWaitEvent(st, h->part_done[buf], 0));
         }
         // hybrid: the PCIe link and the host cores both write COO rows -- the first nd units of the
         // chunk are assembled on the device and DMA'd in full, the rest travel as compact arenas
         const int nd = compact ? std::min(h->part_units, (int)(h->direct_fraction * nu)) : 0;
         Opnd G = X.fixed(QR_G), A = X.fixed(QR_A);
-        build_G_kernel<<<nu, 256, 0, h->stream>>>(q, dZ, u0, const_cast<double *>(G.p), dd, h->d_norm, h->d_bad, nullptr, perm);
+        build_G_kernel<<<nu, 256, 0, st>>>(q, dZ, u0, const_cast<double *>(G.p), dd, h->d_norm, h->d_bad, nullptr, perm);
         ++h->launches;
-        prep_unit_kernel<<<nu, 256, 0, h->stream>>>(q, dZ, wh ? dmu : nullptr, u0, s, G.p, const_cast<double *>(A.p), dd,
-                                                     h->sc_XP, wh ? h->sc_MP : nullptr, pan, h->sc_tau, h->sc_ntau, perm);
+        prep_unit_kernel<<<nu, 256, 0, st>>>(q, dZ, wh ? dmu : nullptr, u0, s, G.p, const_cast<double *>(A.p), dd,
+                                                     X.at(h->sc_XP, pan), wh ? X.at(h->sc_MP, pan) : nullptr, pan, X.at(h->sc_tau, 1),
+                                                     X.at(h->sc_ntau, 1), perm);
         ++h->launches;
         CK(cudaGetLastError());
         Opnd XP = X.mat(h->sc_XP, pan), MP = X.mat(h->sc_MP, pan), EXp = X.mat(h->sc_EX, pan);
@@ -859,19 +882,22 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         Opnd Ef = X.E(s);
         // defect
         X.product(EXp, Ef, 0, XP, 0, h->dp, h->cp, h->dp, 1, 1.0, nullptr);
-        delta_kernel<<<nu, 256, 0, h->stream>>>(q, dZ, h->sc_EX, pan, d_delta, u0, perm);
+        delta_kernel<<<nu, 256, 0, st>>>(q, dZ, X.at(h->sc_EX, pan), pan, d_delta, u0, perm);
         ++h->launches;
         if (E_out) {      // rollouts: keep the (unpadded, full) propagator of every unit
-            if (h->iso) { iso_expand_kernel<<<nu, 256, 0, h->stream>>>(X.ja, h->JA, h->dp); ++h->launches; }
-            extract_E_kernel<<<nu, 256, 0, h->stream>>>(X.ja, h->JA, h->dp, h->d, E_out + (size_t)u0 * h->d * h->d);
+            if (h->iso) { iso_expand_kernel<<<nu, 256, 0, st>>>(X.at(X.ja, h->JA), h->JA, h->dp); ++h->launches; }
+            extract_E_kernel<<<nu, 256, 0, st>>>(X.at(X.ja, h->JA), h->JA, h->dp, h->d, E_out + (size_t)u0 * h->d * h->d);
             ++h->launches;
         }
         if (wj || wh) {
             if (wh) {
                 if (h->iso) {   // W = M X^T is a general matrix: project it onto the iso algebra (half storage)
-                    Opnd Wfull = X.mat(h->sc_dslot, (long long)h->dp * h->dp);
+                    // W (dp x dp per unit) borrows the head of this lane's slice of per-drive slot 0
+                    double *wfull = h->sc_dslot + ub * (long long)h->m * dd;
+                    Opnd Wfull = X.mat(wfull, (long long)h->dp * h->dp);
+                    Wfull.p = wfull;
                     X.product(Wfull, MP, 0, XP, 1, h->dp, h->dp, h->cp, 1, 1.0, nullptr, true);
-                    iso_project_kernel<<<nu, 256, 0, h->stream>>>(h->sc_dslot, (long long)h->dp * h->dp,
+                    iso_project_kernel<<<nu, 256, 0, st>>>(wfull, (long long)h->dp * h->dp,
                                                                   const_cast<double *>(X.W(s).p), dd, h->dp);
                     ++h->launches;
                 } else {
@@ -887,14 +913,14 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
                 if (wh) {   // second order: one product per node and direction, then m x m contractions
                     for (int i = 0; i < QCB_NOPS(QCB_P6); ++i) {
                         X.run(QCB_P6[i], m);
-                        X.contract(X.reg(QR_U), m, X.reg(QCB_P6_PARTNER[i]), m, h->sc_H, i > 0);
+                        X.contract(X.reg(QR_U), m, X.reg(QCB_P6_PARTNER[i]), m, X.at(h->sc_H, (long long)std::max(1, m) * std::max(1, m)), i > 0);
                     }
                 }
                 for (int l = 0; l < s; ++l) {
                     X.level = l;
                     if (wh) {
                         X.run(QCB_P7U[0], m);
-                        X.contract(X.reg(QR_U), m, X.reg(QR_L), m, h->sc_H, 1);
+                        X.contract(X.reg(QR_U), m, X.reg(QR_L), m, X.at(h->sc_H, (long long)std::max(1, m) * std::max(1, m)), 1);
                     }
                     X.run(QCB_P7L[0], m);
                     X.cur ^= 1;
@@ -905,62 +931,63 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             X.product(GE, G, 0, Ef, 0, h->dp, ncol, h->dp, 1, 1.0, nullptr);
             const long long esz = (long long)h->dp * h->dp;   // the arena always holds the full E
             Opnd JU = X.mat(X.ja + esz, h->JA, pan), JT = X.mat(X.ja + esz + m * pan, h->JA);
-            if (m > 0) X.product(JU, L, 0, XP, 0, h->dp, h->cp, h->dp, m, 1.0, h->sc_ntau);
+            if (m > 0) X.product(JU, L, 0, XP, 0, h->dp, h->cp, h->dp, m, 1.0, X.at(h->sc_ntau, 1));
             X.product(JT, GE, 0, XP, 0, h->dp, h->cp, h->dp, 1, -1.0, nullptr);
-            arena_consts_kernel<<<(nu + 127) / 128, 128, 0, h->stream>>>(X.ja, h->JA, esz + (m + 1) * pan, nu);
+            arena_consts_kernel<<<(nu + 127) / 128, 128, 0, st>>>(X.at(X.ja, h->JA), h->JA, esz + (m + 1) * pan, nu);
             if (h->iso) {   // right block column of E from the computed left one: the COO x-block is then c
                             // contiguous copies of -E (long runs for the device gather and the host expansion)
-                iso_expand_kernel<<<nu, 256, 0, h->stream>>>(X.ja, h->JA, h->dp);
+                iso_expand_kernel<<<nu, 256, 0, st>>>(X.at(X.ja, h->JA), h->JA, h->dp);
                 ++h->launches;
             }
             ++h->launches;
             if (wh) {
                 Opnd Wt = X.W(s);
                 Opnd HXU = X.mat(X.ha, h->HA, pan), HXT = X.mat(X.ha + m * pan, h->HA);
-                if (m > 0) X.product(HXU, L, 1, MP, 0, h->dp, h->cp, h->dp, m, 1.0, h->sc_ntau);
+                if (m > 0) X.product(HXU, L, 1, MP, 0, h->dp, h->cp, h->dp, m, 1.0, X.at(h->sc_ntau, 1));
                 X.product(HXT, GE, 1, MP, 0, h->dp, h->cp, h->dp, 1, -1.0, nullptr);
                 X.product(WE, Wt, 0, Ef, 1, h->dp, ncol, h->dp, 1, 1.0, nullptr);
                 X.product(GW, G, 1, Wt, 0, h->dp, ncol, h->dp, 1, 1.0, nullptr);
                 if (m > 0) {
-                    X.contract(WE, 1, X.reg(QR_GJ), m, h->sc_c1, 0);
-                    X.contract(GW, 1, L, m, h->sc_c2, 0);
+                    X.contract(WE, 1, X.reg(QR_GJ), m, X.at(h->sc_c1, std::max(1, m)), 0);
+                    X.contract(GW, 1, L, m, X.at(h->sc_c2, std::max(1, m)), 0);
                 }
-                X.contract(GW, 1, GE, 1, h->sc_c3, 0);
-                finalize_scalars_kernel<<<nu, 64, 0, h->stream>>>(m, h->sc_tau, h->sc_H, h->sc_c1, h->sc_c2, h->sc_c3,
-                                                                  X.ha, h->HA, (m + 1) * pan, h->iso ? 2.0 : 1.0);
+                X.contract(GW, 1, GE, 1, X.at(h->sc_c3, 1), 0);
+                finalize_scalars_kernel<<<nu, 64, 0, st>>>(m, X.at(h->sc_tau, 1), X.at(h->sc_H, (long long)std::max(1, m) * std::max(1, m)),
+                                                          X.at(h->sc_c1, std::max(1, m)), X.at(h->sc_c2, std::max(1, m)), X.at(h->sc_c3, 1),
+                                                          X.at(X.ha, h->HA), h->HA, (m + 1) * pan, h->iso ? 2.0 : 1.0);
                 ++h->launches;
             }
             if (wj && d_jac && !compact) {
                 if (h->run_assembly) {
                     if (!h->d_jpieces) upload_pieces(h, h->h_jcode, h->jnnz_unit, &h->d_jpieces, &h->n_jpieces);
-                    assemble_runs_kernel<<<(unsigned)((size_t)nu * h->n_jpieces), 256, 0, h->stream>>>(
-                        X.ja, h->JA, h->d_jcode, h->jnnz_unit, h->d_jpieces, h->n_jpieces, d_jac, u0, h->nk, u0, perm);
+                    assemble_runs_kernel<<<(unsigned)((size_t)nu * h->n_jpieces), 256, 0, st>>>(
+                        X.at(X.ja, h->JA), h->JA, h->d_jcode, h->jnnz_unit, h->d_jpieces, h->n_jpieces, d_jac, u0, h->nk, u0, perm);
                 } else {
                     int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->jnnz_unit / 4096));
-                    assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ja, h->JA, h->d_jcode, h->jnnz_unit, d_jac, u0, h->nk, cpu, u0, perm);
+                    assemble_kernel<<<nu * cpu, 256, 0, st>>>(X.at(X.ja, h->JA), h->JA, h->d_jcode, h->jnnz_unit, d_jac, u0, h->nk, cpu, u0, perm);
                 }
                 ++h->launches;
             }
             if (wh && d_hess && !compact) {
                 if (h->run_assembly) {
                     if (!h->d_hpieces) upload_pieces(h, h->h_hcode, h->hnnz_unit, &h->d_hpieces, &h->n_hpieces);
-                    assemble_runs_kernel<<<(unsigned)((size_t)nu * h->n_hpieces), 256, 0, h->stream>>>(
-                        X.ha, h->HA, h->d_hcode, h->hnnz_unit, h->d_hpieces, h->n_hpieces, d_hess, u0, h->nk, u0, perm);
+                    assemble_runs_kernel<<<(unsigned)((size_t)nu * h->n_hpieces), 256, 0, st>>>(
+                        X.at(X.ha, h->HA), h->HA, h->d_hcode, h->hnnz_unit, h->d_hpieces, h->n_hpieces, d_hess, u0, h->nk, u0, perm);
                 } else {
                     int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->hnnz_unit / 4096));
-                    assemble_kernel<<<nu * cpu, 256, 0, h->stream>>>(X.ha, h->HA, h->d_hcode, h->hnnz_unit, d_hess, u0, h->nk, cpu, u0, perm);
+                    assemble_kernel<<<nu * cpu, 256, 0, st>>>(X.at(X.ha, h->HA), h->HA, h->d_hcode, h->hnnz_unit, d_hess, u0, h->nk, cpu, u0, perm);
                 }
                 ++h->launches;
             }
             if (compact && nd > 0) {
                 if (wj && host->jac) {
                     int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->jnnz_unit / 4096));
-                    assemble_kernel<<<nd * cpu, 256, 0, h->stream>>>(X.ja, h->JA, h->d_jcode, h->jnnz_unit, h->part_j[buf], u0, h->nk, cpu, 0);
+                    assemble_kernel<<<nd * cpu, 256, 0, st>>>(X.ja, h->JA, h->d_jcode, h->jnnz_unit, h->part_j[buf], u0, h->nk, cpu, 0);
                     ++h->launches;
                 }
                 if (wh && host->hess) {
                     int cpu = (int)std::min<int64_t>(64, std::max<int64_t>(1, h->hnnz_unit / 4096));
-                    assemble_kernel<<<nd * cpu, 256, 0, h->stream>>>(X.ha, h->HA, h->d_hcode, h->hnnz_unit, h->part_h[buf], u0, h->nk, cpu, 0);
+                    assemble_kernel<<<nd * cpu, 256, 0, st>>>(X.ha, h->HA, h->d_hcode, h->hnnz_unit, h->part_h[buf], u0, h->nk, cpu, 0);
                     ++h->launches;
                 }
             }
@@ -1009,6 +1036,10 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         }
     }
     if (compact) expand_prev(chunk_idx - 1);
+    if (lanes) {        // join: everything the caller orders after this call waits for both lanes
+        CK(cudaEventRecord(h->lane_ev[1], h->stream2));
+        CK(cudaStreamWaitEvent(h->stream, h->lane_ev[1], 0));
+    }
 }
 
 template <int D>
@@ -1358,6 +1389,8 @@ void qcb_destroy(qcb_handle h) {
     for (auto &e : h->prof_ev) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    if (h->stream2) cudaStreamDestroy(h->stream2);
+    for (int i = 0; i < 2; ++i) if (h->lane_ev[i]) cudaEventDestroy(h->lane_ev[i]);
     delete h;
 }
 
