@@ -141,6 +141,28 @@ def test_d128_chunks_take_their_own_squaring_count(built_libs, monkeypatch):
         assert rel_err(dj[k * nj:(k + 1) * nj], ref[1][k * nj:(k + 1) * nj]) < TOL, k
         assert rel_err(dh[k * nh:(k + 1) * nh], ref[2][k * nh:(k + 1) * nh]) < TOL, k
     ev.close()
+    # default scratch budget: the whole slab fits, so the squaring classes run as concurrent lanes on
+    # two streams over disjoint scratch slices; twice in a row (the second call reuses everything)
+    monkeypatch.delenv("QCB_SCRATCH_MB")
+    ev = Evaluator(L, w.G_drift, w.G_drives)
+    for _ in range(2):
+        dd = torch.zeros(ev.defect_dim, dtype=torch.float64, device="cuda")
+        dj = torch.zeros(ev.jacobian_nnz, dtype=torch.float64, device="cuda")
+        dh = torch.zeros(ev.hessian_nnz, dtype=torch.float64, device="cuda")
+        ev.eval_all_device(dZ, dmu, dd, dj, dh)
+        dd, dj, dh = dd.cpu().numpy(), dj.cpu().numpy(), dh.cpu().numpy()
+        assert rel_err(dd, ref[0]) < TOL
+        for k in range(L.N - 1):
+            assert rel_err(dj[k * nj:(k + 1) * nj], ref[1][k * nj:(k + 1) * nj]) < TOL, k
+            assert rel_err(dh[k * nh:(k + 1) * nh], ref[2][k * nh:(k + 1) * nh]) < TOL, k
+    # lanes and the serial order give the same numbers (same chunks, same kernels)
+    monkeypatch.setenv("QCB_NO_LANES", "1")
+    d2 = torch.zeros(ev.defect_dim, dtype=torch.float64, device="cuda")
+    j2 = torch.zeros(ev.jacobian_nnz, dtype=torch.float64, device="cuda")
+    h2 = torch.zeros(ev.hessian_nnz, dtype=torch.float64, device="cuda")
+    ev.eval_all_device(dZ, dmu, d2, j2, h2)
+    assert np.array_equal(d2.cpu().numpy(), dd) and np.array_equal(j2.cpu().numpy(), dj) and np.array_equal(h2.cpu().numpy(), dh)
+    ev.close()
 
 
 # ---- call variants of the ABI ----------------------------------------------------------------------
