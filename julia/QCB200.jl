@@ -103,6 +103,55 @@ B200BilinearIntegrator(q::SamplingTrajectory, traj; kw...) =
     B200BilinearIntegrator(q.systems, state_names(q), drive_name(q), traj,
                            q.base_trajectory isa UnitaryTrajectory ? q.systems[1].levels : 1; kw...)
 
+# Terminal fidelities (include/qcb200.h: qcb_fidelity_*): the losses of src/quantum_objectives.jl
+# (unitary :173-191, ket :21-27, coherent ket :88-103) as quadratic forms evaluated on the GPU.  The
+# objective Q*|1-F| (:199) and the constraint F_min - F (src/quantum_constraints.jl:112) follow by the
+# chain rule below, exactly as TerminalObjective / NonlinearKnotPointConstraint wrap the loss closures.
+const FID_UNITARY, FID_KET, FID_COHERENT_KET, FID_UNITARY_SUBSPACE = Int32(0), Int32(1), Int32(2), Int32(3)
+
+mutable struct B200Fidelity
+    handle::Ptr{Cvoid}
+    x_dim::Int
+end
+
+function B200Fidelity(kind::Int32, goal::AbstractArray{ComplexF64}, n::Int; count::Int=1,
+                      subspace::Union{Nothing,Vector{Int}}=nothing, device::Int=0)
+    g = reinterpret(Float64, vec(Matrix{ComplexF64}(reshape(goal, :, 1))))   # interleaved (re, im), column-major
+    sub = isnothing(subspace) ? Int32[] : Int32.(subspace .- 1)
+    h = Ref{Ptr{Cvoid}}(C_NULL)
+    st = GC.@preserve g sub ccall((:qcb_fidelity_create, LIB), Cint,
+        (Ref{Ptr{Cvoid}}, Int32, Int32, Int32, Ptr{Float64}, Ptr{Int32}, Int32, Int32),
+        h, kind, n, count, g, isempty(sub) ? C_NULL : pointer(sub), length(sub), device)
+    st == 0 || error(unsafe_string(ccall((:qcb_last_error, LIB), Cstring, (Ptr{Cvoid},), C_NULL)))
+    f = B200Fidelity(h[], ccall((:qcb_fidelity_x_dim, LIB), Int64, (Ptr{Cvoid},), h[]))
+    finalizer(o -> ccall((:qcb_fidelity_destroy, LIB), Cvoid, (Ptr{Cvoid},), o.handle), f)
+    return f
+end
+
+# F(x) and, optionally, its gradient (x = the terminal iso-vec state, e.g. traj[end][name])
+function fidelity!(grad::Union{Nothing,Vector{Float64}}, f::B200Fidelity, x::Vector{Float64})
+    F = Ref{Float64}(0.0)
+    GC.@preserve grad x st = ccall((:qcb_fidelity_eval, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Float64}, Ref{Float64}, Ptr{Float64}, Ptr{Float64}),
+        f.handle, x, F, isnothing(grad) ? C_NULL : pointer(grad), C_NULL)
+    st == 0 || error("qcb_fidelity_eval failed with status $st")
+    return F[]
+end
+
+# Q * |1 - F| and its gradient: what UnitaryInfidelityObjective / KetInfidelityObjective hand to Ipopt
+function infidelity_objective!(grad::Vector{Float64}, f::B200Fidelity, x::Vector{Float64}; Q::Float64=100.0)
+    F = fidelity!(grad, f, x)
+    grad .*= -Q * sign(1 - F)
+    return Q * abs(1 - F)
+end
+
+# F_min - F <= 0 and its Jacobian row: Final*FidelityConstraint
+function fidelity_constraint!(jac_row::Vector{Float64}, f::B200Fidelity, x::Vector{Float64}, F_min::Float64)
+    F = fidelity!(jac_row, f, x)
+    jac_row .*= -1.0
+    return F_min - F
+end
+
 # Objective terms around the integrator (include/qcb200.h: qcb_aux_*): quadratic regularisers and the
 # minimum-time term in the form the reference's own solver logs pin (DESIGN.md section 6).
 struct QcbAuxDesc

@@ -801,8 +801,9 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     // are bound by the host cores and keep the natural order (contiguous D2H ranges).
     const int *perm = nullptr;
     h->h_class_end.clear();
-    if (!host && !E_out && h->S == 1 && (int)h->h_unit_norm.size() == h->units && !getenv("QCB_UNIFORM_SQUARINGS") &&
-        !getenv("QCB_NO_UNIT_SORT")) {
+    // switches are read per call (tests flip them between calls), never inside the chunk loop
+    const bool per_unit_s = (int)h->h_unit_norm.size() == h->units && !getenv("QCB_UNIFORM_SQUARINGS");
+    if (!host && !E_out && h->S == 1 && per_unit_s && !getenv("QCB_NO_UNIT_SORT")) {
         std::vector<int> cls(h->units);
         int lo = QCB_MAX_SQUARINGS, hi = 0;
         for (int u = 0; u < h->units; ++u) {
@@ -848,7 +849,7 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         // squarings of this chunk: what the largest ||dt G(u)||_1 among its units needs (smooth pulses
         // have slowly varying norms, so quiet stretches of the trajectory skip levels the peaks need)
         int s = s_slab;
-        if ((int)h->h_unit_norm.size() == h->units && !getenv("QCB_UNIFORM_SQUARINGS")) {
+        if (per_unit_s) {
             double mx = 0.0;
             for (int u = u0; u < u0 + nu; ++u) mx = std::max(mx, h->h_unit_norm[perm ? h->h_perm[u] : u]);
             s = std::min(s_slab, std::max(0, qcb_squarings(mx)));
