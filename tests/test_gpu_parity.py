@@ -104,6 +104,32 @@ def test_d128_drive_sparsity_classes(mix, iso, built_libs):
     ev.close()
 
 
+def test_d128_two_systems_with_different_sparse_drives(built_libs):
+    """Sampling batch on the large-d path (S = 2, d = 128): every system has its own ELL tables for
+    the sparse drive products (second system: drives in reverse order and rescaled, detuned drift)."""
+    from qcb200.layout import KnotLayout, JAC_BLOCK_DIAG
+    w = workloads.make("cfg5", N=3)
+    d, c, m, N = w.layout.d, w.layout.c, w.layout.m, 3
+    L = KnotLayout.smooth_pulse(d, c, m, N, 2, JAC_BLOCK_DIAG, with_derivatives=False)
+    G0 = np.stack([w.G_drift[0], 1.1 * w.G_drift[0]])
+    Gd = np.stack([w.G_drives[0], 0.9 * w.G_drives[0][::-1]])
+    rng = np.random.default_rng(8)
+    Z = np.zeros((N, L.z_dim))
+    Zs = w.Z.reshape(N, w.layout.z_dim)
+    for s in range(2):
+        Z[:, L.x_off[s]:L.x_off[s] + L.x_dim] = np.roll(Zs[:, :L.x_dim], s, axis=0)
+    Z[:, L.u_off:L.u_off + m] = 0.1 * rng.normal(size=(N, m))
+    Z[:, L.dt_off] = 0.1 * (1 + 0.1 * rng.uniform(-1, 1, N))
+    Z = Z.reshape(-1)
+    mu = rng.normal(size=2 * (N - 1) * L.x_dim)
+    OL = oracle_layout(L)
+    ev = Evaluator(L, G0, Gd)
+    ref = P.evaluate(OL, G0, Gd, Z, mu)
+    d1, j1, h1 = ev.eval_all(Z, mu)
+    assert rel_err(d1, ref[0]) < TOL and rel_err(j1, ref[1]) < TOL and rel_err(h1, ref[2]) < TOL
+    ev.close()
+
+
 def test_d128_chunks_take_their_own_squaring_count(built_libs, monkeypatch):
     """Large-d path: with a scratch budget of a few units per chunk and timesteps that grow along the
     trajectory, successive chunks run 0, 1, 2, ... squaring levels; every unit must still match the port."""
