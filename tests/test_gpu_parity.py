@@ -104,6 +104,42 @@ def test_d128_drive_sparsity_classes(mix, iso, built_libs):
     ev.close()
 
 
+@pytest.mark.parametrize("iso,dense", [(False, False), (True, True), (False, True)])
+def test_d128_device_route_variants(iso, dense, built_libs):
+    """Device-resident calls on the large-d path with timesteps spread over several squaring classes
+    (sorted units, concurrent lanes) for the full-storage kernels (iso=False) and for dense drive
+    generators (no ELL products), against the port."""
+    import torch
+    w = workloads.make("cfg5", N=11)
+    L = w.layout
+    OL = oracle_layout(L)
+    G0, Gd = np.array(w.G_drift), np.array(w.G_drives)
+    if not iso:
+        G0[0, 0, 1] += 0.05
+    if dense:
+        m = Gd.shape[1]
+        Gd = np.stack([sum((0.4 + 0.05 * t) * Gd[0, (j + t) % m] for t in range(m)) for j in range(m)])[None]
+    Z = w.Z.reshape(L.N, L.z_dim).copy()
+    Z[:, L.dt_off] *= np.random.default_rng(9).permutation(np.linspace(0.4, 5.0, L.N))
+    if dense:
+        Z[:, L.u_off:L.u_off + L.m] *= 0.3
+    Z = Z.reshape(-1)
+    ev = Evaluator(L, G0, Gd)
+    ref = P.evaluate(OL, G0, Gd, Z, w.mu)
+    dZ, dmu = torch.from_numpy(Z).cuda(), torch.from_numpy(w.mu).cuda()
+    dd = torch.zeros(ev.defect_dim, dtype=torch.float64, device="cuda")
+    dj = torch.zeros(ev.jacobian_nnz, dtype=torch.float64, device="cuda")
+    dh = torch.zeros(ev.hessian_nnz, dtype=torch.float64, device="cuda")
+    ev.eval_all_device(dZ, dmu, dd, dj, dh)
+    dd, dj, dh = dd.cpu().numpy(), dj.cpu().numpy(), dh.cpu().numpy()
+    nj, nh = L.jac_nnz_unit, L.hess_nnz_unit
+    assert rel_err(dd, ref[0]) < TOL
+    for k in range(L.N - 1):
+        assert rel_err(dj[k * nj:(k + 1) * nj], ref[1][k * nj:(k + 1) * nj]) < TOL, k
+        assert rel_err(dh[k * nh:(k + 1) * nh], ref[2][k * nh:(k + 1) * nh]) < TOL, k
+    ev.close()
+
+
 def test_d128_two_systems_with_different_sparse_drives(built_libs):
     """Sampling batch on the large-d path (S = 2, d = 128): every system has its own ELL tables for
     the sparse drive products (second system: drives in reverse order and rescaled, detuned drift)."""
