@@ -1070,11 +1070,20 @@ void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     const size_t unit_d = small_unit_doubles(h->d, h->c, h->m, s);
     if (small_smem_doubles(h->d, h->c, h->m, s, 1) * 8 > 227 * 1024)
         throw CudaFail{cudaErrorInvalidValue, "small-path shared memory exceeds 227 KB", __LINE__};
-    // units per CTA: fill up to 512 threads / ~100 KB so that two CTAs share an SM
+    // units per CTA: the kernel is latency bound (dependent tiny products, sub-warp barriers), so what
+    // counts is the number of units resident per SM = CTAs that fit (shared memory, threads) x upc.
+    // Small problems keep upc low enough to put a CTA on every SM twice over.
     int upc = 1;
-    while (upc < 16 && (upc * 2) * tpu <= 256 && small_smem_doubles(h->d, h->c, h->m, s, upc * 2) * 8 <= 100 * 1024 &&
-           (long long)(upc * 2) * h->n_sm * 2 <= h->units)
-        upc *= 2;
+    long best_resident = 0;
+    for (int cand = 1; cand <= 16; cand *= 2) {
+        if (cand * tpu > 512) break;
+        if (cand > 1 && (long long)cand * h->n_sm * 2 > h->units) break;
+        const size_t bytes = small_smem_doubles(h->d, h->c, h->m, s, cand) * 8 + 1024;   // + per-CTA reservation
+        if (bytes > 227 * 1024) break;
+        const long ctas = std::min<long>(std::min<long>(32, (long)(228 * 1024 / bytes)), 2048 / (cand * tpu));
+        const long resident = ctas * cand;
+        if (resident >= best_resident) { best_resident = resident; upc = cand; }
+    }
     p.tpu = tpu; p.upc = upc; p.unit_doubles = (int)unit_d;
     const size_t smem = small_smem_doubles(h->d, h->c, h->m, s, upc) * sizeof(double);
     switch (h->d) {

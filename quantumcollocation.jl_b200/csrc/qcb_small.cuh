@@ -392,7 +392,8 @@ static inline size_t small_unit_doubles(int d, int c, int m, int smax) {
     n += 3 * dc;                                   // X, Xn, M panels
     n += dd + (m + 1) * dc + 2;                    // Jacobian arena
     n += (m + 1) * dc + (size_t)m * m + m + 2;     // Hessian arena
-    n += (size_t)m * m + 128;                      // H accumulator + reduction scratch (8 per warp)
+    n += (size_t)m * m + (dd <= 32 ? 0 : 128);     // H accumulator + reduction scratch (8 per warp; units of
+                                                   // at most 32 threads reduce with shuffles and need none)
     return (n + 1) & ~(size_t)1;                   // keep every unit 16-byte aligned
 }
 static inline size_t small_smem_doubles(int d, int c, int m, int smax, int upc = 1) {
