@@ -400,8 +400,13 @@ static inline size_t small_smem_doubles(int d, int c, int m, int smax, int upc =
     return (size_t)upc * small_unit_doubles(d, c, m, smax) + (size_t)upc + 2;
 }
 
+// At most 512 threads per CTA (host: upc * tpu <= 512), so the compiler may use up to 128 registers.
+// Without the bound the run-time-d instance took 167 and could not be launched with 416..512 threads
+// (d = 20..23).  Capping D = 4 at 64 or 85 registers for more resident warps was measured slower
+// (spills: 0.60 / 0.57 ms against 0.51 ms on cfg4).
 template <int D>
-__global__ void small_unit_kernel(const __grid_constant__ SmallParams p) {
+__global__ void __launch_bounds__(512, 1)
+small_unit_kernel(const __grid_constant__ SmallParams p) {
     extern __shared__ __align__(16) double sm[];
     const int d = D > 0 ? D : p.d, c = p.c, m = p.m, dd = d * d, dc = d * c;
     const int ld = D > 0 ? ((D & 1) ? D : D + 1) : small_ld(d), msz = ld * d;

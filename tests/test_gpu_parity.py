@@ -521,7 +521,8 @@ def test_large_path_full_storage_d128_without_iso_structure(built_libs):
     ev.close()
 
 
-@pytest.mark.parametrize("d,c,m,S", [(2, 1, 1, 1), (5, 2, 3, 2), (7, 1, 2, 1), (9, 3, 1, 2), (14, 2, 2, 1), (20, 1, 5, 1), (40, 3, 2, 1)])
+@pytest.mark.parametrize("d,c,m,S", [(2, 1, 1, 1), (5, 2, 3, 2), (7, 1, 2, 1), (9, 3, 1, 2), (14, 2, 2, 1), (20, 1, 5, 1),
+                                     (22, 1, 2, 1), (23, 2, 1, 1), (40, 3, 2, 1)])
 def test_odd_shapes_and_general_generators(d, c, m, S, built_libs):
     """Dimensions without a specialised instance (run-time-d interpreter), odd d, several systems,
     non-skew generators, and d = 40 (large-d path padded to 64)."""
