@@ -128,6 +128,19 @@ void aux_ensure(qcb_aux_s *a, double **p, size_t n) { if (!*p) CK(cudaMalloc(p, 
 void aux_out(qcb_aux_s *a, size_t n) {
     if (a->out_cap < n) { if (a->dout) CK(cudaFree(a->dout)); CK(cudaMalloc(&a->dout, n * 8)); a->out_cap = n; }
 }
+// Host -> device copy of the knot columns [lo, hi) only (same layout on the device, so the kernels
+// index Z as before).  The control / timestep columns are a few dozen doubles of a knot that may be
+// thousands wide (cfg5: 38 of 16 422): a strided copy moves 0.6 MB instead of 132 MB per callback.
+void aux_upload_columns(qcb_aux_s *a, const double *Z, int lo, int hi) {
+    lo = std::max(0, lo); hi = std::min(a->z_dim, hi);
+    if (hi <= lo) return;
+    const size_t pitch = (size_t)a->z_dim * 8;
+    if ((size_t)(hi - lo) * 2 > (size_t)a->z_dim)
+        CK(cudaMemcpyAsync(a->dZ, Z, (size_t)a->N * pitch, cudaMemcpyHostToDevice, a->stream));
+    else
+        CK(cudaMemcpy2DAsync(a->dZ + lo, pitch, Z + lo, pitch, (size_t)(hi - lo) * 8, (size_t)a->N,
+                             cudaMemcpyHostToDevice, a->stream));
+}
 }  // namespace
 
 extern "C" {
@@ -223,7 +236,14 @@ qcb_status qcb_aux_derivative_eval(qcb_aux a, const double *Z, const double *mu,
         CK(cudaSetDevice(a->device));
         const size_t n = (size_t)qcb_aux_derivative_dim(a);
         if (n == 0) return QCB_OK;
-        CK(cudaMemcpyAsync(a->dZ, Z, (size_t)a->N * a->z_dim * 8, cudaMemcpyHostToDevice, a->stream));
+        {
+            int lo = a->dt_off, hi = a->dt_off + 1;
+            for (int r = 0; r < a->deriv_rows; ++r) {
+                lo = std::min(lo, std::min(a->row_x[r], a->row_dx[r]));
+                hi = std::max(hi, std::max(a->row_x[r], a->row_dx[r]) + 1);
+            }
+            aux_upload_columns(a, Z, lo, hi);
+        }
         if (mu) { aux_ensure(a, &a->dmu, std::max(n, (size_t)qcb_aux_leakage_dim(a))); CK(cudaMemcpyAsync(a->dmu, mu, n * 8, cudaMemcpyHostToDevice, a->stream)); }
         aux_out(a, 6 * n);
         double *dd = a->dout, *dj = a->dout + n, *dh = a->dout + 5 * n;
@@ -254,7 +274,11 @@ qcb_status qcb_aux_leakage_eval(qcb_aux a, const double *Z, const double *Qs, do
         CK(cudaSetDevice(a->device));
         const size_t n = (size_t)qcb_aux_leakage_dim(a), N = (size_t)a->N;
         if (n == 0) { if (objective) *objective = 0.0; return QCB_OK; }
-        CK(cudaMemcpyAsync(a->dZ, Z, N * a->z_dim * 8, cudaMemcpyHostToDevice, a->stream));
+        {
+            int lo = a->z_dim, hi = 0;
+            for (int o : a->leak) { lo = std::min(lo, o); hi = std::max(hi, o + 1); }
+            aux_upload_columns(a, Z, lo, hi);
+        }
         if (Qs) { aux_ensure(a, &a->dQ, N); CK(cudaMemcpyAsync(a->dQ, Qs, N * 8, cudaMemcpyHostToDevice, a->stream)); }
         if (mu) { aux_ensure(a, &a->dmu, std::max(n, (size_t)qcb_aux_derivative_dim(a))); CK(cudaMemcpyAsync(a->dmu, mu, n * 8, cudaMemcpyHostToDevice, a->stream)); }
         aux_out(a, std::max(4 * n + N, 6 * (size_t)qcb_aux_derivative_dim(a)));
@@ -333,7 +357,11 @@ qcb_status qcb_aux_regularizer_eval(qcb_aux a, const double *Z, int32_t n_terms,
             CK(cudaMemcpyAsync(a->d_reg_off, ro.data(), rows * sizeof(int), cudaMemcpyHostToDevice, a->stream));
             CK(cudaMemcpyAsync(a->d_reg_R, rr.data(), rows * 8, cudaMemcpyHostToDevice, a->stream));
         }
-        CK(cudaMemcpyAsync(a->dZ, Z, N * zd * 8, cudaMemcpyHostToDevice, a->stream));
+        {
+            int lo = a->dt_off, hi = a->dt_off + 1;
+            for (int o : ro) { lo = std::min(lo, o); hi = std::max(hi, o + 1); }
+            aux_upload_columns(a, Z, lo, hi);
+        }
         aux_out(a, std::max(N + N * zd + N * per, std::max(4 * (size_t)qcb_aux_leakage_dim(a) + N, 6 * (size_t)qcb_aux_derivative_dim(a))));
         double *dobj = a->dout, *dg = dobj + N, *dh = dg + N * zd;
         qcb::aux_regularizer_kernel<<<(unsigned)N, 128, 0, a->stream>>>(a->dZ, a->N, a->z_dim, a->dt_off, (int)rows, a->d_reg_off,
@@ -371,7 +399,7 @@ qcb_status qcb_aux_timesteps_equal(qcb_aux a, const double *Z, int64_t row_base,
     try {
         CK(cudaSetDevice(a->device));
         const size_t N = (size_t)a->N;
-        CK(cudaMemcpyAsync(a->dZ, Z, N * a->z_dim * 8, cudaMemcpyHostToDevice, a->stream));
+        aux_upload_columns(a, Z, a->dt_off, a->dt_off + 1);
         aux_out(a, 3 * N);
         double *dd = a->dout, *dj = a->dout + N;
         qcb::aux_dt_equal_kernel<<<(unsigned)((K + 127) / 128), 128, 0, a->stream>>>(a->dZ, a->N, a->z_dim, a->dt_off,
