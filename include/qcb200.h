@@ -260,14 +260,18 @@ qcb_status qcb_aux_leakage_eval(qcb_aux a, const double *Z, const double *Qs, do
  * This form reproduces the objective values printed in the reference's solver logs to 1e-14
  * (docs/literate/examples/multilevel_transmon.jl:139, two_qubit_gates.jl:261) on the solved
  * trajectories the reference ships (docs/data), see tests/test_reference_fixtures.py.
- * Terms: component offsets off[i] / sizes dim[i] inside a knot, weights R concatenated.  grad_Z:
- * [N * z_dim] dense gradient (overwritten).  hess_vals: per knot, {(v,v), (v,dt)} for every regularised
- * entry then one (dt,dt) value: N * (2 rows + 1) numbers in the order of qcb_aux_regularizer_structure. */
+ * Terms: component offsets off[i] / sizes dim[i] inside a knot, weights R concatenated; rows = sum of
+ * the sizes.  Outputs are compact, in row order, for the caller to scatter:
+ * grad_vals [N * (rows + 1)]: per knot dJ/dv for every regularised entry, then dJ/d(dt) (which
+ * includes D for the first N-1 knots); their 1-based columns of Z come from
+ * qcb_aux_regularizer_structure (grad_cols).  hess_vals [N * (2 rows + 1)]: per knot {(v,v), (v,dt)}
+ * for every regularised entry, then (dt,dt); 1-based upper-triangle COO in hess_rows / hess_cols.
+ * A component named by two terms yields two entries (Ipopt sums duplicates).  Any output may be NULL. */
 qcb_status qcb_aux_regularizer_structure(qcb_aux a, int32_t n_terms, const int32_t *off, const int32_t *dim,
-                                         int64_t *hess_rows, int64_t *hess_cols);
+                                         int64_t *grad_cols, int64_t *hess_rows, int64_t *hess_cols);
 qcb_status qcb_aux_regularizer_eval(qcb_aux a, const double *Z, int32_t n_terms, const int32_t *off,
                                     const int32_t *dim, const double *R, double min_time_D, double *objective,
-                                    double *grad_Z, double *hess_vals);
+                                    double *grad_vals, double *hess_vals);
 /* TimeStepsAllEqualConstraint (applied by every template, "timesteps all equal constraint" in the
  * logs; 2 nnz per row = the 98 / 198 of SURVEY.md 8a-a5): rows t = 1..N-1: dt_t - dt_N = 0.
  * delta [N-1]; Jacobian COO (1-based) and values (+1, -1) [2 (N-1)].  Any output may be NULL. */

@@ -163,6 +163,8 @@ end
 mutable struct B200ObjectiveTerms
     handle::Ptr{Cvoid}
     off::Vector{Int32}; dim::Vector{Int32}; R::Vector{Float64}; D::Float64
+    grad_cols::Vector{Int64}      # 1-based columns of Z of the compact gradient values
+    grad_vals::Vector{Float64}
 end
 
 function B200ObjectiveTerms(traj::NamedTrajectory, names::Vector{Symbol}, Rs::Vector{Float64}; D::Float64=0.0, device::Int=0)
@@ -174,18 +176,27 @@ function B200ObjectiveTerms(traj::NamedTrajectory, names::Vector{Symbol}, Rs::Ve
     off = Int32[traj.components[n][1] - 1 for n in names]
     dim = Int32[length(traj.components[n]) for n in names]
     R = vcat([fill(Rs[i], dim[i]) for i in eachindex(names)]...)
-    obj = B200ObjectiveTerms(h[], off, dim, R, D)
+    ng = traj.N * (sum(dim) + 1)
+    cols = Vector{Int64}(undef, ng)
+    GC.@preserve off dim cols ccall((:qcb_aux_regularizer_structure, LIB), Cint,
+        (Ptr{Cvoid}, Int32, Ptr{Int32}, Ptr{Int32}, Ptr{Int64}, Ptr{Int64}, Ptr{Int64}),
+        h[], length(dim), off, dim, cols, C_NULL, C_NULL)
+    obj = B200ObjectiveTerms(h[], off, dim, R, D, cols, zeros(ng))
     finalizer(o -> ccall((:qcb_aux_destroy, LIB), Cvoid, (Ptr{Cvoid},), o.handle), obj)
     return obj
 end
 
-# value and dense gradient over Z (what Ipopt's eval_f / eval_grad_f add to the terminal objective)
+# value; the gradient is ADDED into `grad` (length of Z) at the regularised entries and the timesteps --
+# what Ipopt's eval_f / eval_grad_f need on top of the terminal objective
 function objective_and_gradient!(grad::Vector{Float64}, o::B200ObjectiveTerms, Z::Vector{Float64})
     J = Ref{Float64}(0.0)
-    GC.@preserve grad Z o st = ccall((:qcb_aux_regularizer_eval, LIB), Cint,
+    GC.@preserve Z o st = ccall((:qcb_aux_regularizer_eval, LIB), Cint,
         (Ptr{Cvoid}, Ptr{Float64}, Int32, Ptr{Int32}, Ptr{Int32}, Ptr{Float64}, Float64, Ref{Float64}, Ptr{Float64}, Ptr{Float64}),
-        o.handle, Z, length(o.dim), o.off, o.dim, o.R, o.D, J, grad, C_NULL)
+        o.handle, Z, length(o.dim), o.off, o.dim, o.R, o.D, J, o.grad_vals, C_NULL)
     st == 0 || error("qcb_aux_regularizer_eval failed with status $st")
+    @inbounds for i in eachindex(o.grad_cols)
+        grad[o.grad_cols[i]] += o.grad_vals[i]
+    end
     return J[]
 end
 

@@ -76,7 +76,7 @@ SYMBOLS = {
     "qcb_aux_derivative_structure": (ctypes.c_int, [c_vp, ctypes.c_int64, c_lp, c_lp, c_lp, c_lp]),
     "qcb_aux_derivative_eval": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "qcb_aux_leakage_eval": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_double, c_vp, c_dp, c_vp, c_vp, c_vp, c_vp]),
-    "qcb_aux_regularizer_structure": (ctypes.c_int, [c_vp, ctypes.c_int32, c_ip, c_ip, c_lp, c_lp]),
+    "qcb_aux_regularizer_structure": (ctypes.c_int, [c_vp, ctypes.c_int32, c_ip, c_ip, c_lp, c_lp, c_lp]),
     "qcb_aux_regularizer_eval": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, c_ip, c_ip, c_vp, ctypes.c_double, c_dp, c_vp, c_vp]),
     "qcb_aux_timesteps_equal": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int64, c_vp, c_lp, c_lp, c_vp]),
     "qcb_fidelity_eval_batch_device_noalloc": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int64, c_vp, c_vp]),

@@ -302,30 +302,42 @@ class Aux:
         return off, dim, np.ascontiguousarray(R)
 
     def regularizer_structure(self, terms):
-        """1-based upper-triangle COO of the objective Hessian of `regularizer_eval` (same order)."""
+        """(grad_cols, (hess_rows, hess_cols)): 1-based columns of Z of the compact gradient of
+        `regularizer_eval` and the upper-triangle COO of its Hessian values (same orders)."""
         off, dim, _ = self._terms(terms)
-        n = self.N * (2 * int(dim.sum()) + 1)
-        hr, hc = np.empty(n, dtype=np.int64), np.empty(n, dtype=np.int64)
+        rows = int(dim.sum())
+        gc = np.empty(self.N * (rows + 1), dtype=np.int64)
+        hr, hc = np.empty(self.N * (2 * rows + 1), dtype=np.int64), np.empty(self.N * (2 * rows + 1), dtype=np.int64)
         ip = lambda a: a.ctypes.data_as(_lib.c_ip) if len(a) else None
-        st = self.lib.qcb_aux_regularizer_structure(self.h, len(dim), ip(off), ip(dim), hr.ctypes.data_as(_lib.c_lp), hc.ctypes.data_as(_lib.c_lp))
+        lp = lambda a: a.ctypes.data_as(_lib.c_lp)
+        st = self.lib.qcb_aux_regularizer_structure(self.h, len(dim), ip(off), ip(dim), lp(gc), lp(hr), lp(hc))
         if st != 0:
             raise _lib.QcbError(st, "regulariser structure failed")
-        return hr, hc
+        return gc, (hr, hc)
 
     def regularizer_eval(self, Z, terms, min_time_D=0.0, want_hessian=True):
         """terms: [(offset in knot, dim, R scalar or [dim])].  J = sum 1/2 R (dt v)^2 + D sum_{t<N} dt.
-        Returns (J, dense gradient [N*z_dim], Hessian values)."""
+        Returns (J, compact gradient values [N*(rows+1)], Hessian values [N*(2 rows+1)])."""
         Z = np.ascontiguousarray(Z, dtype=np.float64)
         off, dim, R = self._terms(terms)
+        rows = int(dim.sum())
         obj = ctypes.c_double(0.0)
-        grad = np.empty(self.N * self.z_dim)
-        hess = np.empty(self.N * (2 * int(dim.sum()) + 1)) if want_hessian else None
+        grad = np.empty(self.N * (rows + 1))
+        hess = np.empty(self.N * (2 * rows + 1)) if want_hessian else None
         ip = lambda a: a.ctypes.data_as(_lib.c_ip) if len(a) else None
         st = self.lib.qcb_aux_regularizer_eval(self.h, _ptr(Z), len(dim), ip(off), ip(dim), _ptr(R) if len(R) else None,
                                                float(min_time_D), ctypes.byref(obj), _ptr(grad), _ptr(hess))
         if st != 0:
             raise _lib.QcbError(st, "regulariser evaluation failed")
         return obj.value, grad, hess
+
+    def regularizer_gradient(self, Z, terms, min_time_D=0.0):
+        """Dense gradient over Z (length N*z_dim), scattered from the compact values."""
+        _, g, _ = self.regularizer_eval(Z, terms, min_time_D, want_hessian=False)
+        gc, _ = self.regularizer_structure(terms)
+        dense = np.zeros(self.N * self.z_dim)
+        np.add.at(dense, gc - 1, g)
+        return dense
 
     def timesteps_equal(self, Z, row_base=0):
         """Rows dt_t - dt_N (t < N): (delta, (rows, cols), values)."""

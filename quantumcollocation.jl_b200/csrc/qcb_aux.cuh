@@ -70,25 +70,22 @@ __global__ void aux_leakage_kernel(const double *Z, const double *Q, const doubl
 // Quadratic regularisers and the minimum-time term of the objective, one CTA per knot t:
 //   J = sum_rows 1/2 R_r (dt_t v_{t,r})^2  (all N knots)  +  D sum_{t<N} dt_t
 // (the form the reference's solver logs pin: tests/test_reference_fixtures.py).  Per knot:
-//   obj_terms[t]; grad[t][z_dim] (dense, zeroed here first); hess[t][2 rows + 1] =
+//   obj_terms[t]; grad[t][rows + 1] = {dJ/dv_r = R dt^2 v_r per row, then dJ/ddt}; hess[t][2 rows + 1] =
 //   {(v_r,v_r) = R dt^2, (v_r,dt) = 2 R dt v_r} per row, then (dt,dt) = sum_r R v_r^2.
+// Compact outputs in row order (the caller scatters them: a dense gradient over Z would be
+// N * z_dim doubles -- 132 MB for cfg5 -- to carry 2000 * 37 numbers).
 __global__ void aux_regularizer_kernel(const double *Z, int N, int z_dim, int dt_off, int rows, const int *row_off,
                                        const double *row_R, double D, double *obj_terms, double *grad, double *hess) {
     const int t = blockIdx.x;
     const double *z = Z + (long long)t * z_dim;
     const double dt = z[dt_off];
-    double *g = grad ? grad + (long long)t * z_dim : nullptr;
-    if (g) {
-        for (int i = threadIdx.x; i < z_dim; i += blockDim.x) g[i] = 0.0;
-        __syncthreads();
-    }
     double part = 0.0, gdt = 0.0, hdt = 0.0;
     for (int r = threadIdx.x; r < rows; r += blockDim.x) {
         const double v = z[row_off[r]], R = row_R[r];
         part = fma(0.5 * R * dt * dt, v * v, part);
         gdt = fma(R * dt, v * v, gdt);
         hdt = fma(R, v * v, hdt);
-        if (g) atomicAdd(g + row_off[r], R * dt * dt * v);      // two terms may regularise one component
+        if (grad) grad[(long long)t * (rows + 1) + r] = R * dt * dt * v;
         if (hess) {
             double *h = hess + (long long)t * (2 * rows + 1) + 2 * r;
             h[0] = R * dt * dt; h[1] = 2.0 * R * dt * v;
@@ -108,7 +105,7 @@ __global__ void aux_regularizer_kernel(const double *Z, int N, int z_dim, int dt
         for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { s0 += red[0][w]; s1 += red[1][w]; s2 += red[2][w]; }
         const bool timed = t < N - 1;
         if (obj_terms) obj_terms[t] = s0 + (timed ? D * dt : 0.0);
-        if (g) atomicAdd(g + dt_off, s1 + (timed ? D : 0.0));
+        if (grad) grad[(long long)t * (rows + 1) + rows] = s1 + (timed ? D : 0.0);
         if (hess) hess[(long long)t * (2 * rows + 1) + 2 * rows] = s2;
     }
 }
@@ -320,8 +317,8 @@ bool aux_reg_rows(qcb_aux a, int32_t n_terms, const int32_t *off, const int32_t 
 }  // namespace
 
 qcb_status qcb_aux_regularizer_structure(qcb_aux a, int32_t n_terms, const int32_t *off, const int32_t *dim,
-                                         int64_t *hess_rows, int64_t *hess_cols) {
-    if (!a || n_terms < 0 || (n_terms > 0 && (!off || !dim)) || !hess_rows || !hess_cols) return QCB_ERR_ARG;
+                                         int64_t *grad_cols, int64_t *hess_rows, int64_t *hess_cols) {
+    if (!a || n_terms < 0 || (n_terms > 0 && (!off || !dim))) return QCB_ERR_ARG;
     std::vector<int> ro; std::vector<double> rr;
     if (!aux_reg_rows(a, n_terms, off, dim, nullptr, ro, rr)) { a->err = "regulariser component outside the knot"; return QCB_ERR_ARG; }
     const int64_t rows = (int64_t)ro.size(), per = 2 * rows + 1;
@@ -329,16 +326,20 @@ qcb_status qcb_aux_regularizer_structure(qcb_aux a, int32_t n_terms, const int32
         const int64_t zb = (int64_t)t * a->z_dim, dtc = zb + a->dt_off;
         for (int64_t r = 0; r < rows; ++r) {
             const int64_t v = zb + ro[r], e = t * per + 2 * r;
-            hess_rows[e] = v + 1; hess_cols[e] = v + 1;
-            hess_rows[e + 1] = std::min(v, dtc) + 1; hess_cols[e + 1] = std::max(v, dtc) + 1;
+            if (grad_cols) grad_cols[t * (rows + 1) + r] = v + 1;
+            if (hess_rows && hess_cols) {
+                hess_rows[e] = v + 1; hess_cols[e] = v + 1;
+                hess_rows[e + 1] = std::min(v, dtc) + 1; hess_cols[e + 1] = std::max(v, dtc) + 1;
+            }
         }
-        hess_rows[t * per + 2 * rows] = dtc + 1; hess_cols[t * per + 2 * rows] = dtc + 1;
+        if (grad_cols) grad_cols[t * (rows + 1) + rows] = dtc + 1;
+        if (hess_rows && hess_cols) { hess_rows[t * per + 2 * rows] = dtc + 1; hess_cols[t * per + 2 * rows] = dtc + 1; }
     }
     return QCB_OK;
 }
 
 qcb_status qcb_aux_regularizer_eval(qcb_aux a, const double *Z, int32_t n_terms, const int32_t *off, const int32_t *dim,
-                                    const double *R, double min_time_D, double *objective, double *grad_Z,
+                                    const double *R, double min_time_D, double *objective, double *grad_vals,
                                     double *hess_vals) {
     if (!a || !Z || n_terms < 0 || (n_terms > 0 && (!off || !dim || !R))) return QCB_ERR_ARG;
     std::vector<int> ro; std::vector<double> rr;
@@ -362,16 +363,16 @@ qcb_status qcb_aux_regularizer_eval(qcb_aux a, const double *Z, int32_t n_terms,
             for (int o : ro) { lo = std::min(lo, o); hi = std::max(hi, o + 1); }
             aux_upload_columns(a, Z, lo, hi);
         }
-        aux_out(a, std::max(N + N * zd + N * per, std::max(4 * (size_t)qcb_aux_leakage_dim(a) + N, 6 * (size_t)qcb_aux_derivative_dim(a))));
-        double *dobj = a->dout, *dg = dobj + N, *dh = dg + N * zd;
+        aux_out(a, std::max(N + N * (rows + 1) + N * per, std::max(4 * (size_t)qcb_aux_leakage_dim(a) + N, 6 * (size_t)qcb_aux_derivative_dim(a))));
+        double *dobj = a->dout, *dg = dobj + N, *dh = dg + N * (rows + 1);
         qcb::aux_regularizer_kernel<<<(unsigned)N, 128, 0, a->stream>>>(a->dZ, a->N, a->z_dim, a->dt_off, (int)rows, a->d_reg_off,
-                                                                       a->d_reg_R, min_time_D, dobj, grad_Z ? dg : nullptr,
+                                                                       a->d_reg_R, min_time_D, dobj, grad_vals ? dg : nullptr,
                                                                        hess_vals ? dh : nullptr);
         ++a->launches;
         CK(cudaGetLastError());
         std::vector<double> terms(N);
         CK(cudaMemcpyAsync(terms.data(), dobj, N * 8, cudaMemcpyDeviceToHost, a->stream));
-        if (grad_Z) CK(cudaMemcpyAsync(grad_Z, dg, N * zd * 8, cudaMemcpyDeviceToHost, a->stream));
+        if (grad_vals) CK(cudaMemcpyAsync(grad_vals, dg, N * (rows + 1) * 8, cudaMemcpyDeviceToHost, a->stream));
         if (hess_vals) CK(cudaMemcpyAsync(hess_vals, dh, N * per * 8, cudaMemcpyDeviceToHost, a->stream));
         CK(cudaStreamSynchronize(a->stream));
         if (objective) { double s = 0; for (double v : terms) s += v; *objective = s; }   // N knot terms computed on the GPU

@@ -456,11 +456,11 @@ class QuadraticRegularizer:
         return self.aux.regularizer_eval(traj.datavec, [self.term], want_hessian=False)[0]
 
     def gradient(self, grad: np.ndarray, traj) -> np.ndarray:
-        grad[:] = self.aux.regularizer_eval(traj.datavec, [self.term], want_hessian=False)[1]
+        grad[:] = self.aux.regularizer_gradient(traj.datavec, [self.term])
         return grad
 
     def hessian_structure(self):
-        return self.aux.regularizer_structure([self.term])
+        return self.aux.regularizer_structure([self.term])[1]
 
     def hessian_values(self, traj):
         return self.aux.regularizer_eval(traj.datavec, [self.term])[2]
@@ -478,7 +478,7 @@ class MinimumTimeObjective:
         return self.aux.regularizer_eval(traj.datavec, [], self.D, want_hessian=False)[0]
 
     def gradient(self, grad: np.ndarray, traj) -> np.ndarray:
-        grad[:] = self.aux.regularizer_eval(traj.datavec, [], self.D, want_hessian=False)[1]
+        grad[:] = self.aux.regularizer_gradient(traj.datavec, [], self.D)
         return grad
 
 

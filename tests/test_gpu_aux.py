@@ -78,10 +78,14 @@ def test_regularizer_min_time_and_equal_timesteps(built_libs):
     Z = Z.reshape(-1)
     terms = [(L.u_off, m, 1e-2), (L.u_off + m, m, [0.3, 0.7]), (L.u_off, m, 0.05)]     # u twice
     aux = Aux(L.N, L.z_dim, L.dt_off)
-    J, g, hv = aux.regularizer_eval(Z, terms, min_time_D=7.5)
+    J, gv, hv = aux.regularizer_eval(Z, terms, min_time_D=7.5)
     J0, g0, H0 = O.quadratic_regularizer(Z, L.N, L.z_dim, L.dt_off, terms, 7.5)
+    gc, (hr, hc) = aux.regularizer_structure(terms)
+    assert len(gv) == len(gc) == L.N * (3 * m + 1)          # compact: one value per regularised entry + dt
+    g = np.zeros(L.N * L.z_dim)
+    np.add.at(g, gc - 1, gv)                                 # u is named by two terms: its entries add up
+    assert np.array_equal(g, aux.regularizer_gradient(Z, terms, 7.5))
     assert abs(J - J0) <= 1e-14 * abs(J0) and rel_err(g, g0.reshape(-1)) < 1e-14
-    hr, hc = aux.regularizer_structure(terms)
     assert len(hr) == len(hv) == L.N * (2 * 3 * m + 1) and np.all(hr <= hc)
     dense = np.zeros((L.N * L.z_dim,) * 2)
     np.add.at(dense, (hr - 1, hc - 1), hv)
@@ -98,7 +102,7 @@ def test_regularizer_min_time_and_equal_timesteps(built_libs):
     # minimum time alone: D on the first N-1 timesteps
     Jt, gt, _ = aux.regularizer_eval(Z, [], 100.0)
     dts = Z.reshape(L.N, L.z_dim)[:, L.dt_off]
-    assert abs(Jt - 100.0 * dts[:-1].sum()) < 1e-12 and np.count_nonzero(gt) == L.N - 1
+    assert abs(Jt - 100.0 * dts[:-1].sum()) < 1e-12 and np.array_equal(gt, np.r_[np.full(L.N - 1, 100.0), 0.0])
     # equal timesteps
     delta, (jr, jc), vals = aux.timesteps_equal(Z, row_base=11)
     assert np.array_equal(delta, O.timesteps_all_equal(Z, L.N, L.z_dim, L.dt_off))
