@@ -912,11 +912,11 @@ assemble_runs_kernel(const double *arena, long long arena_stride, const uint32_t
         for (unsigned e0 = threadIdx.x; e0 < n2; e0 += U * blockDim.x) {
             double2 v[U];
 #pragma unroll
-            for (int u = 0; u < U; ++u) { const unsigned e = e0 + u * blockDim.x; if (e < n2) v[u] = s2[e]; }
+            for (int u = 0; u < U; ++u) { const unsigned e = e0 + u * blockDim.x; if (e < n2) v[u] = __ldg(s2 + e); }
 #pragma unroll
             for (int u = 0; u < U; ++u) {
                 const unsigned e = e0 + u * blockDim.x;
-                if (e < n2) o2[e] = neg ? make_double2(-v[u].x, -v[u].y) : v[u];
+                if (e < n2) __stcs(o2 + e, neg ? make_double2(-v[u].x, -v[u].y) : v[u]);   // written once, never re-read here
             }
         }
         if ((pc.len & 1) && threadIdx.x == 0) o[pc.len - 1] = neg ? -s[pc.len - 1] : s[pc.len - 1];
