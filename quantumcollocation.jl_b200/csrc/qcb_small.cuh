@@ -69,6 +69,14 @@ __device__ __forceinline__ double *sm_resolve(const SmallCtx &x, int r) {
     }
 }
 
+// Barrier among the threads of one unit.  A unit of at most 32 threads lives inside one warp (tpu is a
+// power of two, units are aligned), so its producer/consumer steps need a warp barrier only; the
+// CTA-wide barrier is kept for larger units and for the one CTA-level exchange (the squaring count).
+__device__ __forceinline__ void unit_barrier(int tpu) {
+    if (tpu <= 32) __syncwarp();
+    else __syncthreads();
+}
+
 template <int D, int AS, int BS> __device__ __forceinline__ double dot_k(const double *a, const double *b, double acc, int d, int ld) {
     // AS / BS: 1 = unit stride, 0 = stride ld
     if (D > 0) {
@@ -113,7 +121,7 @@ template <int D, bool SYNC = true> __device__ __noinline__ void sm_run_op(const 
         if (op.ident >= 0 && r == q) acc += c_taylor[op.ident];
         dst[off] = acc;
     }
-    if (SYNC) __syncthreads();
+    if (SYNC) unit_barrier(x.tpu);
 }
 
 // ---- compile-time ops (D > 0): one specialised routine per table entry -- register bases are
@@ -166,7 +174,7 @@ __device__ __forceinline__ void sm_run_static_impl(const SmallCtx &x, std::integ
         }
         dst[off] = acc;
     }
-    if (SYNC) __syncthreads();
+    if (SYNC) unit_barrier(x.tpu);
 }
 template <int D, const qcb_op *TAB, int I, bool SYNC = true> __device__ __forceinline__ void sm_run_static(const SmallCtx &x) {
     sm_run_static_impl<D, TAB, I, SYNC>(x, std::make_integer_sequence<int, TAB[I].nterm>{},
@@ -460,7 +468,7 @@ small_unit_kernel(const __grid_constant__ SmallParams p) {
         G[off] = v;
     }
     for (int e = e0; e < m * m; e += tpu) Hacc[e] = 0.0;
-    __syncthreads();
+    unit_barrier(tpu);
     // ---- ||dt G||_1 per unit, then one squaring count for the CTA ----
     {
         double mine = 0.0;
@@ -491,7 +499,7 @@ small_unit_kernel(const __grid_constant__ SmallParams p) {
     if (threadIdx.x == 0 && s > 0) atomicMax(p.bad_flag + 1, s);
     const double tau = ldexp(dt, -s);
     for (int e = e0; e < dd; e += tpu) { const int off = (e % d) + (e / d) * ld; A[off] = tau * G[off]; }
-    __syncthreads();
+    unit_barrier(tpu);
 
     const bool tang = want_jac || want_hess;
     double *Wt = x.W + s * msz;
@@ -508,7 +516,7 @@ small_unit_kernel(const __grid_constant__ SmallParams p) {
     x.level = 0;
     sm_run_one<D, QCB_P1, 0, false>(x, c_P1);                                           // A2
     if (tang) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P5, 0, false>(x, c_P5); }   // dA2_j
-    __syncthreads();
+    unit_barrier(tpu);
     sm_run_one<D, QCB_P1, 1, false>(x, c_P1);                                           // A3
     sm_run_one<D, QCB_P1, 2, false>(x, c_P1);                                           // A4
     if (tang) for (int j = 0; j < m; ++j) {
@@ -516,22 +524,22 @@ small_unit_kernel(const __grid_constant__ SmallParams p) {
         sm_run_one<D, QCB_P5, 1, false>(x, c_P5);                                       // dA3_j
         sm_run_one<D, QCB_P5, 2, false>(x, c_P5);                                       // dA4_j
     }
-    __syncthreads();
+    unit_barrier(tpu);
     sm_run_one<D, QCB_P1, 3, false>(x, c_P1);                                           // Z2
     if (tang) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P5, 3, false>(x, c_P5); }   // dZ2_j
-    __syncthreads();
+    unit_barrier(tpu);
     sm_run_one<D, QCB_P1, 4, false>(x, c_P1);                                           // Z1
     if (tang) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P5, 4, false>(x, c_P5); }   // dZ1_j
-    __syncthreads();
+    unit_barrier(tpu);
     sm_run_one<D, QCB_P1, 5, false>(x, c_P1);                                           // E[0]
     if (tang) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P5, 5, false>(x, c_P5); }   // L_j
-    __syncthreads();
+    unit_barrier(tpu);
     // ---- squarings (Jacobian-only calls advance L_j in the same steps) ----
     for (int l = 0; l < s; ++l) {
         x.level = l;
         sm_run_one<D, QCB_P2, 0, false>(x, c_P2);
         if (tang && !want_hess) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P7L, 0, false>(x, c_P7L); }
-        __syncthreads();
+        unit_barrier(tpu);
         if (tang && !want_hess) x.lcur ^= 1;
     }
     const double *E = x.E + s * msz;
@@ -568,7 +576,7 @@ small_unit_kernel(const __grid_constant__ SmallParams p) {
             for (int j = 0; j < m; ++j) sm_level_pass<D>(x, j, l, c_P7U, red, Hacc + j * m);
             x.level = l;
             for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P7L, 0, false>(x, c_P7L); }
-            __syncthreads();
+            unit_barrier(tpu);
             x.lcur ^= 1;
         }
     }
@@ -589,7 +597,7 @@ small_unit_kernel(const __grid_constant__ SmallParams p) {
         GE[off] = g1; WE[off] = g2; GW[off] = g3;
         JA[e] = E[off];
     }
-    __syncthreads();
+    unit_barrier(tpu);
     double *JU = JA + dd, *JT = JU + m * dc;
     for (int j = 0; j < m; ++j) sm_panel(JU + j * dc, Lfin + j * msz, 0, X, d, ld, c, -tau, e0, tpu);
     sm_panel(JT, GE, 0, X, d, ld, c, -1.0, e0, tpu);
@@ -598,7 +606,7 @@ small_unit_kernel(const __grid_constant__ SmallParams p) {
         double *HXU = HA, *HXT = HA + m * dc, *HUU = HXT + dc, *HUT = HUU + m * m, *HTT = HUT + m;
         for (int j = 0; j < m; ++j) sm_panel(HXU + j * dc, Lfin + j * msz, 1, Mu, d, ld, c, -tau, e0, tpu);
         sm_panel(HXT, GE, 1, Mu, d, ld, c, -1.0, e0, tpu);
-        __syncthreads();                                  // Hacc complete (written by e0 == 0 lanes)
+        unit_barrier(tpu);                                  // Hacc complete (written by e0 == 0 lanes)
         for (int e = e0; e < m * m; e += tpu) {
             const int i = e / m, j = e % m;
             HUU[e] = -tau * tau * (Hacc[i * m + j] + Hacc[j * m + i]);
@@ -611,7 +619,7 @@ small_unit_kernel(const __grid_constant__ SmallParams p) {
         double c3 = sm_dot(GW, GE, d, ld, e0, tpu, red);
         if (e0 == 0) { HTT[0] = -c3; HTT[1] = 0.0; }
     }
-    __syncthreads();
+    unit_barrier(tpu);
     if (!live) return;
     // ---- compact host transfer: hand over the arenas themselves ----
     if (want_jac && p.ja_out) {
