@@ -119,7 +119,12 @@ qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu,
 
 /* ---- evaluation, device buffers (inputs/outputs already resident in HBM) ---------------
  * Same semantics; all pointers are device pointers on the handle's device; the work is
- * ordered on the handle's stream and the call returns after it has completed. */
+ * ordered on the handle's OWN stream (qcb_stream) and the call returns after it has completed.
+ * Stream ordering is the caller's job on the way in: every input and output buffer must be idle
+ * when the call is made -- synchronise the stream that produced the inputs (or last touched the
+ * outputs) first.  The library's stream is non-blocking and does not wait for the legacy default
+ * stream or for any other stream.  The same holds for qcb_fidelity_eval_batch_device_noalloc and
+ * for device pointers handed to qcb_ipc_* peers. */
 qcb_status qcb_eval_all_device(qcb_handle h, const double *dZ, const double *dmu,
                                double *d_delta, double *d_jac_vals, double *d_hess_vals);
 

@@ -286,6 +286,18 @@ def _hess_value(src, ev):
     return ev["H_dtdt"]
 
 
+def assemble_unit(layout: Layout, s: int, ev: dict):
+    """COO value vectors (delta, jac, hess) of ONE unit of system s in the native order, from the
+    dictionary of blocks `unit_eval` returns (or one loaded from a golden file).  hess is None when
+    the dictionary holds no second-order blocks."""
+    delta = np.asarray(ev["delta"]).T.reshape(-1)
+    jac = np.array([_jac_value(e[2], ev) for e in layout.jac_unit_pattern(s)])
+    hess = None
+    if "H_uu" in ev:
+        hess = np.array([_hess_value(e[2], ev) for e in layout.hess_unit_pattern(s)])
+    return delta, jac, hess
+
+
 def evaluate(layout: Layout, G0, Gd, Z, mu=None, want_jac=True, want_hess=True,
              k_range=None):
     """Whole-trajectory oracle evaluation in the native structure order.

@@ -21,6 +21,15 @@ def _ptr(a):
     return a.data_ptr()   # torch tensor
 
 
+def _sync_producers(*buffers):
+    """Synchronise torch's current stream on the device of any torch tensor among `buffers`."""
+    for b in buffers:
+        if b is not None and not isinstance(b, (int, np.ndarray)) and getattr(b, "is_cuda", False):
+            import torch
+            torch.cuda.current_stream(b.device).synchronize()
+            return
+
+
 def _colmajor(M):
     """[..., d, d] row-major numpy (M[r, c]) -> contiguous buffer holding column-major matrices."""
     return np.ascontiguousarray(np.swapaxes(np.asarray(M, dtype=np.float64), -1, -2))
@@ -143,6 +152,9 @@ class Evaluator:
 
     # -- evaluation with device buffers (torch CUDA tensors or raw device addresses) --
     def eval_all_device(self, dZ, dmu, d_delta, d_jac, d_hess):
+        """Device-resident evaluation.  The library runs on its own stream, so torch tensors are made
+        idle first (include/qcb200.h: every buffer must be idle when the call is made)."""
+        _sync_producers(dZ, dmu, d_delta, d_jac, d_hess)
         self._check(self.lib.qcb_eval_all_device(self.h, _ptr(dZ), _ptr(dmu), _ptr(d_delta), _ptr(d_jac), _ptr(d_hess)))
 
     def rollout(self, Z, x_init=None):

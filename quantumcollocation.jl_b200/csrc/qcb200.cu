@@ -1714,7 +1714,9 @@ __global__ void fid_grad_batch_kernel(const double *G, const double *p, double *
 
 namespace {
 constexpr int kMaxDevices = 64;
-double *g_noalloc_ptr[kMaxDevices] = {nullptr};   // device address of g_noalloc_proj, per device
+// Device address of g_noalloc_proj, per device.  Atomic because two host threads may make their
+// first call on a device at the same time: both look the address up and store the same value.
+std::atomic<double *> g_noalloc_ptr[kMaxDevices];
 }  // namespace
 
 extern "C" qcb_status qcb_fidelity_eval_batch_device_noalloc(qcb_fidelity f, const double *d_X, int64_t count,
@@ -1729,14 +1731,14 @@ extern "C" qcb_status qcb_fidelity_eval_batch_device_noalloc(qcb_fidelity f, con
     }
     if (f->device < 0 || f->device >= kMaxDevices) return QCB_ERR_ARG;
     cudaError_t e = cudaSetDevice(f->device);
-    if (e == cudaSuccess && !g_noalloc_ptr[f->device]) {
+    if (e == cudaSuccess && !g_noalloc_ptr[f->device].load(std::memory_order_acquire)) {
         // one-time set-up on this device (this device is current): resolve the symbol's address
         double *ptr = nullptr;
         e = cudaGetSymbolAddress((void **)&ptr, g_noalloc_proj);
-        if (e == cudaSuccess) g_noalloc_ptr[f->device] = ptr;
+        if (e == cudaSuccess) g_noalloc_ptr[f->device].store(ptr, std::memory_order_release);
     }
     if (e == cudaSuccess) {
-        double *p = g_noalloc_ptr[f->device];
+        double *p = g_noalloc_ptr[f->device].load(std::memory_order_acquire);
         const int64_t n = f->x_dim;
         dim3 g1((unsigned)f->R, (unsigned)count), g2((unsigned)((n + 255) / 256), (unsigned)count);
         // every projection slot read below is written first in this same call: nothing has to start at zero

@@ -82,6 +82,53 @@ def test_cfg5_d128_against_port_and_scipy_spot(built_libs):
     ev.close()
 
 
+def _block_errs(L, got, ref):
+    """Block-normwise errors of one unit's Jacobian / Hessian COO vectors, block by block, from the
+    per-entry source tags of the oracle's structure generator."""
+    OL = oracle_layout(L)
+    out = {}
+    for nm, pat, a, b in (("jac", OL.jac_unit_pattern(0), got[1], ref[1]), ("hess", OL.hess_unit_pattern(0), got[2], ref[2])):
+        tags = np.array([e[2][0] + (str(e[2][1]) if e[2][0] in ("U", "XU") else "") for e in pat])
+        for t in np.unique(tags):
+            sel = tags == t
+            out[f"{nm}.{t}"] = rel_err(a[sel], b[sel]) if np.abs(b[sel]).max() > 0 else float(np.abs(a[sel]).max())
+    out["delta"] = rel_err(got[0], ref[0])
+    return out
+
+
+@pytest.mark.parametrize("storage", ["iso", "full"])
+def test_cfg5_d128_against_committed_scipy_goldens(storage, built_libs, monkeypatch):
+    """Headline shape, independent check: every block (-E, all 12 L_j X panels, G E X, all of (x,u),
+    (x,dt), (u,u), (u,dt), (dt,dt)) of two full cfg5 units -- one without squarings, one with three --
+    against tests/golden/oracle_cfg5.npz (scipy Pade expm / expm_frechet / block-triangular second
+    order, generated offline by tests/golden/make_golden_cfg5.py), 1e-10 block-normwise, on the iso
+    half-storage kernels and on the full-storage kernels."""
+    from test_oracle import cfg5_golden
+    if storage == "full":
+        monkeypatch.setenv("QCB_NO_ISO", "1")
+    w, OL, g, units = cfg5_golden()
+    L = w.layout
+    ev = Evaluator(L, w.G_drift, w.G_drives)
+    d1, j1, h1 = ev.eval_all(g["Z"], g["mu"])
+    nj, nh, xd = L.jac_nnz_unit, L.hess_nnz_unit, L.x_dim
+    for k, ref in enumerate(units):
+        got = (d1[k * xd:(k + 1) * xd], j1[k * nj:(k + 1) * nj], h1[k * nh:(k + 1) * nh])
+        errs = _block_errs(L, got, ref)
+        assert len(errs) == 1 + 3 + L.m + L.m + 1 + 3, sorted(errs)      # delta; E, T, I; U0..; XU0..; XT; UU, UT, TT
+        bad = {b: e for b, e in errs.items() if e > TOL}
+        assert not bad, (storage, k, bad)
+    # device-resident route (sorted squaring classes, two lanes) gives the same numbers
+    import torch
+    dZ, dmu = torch.from_numpy(g["Z"]).cuda(), torch.from_numpy(g["mu"]).cuda()
+    dd = torch.zeros(ev.defect_dim, dtype=torch.float64, device="cuda")
+    dj = torch.zeros(ev.jacobian_nnz, dtype=torch.float64, device="cuda")
+    dh = torch.zeros(ev.hessian_nnz, dtype=torch.float64, device="cuda")
+    torch.cuda.synchronize()
+    ev.eval_all_device(dZ, dmu, dd, dj, dh)
+    assert rel_err(dj.cpu().numpy(), j1) < 1e-13 and rel_err(dh.cpu().numpy(), h1) < 1e-13
+    ev.close()
+
+
 @pytest.mark.parametrize("mix,iso", [(1, False), (2, True), (3, True), (3, False), (12, True)])
 def test_d128_drive_sparsity_classes(mix, iso, built_libs):
     """Large-d path with drive generators of 2, 3 (ELL width 2 / 4: gather products) and 12 nonzeros

@@ -237,3 +237,43 @@ def test_aux_oracle_definitions():
     obj, grad, con, cjac, chess = O.leakage(Z, N, zd, 3, [0, 2, 3], Qs=np.full(N, 2.0), value=0.1, mu=np.ones(N * 3))
     assert abs(obj - 2.0 * np.sum(Zm[:, [3, 5, 6]] ** 2) / 3) < 1e-13
     assert np.allclose(con, Zm[:, [3, 5, 6]] ** 2 - 0.1) and np.allclose(cjac, 2 * Zm[:, [3, 5, 6]])
+
+
+# ---- cfg5 goldens: every block of two full d = 128 units from the scipy oracle (make_golden_cfg5.py) ----
+def cfg5_golden():
+    """(workload, Z, mu, [(delta, jac, hess) per unit]) from tests/golden/oracle_cfg5.npz."""
+    g = np.load(os.path.join(GOLD, "oracle_cfg5.npz"))
+    w = workloads.make("cfg5", N=3, seed=11)
+    OL = oracle_layout(w.layout)
+    units = []
+    for k in range(w.layout.K):
+        ev = {key[len(f"u{k}."):]: g[key] for key in g.files if key.startswith(f"u{k}.")}
+        units.append(O.assemble_unit(OL, 0, ev))
+    return w, OL, g, units
+
+
+def test_cfg5_golden_inputs_and_port(built_libs):
+    """The committed cfg5 goldens belong to the seeded workload (same mu, same Z apart from the two
+    scaled timesteps), cover s = 0 and s = 3, and the C port reproduces every block of both units."""
+    w, OL, g, units = cfg5_golden()
+    L = w.layout
+    assert np.array_equal(w.mu, g["mu"])
+    Zg, Zw = g["Z"].reshape(L.N, L.z_dim), w.Z.reshape(L.N, L.z_dim)
+    mask = np.ones(L.z_dim, dtype=bool)
+    mask[L.dt_off] = False
+    assert np.array_equal(Zg[:, mask], Zw[:, mask])
+    assert O_squarings(float(g["u0.norm1"])) == 0 and O_squarings(float(g["u1.norm1"])) == 3
+    d1, j1, h1 = P.evaluate(OL, w.G_drift, w.G_drives, g["Z"], g["mu"])
+    nj, nh, xd = L.jac_nnz_unit, L.hess_nnz_unit, L.x_dim
+    for k, (d0, j0, h0) in enumerate(units):
+        assert rel_err(d1[k * xd:(k + 1) * xd], d0) < 1e-12, k
+        assert rel_err(j1[k * nj:(k + 1) * nj], j0) < 1e-11, k
+        assert rel_err(h1[k * nh:(k + 1) * nh], h0) < 1e-10, k
+
+
+def O_squarings(norm1, theta=0.5):
+    s, t = 0, theta
+    while norm1 > t:
+        t *= 2.0
+        s += 1
+    return s
