@@ -155,8 +155,20 @@ qcb_status qcb_device_to_host(int32_t device, void *dst_host, const void *src_de
 qcb_status qcb_host_alloc(void **ptr, size_t bytes);
 void qcb_host_free(void *ptr);
 
+/* Host-side output formatting (no counterpart in the reference).  On the large-d path the COO
+ * vectors are written into the caller's buffers by a pool of host threads from the compact arenas
+ * the GPU sends.  qcb_host_threads: size of that pool -- QCB_HOST_THREADS, else OMP_NUM_THREADS,
+ * else (cores this process may run on) / LOCAL_WORLD_SIZE; threads are pinned one per core
+ * (QCB_HOST_PIN=0: not pinned).  qcb_host_stream_fill: writes `bytes` of dst with the same
+ * streaming stores on the same pool and reports the wall time -- the measured host-write roofline
+ * that bench.py prints beside the end-to-end number. */
+int32_t qcb_host_threads(void);
+qcb_status qcb_host_stream_fill(void *dst, size_t bytes, double *seconds);
+
 /* Number of kernels this handle has launched since creation, and per-phase timings of the
- * last host-buffer call in milliseconds: [0] H2D, [1] kernels, [2] D2H, [3] total. */
+ * last host-buffer call in milliseconds: [0] H2D, [1] kernels with the device->host copies and the
+ * host-side expansion that overlap them, [2] always 0 (device->host is not separable: it is part
+ * of [1]), [3] total. */
 int64_t qcb_kernel_launches(qcb_handle h);
 qcb_status qcb_get_timings(qcb_handle h, double ms[4]);
 /* Bytes the last host-buffer call moved over PCIe: [0] host->device, [1] device->host.  On the

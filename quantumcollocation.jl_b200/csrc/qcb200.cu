@@ -6,14 +6,18 @@
 #include <cstdlib>
 #include <cstring>
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <functional>
+#include <map>
 #include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
 
 #include <immintrin.h>
+#include <pthread.h>
+#include <sched.h>
 
 #include <cuda_runtime.h>
 
@@ -34,6 +38,9 @@ struct CudaFail { cudaError_t e; const char *what; int line; };
         cudaError_t e_ = (call);                                         \
         if (e_ != cudaSuccess) throw CudaFail{e_, #call, __LINE__};      \
     } while (0)
+
+// the fused small-d kernel cannot hold a unit with this many squaring levels in shared memory
+struct SmallCapacity { int squarings; };
 
 struct Entry { int64_t row, col; uint32_t code; };
 
@@ -283,11 +290,17 @@ __attribute__((target("avx512f"))) void fill_run_avx512(double *dst, double v, s
 
 // Persistent worker threads for the host-side expansion (created once per process, shared by all
 // handles): run(fn) executes fn() on every worker and on the caller, returns when all are done.
+// Size: QCB_HOST_THREADS, else OMP_NUM_THREADS, else the cores this process may run on divided by
+// LOCAL_WORLD_SIZE (one process per GPU on one host: N ranks must not each start a thread per core).
+// Workers are pinned one per core, rank r taking the r-th block of the allowed cores, so that the
+// ranks' streaming stores do not migrate between cores (QCB_HOST_PIN=0 disables pinning).
+// run() is serialised by a mutex: handles driven from different host threads take turns.
 class HostPool {
 public:
     static HostPool &get() { static HostPool p; return p; }
     int size() const { return (int)workers_.size() + 1; }
     void run(const std::function<void()> &fn) {
+        std::lock_guard<std::mutex> serial(run_m_);
         {
             std::lock_guard<std::mutex> lk(m_);
             fn_ = &fn; pending_ = (int)workers_.size(); ++epoch_;
@@ -299,9 +312,31 @@ public:
         fn_ = nullptr;
     }
 private:
+    static int env_int(const char *name) { const char *e = getenv(name); return e ? atoi(e) : 0; }
     HostPool() {
-        const int n = (int)std::max(1u, std::thread::hardware_concurrency());
-        for (int i = 1; i < n; ++i) workers_.emplace_back([this] { loop(); });
+        std::vector<int> cores;
+        cpu_set_t set;
+        CPU_ZERO(&set);
+        if (sched_getaffinity(0, sizeof(set), &set) == 0)
+            for (int c = 0; c < CPU_SETSIZE; ++c) if (CPU_ISSET(c, &set)) cores.push_back(c);
+        if (cores.empty()) for (unsigned c = 0; c < std::max(1u, std::thread::hardware_concurrency()); ++c) cores.push_back((int)c);
+        const int world = std::max(1, env_int("LOCAL_WORLD_SIZE")), rank = std::max(0, env_int("LOCAL_RANK")) % world;
+        int n = env_int("QCB_HOST_THREADS");
+        if (n <= 0) n = env_int("OMP_NUM_THREADS");
+        if (n <= 0) n = std::max(1, (int)cores.size() / world);
+        n = std::max(1, std::min(n, (int)cores.size()));
+        const char *pin_env = getenv("QCB_HOST_PIN");
+        const bool pin = !(pin_env && atoi(pin_env) == 0) && (int)cores.size() >= n;
+        const int first = (int)(((long long)rank * n) % (long long)cores.size());
+        for (int i = 1; i < n; ++i) {
+            workers_.emplace_back([this] { loop(); });
+            if (pin) {
+                cpu_set_t one;
+                CPU_ZERO(&one);
+                CPU_SET(cores[(size_t)(first + i) % cores.size()], &one);
+                pthread_setaffinity_np(workers_.back().native_handle(), sizeof(one), &one);
+            }
+        }
     }
     ~HostPool() {
         { std::lock_guard<std::mutex> lk(m_); stop_ = true; ++epoch_; }
@@ -324,7 +359,7 @@ private:
         }
     }
     std::vector<std::thread> workers_;
-    std::mutex m_;
+    std::mutex m_, run_m_;
     std::condition_variable cv_, done_;
     const std::function<void()> *fn_ = nullptr;
     int pending_ = 0;
@@ -1002,37 +1037,51 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             }
             CK(cudaEventRecord(h->chunk_events[chunk_idx], h->stream));
             CK(cudaStreamWaitEvent(h->copy_stream, h->chunk_events[chunk_idx], 0));
-            if (host->delta)
+            if (host->delta) {
                 CK(cudaMemcpyAsync(host->delta + (size_t)u0 * h->xdim, d_delta + (size_t)u0 * h->xdim,
-                                   (size_t)nu * h->xdim * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)nu * h->xdim * 8);
+                                   (size_t)nu * h->xdim * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                h->xfer[1] += (int64_t)((size_t)nu * h->xdim * 8);
+            }
             if (compact) {
                 // compact transfer: the value arenas (every distinct number once) cross PCIe; the
                 // host cores write the COO vectors from them while the GPU works on the next chunk
-                if (wj && host->jac && nu > nd)
+                if (wj && host->jac && nu > nd) {
                     CK(cudaMemcpyAsync(h->stage_j[buf] + (size_t)nd * h->JA, X.ja + (size_t)nd * h->JA,
-                                       (size_t)(nu - nd) * h->JA * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)(nu - nd) * h->JA * 8);
-                if (wh && host->hess && nu > nd)
+                                       (size_t)(nu - nd) * h->JA * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                    h->xfer[1] += (int64_t)((size_t)(nu - nd) * h->JA * 8);
+                }
+                if (wh && host->hess && nu > nd) {
                     CK(cudaMemcpyAsync(h->stage_h[buf] + (size_t)nd * h->HA, X.ha + (size_t)nd * h->HA,
-                                       (size_t)(nu - nd) * h->HA * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)(nu - nd) * h->HA * 8);
+                                       (size_t)(nu - nd) * h->HA * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                    h->xfer[1] += (int64_t)((size_t)(nu - nd) * h->HA * 8);
+                }
                 CK(cudaEventRecord(h->copied[buf], h->copy_stream));
                 if (nd > 0) {
-                    if (wj && host->jac)
+                    if (wj && host->jac) {
                         CK(cudaMemcpyAsync(host->jac + (size_t)u0 * h->jnnz_unit, h->part_j[buf],
-                                           (size_t)nd * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)nd * h->jnnz_unit * 8);
-                    if (wh && host->hess)
+                                           (size_t)nd * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                        h->xfer[1] += (int64_t)((size_t)nd * h->jnnz_unit * 8);
+                    }
+                    if (wh && host->hess) {
                         CK(cudaMemcpyAsync(host->hess + (size_t)u0 * h->hnnz_unit, h->part_h[buf],
-                                           (size_t)nd * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)nd * h->hnnz_unit * 8);
+                                           (size_t)nd * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                        h->xfer[1] += (int64_t)((size_t)nd * h->hnnz_unit * 8);
+                    }
                 }
                 CK(cudaEventRecord(h->part_done[buf], h->copy_stream));
                 expand_prev(chunk_idx - 1);
                 prev_u0 = u0; prev_nu = nu; prev_nd = nd;
             } else {
-                if (wj && host->jac)
+                if (wj && host->jac) {
                     CK(cudaMemcpyAsync(host->jac + (size_t)u0 * h->jnnz_unit, d_jac + (size_t)u0 * h->jnnz_unit,
-                                       (size_t)nu * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)nu * h->jnnz_unit * 8);
-                if (wh && host->hess)
+                                       (size_t)nu * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                    h->xfer[1] += (int64_t)((size_t)nu * h->jnnz_unit * 8);
+                }
+                if (wh && host->hess) {
                     CK(cudaMemcpyAsync(host->hess + (size_t)u0 * h->hnnz_unit, d_hess + (size_t)u0 * h->hnnz_unit,
-                                       (size_t)nu * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)nu * h->hnnz_unit * 8);
+                                       (size_t)nu * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                    h->xfer[1] += (int64_t)((size_t)nu * h->hnnz_unit * 8);
+                }
             }
         }
     }
@@ -1068,8 +1117,7 @@ void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     int tpu = 1;
     if (dd <= 32) { while (tpu < dd) tpu <<= 1; } else tpu = std::min(512, round_up(dd, 32));
     const size_t unit_d = small_unit_doubles(h->d, h->c, h->m, s);
-    if (small_smem_doubles(h->d, h->c, h->m, s, 1) * 8 > 227 * 1024)
-        throw CudaFail{cudaErrorInvalidValue, "small-path shared memory exceeds 227 KB", __LINE__};
+    if (small_smem_doubles(h->d, h->c, h->m, s, 1) * 8 > 227 * 1024) throw SmallCapacity{s};
     // units per CTA: the kernel is latency bound (dependent tiny products, sub-warp barriers), so what
     // counts is the number of units resident per SM = CTAs that fit (shared memory, threads) x upc.
     // Small problems keep upc low enough to put a CTA on every SM twice over.
@@ -1132,7 +1180,17 @@ qcb_status eval_device(qcb_handle_s *h, const double *dZ, const double *dmu, dou
         int cap = std::min(h->s_hint, QCB_MAX_SQUARINGS);
         for (int attempt = 0;; ++attempt) {
             CK(cudaMemsetAsync(h->d_bad, 0, 2 * sizeof(int), h->stream));
-            eval_small(h, dZ, dmu, d_delta, compact ? nullptr : d_jac, compact ? nullptr : d_hess, want, cap, E_out, compact);
+            try {
+                eval_small(h, dZ, dmu, d_delta, compact ? nullptr : d_jac, compact ? nullptr : d_hess, want, cap, E_out, compact);
+            } catch (const SmallCapacity &sc) {
+                // a pulse whose ||dt*G(u)||_1 needs more squaring levels than a unit of this size can keep
+                // in shared memory: reported like any other out-of-range input (Ipopt: evaluation failed)
+                char buf[200];
+                snprintf(buf, sizeof buf, "||dt*G(u)||_1 needs %d squarings; the fused small-d kernel holds fewer for d = %d "
+                                          "(create the handle with force_path = 2 for such pulses)", sc.squarings, h->d);
+                h->err = buf;
+                return QCB_ERR_RANGE;
+            }
             CK(cudaMemcpyAsync(h->h_flags, h->d_bad, 2 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
             CK(cudaStreamSynchronize(h->stream));
             if (h->h_flags[0] & 1) { h->err = range_msg; return QCB_ERR_RANGE; }
@@ -1143,8 +1201,10 @@ qcb_status eval_device(qcb_handle_s *h, const double *dZ, const double *dmu, dou
         h->s_hint = std::max(h->h_flags[1], 0);
         if (host) {
             const bool wj = (want & 1) && host->jac, wh = (want & 2) && host->hess;
-            if (host->delta)
-                CK(cudaMemcpyAsync(host->delta, d_delta, (size_t)h->units * h->xdim * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)h->units * h->xdim * 8);
+            if (host->delta) {
+                CK(cudaMemcpyAsync(host->delta, d_delta, (size_t)h->units * h->xdim * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                h->xfer[1] += (int64_t)((size_t)h->units * h->xdim * 8);
+            }
             if (compact) {
                 if (wj) { CK(cudaMemcpyAsync(h->hs_ja, h->d_ja_all, (size_t)h->units * h->JA * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)h->units * h->JA * 8; }
                 if (wh) { CK(cudaMemcpyAsync(h->hs_ha, h->d_ha_all, (size_t)h->units * h->HA * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)h->units * h->HA * 8; }
@@ -1155,10 +1215,14 @@ qcb_status eval_device(qcb_handle_s *h, const double *dZ, const double *dmu, dou
                 if (wh) jobs[nj++] = {&h->hsegs, h->hs_ha, h->HA, host->hess, h->hnnz_unit};
                 if (nj > 0) expand_units(jobs, nj, h->nk, 0, h->units);
             } else {
-                if (wj)
-                    CK(cudaMemcpyAsync(host->jac, d_jac, (size_t)h->units * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)h->units * h->jnnz_unit * 8);
-                if (wh)
-                    CK(cudaMemcpyAsync(host->hess, d_hess, (size_t)h->units * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream)); h->xfer[1] += (int64_t)((size_t)h->units * h->hnnz_unit * 8);
+                if (wj) {
+                    CK(cudaMemcpyAsync(host->jac, d_jac, (size_t)h->units * h->jnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                    h->xfer[1] += (int64_t)((size_t)h->units * h->jnnz_unit * 8);
+                }
+                if (wh) {
+                    CK(cudaMemcpyAsync(host->hess, d_hess, (size_t)h->units * h->hnnz_unit * 8, cudaMemcpyDeviceToHost, h->copy_stream));
+                    h->xfer[1] += (int64_t)((size_t)h->units * h->hnnz_unit * 8);
+                }
                 CK(cudaStreamSynchronize(h->copy_stream));
             }
         }
@@ -1494,6 +1558,7 @@ qcb_status qcb_set_structure(qcb_handle h, int64_t row_base, const int64_t *jr, 
                 else if (slot != code) return fail(h, QCB_ERR_STRUCTURE, "Jacobian pattern differs between intervals");
             }
             upload_codes(h, &h->d_jcode, codes);
+            if (per != h->jnnz_unit) free_scratch(h);     // staging buffers were sized with the old nnz
             h->jnnz_unit = per;
             h->custom_j = true;
             h->h_jcode = codes;
@@ -1511,6 +1576,7 @@ qcb_status qcb_set_structure(qcb_handle h, int64_t row_base, const int64_t *jr, 
                 else if (v == h->dt_off) { kind = 2; idx = 0; }
                 else { kind = 3; idx = 0; }
             };
+            std::vector<std::map<std::pair<int64_t, int64_t>, int64_t>> seen_pairs(h->S);   // pair -> first entry
             for (int64_t p = 0; p < hn; ++p) {
                 const int64_t un = p / per, e = p % per;
                 const int s = (int)(un / h->nk), kl = (int)(un % h->nk), k = h->k0 + kl;
@@ -1527,11 +1593,24 @@ qcb_status qcb_set_structure(qcb_handle h, int64_t row_base, const int64_t *jr, 
                 else if (ka == 1 && kb == 1) code = cd.hUU(std::min(ia, ib), std::max(ia, ib));
                 else if (ka == 1 && kb == 2) code = cd.hUT(ia);
                 else if (ka == 2 && kb == 2) code = cd.hTT();
+                // MOI sums entries that name the same variable pair, in either order: when the adopted
+                // structure lists a pair twice (both triangles, or a plain repeat) only its first
+                // occurrence carries the value, later ones are filled with 0
+                if (code != cd.hZero()) {
+                    const std::pair<int64_t, int64_t> key{std::min(a, b), std::max(a, b)};
+                    if (kl == 0) {
+                        if (!seen_pairs[s].insert({key, e}).second) code = cd.hZero();
+                    } else {
+                        auto it = seen_pairs[s].find(key);
+                        if (it != seen_pairs[s].end() && it->second != e) code = cd.hZero();
+                    }
+                }
                 uint32_t &slot = codes[(size_t)s * per + e];
                 if (kl == 0) slot = code;
                 else if (slot != code) return fail(h, QCB_ERR_STRUCTURE, "Hessian pattern differs between intervals");
             }
             upload_codes(h, &h->d_hcode, codes);
+            if (per != h->hnnz_unit) free_scratch(h);
             h->hnnz_unit = per;
             h->custom_h = true;
             h->h_hcode = codes;
@@ -1651,6 +1730,30 @@ qcb_status qcb_rollout(qcb_handle h, const double *Z, const double *x_init, doub
     } catch (const CudaFail &f) {
         return fail_cuda(h, f);
     }
+}
+
+int32_t qcb_host_threads(void) { return HostPool::get().size(); }
+
+qcb_status qcb_host_stream_fill(void *dst, size_t bytes, double *seconds) {
+    if (!dst || bytes < 8) return QCB_ERR_ARG;
+    static const bool has512 = __builtin_cpu_supports("avx512f");
+    double *out = static_cast<double *>(dst);
+    const size_t n = bytes / 8, piece = 1u << 18;     // 2 MiB pieces, handed out dynamically
+    std::atomic<size_t> next{0};
+    std::function<void()> work = [&]() {
+        for (;;) {
+            const size_t b = next.fetch_add(piece);
+            if (b >= n) break;
+            const size_t len = std::min(piece, n - b);
+            if (has512) fill_run_avx512(out + b, 1.0, len);
+            else for (size_t i = 0; i < len; ++i) out[b + i] = 1.0;
+        }
+        if (has512) _mm_sfence();
+    };
+    const auto t0 = std::chrono::steady_clock::now();
+    HostPool::get().run(work);
+    if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return QCB_OK;
 }
 
 qcb_status qcb_host_alloc(void **ptr, size_t bytes) {

@@ -358,6 +358,33 @@ def test_custom_structure_permutation_and_structural_zeros(path, built_libs):
     ev.close()
 
 
+def test_custom_structure_with_both_triangles_counts_each_pair_once(built_libs):
+    """A reference-side Hessian structure that lists (a, b) and (b, a): MOI sums the two, so only the
+    first occurrence may carry the value.  Also: adopting a structure after a host-buffer evaluation
+    (staging buffers sized with the old nnz) must not corrupt anything."""
+    w = workloads.make("cfg2", N=5)
+    L = w.layout
+    ev = Evaluator(L, w.G_drift, w.G_drives, force_path=2)
+    d, j, h = ev.eval_all(w.Z, w.mu)                    # allocates the large-path staging first
+    hr, hc = ev.hessian_structure()
+    nh = L.hess_nnz_unit
+    off = hr != hc
+    rows2, cols2 = [], []
+    for k in range(L.K):
+        sl = slice(k * nh, (k + 1) * nh)
+        o = off[sl]
+        rows2.append(np.concatenate([hr[sl], hc[sl][o]]))     # upper triangle, then its mirror
+        cols2.append(np.concatenate([hc[sl], hr[sl][o]]))
+    n_off = int(off[:nh].sum())
+    ev.set_structure(None, (np.concatenate(rows2), np.concatenate(cols2)))
+    assert ev.hessian_nnz == L.K * (nh + n_off)
+    d2, j2, h2 = ev.eval_all(w.Z, w.mu)
+    h2 = h2.reshape(L.K, nh + n_off)
+    assert np.array_equal(h2[:, :nh], h.reshape(L.K, nh)) and np.all(h2[:, nh:] == 0)
+    assert np.array_equal(j2, j) and np.array_equal(d2, d)
+    ev.close()
+
+
 # ---- edge cases -------------------------------------------------------------------------------------
 def test_minimal_trajectory_two_knots_and_zero_controls(built_libs):
     w = workloads.make("cfg1_drift", N=2, u_scale=0.0)
