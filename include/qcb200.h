@@ -70,6 +70,20 @@ typedef struct {
     const int32_t *x_off;   /* [S] 0-based offset of each system's state inside a knot */
     const double *G_drift;  /* [S][d*d]    */
     const double *G_drives; /* [S][m][d*d] */
+    /* Optional state index map (both NULL: the state is the d*c contiguous entries at x_off[s]).
+     * For integrators whose state is a concatenation of several named components --
+     * VariationalKetIntegrator / VariationalUnitaryIntegrator, src/quantum_integrators.jl:140-169:
+     * x = vcat(state, variations...) under the block generator var_G(G, G_vars).  The kernels work
+     * on the d x c panel X (column-major, entry i = row + col*d); the maps say where each panel entry
+     * lives on the caller's side:
+     *   x_index   [S][d*c]  0-based offset inside a knot of panel entry i of system s (x_off is ignored);
+     *   row_index [d*c]     0-based position of panel entry i among the unit's defect rows / multipliers
+     *                       (NULL: identity).  For the unitary variant, whose vector is
+     *                       [vec(U); vec(U_v1); ...] while the panel stacks the blocks row-wise, this is
+     *                       the permutation (block b, row r, column q) -> b*d0*c + q*d0 + r.
+     * A caller compiled against the older struct (struct_bytes up to G_drives) is still accepted. */
+    const int32_t *x_index;
+    const int32_t *row_index;
 } qcb_desc;
 
 /* ---- life cycle -------------------------------------------------------------------- */
@@ -144,6 +158,19 @@ qcb_status qcb_rollout(qcb_handle h, const double *Z, const double *x_init, doub
  * means); every other rank maps them with qcb_ipc_open and passes `mapped + slab offset` as the
  * output pointers of qcb_eval_all_device: its kernels then store the slab straight into the host
  * rank's HBM over NVLink while they compute -- the gather is fused into the producing kernels. */
+/* Compact delivery (the faster form of the same gather): a Jacobian of the unitary path repeats -E once
+ * per state column, so the COO vectors are ~5x larger than the distinct numbers behind them.
+ * qcb_eval_arenas_device evaluates the slab like qcb_eval_all_device but stores, per unit, the value
+ * arenas (qcb_arena_doubles(h, 0) doubles for the Jacobian, (h, 1) for the Hessian; unit u of the slab at
+ * offset u * that size) -- into the Ipopt rank's memory when the pointers are IPC mappings; delta is
+ * delivered as before.  qcb_assemble_device then runs on the Ipopt rank: it writes the COO value vectors
+ * of n_units units, laid out [system][nk_src intervals] as their source slab produced them, from such
+ * arenas (any handle of the same problem holds the per-unit tables).  Large-d path only. */
+int64_t qcb_arena_doubles(qcb_handle h, int32_t which);
+qcb_status qcb_eval_arenas_device(qcb_handle h, const double *dZ, const double *dmu, double *d_delta,
+                                  double *d_jac_arenas, double *d_hess_arenas);
+qcb_status qcb_assemble_device(qcb_handle h, const double *d_jac_arenas, const double *d_hess_arenas,
+                               int64_t n_units, int32_t nk_src, double *d_jac_vals, double *d_hess_vals);
 qcb_status qcb_device_alloc(int32_t device, void **ptr, size_t bytes);
 void qcb_device_free(int32_t device, void *ptr);
 qcb_status qcb_ipc_export(int32_t device, void *ptr, unsigned char handle[64]);
@@ -192,6 +219,9 @@ qcb_status qcb_profile_read(qcb_handle h, double out[4]);
 #define QCB_FID_KET 1               /* ket_fidelity_loss, :21-27 */
 #define QCB_FID_COHERENT_KET 2      /* coherent_ket_fidelity, :88-103 (x = concatenated kets) */
 #define QCB_FID_UNITARY_SUBSPACE 3  /* EmbeddedOperator variant, :182-191 */
+#define QCB_FID_DENSITY_PURE 4      /* density_matrix_pure_state_infidelity_loss, :232-239: F = Re(psi' rho psi),
+                                       LINEAR in x = [vec(Re rho); vec(Im rho)] (gradient constant, Hessian 0);
+                                       goal = psi (n complex entries) */
 
 /* n: Hilbert dimension; count: number of kets (COHERENT_KET) else 1; subspace: 0-based level
  * indices (UNITARY_SUBSPACE; goal is then n_sub x n_sub), NULL otherwise. */
@@ -229,6 +259,26 @@ qcb_status qcb_fidelity_eval(qcb_fidelity f, const double *x, double *F, double 
  * race with each other -- serialise them.  Returns after the work has completed. */
 qcb_status qcb_fidelity_eval_batch_device_noalloc(qcb_fidelity f, const double *d_X, int64_t count,
                                                   double *d_F, double *d_grad);
+
+/* ---- free-phase unitary fidelity -------------------------------------------
+ * UnitaryFreePhaseInfidelityObjective (src/quantum_objectives.jl:203-226) and the theta-parametrised
+ * FinalUnitaryFidelityConstraint (src/quantum_constraints.jl:123-144): the loss acts on z = [x_N; theta]
+ * with theta a set of global variables and compares U with U_goal(theta).  The reference takes U_goal as
+ * a Julia function; across a C ABI the family is the one free-phase problems use, a diagonal phase
+ * factor:  U_goal(theta) = D(theta) U_goal (side 0) or U_goal D(theta) (side 1),
+ * D = diag(exp(i phi)), phi = P theta, with P the n x n_theta matrix `phase_map` (column-major: the
+ * diagonal of each commuting phase generator, e.g. of Z on one qubit).  Any other U_goal(theta) stays on
+ * the Julia path.
+ *   F(x, theta) = |tr(U_goal(theta)' U)|^2 / n^2
+ * x: 2 n^2 doubles (iso-vec of U), theta: n_theta doubles (host).  grad: x_dim + n_theta entries over
+ * z = [x; theta]; hess: dense (x_dim + n_theta)^2, column-major; F, grad, hess may be NULL.  The
+ * objective Q |1 - F| and the constraint F_min - F follow by the chain rule in the shim. */
+typedef struct qcb_free_phase_s *qcb_free_phase;
+qcb_status qcb_free_phase_create(qcb_free_phase *out, int32_t n, const double *goal_re_im, int32_t n_theta,
+                                 const double *phase_map, int32_t side, int32_t device);
+void qcb_free_phase_destroy(qcb_free_phase f);
+qcb_status qcb_free_phase_eval(qcb_free_phase f, const double *x, const double *theta, double *F, double *grad,
+                               double *hess);
 
 /* ---- auxiliary knot-point terms ------------------------------------------
  * The cheap terms every problem template adds around the bilinear integrator:
@@ -294,6 +344,15 @@ qcb_status qcb_aux_regularizer_eval(qcb_aux a, const double *Z, int32_t n_terms,
  * delta [N-1]; Jacobian COO (1-based) and values (+1, -1) [2 (N-1)].  Any output may be NULL. */
 qcb_status qcb_aux_timesteps_equal(qcb_aux a, const double *Z, int64_t row_base, double *delta, int64_t *jac_rows,
                                    int64_t *jac_cols, double *jac_vals);
+
+/* UnitarySensitivityObjective (src/quantum_objectives.jl:255-279):
+ *     J = sum_{t in times} Q_t * scale^4 * |tr(U_t' U_t)|^2 / n^2,   U_t = iso_vec_to_operator(x_t),
+ * on a (variational) state component of x_dim = 2 n^2 entries at offset x_off of a knot; times are
+ * 1-based knot indices.  tr(U'U) = ||x_t||^2, so the term is a quartic in x_t.  Outputs (host, any may
+ * be NULL): objective; grad_vals [n_times][x_dim]; hess_vals [n_times][x_dim][x_dim] dense. */
+qcb_status qcb_aux_sensitivity_eval(qcb_aux a, const double *Z, int32_t x_off, int32_t x_dim, int32_t n,
+                                    int32_t n_times, const int32_t *times, const double *Qs, double scale,
+                                    double *objective, double *grad_vals, double *hess_vals);
 
 #ifdef __cplusplus
 }

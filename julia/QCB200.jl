@@ -18,6 +18,7 @@ struct QcbDesc                      # mirrors qcb_desc, include/qcb200.h
     u_off::Int32; dt_off::Int32; jac_mode::Int32; device::Int32; k_begin::Int32; k_end::Int32
     force_path::Int32
     x_off::Ptr{Int32}; G_drift::Ptr{Float64}; G_drives::Ptr{Float64}
+    x_index::Ptr{Int32}; row_index::Ptr{Int32}      # optional state index map (variational integrators)
 end
 
 mutable struct B200BilinearIntegrator <: DirectTrajOpt.AbstractIntegrator
@@ -38,19 +39,27 @@ templates' own seam:  `SmoothPulseProblem(qtraj, N; integrator = B200BilinearInt
 its integrators (sampling_problem.jl:153), replace `prob.integrators[i]` after construction.
 """
 function B200BilinearIntegrator(systems::Vector, state_names::Vector{Symbol}, drive::Symbol,
-                                traj::NamedTrajectory, columns::Int; device::Int = 0, jac_mode::Int = 0)
-    d = 2 * systems[1].levels
+                                traj::NamedTrajectory, columns::Int; device::Int = 0, jac_mode::Int = 0,
+                                generator = (s, u) -> s.G(u, 0.0))
     m = systems[1].n_drives
+    d = size(generator(systems[1], zeros(m)), 1)     # 2n (ket / unitary) or 2n^2 (density, sys.𝒢)
     # matrices are dense column-major Float64: exactly what the C ABI wants
-    G0 = reduce(hcat, [vec(Matrix{Float64}(s.G(zeros(m), 0.0))) for s in systems])
-    Gd = reduce(hcat, [vec(Matrix{Float64}(s.G(Float64.(1:m .== j), 0.0)) .- reshape(G0[:, i], d, d))
+    G0 = reduce(hcat, [vec(Matrix{Float64}(generator(s, zeros(m)))) for s in systems])
+    Gd = reduce(hcat, [vec(Matrix{Float64}(generator(s, Float64.(1:m .== j))) .- reshape(G0[:, i], d, d))
                        for (i, s) in enumerate(systems) for j in 1:m])
+    return create_handle(d, columns, m, traj, length(systems), state_names, drive, G0, Gd;
+                         device = device, jac_mode = jac_mode)
+end
+
+function create_handle(d, columns, m, traj, S, state_names, drive, G0, Gd; device = 0, jac_mode = 0,
+                       x_index::Vector{Int32} = Int32[], row_index::Vector{Int32} = Int32[])
     x_off = Int32[first(traj.components[n]) - 1 for n in state_names]
-    desc = QcbDesc(sizeof(QcbDesc), d, columns, m, traj.N, length(systems), traj.dim,
+    desc = QcbDesc(sizeof(QcbDesc), d, columns, m, traj.N, S, traj.dim,
                    first(traj.components[drive]) - 1, first(traj.components[traj.timestep]) - 1,
-                   jac_mode, device, 0, 0, 0, pointer(x_off), pointer(G0), pointer(Gd))
+                   jac_mode, device, 0, 0, 0, pointer(x_off), pointer(G0), pointer(Gd),
+                   isempty(x_index) ? C_NULL : pointer(x_index), isempty(row_index) ? C_NULL : pointer(row_index))
     h = Ref{Ptr{Cvoid}}(C_NULL)
-    GC.@preserve x_off G0 Gd begin
+    GC.@preserve x_off G0 Gd x_index row_index begin
         st = ccall((:qcb_create, LIB), Cint, (Ref{Ptr{Cvoid}}, Ref{QcbDesc}), h, desc)
     end
     st == 0 || error(unsafe_string(ccall((:qcb_last_error, LIB), Cstring, (Ptr{Cvoid},), C_NULL)))
@@ -92,22 +101,95 @@ function hessian_of_lagrangian_values!(vals::AbstractVector{Float64}, int::B200B
         (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}), int.handle, Z, μ, vals))
 end
 
+# Structure queries: what the MOI evaluator of DirectTrajOpt asks of an integrator before the solve.
+# The generic names below are [memory] (SURVEY.md 8b); the arrays are 1-based, rows relative to
+# `row_base` (the offset of this integrator's defect rows in the constraint vector).
+function jacobian_structure(int::B200BilinearIntegrator; row_base::Int = 0)
+    rows, cols = Vector{Int64}(undef, int.jac_nnz), Vector{Int64}(undef, int.jac_nnz)
+    GC.@preserve rows cols check(int.handle, ccall((:qcb_jacobian_structure, LIB), Cint,
+        (Ptr{Cvoid}, Int64, Ptr{Int64}, Ptr{Int64}), int.handle, row_base, rows, cols))
+    return collect(zip(rows, cols))
+end
+function hessian_structure(int::B200BilinearIntegrator)
+    rows, cols = Vector{Int64}(undef, int.hess_nnz), Vector{Int64}(undef, int.hess_nnz)
+    GC.@preserve rows cols check(int.handle, ccall((:qcb_hessian_structure, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Int64}, Ptr{Int64}), int.handle, rows, cols))
+    return collect(zip(rows, cols))
+end
+# [memory] names DirectTrajOpt's evaluator may dispatch on instead of the two above
+const jacobian! = jacobian_values!
+const hessian_of_lagrangian! = hessian_of_lagrangian_values!
+
+# all three from one pass (one H2D of Z, one evaluation): for evaluators that cache per iterate
+function evaluate_all!(δ::Vector{Float64}, jac::Vector{Float64}, hess::Vector{Float64},
+                       int::B200BilinearIntegrator, Z::Vector{Float64}, μ::Vector{Float64})
+    GC.@preserve δ jac hess Z μ check(int.handle, ccall((:qcb_eval_all, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}),
+        int.handle, Z, μ, δ, jac, hess))
+end
+
 # Dispatch mirroring src/quantum_integrators.jl:28-101
 B200BilinearIntegrator(q::UnitaryTrajectory, traj; kw...) =
     B200BilinearIntegrator([get_system(q)], [state_name(q)], drive_name(q), traj, get_system(q).levels; kw...)
 B200BilinearIntegrator(q::KetTrajectory, traj; kw...) =
     B200BilinearIntegrator([get_system(q)], [state_name(q)], drive_name(q), traj, 1; kw...)
+# DensityTrajectory (:52-56): the Lindbladian sys.𝒢 on the density iso-vec, d = 2n^2, one column
+B200BilinearIntegrator(q::DensityTrajectory, traj; kw...) =
+    B200BilinearIntegrator([get_system(q)], [state_name(q)], drive_name(q), traj, 1;
+                           generator = (s, u) -> s.𝒢(u, 0.0), kw...)
+# MultiKetTrajectory (:63-74) returns a Vector, one integrator per ket, like the reference ...
 B200BilinearIntegrator(q::MultiKetTrajectory, traj; kw...) =
+    [B200BilinearIntegrator([get_system(q)], [n], drive_name(q), traj, 1; kw...) for n in state_names(q)]
+# ... and, fused, one handle that evaluates every ket of a knot in one launch
+B200FusedIntegrator(q::MultiKetTrajectory, traj; kw...) =
     B200BilinearIntegrator(fill(get_system(q), length(state_names(q))), state_names(q), drive_name(q), traj, 1; kw...)
 B200BilinearIntegrator(q::SamplingTrajectory, traj; kw...) =
     B200BilinearIntegrator(q.systems, state_names(q), drive_name(q), traj,
                            q.base_trajectory isa UnitaryTrajectory ? q.systems[1].levels : 1; kw...)
+
+# SamplingProblem hard-codes `BilinearIntegrator(sampling_qtraj, N)` (sampling_problem.jl:153); MinimumTimeProblem
+# re-uses the vector (minimum_time_problem.jl:131).  Swap the stock bilinear integrators of a built
+# problem for one fused handle (all systems of a knot in one launch); other integrators stay.
+function replace_integrators!(qcp, qtraj; kw...)
+    ints = qcp.prob.integrators
+    keep = [i for i in ints if !(i isa DirectTrajOpt.BilinearIntegrator)]
+    empty!(ints)
+    push!(ints, B200BilinearIntegrator(qtraj, qcp.prob.trajectory; kw...))
+    append!(ints, keep)
+    return qcp
+end
+
+# Variational integrators (src/quantum_integrators.jl:140-169): x = vcat(state, variations...) under
+# var_G(G, G_vars / scale).  The panel stacks the blocks row-wise; x_index / row_index tell the library
+# where each panel entry lives in the knot and among the defect rows (include/qcb200.h, qcb_desc).
+function B200VariationalIntegrator(sys, traj::NamedTrajectory, names::Vector{Symbol}, drive::Symbol,
+                                   columns::Int, scales::Vector{Float64}; device::Int = 0, jac_mode::Int = 0)
+    m, d0, nb = sys.n_drives, 2 * sys.levels, length(names)
+    gen(u) = Matrix{Float64}(Isomorphisms.var_G(sys.G(u), [G(u) / sc for (sc, G) in zip(scales, sys.G_vars)]))
+    d = nb * d0
+    G0 = vec(gen(zeros(m)))
+    Gd = reduce(hcat, [vec(gen(Float64.(1:m .== j))) .- G0 for j in 1:m])
+    x_index, row_index = zeros(Int32, d * columns), zeros(Int32, d * columns)
+    for (b, nm) in enumerate(names), q in 1:columns, r in 1:d0
+        e = (b - 1) * d0 + r + (q - 1) * d                       # panel entry, 1-based
+        x_index[e] = traj.components[nm][(q - 1) * d0 + r] - 1
+        row_index[e] = (b - 1) * d0 * columns + (q - 1) * d0 + r - 1
+    end
+    return create_handle(d, columns, m, traj, 1, [names[1]], drive, G0, Gd; device = device, jac_mode = jac_mode,
+                         x_index = x_index, row_index = row_index)
+end
+VariationalKetIntegrator(sys, traj, ψ̃::Symbol, vars::AbstractVector{Symbol}, u::Symbol; scale::Float64 = 1.0, kw...) =
+    B200VariationalIntegrator(sys, traj, vcat(ψ̃, vars...), u, 1, fill(scale, length(vars)); kw...)
+VariationalUnitaryIntegrator(sys, traj, Ũ⃗::Symbol, vars::AbstractVector{Symbol}, u::Symbol;
+                             scales::AbstractVector{<:Float64} = fill(1.0, length(vars)), kw...) =
+    B200VariationalIntegrator(sys, traj, vcat(Ũ⃗, vars...), u, sys.levels, collect(scales); kw...)
 
 # Terminal fidelities (include/qcb200.h: qcb_fidelity_*): the losses of src/quantum_objectives.jl
 # (unitary :173-191, ket :21-27, coherent ket :88-103) as quadratic forms evaluated on the GPU.  The
 # objective Q*|1-F| (:199) and the constraint F_min - F (src/quantum_constraints.jl:112) follow by the
 # chain rule below, exactly as TerminalObjective / NonlinearKnotPointConstraint wrap the loss closures.
 const FID_UNITARY, FID_KET, FID_COHERENT_KET, FID_UNITARY_SUBSPACE = Int32(0), Int32(1), Int32(2), Int32(3)
+const FID_DENSITY_PURE = Int32(4)    # density_matrix_pure_state_infidelity_loss, src/quantum_objectives.jl:232-239
 
 mutable struct B200Fidelity
     handle::Ptr{Cvoid}
@@ -200,8 +282,68 @@ function objective_and_gradient!(grad::Vector{Float64}, o::B200ObjectiveTerms, Z
     return J[]
 end
 
-# Old (docs / BASELINE.json) names
+# Free-phase fidelity (src/quantum_objectives.jl:203-226; src/quantum_constraints.jl:123-144) for
+# U_goal(θ) = diag(exp(i P θ)) U_goal (side 0) or U_goal diag(...) (side 1); z = [x_N; θ]
+mutable struct B200FreePhase
+    handle::Ptr{Cvoid}
+    x_dim::Int
+    n_theta::Int
+end
+function B200FreePhase(U_goal::AbstractMatrix{ComplexF64}, phase_map::AbstractMatrix{Float64}; side::Int = 0, device::Int = 0)
+    n = size(U_goal, 1)
+    g = reinterpret(Float64, vec(Matrix{ComplexF64}(U_goal)))
+    P = Matrix{Float64}(phase_map)                         # n x n_theta, column-major
+    h = Ref{Ptr{Cvoid}}(C_NULL)
+    st = GC.@preserve g P ccall((:qcb_free_phase_create, LIB), Cint,
+        (Ref{Ptr{Cvoid}}, Int32, Ptr{Float64}, Int32, Ptr{Float64}, Int32, Int32),
+        h, n, g, size(P, 2), P, side, device)
+    st == 0 || error(unsafe_string(ccall((:qcb_last_error, LIB), Cstring, (Ptr{Cvoid},), C_NULL)))
+    f = B200FreePhase(h[], 2 * n * n, size(P, 2))
+    finalizer(o -> ccall((:qcb_free_phase_destroy, LIB), Cvoid, (Ptr{Cvoid},), o.handle), f)
+    return f
+end
+# F and its gradient over z = [x; θ] (grad has x_dim + n_theta entries; hess, if given, (x_dim+n_theta)^2)
+function free_phase_fidelity!(grad::Union{Nothing,Vector{Float64}}, f::B200FreePhase, x::Vector{Float64}, θ::Vector{Float64};
+                              hess::Union{Nothing,Matrix{Float64}} = nothing)
+    F = Ref{Float64}(0.0)
+    GC.@preserve grad x θ hess st = ccall((:qcb_free_phase_eval, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Ref{Float64}, Ptr{Float64}, Ptr{Float64}),
+        f.handle, x, θ, F, isnothing(grad) ? C_NULL : pointer(grad), isnothing(hess) ? C_NULL : pointer(hess))
+    st == 0 || error("qcb_free_phase_eval failed with status $st")
+    return F[]
+end
+
+# UnitarySensitivityObjective (src/quantum_objectives.jl:263-279) through an aux handle `a` (Ptr from qcb_aux_create)
+function sensitivity_objective!(grad_vals::Matrix{Float64}, a::Ptr{Cvoid}, Z::Vector{Float64}, x_off::Int, x_dim::Int,
+                                n::Int, times::Vector{Int32}, Qs::Vector{Float64}, scale::Float64)
+    J = Ref{Float64}(0.0)
+    GC.@preserve grad_vals Z times Qs st = ccall((:qcb_aux_sensitivity_eval, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Float64}, Int32, Int32, Int32, Int32, Ptr{Int32}, Ptr{Float64}, Float64, Ref{Float64}, Ptr{Float64}, Ptr{Float64}),
+        a, Z, x_off, x_dim, n, length(times), times, Qs, scale, J, grad_vals, C_NULL)
+    st == 0 || error("qcb_aux_sensitivity_eval failed with status $st")
+    return J[]
+end
+
+# Old (docs / BASELINE.json) names, SURVEY.md Appendix A
 const UnitaryIntegrator = B200BilinearIntegrator
 const KetIntegrator = B200BilinearIntegrator
+const DensityOperatorIntegrator = B200BilinearIntegrator
+# problem templates under their docs-era names: build the trajectory object, pass this integrator through
+# the template's own `integrator=` seam (smooth_pulse_problem.jl:57,103-127)
+function UnitarySmoothPulseProblem(sys, U_goal, T, Δt; device::Int = 0, kwargs...)
+    qtraj = UnitaryTrajectory(sys, U_goal, T * Δt)
+    traj = NamedTrajectory(qtraj, T)
+    return SmoothPulseProblem(qtraj, T; integrator = B200BilinearIntegrator(qtraj, traj; device = device), kwargs...)
+end
+function QuantumStateSmoothPulseProblem(sys, ψ_init, ψ_goal, T, Δt; device::Int = 0, kwargs...)
+    qtraj = KetTrajectory(sys, ψ_init, ψ_goal, T * Δt)
+    traj = NamedTrajectory(qtraj, T)
+    return SmoothPulseProblem(qtraj, T; integrator = B200BilinearIntegrator(qtraj, traj; device = device), kwargs...)
+end
+function UnitarySamplingProblem(systems, U_goal, T, Δt; device::Int = 0, kwargs...)
+    qcp = UnitarySmoothPulseProblem(systems[1], U_goal, T, Δt; device = device)
+    sqcp = SamplingProblem(qcp, systems; kwargs...)
+    return replace_integrators!(sqcp, SamplingTrajectory(qcp.qtraj, systems); device = device)
+end
 
 end # module

@@ -552,3 +552,129 @@ def leakage_indices(subspace, levels):
                 if (i in sub) != (j in sub):
                     idx.append(j * 2 * n + part + i)
     return np.asarray(idx, dtype=np.int64)
+
+
+# --------------------------------------------------------------------------- #
+# open-system and variational generators, free-phase, sensitivity and density
+# losses.  Restated from src/quantum_integrators.jl:52-56,126-169 and
+# src/quantum_objectives.jl:203-279, src/quantum_constraints.jl:123-144.  The iso-vec of a density
+# matrix ([vec(Re rho); vec(Im rho)]), the Lindbladian `sys.𝒢` and `Isomorphisms.var_G` live in
+# PiccoloQuantumObjects 0.10 (not in the tree): their forms here are restated from memory of that
+# package [memory] -- parity for them is unpinned, like every value-level item of this path.
+# --------------------------------------------------------------------------- #
+
+
+def density_to_iso_vec(rho):
+    rho = np.asarray(rho, dtype=complex)
+    return np.concatenate([rho.real.T.reshape(-1), rho.imag.T.reshape(-1)])     # column-major vec
+
+
+def iso_vec_to_density(x):
+    n = int(round(np.sqrt(len(x) / 2)))
+    return (x[:n * n] + 1j * x[n * n:]).reshape(n, n).T
+
+
+def lindblad_generators(H_drift, H_drives, dissipators=()):
+    """(G_drift, [G_j]) of d/dt rho_iso = (G_drift + sum_j u_j G_j) rho_iso for
+    rho' = -i[H, rho] + sum_L (L rho L^† - 1/2 {L^†L, rho}), vec column-major:
+    vec(A rho B) = (B^T kron A) vec(rho); iso(M) = [[Re M, -Im M], [Im M, Re M]]."""
+    n = np.asarray(H_drift).shape[0]
+    I = np.eye(n)
+
+    def ad(H):
+        H = np.asarray(H, dtype=complex)
+        return -1j * (np.kron(I, H) - np.kron(H.T, I))
+    D = np.zeros((n * n, n * n), dtype=complex)
+    for Lop in dissipators:
+        Lop = np.asarray(Lop, dtype=complex)
+        LdL = Lop.conj().T @ Lop
+        D += np.kron(Lop.conj(), Lop) - 0.5 * np.kron(I, LdL) - 0.5 * np.kron(LdL.T, I)
+    return iso(ad(H_drift) + D), [iso(ad(h)) for h in H_drives]
+
+
+def var_G(G, G_vars):
+    """Isomorphisms.var_G: block lower-triangular generator of [x; dx/da_1; ...]:
+    d/dt x_v = G x_v + G_v x  (src/quantum_integrators.jl:149,166)."""
+    d, nv = G.shape[0], len(G_vars)
+    out = np.zeros(((1 + nv) * d, (1 + nv) * d))
+    for b in range(1 + nv):
+        out[b * d:(b + 1) * d, b * d:(b + 1) * d] = G
+    for v, Gv in enumerate(G_vars):
+        out[(v + 1) * d:(v + 2) * d, :d] = Gv
+    return out
+
+
+def density_pure_state_fidelity(x, psi):
+    """src/quantum_objectives.jl:232-239: real(psi' * rho * psi)."""
+    psi = np.asarray(psi, dtype=complex)
+    return float(np.real(psi.conj() @ iso_vec_to_density(x) @ psi))
+
+
+def free_phase_goal(U_goal, phase_map, theta, side=0):
+    D = np.diag(np.exp(1j * (np.asarray(phase_map) @ np.asarray(theta))))
+    return D @ U_goal if side == 0 else U_goal @ D
+
+
+def free_phase_fidelity(z, U_goal, phase_map, side=0):
+    """l(z) of src/quantum_objectives.jl:211-214 without the |1 - .|: z = [x; theta],
+    unitary_fidelity_loss(x, U_goal(theta)) with U_goal(theta) = diag(e^{i P theta}) U_goal."""
+    nt = np.asarray(phase_map).shape[1]
+    x, theta = (z[:-nt], z[-nt:]) if nt else (z, np.zeros(0))
+    return unitary_fidelity(x, free_phase_goal(U_goal, phase_map, theta, side))
+
+
+def free_phase_vgh(z, U_goal, phase_map, side=0):
+    """F, gradient and dense Hessian over z = [x; theta], analytically: with A(theta) the 2 x x_dim
+    matrix of the linear forms (Re, Im) of tr(U_goal(theta)' U), F = |A x|^2 / n^2; the theta
+    derivatives of A come from d/dtheta_k of the goal, -i P_k-weighted."""
+    U_goal = np.asarray(U_goal, dtype=complex)
+    P = np.asarray(phase_map, dtype=float)
+    n, nt = U_goal.shape[0], P.shape[1]
+    x, theta = (z[:-nt], z[-nt:]) if nt else (z, np.zeros(0))
+    xd = len(x)
+
+    def forms(Ug):    # rows (Re, Im) of tr(Ug' U) as linear forms of x
+        return np.array([operator_to_iso_vec(Ug), operator_to_iso_vec(1j * Ug)])
+    Ug = free_phase_goal(U_goal, P, theta, side)
+    dUg, d2Ug = [], [[None] * nt for _ in range(nt)]
+    for k in range(nt):
+        Dk = np.diag(1j * P[:, k])
+        dUg.append(Dk @ Ug if side == 0 else Ug @ Dk)
+        for l in range(nt):
+            Dkl = np.diag(-(P[:, k] * P[:, l]))
+            d2Ug[k][l] = Dkl @ Ug if side == 0 else Ug @ Dkl
+    A = forms(Ug)
+    s = A @ x                                       # (Re S, Im S)
+    w = 1.0 / n ** 2
+    dA = [forms(D) for D in dUg]
+    ds = np.array([a @ x for a in dA]).reshape(nt, 2)
+    g = np.concatenate([2 * w * (A.T @ s), 2 * w * (ds @ s)])
+    H = np.zeros((xd + nt, xd + nt))
+    H[:xd, :xd] = 2 * w * (A.T @ A)
+    for k in range(nt):
+        H[:xd, xd + k] = H[xd + k, :xd] = 2 * w * (A.T @ ds[k] + dA[k].T @ s)
+        for l in range(nt):
+            H[xd + k, xd + l] = 2 * w * (ds[k] @ ds[l] + s @ (forms(d2Ug[k][l]) @ x))
+    return w * float(s @ s), g, H
+
+
+def unitary_self_overlap(x):
+    """unitary_fidelity_loss(Ũ⃗) of src/quantum_objectives.jl:255-261: |tr(U'U)|^2 / n^2."""
+    U = iso_vec_to_operator(x)
+    return abs(np.trace(U.conj().T @ U)) ** 2 / U.shape[0] ** 2
+
+
+def sensitivity_objective(Z, N, z_dim, x_off, x_dim, times, Qs=None, scale=1.0):
+    """UnitarySensitivityObjective (:263-279): sum_t Q_t scale^4 |tr(U_t'U_t)|^2/n^2, times 1-based.
+    Returns (J, grad [len(times), x_dim], hess [len(times), x_dim, x_dim])."""
+    Zk = np.asarray(Z).reshape(N, z_dim)
+    n = int(round(np.sqrt(x_dim / 2)))
+    Qs = np.ones(len(times)) if Qs is None else np.asarray(Qs, dtype=float)
+    J, g, Hs = 0.0, [], []
+    for q, t in zip(Qs, times):
+        x = Zk[t - 1, x_off:x_off + x_dim]
+        s = float(x @ x)
+        J += q * scale ** 4 * unitary_self_overlap(x)
+        g.append(q * scale ** 4 * 4 * s * x / n ** 2)
+        Hs.append(q * scale ** 4 * (4 * s * np.eye(x_dim) + 8 * np.outer(x, x)) / n ** 2)
+    return J, np.array(g), np.array(Hs)

@@ -21,7 +21,7 @@ class QcbDesc(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in (
         "struct_bytes", "d", "c", "m", "N", "S", "z_dim", "u_off", "dt_off", "jac_mode", "device",
         "k_begin", "k_end", "force_path")] + [
-        ("x_off", c_ip), ("G_drift", c_dp), ("G_drives", c_dp)]
+        ("x_off", c_ip), ("G_drift", c_dp), ("G_drives", c_dp), ("x_index", c_ip), ("row_index", c_ip)]
 
 
 class QcbAuxDesc(ctypes.Structure):
@@ -50,6 +50,9 @@ SYMBOLS = {
     "qcb_eval_all": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "qcb_eval_all_device": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "qcb_rollout": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp]),
+    "qcb_arena_doubles": (ctypes.c_int64, [c_vp, ctypes.c_int32]),
+    "qcb_eval_arenas_device": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "qcb_assemble_device": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int64, ctypes.c_int32, c_vp, c_vp]),
     "qcb_device_alloc": (ctypes.c_int, [ctypes.c_int32, ctypes.POINTER(c_vp), ctypes.c_size_t]),
     "qcb_device_free": (None, [ctypes.c_int32, c_vp]),
     "qcb_ipc_export": (ctypes.c_int, [ctypes.c_int32, c_vp, ctypes.c_char_p]),
@@ -81,6 +84,12 @@ SYMBOLS = {
     "qcb_aux_regularizer_structure": (ctypes.c_int, [c_vp, ctypes.c_int32, c_ip, c_ip, c_lp, c_lp, c_lp]),
     "qcb_aux_regularizer_eval": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, c_ip, c_ip, c_vp, ctypes.c_double, c_dp, c_vp, c_vp]),
     "qcb_aux_timesteps_equal": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int64, c_vp, c_lp, c_lp, c_vp]),
+    "qcb_free_phase_create": (ctypes.c_int, [ctypes.POINTER(c_vp), ctypes.c_int32, c_dp, ctypes.c_int32, c_dp,
+                                             ctypes.c_int32, ctypes.c_int32]),
+    "qcb_free_phase_destroy": (None, [c_vp]),
+    "qcb_free_phase_eval": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "qcb_aux_sensitivity_eval": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                                c_ip, c_vp, ctypes.c_double, c_dp, c_vp, c_vp]),
     "qcb_fidelity_eval_batch_device_noalloc": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int64, c_vp, c_vp]),
 }
 

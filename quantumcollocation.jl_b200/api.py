@@ -48,12 +48,16 @@ class Evaluator:
         self._g0 = _colmajor(G_drift)
         self._gd = _colmajor(G_drives) if L.m else np.zeros(1)
         self._xo = np.asarray(L.x_off, dtype=np.int32)
+        self._xi = None if L.x_index is None else np.ascontiguousarray(L.x_index, dtype=np.int32).reshape(L.S, L.x_dim)
+        self._ri = None if L.row_index is None else np.ascontiguousarray(L.row_index, dtype=np.int32).reshape(L.x_dim)
         desc = _lib.QcbDesc(
             struct_bytes=ctypes.sizeof(_lib.QcbDesc), d=L.d, c=L.c, m=L.m, N=L.N, S=L.S, z_dim=L.z_dim,
             u_off=L.u_off, dt_off=L.dt_off, jac_mode=L.jac_mode, device=device, k_begin=k_begin, k_end=k_end,
             force_path=force_path,
             x_off=self._xo.ctypes.data_as(_lib.c_ip), G_drift=self._g0.ctypes.data_as(_lib.c_dp),
-            G_drives=self._gd.ctypes.data_as(_lib.c_dp))
+            G_drives=self._gd.ctypes.data_as(_lib.c_dp),
+            x_index=None if self._xi is None else self._xi.ctypes.data_as(_lib.c_ip),
+            row_index=None if self._ri is None else self._ri.ctypes.data_as(_lib.c_ip))
         h = ctypes.c_void_p()
         st = self.lib.qcb_create(ctypes.byref(h), ctypes.byref(desc))
         if st != 0:
@@ -157,6 +161,20 @@ class Evaluator:
         _sync_producers(dZ, dmu, d_delta, d_jac, d_hess)
         self._check(self.lib.qcb_eval_all_device(self.h, _ptr(dZ), _ptr(dmu), _ptr(d_delta), _ptr(d_jac), _ptr(d_hess)))
 
+    def arena_doubles(self):
+        """(Jacobian, Hessian) value-arena sizes per unit, in doubles."""
+        return self.lib.qcb_arena_doubles(self.h, 0), self.lib.qcb_arena_doubles(self.h, 1)
+
+    def eval_arenas_device(self, dZ, dmu, d_delta, d_jac_arenas, d_hess_arenas):
+        """Like eval_all_device, but the per-unit value arenas are delivered instead of COO vectors."""
+        _sync_producers(dZ, dmu, d_delta, d_jac_arenas, d_hess_arenas)
+        self._check(self.lib.qcb_eval_arenas_device(self.h, _ptr(dZ), _ptr(dmu), _ptr(d_delta), _ptr(d_jac_arenas), _ptr(d_hess_arenas)))
+
+    def assemble_device(self, d_jac_arenas, d_hess_arenas, n_units, nk_src, d_jac, d_hess):
+        """COO value vectors of `n_units` units from their arenas (runs on this handle's GPU)."""
+        _sync_producers(d_jac_arenas, d_hess_arenas, d_jac, d_hess)
+        self._check(self.lib.qcb_assemble_device(self.h, _ptr(d_jac_arenas), _ptr(d_hess_arenas), n_units, nk_src, _ptr(d_jac), _ptr(d_hess)))
+
     def rollout(self, Z, x_init=None):
         """States [S, N, x_dim] of x_{k+1} = exp(dt_k G(u_k)) x_k (x_init [S, x_dim] or knot 1 of Z)."""
         L = self.layout
@@ -199,7 +217,7 @@ class Evaluator:
 
 class Fidelity:
     """Terminal fidelity F(x_N) and its derivatives on the GPU (include/qcb200.h, qcb_fidelity_*)."""
-    UNITARY, KET, COHERENT_KET, UNITARY_SUBSPACE = 0, 1, 2, 3
+    UNITARY, KET, COHERENT_KET, UNITARY_SUBSPACE, DENSITY_PURE = 0, 1, 2, 3, 4
 
     def __init__(self, kind: int, goal, n: Optional[int] = None, subspace=None, device: int = 0):
         self.lib = _lib.load()
@@ -207,7 +225,7 @@ class Fidelity:
         if kind == self.UNITARY:
             n = goal.shape[0]; count = 1
             flat = goal.T.reshape(-1)
-        elif kind == self.KET:
+        elif kind in (self.KET, self.DENSITY_PURE):
             n = goal.shape[0]; count = 1
             flat = goal.reshape(-1)
         elif kind == self.COHERENT_KET:
@@ -241,6 +259,54 @@ class Fidelity:
     def close(self):
         if getattr(self, "h", None):
             self.lib.qcb_fidelity_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class FreePhaseFidelity:
+    """F(x, theta) = |tr(U_goal(theta)' U)|^2 / n^2 with U_goal(theta) = diag(e^{i P theta}) U_goal
+    (side 0) or U_goal diag(e^{i P theta}) (side 1) -- include/qcb200.h, qcb_free_phase_*."""
+
+    def __init__(self, U_goal, phase_map, side: int = 0, device: int = 0):
+        self.lib = _lib.load()
+        U_goal = np.asarray(U_goal, dtype=complex)
+        self.n = U_goal.shape[0]
+        P = np.asarray(phase_map, dtype=np.float64)
+        P = P.reshape(self.n, P.size // self.n)
+        self.n_theta = P.shape[1]
+        flat = U_goal.T.reshape(-1)
+        gi = np.ascontiguousarray(np.stack([flat.real, flat.imag], axis=-1).reshape(-1))
+        Pc = np.ascontiguousarray(P.T)                     # column-major n x n_theta
+        h = ctypes.c_void_p()
+        st = self.lib.qcb_free_phase_create(ctypes.byref(h), self.n, gi.ctypes.data_as(_lib.c_dp), self.n_theta,
+                                            Pc.ctypes.data_as(_lib.c_dp) if self.n_theta else None, side, device)
+        if st != 0:
+            raise _lib.QcbError(st, self.lib.qcb_last_error(None).decode())
+        self.h = h
+        self.x_dim = 2 * self.n * self.n
+        self.z_dim = self.x_dim + self.n_theta
+
+    def eval(self, x, theta, want_grad=True, want_hess=False):
+        """(F, grad over [x; theta], dense Hessian over [x; theta])."""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        theta = np.ascontiguousarray(theta, dtype=np.float64).reshape(self.n_theta)
+        assert x.shape == (self.x_dim,)
+        F = np.zeros(1)
+        g = np.empty(self.z_dim) if want_grad else None
+        H = np.empty((self.z_dim, self.z_dim)) if want_hess else None
+        st = self.lib.qcb_free_phase_eval(self.h, _ptr(x), _ptr(theta) if self.n_theta else None, _ptr(F), _ptr(g), _ptr(H))
+        if st != 0:
+            raise _lib.QcbError(st, "free-phase fidelity evaluation failed")
+        return float(F[0]), g, H
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.qcb_free_phase_destroy(self.h)
             self.h = None
 
     def __del__(self):
@@ -350,6 +416,22 @@ class Aux:
         dense = np.zeros(self.N * self.z_dim)
         np.add.at(dense, gc - 1, g)
         return dense
+
+    def sensitivity_eval(self, Z, x_off, x_dim, times, Qs=None, scale=1.0, want_hessian=True):
+        """UnitarySensitivityObjective: (J, grad [T, x_dim], hess [T, x_dim, x_dim]); times 1-based."""
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        times = np.ascontiguousarray(times, dtype=np.int32)
+        T = len(times)
+        n = int(round(np.sqrt(x_dim / 2)))
+        Qs = None if Qs is None else np.ascontiguousarray(Qs, dtype=np.float64)
+        obj = ctypes.c_double(0.0)
+        grad = np.empty((T, x_dim))
+        hess = np.empty((T, x_dim, x_dim)) if want_hessian else None
+        st = self.lib.qcb_aux_sensitivity_eval(self.h, _ptr(Z), x_off, x_dim, n, T, times.ctypes.data_as(_lib.c_ip) if T else None,
+                                               _ptr(Qs), float(scale), ctypes.byref(obj), _ptr(grad), _ptr(hess))
+        if st != 0:
+            raise _lib.QcbError(st, "sensitivity objective evaluation failed")
+        return obj.value, grad, hess
 
     def timesteps_equal(self, Z, row_base=0):
         """Rows dt_t - dt_N (t < N): (delta, (rows, cols), values)."""

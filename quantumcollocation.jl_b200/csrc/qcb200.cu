@@ -130,6 +130,28 @@ struct qcb_handle_s {
     double direct_fraction = 0.0;
     cudaEvent_t copied[2] = {nullptr, nullptr}, part_done[2] = {nullptr, nullptr};
 
+    // arena delivery (qcb_eval_arenas_device): where the per-unit value arenas of the slab are written
+    // instead of being assembled into COO vectors here; may be another GPU's memory
+    double *arena_out_j = nullptr, *arena_out_h = nullptr;
+
+    // State index map (variational integrators, src/quantum_integrators.jl:140-169: the state is a
+    // concatenation of several named components).  When the caller gives one, the kernels work on a
+    // packed copy of Z ([all panels | u | dt] per knot -- z_dim, x_off, u_off, dt_off above then
+    // describe that packed knot) and `ext` keeps the caller's layout for the structure arrays, the
+    // gather of Z / mu on the way in and the row order of delta on the way out.
+    struct Ext {
+        bool on = false, row_identity = true;
+        int z_dim = 0, u_off = 0, dt_off = 0;
+        std::vector<int> xmap, rmap;               // [S][xdim] knot offsets; [xdim] defect rows
+        int *d_xmap = nullptr, *d_rmap = nullptr;
+        double *dZ_ext = nullptr, *dZp = nullptr, *dmup = nullptr, *d_delta_p = nullptr;
+    } ext;
+    int64_t ez() const { return ext.on ? ext.z_dim : z_dim; }
+    int64_t eu() const { return ext.on ? ext.u_off : u_off; }
+    int64_t et() const { return ext.on ? ext.dt_off : dt_off; }
+    int64_t ecol_x(int s, int q) const { return ext.on ? ext.xmap[(size_t)s * xdim + q] : x_off[s] + q; }
+    int64_t erow(int r) const { return ext.on ? ext.rmap[r] : r; }
+
     UnitGeom geom() const {
         UnitGeom q;
         q.d = d; q.c = c; q.m = m; q.dp = dp; q.cp = cp; q.z_dim = z_dim; q.u_off = u_off; q.dt_off = dt_off;
@@ -170,18 +192,18 @@ std::vector<Entry> jac_pattern(qcb_handle_s *h, int s) {
     v.reserve((size_t)h->jnnz_unit);
     for (int q = 0; q < xd; ++q) {
         const int b = q / d, qq = q % d;
-        const int64_t col = h->x_off[s] + q;
+        const int64_t col = h->ecol_x(s, q);
         if (h->jac_mode == QCB_JAC_DENSE_X) {
             for (int r = 0; r < xd; ++r)
-                v.push_back({r, col, (r / d == b) ? cd.jE(r % d, qq) : cd.jZero()});
+                v.push_back({h->erow(r), col, (r / d == b) ? cd.jE(r % d, qq) : cd.jZero()});
         } else {
-            for (int rr = 0; rr < d; ++rr) v.push_back({(int64_t)b * d + rr, col, cd.jE(rr, qq)});
+            for (int rr = 0; rr < d; ++rr) v.push_back({h->erow(b * d + rr), col, cd.jE(rr, qq)});
         }
     }
     for (int j = 0; j < m; ++j)
-        for (int r = 0; r < xd; ++r) v.push_back({r, (int64_t)h->u_off + j, cd.jU(j, r)});
-    for (int r = 0; r < xd; ++r) v.push_back({r, (int64_t)h->dt_off, cd.jT(r)});
-    for (int r = 0; r < xd; ++r) v.push_back({r, (int64_t)h->z_dim + h->x_off[s] + r, cd.jOne()});
+        for (int r = 0; r < xd; ++r) v.push_back({h->erow(r), h->eu() + j, cd.jU(j, r)});
+    for (int r = 0; r < xd; ++r) v.push_back({h->erow(r), h->et(), cd.jT(r)});
+    for (int r = 0; r < xd; ++r) v.push_back({h->erow(r), h->ez() + h->ecol_x(s, r), cd.jOne()});
     std::stable_sort(v.begin(), v.end(), [](const Entry &a, const Entry &b) {
         return a.col != b.col ? a.col < b.col : a.row < b.row;
     });
@@ -195,12 +217,12 @@ std::vector<Entry> hess_pattern(qcb_handle_s *h, int s) {
     v.reserve((size_t)h->hnnz_unit);
     auto add = [&](int64_t a, int64_t b, uint32_t code) { v.push_back({std::min(a, b), std::max(a, b), code}); };
     for (int j = 0; j < m; ++j)
-        for (int i = 0; i < xd; ++i) add(h->x_off[s] + i, h->u_off + j, cd.hXU(j, i));
-    for (int i = 0; i < xd; ++i) add(h->x_off[s] + i, h->dt_off, cd.hXT(i));
+        for (int i = 0; i < xd; ++i) add(h->ecol_x(s, i), h->eu() + j, cd.hXU(j, i));
+    for (int i = 0; i < xd; ++i) add(h->ecol_x(s, i), h->et(), cd.hXT(i));
     for (int i = 0; i < m; ++i)
-        for (int j = i; j < m; ++j) add(h->u_off + i, h->u_off + j, cd.hUU(i, j));
-    for (int j = 0; j < m; ++j) add(h->u_off + j, h->dt_off, cd.hUT(j));
-    add(h->dt_off, h->dt_off, cd.hTT());
+        for (int j = i; j < m; ++j) add(h->eu() + i, h->eu() + j, cd.hUU(i, j));
+    for (int j = 0; j < m; ++j) add(h->eu() + j, h->et(), cd.hUT(j));
+    add(h->et(), h->et(), cd.hTT());
     std::stable_sort(v.begin(), v.end(), [](const Entry &a, const Entry &b) {
         return a.col != b.col ? a.col < b.col : a.row < b.row;
     });
@@ -778,6 +800,26 @@ void ensure_scratch(qcb_handle_s *h, int s_need) {
 }
 
 struct HostOut { double *delta, *jac, *hess; bool compact; };
+
+// dst[unit] = src[unit]: one arena (stride doubles) per unit, 16-byte accesses; dst may be peer memory.
+constexpr long long SHIP_PIECE = 8192;
+__global__ void __launch_bounds__(256)
+arena_ship_kernel(const double *src, long long stride, double *dst, int u0, const int *perm) {
+    const int unit = blockIdx.y;
+    const long long ug = perm ? perm[u0 + unit] : u0 + unit;
+    const long long b = (long long)blockIdx.x * SHIP_PIECE, len = min(SHIP_PIECE, stride - b);
+    const double *s = src + (long long)unit * stride + b;
+    double *o = dst + ug * stride + b;
+    if (((reinterpret_cast<uintptr_t>(o) | reinterpret_cast<uintptr_t>(s)) & 15) == 0) {
+        const double2 *s2 = reinterpret_cast<const double2 *>(s);
+        double2 *o2 = reinterpret_cast<double2 *>(o);
+        const long long n2 = len >> 1;
+        for (long long e = threadIdx.x; e < n2; e += blockDim.x) o2[e] = __ldg(s2 + e);
+        if ((len & 1) && threadIdx.x == 0) o[len - 1] = s[len - 1];
+    } else {
+        for (long long e = threadIdx.x; e < len; e += blockDim.x) o[e] = s[e];
+    }
+}
 void ensure_out(qcb_handle_s *h, double **p, size_t n);
 
 // norm pre-pass over the whole slab -> uniform number of squarings (or -1)
@@ -993,6 +1035,20 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
                                                           X.at(X.ha, h->HA), h->HA, (m + 1) * pan, h->iso ? 2.0 : 1.0);
                 ++h->launches;
             }
+            if (h->arena_out_j || h->arena_out_h) {
+                // multi-GPU delivery of the compact form: every distinct number of the unit once, stored
+                // straight into the Ipopt rank's HBM (NVLink peer stores); that rank assembles the COO vectors
+                if (wj && h->arena_out_j) {
+                    arena_ship_kernel<<<dim3((unsigned)((h->JA + SHIP_PIECE - 1) / SHIP_PIECE), (unsigned)nu), 256, 0, st>>>(
+                        X.at(X.ja, h->JA), h->JA, h->arena_out_j, u0, perm);
+                    ++h->launches;
+                }
+                if (wh && h->arena_out_h) {
+                    arena_ship_kernel<<<dim3((unsigned)((h->HA + SHIP_PIECE - 1) / SHIP_PIECE), (unsigned)nu), 256, 0, st>>>(
+                        X.at(X.ha, h->HA), h->HA, h->arena_out_h, u0, perm);
+                    ++h->launches;
+                }
+            }
             if (wj && d_jac && !compact) {
                 if (h->run_assembly) {
                     if (!h->d_jpieces) upload_pieces(h, h->h_jcode, h->jnnz_unit, &h->d_jpieces, &h->n_jpieces);
@@ -1148,9 +1204,67 @@ void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     CK(cudaGetLastError());
 }
 
+// State index map: the caller's Z / mu (device copies) -> the packed layout the kernels read.
+// One CTA per knot of the slab (plus the halo knot); mu rows are reordered from the caller's defect
+// rows to panel order.
+__global__ void pack_knots_kernel(const double *Zext, int ez, double *Zp, int zp, const int *xmap, int nx, int eu, int m,
+                                  int et, int k_lo) {
+    const long long k = k_lo + blockIdx.x;
+    const double *src = Zext + k * ez;
+    double *dst = Zp + k * zp;
+    for (int i = threadIdx.x; i < nx; i += blockDim.x) dst[i] = src[xmap[i]];
+    for (int j = threadIdx.x; j < m; j += blockDim.x) dst[nx + j] = src[eu + j];
+    if (threadIdx.x == 0) dst[nx + m] = src[et];
+}
+__global__ void permute_rows_kernel(const double *src, double *dst, const int *rmap, int xdim, long long rows, int scatter) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= rows * xdim) return;
+    const long long r = t / xdim;
+    const int i = (int)(t % xdim);
+    if (scatter) dst[r * xdim + rmap[i]] = src[t];      // panel order -> caller's rows
+    else dst[t] = src[r * xdim + rmap[i]];              // caller's rows -> panel order
+}
+
+qcb_status eval_device_inner(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_delta, double *d_jac,
+                             double *d_hess, int want, const HostOut *host, double *E_out);
+
 // common driver: device inputs -> device outputs (+ optional streamed host outputs)
 qcb_status eval_device(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_delta, double *d_jac,
                        double *d_hess, int want, const HostOut *host, double *E_out = nullptr) {
+    if (!h->ext.on) return eval_device_inner(h, dZ, dmu, d_delta, d_jac, d_hess, want, host, E_out);
+    qcb_handle_s::Ext &x = h->ext;
+    ensure_out(h, &x.dZp, (size_t)h->N * h->z_dim);
+    pack_knots_kernel<<<h->nk + 1, 128, 0, h->stream>>>(dZ, x.z_dim, x.dZp, h->z_dim, x.d_xmap, h->S * h->xdim, x.u_off,
+                                                         h->m, x.dt_off, h->k0);
+    ++h->launches;
+    const double *mu_in = dmu;
+    if (dmu && !x.row_identity) {
+        const long long rows = (long long)h->S * h->K;
+        ensure_out(h, &x.dmup, (size_t)rows * h->xdim);
+        permute_rows_kernel<<<(unsigned)((rows * h->xdim + 255) / 256), 256, 0, h->stream>>>(dmu, x.dmup, x.d_rmap, h->xdim, rows, 0);
+        ++h->launches;
+        mu_in = x.dmup;
+    }
+    CK(cudaGetLastError());
+    if (x.row_identity) return eval_device_inner(h, x.dZp, mu_in, d_delta, d_jac, d_hess, want, host, E_out);
+    // delta leaves the kernels in panel order: evaluate into a scratch vector, reorder, then deliver
+    ensure_out(h, &x.d_delta_p, (size_t)h->units * h->xdim);
+    HostOut inner;
+    if (host) { inner = *host; inner.delta = nullptr; }
+    qcb_status st = eval_device_inner(h, x.dZp, mu_in, x.d_delta_p, d_jac, d_hess, want, host ? &inner : nullptr, E_out);
+    if (st != QCB_OK) return st;
+    permute_rows_kernel<<<(unsigned)(((long long)h->units * h->xdim + 255) / 256), 256, 0, h->stream>>>(
+        x.d_delta_p, d_delta, x.d_rmap, h->xdim, h->units, 1);
+    ++h->launches;
+    CK(cudaGetLastError());
+    if (host && host->delta)
+        CK(cudaMemcpyAsync(host->delta, d_delta, (size_t)h->units * h->xdim * 8, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return QCB_OK;
+}
+
+qcb_status eval_device_inner(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_delta, double *d_jac,
+                             double *d_hess, int want, const HostOut *host, double *E_out) {
     const char *range_msg = "non-finite input or ||dt*G(u)||_1 beyond the supported range";
     if (h->large) {
         const int s = slab_squarings(h, dZ);
@@ -1287,7 +1401,11 @@ const char *qcb_last_error(qcb_handle h) { return h ? h->err.c_str() : g_create_
 qcb_status qcb_create(qcb_handle *out, const qcb_desc *desc) {
     if (!out || !desc) return fail(nullptr, QCB_ERR_ARG, "null argument");
     *out = nullptr;
-    if (desc->struct_bytes != (int32_t)sizeof(qcb_desc)) return fail(nullptr, QCB_ERR_ARG, "qcb_desc.struct_bytes mismatch");
+    const bool has_maps = desc->struct_bytes == (int32_t)sizeof(qcb_desc);     // older callers stop before x_index
+    if (!has_maps && desc->struct_bytes != (int32_t)offsetof(qcb_desc, x_index))
+        return fail(nullptr, QCB_ERR_ARG, "qcb_desc.struct_bytes mismatch");
+    const int32_t *x_index = has_maps ? desc->x_index : nullptr, *row_index = has_maps ? desc->row_index : nullptr;
+    if (row_index && !x_index) return fail(nullptr, QCB_ERR_ARG, "row_index needs x_index");
     if (desc->d < 1 || desc->c < 1 || desc->m < 0 || desc->N < 2 || desc->S < 1 || desc->z_dim < 1)
         return fail(nullptr, QCB_ERR_ARG, "bad dimensions in qcb_desc");
     if (desc->m > CONTRACT_MAXI) return fail(nullptr, QCB_ERR_ARG, "more than 32 drives are not supported");
@@ -1296,8 +1414,28 @@ qcb_status qcb_create(qcb_handle *out, const qcb_desc *desc) {
     if (desc->jac_mode != QCB_JAC_DENSE_X && desc->jac_mode != QCB_JAC_BLOCK_DIAG)
         return fail(nullptr, QCB_ERR_ARG, "bad jac_mode");
     const int xdim = desc->d * desc->c;
-    for (int s = 0; s < desc->S; ++s)
-        if (desc->x_off[s] < 0 || desc->x_off[s] + xdim > desc->z_dim) return fail(nullptr, QCB_ERR_ARG, "x_off out of the knot");
+    if (x_index) {
+        // every state entry names a distinct place of the knot, none of them a control or the timestep
+        for (int s = 0; s < desc->S; ++s) {
+            std::vector<char> used((size_t)desc->z_dim, 0);
+            for (int q = 0; q < xdim; ++q) {
+                const int o = x_index[(size_t)s * xdim + q];
+                if (o < 0 || o >= desc->z_dim || used[(size_t)o] || o == desc->dt_off || (o >= desc->u_off && o < desc->u_off + desc->m))
+                    return fail(nullptr, QCB_ERR_ARG, "x_index: entries must be distinct state positions inside the knot");
+                used[(size_t)o] = 1;
+            }
+        }
+        if (row_index) {
+            std::vector<char> used((size_t)xdim, 0);
+            for (int q = 0; q < xdim; ++q) {
+                if (row_index[q] < 0 || row_index[q] >= xdim || used[(size_t)row_index[q]]) return fail(nullptr, QCB_ERR_ARG, "row_index is not a permutation of the unit's rows");
+                used[(size_t)row_index[q]] = 1;
+            }
+        }
+    } else {
+        for (int s = 0; s < desc->S; ++s)
+            if (desc->x_off[s] < 0 || desc->x_off[s] + xdim > desc->z_dim) return fail(nullptr, QCB_ERR_ARG, "x_off out of the knot");
+    }
     if (desc->u_off < 0 || desc->u_off + desc->m > desc->z_dim || desc->dt_off < 0 || desc->dt_off >= desc->z_dim)
         return fail(nullptr, QCB_ERR_ARG, "u_off / dt_off out of the knot");
     const int K = desc->N - 1;
@@ -1323,6 +1461,19 @@ qcb_status qcb_create(qcb_handle *out, const qcb_desc *desc) {
         h->z_dim = desc->z_dim; h->u_off = desc->u_off; h->dt_off = desc->dt_off; h->jac_mode = desc->jac_mode;
         h->k0 = k0; h->k1 = k1; h->nk = k1 - k0; h->units = h->S * h->nk; h->xdim = xdim;
         h->x_off.assign(desc->x_off, desc->x_off + desc->S);
+        if (x_index) {
+            // kernels see a packed knot [panel of system 0 | ... | u | dt]; the caller's layout stays in ext
+            h->ext.on = true;
+            h->ext.z_dim = desc->z_dim; h->ext.u_off = desc->u_off; h->ext.dt_off = desc->dt_off;
+            h->ext.xmap.assign(x_index, x_index + (size_t)desc->S * xdim);
+            h->ext.rmap.resize(xdim);
+            for (int q = 0; q < xdim; ++q) {
+                h->ext.rmap[q] = row_index ? row_index[q] : q;
+                if (h->ext.rmap[q] != q) h->ext.row_identity = false;
+            }
+            for (int s = 0; s < desc->S; ++s) h->x_off[s] = s * xdim;
+            h->u_off = desc->S * xdim; h->dt_off = h->u_off + desc->m; h->z_dim = h->dt_off + 1;
+        }
         // path selection: the fused kernel needs every register of a unit in shared memory
         const size_t small_need = small_smem_doubles(h->d, h->c, h->m, 3) * sizeof(double);
         h->large = small_need > 200 * 1024;
@@ -1427,6 +1578,12 @@ qcb_status qcb_create(qcb_handle *out, const qcb_desc *desc) {
                 h->sparse_drives = true;
             }
         }
+        if (h->ext.on) {
+            CK(cudaMalloc(&h->ext.d_xmap, h->ext.xmap.size() * sizeof(int)));
+            CK(cudaMemcpy(h->ext.d_xmap, h->ext.xmap.data(), h->ext.xmap.size() * sizeof(int), cudaMemcpyHostToDevice));
+            CK(cudaMalloc(&h->ext.d_rmap, h->ext.rmap.size() * sizeof(int)));
+            CK(cudaMemcpy(h->ext.d_rmap, h->ext.rmap.data(), h->ext.rmap.size() * sizeof(int), cudaMemcpyHostToDevice));
+        }
         CK(cudaMalloc(&h->d_xoff, h->S * sizeof(int)));
         CK(cudaMemcpy(h->d_xoff, h->x_off.data(), h->S * sizeof(int), cudaMemcpyHostToDevice));
         CK(cudaMalloc(&h->d_norm, sizeof(unsigned long long)));
@@ -1449,7 +1606,8 @@ void qcb_destroy(qcb_handle h) {
     free_scratch(h);
     void *ptrs[] = {h->dG0, h->dGd, h->d_xoff, h->d_jcode, h->d_hcode, h->d_norm, h->d_bad, h->dZ, h->dmu, h->d_delta, h->d_jac, h->d_hess,
                     h->d_Eall, h->d_states, h->d_xinit, h->d_ja_all, h->d_ha_all,
-                    h->d_ell_idx, h->d_ellT_idx, h->d_ell_val, h->d_ellT_val, h->d_unit_norm, h->d_perm, h->d_jpieces, h->d_hpieces};
+                    h->d_ell_idx, h->d_ellT_idx, h->d_ell_val, h->d_ellT_val, h->d_unit_norm, h->d_perm, h->d_jpieces, h->d_hpieces,
+                    h->ext.d_xmap, h->ext.d_rmap, h->ext.dZ_ext, h->ext.dZp, h->ext.dmup, h->ext.d_delta_p};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (h->h_flags) cudaFreeHost(h->h_flags);
@@ -1505,7 +1663,7 @@ qcb_status qcb_jacobian_structure(qcb_handle h, int64_t row_base, int64_t *rows,
     for (int s = 0; s < h->S; ++s) {
         std::vector<Entry> pat = jac_pattern(h, s);
         for (int kl = 0; kl < h->nk; ++kl) {
-            const int64_t rb = row_base + ((int64_t)s * h->nk + kl) * h->xdim, cb = (int64_t)(h->k0 + kl) * h->z_dim;
+            const int64_t rb = row_base + ((int64_t)s * h->nk + kl) * h->xdim, cb = (int64_t)(h->k0 + kl) * h->ez();
             for (auto &e : pat) { rows[p] = rb + e.row + 1; cols[p] = cb + e.col + 1; ++p; }
         }
     }
@@ -1519,7 +1677,7 @@ qcb_status qcb_hessian_structure(qcb_handle h, int64_t *rows, int64_t *cols) {
     for (int s = 0; s < h->S; ++s) {
         std::vector<Entry> pat = hess_pattern(h, s);
         for (int kl = 0; kl < h->nk; ++kl) {
-            const int64_t cb = (int64_t)(h->k0 + kl) * h->z_dim;
+            const int64_t cb = (int64_t)(h->k0 + kl) * h->ez();
             for (auto &e : pat) { rows[p] = cb + e.row + 1; cols[p] = cb + e.col + 1; ++p; }
         }
     }
@@ -1531,6 +1689,13 @@ qcb_status qcb_set_structure(qcb_handle h, int64_t row_base, const int64_t *jr, 
     if (!h) return QCB_ERR_ARG;
     Codes cd{h};
     const int d = h->d, xd = h->xdim, m = h->m;
+    const int64_t EZ = h->ez(), EU = h->eu(), ET = h->et();
+    // caller-side knot offset -> panel entry of system s (-1: not a state entry); defect row -> panel entry
+    std::vector<std::vector<int>> x_of(h->S, std::vector<int>((size_t)EZ, -1));
+    for (int s = 0; s < h->S; ++s)
+        for (int q = 0; q < xd; ++q) x_of[s][(size_t)h->ecol_x(s, q)] = q;
+    std::vector<int> panel_of_row(xd);
+    for (int r = 0; r < xd; ++r) panel_of_row[(size_t)h->erow(r)] = r;
     try {
         CK(cudaSetDevice(h->device));
         if (jr && jc && jn > 0) {
@@ -1540,19 +1705,18 @@ qcb_status qcb_set_structure(qcb_handle h, int64_t row_base, const int64_t *jr, 
             for (int64_t p = 0; p < jn; ++p) {
                 const int64_t un = p / per, e = p % per;
                 const int s = (int)(un / h->nk), kl = (int)(un % h->nk), k = h->k0 + kl;
-                const int64_t r = jr[p] - 1 - row_base - un * xd;
-                const int64_t col = jc[p] - 1 - (int64_t)k * h->z_dim;
-                if (r < 0 || r >= xd) return fail(h, QCB_ERR_STRUCTURE, "Jacobian row outside its unit: entries must be grouped [system][interval]");
-                if (col < 0 || col >= 2 * (int64_t)h->z_dim) return fail(h, QCB_ERR_STRUCTURE, "Jacobian column outside knots k, k+1 of its unit");
+                const int64_t r_ext = jr[p] - 1 - row_base - un * xd;
+                const int64_t col = jc[p] - 1 - (int64_t)k * EZ;
+                if (r_ext < 0 || r_ext >= xd) return fail(h, QCB_ERR_STRUCTURE, "Jacobian row outside its unit: entries must be grouped [system][interval]");
+                if (col < 0 || col >= 2 * EZ) return fail(h, QCB_ERR_STRUCTURE, "Jacobian column outside knots k, k+1 of its unit");
+                const int r = panel_of_row[(size_t)r_ext];
                 uint32_t code = cd.jZero();
-                if (col >= h->x_off[s] && col < h->x_off[s] + xd) {
-                    const int qx = (int)(col - h->x_off[s]);
-                    if (qx / d == r / d) code = cd.jE((int)(r % d), qx % d);
-                } else if (col >= h->u_off && col < h->u_off + m) code = cd.jU((int)(col - h->u_off), (int)r);
-                else if (col == h->dt_off) code = cd.jT((int)r);
-                else if (col >= h->z_dim + h->x_off[s] && col < h->z_dim + h->x_off[s] + xd) {
-                    if (col - h->z_dim - h->x_off[s] == r) code = cd.jOne();
-                }
+                if (col < EZ && x_of[s][(size_t)col] >= 0) {
+                    const int qx = x_of[s][(size_t)col];
+                    if (qx / d == r / d) code = cd.jE(r % d, qx % d);
+                } else if (col >= EU && col < EU + m) code = cd.jU((int)(col - EU), r);
+                else if (col == ET) code = cd.jT(r);
+                else if (col >= EZ && x_of[s][(size_t)(col - EZ)] == r) code = cd.jOne();
                 uint32_t &slot = codes[(size_t)s * per + e];
                 if (kl == 0) slot = code;
                 else if (slot != code) return fail(h, QCB_ERR_STRUCTURE, "Jacobian pattern differs between intervals");
@@ -1571,17 +1735,17 @@ qcb_status qcb_set_structure(qcb_handle h, int64_t row_base, const int64_t *jr, 
             const int64_t per = hn / h->units;
             std::vector<uint32_t> codes((size_t)h->S * per);
             auto classify = [&](int s, int64_t v, int &kind, int &idx) {   // 0 x, 1 u, 2 dt, 3 other
-                if (v >= h->x_off[s] && v < h->x_off[s] + xd) { kind = 0; idx = (int)(v - h->x_off[s]); }
-                else if (v >= h->u_off && v < h->u_off + m) { kind = 1; idx = (int)(v - h->u_off); }
-                else if (v == h->dt_off) { kind = 2; idx = 0; }
+                if (x_of[s][(size_t)v] >= 0) { kind = 0; idx = x_of[s][(size_t)v]; }
+                else if (v >= EU && v < EU + m) { kind = 1; idx = (int)(v - EU); }
+                else if (v == ET) { kind = 2; idx = 0; }
                 else { kind = 3; idx = 0; }
             };
             std::vector<std::map<std::pair<int64_t, int64_t>, int64_t>> seen_pairs(h->S);   // pair -> first entry
             for (int64_t p = 0; p < hn; ++p) {
                 const int64_t un = p / per, e = p % per;
                 const int s = (int)(un / h->nk), kl = (int)(un % h->nk), k = h->k0 + kl;
-                const int64_t a = hr[p] - 1 - (int64_t)k * h->z_dim, b = hc[p] - 1 - (int64_t)k * h->z_dim;
-                if (a < 0 || a >= h->z_dim || b < 0 || b >= h->z_dim)
+                const int64_t a = hr[p] - 1 - (int64_t)k * EZ, b = hc[p] - 1 - (int64_t)k * EZ;
+                if (a < 0 || a >= EZ || b < 0 || b >= EZ)
                     return fail(h, QCB_ERR_STRUCTURE, "Hessian entry outside the knot of its unit: entries must be grouped [system][interval]");
                 int ka, ia, kb, ib;
                 classify(s, a, ka, ia);
@@ -1637,33 +1801,83 @@ qcb_status qcb_eval_all_device(qcb_handle h, const double *dZ, const double *dmu
     }
 }
 
+int64_t qcb_arena_doubles(qcb_handle h, int32_t which) { return h ? (which == 0 ? h->JA : h->HA) : 0; }
+
+qcb_status qcb_eval_arenas_device(qcb_handle h, const double *dZ, const double *dmu, double *d_delta,
+                                  double *d_jac_arenas, double *d_hess_arenas) {
+    if (!h || !dZ) return fail(h, QCB_ERR_ARG, "null argument");
+    if (!h->large) return fail(h, QCB_ERR_ARG, "arena delivery exists on the large-d path only (small units are cheaper to deliver assembled)");
+    try {
+        CK(cudaSetDevice(h->device));
+        const int want = (d_jac_arenas ? 1 : 0) | ((d_hess_arenas && dmu) ? 2 : 0);
+        if (!d_delta) { ensure_out(h, &h->d_delta, (size_t)h->units * h->xdim); d_delta = h->d_delta; }
+        h->arena_out_j = d_jac_arenas; h->arena_out_h = d_hess_arenas;
+        qcb_status st;
+        try { st = eval_device(h, dZ, dmu, d_delta, nullptr, nullptr, want, nullptr); }
+        catch (...) { h->arena_out_j = h->arena_out_h = nullptr; throw; }
+        h->arena_out_j = h->arena_out_h = nullptr;
+        return st;
+    } catch (const CudaFail &f) {
+        return fail_cuda(h, f);
+    }
+}
+
+qcb_status qcb_assemble_device(qcb_handle h, const double *d_jac_arenas, const double *d_hess_arenas, int64_t n_units,
+                               int32_t nk_src, double *d_jac_vals, double *d_hess_vals) {
+    if (!h || n_units < 0 || nk_src < 1) return fail(h, QCB_ERR_ARG, "bad argument");
+    if ((d_jac_arenas && !d_jac_vals) || (d_hess_arenas && !d_hess_vals)) return fail(h, QCB_ERR_ARG, "null output");
+    if (n_units == 0) return QCB_OK;
+    try {
+        CK(cudaSetDevice(h->device));
+        if (d_jac_arenas) {
+            if (!h->d_jpieces) upload_pieces(h, h->h_jcode, h->jnnz_unit, &h->d_jpieces, &h->n_jpieces);
+            assemble_runs_kernel<<<(unsigned)((size_t)n_units * h->n_jpieces), 256, 0, h->stream>>>(
+                d_jac_arenas, h->JA, h->d_jcode, h->jnnz_unit, h->d_jpieces, h->n_jpieces, d_jac_vals, 0, nk_src, 0, nullptr);
+            ++h->launches;
+        }
+        if (d_hess_arenas) {
+            if (!h->d_hpieces) upload_pieces(h, h->h_hcode, h->hnnz_unit, &h->d_hpieces, &h->n_hpieces);
+            assemble_runs_kernel<<<(unsigned)((size_t)n_units * h->n_hpieces), 256, 0, h->stream>>>(
+                d_hess_arenas, h->HA, h->d_hcode, h->hnnz_unit, h->d_hpieces, h->n_hpieces, d_hess_vals, 0, nk_src, 0, nullptr);
+            ++h->launches;
+        }
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(h->stream));
+        return QCB_OK;
+    } catch (const CudaFail &f) {
+        return fail_cuda(h, f);
+    }
+}
+
 qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu, double *delta, double *jac, double *hess) {
     if (!h || !Z) return fail(h, QCB_ERR_ARG, "null argument");
     if (hess && !mu) return fail(h, QCB_ERR_ARG, "Hessian values need the multipliers");
     try {
         CK(cudaSetDevice(h->device));
-        const size_t nz = (size_t)h->N * h->z_dim, nmu = (size_t)h->S * h->K * h->xdim;
+        const size_t ezd = (size_t)h->ez();          // knot width of the caller's Z
+        const size_t nz = (size_t)h->N * ezd, nmu = (size_t)h->S * h->K * h->xdim;
+        double **dZ_in = h->ext.on ? &h->ext.dZ_ext : &h->dZ;
         // large-d path: send the compact value arenas over PCIe and expand on the host cores
         // (QCB_E2E_DIRECT=1 restores device-side assembly + full-size D2H)
         // (small-d path: only when the COO vectors are >= 4x larger than the arenas, e.g. dense-x Jacobians)
         const bool compact = (jac || hess) && !getenv("QCB_E2E_DIRECT") &&
                              (h->large || (h->jnnz_unit + h->hnnz_unit) >= 4 * (h->JA + h->HA));
-        ensure_out(h, &h->dZ, nz);
+        ensure_out(h, dZ_in, nz);
         ensure_out(h, &h->d_delta, (size_t)h->units * h->xdim);
         if (jac && !compact) ensure_out(h, &h->d_jac, (size_t)h->units * h->jnnz_unit);
         if (hess) ensure_out(h, &h->dmu, nmu);
         if (hess && !compact) ensure_out(h, &h->d_hess, (size_t)h->units * h->hnnz_unit);
         CK(cudaEventRecord(h->ev[0], h->stream));
         // only the knots of this slab (plus the halo knot k_end) are needed on the device
-        CK(cudaMemcpyAsync(h->dZ + (size_t)h->k0 * h->z_dim, Z + (size_t)h->k0 * h->z_dim,
-                           (size_t)(h->nk + 1) * h->z_dim * 8, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(*dZ_in + (size_t)h->k0 * ezd, Z + (size_t)h->k0 * ezd,
+                           (size_t)(h->nk + 1) * ezd * 8, cudaMemcpyHostToDevice, h->stream));
         if (hess) {
             for (int s = 0; s < h->S; ++s) {
                 const size_t off = ((size_t)s * h->K + h->k0) * h->xdim;
                 CK(cudaMemcpyAsync(h->dmu + off, mu + off, (size_t)h->nk * h->xdim * 8, cudaMemcpyHostToDevice, h->stream));
             }
         }
-        h->xfer[0] = (int64_t)(h->nk + 1) * h->z_dim * 8 + (hess ? (int64_t)h->S * h->nk * h->xdim * 8 : 0);
+        h->xfer[0] = (int64_t)(h->nk + 1) * (int64_t)ezd * 8 + (hess ? (int64_t)h->S * h->nk * h->xdim * 8 : 0);
         h->xfer[1] = 0;   // counted where the device->host copies are issued
         h->xfer_compact = compact;
         CK(cudaEventRecord(h->ev[1], h->stream));
@@ -1671,7 +1885,7 @@ qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu, double 
         int want = (jac ? 1 : 0) | (hess ? 2 : 0);
         // in compact mode no device COO buffer exists (the arenas travel instead): `want` alone says
         // what is evaluated
-        qcb_status st = eval_device(h, h->dZ, hess ? h->dmu : nullptr, h->d_delta,
+        qcb_status st = eval_device(h, *dZ_in, hess ? h->dmu : nullptr, h->d_delta,
                                     (jac && !compact) ? h->d_jac : nullptr, (hess && !compact) ? h->d_hess : nullptr,
                                     want, &ho);
         CK(cudaEventRecord(h->ev[2], h->stream));
@@ -1702,6 +1916,7 @@ qcb_status qcb_eval_hessian(qcb_handle h, const double *Z, const double *mu, dou
 qcb_status qcb_rollout(qcb_handle h, const double *Z, const double *x_init, double *states) {
     if (!h || !Z || !states) return fail(h, QCB_ERR_ARG, "null argument");
     if (h->k0 != 0 || h->k1 != h->K) return fail(h, QCB_ERR_ARG, "a rollout needs a handle that owns the whole trajectory");
+    if (h->ext.on) return fail(h, QCB_ERR_ARG, "rollouts are not available on a handle created with a state index map");
     try {
         CK(cudaSetDevice(h->device));
         const size_t nz = (size_t)h->N * h->z_dim, dd = (size_t)h->d * h->d, ns = (size_t)h->S * h->N * h->xdim;
@@ -1768,6 +1983,7 @@ void qcb_host_free(void *ptr) { if (ptr) cudaFreeHost(ptr); }
 
 #include "qcb_fidelity.cuh"
 #include "qcb_aux.cuh"
+#include "qcb_global.cuh"
 
 // =========================================================================================
 // Allocation-free batched fidelity (declared in include/qcb200.h next to qcb_fidelity_eval)
@@ -1799,9 +2015,14 @@ fid_project_batch_kernel(const double *G, const double *X, double *p, int64_t n,
     }
 }
 __global__ void fid_grad_batch_kernel(const double *G, const double *p, double *grad, double *F,
-                                      int64_t n, int64_t R, double w) {
+                                      int64_t n, int64_t R, double w, int linear) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
     const double *pb = p + b * R;
+    if (linear) {
+        if (i < n && grad) grad[b * n + i] = w * G[i];
+        if (i == 0 && F) F[b] = w * pb[0];
+        return;
+    }
     if (i < n && grad) {
         double v = 0.0;
         for (int64_t r = 0; r < R; ++r) v = fma(G[r * n + i], pb[r], v);
@@ -1846,7 +2067,7 @@ extern "C" qcb_status qcb_fidelity_eval_batch_device_noalloc(qcb_fidelity f, con
         dim3 g1((unsigned)f->R, (unsigned)count), g2((unsigned)((n + 255) / 256), (unsigned)count);
         // every projection slot read below is written first in this same call: nothing has to start at zero
         qcb::fid_project_batch_kernel<<<g1, 256, 0, f->stream>>>(f->dG, d_X, p, n, f->R);
-        qcb::fid_grad_batch_kernel<<<g2, 256, 0, f->stream>>>(f->dG, p, d_grad, d_F, n, f->R, f->w);
+        qcb::fid_grad_batch_kernel<<<g2, 256, 0, f->stream>>>(f->dG, p, d_grad, d_F, n, f->R, f->w, f->linear);
         e = cudaGetLastError();
         if (e == cudaSuccess) e = cudaStreamSynchronize(f->stream);
     }

@@ -7,6 +7,7 @@ struct qcb_fidelity_s {
     int device = 0;
     int64_t x_dim = 0, R = 0;
     double w = 1.0;
+    int linear = 0;           // density kind: F = w * (g_0 . x), not a sum of squares
     double *dG = nullptr;     // [R][x_dim] row-major
     double *dx = nullptr, *dp = nullptr, *dgrad = nullptr, *dF = nullptr, *dH = nullptr;
     cudaStream_t stream = nullptr;
@@ -30,8 +31,14 @@ __global__ void __launch_bounds__(256) fid_project_kernel(const double *G, const
         p[blockIdx.x] = s;
     }
 }
-__global__ void fid_grad_kernel(const double *G, const double *p, double *grad, double *F, int64_t n, int64_t R, double w) {
+__global__ void fid_grad_kernel(const double *G, const double *p, double *grad, double *F, int64_t n, int64_t R, double w,
+                                int linear) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (linear) {       // F = w g.x: constant gradient, no curvature
+        if (i < n) grad[i] = w * G[i];
+        if (i == 0) *F = w * p[0];
+        return;
+    }
     if (i < n) {
         double v = 0.0;
         for (int64_t r = 0; r < R; ++r) v = fma(G[r * n + i], p[r], v);
@@ -43,11 +50,11 @@ __global__ void fid_grad_kernel(const double *G, const double *p, double *grad, 
         *F = w * f;
     }
 }
-__global__ void fid_hess_kernel(const double *G, double *H, int64_t n, int64_t R, double w) {
+__global__ void fid_hess_kernel(const double *G, double *H, int64_t n, int64_t R, double w, int linear) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
     if (i >= n) return;
     double v = 0.0;
-    for (int64_t r = 0; r < R; ++r) v = fma(G[r * n + i], G[r * n + j], v);
+    for (int64_t r = 0; r < R && !linear; ++r) v = fma(G[r * n + i], G[r * n + j], v);
     H[i + j * n] = 2.0 * w * v;
 }
 
@@ -124,6 +131,17 @@ qcb_status qcb_fidelity_create(qcb_fidelity *out, int32_t kind, int32_t n, int32
                     add_isovec(row, n, sub, colb, goal + 2 * (size_t)a * n_sub, n_sub, ph == 0 ? 1.0 : 0.0, ph == 0 ? 0.0 : 1.0);
                     std::copy(row.begin(), row.end(), G.begin() + r * xd); ++r;
                 }
+    } else if (kind == QCB_FID_DENSITY_PURE) {
+        // F = Re(psi^dagger rho psi) on rho_iso = [vec(Re rho); vec(Im rho)] (column-major vec):
+        //   sum_ij Re(c_ij) Re(rho_ij) - Im(c_ij) Im(rho_ij),  c_ij = conj(psi_i) psi_j
+        xd = 2LL * n * n; w = 1.0; R = 1;
+        G.assign(xd, 0.0);
+        for (int j = 0; j < n; ++j)
+            for (int i = 0; i < n; ++i) {
+                const double ar = goal[2 * i], ai = goal[2 * i + 1], br = goal[2 * j], bi = goal[2 * j + 1];
+                G[(size_t)i + (size_t)j * n] = ar * br + ai * bi;                           // Re(conj(a) b)
+                G[(size_t)n * n + i + (size_t)j * n] = -(ar * bi - ai * br);                // -Im(conj(a) b)
+            }
     } else {
         return fail(nullptr, QCB_ERR_ARG, "unknown fidelity kind");
     }
@@ -135,7 +153,7 @@ qcb_status qcb_fidelity_create(qcb_fidelity *out, int32_t kind, int32_t n, int32
             delete f;
             return fail(nullptr, QCB_ERR_CUDA, "no usable CUDA device: this library has no CPU fallback");
         }
-        f->device = device; f->x_dim = xd; f->R = R; f->w = w;
+        f->device = device; f->x_dim = xd; f->R = R; f->w = w; f->linear = kind == QCB_FID_DENSITY_PURE;
         CK(cudaSetDevice(device));
         CK(cudaStreamCreateWithFlags(&f->stream, cudaStreamNonBlocking));
         CK(cudaMalloc(&f->dG, G.size() * 8));
@@ -172,7 +190,7 @@ qcb_status qcb_fidelity_eval(qcb_fidelity f, const double *x, double *F, double 
         const int64_t n = f->x_dim;
         CK(cudaMemcpyAsync(f->dx, x, n * 8, cudaMemcpyHostToDevice, f->stream));
         qcb::fid_project_kernel<<<(unsigned)f->R, 256, 0, f->stream>>>(f->dG, f->dx, f->dp, n);
-        qcb::fid_grad_kernel<<<(unsigned)((n + 255) / 256), 256, 0, f->stream>>>(f->dG, f->dp, f->dgrad, f->dF, n, f->R, f->w);
+        qcb::fid_grad_kernel<<<(unsigned)((n + 255) / 256), 256, 0, f->stream>>>(f->dG, f->dp, f->dgrad, f->dF, n, f->R, f->w, f->linear);
         CK(cudaGetLastError());
         if (F) CK(cudaMemcpyAsync(F, f->dF, 8, cudaMemcpyDeviceToHost, f->stream));
         if (grad) CK(cudaMemcpyAsync(grad, f->dgrad, n * 8, cudaMemcpyDeviceToHost, f->stream));
@@ -180,7 +198,7 @@ qcb_status qcb_fidelity_eval(qcb_fidelity f, const double *x, double *F, double 
             if (!f->dH) {
                 CK(cudaMalloc(&f->dH, (size_t)n * n * 8));
                 dim3 grid((unsigned)((n + 255) / 256), (unsigned)n);
-                qcb::fid_hess_kernel<<<grid, 256, 0, f->stream>>>(f->dG, f->dH, n, f->R, f->w);
+                qcb::fid_hess_kernel<<<grid, 256, 0, f->stream>>>(f->dG, f->dH, n, f->R, f->w, f->linear);
                 CK(cudaGetLastError());
             }
             CK(cudaMemcpyAsync(hess, f->dH, (size_t)n * n * 8, cudaMemcpyDeviceToHost, f->stream));

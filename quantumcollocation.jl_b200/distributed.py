@@ -96,6 +96,115 @@ def gpu_compute(evaluator):
     return compute
 
 
+class _RootBuffers:
+    """Device buffers on the root GPU, mapped into every other rank's process with CUDA IPC."""
+
+    def __init__(self, sizes, device_index, root, group):
+        import ctypes
+        import torch
+        import torch.distributed as dist
+        from . import _lib
+        self.lib, self.dev, self.root = _lib.load(), device_index, root
+        self.rank = dist.get_rank(group)
+        self.sizes = list(sizes)
+        handles = torch.zeros(len(self.sizes), 64, dtype=torch.uint8)
+        self.base = []
+        if self.rank == root:
+            for i, n in enumerate(self.sizes):
+                p = ctypes.c_void_p()
+                if self.lib.qcb_device_alloc(device_index, ctypes.byref(p), max(n, 1) * 8) != 0:
+                    raise MemoryError("qcb_device_alloc failed")
+                buf = ctypes.create_string_buffer(64)
+                assert self.lib.qcb_ipc_export(device_index, p, buf) == 0
+                handles[i] = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8)
+                self.base.append(p.value)
+        obj = [handles.numpy().tobytes() if self.rank == root else None]
+        dist.broadcast_object_list(obj, src=root, group=group)
+        if self.rank != root:
+            raw = obj[0]
+            for i in range(len(self.sizes)):
+                p = ctypes.c_void_p()
+                if self.lib.qcb_ipc_open(device_index, raw[64 * i:64 * (i + 1)], ctypes.byref(p)) != 0:
+                    raise RuntimeError("qcb_ipc_open failed (no peer access between the GPUs?)")
+                self.base.append(p.value)
+
+    def fetch(self, i):
+        """Root only: buffer i as a host numpy array (verification)."""
+        assert self.rank == self.root
+        a = np.empty(self.sizes[i])
+        assert self.lib.qcb_device_to_host(self.dev, a.ctypes.data, self.base[i], self.sizes[i] * 8) == 0
+        return a
+
+    def close(self):
+        for p in self.base:
+            if self.rank == self.root:
+                self.lib.qcb_device_free(self.dev, p)
+            else:
+                self.lib.qcb_ipc_close(self.dev, p)
+        self.base = []
+
+
+class ArenaDelivery:
+    """The data plane of SURVEY.md 8e with the gather fused into the producing kernels AND kept compact:
+    ``broadcast`` sends Z and mu from the Ipopt rank (NCCL); every other rank's kernels store the value
+    arenas of their slab (every distinct number once: ~5x fewer bytes than the COO vectors on the unitary
+    path, whose Jacobian repeats -E per state column) into the Ipopt rank's HBM over NVLink; the Ipopt
+    rank evaluates its own slab straight into the COO vectors and, after the barrier, assembles the
+    other slabs from the delivered arenas.  S == 1 layouts on the large-d path."""
+
+    def __init__(self, evaluator, layout, device_index: int, root: int = 0, group=None):
+        import torch.distributed as dist
+        if layout.S != 1:
+            raise ValueError("arena delivery needs S == 1")
+        self.dist, self.group = dist, group
+        self.ev, self.L, self.dev, self.root = evaluator, layout, device_index, root
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        L = layout
+        self.JA, self.HA = evaluator.arena_doubles()
+        self.bounds = [slab_bounds(L.K, r, self.world) for r in range(self.world)]
+        # [0] delta, [1] Jacobian values, [2] Hessian values (the results, on the root);
+        # [3] / [4] arenas of every unit the root does not evaluate itself
+        self.buf = _RootBuffers((L.K * L.x_dim, L.K * L.jac_nnz_unit, L.K * L.hess_nnz_unit, L.K * self.JA, L.K * self.HA),
+                                device_index, root, group)
+        self.k0, self.k1 = evaluator.k_begin, evaluator.k_end
+
+    def broadcast(self, Z, mu):
+        """NCCL broadcast of Z and mu (device tensors; allocated by the caller on every rank)."""
+        import torch
+        self.dist.broadcast(Z, src=self.root, group=self.group)
+        if mu is not None:
+            self.dist.broadcast(mu, src=self.root, group=self.group)
+        torch.cuda.current_stream(Z.device).synchronize()     # the library runs on its own stream
+
+    def evaluate(self, dZ, dmu):
+        L, b, k0 = self.L, self.buf.base, self.k0
+        if self.rank == self.root:
+            self.ev.eval_all_device(dZ, dmu, b[0] + 8 * k0 * L.x_dim, b[1] + 8 * k0 * L.jac_nnz_unit,
+                                    b[2] + 8 * k0 * L.hess_nnz_unit)
+        else:
+            self.ev.eval_arenas_device(dZ, dmu, b[0] + 8 * k0 * L.x_dim, b[3] + 8 * k0 * self.JA, b[4] + 8 * k0 * self.HA)
+        self.dist.barrier(group=self.group)
+        if self.rank == self.root:
+            # every maximal run of intervals owned by other ranks (root 0: one run)
+            for a, e in self._foreign_runs():
+                self.ev.assemble_device(b[3] + 8 * a * self.JA, b[4] + 8 * a * self.HA, e - a, e - a,
+                                        b[1] + 8 * a * L.jac_nnz_unit, b[2] + 8 * a * L.hess_nnz_unit)
+
+    def _foreign_runs(self):
+        runs, K = [], self.L.K
+        if self.k0 > 0:
+            runs.append((0, self.k0))
+        if self.k1 < K:
+            runs.append((self.k1, K))
+        return runs
+
+    def fetch(self):
+        return [self.buf.fetch(i) for i in range(3)]
+
+    def close(self):
+        self.buf.close()
+
+
 class PeerDelivery:
     """Fused gather: every rank's kernels store their slab of the value vectors directly into buffers
     that live in the root GPU's HBM, mapped into each process with CUDA IPC (NVLink peer stores);

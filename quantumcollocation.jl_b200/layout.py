@@ -7,7 +7,7 @@ whatever the caller's ``NamedTrajectory`` says (reference: the flat datavec has 
 from __future__ import annotations
 
 from dataclasses import dataclass, field
-from typing import List
+from typing import List, Optional
 
 JAC_DENSE_X = 0   # x_k block of the Jacobian stored as a dense x_dim^2 block (docs-era structure)
 JAC_BLOCK_DIAG = 1  # x_k block stored as c diagonal blocks of d^2 (only feasible choice for d=128)
@@ -25,6 +25,11 @@ class KnotLayout:
     u_off: int = 0
     dt_off: int = 0
     jac_mode: int = JAC_DENSE_X
+    # optional state index map (include/qcb200.h, qcb_desc.x_index / row_index): the state is gathered
+    # from several named components -- [S][x_dim] knot offsets of the panel entries, and the position
+    # of every panel entry among the unit's defect rows (None: contiguous state at x_off, identity rows)
+    x_index: Optional[List[List[int]]] = None
+    row_index: Optional[List[int]] = None
 
     @property
     def x_dim(self) -> int:

@@ -20,8 +20,8 @@ from typing import Dict, List, Optional, Sequence
 
 import numpy as np
 
-from .api import Aux, Evaluator, Fidelity
-from .isomorphisms import G_of_H, ket_to_iso, operator_to_iso_vec
+from .api import Aux, Evaluator, Fidelity, FreePhaseFidelity
+from .isomorphisms import G_of_H, ket_to_iso, lindblad_generators, operator_to_iso_vec, var_G
 from .layout import JAC_BLOCK_DIAG, JAC_DENSE_X, KnotLayout
 
 
@@ -43,12 +43,52 @@ class QuantumSystem:
         return self.G_drift + np.tensordot(np.asarray(u, dtype=float), self.G_drives, axes=1)
 
 
+class OpenQuantumSystem:
+    """``OpenQuantumSystem(H_drift, H_drives, dissipation_operators)`` with the Lindbladian generator
+    ``.𝒢(u)`` on the density iso-vec (2 n^2 entries); here ``.G_drift`` / ``.G_drives`` hold its
+    constant and per-drive parts (dense, not skew-symmetric)."""
+
+    def __init__(self, H_drift, H_drives: Sequence, dissipation_operators: Sequence = ()):
+        self.H_drift = np.asarray(H_drift, dtype=complex)
+        self.H_drives = [np.asarray(h, dtype=complex) for h in H_drives]
+        self.dissipation_operators = [np.asarray(L, dtype=complex) for L in dissipation_operators]
+        self.levels = self.H_drift.shape[0]
+        self.n_drives = len(self.H_drives)
+        self.G_drift, self.G_drives = lindblad_generators(self.H_drift, self.H_drives, self.dissipation_operators)
+
+    def G(self, u, t: float = 0.0):
+        return self.G_drift + np.tensordot(np.asarray(u, dtype=float), self.G_drives, axes=1)
+
+
+class VariationalQuantumSystem:
+    """``VariationalQuantumSystem(H_drives, H_vars)`` (docs/literate/man/unitary_problem_templates.jl:161):
+    ``G(u)`` of the nominal system plus one generator per variation, each linear in the drives:
+    ``G_vars[v](u) = Gv_drift[v] + sum_j u_j Gv_drives[v][j]``."""
+
+    def __init__(self, H_drift, H_drives: Sequence, H_vars: Sequence, H_var_drives: Optional[Sequence] = None):
+        self.base = QuantumSystem(H_drift, H_drives)
+        self.levels, self.n_drives = self.base.levels, self.base.n_drives
+        self.Gv_drift = [G_of_H(h) for h in H_vars]
+        zero = np.zeros((2 * self.levels, 2 * self.levels))
+        self.Gv_drives = [[zero] * self.n_drives for _ in H_vars] if H_var_drives is None else \
+            [[G_of_H(h) for h in hs] for hs in H_var_drives]
+
+    def G(self, u, t: float = 0.0):
+        return self.base.G(u)
+
+    @property
+    def G_vars(self):
+        return [lambda u, v=v: self.Gv_drift[v] + np.tensordot(np.asarray(u, dtype=float), np.array(self.Gv_drives[v]), axes=1)
+                for v in range(len(self.Gv_drift))]
+
+
 class NamedTrajectory:
     """Knot-major container: components are (dim_i, N) arrays stacked in insertion order;
-    ``datavec`` is the flat ``Z`` of length ``dim * N`` (src/quantum_objectives.jl:353)."""
+    ``datavec`` is the flat ``Z`` of length ``dim * N`` (src/quantum_objectives.jl:353); global
+    variables (``global_data``) follow the knots, ``global_dim`` entries (:353)."""
 
     def __init__(self, components: Dict[str, np.ndarray], timestep: str = "dt", controls=("u",),
-                 goal: Optional[dict] = None):
+                 goal: Optional[dict] = None, global_data: Optional[Dict[str, np.ndarray]] = None):
         self.names = list(components)
         comps = OrderedDict((k, np.atleast_2d(np.asarray(v, dtype=float))) for k, v in components.items())
         self.N = next(iter(comps.values())).shape[1]
@@ -64,7 +104,13 @@ class NamedTrajectory:
         self.timestep = timestep
         self.controls = tuple(controls)
         self.goal = goal or {}
-        self.global_dim = 0
+        self.global_data = OrderedDict((k, np.atleast_1d(np.asarray(v, dtype=float))) for k, v in (global_data or {}).items())
+        self.global_dims = {k: len(v) for k, v in self.global_data.items()}
+        self.global_components, goff = {}, 0
+        for k, v in self.global_data.items():
+            self.global_components[k] = np.arange(goff, goff + len(v))
+            goff += len(v)
+        self.global_dim = goff
 
     @classmethod
     def from_jld2(cls, path: str, key: str = "traj") -> "NamedTrajectory":
@@ -103,6 +149,16 @@ class KetTrajectory:
     def __init__(self, system: QuantumSystem, psi_init, psi_goal, state_name="psi_iso", drive_name="u"):
         self.system = system
         self.init, self.goal = np.asarray(psi_init, dtype=complex), np.asarray(psi_goal, dtype=complex)
+        self.state_name, self.drive_name = state_name, drive_name
+        self.columns = 1
+
+
+class DensityTrajectory:
+    """``DensityTrajectory(sys::OpenQuantumSystem, rho_init, rho_goal)``: state = density iso-vec."""
+
+    def __init__(self, system: OpenQuantumSystem, rho_init, rho_goal, state_name="rho_iso", drive_name="u"):
+        self.system = system
+        self.init, self.goal = np.asarray(rho_init, dtype=complex), np.asarray(rho_goal, dtype=complex)
         self.state_name, self.drive_name = state_name, drive_name
         self.columns = 1
 
@@ -182,6 +238,13 @@ def BilinearIntegrator(qtraj, traj: NamedTrajectory, fused: bool = False, device
     evaluates every state of a knot in one launch (knot x sample batching).
     """
     kw = dict(device=device, force_path=force_path)
+    if isinstance(qtraj, DensityTrajectory):
+        # src/quantum_integrators.jl:52-56: BilinearIntegrator(sys.𝒢, :ρ⃗̃, :u, traj); the generator acts on
+        # the whole density iso-vec (c = 1, d = 2 n^2)
+        sys_ = qtraj.system
+        d = 2 * sys_.levels ** 2
+        L = _layout_from_traj(traj, [qtraj.state_name], qtraj.drive_name, d, 1, jac_mode)
+        return Integrator(L, sys_.G_drift[None], sys_.G_drives[None], **kw)
     if isinstance(qtraj, (UnitaryTrajectory, KetTrajectory)):
         sys_ = qtraj.system
         d = 2 * sys_.levels
@@ -203,6 +266,54 @@ def BilinearIntegrator(qtraj, traj: NamedTrajectory, fused: bool = False, device
         L = _layout_from_traj(traj, [nm], qtraj.drive_name, d, cols, jac_mode)
         out.append(Integrator(L, s.G_drift[None], s.G_drives[None], **kw))
     return out
+
+
+def _variational_integrator(sys_: VariationalQuantumSystem, traj: NamedTrajectory, names: Sequence[str], u_name: str,
+                            columns: int, scales: Sequence[float], device: int, force_path: int, jac_mode):
+    """Shared body of the two variational integrators: generator var_G(G(u), [G_v(u)/scale]) on the
+    row-stacked panel [X; X_v1; ...]; the state is gathered from the named components through the
+    state index map of qcb_desc (x_index / row_index)."""
+    d0, nb = 2 * sys_.levels, len(names)
+    if len(scales) != nb - 1 or nb - 1 != len(sys_.Gv_drift):
+        raise ValueError("one variation component and one scale per variational generator")
+    d, c = nb * d0, columns
+    G0 = var_G(sys_.base.G_drift, [g / sc for g, sc in zip(sys_.Gv_drift, scales)])
+    Gd = np.array([var_G(sys_.base.G_drives[j], [sys_.Gv_drives[v][j] / scales[v] for v in range(nb - 1)])
+                   for j in range(sys_.n_drives)]).reshape(sys_.n_drives, d, d)
+    # panel entry (block b, row r, column q) = r + b*d0 + q*d  <->  component b, entry q*d0 + r
+    x_index, row_index = np.zeros(d * c, dtype=np.int64), np.zeros(d * c, dtype=np.int64)
+    for b, nm in enumerate(names):
+        idx = traj.components[nm]
+        if len(idx) != d0 * c:
+            raise ValueError(f"state component {nm} must have {d0 * c} entries")
+        for q in range(c):
+            for r in range(d0):
+                x_index[b * d0 + r + q * d] = idx[q * d0 + r]
+                row_index[b * d0 + r + q * d] = b * d0 * c + q * d0 + r
+    u_idx, dt_idx = traj.components[u_name], traj.components[traj.timestep]
+    if jac_mode is None:
+        jac_mode = JAC_BLOCK_DIAG if d * c > 512 else JAC_DENSE_X
+    L = KnotLayout(d=d, c=c, m=len(u_idx), N=traj.N, S=1, z_dim=traj.dim, x_off=[0], u_off=int(u_idx[0]),
+                   dt_off=int(dt_idx[0]), jac_mode=jac_mode, x_index=[x_index.tolist()], row_index=row_index.tolist())
+    return Integrator(L, G0[None], Gd[None], device=device, force_path=force_path)
+
+
+def VariationalKetIntegrator(sys_: VariationalQuantumSystem, traj: NamedTrajectory, psi_name: str,
+                             variation_names: Sequence[str], u_name: str, scale: float = 1.0, device: int = 0,
+                             force_path: int = 0, jac_mode: Optional[int] = None):
+    """src/quantum_integrators.jl:140-152: state vcat(psi, variations...), G = var_G(sys.G(u), [G_v(u)/scale])."""
+    return _variational_integrator(sys_, traj, [psi_name, *variation_names], u_name, 1,
+                                   [scale] * len(variation_names), device, force_path, jac_mode)
+
+
+def VariationalUnitaryIntegrator(sys_: VariationalQuantumSystem, traj: NamedTrajectory, U_name: str,
+                                 variation_names: Sequence[str], u_name: str, scales: Optional[Sequence[float]] = None,
+                                 device: int = 0, force_path: int = 0, jac_mode: Optional[int] = None):
+    """src/quantum_integrators.jl:154-169: var_G(I (x) G0, [I (x) G_v / scale]) on vcat(U_iso, variations...)
+    = var_G(G0, [G_v/scale]) on the row-stacked panels."""
+    scales = [1.0] * len(variation_names) if scales is None else list(scales)
+    return _variational_integrator(sys_, traj, [U_name, *variation_names], u_name, sys_.levels, scales, device,
+                                   force_path, jac_mode)
 
 
 def rollout(integrator: Integrator, traj: NamedTrajectory, x_init=None) -> np.ndarray:
@@ -330,6 +441,106 @@ def CoherentKetInfidelityObjective(psi_goals, names: Sequence[str], traj: NamedT
     return TerminalObjective(Fidelity(Fidelity.COHERENT_KET, np.array(psi_goals), device=device), names, traj, Q)
 
 
+def DensityMatrixPureStateInfidelityObjective(name: str, psi_goal, traj: NamedTrajectory, Q: float = 100.0, device=0):
+    """src/quantum_objectives.jl:241-249: Q * |1 - real(psi' rho psi)| on the terminal density iso-vec."""
+    return TerminalObjective(Fidelity(Fidelity.DENSITY_PURE, np.asarray(psi_goal, dtype=complex), device=device), [name], traj, Q)
+
+
+class FreePhaseTerminalObjective:
+    """``Q * |1 - F(x_N, theta)|`` on z = [x_N; theta] (TerminalObjective with global components,
+    src/quantum_objectives.jl:215)."""
+
+    def __init__(self, fidelity: FreePhaseFidelity, name: str, theta_names: Sequence[str], traj: NamedTrajectory, Q: float):
+        self.fidelity, self.name, self.theta_names, self.Q = fidelity, name, list(theta_names), float(Q)
+        self.idx = traj.components[name]
+        self.gidx = np.concatenate([traj.global_components[n] for n in self.theta_names])
+        if len(self.gidx) != fidelity.n_theta or len(self.idx) != fidelity.x_dim:
+            raise ValueError("component sizes do not match the goal / phase map")
+
+    def _z(self, traj):
+        theta = np.concatenate([traj.global_data[n] for n in self.theta_names])
+        return np.ascontiguousarray(traj.data[self.idx, traj.N - 1]), theta
+
+    def __call__(self, traj):
+        F, _, _ = self.fidelity.eval(*self._z(traj), want_grad=False)
+        return self.Q * abs(1.0 - F)
+
+    def gradient(self, grad: np.ndarray, traj) -> np.ndarray:
+        """grad = zeros(traj.dim * traj.N + traj.global_dim)  (src/quantum_objectives.jl:353)."""
+        F, g, _ = self.fidelity.eval(*self._z(traj))
+        grad[:] = 0.0
+        sg = -np.sign(1.0 - F) * self.Q
+        grad[(traj.N - 1) * traj.dim + self.idx] = sg * g[:self.fidelity.x_dim]
+        grad[traj.N * traj.dim + self.gidx] = sg * g[self.fidelity.x_dim:]
+        return grad
+
+    def hessian_values(self, traj) -> np.ndarray:
+        """Dense block over [x_N; theta]."""
+        F, _, H = self.fidelity.eval(*self._z(traj), want_grad=False, want_hess=True)
+        return -np.sign(1.0 - F) * self.Q * H
+
+
+def UnitaryFreePhaseInfidelityObjective(U_goal, phase_map, name: str, theta_names, traj: NamedTrajectory, Q: float = 100.0,
+                                        side: int = 0, device=0):
+    """src/quantum_objectives.jl:203-226 for the goal family U_goal(theta) = diag(e^{i P theta}) U_goal
+    (side 1: U_goal diag(...)); ``theta_names`` a name or a list of global components."""
+    if isinstance(theta_names, str):
+        theta_names = [theta_names]
+    return FreePhaseTerminalObjective(FreePhaseFidelity(U_goal, phase_map, side, device), name, theta_names, traj, Q)
+
+
+class UnitarySensitivityObjective:
+    """``UnitarySensitivityObjective(name, traj, times; Qs, scale)`` (src/quantum_objectives.jl:263-279):
+    sum_t Q_t * scale^4 * |tr(U_t' U_t)|^2 / n^2 on a variational state component; times 1-based."""
+
+    def __init__(self, name: str, traj: NamedTrajectory, times: Sequence[int], Qs=None, scale: float = 1.0, device=0):
+        idx = traj.components[name]
+        self.x_off, self.x_dim = int(idx[0]), len(idx)
+        self.times = np.asarray(times, dtype=np.int64)
+        self.Qs = np.ones(len(self.times)) if Qs is None else np.asarray(Qs, dtype=float)
+        self.scale = float(scale)
+        self.aux = Aux(traj.N, traj.dim, int(traj.components[traj.timestep][0]), device=device)
+        self.cols = ((self.times - 1)[:, None] * traj.dim + idx[None, :]).reshape(-1)
+
+    def __call__(self, traj):
+        return self.aux.sensitivity_eval(traj.datavec, self.x_off, self.x_dim, self.times, self.Qs, self.scale, False)[0]
+
+    def gradient(self, grad: np.ndarray, traj) -> np.ndarray:
+        grad[:] = 0.0
+        g = self.aux.sensitivity_eval(traj.datavec, self.x_off, self.x_dim, self.times, self.Qs, self.scale, False)[1]
+        np.add.at(grad, self.cols, g.reshape(-1))
+        return grad
+
+    def hessian_values(self, traj) -> np.ndarray:
+        """[len(times), x_dim, x_dim] dense blocks."""
+        return self.aux.sensitivity_eval(traj.datavec, self.x_off, self.x_dim, self.times, self.Qs, self.scale, True)[2]
+
+
+class FinalFreePhaseFidelityConstraint:
+    """theta-parametrised ``FinalUnitaryFidelityConstraint`` (src/quantum_constraints.jl:123-144):
+    [final_fidelity - F(x_N, theta)] <= 0 (NonlinearGlobalKnotPointConstraint, times = [N])."""
+
+    def __init__(self, fidelity: FreePhaseFidelity, name: str, theta_names: Sequence[str], final_fidelity: float,
+                 traj: NamedTrajectory):
+        self._obj = FreePhaseTerminalObjective(fidelity, name, theta_names, traj, 1.0)
+        self.fidelity, self.final_fidelity = fidelity, float(final_fidelity)
+        self.equality, self.times = False, [traj.N]
+
+    def value(self, traj):
+        F, _, _ = self.fidelity.eval(*self._obj._z(traj), want_grad=False)
+        return np.array([self.final_fidelity - F])
+
+    def jacobian(self, traj):
+        """(cols [1-based into [Z; globals]], values) of the single row."""
+        _, g, _ = self.fidelity.eval(*self._obj._z(traj))
+        cols = np.concatenate([(traj.N - 1) * traj.dim + self._obj.idx, traj.N * traj.dim + self._obj.gidx]) + 1
+        return cols, -g
+
+    def hessian_of_lagrangian(self, traj, mu: float):
+        _, _, H = self.fidelity.eval(*self._obj._z(traj), want_grad=False, want_hess=True)
+        return -mu * H
+
+
 class FinalFidelityConstraint:
     """``[final_fidelity - F(x_N)] <= 0`` at knot N (equality=false, times=[traj.N])."""
 
@@ -352,9 +563,16 @@ class FinalFidelityConstraint:
         return -mu * H
 
 
-def FinalUnitaryFidelityConstraint(U_goal, name, final_fidelity, traj, subspace=None, device=0):
-    """src/quantum_constraints.jl:106-121."""
+def FinalUnitaryFidelityConstraint(U_goal, name, final_fidelity, traj, subspace=None, device=0,
+                                   theta_names=None, phase_map=None, side: int = 0):
+    """src/quantum_constraints.jl:106-121; with ``theta_names`` + ``phase_map`` the theta-parametrised
+    method (:123-144) for U_goal(theta) = diag(e^{i P theta}) U_goal."""
     U_goal = np.asarray(U_goal, dtype=complex)
+    if theta_names is not None:
+        if isinstance(theta_names, str):
+            theta_names = [theta_names]
+        return FinalFreePhaseFidelityConstraint(FreePhaseFidelity(U_goal, phase_map, side, device), name, theta_names,
+                                                final_fidelity, traj)
     if subspace is None:
         f = Fidelity(Fidelity.UNITARY, U_goal, device=device)
     else:

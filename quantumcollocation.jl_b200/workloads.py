@@ -11,7 +11,7 @@ from typing import Optional
 
 import numpy as np
 
-from .isomorphisms import G_of_H, ket_to_iso, operator_to_iso_vec
+from .isomorphisms import G_of_H, density_to_iso_vec, ket_to_iso, lindblad_generators, operator_to_iso_vec
 from .layout import JAC_BLOCK_DIAG, JAC_DENSE_X, KnotLayout
 
 X2 = np.array([[0, 1], [1, 0]], dtype=complex)
@@ -107,8 +107,37 @@ def _systems(name):
     raise KeyError(name)
 
 
+def make_lindblad(N: Optional[int] = None, seed: int = 0, u_scale: float = 0.1) -> Workload:
+    """Open 3-level transmon (cfg2's Hamiltonian) with relaxation a and dephasing a'a: the
+    DensityTrajectory / `sys.𝒢` path of src/quantum_integrators.jl:52-56 -- dense, non-skew
+    18 x 18 generator on the density iso-vec, c = 1.  States: random density matrices."""
+    a = annihilate(3)
+    nop = a.conj().T @ a
+    Hd = -0.2 / 2 * nop @ (nop - np.eye(3))
+    drives = [a + a.conj().T, 1j * (a - a.conj().T)]
+    diss = [np.sqrt(0.02) * a, np.sqrt(0.01) * nop]
+    G0, Gd = lindblad_generators(Hd, drives, diss)
+    N = N or 100
+    n, m = 3, 2
+    L = KnotLayout.smooth_pulse(2 * n * n, 1, m, N, 1, JAC_DENSE_X)
+    rng = np.random.default_rng(seed)
+    Z = np.zeros((N, L.z_dim))
+    for k in range(N):
+        A = rng.normal(size=(n, n)) + 1j * rng.normal(size=(n, n))
+        rho = A @ A.conj().T
+        Z[k, :L.x_dim] = density_to_iso_vec(rho / np.trace(rho).real)
+    Z[:, L.u_off:L.u_off + m] = np.clip(u_scale * rng.normal(size=(N, m)), -1, 1)
+    Z[:, L.u_off + m:] = 0.01 * rng.normal(size=(N, L.z_dim - L.u_off - m))
+    Z[:, L.dt_off] = 0.1 * (1 + 0.1 * rng.uniform(-1, 1, N))
+    Z[:, L.dt_off - 1] = np.concatenate([[0], np.cumsum(Z[:-1, L.dt_off])])
+    mu = rng.normal(size=(N - 1) * L.x_dim)
+    return Workload("lindblad3", L, G0[None], Gd[None], Z.reshape(-1), mu, None, "density")
+
+
 def make(name: str, N: Optional[int] = None, S: Optional[int] = None, seed: int = 0,
          jac_mode: Optional[int] = None, u_scale: float = 0.1) -> Workload:
+    if name == "lindblad3":
+        return make_lindblad(N, seed, u_scale)
     systems, dt, N0, goal, kind = _systems(name)
     if S is not None:
         systems = systems[:S]

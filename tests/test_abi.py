@@ -42,7 +42,7 @@ def test_descriptor_struct_matches_header():
     body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
     fields = re.findall(r"\b(\w+);", body)
     assert fields == [f[0] for f in _lib.QcbDesc._fields_]
-    assert ctypes.sizeof(_lib.QcbDesc) == 14 * 4 + 3 * 8
+    assert ctypes.sizeof(_lib.QcbDesc) == 14 * 4 + 5 * 8
 
 
 def test_create_rejects_bad_descriptors_and_has_no_cpu_fallback(built_libs):

@@ -277,3 +277,66 @@ def O_squarings(norm1, theta=0.5):
         t *= 2.0
         s += 1
     return s
+
+
+# ---- SURVEY 8f-2 / a3 restatements ----------------------------------------------------------------
+def test_lindblad_generator_matches_the_master_equation():
+    rng = np.random.default_rng(40)
+    n = 3
+    H = rng.normal(size=(n, n)) + 1j * rng.normal(size=(n, n)); H = H + H.conj().T
+    Hj = rng.normal(size=(n, n)) + 1j * rng.normal(size=(n, n)); Hj = Hj + Hj.conj().T
+    Ls = [rng.normal(size=(n, n)) + 1j * rng.normal(size=(n, n)) for _ in range(2)]
+    G0, Gd = O.lindblad_generators(H, [Hj], Ls)
+    r = rng.normal(size=(n, n)) + 1j * rng.normal(size=(n, n)); r = r @ r.conj().T; r /= np.trace(r)
+    u = 0.37
+    Hu = H + u * Hj
+    rhs = -1j * (Hu @ r - r @ Hu) + sum(L @ r @ L.conj().T - 0.5 * (L.conj().T @ L @ r + r @ L.conj().T @ L) for L in Ls)
+    got = (G0 + u * Gd[0]) @ O.density_to_iso_vec(r)
+    assert np.abs(got - O.density_to_iso_vec(rhs)).max() < 1e-13
+    assert abs(np.trace(O.iso_vec_to_density(got))) < 1e-13                 # trace preserving
+    assert np.abs(G0 + G0.T).max() > 1e-2                                   # not skew-symmetric
+    # without dissipation it reduces to the closed-system generator acting on both sides
+    G0c, _ = O.lindblad_generators(H, [Hj], [])
+    assert np.abs(G0c + G0c.T).max() < 1e-13
+
+
+def test_var_G_is_the_parameter_derivative_of_the_flow():
+    """d/da exp(t (G + a G_v)) x at a = 0 equals the variation block of exp(t var_G(G, [G_v])) [x; 0]."""
+    from scipy.linalg import expm
+    rng = np.random.default_rng(41)
+    d = 4
+    G = rng.normal(size=(d, d)); G = G - G.T
+    Gv = rng.normal(size=(d, d)); Gv = Gv - Gv.T
+    x = rng.normal(size=d)
+    big = expm(0.7 * O.var_G(G, [Gv])) @ np.concatenate([x, np.zeros(d)])
+    h = 1e-6
+    fd = (expm(0.7 * (G + h * Gv)) @ x - expm(0.7 * (G - h * Gv)) @ x) / (2 * h)
+    assert np.abs(big[:d] - expm(0.7 * G) @ x).max() < 1e-13 and np.abs(big[d:] - fd).max() < 1e-8
+
+
+def test_free_phase_and_sensitivity_derivatives_by_finite_differences():
+    rng = np.random.default_rng(42)
+    n, nt = 3, 2
+    Ug = np.linalg.qr(rng.normal(size=(n, n)) + 1j * rng.normal(size=(n, n)))[0]
+    P = rng.integers(-1, 2, size=(n, nt)).astype(float)
+    z = rng.normal(size=2 * n * n + nt)
+    for side in (0, 1):
+        F, g, H = O.free_phase_vgh(z, Ug, P, side)
+        assert abs(F - O.free_phase_fidelity(z, Ug, P, side)) < 1e-14
+        h = 1e-5
+        gfd = np.array([(O.free_phase_fidelity(z + h * e, Ug, P, side) - O.free_phase_fidelity(z - h * e, Ug, P, side)) / (2 * h) for e in np.eye(len(z))])
+        Hfd = np.array([(O.free_phase_vgh(z + h * e, Ug, P, side)[1] - O.free_phase_vgh(z - h * e, Ug, P, side)[1]) / (2 * h) for e in np.eye(len(z))])
+        assert np.abs(g - gfd).max() < 1e-9 and np.abs(H - Hfd).max() < 1e-9
+    N, zd = 4, 11
+    Z = rng.normal(size=N * zd)
+    J, g, Hs = O.sensitivity_objective(Z, N, zd, 1, 8, [2, 4], [1.5, 0.5], 1.3)
+    h = 1e-6
+    for i, t in enumerate([2, 4]):
+        e = np.zeros_like(Z); e[(t - 1) * zd + 1 + 3] = h
+        fd = (O.sensitivity_objective(Z + e, N, zd, 1, 8, [2, 4], [1.5, 0.5], 1.3)[0] - O.sensitivity_objective(Z - e, N, zd, 1, 8, [2, 4], [1.5, 0.5], 1.3)[0]) / (2 * h)
+        assert abs(fd - g[i, 3]) < 1e-6 * max(1, abs(fd))
+        gp = O.sensitivity_objective(Z + e, N, zd, 1, 8, [2, 4], [1.5, 0.5], 1.3)[1][i]
+        gm = O.sensitivity_objective(Z - e, N, zd, 1, 8, [2, 4], [1.5, 0.5], 1.3)[1][i]
+        assert np.abs((gp - gm) / (2 * h) - Hs[i][:, 3]).max() < 1e-5
+    psi = rng.normal(size=n) + 1j * rng.normal(size=n); psi /= np.linalg.norm(psi)
+    assert abs(O.density_pure_state_fidelity(O.density_to_iso_vec(np.outer(psi, psi.conj())), psi) - 1) < 1e-14
