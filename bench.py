@@ -170,6 +170,10 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-mix", action="store_true", help="skip the per-callback timings (profiling runs)")
     ap.add_argument("--out-mem", default="auto", choices=["auto", "pinned", "pageable"])
+    ap.add_argument("--dt-scale", type=float, default=1.0,
+                    help="multiply every timestep of the synthetic trajectory (sensitivity of the headline to ||dt*G||: "
+                         "each factor of 2 adds one squaring level)")
+    ap.add_argument("--no-small", action="store_true", help="skip the small-d configs (cfg1-4) side table")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
 
@@ -205,6 +209,8 @@ def main():
 
     w = workloads.make(args.workload, N=args.knots)
     L = w.layout
+    if args.dt_scale != 1.0:
+        w.Z.reshape(L.N, L.z_dim)[:, L.dt_off] *= args.dt_scale
     K = L.K
     k0, k1 = (K * rank) // world, (K * (rank + 1)) // world
     ev = Evaluator(L, w.G_drift, w.G_drives, device=local, k_begin=k0, k_end=k1)
@@ -322,23 +328,61 @@ def main():
             except Exception as exc:      # the objective side is auxiliary to the metric: never fail the bench on it
                 callback_mix["objective_note"] = f"not measured: {exc}"
 
-    # ---- N > 1: device-complete on the rank that hosts Ipopt -- every rank's kernels store their
-    #      slab straight into rank 0's HBM (CUDA IPC peer mapping, NVLink): the gather is fused ----
-    peer = None
+    # ---- N > 1: the data plane north_star prescribes -- Z and mu broadcast from the rank that hosts Ipopt,
+    #      every value vector complete in that rank's HBM at the end of the step.  Three drivers:
+    #      arena   compact value arenas stored over NVLink by the producing kernels, COO vectors assembled on
+    #              the Ipopt rank (the product path; this is the N > 1 `value`);
+    #      peer    the COO slabs themselves stored over NVLink (5x more bytes through one GPU's links);
+    #      nccl    plain NCCL broadcast + gather (SlabCoordinator), the baseline the fused forms must beat. ----
+    peer = plane = None
     if world > 1 and L.S == 1:
         from qcb200 import distributed as qdist
-        pd = qdist.PeerDelivery(ev, L, local)
-        pd.evaluate(dZ, dmu)
+
+        def wall(fn, steps):
+            fn()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                fn()
+            torch.cuda.synchronize()
+            return max_over_ranks(time.perf_counter() - t0) / steps
+
+        # inputs live on the Ipopt rank only; the broadcast is inside every timed step
+        bZ = dZ if rank == 0 else torch.empty_like(dZ)
+        bmu = dmu if rank == 0 else torch.empty_like(dmu)
+        del d_jac, d_hess               # the drivers own their result buffers
+        torch.cuda.empty_cache()
+        ad = qdist.ArenaDelivery(ev, L, local)
+
+        def arena_step():
+            ad.broadcast(bZ, bmu)
+            ad.evaluate(bZ, bmu)
+        dt_arena = wall(arena_step, args.steps)
+        dt_bcast = wall(lambda: ad.broadcast(bZ, bmu), args.steps)
+        plane = {"value": units_total / dt_arena, "unit": "knot-evals/s", "ms_per_step": 1e3 * dt_arena,
+                 "broadcast_ms": 1e3 * dt_bcast,
+                 "bytes_over_nvlink_per_step": int(8 * (K - (k1 - k0)) * (sum(ev.arena_doubles()) + L.x_dim)),
+                 "what": "NCCL broadcast of Z and mu from rank 0 + slab evaluation + value arenas stored into rank 0's HBM by "
+                         "the producing kernels (CUDA IPC peer mapping) + COO assembly on rank 0; ends with every value vector "
+                         "complete in rank 0's HBM"}
         barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            pd.evaluate(dZ, dmu)          # ends with a barrier: all slabs have landed
-        torch.cuda.synchronize()
-        dtp = max_over_ranks(time.perf_counter() - t0) / args.steps
+        ad.close()
+        pd = qdist.PeerDelivery(ev, L, local)
+        dtp = wall(lambda: pd.evaluate(dZ, dmu), max(1, args.steps // 2))
         peer = {"value": units_total / dtp, "unit": "knot-evals/s", "ms_per_step": 1e3 * dtp,
-                "what": "all value vectors resident in rank 0's HBM; remote ranks write through IPC-mapped peer pointers"}
+                "what": "COO slabs stored into rank 0's HBM through IPC-mapped peer pointers (no broadcast in this figure)"}
         barrier()
         pd.close()
+        try:        # NCCL baseline: broadcast + three padded gathers (needs the full vectors twice on rank 0)
+            co = qdist.SlabCoordinator(L, qdist.gpu_compute(ev), dev)
+            dtn = wall(lambda: co.evaluate(dZ, dmu) if rank == 0 else co.evaluate(), 1)
+            plane["nccl_baseline"] = {"value": units_total / dtn, "ms_per_step": 1e3 * dtn,
+                                      "what": "SlabCoordinator: dist.broadcast(Z, mu) + dist.gather of the COO slabs"}
+        except Exception as exc:
+            plane["nccl_baseline"] = {"value": None, "note": f"not measured: {type(exc).__name__}: {exc}"[:300]}
+            torch.cuda.empty_cache()
+        barrier()
+        d_jac = d_hess = None
 
     # ---------------- end-to-end through the host-buffer API (`e2e`) ----------------
     e2e = None
@@ -432,11 +476,79 @@ def main():
             shm.close()
             if rank == 0:
                 shm.unlink()
+        # host-write roofline: the same streaming stores, the same thread pool, the same result buffer
+        host_gbs = None
+        if world == 1:
+            try:
+                lib = qcb200.load_library()
+                import ctypes
+                sec = ctypes.c_double(0.0)
+                nbytes = min(8 * n_jac, 8 << 30)
+                best = None
+                for _ in range(3):
+                    lib.qcb_host_stream_fill(p_jac, nbytes, ctypes.byref(sec))
+                    best = sec.value if best is None else min(best, sec.value)
+                host_gbs = nbytes / best / 1e9
+            except Exception:
+                host_gbs = None
         e2e = {"value": units_total / (dt / args.steps), "unit": "knot-evals/s", "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "host_result_bytes_per_step": int(host_written),
                "result_buffers": ("shared pinned" if world > 1 else ("pinned" if out_pinned else "pageable")),
                "ms_per_step": 1e3 * dt / args.steps,
                "last_call_rank0_ms": tm}
+        if host_gbs:
+            e2e["host_threads"] = int(qcb200.load_library().qcb_host_threads())
+            e2e["host_write_gbs"] = host_gbs
+            e2e["achieved_host_write_gbs"] = host_written / (dt / args.steps) / 1e9
+            e2e["frac_of_host_write_peak"] = e2e["achieved_host_write_gbs"] / host_gbs
+            e2e["bound"] = ("host DRAM writes: the COO vectors (host_result_bytes_per_step) are written into the caller's "
+                            "buffers by the host cores from the compact arenas; host_write_gbs is the same pool filling "
+                            "the same buffer with streaming stores")
+
+    # ---------------- small-d configs of BASELINE.json (cfg1-4), N = 1 only ----------------
+    small_cfgs = None
+    if rank == 0 and world == 1 and not args.no_small and args.workload == "cfg5" and args.knots is None:
+        small_cfgs = {}
+        try:
+            pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0)
+        except Exception:
+            pk = 6650.0
+        flushbuf = torch.empty(64 * 1024 * 1024, dtype=torch.float64, device=dev)
+        for nm in ("cfg1", "cfg2", "cfg3", "cfg3_ket", "cfg4"):
+            try:
+                ws = workloads.make(nm)
+                Ls = ws.layout
+                evs = Evaluator(Ls, ws.G_drift, ws.G_drives, device=local)
+                sZ, smu = torch.from_numpy(ws.Z).to(dev), torch.from_numpy(ws.mu).to(dev)
+                sd = torch.empty(evs.defect_dim, dtype=torch.float64, device=dev)
+                sj = torch.empty(evs.jacobian_nnz, dtype=torch.float64, device=dev)
+                sh = torch.empty(evs.hessian_nnz, dtype=torch.float64, device=dev)
+                sst = torch.cuda.ExternalStream(evs.stream, device=dev)
+                for _ in range(3):
+                    evs.eval_all_device(sZ, smu, sd, sj, sh)
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                tot = 0.0
+                reps = 10
+                for _ in range(reps):
+                    flushbuf.add_(1.0)
+                    torch.cuda.synchronize()
+                    a.record(sst)
+                    evs.eval_all_device(sZ, smu, sd, sj, sh)
+                    b.record(sst); b.synchronize()
+                    tot += a.elapsed_time(b)
+                ms = tot / reps
+                un = Ls.S * Ls.K
+                gbs = algorithmic_bytes_per_unit(Ls) * un / (ms * 1e-3) / 1e9
+                small_cfgs[nm] = {"value": un / (ms * 1e-3), "unit": "knot-evals/s", "ms_per_step": ms, "units": un,
+                                  "d": Ls.d, "c": Ls.c, "m": Ls.m, "S": Ls.S,
+                                  "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk, "unit": "GB/s", "frac": gbs / pk,
+                                               "fp64_tflops_survey_convention": survey_flops_per_unit(Ls) * un / (ms * 1e-3) / 1e12},
+                                  "timing": "CUDA events on the library's stream around one device-resident call (launch, status "
+                                            "read-back and synchronisation included), L2 flushed between calls"}
+                evs.close()
+            except Exception as exc:
+                small_cfgs[nm] = {"value": None, "note": f"{type(exc).__name__}: {exc}"[:200]}
+        del flushbuf
 
     # ---------------- CPU baseline (rank 0, N = 1 only) ----------------
     cpu = None
@@ -487,6 +599,14 @@ def main():
                         "unit": "GB/s", "frac": gbs / pk,
                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6.65 TB/s",
                         "traffic": None, "bytes_per_unit": algorithmic_bytes_per_unit(L)}
+        slab_local = None
+        if plane is not None:
+            # N > 1: the headline is the Ipopt-rank-complete number (broadcast and delivery inside the step);
+            # the collective-free slab evaluation explains it
+            slab_local = {"value": value, "unit": "knot-evals/s", "ms_per_step": ms_dev,
+                          "what": "every rank evaluates its slab with inputs resident, results left on its own GPU "
+                                  "(CUDA events, max over ranks): no data-path exchange"}
+            value, ms_dev = plane["value"], plane["ms_per_step"]
         line = {
             "metric": "knot-pt evals/sec (defect+Jac+Hess)", "value": value, "unit": "knot-evals/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True,
@@ -494,12 +614,16 @@ def main():
             "config": {"workload": f"{args.workload}: {WORKLOAD_DESC[args.workload]}", "units": units_total, "d": L.d,
                        "c": L.c, "m": L.m, "N": L.N, "S": L.S,
                        "jac_structure": "block-diagonal" if L.jac_mode else "dense-x",
-                       "parallelism": f"time-slab x{world}" if world > 1 else "single GPU",
+                       "parallelism": (f"time-slab x{world}; Z, mu broadcast from rank 0 (NCCL), value arenas delivered to rank 0 over "
+                                       f"NVLink by the producing kernels, COO assembly on rank 0") if world > 1 else "single GPU",
                        "l2": "inputs+outputs per step exceed L2 (no flush needed)" if flush is None
                              else "L2 flushed between timed steps (512 MB read-modify-write)"},
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-            "callback_mix": callback_mix, "peer_gather": peer,
+            "callback_mix": callback_mix, "data_plane": plane, "slab_local": slab_local, "peer_gather": peer,
+            "small_configs": small_cfgs,
         }
+        if args.dt_scale != 1.0:
+            line["config"]["dt_scale"] = args.dt_scale
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
