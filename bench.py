@@ -97,8 +97,10 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_port_throughput(w, sample_units, threads, repeats=1):
-    """Oracle port (oracle/qc_port.c, built -march=native on this box) on the host cores."""
+def cpu_port_throughput(w, sample_units, threads, repeats=1, blas=True):
+    """Oracle port (oracle/qc_port.c, built -march=native on this box) on the host cores; its matrix
+    products go through numpy's bundled OpenBLAS (single-threaded per call, OpenMP over units) unless
+    blas=False (the port's own loops)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import qc_port
     import qc_oracle
@@ -109,6 +111,11 @@ def cpu_port_throughput(w, sample_units, threads, repeats=1):
         native = True
     except Exception:
         native = False
+    blas_desc = ""
+    try:
+        blas_desc = qc_port.use_numpy_openblas(native, enable=blas)
+    except Exception:
+        blas_desc = ""
     nk = max(1, min(L.K, sample_units // L.S))
     best = None
     qc_port.slot_codes(OL)          # structure set-up is not part of an evaluation
@@ -121,7 +128,18 @@ def cpu_port_throughput(w, sample_units, threads, repeats=1):
         qc_port.evaluate_coo(OL, w.G_drift, w.G_drives, w.Z, w.mu, (0, nk), threads, native, out)
         dt = time.perf_counter() - t
         best = dt if best is None else min(best, dt)
-    return nk * L.S / best, nk * L.S, native
+    return nk * L.S / best, nk * L.S, native, blas_desc
+
+
+def port_flops_per_unit(L, squarings=0):
+    """Matrix-product flops the port executes per unit (full storage, sparse drive products excluded):
+    (30 + 3 s) per-unit products and (11 + 3 s) per-drive products of 2 d^3, plus the panel products."""
+    return 2.0 * L.d ** 3 * ((30 + 3 * squarings) + L.m * (11 + 3 * squarings)) + 2.0 * L.d ** 2 * L.c * (2 * L.m + 4)
+
+
+def cpu_sample_units(L, cores, override=None):
+    """Units per CPU evaluation: the same for the cpu_baseline leg and for --impl reference."""
+    return override or (32 * cores if L.d >= 64 else 8192 * cores)
 
 
 def run_reference(args):
@@ -135,10 +153,10 @@ def run_reference(args):
     cores = os.cpu_count() or 1
     w = workloads.make(args.workload, N=args.knots)
     L = w.layout
-    per_step = max(cores, min(L.S * L.K, args.ref_units or (4 * cores if L.d >= 64 else 4096 * cores)))
+    per_step = max(cores, min(L.S * L.K, cpu_sample_units(L, cores, args.ref_units)))
     rates = []
     for i in range(args.warmup + args.steps):
-        r, n_units, native = cpu_port_throughput(w, per_step, cores)
+        r, n_units, native, blas_desc = cpu_port_throughput(w, per_step, cores)
         if i >= args.warmup:
             rates.append(r)
     v = float(np.mean(rates))
@@ -146,11 +164,13 @@ def run_reference(args):
         "impl": "reference", "metric": "knot-pt evals/sec (defect+Jac+Hess)", "value": v, "unit": "knot-evals/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * n_units / v,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {WORKLOAD_DESC.get(args.workload, '')}", "units_per_step_sample": n_units,
-                   "d": L.d, "c": L.c, "m": L.m, "N": L.N, "S": L.S},
+        "config": {"workload": f"{args.workload}: {WORKLOAD_DESC.get(args.workload, '')}", "units": L.S * L.K,
+                   "units_per_step_sample": n_units, "d": L.d, "c": L.c, "m": L.m, "N": L.N, "S": L.S},
         "cpu_baseline": {"value": v, "unit": "knot-evals/s", "cores": cores, "kind": "port",
-                         "sample": f"first {n_units} of {L.S * L.K} units per step, OpenMP over units, "
-                                   f"{'-march=native' if native else '-march=x86-64-v3'}"},
+                         "gemm": blas_desc or "the port's own loops",
+                         "gflops": v * port_flops_per_unit(L) / 1e9,
+                         "sample": f"first {n_units} of {L.S * L.K} units per step (units are independent: a per-unit rate), "
+                                   f"OpenMP over units, {'-march=native' if native else '-march=x86-64-v3'}"},
         "e2e": {"value": v, "unit": "knot-evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -295,11 +315,35 @@ def main():
         return max_over_ranks(a.elapsed_time(b)) / reps
     callback_mix = None
     if not args.no_mix:
-        t_g = timed(lambda: ev.eval_all_device(dZ, None, d_delta, None, None))
-        t_j = timed(lambda: ev.eval_all_device(dZ, None, d_delta, d_jac, None))
-        t_h = timed(lambda: ev.eval_all_device(dZ, dmu, d_delta, None, d_hess))
+        # Ipopt's protocol on an iterate: eval_g(new_x = 1) first, then eval_jac_g and eval_h with new_x = 0 --
+        # the library keeps what depends on Z alone between them (qcb_eval_all_device_x).  The three calls
+        # are timed in that order, each iteration starting from a new_x = 1 call, so that nothing is reused
+        # that a real iteration would not have.
+        def protocol(reps=3):
+            ev3 = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            acc = [0.0, 0.0, 0.0]
+            for it in range(reps + 1):
+                ev3[0].record(st)
+                ev.eval_all_device_x(dZ, None, True, d_delta, None, None)
+                ev3[1].record(st)
+                ev.eval_all_device_x(dZ, None, False, d_delta, d_jac, None)
+                ev3[2].record(st)
+                ev.eval_all_device_x(dZ, dmu, False, d_delta, None, d_hess)
+                ev3[3].record(st); ev3[3].synchronize()
+                if it:      # first round is a warm-up
+                    for q in range(3):
+                        acc[q] += ev3[q].elapsed_time(ev3[q + 1])
+            return [max_over_ranks(a) / reps for a in acc]
+        t_g, t_j, t_h = protocol()
+        t_j1 = timed(lambda: ev.eval_all_device(dZ, None, d_delta, d_jac, None))
+        t_h1 = timed(lambda: ev.eval_all_device(dZ, dmu, d_delta, None, d_hess))
         callback_mix = {"eval_g_ms": t_g, "eval_jac_g_ms": t_j, "eval_h_ms": t_h,
                         "evaluator_ms_per_ipopt_iteration": (55 * t_g + 51 * t_j + 50 * t_h) / 50.0,
+                        "eval_jac_g_ms_recomputing": t_j1, "eval_h_ms_recomputing": t_h1,
+                        "evaluator_ms_per_ipopt_iteration_recomputing": (55 * t_g + 51 * t_j1 + 50 * t_h1) / 50.0,
+                        "protocol": "per iteration eval_g with new_x = 1, then eval_jac_g and eval_h with new_x = 0 (propagators, "
+                                    "then tangents and the Jacobian arena, are reused), timed in that order; the *_recomputing "
+                                    "figures are the same callbacks without reuse",
                         "mix": "55 g : 51 jac : 50 hess per 50 iterations (docs/literate/examples/multilevel_transmon.jl:147-153)"}
         # objective side of the same log (55 f : 51 grad f): terminal infidelity + the three quadratic
         # regularisers, through the host-buffer entry points (their transfers included)
@@ -554,11 +598,20 @@ def main():
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
-        sample = args.ref_units or (32 * cores if L.d >= 64 else 8192 * cores)
-        rate, n_units, native = cpu_port_throughput(w, sample, cores)
+        sample = cpu_sample_units(L, cores, args.ref_units)
+        rate, n_units, native, blas_desc = cpu_port_throughput(w, sample, cores)
         cpu = {"value": rate, "unit": "knot-evals/s", "cores": cores, "kind": "port",
+               "gemm": blas_desc or "the port's own loops", "gflops": rate * port_flops_per_unit(L) / 1e9,
                "sample": f"first {n_units} of {units_total} units, one pass, OpenMP over units, "
                          f"{'-march=native' if native else '-march=x86-64-v3'}"}
+        try:    # the same port at one thread, and with its own (un-blocked) loops instead of the BLAS
+            r1, n1, _, _ = cpu_port_throughput(w, max(1, n_units // cores), 1)
+            cpu["one_thread"] = {"value": r1, "units": n1, "gflops": r1 * port_flops_per_unit(L) / 1e9}
+            if blas_desc:
+                r2, n2, _, _ = cpu_port_throughput(w, sample, cores, blas=False)
+                cpu["plain_loops"] = {"value": r2, "units": n2, "note": "round-1 baseline: column-axpy products, no BLAS"}
+        except Exception as exc:
+            cpu["one_thread"] = {"value": None, "note": str(exc)[:200]}
 
     if rank == 0:
         peaks = {}

@@ -142,6 +142,17 @@ qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu,
 qcb_status qcb_eval_all_device(qcb_handle h, const double *dZ, const double *dmu,
                                double *d_delta, double *d_jac_vals, double *d_hess_vals);
 
+/* The same call with Ipopt's `new_x` flag (Ipopt passes it to eval_g / eval_jac_g / eval_h: 0 means "x is
+ * the point of the previous callback").  new_x != 0: identical to qcb_eval_all_device.  new_x == 0: the
+ * caller promises that dZ holds the same values as in the previous call on this handle; what depends on
+ * Z alone (the propagators, their forward tangents, the Jacobian arena) is then taken from the handle's
+ * scratch instead of being recomputed, so that eval_g -> eval_jac_g -> eval_h on one iterate cost one
+ * pass; dmu may differ (Ipopt's new_lambda).  Results are bit-identical to the recomputing call.  Only
+ * whole-slab scratch keeps the intermediates (large-d path, slab within the scratch budget); otherwise,
+ * and on the small-d path, the call silently recomputes. */
+qcb_status qcb_eval_all_device_x(qcb_handle h, const double *dZ, const double *dmu, int32_t new_x,
+                                 double *d_delta, double *d_jac_vals, double *d_hess_vals);
+
 /* ---- rollout --------------------------------------------------------------
  * x_{k+1} = exp(dt_k G(u_k)) x_k for k = 1..N-1 with the controls and timesteps of Z held constant
  * over each interval -- the propagation behind sync_trajectory! / rollout fidelity

@@ -53,9 +53,24 @@ static void transpose(double *T, const double *A, int d) {
         for (int i = 0; i < d; ++i) T[j + (size_t)i * d] = A[i + (size_t)j * d];
 }
 
+/* Optional BLAS for the matrix products (a fair CPU denominator for the large-d shape): when the
+ * harness hands over a cblas_dgemm with 64-bit integer arguments (the OpenBLAS that numpy bundles:
+ * scipy_cblas_dgemm64_), products of dimension >= 32 go through it; OpenMP threads over units, so
+ * that BLAS must run single-threaded.  NULL: the plain loops below. */
+typedef void (*dgemm64_fn)(int order, int ta, int tb, int64_t M, int64_t N, int64_t K, double alpha,
+                           const double *A, int64_t lda, const double *B, int64_t ldb, double beta,
+                           double *C, int64_t ldc);
+static dgemm64_fn g_dgemm = 0;
+void qc_port_set_dgemm(void *fn) { g_dgemm = (dgemm64_fn)fn; }
+int qc_port_has_dgemm(void) { return g_dgemm != 0; }
+
 /* C (MxN, ld ldc) += A (MxK col-major, lda) * B (KxN col-major, ldb) */
 static void gemm_nn_acc(double *restrict C, const double *restrict A, const double *restrict B,
                         int M, int N, int K, int lda, int ldb, int ldc) {
+    if (g_dgemm && M >= 32 && K >= 32) {
+        g_dgemm(102 /* CblasColMajor */, 111, 111 /* CblasNoTrans */, M, N, K, 1.0, A, lda, B, ldb, 1.0, C, ldc);
+        return;
+    }
     int j = 0;
     for (; j + 4 <= N; j += 4) {
         double *c0 = C + (size_t)j * ldc, *c1 = c0 + ldc, *c2 = c1 + ldc, *c3 = c2 + ldc;

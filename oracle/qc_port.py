@@ -48,6 +48,44 @@ def _p(a):
     return None if a is None else a.ctypes.data_as(_dp)
 
 
+_blas = {}
+
+
+def use_numpy_openblas(native: bool = False, enable: bool = True) -> str:
+    """Route the port's matrix products (dimension >= 32) through the OpenBLAS that numpy bundles
+    (numpy.libs/libscipy_openblas64_*.so: scipy_cblas_dgemm64_, ILP64), single-threaded per call --
+    the port itself threads over units with OpenMP.  Returns a description, or "" if unavailable."""
+    lb = lib(native)
+    lb.qc_port_set_dgemm.argtypes = [ctypes.c_void_p]
+    if not enable:
+        lb.qc_port_set_dgemm(None)
+        return ""
+    if "lib" not in _blas:
+        import glob
+        cands = glob.glob(os.path.join(os.path.dirname(os.path.dirname(np.__file__)), "numpy.libs", "libscipy_openblas64_*.so"))
+        _blas["lib"] = None
+        for c in cands:
+            try:
+                B = ctypes.CDLL(c)
+                fn = ctypes.cast(B.scipy_cblas_dgemm64_, ctypes.c_void_p).value
+                B.scipy_openblas_set_num_threads64_.argtypes = [ctypes.c_int]
+                B.scipy_openblas_set_num_threads64_(1)
+                ver = ""
+                try:
+                    B.scipy_openblas_get_config64_.restype = ctypes.c_char_p
+                    ver = B.scipy_openblas_get_config64_().decode()
+                except Exception:
+                    pass
+                _blas.update(lib=B, fn=fn, desc=f"numpy's bundled OpenBLAS ({os.path.basename(c)}; {ver})".strip())
+                break
+            except Exception:
+                continue
+    if not _blas.get("lib"):
+        return ""
+    lb.qc_port_set_dgemm(_blas["fn"])
+    return _blas["desc"]
+
+
 def evaluate_arenas(layout, G0, Gd, Z, mu=None, want_jac=True, want_hess=True, k_range=None,
                     nthreads=0, native=False):
     """Returns (delta [S*nk*x_dim], jac_arena [S*nk, JA] or None, hess_arena [S*nk, HA] or None)."""

@@ -49,6 +49,7 @@ SYMBOLS = {
     "qcb_eval_hessian": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp]),
     "qcb_eval_all": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "qcb_eval_all_device": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "qcb_eval_all_device_x": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int32, c_vp, c_vp, c_vp]),
     "qcb_rollout": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp]),
     "qcb_arena_doubles": (ctypes.c_int64, [c_vp, ctypes.c_int32]),
     "qcb_eval_arenas_device": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),

@@ -161,6 +161,12 @@ class Evaluator:
         _sync_producers(dZ, dmu, d_delta, d_jac, d_hess)
         self._check(self.lib.qcb_eval_all_device(self.h, _ptr(dZ), _ptr(dmu), _ptr(d_delta), _ptr(d_jac), _ptr(d_hess)))
 
+    def eval_all_device_x(self, dZ, dmu, new_x, d_delta, d_jac, d_hess):
+        """eval_all_device with Ipopt's new_x flag: new_x = False reuses what the previous call on the
+        same Z left in the handle's scratch (include/qcb200.h, qcb_eval_all_device_x)."""
+        _sync_producers(dZ, dmu, d_delta, d_jac, d_hess)
+        self._check(self.lib.qcb_eval_all_device_x(self.h, _ptr(dZ), _ptr(dmu), 1 if new_x else 0, _ptr(d_delta), _ptr(d_jac), _ptr(d_hess)))
+
     def arena_doubles(self):
         """(Jacobian, Hessian) value-arena sizes per unit, in doubles."""
         return self.lib.qcb_arena_doubles(self.h, 0), self.lib.qcb_arena_doubles(self.h, 1)

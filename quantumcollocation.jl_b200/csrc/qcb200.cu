@@ -98,7 +98,7 @@ struct qcb_handle_s {
 
     // large-path scratch
     int chunk_units = 0, s_cap = -1;
-    double *sc_fixed = nullptr, *sc_E = nullptr, *sc_W = nullptr, *sc_dslot = nullptr, *sc_L[2] = {nullptr, nullptr};
+    double *sc_fixed = nullptr, *sc_E = nullptr, *sc_W = nullptr, *sc_dslot = nullptr, *sc_L = nullptr;   // sc_L: [s_cap + 1] levels
     double *sc_XP = nullptr, *sc_MP = nullptr, *sc_EX = nullptr, *sc_ja = nullptr, *sc_ha = nullptr;
     double *sc_H = nullptr, *sc_c1 = nullptr, *sc_c2 = nullptr, *sc_c3 = nullptr, *sc_tau = nullptr, *sc_ntau = nullptr;
     int small_threads = 0;
@@ -129,6 +129,13 @@ struct qcb_handle_s {
     // host DRAM write bandwidth (~107 GB/s), so splitting the work between them gains nothing.
     double direct_fraction = 0.0;
     cudaEvent_t copied[2] = {nullptr, nullptr}, part_done[2] = {nullptr, nullptr};
+
+    // What the scratch still holds of the last evaluation's Z (new_x = 0 calls reuse it): bit0 the
+    // propagator chain (G, A, powers, E levels, E X), bit1 the forward tangents (per-drive registers,
+    // L_j at every level, G E, the Jacobian arena).  Valid only for device-resident whole-slab calls.
+    int cache_have = 0;
+    int cache_s_slab = -1;
+    int reuse = 0;                 // set by the *_x entry points for the call in flight
 
     // arena delivery (qcb_eval_arenas_device): where the per-unit value arenas of the slab are written
     // instead of being assembled into COO vectors here; may be another GPU's memory
@@ -525,7 +532,6 @@ struct LargeExec {
     int u0;        // slab-local index of the chunk's first unit
     int s;         // squarings (uniform)
     int level = 0;
-    int cur = 0;   // which L buffer holds the current level
     long long dd, pan;
     double *ja = nullptr, *ha = nullptr;   // value arenas (BASE pointers of the scratch arrays: see ubase)
     // Lane support: squaring classes run concurrently on two streams, each on its own slice of the
@@ -544,6 +550,8 @@ struct LargeExec {
     }
     Opnd W(int lvl) const { return mat(h->sc_W + (long long)lvl * h->chunk_units * dd, dd); }
     Opnd fixed(int r) const { return mat(h->sc_fixed + (long long)r * h->chunk_units * dd, dd); }
+    // L_j of every squaring level stays (a later Hessian call on the same Z contracts against each of them)
+    Opnd Llev(int lvl) const { return mat(h->sc_L + (long long)lvl * h->chunk_units * h->m * dd, (long long)h->m * dd, dd); }
     Opnd reg(int r) const {
         if (r < QR_NUM_FIXED) return fixed(r);
         switch (r) {
@@ -554,8 +562,8 @@ struct LargeExec {
         case QR_E0: return E(0);
         case QR_W0: return W(0);
         case QR_GJ: return mat(h->dGd, 0, dd, (long long)h->m * dd);
-        case QR_L: return mat(h->sc_L[cur], (long long)h->m * dd, dd);
-        case QR_LN: return mat(h->sc_L[cur ^ 1], (long long)h->m * dd, dd);
+        case QR_L: return Llev(level);
+        case QR_LN: return Llev(level + 1);
         default: return mat(h->sc_dslot + (long long)qcb_dslot(r) * h->chunk_units * h->m * dd, (long long)h->m * dd, dd);
         }
     }
@@ -671,7 +679,8 @@ struct LargeExec {
 };
 
 void free_scratch(qcb_handle_s *h) {
-    double **ptrs[] = {&h->sc_fixed, &h->sc_E, &h->sc_W, &h->sc_dslot, &h->sc_L[0], &h->sc_L[1], &h->sc_XP, &h->sc_MP,
+    h->cache_have = 0;
+    double **ptrs[] = {&h->sc_fixed, &h->sc_E, &h->sc_W, &h->sc_dslot, &h->sc_L, &h->sc_XP, &h->sc_MP,
                        &h->sc_EX, &h->sc_ja, &h->sc_ha, &h->sc_H, &h->sc_c1, &h->sc_c2, &h->sc_c3, &h->sc_tau, &h->sc_ntau};
     for (auto p : ptrs)
         if (*p) { cudaFree(*p); *p = nullptr; }
@@ -696,6 +705,7 @@ void free_scratch(qcb_handle_s *h) {
 // the expansion pipeline starts after a few milliseconds instead of a third of the evaluation.
 int compact_step(const qcb_handle_s *h) {
     if (getenv("QCB_E2E_BIG_CHUNKS")) return h->chunk_units;
+    if (const char *e = getenv("QCB_E2E_UNITS")) return (int)std::min<long long>(h->chunk_units, std::max(1L, atol(e)));
     const long long slots = (long long)h->n_sm * (h->iso ? 2 : 1);
     const long long tiles = h->iso ? (h->dp / 128) : ((h->dp % 128 == 0) ? (long long)(h->dp / 128) * (h->dp / 128)
                                                                           : (long long)(h->dp / 64) * (h->dp / 64));
@@ -735,7 +745,7 @@ void ensure_compact(qcb_handle_s *h) {
 
 size_t scratch_bytes_per_unit(const qcb_handle_s *h, int s_cap) {
     const size_t dd = (size_t)h->msz, pan = (size_t)h->dp * h->cp;
-    size_t n = (QR_NUM_FIXED + 2 * (size_t)(s_cap + 1) + (size_t)(QCB_NUM_DSLOTS + 2) * h->m) * dd;
+    size_t n = (QR_NUM_FIXED + 1 + 2 * (size_t)(s_cap + 1) + (size_t)(QCB_NUM_DSLOTS + s_cap + 1) * h->m) * dd;
     n += 3 * pan + h->JA + h->HA + (size_t)h->m * h->m + 2 * h->m + 3;
     return n * sizeof(double);
 }
@@ -750,7 +760,7 @@ void ensure_scratch(qcb_handle_s *h, int s_need) {
     {
         size_t free_b = 0, total_b = 0;
         if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess)
-            budget_mb = std::min<size_t>(24576, std::max<size_t>(512, (free_b >> 20) / 4));
+            budget_mb = std::min<size_t>(40960, std::max<size_t>(512, (free_b >> 20) / 4));
         else
             cudaGetLastError();
     }
@@ -779,12 +789,11 @@ void ensure_scratch(qcb_handle_s *h, int s_need) {
     h->chunk_units = (int)cu;
     const size_t dd = (size_t)h->msz, pan = (size_t)h->dp * h->cp, n = (size_t)cu;
     const size_t mm = std::max(1, h->m);
-    CK(cudaMalloc(&h->sc_fixed, QR_NUM_FIXED * n * dd * 8));
+    CK(cudaMalloc(&h->sc_fixed, (QR_NUM_FIXED + 1) * n * dd * 8));     // + one register for G E
     CK(cudaMalloc(&h->sc_E, (size_t)(s_cap + 1) * n * dd * 8));
     CK(cudaMalloc(&h->sc_W, (size_t)(s_cap + 1) * n * dd * 8));
     CK(cudaMalloc(&h->sc_dslot, (size_t)QCB_NUM_DSLOTS * n * mm * dd * 8));
-    CK(cudaMalloc(&h->sc_L[0], n * mm * dd * 8));
-    CK(cudaMalloc(&h->sc_L[1], n * mm * dd * 8));
+    CK(cudaMalloc(&h->sc_L, (size_t)(s_cap + 1) * n * mm * dd * 8));
     CK(cudaMalloc(&h->sc_XP, n * pan * 8));
     CK(cudaMalloc(&h->sc_MP, n * pan * 8));
     CK(cudaMalloc(&h->sc_EX, n * pan * 8));
@@ -904,8 +913,13 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     // streams.  A small class (a few dozen units: launches of one or two CTA waves) then fills the
     // SM slots the big class leaves idle in its wave tails instead of serialising ~50 under-filled
     // launches behind it -- what strong scaling over 8 GPUs (250 units per GPU) otherwise pays for.
-    const bool lanes = perm && h->chunk_units >= h->units && (long long)h->m * dd >= (long long)h->dp * h->dp &&
-                       !h->profiling && !getenv("QCB_NO_LANES");   // per-launch timing needs kernels that run alone
+    // When the scratch holds the whole slab every chunk works on its own slice (offset = its first
+    // position): nothing is overwritten by a later chunk, which is what lets a new_x = 0 call find the
+    // previous call's intermediates in place.
+    const bool slices = !host && !E_out && h->chunk_units >= h->units && (long long)h->m * dd >= (long long)h->dp * h->dp;
+    const bool lanes = perm && slices && !h->profiling && !getenv("QCB_NO_LANES");   // per-launch timing needs kernels that run alone
+    const int reuse = slices ? (h->reuse & h->cache_have) : 0;
+    h->cache_have = 0;              // re-established below once this call's launches are queued
     if (lanes) {
         if (!h->stream2) CK(cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking));
         if (!h->lane_ev[0]) for (int i = 0; i < 2; ++i) CK(cudaEventCreateWithFlags(&h->lane_ev[i], cudaEventDisableTiming));
@@ -921,7 +935,7 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             if (class_idx < h->h_class_end.size()) nu = std::min(nu, h->h_class_end[class_idx] - u0);
         }
         nu_next = nu;
-        const long long ub = lanes ? u0 : 0;                           // scratch slice of this chunk
+        const long long ub = slices ? u0 : 0;                          // scratch slice of this chunk
         cudaStream_t st = (lanes && (chunk_idx & 1)) ? h->stream2 : h->stream;
         // squarings of this chunk: what the largest ||dt G(u)||_1 among its units needs (smooth pulses
         // have slowly varying norms, so quiet stretches of the trajectory skip levels the peaks need)
@@ -945,21 +959,26 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         // chunk are assembled on the device and DMA'd in full, the rest travel as compact arenas
         const int nd = compact ? std::min(h->part_units, (int)(h->direct_fraction * nu)) : 0;
         Opnd G = X.fixed(QR_G), A = X.fixed(QR_A);
-        build_G_kernel<<<nu, 256, 0, st>>>(q, dZ, u0, const_cast<double *>(G.p), dd, h->d_norm, h->d_bad, nullptr, perm);
-        ++h->launches;
+        if (!(reuse & 1)) {
+            build_G_kernel<<<nu, 256, 0, st>>>(q, dZ, u0, const_cast<double *>(G.p), dd, h->d_norm, h->d_bad, nullptr, perm);
+            ++h->launches;
+        }
+        // panels of X and M, tau, A = tau G (cheap; M changes with the multipliers even when Z does not)
         prep_unit_kernel<<<nu, 256, 0, st>>>(q, dZ, wh ? dmu : nullptr, u0, s, G.p, const_cast<double *>(A.p), dd,
                                                      X.at(h->sc_XP, pan), wh ? X.at(h->sc_MP, pan) : nullptr, pan, X.at(h->sc_tau, 1),
                                                      X.at(h->sc_ntau, 1), perm);
         ++h->launches;
         CK(cudaGetLastError());
         Opnd XP = X.mat(h->sc_XP, pan), MP = X.mat(h->sc_MP, pan), EXp = X.mat(h->sc_EX, pan);
-        // polynomial + squarings
-        X.level = 0;
-        for (int i = 0; i < QCB_NOPS(QCB_P1); ++i) X.run(QCB_P1[i], 1);
-        for (int l = 0; l < s; ++l) { X.level = l; X.run(QCB_P2[0], 1); }
         Opnd Ef = X.E(s);
-        // defect
-        X.product(EXp, Ef, 0, XP, 0, h->dp, h->cp, h->dp, 1, 1.0, nullptr);
+        if (!(reuse & 1)) {
+            // polynomial + squarings
+            X.level = 0;
+            for (int i = 0; i < QCB_NOPS(QCB_P1); ++i) X.run(QCB_P1[i], 1);
+            for (int l = 0; l < s; ++l) { X.level = l; X.run(QCB_P2[0], 1); }
+            // defect
+            X.product(EXp, Ef, 0, XP, 0, h->dp, h->cp, h->dp, 1, 1.0, nullptr);
+        }
         delta_kernel<<<nu, 256, 0, st>>>(q, dZ, X.at(h->sc_EX, pan), pan, d_delta, u0, perm);
         ++h->launches;
         if (E_out) {      // rollouts: keep the (unpadded, full) propagator of every unit
@@ -968,10 +987,16 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             ++h->launches;
         }
         if (wj || wh) {
+            const bool tangents = !(reuse & 2);      // forward tangents, L_j levels, G E and the Jacobian arena
             if (wh) {
                 if (h->iso) {   // W = M X^T is a general matrix: project it onto the iso algebra (half storage)
-                    // W (dp x dp per unit) borrows the head of this lane's slice of per-drive slot 0
-                    double *wfull = h->sc_dslot + ub * (long long)h->m * dd;
+                    // W (dp x dp per unit) borrows the head of this slice of the per-drive temporary U (dead
+                    // until the first second-order product; the persistent per-drive registers stay intact)
+                    // (with a single drive in half storage U is smaller than W: the head of the whole per-drive
+                    // region is used then, and nothing is kept across calls -- see `slices`)
+                    double *wfull = ((long long)h->m * dd >= (long long)h->dp * h->dp)
+                                        ? h->sc_dslot + ((long long)qcb_dslot(QR_U) * h->chunk_units + ub) * h->m * dd
+                                        : h->sc_dslot + ub * (long long)h->m * dd;
                     Opnd Wfull = X.mat(wfull, (long long)h->dp * h->dp);
                     Wfull.p = wfull;
                     X.product(Wfull, MP, 0, XP, 1, h->dp, h->dp, h->cp, 1, 1.0, nullptr, true);
@@ -985,9 +1010,9 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
                 X.level = 0;
                 for (int i = 0; i < QCB_NOPS(QCB_P4); ++i) X.run(QCB_P4[i], 1);
             }
-            X.level = 0; X.cur = 0;
+            X.level = 0;
             if (m > 0) {
-                for (int i = 0; i < QCB_NOPS(QCB_P5); ++i) X.run(QCB_P5[i], m);
+                if (tangents) for (int i = 0; i < QCB_NOPS(QCB_P5); ++i) X.run(QCB_P5[i], m);
                 if (wh) {   // second order: one product per node and direction, then m x m contractions
                     for (int i = 0; i < QCB_NOPS(QCB_P6); ++i) {
                         X.run(QCB_P6[i], m);
@@ -1000,24 +1025,27 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
                         X.run(QCB_P7U[0], m);
                         X.contract(X.reg(QR_U), m, X.reg(QR_L), m, X.at(h->sc_H, (long long)std::max(1, m) * std::max(1, m)), 1);
                     }
-                    X.run(QCB_P7L[0], m);
-                    X.cur ^= 1;
+                    if (tangents) X.run(QCB_P7L[0], m);
                 }
             }
-            // final blocks
-            Opnd GE = X.fixed(QR_A2), WE = X.fixed(QR_A3), GW = X.fixed(QR_A4), L = X.reg(QR_L);
-            X.product(GE, G, 0, Ef, 0, h->dp, ncol, h->dp, 1, 1.0, nullptr);
+            // final blocks.  G E has a register of its own (the powers A2..A4 must survive for a later
+            // Hessian call on the same Z); W E^T and G^T W reuse reverse-sweep registers that are dead by now
+            X.level = s;
+            Opnd GE = X.fixed(QR_NUM_FIXED), WE = X.fixed(QR_ZB1), GW = X.fixed(QR_ZB2), L = X.reg(QR_L);
             const long long esz = (long long)h->dp * h->dp;   // the arena always holds the full E
-            Opnd JU = X.mat(X.ja + esz, h->JA, pan), JT = X.mat(X.ja + esz + m * pan, h->JA);
-            if (m > 0) X.product(JU, L, 0, XP, 0, h->dp, h->cp, h->dp, m, 1.0, X.at(h->sc_ntau, 1));
-            X.product(JT, GE, 0, XP, 0, h->dp, h->cp, h->dp, 1, -1.0, nullptr);
-            arena_consts_kernel<<<(nu + 127) / 128, 128, 0, st>>>(X.at(X.ja, h->JA), h->JA, esz + (m + 1) * pan, nu);
-            if (h->iso) {   // right block column of E from the computed left one: the COO x-block is then c
-                            // contiguous copies of -E (long runs for the device gather and the host expansion)
-                iso_expand_kernel<<<nu, 256, 0, st>>>(X.at(X.ja, h->JA), h->JA, h->dp);
+            if (tangents) {
+                X.product(GE, G, 0, Ef, 0, h->dp, ncol, h->dp, 1, 1.0, nullptr);
+                Opnd JU = X.mat(X.ja + esz, h->JA, pan), JT = X.mat(X.ja + esz + m * pan, h->JA);
+                if (m > 0) X.product(JU, L, 0, XP, 0, h->dp, h->cp, h->dp, m, 1.0, X.at(h->sc_ntau, 1));
+                X.product(JT, GE, 0, XP, 0, h->dp, h->cp, h->dp, 1, -1.0, nullptr);
+                arena_consts_kernel<<<(nu + 127) / 128, 128, 0, st>>>(X.at(X.ja, h->JA), h->JA, esz + (m + 1) * pan, nu);
                 ++h->launches;
+                if (h->iso) {   // right block column of E from the computed left one: the COO x-block is then c
+                                // contiguous copies of -E (long runs for the device gather and the host expansion)
+                    iso_expand_kernel<<<nu, 256, 0, st>>>(X.at(X.ja, h->JA), h->JA, h->dp);
+                    ++h->launches;
+                }
             }
-            ++h->launches;
             if (wh) {
                 Opnd Wt = X.W(s);
                 Opnd HXU = X.mat(X.ha, h->HA, pan), HXT = X.mat(X.ha + m * pan, h->HA);
@@ -1142,6 +1170,10 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         }
     }
     if (compact) expand_prev(chunk_idx - 1);
+    if (slices) {       // every slice is intact: a new_x = 0 call may pick up from here
+        h->cache_have = 1 | (((wj || wh) || (reuse & 2)) ? 2 : 0);
+        h->cache_s_slab = s_slab;
+    }
     if (lanes) {        // join: everything the caller orders after this call waits for both lanes
         CK(cudaEventRecord(h->lane_ev[1], h->stream2));
         CK(cudaStreamWaitEvent(h->stream, h->lane_ev[1], 0));
@@ -1267,7 +1299,10 @@ qcb_status eval_device_inner(qcb_handle_s *h, const double *dZ, const double *dm
                              double *d_hess, int want, const HostOut *host, double *E_out) {
     const char *range_msg = "non-finite input or ||dt*G(u)||_1 beyond the supported range";
     if (h->large) {
-        const int s = slab_squarings(h, dZ);
+        // new_x = 0: the norms, the squaring classes and the unit order are those of the previous call
+        const bool same_x = (h->reuse & h->cache_have & 1) && !host && !E_out && h->cache_s_slab >= 0;
+        const int s = same_x ? h->cache_s_slab : slab_squarings(h, dZ);
+        if (!same_x) h->cache_have = 0;
         if (s < 0) { h->err = range_msg; return QCB_ERR_RANGE; }
         eval_large(h, dZ, dmu, d_delta, d_jac, d_hess, want, host, s, E_out);
     } else {
@@ -1847,6 +1882,15 @@ qcb_status qcb_assemble_device(qcb_handle h, const double *d_jac_arenas, const d
     } catch (const CudaFail &f) {
         return fail_cuda(h, f);
     }
+}
+
+qcb_status qcb_eval_all_device_x(qcb_handle h, const double *dZ, const double *dmu, int32_t new_x, double *d_delta,
+                                 double *d_jac, double *d_hess) {
+    if (!h) return QCB_ERR_ARG;
+    h->reuse = new_x ? 0 : 3;
+    qcb_status st = qcb_eval_all_device(h, dZ, dmu, d_delta, d_jac, d_hess);
+    h->reuse = 0;
+    return st;
 }
 
 qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu, double *delta, double *jac, double *hess) {

@@ -634,3 +634,64 @@ def test_many_drives(d, m, built_libs):
     d0, j0, h0 = P.evaluate(oracle_layout(L), G0, Gd, Z.reshape(-1), mu)
     assert rel_err(d1, d0) < TOL and rel_err(j1, j0) < TOL and rel_err(h1, h0) < TOL
     ev.close()
+
+
+# ---- Ipopt's new_x flag: eval_g -> eval_jac_g -> eval_h on one iterate reuse the Z-only intermediates ----
+@pytest.mark.parametrize("storage", ["iso", "full"])
+def test_new_x_reuse_is_bit_identical_and_a_new_point_recomputes(storage, built_libs, monkeypatch):
+    import torch
+    if storage == "full":
+        monkeypatch.setenv("QCB_NO_ISO", "1")
+    w = workloads.make("cfg5", N=9)
+    L = w.layout
+    Zk = w.Z.reshape(L.N, L.z_dim).copy()
+    Zk[2, L.dt_off] *= 3.0        # two squaring classes -> two lanes, sorted units
+    Zk[5, L.dt_off] *= 6.0
+    Z1 = Zk.reshape(-1)
+    ev = Evaluator(L, w.G_drift, w.G_drives)
+    cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    nanv = lambda n: torch.full((n,), float("nan"), dtype=torch.float64, device="cuda")
+    dZ, dmu = cu(Z1), cu(w.mu)
+    ref_d, ref_j, ref_h = nanv(ev.defect_dim), nanv(ev.jacobian_nnz), nanv(ev.hessian_nnz)
+    ev.eval_all_device(dZ, dmu, ref_d, ref_j, ref_h)                       # plain call: the reference
+    launches_full = ev.kernel_launches
+    # Ipopt's order on a new iterate: eval_g(new_x = 1), eval_jac_g(0), eval_h(0, new multipliers)
+    d, j, h = nanv(ev.defect_dim), nanv(ev.jacobian_nnz), nanv(ev.hessian_nnz)
+    ev.eval_all_device_x(dZ, None, True, d, None, None)
+    l0 = ev.kernel_launches
+    ev.eval_all_device_x(dZ, None, False, d, j, None)
+    l1 = ev.kernel_launches
+    ev.eval_all_device_x(dZ, dmu, False, d, None, h)
+    l2 = ev.kernel_launches
+    assert torch.equal(d, ref_d) and torch.equal(j, ref_j) and torch.equal(h, ref_h)
+    assert (l1 - l0) + (l2 - l1) < launches_full + 8, "the cached calls must not redo the whole pass"
+    # new multipliers on the same point
+    mu2 = cu(2.0 * w.mu)
+    h2, h2ref = nanv(ev.hessian_nnz), nanv(ev.hessian_nnz)
+    ev.eval_all_device_x(dZ, mu2, False, d, None, h2)
+    ev.eval_all_device(dZ, mu2, d, None, h2ref)
+    assert torch.equal(h2, h2ref) and not torch.equal(h2, ref_h)
+    # a Jacobian request served from the arena the Hessian call left behind
+    j3 = nanv(ev.jacobian_nnz)
+    ev.eval_all_device_x(dZ, None, False, d, j3, None)
+    assert torch.equal(j3, ref_j)
+    # a new point (new_x = 1) is recomputed: compare with a fresh handle
+    Z2 = Z1.copy(); Z2.reshape(L.N, L.z_dim)[:, L.u_off:L.u_off + L.m] *= 1.5
+    dZ2 = cu(Z2)
+    ev.eval_all_device_x(dZ2, dmu, True, d, j, h)
+    fresh = Evaluator(L, w.G_drift, w.G_drives)
+    fd, fj, fh = nanv(ev.defect_dim), nanv(ev.jacobian_nnz), nanv(ev.hessian_nnz)
+    fresh.eval_all_device(dZ2, dmu, fd, fj, fh)
+    assert torch.equal(d, fd) and torch.equal(j, fj) and torch.equal(h, fh) and not torch.equal(j, ref_j)
+    # and against the independent port
+    OL = oracle_layout(L)
+    pd_, pj, ph = P.evaluate(OL, w.G_drift, w.G_drives, Z2, w.mu)
+    assert rel_err(j.cpu().numpy(), pj) < TOL and rel_err(h.cpu().numpy(), ph) < TOL
+    # small-d path: the flag is accepted and the call recomputes
+    ws = workloads.make("cfg2", N=6)
+    es = Evaluator(ws.layout, ws.G_drift, ws.G_drives)
+    sd, sj, sh = nanv(es.defect_dim), nanv(es.jacobian_nnz), nanv(es.hessian_nnz)
+    es.eval_all_device_x(cu(ws.Z), cu(ws.mu), False, sd, sj, sh)
+    r = es.eval_all(ws.Z, ws.mu)
+    assert np.array_equal(sj.cpu().numpy(), r[1]) and np.array_equal(sh.cpu().numpy(), r[2])
+    ev.close(); fresh.close(); es.close()
