@@ -1180,9 +1180,9 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     }
 }
 
-template <int D>
+template <int D, int C = 0, int M = 0, int TPU = 0>
 void launch_small(qcb_handle_s *h, const SmallParams &p, size_t smem) {
-    auto kern = small_unit_kernel<D>;
+    auto kern = small_unit_kernel<D, C, M, TPU>;
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int ctas = (p.units + p.upc - 1) / p.upc;
     kern<<<ctas, p.upc * p.tpu, smem, h->stream>>>(p);
@@ -1201,7 +1201,8 @@ void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     p.jcode = h->d_jcode; p.hcode = h->d_hcode; p.jnnz = h->jnnz_unit; p.hnnz = h->hnnz_unit;
     p.want = want; p.smax = s; p.bad_flag = h->d_bad;
     // threads per unit: one per matrix element, as a power of two <= 32 or a multiple of 32 (<= 512)
-    const int dd = h->d * h->d;
+    // run-time d: one thread per matrix element; compile-time d: one thread per register tile of RB rows
+    const int dd = (h->d / small_tile_rows(h->d)) * h->d;
     int tpu = 1;
     if (dd <= 32) { while (tpu < dd) tpu <<= 1; } else tpu = std::min(512, round_up(dd, 32));
     const size_t unit_d = small_unit_doubles(h->d, h->c, h->m, s);
@@ -1212,7 +1213,7 @@ void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     int upc = 1;
     long best_resident = 0;
     for (int cand = 1; cand <= 16; cand *= 2) {
-        if (cand * tpu > 512) break;
+        if (cand * tpu > (small_tiled(h->d) ? 256 : 512)) break;
         if (cand > 1 && (long long)cand * h->n_sm * 2 > h->units) break;
         const size_t bytes = small_smem_doubles(h->d, h->c, h->m, s, cand) * 8 + 1024;   // + per-CTA reservation
         if (bytes > 227 * 1024) break;
@@ -1222,6 +1223,12 @@ void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     }
     p.tpu = tpu; p.upc = upc; p.unit_doubles = (int)unit_d;
     const size_t smem = small_smem_doubles(h->d, h->c, h->m, s, upc) * sizeof(double);
+    // fully specialised instances of the BASELINE shapes (state columns, drives, threads per unit)
+    const int dcm = h->d * 10000 + h->c * 100 + h->m;
+    if (dcm == 40202 && tpu == 8) { launch_small<4, 2, 2, 8>(h, p, smem); ++h->launches; CK(cudaGetLastError()); return; }
+    if (dcm == 60302 && tpu == 64) { launch_small<6, 3, 2, 64>(h, p, smem); ++h->launches; CK(cudaGetLastError()); return; }
+    if (dcm == 180904 && tpu == 352) { launch_small<18, 9, 4, 352>(h, p, smem); ++h->launches; CK(cudaGetLastError()); return; }
+    if (dcm == 180104 && tpu == 352) { launch_small<18, 1, 4, 352>(h, p, smem); ++h->launches; CK(cudaGetLastError()); return; }
     switch (h->d) {
     case 4: launch_small<4>(h, p, smem); break;
     case 6: launch_small<6>(h, p, smem); break;

@@ -40,20 +40,34 @@ struct SmallParams {
 
 // Matrices live in shared memory with an odd leading dimension (ld = d + 1 for even d): column and
 // row (transposed) walks are then both free of bank conflicts.
-QCB_HD static inline int small_ld(int d) { return (d & 1) ? d : d + 1; }
+// The compile-time instances (register-tiled products, 16-byte shared-memory loads) use ld = d; the
+// run-time-d interpreter keeps an odd leading dimension (scalar row and column walks without conflicts).
+QCB_HD static inline bool small_static_d(int d) { return d == 4 || d == 6 || d == 8 || d == 10 || d == 12 || d == 16 || d == 18; }
+// Rows of the register tile a thread owns in the products of the compile-time instances (1: one element
+// per thread).  Measured: the tile form wins for d = 4 (cfg1 / cfg4); for d = 6 and d = 18 the fewer
+// threads per unit it implies slow the element-wise phases (loads, panels, COO stores) by more than the
+// products gain (cfg2 0.056 -> 0.081 ms, cfg3 0.37 -> 0.77 ms), so those stay at one element per thread.
+QCB_HD static inline int small_tile_rows(int d) { return d == 4 ? 2 : 1; }
+QCB_HD static inline bool small_tiled(int d) { return small_tile_rows(d) > 1; }
+QCB_HD static inline int small_ld(int d) { return small_tiled(d) ? d : ((d & 1) ? d : d + 1); }
 
-struct SmallCtx {
-    int d, ld, msz, m, level, j;
-    int e0, tpu;     // this thread's first element and the element stride
+// M_ / TPU_ > 0: drives and threads per unit known at compile time (the instances of the BASELINE shapes):
+// loops over drives unroll and the index arithmetic folds; 0: read from the launch parameters.
+template <int M_, int TPU_> struct SmallCtxT {
+    int d, ld, msz, m_, level, j;
+    int e0, tpu_;    // this thread's first element and the element stride
     double *fixed;   // [QR_NUM_FIXED][msz]
     double *E, *W;   // [smax+1][msz]
     double *dpersist;  // [QCB_NUM_DPERSIST][m][msz]: DA2, DA3, DA4, DZ1, DZ2 of every direction
     double *L;       // [2][m][msz]: L_j at the current / next squaring level
     int lcur;        // which half of L holds the current level
     const double *Gs;  // [m][msz] the unit's drive generators, staged in shared memory
+    __device__ __forceinline__ int m() const { return M_ > 0 ? M_ : m_; }
+    __device__ __forceinline__ int tpu() const { return TPU_ > 0 ? TPU_ : tpu_; }
 };
 
-__device__ __forceinline__ double *sm_resolve(const SmallCtx &x, int r) {
+template <class Ctx>
+__device__ __forceinline__ double *sm_resolve(const Ctx &x, int r) {
     if (r < QR_NUM_FIXED) return x.fixed + r * x.msz;
     switch (r) {
     case QR_EL: return x.E + x.level * x.msz;
@@ -63,9 +77,9 @@ __device__ __forceinline__ double *sm_resolve(const SmallCtx &x, int r) {
     case QR_E0: return x.E;
     case QR_W0: return x.W;
     case QR_GJ: return const_cast<double *>(x.Gs) + x.j * x.msz;
-    case QR_L: return x.L + (x.lcur * x.m + x.j) * x.msz;
-    case QR_LN: return x.L + ((x.lcur ^ 1) * x.m + x.j) * x.msz;
-    default: return x.dpersist + (qcb_dpersist(r) * x.m + x.j) * x.msz;   // QR_U is never stored here
+    case QR_L: return x.L + (x.lcur * x.m() + x.j) * x.msz;
+    case QR_LN: return x.L + ((x.lcur ^ 1) * x.m() + x.j) * x.msz;
+    default: return x.dpersist + (qcb_dpersist(r) * x.m() + x.j) * x.msz;   // QR_U is never stored here
     }
 }
 
@@ -77,10 +91,61 @@ __device__ __forceinline__ void unit_barrier(int tpu) {
     else __syncthreads();
 }
 
+// ---- compile-time ops (D > 0): one specialised routine per table entry -- register bases are
+//      constants, the k loops unroll with immediate offsets, Taylor coefficients are immediates ----
+template <int D> struct SmDims {
+    static constexpr int RB = (D == 4) ? 2 : 1;   // == small_tile_rows(D)
+    static constexpr int ld = RB > 1 ? D : ((D & 1) ? D : D + 1);
+    static constexpr int msz = ld * D;
+    static constexpr int NT = (D / RB) * D;       // tiles per matrix (D = 0: unused)
+};
+
+// N doubles (N even) from 16-byte aligned shared memory: LDS.128
+template <int N> __device__ __forceinline__ void lds_vec(double (&v)[N], const double *p) {
+#pragma unroll
+    for (int i = 0; i < N; i += 2) {
+        const double2 t = *reinterpret_cast<const double2 *>(p + i);
+        v[i] = t.x; v[i + 1] = t.y;
+    }
+}
+template <int N> __device__ __forceinline__ void sts_vec(double *p, const double (&v)[N]) {
+#pragma unroll
+    for (int i = 0; i < N; i += 2) *reinterpret_cast<double2 *>(p + i) = make_double2(v[i], v[i + 1]);
+}
+// acc[i] += sum_k op(A)(r0 + i, k) * op(B)(k, q), i < RB: the column of op(B) is read once into registers,
+// op(A) arrives RB rows at a time -- (RB + 1) / (2 RB) 16-byte loads per FMA instead of two 8-byte loads
+template <int D, int RB, bool TA, bool TB>
+__device__ __forceinline__ void tile_mac(double (&acc)[RB], const double *A, const double *B, int r0, int q) {
+    double b[D];
+    if (!TB) lds_vec<D>(b, B + q * D);
+    else {
+#pragma unroll
+        for (int k = 0; k < D; ++k) b[k] = B[q + k * D];
+    }
+    if (!TA) {
+#pragma unroll
+        for (int k = 0; k < D; ++k) {
+            double a[RB];
+            lds_vec<RB>(a, A + r0 + k * D);
+#pragma unroll
+            for (int i = 0; i < RB; ++i) acc[i] = fma(a[i], b[k], acc[i]);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < RB; ++i) {
+            double a[D];
+            lds_vec<D>(a, A + (r0 + i) * D);
+            double p0 = 0.0, p1 = 0.0;      // two chains per row: RB rows x 2 keep the FP64 pipe fed
+#pragma unroll
+            for (int k = 0; k + 1 < D; k += 2) { p0 = fma(a[k], b[k], p0); p1 = fma(a[k + 1], b[k + 1], p1); }
+            acc[i] += p0 + p1;
+        }
+    }
+}
 template <int D, int AS, int BS> __device__ __forceinline__ double dot_k(const double *a, const double *b, double acc, int d, int ld) {
     // AS / BS: 1 = unit stride, 0 = stride ld
     if (D > 0) {
-        constexpr int LD = (D & 1) ? D : D + 1;
+        constexpr int LD = SmDims<D>::ld;
         // four independent partial sums: the FP64 FMA latency chain would otherwise bound an op
         double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0;
 #pragma unroll
@@ -101,10 +166,10 @@ template <int D, int AS, int BS> __device__ __forceinline__ double dot_k(const d
 }
 
 // dst = sum_t op(a)op(b) + sum_r c*reg + c*I for this thread's unit.  Ends with a CTA barrier.
-template <int D, bool SYNC = true> __device__ __noinline__ void sm_run_op(const SmallCtx &x, const qcb_op &op) {
-    const int d = D > 0 ? D : x.d, ld = D > 0 ? ((D & 1) ? D : D + 1) : x.ld, dd = d * d;
+template <int D, bool SYNC = true, class Ctx> __device__ __noinline__ void sm_run_op(const Ctx &x, const qcb_op &op) {
+    const int d = D > 0 ? D : x.d, ld = D > 0 ? SmDims<D>::ld : x.ld, dd = d * d;
     double *dst = sm_resolve(x, op.dst);
-    for (int e = x.e0; e < dd; e += x.tpu) {
+    for (int e = x.e0; e < dd; e += x.tpu()) {
         const int r = e % d, q = e / d;
         double acc = 0.0;
         for (int t = 0; t < op.nterm; ++t) {
@@ -121,16 +186,10 @@ template <int D, bool SYNC = true> __device__ __noinline__ void sm_run_op(const 
         if (op.ident >= 0 && r == q) acc += c_taylor[op.ident];
         dst[off] = acc;
     }
-    if (SYNC) unit_barrier(x.tpu);
+    if (SYNC) unit_barrier(x.tpu());
 }
 
-// ---- compile-time ops (D > 0): one specialised routine per table entry -- register bases are
-//      constants, the k loops unroll with immediate offsets, Taylor coefficients are immediates ----
-template <int D> struct SmDims {
-    static constexpr int ld = (D & 1) ? D : D + 1;
-    static constexpr int msz = ld * D;
-};
-template <int D, int R> __device__ __forceinline__ double *sm_resolve_s(const SmallCtx &x) {
+template <int D, int R, class Ctx> __device__ __forceinline__ double *sm_resolve_s(const Ctx &x) {
     constexpr int MSZ = SmDims<D>::msz;
     if constexpr (R < QR_NUM_FIXED) return x.fixed + R * MSZ;
     else if constexpr (R == QR_EL) return x.E + x.level * MSZ;
@@ -140,82 +199,125 @@ template <int D, int R> __device__ __forceinline__ double *sm_resolve_s(const Sm
     else if constexpr (R == QR_E0) return x.E;
     else if constexpr (R == QR_W0) return x.W;
     else if constexpr (R == QR_GJ) return const_cast<double *>(x.Gs) + x.j * MSZ;
-    else if constexpr (R == QR_L) return x.L + (x.lcur * x.m + x.j) * MSZ;
-    else if constexpr (R == QR_LN) return x.L + ((x.lcur ^ 1) * x.m + x.j) * MSZ;
-    else return x.dpersist + ((R - QR_DA2) * x.m + x.j) * MSZ;
+    else if constexpr (R == QR_L) return x.L + (x.lcur * x.m() + x.j) * MSZ;
+    else if constexpr (R == QR_LN) return x.L + ((x.lcur ^ 1) * x.m() + x.j) * MSZ;
+    else return x.dpersist + ((R - QR_DA2) * x.m() + x.j) * MSZ;
 }
-template <int D, const qcb_op *TAB, int I, int T>
-__device__ __forceinline__ double sm_term_s(const SmallCtx &x, int r, int q) {
+template <int D, const qcb_op *TAB, int I, int T, class Ctx>
+__device__ __forceinline__ double sm_term_s(const Ctx &x, int r, int q) {
     constexpr qcb_term tm = TAB[I].term[T];
     constexpr int LD = SmDims<D>::ld;
     const double *a = sm_resolve_s<D, tm.a>(x) + (tm.ta ? r * LD : r);
     const double *b = sm_resolve_s<D, tm.b>(x) + (tm.tb ? q : q * LD);
     return dot_k<D, (tm.ta ? 1 : 0), (tm.tb ? 0 : 1)>(a, b, 0.0, D, LD);
 }
-template <int D, const qcb_op *TAB, int I, int L>
-__device__ __forceinline__ double sm_lin_s(const SmallCtx &x, int off) {
+template <int D, const qcb_op *TAB, int I, int T, class Ctx>
+__device__ __forceinline__ void sm_term_tile(const Ctx &x, int r0, int q, double (&acc)[SmDims<D>::RB]) {
+    constexpr qcb_term tm = TAB[I].term[T];
+    tile_mac<D, SmDims<D>::RB, (tm.ta != 0), (tm.tb != 0)>(acc, sm_resolve_s<D, tm.a>(x), sm_resolve_s<D, tm.b>(x), r0, q);
+}
+template <int D, const qcb_op *TAB, int I, int L, class Ctx>
+__device__ __forceinline__ void sm_lin_tile(const Ctx &x, int off, double (&acc)[SmDims<D>::RB]) {
+    constexpr qcb_lin ln = TAB[I].lin[L];
+    constexpr double cf = QCB_TAYLOR[ln.coef];
+    double v[SmDims<D>::RB];
+    lds_vec<SmDims<D>::RB>(v, sm_resolve_s<D, ln.reg>(x) + off);
+#pragma unroll
+    for (int i = 0; i < SmDims<D>::RB; ++i) acc[i] = fma(cf, v[i], acc[i]);
+}
+template <int D, const qcb_op *TAB, int I, int L, class Ctx>
+__device__ __forceinline__ double sm_lin_s(const Ctx &x, int off) {
     constexpr qcb_lin ln = TAB[I].lin[L];
     constexpr double cf = QCB_TAYLOR[ln.coef];
     return cf * sm_resolve_s<D, ln.reg>(x)[off];
 }
-template <int D, const qcb_op *TAB, int I, bool SYNC, int... T, int... L>
-__device__ __forceinline__ void sm_run_static_impl(const SmallCtx &x, std::integer_sequence<int, T...>,
+template <int D, const qcb_op *TAB, int I, bool SYNC, class Ctx, int... T, int... L>
+__device__ __forceinline__ void sm_run_static_impl(const Ctx &x, std::integer_sequence<int, T...>,
                                                    std::integer_sequence<int, L...>) {
     constexpr qcb_op op = TAB[I];
-    constexpr int LD = SmDims<D>::ld;
     double *dst = sm_resolve_s<D, op.dst>(x);
-    for (int e = x.e0; e < D * D; e += x.tpu) {
-        const int r = e % D, q = e / D, off = r + q * LD;
-        double acc = (0.0 + ... + sm_term_s<D, TAB, I, T>(x, r, q));
-        acc += (0.0 + ... + sm_lin_s<D, TAB, I, L>(x, off));
-        if constexpr (op.ident >= 0) {
-            constexpr double ci = QCB_TAYLOR[op.ident >= 0 ? op.ident : 0];
-            if (r == q) acc += ci;
+    if constexpr (SmDims<D>::RB > 1) {          // register tiles: RB rows of one column per thread
+        constexpr int RB = SmDims<D>::RB, NT = SmDims<D>::NT, NRB = D / RB;
+        for (int t = x.e0; t < NT; t += x.tpu()) {
+            const int q = t / NRB, r0 = (t - q * NRB) * RB, off = r0 + q * D;
+            double acc[RB];
+#pragma unroll
+            for (int i = 0; i < RB; ++i) acc[i] = 0.0;
+            (sm_term_tile<D, TAB, I, T>(x, r0, q, acc), ...);
+            (sm_lin_tile<D, TAB, I, L>(x, off, acc), ...);
+            if constexpr (op.ident >= 0) {
+                constexpr double ci = QCB_TAYLOR[op.ident >= 0 ? op.ident : 0];
+#pragma unroll
+                for (int i = 0; i < RB; ++i) if (r0 + i == q) acc[i] += ci;
+            }
+            sts_vec<RB>(dst + off, acc);
         }
-        dst[off] = acc;
+    } else {                                    // one element per thread
+        constexpr int LD = SmDims<D>::ld;
+        for (int e = x.e0; e < D * D; e += x.tpu()) {
+            const int r = e % D, q = e / D, off = r + q * LD;
+            double acc = (0.0 + ... + sm_term_s<D, TAB, I, T>(x, r, q));
+            acc += (0.0 + ... + sm_lin_s<D, TAB, I, L>(x, off));
+            if constexpr (op.ident >= 0) {
+                constexpr double ci = QCB_TAYLOR[op.ident >= 0 ? op.ident : 0];
+                if (r == q) acc += ci;
+            }
+            dst[off] = acc;
+        }
     }
-    if (SYNC) unit_barrier(x.tpu);
+    if (SYNC) unit_barrier(x.tpu());
 }
-template <int D, const qcb_op *TAB, int I, bool SYNC = true> __device__ __forceinline__ void sm_run_static(const SmallCtx &x) {
+template <int D, const qcb_op *TAB, int I, bool SYNC = true, class Ctx> __device__ __forceinline__ void sm_run_static(const Ctx &x) {
     sm_run_static_impl<D, TAB, I, SYNC>(x, std::make_integer_sequence<int, TAB[I].nterm>{},
                                   std::make_integer_sequence<int, TAB[I].nlin>{});
 }
-template <int D, const qcb_op *TAB, int... I>
-__device__ __forceinline__ void sm_run_table_impl(const SmallCtx &x, std::integer_sequence<int, I...>) {
+template <int D, const qcb_op *TAB, class Ctx, int... I>
+__device__ __forceinline__ void sm_run_table_impl(const Ctx &x, std::integer_sequence<int, I...>) {
     (sm_run_static<D, TAB, I>(x), ...);
 }
 // run ops 0..N-1 of a table: specialised code for D > 0, the interpreter otherwise
-template <int D, const qcb_op *TAB, int N> __device__ __forceinline__ void sm_run_table(const SmallCtx &x, const qcb_op *ctab) {
+template <int D, const qcb_op *TAB, int N, class Ctx> __device__ __forceinline__ void sm_run_table(const Ctx &x, const qcb_op *ctab) {
     if constexpr (D > 0) sm_run_table_impl<D, TAB>(x, std::make_integer_sequence<int, N>{});
     else for (int i = 0; i < N; ++i) sm_run_op<0>(x, ctab[i]);
 }
-template <int D, const qcb_op *TAB, int I, bool SYNC = true> __device__ __forceinline__ void sm_run_one(const SmallCtx &x, const qcb_op *ctab) {
+template <int D, const qcb_op *TAB, int I, bool SYNC = true, class Ctx> __device__ __forceinline__ void sm_run_one(const Ctx &x, const qcb_op *ctab) {
     if constexpr (D > 0) sm_run_static<D, TAB, I, SYNC>(x);
     else sm_run_op<0, SYNC>(x, ctab[I]);
 }
 
-// value of the product terms of op I at element (r, q) -- no store (fused contractions)
-template <int D, const qcb_op *TAB, int I, int... T>
-__device__ __forceinline__ double sm_products_s(const SmallCtx &x, int r, int q, std::integer_sequence<int, T...>) {
+// value of the product terms of op I at element (r, q) -- no store (fused contractions); run-time d only
+template <class Ctx> __device__ __forceinline__ double sm_products_rt(const Ctx &x, const qcb_op &op, int r, int q) {
+    const int d = x.d, ld = x.ld;
+    double acc = 0.0;
+    for (int t = 0; t < op.nterm; ++t) {
+        const int ta = op.term[t].ta, tb = op.term[t].tb;
+        const double *a = sm_resolve(x, op.term[t].a) + (ta ? r * ld : r);
+        const double *b = sm_resolve(x, op.term[t].b) + (tb ? q : q * ld);
+        const int as = ta ? 1 : ld, bs = tb ? ld : 1;
+        for (int k = 0; k < d; ++k) acc = fma(a[k * as], b[k * bs], acc);
+    }
+    return acc;
+}
+// compile-time d, one element
+template <int D, const qcb_op *TAB, int I, class Ctx, int... T>
+__device__ __forceinline__ double sm_products_s(const Ctx &x, int r, int q, std::integer_sequence<int, T...>) {
     return (0.0 + ... + sm_term_s<D, TAB, I, T>(x, r, q));
 }
-template <int D, const qcb_op *TAB, int I>
-__device__ __forceinline__ double sm_products(const SmallCtx &x, const qcb_op *ctab, int r, int q) {
-    if constexpr (D > 0) {
-        return sm_products_s<D, TAB, I>(x, r, q, std::make_integer_sequence<int, TAB[I].nterm>{});
-    } else {
-        const qcb_op &op = ctab[I];
-        const int d = x.d, ld = x.ld;
-        double acc = 0.0;
-        for (int t = 0; t < op.nterm; ++t) {
-            const int ta = op.term[t].ta, tb = op.term[t].tb;
-            const double *a = sm_resolve(x, op.term[t].a) + (ta ? r * ld : r);
-            const double *b = sm_resolve(x, op.term[t].b) + (tb ? q : q * ld);
-            const int as = ta ? 1 : ld, bs = tb ? ld : 1;
-            for (int k = 0; k < d; ++k) acc = fma(a[k * as], b[k * bs], acc);
-        }
-        return acc;
-    }
+template <int D, const qcb_op *TAB, int I, class Ctx>
+__device__ __forceinline__ double sm_products_e(const Ctx &x, int r, int q) {
+    return sm_products_s<D, TAB, I>(x, r, q, std::make_integer_sequence<int, TAB[I].nterm>{});
+}
+// the same for a register tile (compile-time d): u[i] = products of op I at rows r0 + i of column q
+template <int D, const qcb_op *TAB, int I, class Ctx, int... T>
+__device__ __forceinline__ void sm_products_tile_impl(const Ctx &x, int r0, int q, double (&u)[SmDims<D>::RB],
+                                                      std::integer_sequence<int, T...>) {
+#pragma unroll
+    for (int i = 0; i < SmDims<D>::RB; ++i) u[i] = 0.0;
+    (sm_term_tile<D, TAB, I, T>(x, r0, q, u), ...);
+}
+template <int D, const qcb_op *TAB, int I, class Ctx>
+__device__ __forceinline__ void sm_products_tile(const Ctx &x, int r0, int q, double (&u)[SmDims<D>::RB]) {
+    sm_products_tile_impl<D, TAB, I>(x, r0, q, u, std::make_integer_sequence<int, TAB[I].nterm>{});
 }
 
 // Sum over the threads of a unit, result in every thread of the unit.  tpu is a power of two <= 32
@@ -349,8 +451,8 @@ __device__ __forceinline__ void unit_reduce_add8(double (&a)[8], int nn, int tpu
 
 // Second order at the polynomial level for direction j, all product nodes at once and nothing
 // stored:  Hrow[i] += sum_nodes sum_e (Xdot_j^T Nbar)[e] * Ydot_i[e].
-template <int D> __device__ __noinline__ void sm_p6_pass(SmallCtx &x, int j, const qcb_op *ctab, double *red_unit, double *Hrow) {
-    const int d = D > 0 ? D : x.d, ld = D > 0 ? ((D & 1) ? D : D + 1) : x.ld, msz = ld * d, m = x.m;
+template <int D, class Ctx> __device__ __noinline__ void sm_p6_pass(Ctx &x, int j, const qcb_op *ctab, double *red_unit, double *Hrow) {
+    const int d = D > 0 ? D : x.d, ld = D > 0 ? SmDims<D>::ld : x.ld, msz = ld * d, m = x.m();
     constexpr int pr0 = QCB_P6_PARTNER[0], pr1 = QCB_P6_PARTNER[1], pr2 = QCB_P6_PARTNER[2], pr3 = QCB_P6_PARTNER[3];
     auto partner_base = [&](int reg) {
         return (reg == QR_GJ) ? x.Gs : x.dpersist + (long long)qcb_dpersist(reg) * m * msz;
@@ -360,37 +462,93 @@ template <int D> __device__ __noinline__ void sm_p6_pass(SmallCtx &x, int j, con
     for (int i0 = 0; i0 < m; i0 += 8) {
         const int nn = min(8, m - i0);
         double a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        for (int e = x.e0; e < d * d; e += x.tpu) {
-            const int r = e % d, q = e / d, off = r + q * ld;
-            const double u0 = sm_products<D, QCB_P6, 0>(x, ctab, r, q), u1 = sm_products<D, QCB_P6, 1>(x, ctab, r, q);
-            const double u2 = sm_products<D, QCB_P6, 2>(x, ctab, r, q), u3 = sm_products<D, QCB_P6, 3>(x, ctab, r, q);
+        if constexpr (D > 0 && SmDims<D>::RB > 1) {
+            constexpr int RB = SmDims<D>::RB, NT = SmDims<D>::NT, NRB = D / RB;
+            for (int t = x.e0; t < NT; t += x.tpu()) {
+                const int q = t / NRB, r0 = (t - q * NRB) * RB, off = r0 + q * D;
+                double u0[RB], u1[RB], u2[RB], u3[RB];
+                sm_products_tile<D, QCB_P6, 0>(x, r0, q, u0);
+                sm_products_tile<D, QCB_P6, 1>(x, r0, q, u1);
+                sm_products_tile<D, QCB_P6, 2>(x, r0, q, u2);
+                sm_products_tile<D, QCB_P6, 3>(x, r0, q, u3);
 #pragma unroll
-            for (int t = 0; t < 8; ++t)
-                if (t < nn) {
-                    const long long po = (long long)(i0 + t) * msz + off;
-                    a[t] = fma(u0, part[0][po], fma(u1, part[1][po], fma(u2, part[2][po], fma(u3, part[3][po], a[t]))));
+                for (int tt = 0; tt < 8; ++tt)
+                    if (tt < nn) {
+                        const long long po = (long long)(i0 + tt) * msz + off;
+                        double pv[RB], acc2 = 0.0;       // one partner at a time: registers, not bandwidth, are short here
+                        lds_vec<RB>(pv, part[0] + po);
+#pragma unroll
+                        for (int i = 0; i < RB; ++i) a[tt] = fma(u0[i], pv[i], a[tt]);
+                        lds_vec<RB>(pv, part[1] + po);
+#pragma unroll
+                        for (int i = 0; i < RB; ++i) acc2 = fma(u1[i], pv[i], acc2);
+                        lds_vec<RB>(pv, part[2] + po);
+#pragma unroll
+                        for (int i = 0; i < RB; ++i) a[tt] = fma(u2[i], pv[i], a[tt]);
+                        lds_vec<RB>(pv, part[3] + po);
+#pragma unroll
+                        for (int i = 0; i < RB; ++i) acc2 = fma(u3[i], pv[i], acc2);
+                        a[tt] += acc2;
+                    }
+            }
+        } else {
+            for (int e = x.e0; e < d * d; e += x.tpu()) {
+                const int r = e % d, q = e / d, off = r + q * ld;
+                double u0, u1, u2, u3;
+                if constexpr (D > 0) {
+                    u0 = sm_products_e<D, QCB_P6, 0>(x, r, q); u1 = sm_products_e<D, QCB_P6, 1>(x, r, q);
+                    u2 = sm_products_e<D, QCB_P6, 2>(x, r, q); u3 = sm_products_e<D, QCB_P6, 3>(x, r, q);
+                } else {
+                    u0 = sm_products_rt(x, ctab[0], r, q); u1 = sm_products_rt(x, ctab[1], r, q);
+                    u2 = sm_products_rt(x, ctab[2], r, q); u3 = sm_products_rt(x, ctab[3], r, q);
                 }
+#pragma unroll
+                for (int t = 0; t < 8; ++t)
+                    if (t < nn) {
+                        const long long po = (long long)(i0 + t) * msz + off;
+                        a[t] = fma(u0, part[0][po], fma(u1, part[1][po], fma(u2, part[2][po], fma(u3, part[3][po], a[t]))));
+                    }
+            }
         }
-        unit_reduce_add8(a, nn, x.tpu, x.e0, red_unit, Hrow + i0);
+        unit_reduce_add8(a, nn, x.tpu(), x.e0, red_unit, Hrow + i0);
     }
 }
 
 // One squaring level for direction j:  Hrow[i] += sum_e (L_j^T W[l+1])[e] * L_i[e]
-template <int D> __device__ __noinline__ void sm_level_pass(SmallCtx &x, int j, int level, const qcb_op *ctab, double *red_unit, double *Hrow) {
-    const int d = D > 0 ? D : x.d, ld = D > 0 ? ((D & 1) ? D : D + 1) : x.ld, msz = ld * d, m = x.m;
+template <int D, class Ctx> __device__ __noinline__ void sm_level_pass(Ctx &x, int j, int level, const qcb_op *ctab, double *red_unit, double *Hrow) {
+    const int d = D > 0 ? D : x.d, ld = D > 0 ? SmDims<D>::ld : x.ld, msz = ld * d, m = x.m();
     const double *Lbase = x.L + (long long)x.lcur * m * msz;
     x.j = j; x.level = level;
     for (int i0 = 0; i0 < m; i0 += 8) {
         const int nn = min(8, m - i0);
         double a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        for (int e = x.e0; e < d * d; e += x.tpu) {
-            const int r = e % d, q = e / d, off = r + q * ld;
-            const double u = sm_products<D, QCB_P7U, 0>(x, ctab, r, q);
+        if constexpr (D > 0 && SmDims<D>::RB > 1) {
+            constexpr int RB = SmDims<D>::RB, NT = SmDims<D>::NT, NRB = D / RB;
+            for (int t = x.e0; t < NT; t += x.tpu()) {
+                const int q = t / NRB, r0 = (t - q * NRB) * RB, off = r0 + q * D;
+                double u[RB];
+                sm_products_tile<D, QCB_P7U, 0>(x, r0, q, u);
 #pragma unroll
-            for (int t = 0; t < 8; ++t)
-                if (t < nn) a[t] = fma(u, Lbase[(long long)(i0 + t) * msz + off], a[t]);
+                for (int tt = 0; tt < 8; ++tt)
+                    if (tt < nn) {
+                        double l[RB];
+                        lds_vec<RB>(l, Lbase + (long long)(i0 + tt) * msz + off);
+#pragma unroll
+                        for (int i = 0; i < RB; ++i) a[tt] = fma(u[i], l[i], a[tt]);
+                    }
+            }
+        } else {
+            for (int e = x.e0; e < d * d; e += x.tpu()) {
+                const int r = e % d, q = e / d, off = r + q * ld;
+                double u;
+                if constexpr (D > 0) u = sm_products_e<D, QCB_P7U, 0>(x, r, q);
+                else u = sm_products_rt(x, ctab[0], r, q);
+#pragma unroll
+                for (int t = 0; t < 8; ++t)
+                    if (t < nn) a[t] = fma(u, Lbase[(long long)(i0 + t) * msz + off], a[t]);
+            }
         }
-        unit_reduce_add8(a, nn, x.tpu, x.e0, red_unit, Hrow + i0);
+        unit_reduce_add8(a, nn, x.tpu(), x.e0, red_unit, Hrow + i0);
     }
 }
 
@@ -400,7 +558,8 @@ static inline size_t small_unit_doubles(int d, int c, int m, int smax) {
     n += 3 * dc;                                   // X, Xn, M panels
     n += dd + (m + 1) * dc + 2;                    // Jacobian arena
     n += (m + 1) * dc + (size_t)m * m + m + 2;     // Hessian arena
-    n += (size_t)m * m + (dd <= 32 ? 0 : 128);     // H accumulator + reduction scratch (8 per warp; units of
+    const size_t tiles = (size_t)(d / small_tile_rows(d)) * d;
+    n += (size_t)m * m + (tiles <= 32 ? 0 : 128);  // H accumulator + reduction scratch (8 per warp; units of
                                                    // at most 32 threads reduce with shuffles and need none)
     return (n + 1) & ~(size_t)1;                   // keep every unit 16-byte aligned
 }
@@ -412,13 +571,18 @@ static inline size_t small_smem_doubles(int d, int c, int m, int smax, int upc =
 // Without the bound the run-time-d instance took 167 and could not be launched with 416..512 threads
 // (d = 20..23).  Capping D = 4 at 64 or 85 registers for more resident warps was measured slower
 // (spills: 0.60 / 0.57 ms against 0.51 ms on cfg4).
-template <int D>
-__global__ void __launch_bounds__(512, 1)
+// The compile-time instances run at most 256 threads per CTA (register tiles: a unit needs few threads,
+// and the tiles want more than 128 registers).
+// C, M, TPU > 0: state columns, drives and threads per unit fixed at compile time (the BASELINE shapes
+// d/c/m = 4/2/2, 6/3/2, 18/9/4, 18/1/4): ncu on the generic d = 4 instance showed 60 % of the executed
+// instructions to be integer arithmetic and branches of run-time loop bounds, 8 % DFMA.
+template <int D, int C = 0, int M = 0, int TPU = 0>
+__global__ void __launch_bounds__(SmDims<D>::RB > 1 ? 256 : 512, 1)
 small_unit_kernel(const __grid_constant__ SmallParams p) {
     extern __shared__ __align__(16) double sm[];
-    const int d = D > 0 ? D : p.d, c = p.c, m = p.m, dd = d * d, dc = d * c;
-    const int ld = D > 0 ? ((D & 1) ? D : D + 1) : small_ld(d), msz = ld * d;
-    const int tpu = p.tpu, ul = threadIdx.x / tpu, e0 = threadIdx.x % tpu;
+    const int d = D > 0 ? D : p.d, c = C > 0 ? C : p.c, m = M > 0 ? M : p.m, dd = d * d, dc = d * c;
+    const int ld = D > 0 ? SmDims<D>::ld : small_ld(d), msz = ld * d;
+    const int tpu = TPU > 0 ? TPU : p.tpu, ul = threadIdx.x / tpu, e0 = threadIdx.x % tpu;
     int ug = blockIdx.x * p.upc + ul;                 // slab-local unit index = sys*nk + kl
     const bool live = ug < p.units;                   // tail CTA: spare slots shadow the last unit
     if (!live) ug = p.units - 1;
@@ -426,8 +590,8 @@ small_unit_kernel(const __grid_constant__ SmallParams p) {
     const double *zk = p.Z + (long long)k * p.z_dim, *zn = zk + p.z_dim;
     const double *G0 = p.G0 + (long long)sys * dd, *Gd = p.Gd + (long long)sys * m * dd;
 
-    SmallCtx x;
-    x.d = d; x.ld = ld; x.msz = msz; x.m = m; x.level = 0; x.j = 0; x.e0 = e0; x.tpu = tpu;
+    SmallCtxT<M, TPU> x;
+    x.d = d; x.ld = ld; x.msz = msz; x.m_ = m; x.level = 0; x.j = 0; x.e0 = e0; x.tpu_ = tpu;
     double *ptr = sm + (size_t)ul * p.unit_doubles;
     x.fixed = ptr; ptr += QR_NUM_FIXED * msz;
     x.E = ptr; ptr += (p.smax + 1) * msz;
