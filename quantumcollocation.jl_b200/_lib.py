@@ -9,7 +9,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libqcb200.so")
+LIB_PATH = os.environ.get("QCB200_LIB") or os.path.join(_HERE, "csrc", "libqcb200.so")   # QCB200_LIB: another build of the same ABI
 
 c_dp = ctypes.POINTER(ctypes.c_double)
 c_ip = ctypes.POINTER(ctypes.c_int32)

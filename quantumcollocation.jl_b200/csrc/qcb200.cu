@@ -1225,7 +1225,7 @@ void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     const size_t smem = small_smem_doubles(h->d, h->c, h->m, s, upc) * sizeof(double);
     // fully specialised instances of the BASELINE shapes (state columns, drives, threads per unit)
     const int dcm = h->d * 10000 + h->c * 100 + h->m;
-    if (dcm == 40202 && tpu == 8) { launch_small<4, 2, 2, 8>(h, p, smem); ++h->launches; CK(cudaGetLastError()); return; }
+    if (dcm == 40202 && tpu == 16 / QCB_TILE4) { launch_small<4, 2, 2, 16 / QCB_TILE4>(h, p, smem); ++h->launches; CK(cudaGetLastError()); return; }
     if (dcm == 60302 && tpu == 64) { launch_small<6, 3, 2, 64>(h, p, smem); ++h->launches; CK(cudaGetLastError()); return; }
     if (dcm == 180904 && tpu == 352) { launch_small<18, 9, 4, 352>(h, p, smem); ++h->launches; CK(cudaGetLastError()); return; }
     if (dcm == 180104 && tpu == 352) { launch_small<18, 1, 4, 352>(h, p, smem); ++h->launches; CK(cudaGetLastError()); return; }

@@ -13,6 +13,10 @@
 #include <utility>
 #include "qcb_program.h"
 
+// rows of the d = 4 register tile: measured on cfg4 -- 1: 0.352 ms, 2: 0.364 ms, 4: 0.330 ms
+#ifndef QCB_TILE4
+#define QCB_TILE4 4
+#endif
 namespace qcb {
 
 __constant__ qcb_op c_P1[6], c_P2[1], c_P3[1], c_P4[5], c_P5[6], c_P6[4], c_P7U[1], c_P7L[1];
@@ -44,10 +48,10 @@ struct SmallParams {
 // run-time-d interpreter keeps an odd leading dimension (scalar row and column walks without conflicts).
 QCB_HD static inline bool small_static_d(int d) { return d == 4 || d == 6 || d == 8 || d == 10 || d == 12 || d == 16 || d == 18; }
 // Rows of the register tile a thread owns in the products of the compile-time instances (1: one element
-// per thread).  Measured: the tile form wins for d = 4 (cfg1 / cfg4); for d = 6 and d = 18 the fewer
+// per thread).  Measured: the tile form (a whole column per thread) wins for d = 4 (cfg1 / cfg4); for d = 6 and d = 18 the fewer
 // threads per unit it implies slow the element-wise phases (loads, panels, COO stores) by more than the
 // products gain (cfg2 0.056 -> 0.081 ms, cfg3 0.37 -> 0.77 ms), so those stay at one element per thread.
-QCB_HD static inline int small_tile_rows(int d) { return d == 4 ? 2 : 1; }
+QCB_HD static inline int small_tile_rows(int d) { return d == 4 ? QCB_TILE4 : 1; }
 QCB_HD static inline bool small_tiled(int d) { return small_tile_rows(d) > 1; }
 QCB_HD static inline int small_ld(int d) { return small_tiled(d) ? d : ((d & 1) ? d : d + 1); }
 
@@ -94,7 +98,7 @@ __device__ __forceinline__ void unit_barrier(int tpu) {
 // ---- compile-time ops (D > 0): one specialised routine per table entry -- register bases are
 //      constants, the k loops unroll with immediate offsets, Taylor coefficients are immediates ----
 template <int D> struct SmDims {
-    static constexpr int RB = (D == 4) ? 2 : 1;   // == small_tile_rows(D)
+    static constexpr int RB = (D == 4) ? QCB_TILE4 : 1;   // == small_tile_rows(D)
     static constexpr int ld = RB > 1 ? D : ((D & 1) ? D : D + 1);
     static constexpr int msz = ld * D;
     static constexpr int NT = (D / RB) * D;       // tiles per matrix (D = 0: unused)
