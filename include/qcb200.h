@@ -245,6 +245,12 @@ int64_t qcb_fidelity_x_dim(qcb_fidelity f);
  * NULL.  The infidelity objective Q*|1-F| (quantum_objectives.jl:199) and the constraint
  * F_min - F (quantum_constraints.jl:112) follow by the chain rule in the shim. */
 qcb_status qcb_fidelity_eval(qcb_fidelity f, const double *x, double *F, double *grad, double *hess);
+/* The Hessian in factored form: Hess F = 2 w G' G with G [rank][x_dim] row-major, constant in x (rank 2 for
+ * unitary / ket / coherent-ket, 2 + 2 n_sub^2 for the subspace kind, 0 for the linear density kind).  For
+ * large states the dense x_dim^2 block of qcb_fidelity_eval is impractical (cfg5: 537 MB); a caller that
+ * needs Hessian-vector products or a few entries takes the factor instead.  G: rank * x_dim doubles (host). */
+int64_t qcb_fidelity_rank(qcb_fidelity f);
+qcb_status qcb_fidelity_factor(qcb_fidelity f, double *G, double *w);
 
 /* Batched fidelity that never allocates.  It has no counterpart in the reference.
  *

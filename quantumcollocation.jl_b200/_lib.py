@@ -75,6 +75,8 @@ SYMBOLS = {
     "qcb_fidelity_destroy": (None, [c_vp]),
     "qcb_fidelity_x_dim": (ctypes.c_int64, [c_vp]),
     "qcb_fidelity_eval": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "qcb_fidelity_rank": (ctypes.c_int64, [c_vp]),
+    "qcb_fidelity_factor": (ctypes.c_int, [c_vp, c_vp, c_dp]),
     "qcb_aux_create": (ctypes.c_int, [ctypes.POINTER(c_vp), ctypes.POINTER(QcbAuxDesc)]),
     "qcb_aux_destroy": (None, [c_vp]),
     "qcb_aux_derivative_dim": (ctypes.c_int64, [c_vp]),

@@ -262,6 +262,15 @@ class Fidelity:
             raise _lib.QcbError(st, "fidelity evaluation failed")
         return float(F[0]), g, H
 
+    def hessian_factor(self):
+        """(G [rank, x_dim], w): Hess F = 2 w G'G, constant in x (rank 0 for the linear density kind)."""
+        R = self.lib.qcb_fidelity_rank(self.h)
+        G = np.empty((max(R, 1), self.x_dim))
+        w = ctypes.c_double(0.0)
+        if self.lib.qcb_fidelity_factor(self.h, _ptr(G), ctypes.byref(w)) != 0:
+            raise _lib.QcbError(2, "qcb_fidelity_factor failed")
+        return G[:R], w.value
+
     def close(self):
         if getattr(self, "h", None):
             self.lib.qcb_fidelity_destroy(self.h)

@@ -102,7 +102,7 @@ struct qcb_handle_s {
     double *sc_XP = nullptr, *sc_MP = nullptr, *sc_EX = nullptr, *sc_ja = nullptr, *sc_ha = nullptr;
     double *sc_H = nullptr, *sc_c1 = nullptr, *sc_c2 = nullptr, *sc_c3 = nullptr, *sc_tau = nullptr, *sc_ntau = nullptr;
     int small_threads = 0;
-    double *d_Eall = nullptr, *d_states = nullptr, *d_xinit = nullptr;   // rollout buffers
+    double *d_Eall = nullptr, *d_Escan = nullptr, *d_states = nullptr, *d_xinit = nullptr;   // rollout buffers
     // sparse drive generators (ELL): products with G_j become gathers
     bool run_assembly = true;                 // run-based device assembly (QCB_GATHER_ASSEMBLY=1: per-entry gather)
     bool sparse_drives = false;
@@ -1647,7 +1647,7 @@ void qcb_destroy(qcb_handle h) {
     cudaSetDevice(h->device);
     free_scratch(h);
     void *ptrs[] = {h->dG0, h->dGd, h->d_xoff, h->d_jcode, h->d_hcode, h->d_norm, h->d_bad, h->dZ, h->dmu, h->d_delta, h->d_jac, h->d_hess,
-                    h->d_Eall, h->d_states, h->d_xinit, h->d_ja_all, h->d_ha_all,
+                    h->d_Eall, h->d_Escan, h->d_states, h->d_xinit, h->d_ja_all, h->d_ha_all,
                     h->d_ell_idx, h->d_ellT_idx, h->d_ell_val, h->d_ellT_val, h->d_unit_norm, h->d_perm, h->d_jpieces, h->d_hpieces,
                     h->ext.d_xmap, h->ext.d_rmap, h->ext.dZ_ext, h->ext.dZp, h->ext.dmup, h->ext.d_delta_p};
     for (void *p : ptrs)
@@ -1983,6 +1983,38 @@ qcb_status qcb_rollout(qcb_handle h, const double *Z, const double *x_init, doub
         // every propagator E_k in parallel (polynomial + squarings only), then the sequential chain
         qcb_status st = eval_device(h, h->dZ, nullptr, h->d_delta, nullptr, nullptr, 0, nullptr, h->d_Eall);
         if (st != QCB_OK) return st;
+        // Large matrices: the chain x_{k+1} = E_k x_k is a scan.  P_k = E_k ... E_0 for every k by a
+        // Hillis-Steele prefix over the knots -- ceil(log2 K) rounds of batched d x d x d DMMA products on the
+        // whole GPU instead of K dependent panel products on one SM -- then every state is P_k x_0 in parallel.
+        // (Left products: round r combines P_k <- P_k * P_{k - 2^r}.)
+        if (h->large && h->dp == h->d && h->K >= 8 && !getenv("QCB_ROLLOUT_CHAIN")) {
+            ensure_out(h, &h->d_Escan, (size_t)h->units * dd);
+            double *A = h->d_Eall, *B = h->d_Escan;
+            const int K = h->K;
+            for (int step = 1; step < K; step <<= 1) {
+                for (int sys = 0; sys < h->S; ++sys) {
+                    double *As = A + (size_t)sys * K * dd, *Bs = B + (size_t)sys * K * dd;
+                    CK(cudaMemcpyAsync(Bs, As, (size_t)step * dd * 8, cudaMemcpyDeviceToDevice, h->stream));
+                    GemmArgs g;
+                    memset(&g, 0, sizeof(g));
+                    g.M = g.N = g.K = h->dp;
+                    g.alpha = 1.0; g.ndir = 1; g.nterm = 1; g.unit0_global = 0; g.nk = K;
+                    auto opnd = [&](const double *p) { Opnd o; o.p = p; o.su = (long long)dd; o.sd = 0; o.ss = 0; o.ld = h->dp; o.pad_ = 0; return o; };
+                    g.term[0].a = opnd(As + (size_t)step * dd);     // P_k,  k >= step
+                    g.term[0].b = opnd(As);                         // P_{k - step}
+                    g.dst = opnd(Bs + (size_t)step * dd);
+                    launch_gemm(h, g, K - step, h->stream);
+                }
+                std::swap(A, B);
+            }
+            rollout_apply_kernel<<<(unsigned)(h->S * K), 256, 0, h->stream>>>(A, x_init ? h->d_xinit : nullptr, h->dZ, h->d_xoff,
+                                                                             h->d, h->c, K, h->d_states);
+            ++h->launches;
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(states, h->d_states, ns * 8, cudaMemcpyDeviceToHost, h->stream));
+            CK(cudaStreamSynchronize(h->stream));
+            return QCB_OK;
+        }
         const size_t smem = 2 * (size_t)h->xdim * sizeof(double);
         if (smem > 200 * 1024) return fail(h, QCB_ERR_ARG, "state panel too large for the rollout kernel");
         CK(cudaFuncSetAttribute(rollout_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

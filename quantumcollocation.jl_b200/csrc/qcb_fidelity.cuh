@@ -183,6 +183,19 @@ void qcb_fidelity_destroy(qcb_fidelity f) {
 
 int64_t qcb_fidelity_x_dim(qcb_fidelity f) { return f ? f->x_dim : 0; }
 
+int64_t qcb_fidelity_rank(qcb_fidelity f) { return f ? (f->linear ? 0 : f->R) : 0; }
+
+qcb_status qcb_fidelity_factor(qcb_fidelity f, double *G, double *w) {
+    if (!f || !G || !w) return QCB_ERR_ARG;
+    if (cudaSetDevice(f->device) != cudaSuccess ||
+        cudaMemcpy(G, f->dG, (size_t)f->R * f->x_dim * 8, cudaMemcpyDeviceToHost) != cudaSuccess) {
+        cudaGetLastError();
+        return QCB_ERR_CUDA;
+    }
+    *w = f->w;
+    return QCB_OK;
+}
+
 qcb_status qcb_fidelity_eval(qcb_fidelity f, const double *x, double *F, double *grad, double *hess) {
     if (!f || !x) return QCB_ERR_ARG;
     try {

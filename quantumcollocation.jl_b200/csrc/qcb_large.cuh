@@ -978,4 +978,27 @@ rollout_chain_kernel(const double *E, const double *x_init, const double *Z, int
     }
 }
 
+// Rollout from the scanned propagators: states[s][k + 1] = P[s][k] x0[s] with P[k] = E_k ... E_0.
+// One CTA per (system, interval); P is read once (L2 / HBM), x0 comes from the trajectory or the caller.
+__global__ void __launch_bounds__(256)
+rollout_apply_kernel(const double *P, const double *x_init, const double *Z, const int *x_off, int d, int c, int K,
+                     double *states) {
+    const int s = blockIdx.x / K, k = blockIdx.x % K, dc = d * c;
+    const double *Pk = P + ((long long)s * K + k) * d * d;
+    const double *x0 = x_init ? x_init + (long long)s * dc : Z + x_off[s];
+    double *out = states + ((long long)s * (K + 1) + k + 1) * dc;
+    if (k == 0) for (int e = threadIdx.x; e < dc; e += blockDim.x) out[e - dc] = x0[e];      // knot 1: the initial state
+    for (int e = threadIdx.x; e < dc; e += blockDim.x) {
+        const int r = e % d, b = e / d;
+        double a0 = 0.0, a1 = 0.0;
+        int q = 0;
+        for (; q + 1 < d; q += 2) {
+            a0 = fma(Pk[r + (long long)q * d], x0[q + b * d], a0);
+            a1 = fma(Pk[r + (long long)(q + 1) * d], x0[q + 1 + b * d], a1);
+        }
+        if (q < d) a0 = fma(Pk[r + (long long)q * d], x0[q + b * d], a0);
+        out[e] = a0 + a1;
+    }
+}
+
 }  // namespace qcb

@@ -46,6 +46,8 @@ def test_unitary_fidelity_value_gradient_hessian(n, built_libs):
     assert abs(F - O.unitary_fidelity(x, Ug)) < 1e-12 * max(1, abs(F0))
     assert rel_err(g, g0) < 1e-12 and rel_err(H, H0) < 1e-12
     assert abs(f.eval(iso.operator_to_iso_vec(Ug), want_grad=False)[0] - 1.0) < 1e-13
+    Gf, wf = f.hessian_factor()                    # the same Hessian without the dense x_dim^2 block
+    assert Gf.shape == (2, 2 * n * n) and rel_err(2 * wf * Gf.T @ Gf, H0) < 1e-12
 
 
 def test_ket_and_subspace_fidelity(built_libs):

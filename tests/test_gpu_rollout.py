@@ -38,6 +38,29 @@ def test_rollout_matches_scipy_chain(name, N, S, path, built_libs):
     ev.close()
 
 
+def test_large_d_rollout_by_parallel_prefix(built_libs, monkeypatch):
+    """d = 128: the propagators are combined by a Hillis-Steele scan over the knots (batched DMMA
+    products), not by a sequential chain; same states as scipy's chain and as the chain kernel."""
+    w = workloads.make("cfg5", N=23)
+    ev = Evaluator(w.layout, w.G_drift, w.G_drives)
+    l0 = ev.kernel_launches
+    states = ev.rollout(w.Z)
+    n_scan = ev.kernel_launches - l0
+    assert rel_err(states, oracle_rollout(w)) < 1e-12
+    monkeypatch.setenv("QCB_ROLLOUT_CHAIN", "1")
+    chain = ev.rollout(w.Z)
+    assert rel_err(states, chain) < 1e-13
+    # 22 intervals: 5 scan rounds
+    x0 = np.random.default_rng(1).normal(size=(1, w.layout.x_dim))
+    monkeypatch.delenv("QCB_ROLLOUT_CHAIN")
+    a = ev.rollout(w.Z, x_init=x0)
+    monkeypatch.setenv("QCB_ROLLOUT_CHAIN", "1")
+    b = ev.rollout(w.Z, x_init=x0)
+    assert rel_err(a, b) < 1e-13 and np.array_equal(a[0, 0], x0[0])
+    assert n_scan > 0
+    ev.close()
+
+
 def test_rollout_closes_the_dynamics_constraint(built_libs):
     """Feeding the rolled-out states back as the trajectory gives a zero defect (the reference's
     post-solve criterion ||delta||_inf < 1e-3, smooth_pulse_problem.jl:511-515 -- here to rounding)."""
