@@ -181,7 +181,30 @@ int64_t qcb_arena_doubles(qcb_handle h, int32_t which);
 qcb_status qcb_eval_arenas_device(qcb_handle h, const double *dZ, const double *dmu, double *d_delta,
                                   double *d_jac_arenas, double *d_hess_arenas);
 qcb_status qcb_assemble_device(qcb_handle h, const double *d_jac_arenas, const double *d_hess_arenas,
-                               int64_t n_units, int32_t nk_src, double *d_jac_vals, double *d_hess_vals);
+                               int64_t n_units, int32_t nk_src, double *d_jac_vals, double *d_hess_vals,
+                               int32_t parts);
+/* Two-part delivery of the Jacobian arena.  The arena starts with the propagator E; on the unitary path
+ * 90 % of the Jacobian's entries (the x-block, c copies of -E) come from that part alone, and E is known
+ * long before the tangents.  qcb_set_arena_parts(h, 1): the next qcb_eval_arenas_device[_x] computes the
+ * defect and the propagators only and delivers the E part; (h, 2): it computes the tangents and delivers
+ * the rest of the Jacobian arena; (h, 3), the default: everything in one call.  qcb_assemble_device takes
+ * the same `parts`: 1 = the entries copied from the E part, 2 = all other entries, 3 = all. */
+qcb_status qcb_set_arena_parts(qcb_handle h, int32_t parts);
+qcb_status qcb_eval_arenas_device_x(qcb_handle h, const double *dZ, const double *dmu, int32_t new_x,
+                                    double *d_delta, double *d_jac_arenas, double *d_hess_arenas);
+/* Asynchronous mode for the device-pointer calls (qcb_eval_all_device[_x], qcb_eval_arenas_device[_x],
+ * qcb_assemble_device): with it on, a call returns as soon as its kernels are queued on the handle's
+ * streams; qcb_wait(h, 0) blocks until everything queued so far has completed and returns the status the
+ * synchronous call would have returned (QCB_ERR_RANGE for a non-finite input).  qcb_wait(h, 1) / (h, 2) /
+ * (h, 3) block only until the last delivery of the E part / of the rest of the Jacobian arena / of the
+ * Hessian arena by qcb_eval_arenas_device has left this GPU (deliveries run on a side stream behind the
+ * kernels that produce the arenas).  This is what lets the multi-GPU
+ * driver queue the Jacobian side and the Hessian side of one iterate back to back, so that the first
+ * delivery crosses NVLink while the second half is still being computed, and lets the Ipopt rank assemble
+ * foreign slabs while its own kernels run.  Buffers passed to a queued call must stay untouched until the
+ * wait.  No counterpart in the reference. */
+qcb_status qcb_set_async(qcb_handle h, int32_t on);
+qcb_status qcb_wait(qcb_handle h, int32_t what);
 qcb_status qcb_device_alloc(int32_t device, void **ptr, size_t bytes);
 void qcb_device_free(int32_t device, void *ptr);
 qcb_status qcb_ipc_export(int32_t device, void *ptr, unsigned char handle[64]);

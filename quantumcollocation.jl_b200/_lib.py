@@ -53,7 +53,11 @@ SYMBOLS = {
     "qcb_rollout": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp]),
     "qcb_arena_doubles": (ctypes.c_int64, [c_vp, ctypes.c_int32]),
     "qcb_eval_arenas_device": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
-    "qcb_assemble_device": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int64, ctypes.c_int32, c_vp, c_vp]),
+    "qcb_assemble_device": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int64, ctypes.c_int32, c_vp, c_vp, ctypes.c_int32]),
+    "qcb_set_arena_parts": (ctypes.c_int, [c_vp, ctypes.c_int32]),
+    "qcb_eval_arenas_device_x": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int32, c_vp, c_vp, c_vp]),
+    "qcb_set_async": (ctypes.c_int, [c_vp, ctypes.c_int32]),
+    "qcb_wait": (ctypes.c_int, [c_vp, ctypes.c_int32]),
     "qcb_device_alloc": (ctypes.c_int, [ctypes.c_int32, ctypes.POINTER(c_vp), ctypes.c_size_t]),
     "qcb_device_free": (None, [ctypes.c_int32, c_vp]),
     "qcb_ipc_export": (ctypes.c_int, [ctypes.c_int32, c_vp, ctypes.c_char_p]),

@@ -176,10 +176,30 @@ class Evaluator:
         _sync_producers(dZ, dmu, d_delta, d_jac_arenas, d_hess_arenas)
         self._check(self.lib.qcb_eval_arenas_device(self.h, _ptr(dZ), _ptr(dmu), _ptr(d_delta), _ptr(d_jac_arenas), _ptr(d_hess_arenas)))
 
-    def assemble_device(self, d_jac_arenas, d_hess_arenas, n_units, nk_src, d_jac, d_hess):
-        """COO value vectors of `n_units` units from their arenas (runs on this handle's GPU)."""
+    def eval_arenas_device_x(self, dZ, dmu, new_x, d_delta, d_jac_arenas, d_hess_arenas):
+        _sync_producers(dZ, dmu, d_delta, d_jac_arenas, d_hess_arenas)
+        self._check(self.lib.qcb_eval_arenas_device_x(self.h, _ptr(dZ), _ptr(dmu), 1 if new_x else 0, _ptr(d_delta),
+                                                      _ptr(d_jac_arenas), _ptr(d_hess_arenas)))
+
+    def set_async(self, on: bool):
+        """Device-pointer calls return once queued; collect completion with wait()."""
+        self._check(self.lib.qcb_set_async(self.h, 1 if on else 0))
+
+    def wait(self, what: int = 0):
+        """0: everything queued on this handle; 1 / 2 / 3: the last delivery of the E part / of the rest of
+        the Jacobian arena / of the Hessian arena."""
+        self._check(self.lib.qcb_wait(self.h, what))
+
+    def assemble_device(self, d_jac_arenas, d_hess_arenas, n_units, nk_src, d_jac, d_hess, parts: int = 3):
+        """COO value vectors of `n_units` units from their arenas (runs on this handle's GPU).
+        parts: 1 = Jacobian entries that copy the E part of the arena, 2 = all others, 3 = all."""
         _sync_producers(d_jac_arenas, d_hess_arenas, d_jac, d_hess)
-        self._check(self.lib.qcb_assemble_device(self.h, _ptr(d_jac_arenas), _ptr(d_hess_arenas), n_units, nk_src, _ptr(d_jac), _ptr(d_hess)))
+        self._check(self.lib.qcb_assemble_device(self.h, _ptr(d_jac_arenas), _ptr(d_hess_arenas), n_units, nk_src,
+                                                 _ptr(d_jac), _ptr(d_hess), parts))
+
+    def set_arena_parts(self, parts: int):
+        """1: deliver the propagators (E part) only; 2: the rest of the Jacobian arena; 3: everything."""
+        self._check(self.lib.qcb_set_arena_parts(self.h, parts))
 
     def rollout(self, Z, x_init=None):
         """States [S, N, x_dim] of x_{k+1} = exp(dt_k G(u_k)) x_k (x_init [S, x_dim] or knot 1 of Z)."""

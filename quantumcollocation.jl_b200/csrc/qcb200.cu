@@ -140,6 +140,12 @@ struct qcb_handle_s {
     // arena delivery (qcb_eval_arenas_device): where the per-unit value arenas of the slab are written
     // instead of being assembled into COO vectors here; may be another GPU's memory
     double *arena_out_j = nullptr, *arena_out_h = nullptr;
+    cudaEvent_t ship_ev[3] = {nullptr, nullptr, nullptr};   // last delivery of [0] the E part, [1] the rest of the Jacobian arena, [2] the Hessian arena
+    int arena_parts = 3;           // qcb_set_arena_parts: 1 = propagators only (E part), 2 = the rest of the Jacobian arena, 3 = all
+    // Asynchronous mode (qcb_set_async): device-pointer calls return once their work is queued; completion
+    // and the range check are collected by qcb_wait.  Lets a caller queue the Jacobian and the Hessian side
+    // of one iterate back to back and overlap the delivery of the first with the computation of the second.
+    bool async_mode = false;
 
     // State index map (variational integrators, src/quantum_integrators.jl:140-169: the state is a
     // concatenation of several named components).  When the caller gives one, the kernels work on a
@@ -813,10 +819,10 @@ struct HostOut { double *delta, *jac, *hess; bool compact; };
 // dst[unit] = src[unit]: one arena (stride doubles) per unit, 16-byte accesses; dst may be peer memory.
 constexpr long long SHIP_PIECE = 8192;
 __global__ void __launch_bounds__(256)
-arena_ship_kernel(const double *src, long long stride, double *dst, int u0, const int *perm) {
+arena_ship_kernel(const double *src, long long stride, double *dst, int u0, const int *perm, long long lo, long long hi) {
     const int unit = blockIdx.y;
     const long long ug = perm ? perm[u0 + unit] : u0 + unit;
-    const long long b = (long long)blockIdx.x * SHIP_PIECE, len = min(SHIP_PIECE, stride - b);
+    const long long b = lo + (long long)blockIdx.x * SHIP_PIECE, len = min(SHIP_PIECE, hi - b);     // entries [lo, hi) of the arena
     const double *s = src + (long long)unit * stride + b;
     double *o = dst + ug * stride + b;
     if (((reinterpret_cast<uintptr_t>(o) | reinterpret_cast<uintptr_t>(s)) & 15) == 0) {
@@ -981,6 +987,22 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         }
         delta_kernel<<<nu, 256, 0, st>>>(q, dZ, X.at(h->sc_EX, pan), pan, d_delta, u0, perm);
         ++h->launches;
+        const long long e_part = (long long)h->dp * h->dp;        // the arena starts with the full E
+        if (h->arena_out_j && (h->arena_parts & 1) && !(wj && h->arena_parts == 3)) {
+            // propagators first: the x-block of the Jacobian (c copies of -E, 90 % of its entries on the unitary
+            // path) depends on nothing else, so the Ipopt rank can assemble it while the tangents are computed
+            if (h->iso) { iso_expand_kernel<<<nu, 256, 0, st>>>(X.at(X.ja, h->JA), h->JA, h->dp); ++h->launches; }
+            if (h->chunk_events.size() <= chunk_idx) {
+                cudaEvent_t e;
+                CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                h->chunk_events.push_back(e);
+            }
+            CK(cudaEventRecord(h->chunk_events[chunk_idx], st));
+            CK(cudaStreamWaitEvent(h->copy_stream, h->chunk_events[chunk_idx], 0));
+            arena_ship_kernel<<<dim3((unsigned)((e_part + SHIP_PIECE - 1) / SHIP_PIECE), (unsigned)nu), 256, 0, h->copy_stream>>>(
+                X.at(X.ja, h->JA), h->JA, h->arena_out_j, u0, perm, 0, e_part);
+            ++h->launches;
+        }
         if (E_out) {      // rollouts: keep the (unpadded, full) propagator of every unit
             if (h->iso) { iso_expand_kernel<<<nu, 256, 0, st>>>(X.at(X.ja, h->JA), h->JA, h->dp); ++h->launches; }
             extract_E_kernel<<<nu, 256, 0, st>>>(X.at(X.ja, h->JA), h->JA, h->dp, h->d, E_out + (size_t)u0 * h->d * h->d);
@@ -1063,17 +1085,27 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
                                                           X.at(X.ha, h->HA), h->HA, (m + 1) * pan, h->iso ? 2.0 : 1.0);
                 ++h->launches;
             }
-            if (h->arena_out_j || h->arena_out_h) {
+            if ((wj && h->arena_out_j) || (wh && h->arena_out_h)) {
                 // multi-GPU delivery of the compact form: every distinct number of the unit once, stored
-                // straight into the Ipopt rank's HBM (NVLink peer stores); that rank assembles the COO vectors
-                if (wj && h->arena_out_j) {
-                    arena_ship_kernel<<<dim3((unsigned)((h->JA + SHIP_PIECE - 1) / SHIP_PIECE), (unsigned)nu), 256, 0, st>>>(
-                        X.at(X.ja, h->JA), h->JA, h->arena_out_j, u0, perm);
+                // straight into the Ipopt rank's HBM (NVLink peer stores); that rank assembles the COO vectors.
+                // The copy runs on the side stream behind this chunk's kernels, so it overlaps whatever the
+                // compute streams do next (the next chunk, or the Hessian side of the same iterate).
+                if (h->chunk_events.size() <= chunk_idx) {
+                    cudaEvent_t e;
+                    CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                    h->chunk_events.push_back(e);
+                }
+                CK(cudaEventRecord(h->chunk_events[chunk_idx], st));
+                CK(cudaStreamWaitEvent(h->copy_stream, h->chunk_events[chunk_idx], 0));
+                if (wj && h->arena_out_j && (h->arena_parts & 2)) {
+                    const long long lo = h->arena_parts == 3 ? 0 : e_part;       // the E part may have gone ahead
+                    arena_ship_kernel<<<dim3((unsigned)((h->JA - lo + SHIP_PIECE - 1) / SHIP_PIECE), (unsigned)nu), 256, 0, h->copy_stream>>>(
+                        X.at(X.ja, h->JA), h->JA, h->arena_out_j, u0, perm, lo, h->JA);
                     ++h->launches;
                 }
                 if (wh && h->arena_out_h) {
-                    arena_ship_kernel<<<dim3((unsigned)((h->HA + SHIP_PIECE - 1) / SHIP_PIECE), (unsigned)nu), 256, 0, st>>>(
-                        X.at(X.ha, h->HA), h->HA, h->arena_out_h, u0, perm);
+                    arena_ship_kernel<<<dim3((unsigned)((h->HA + SHIP_PIECE - 1) / SHIP_PIECE), (unsigned)nu), 256, 0, h->copy_stream>>>(
+                        X.at(X.ha, h->HA), h->HA, h->arena_out_h, u0, perm, 0, h->HA);
                     ++h->launches;
                 }
             }
@@ -1170,6 +1202,12 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         }
     }
     if (compact) expand_prev(chunk_idx - 1);
+    if (h->arena_out_j || h->arena_out_h) {
+        for (int i = 0; i < 3; ++i) if (!h->ship_ev[i]) CK(cudaEventCreateWithFlags(&h->ship_ev[i], cudaEventDisableTiming));
+        if (h->arena_out_j && (h->arena_parts & 1)) CK(cudaEventRecord(h->ship_ev[0], h->copy_stream));
+        if (wj && h->arena_out_j && (h->arena_parts & 2)) CK(cudaEventRecord(h->ship_ev[1], h->copy_stream));
+        if (wh && h->arena_out_h) CK(cudaEventRecord(h->ship_ev[2], h->copy_stream));
+    }
     if (slices) {       // every slice is intact: a new_x = 0 call may pick up from here
         h->cache_have = 1 | (((wj || wh) || (reuse & 2)) ? 2 : 0);
         h->cache_s_slab = s_slab;
@@ -1384,8 +1422,9 @@ qcb_status eval_device_inner(qcb_handle_s *h, const double *dZ, const double *dm
         }
         return QCB_OK;
     }
+    if (h->async_mode && !host && !h->profiling) return QCB_OK;      // qcb_wait collects completion and the range flag
     CK(cudaStreamSynchronize(h->stream));
-    if (host) CK(cudaStreamSynchronize(h->copy_stream));
+    if (host || h->arena_out_j || h->arena_out_h) CK(cudaStreamSynchronize(h->copy_stream));
     if (h->profiling) {
         for (size_t i = 0; i + 1 < h->prof_used; i += 2) {
             float t = 0;
@@ -1665,6 +1704,7 @@ void qcb_destroy(qcb_handle h) {
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->stream2) cudaStreamDestroy(h->stream2);
     for (int i = 0; i < 2; ++i) if (h->lane_ev[i]) cudaEventDestroy(h->lane_ev[i]);
+    for (int i = 0; i < 3; ++i) if (h->ship_ev[i]) cudaEventDestroy(h->ship_ev[i]);
     delete h;
 }
 
@@ -1851,7 +1891,7 @@ qcb_status qcb_eval_arenas_device(qcb_handle h, const double *dZ, const double *
     if (!h->large) return fail(h, QCB_ERR_ARG, "arena delivery exists on the large-d path only (small units are cheaper to deliver assembled)");
     try {
         CK(cudaSetDevice(h->device));
-        const int want = (d_jac_arenas ? 1 : 0) | ((d_hess_arenas && dmu) ? 2 : 0);
+        const int want = ((d_jac_arenas && (h->arena_parts & 2)) ? 1 : 0) | ((d_hess_arenas && dmu) ? 2 : 0);
         if (!d_delta) { ensure_out(h, &h->d_delta, (size_t)h->units * h->xdim); d_delta = h->d_delta; }
         h->arena_out_j = d_jac_arenas; h->arena_out_h = d_hess_arenas;
         qcb_status st;
@@ -1864,27 +1904,75 @@ qcb_status qcb_eval_arenas_device(qcb_handle h, const double *dZ, const double *
     }
 }
 
+qcb_status qcb_eval_arenas_device_x(qcb_handle h, const double *dZ, const double *dmu, int32_t new_x, double *d_delta,
+                                    double *d_jac_arenas, double *d_hess_arenas) {
+    if (!h) return QCB_ERR_ARG;
+    h->reuse = new_x ? 0 : 3;
+    qcb_status st = qcb_eval_arenas_device(h, dZ, dmu, d_delta, d_jac_arenas, d_hess_arenas);
+    h->reuse = 0;
+    return st;
+}
+
+qcb_status qcb_set_arena_parts(qcb_handle h, int32_t parts) {
+    if (!h || parts < 1 || parts > 3) return QCB_ERR_ARG;
+    h->arena_parts = parts;
+    return QCB_OK;
+}
+
+qcb_status qcb_set_async(qcb_handle h, int32_t on) {
+    if (!h) return QCB_ERR_ARG;
+    if (on && h->ext.on) return fail(h, QCB_ERR_ARG, "asynchronous mode is not available on a handle created with a state index map");
+    h->async_mode = on != 0;
+    return QCB_OK;
+}
+
+qcb_status qcb_wait(qcb_handle h, int32_t what) {
+    if (!h) return QCB_ERR_ARG;
+    try {
+        CK(cudaSetDevice(h->device));
+        if (what >= 1 && what <= 3) {          // the last delivery of the E part (1), of the rest of the Jacobian arena (2),
+            if (h->ship_ev[what - 1]) CK(cudaEventSynchronize(h->ship_ev[what - 1]));   // of the Hessian arena (3) has completed
+            return QCB_OK;
+        }
+        CK(cudaStreamSynchronize(h->stream));
+        if (h->stream2) CK(cudaStreamSynchronize(h->stream2));
+        CK(cudaStreamSynchronize(h->copy_stream));
+        int bad = 0;
+        CK(cudaMemcpy(&bad, h->d_bad, sizeof(int), cudaMemcpyDeviceToHost));
+        if (bad & 1) { h->err = "non-finite input or ||dt*G(u)||_1 beyond the supported range"; return QCB_ERR_RANGE; }
+        return QCB_OK;
+    } catch (const CudaFail &f) {
+        return fail_cuda(h, f);
+    }
+}
+
 qcb_status qcb_assemble_device(qcb_handle h, const double *d_jac_arenas, const double *d_hess_arenas, int64_t n_units,
-                               int32_t nk_src, double *d_jac_vals, double *d_hess_vals) {
+                               int32_t nk_src, double *d_jac_vals, double *d_hess_vals, int32_t parts) {
+    if (parts < 1 || parts > 3) return fail(h, QCB_ERR_ARG, "parts must be 1, 2 or 3");
     if (!h || n_units < 0 || nk_src < 1) return fail(h, QCB_ERR_ARG, "bad argument");
     if ((d_jac_arenas && !d_jac_vals) || (d_hess_arenas && !d_hess_vals)) return fail(h, QCB_ERR_ARG, "null output");
     if (n_units == 0) return QCB_OK;
     try {
         CK(cudaSetDevice(h->device));
+        // on the side stream: the Ipopt rank assembles foreign slabs while its own kernels keep running
+        cudaStream_t st = h->copy_stream;
         if (d_jac_arenas) {
             if (!h->d_jpieces) upload_pieces(h, h->h_jcode, h->jnnz_unit, &h->d_jpieces, &h->n_jpieces);
-            assemble_runs_kernel<<<(unsigned)((size_t)n_units * h->n_jpieces), 256, 0, h->stream>>>(
-                d_jac_arenas, h->JA, h->d_jcode, h->jnnz_unit, h->d_jpieces, h->n_jpieces, d_jac_vals, 0, nk_src, 0, nullptr);
+            // parts: 1 = entries copied from the E part of the arena (the x-block), 2 = everything else
+            const unsigned e_part = (unsigned)((long long)h->dp * h->dp);
+            assemble_runs_kernel<<<(unsigned)((size_t)n_units * h->n_jpieces), 256, 0, st>>>(
+                d_jac_arenas, h->JA, h->d_jcode, h->jnnz_unit, h->d_jpieces, h->n_jpieces, d_jac_vals, 0, nk_src, 0, nullptr,
+                parts == 3 ? 0u : e_part, parts);
             ++h->launches;
         }
         if (d_hess_arenas) {
             if (!h->d_hpieces) upload_pieces(h, h->h_hcode, h->hnnz_unit, &h->d_hpieces, &h->n_hpieces);
-            assemble_runs_kernel<<<(unsigned)((size_t)n_units * h->n_hpieces), 256, 0, h->stream>>>(
+            assemble_runs_kernel<<<(unsigned)((size_t)n_units * h->n_hpieces), 256, 0, st>>>(
                 d_hess_arenas, h->HA, h->d_hcode, h->hnnz_unit, h->d_hpieces, h->n_hpieces, d_hess_vals, 0, nk_src, 0, nullptr);
             ++h->launches;
         }
         CK(cudaGetLastError());
-        CK(cudaStreamSynchronize(h->stream));
+        if (!h->async_mode) CK(cudaStreamSynchronize(st));
         return QCB_OK;
     } catch (const CudaFail &f) {
         return fail_cuda(h, f);

@@ -886,11 +886,15 @@ struct Piece { long long dst; unsigned src; unsigned len; unsigned kind; unsigne
 __global__ void __launch_bounds__(256)
 assemble_runs_kernel(const double *arena, long long arena_stride, const uint32_t *code, long long nnz,
                      const Piece *pieces, int npieces, double *out, int u0_global, int nk, int out_u0,
-                     const int *perm) {
+                     const int *perm, unsigned split = 0, int parts = 3) {
     const int unit = blockIdx.x / npieces, pi = blockIdx.x - unit * npieces;
     const int sys = (perm ? perm[u0_global + unit] : u0_global + unit) / nk;
     const Piece pc = pieces[(long long)sys * npieces + pi];
     if (pc.len == 0) return;
+    if (parts != 3) {       // two-pass assembly: COPY pieces wholly inside arena[0, split) first, the rest later
+        const bool head = pc.kind != 0 && pc.src + pc.len <= split;
+        if (head != (parts == 1)) return;
+    }
     const double *ar = arena + (long long)unit * arena_stride;
     double *o = out + (long long)(perm ? perm[out_u0 + unit] : out_u0 + unit) * nnz + pc.dst;
     if (pc.kind == 0) {

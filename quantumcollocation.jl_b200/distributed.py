@@ -176,19 +176,60 @@ class ArenaDelivery:
             self.dist.broadcast(mu, src=self.root, group=self.group)
         torch.cuda.current_stream(Z.device).synchronize()     # the library runs on its own stream
 
-    def evaluate(self, dZ, dmu):
-        L, b, k0 = self.L, self.buf.base, self.k0
-        if self.rank == self.root:
-            self.ev.eval_all_device(dZ, dmu, b[0] + 8 * k0 * L.x_dim, b[1] + 8 * k0 * L.jac_nnz_unit,
-                                    b[2] + 8 * k0 * L.hess_nnz_unit)
-        else:
-            self.ev.eval_arenas_device(dZ, dmu, b[0] + 8 * k0 * L.x_dim, b[3] + 8 * k0 * self.JA, b[4] + 8 * k0 * self.HA)
-        self.dist.barrier(group=self.group)
-        if self.rank == self.root:
-            # every maximal run of intervals owned by other ranks (root 0: one run)
-            for a, e in self._foreign_runs():
-                self.ev.assemble_device(b[3] + 8 * a * self.JA, b[4] + 8 * a * self.HA, e - a, e - a,
-                                        b[1] + 8 * a * L.jac_nnz_unit, b[2] + 8 * a * L.hess_nnz_unit)
+    def evaluate(self, dZ, dmu, pipelined: bool = True):
+        """One evaluation with every value vector complete in the root's buffers on return.
+
+        pipelined: propagators, tangents and the Hessian side of the iterate are queued back to back as three
+        calls (each reuses what the previous one computed, new_x = 0).  Other ranks: the E part of the
+        Jacobian arena leaves as soon as the squarings are done, the rest of it while the Hessian side is
+        computed, all on a side stream.  Root: after the first barrier it assembles the x-blocks of the foreign
+        slabs (c copies of -E per unit: 90 % of the Jacobian entries on the unitary path) on its side stream
+        while everybody, itself included, is still computing tangents; after the second barrier the remaining
+        Jacobian entries, after the third the Hessian values."""
+        L, b, k0, ev = self.L, self.buf.base, self.k0, self.ev
+        root = self.rank == self.root
+        pd, pj, ph = b[0] + 8 * k0 * L.x_dim, b[1] + 8 * k0 * L.jac_nnz_unit, b[2] + 8 * k0 * L.hess_nnz_unit
+        aj, ah = b[3] + 8 * k0 * self.JA, b[4] + 8 * k0 * self.HA
+        runs = self._foreign_runs() if root else []
+        if not pipelined or dmu is None:
+            if root:
+                ev.eval_all_device(dZ, dmu, pd, pj, ph)
+            else:
+                ev.eval_arenas_device(dZ, dmu, pd, aj, ah)
+            self.dist.barrier(group=self.group)
+            for a, e in runs:
+                ev.assemble_device(b[3] + 8 * a * self.JA, b[4] + 8 * a * self.HA if dmu is not None else None, e - a, e - a,
+                                   b[1] + 8 * a * L.jac_nnz_unit, b[2] + 8 * a * L.hess_nnz_unit)
+            return
+        ev.set_async(True)
+        try:
+            if root:
+                ev.eval_all_device_x(dZ, None, True, pd, pj, None)        # defect + Jacobian values of the own slab
+                ev.eval_all_device_x(dZ, dmu, False, pd, None, ph)        # Hessian values, queued right behind
+            else:
+                ev.set_arena_parts(1)
+                ev.eval_arenas_device_x(dZ, None, True, pd, aj, None)     # propagators: the E part goes ahead
+                ev.set_arena_parts(2)
+                ev.eval_arenas_device_x(dZ, None, False, pd, aj, None)    # tangents; the rest of the Jacobian arena
+                ev.set_arena_parts(3)
+                ev.eval_arenas_device_x(dZ, dmu, False, pd, None, ah)     # Hessian side overlaps that delivery
+                ev.wait(1)
+            self.dist.barrier(group=self.group)                           # every E part has landed
+            for a, e in runs:                                             # x-blocks: c copies of -E per unit
+                ev.assemble_device(b[3] + 8 * a * self.JA, None, e - a, e - a, b[1] + 8 * a * L.jac_nnz_unit, None, parts=1)
+            if not root:
+                ev.wait(2)
+            self.dist.barrier(group=self.group)                           # every Jacobian arena is complete
+            for a, e in runs:
+                ev.assemble_device(b[3] + 8 * a * self.JA, None, e - a, e - a, b[1] + 8 * a * L.jac_nnz_unit, None, parts=2)
+            ev.wait(0)
+            self.dist.barrier(group=self.group)                           # every Hessian arena has landed
+            for a, e in runs:
+                ev.assemble_device(None, b[4] + 8 * a * self.HA, e - a, e - a, None, b[2] + 8 * a * L.hess_nnz_unit)
+            ev.wait(0)
+        finally:
+            ev.set_arena_parts(3)
+            ev.set_async(False)
 
     def _foreign_runs(self):
         runs, K = [], self.L.K

@@ -64,10 +64,17 @@ for cls, cases in ((distributed.PeerDelivery, [("cfg2", 41), ("cfg5", 21)]), (di
         else:
             dZ, dmu = torch.from_numpy(w.Z).to(dev), torch.from_numpy(w.mu).to(dev)
             torch.cuda.synchronize()
-        for rep in range(2):        # twice: the buffers are reused
-            dl.evaluate(dZ, dmu)
-        if rank == 0:
-            same(dl.fetch(), reference(w), f"{cls.__name__} {name} N={N}")
+        ref = reference(w) if rank == 0 else None
+        modes = (True, False) if cls is distributed.ArenaDelivery else (None,)
+        for mode in modes:
+            for rep in range(2):        # twice: the buffers are reused
+                if mode is None:
+                    dl.evaluate(dZ, dmu)
+                else:
+                    dl.evaluate(dZ, dmu, pipelined=mode)
+            if rank == 0:
+                same(dl.fetch(), ref, f"{cls.__name__} {name} N={N}" + ("" if mode is None else (" pipelined" if mode else " plain")))
+            dist.barrier()
         dist.barrier()
         dl.close()
         ev.close()
