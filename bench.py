@@ -396,6 +396,8 @@ def main():
         bmu = dmu if rank == 0 else torch.empty_like(dmu)
         del d_jac, d_hess               # the drivers own their result buffers
         torch.cuda.empty_cache()
+        # (a smaller slab on the Ipopt rank, to make room for its assembly work, was measured slower at 2, 4 and
+        # 8 GPUs: the other ranks' compute + delivery chain is the critical path, not the root -- DESIGN.md 9)
         ad = qdist.ArenaDelivery(ev, L, local)
 
         def arena_step():

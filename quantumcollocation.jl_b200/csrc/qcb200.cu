@@ -1010,6 +1010,35 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         }
         if (wj || wh) {
             const bool tangents = !(reuse & 2);      // forward tangents, L_j levels, G E and the Jacobian arena
+            // Hessian side of an iterate whose tangents are already there (new_x = 0): the (x,u) and (x,dt)
+            // panels -- all but a few hundred numbers of the Hessian arena -- need only L_j, G E and the
+            // multipliers, so they are formed first and, in a multi-GPU delivery, leave while the second-order
+            // sweeps run
+            const bool hx_early = wh && !tangents;
+            const long long h_panels = (long long)(m + 1) * pan;
+            auto hx_panels = [&]() {
+                X.level = s;
+                Opnd GE_ = X.fixed(QR_NUM_FIXED), L_ = X.reg(QR_L);
+                Opnd HXU = X.mat(X.ha, h->HA, pan), HXT = X.mat(X.ha + m * pan, h->HA);
+                if (m > 0) X.product(HXU, L_, 1, MP, 0, h->dp, h->cp, h->dp, m, 1.0, X.at(h->sc_ntau, 1));
+                X.product(HXT, GE_, 1, MP, 0, h->dp, h->cp, h->dp, 1, -1.0, nullptr);
+            };
+            auto ship_h = [&](long long lo, long long hi) {
+                if (h->chunk_events.size() <= chunk_idx) {
+                    cudaEvent_t e;
+                    CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                    h->chunk_events.push_back(e);
+                }
+                CK(cudaEventRecord(h->chunk_events[chunk_idx], st));
+                CK(cudaStreamWaitEvent(h->copy_stream, h->chunk_events[chunk_idx], 0));
+                arena_ship_kernel<<<dim3((unsigned)((hi - lo + SHIP_PIECE - 1) / SHIP_PIECE), (unsigned)nu), 256, 0, h->copy_stream>>>(
+                    X.at(X.ha, h->HA), h->HA, h->arena_out_h, u0, perm, lo, hi);
+                ++h->launches;
+            };
+            if (hx_early) {
+                hx_panels();
+                if (h->arena_out_h) ship_h(0, h_panels);
+            }
             if (wh) {
                 if (h->iso) {   // W = M X^T is a general matrix: project it onto the iso algebra (half storage)
                     // W (dp x dp per unit) borrows the head of this slice of the per-drive temporary U (dead
@@ -1070,9 +1099,7 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             }
             if (wh) {
                 Opnd Wt = X.W(s);
-                Opnd HXU = X.mat(X.ha, h->HA, pan), HXT = X.mat(X.ha + m * pan, h->HA);
-                if (m > 0) X.product(HXU, L, 1, MP, 0, h->dp, h->cp, h->dp, m, 1.0, X.at(h->sc_ntau, 1));
-                X.product(HXT, GE, 1, MP, 0, h->dp, h->cp, h->dp, 1, -1.0, nullptr);
+                if (!hx_early) hx_panels();
                 X.product(WE, Wt, 0, Ef, 1, h->dp, ncol, h->dp, 1, 1.0, nullptr);
                 X.product(GW, G, 1, Wt, 0, h->dp, ncol, h->dp, 1, 1.0, nullptr);
                 if (m > 0) {
@@ -1103,9 +1130,10 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
                         X.at(X.ja, h->JA), h->JA, h->arena_out_j, u0, perm, lo, h->JA);
                     ++h->launches;
                 }
-                if (wh && h->arena_out_h) {
-                    arena_ship_kernel<<<dim3((unsigned)((h->HA + SHIP_PIECE - 1) / SHIP_PIECE), (unsigned)nu), 256, 0, h->copy_stream>>>(
-                        X.at(X.ha, h->HA), h->HA, h->arena_out_h, u0, perm, 0, h->HA);
+                if (wh && h->arena_out_h) {     // the panels may have gone ahead: then only the scalars are left
+                    const long long lo = hx_early ? h_panels : 0;
+                    arena_ship_kernel<<<dim3((unsigned)((h->HA - lo + SHIP_PIECE - 1) / SHIP_PIECE), (unsigned)nu), 256, 0, h->copy_stream>>>(
+                        X.at(X.ha, h->HA), h->HA, h->arena_out_h, u0, perm, lo, h->HA);
                     ++h->launches;
                 }
             }
@@ -1594,7 +1622,12 @@ qcb_status qcb_create(qcb_handle *out, const qcb_desc *desc) {
         if (h->JA >= (1LL << 31) || h->HA >= (1LL << 31)) { delete h; return fail(nullptr, QCB_ERR_ARG, "unit too large for 31-bit slot codes"); }
 
         CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-        CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        {   // side stream (deliveries, foreign-slab assembly, D2H): highest priority, so that its small CTAs take
+            // the SM slots that free up instead of queueing behind a compute kernel's pending waves
+            int lo_p = 0, hi_p = 0;
+            CK(cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p));
+            CK(cudaStreamCreateWithPriority(&h->copy_stream, cudaStreamNonBlocking, hi_p));
+        }
         for (auto &e : h->ev) CK(cudaEventCreate(&e));
         init_constants();
         // generators, padded to dp x dp

@@ -167,6 +167,7 @@ class ArenaDelivery:
         self.buf = _RootBuffers((L.K * L.x_dim, L.K * L.jac_nnz_unit, L.K * L.hess_nnz_unit, L.K * self.JA, L.K * self.HA),
                                 device_index, root, group)
         self.k0, self.k1 = evaluator.k_begin, evaluator.k_end
+        self.trace = None       # set to {} to collect host timestamps of the pipelined step's stages
 
     def broadcast(self, Z, mu):
         """NCCL broadcast of Z and mu (device tensors; allocated by the caller on every rank)."""
@@ -201,6 +202,10 @@ class ArenaDelivery:
                 ev.assemble_device(b[3] + 8 * a * self.JA, b[4] + 8 * a * self.HA if dmu is not None else None, e - a, e - a,
                                    b[1] + 8 * a * L.jac_nnz_unit, b[2] + 8 * a * L.hess_nnz_unit)
             return
+        import time
+        tr = self.trace
+        t0 = time.perf_counter()
+        mark = (lambda name: tr.setdefault(name, []).append(time.perf_counter() - t0)) if tr is not None else (lambda name: None)
         ev.set_async(True)
         try:
             if root:
@@ -213,20 +218,28 @@ class ArenaDelivery:
                 ev.eval_arenas_device_x(dZ, None, False, pd, aj, None)    # tangents; the rest of the Jacobian arena
                 ev.set_arena_parts(3)
                 ev.eval_arenas_device_x(dZ, dmu, False, pd, None, ah)     # Hessian side overlaps that delivery
+                mark("queued")
                 ev.wait(1)
+            mark("E shipped")
             self.dist.barrier(group=self.group)                           # every E part has landed
+            mark("barrier 1")
             for a, e in runs:                                             # x-blocks: c copies of -E per unit
                 ev.assemble_device(b[3] + 8 * a * self.JA, None, e - a, e - a, b[1] + 8 * a * L.jac_nnz_unit, None, parts=1)
             if not root:
                 ev.wait(2)
+            mark("J shipped")
             self.dist.barrier(group=self.group)                           # every Jacobian arena is complete
+            mark("barrier 2")
             for a, e in runs:
                 ev.assemble_device(b[3] + 8 * a * self.JA, None, e - a, e - a, b[1] + 8 * a * L.jac_nnz_unit, None, parts=2)
             ev.wait(0)
+            mark("own work done")
             self.dist.barrier(group=self.group)                           # every Hessian arena has landed
+            mark("barrier 3")
             for a, e in runs:
                 ev.assemble_device(None, b[4] + 8 * a * self.HA, e - a, e - a, None, b[2] + 8 * a * L.hess_nnz_unit)
             ev.wait(0)
+            mark("end")
         finally:
             ev.set_arena_parts(3)
             ev.set_async(False)
