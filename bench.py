@@ -627,9 +627,9 @@ def main():
             achieved = prof["flops"] / (prof["ms"] * 1e-3) / 1e12
             traffic, traffic_src = None, None
             try:    # DRAM bytes per tensor flop of this kernel from the committed ncu --set full capture
-                tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic_bgemm_iso.json")))
+                tj = json.load(open(os.path.join(ROOT, "profiles", "r02_traffic_bgemm_iso.json")))
                 traffic = tj["dram_bytes_per_flop_per_drive_launches"] * prof["flops"] / prof["launches"]
-                traffic_src = "profiles/r01_traffic_bgemm_iso.json: (dram__bytes_read.sum + dram__bytes_write.sum) per tensor flop x flops of the average launch"
+                traffic_src = "profiles/r02_traffic_bgemm_iso.json: (dram__bytes_read.sum + dram__bytes_write.sum) per tensor flop x flops of the average launch"
             except Exception:
                 pass
             roofline = {
