@@ -1271,9 +1271,6 @@ void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     const int dd = (h->d / small_tile_rows(h->d)) * h->d;
     int tpu = 1;
     if (dd <= 32) { while (tpu < dd) tpu <<= 1; } else tpu = std::min(512, round_up(dd, 32));
-    // the specialised tiled instance runs the drive directions side by side: (tiles per matrix) x m threads
-    const bool dirpar = h->d == 4 && h->c == 2 && h->m == 2;
-    if (dirpar) tpu = dd * h->m;
     const size_t unit_d = small_unit_doubles(h->d, h->c, h->m, s);
     if (small_smem_doubles(h->d, h->c, h->m, s, 1) * 8 > 227 * 1024) throw SmallCapacity{s};
     // units per CTA: the kernel is latency bound (dependent tiny products, sub-warp barriers), so what
@@ -1294,7 +1291,7 @@ void eval_small(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     const size_t smem = small_smem_doubles(h->d, h->c, h->m, s, upc) * sizeof(double);
     // fully specialised instances of the BASELINE shapes (state columns, drives, threads per unit)
     const int dcm = h->d * 10000 + h->c * 100 + h->m;
-    if (dirpar) { launch_small<4, 2, 2, (4 / QCB_TILE4) * 4 * 2>(h, p, smem); ++h->launches; CK(cudaGetLastError()); return; }
+    if (dcm == 40202 && tpu == 16 / QCB_TILE4) { launch_small<4, 2, 2, 16 / QCB_TILE4>(h, p, smem); ++h->launches; CK(cudaGetLastError()); return; }
     if (dcm == 60302 && tpu == 64) { launch_small<6, 3, 2, 64>(h, p, smem); ++h->launches; CK(cudaGetLastError()); return; }
     if (dcm == 180904 && tpu == 352) { launch_small<18, 9, 4, 352>(h, p, smem); ++h->launches; CK(cudaGetLastError()); return; }
     if (dcm == 180104 && tpu == 352) { launch_small<18, 1, 4, 352>(h, p, smem); ++h->launches; CK(cudaGetLastError()); return; }

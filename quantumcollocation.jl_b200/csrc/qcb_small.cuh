@@ -13,7 +13,9 @@
 #include <utility>
 #include "qcb_program.h"
 
-// rows of the d = 4 register tile: measured on cfg4 -- 1: 0.352 ms, 2: 0.364 ms, 4: 0.330 ms
+// rows of the d = 4 register tile: measured on cfg4 -- 1: 0.352 ms, 2: 0.364 ms, 4: 0.330 ms.  (Running the m
+// drive directions side by side on m x 4 threads per unit was also measured: 0.40 ms -- 254 registers per
+// thread and idle halves in the per-unit ops cost more than the shorter dependency chain gains.)
 #ifndef QCB_TILE4
 #define QCB_TILE4 4
 #endif
@@ -66,7 +68,6 @@ template <int M_, int TPU_> struct SmallCtxT {
     double *L;       // [2][m][msz]: L_j at the current / next squaring level
     int lcur;        // which half of L holds the current level
     const double *Gs;  // [m][msz] the unit's drive generators, staged in shared memory
-    static constexpr int M = M_, TPU = TPU_;
     __device__ __forceinline__ int m() const { return M_ > 0 ? M_ : m_; }
     __device__ __forceinline__ int tpu() const { return TPU_ > 0 ? TPU_ : tpu_; }
 };
@@ -456,8 +457,7 @@ __device__ __forceinline__ void unit_reduce_add8(double (&a)[8], int nn, int tpu
 
 // Second order at the polynomial level for direction j, all product nodes at once and nothing
 // stored:  Hrow[i] += sum_nodes sum_e (Xdot_j^T Nbar)[e] * Ydot_i[e].
-template <int D, bool DIRPAR, class Ctx> __device__ __noinline__ void sm_p6_pass(Ctx &x, int j, const qcb_op *ctab, double *red_unit, double *Hrow) {
-    const int rw = DIRPAR ? SmDims<D>::NT : x.tpu();      // threads that share this direction's sums
+template <int D, class Ctx> __device__ __noinline__ void sm_p6_pass(Ctx &x, int j, const qcb_op *ctab, double *red_unit, double *Hrow) {
     const int d = D > 0 ? D : x.d, ld = D > 0 ? SmDims<D>::ld : x.ld, msz = ld * d, m = x.m();
     constexpr int pr0 = QCB_P6_PARTNER[0], pr1 = QCB_P6_PARTNER[1], pr2 = QCB_P6_PARTNER[2], pr3 = QCB_P6_PARTNER[3];
     auto partner_base = [&](int reg) {
@@ -516,13 +516,12 @@ template <int D, bool DIRPAR, class Ctx> __device__ __noinline__ void sm_p6_pass
                     }
             }
         }
-        unit_reduce_add8(a, nn, rw, x.e0, red_unit, Hrow + i0);
+        unit_reduce_add8(a, nn, x.tpu(), x.e0, red_unit, Hrow + i0);
     }
 }
 
 // One squaring level for direction j:  Hrow[i] += sum_e (L_j^T W[l+1])[e] * L_i[e]
-template <int D, bool DIRPAR, class Ctx> __device__ __noinline__ void sm_level_pass(Ctx &x, int j, int level, const qcb_op *ctab, double *red_unit, double *Hrow) {
-    const int rw = DIRPAR ? SmDims<D>::NT : x.tpu();
+template <int D, class Ctx> __device__ __noinline__ void sm_level_pass(Ctx &x, int j, int level, const qcb_op *ctab, double *red_unit, double *Hrow) {
     const int d = D > 0 ? D : x.d, ld = D > 0 ? SmDims<D>::ld : x.ld, msz = ld * d, m = x.m();
     const double *Lbase = x.L + (long long)x.lcur * m * msz;
     x.j = j; x.level = level;
@@ -555,7 +554,7 @@ template <int D, bool DIRPAR, class Ctx> __device__ __noinline__ void sm_level_p
                     if (t < nn) a[t] = fma(u, Lbase[(long long)(i0 + t) * msz + off], a[t]);
             }
         }
-        unit_reduce_add8(a, nn, rw, x.e0, red_unit, Hrow + i0);
+        unit_reduce_add8(a, nn, x.tpu(), x.e0, red_unit, Hrow + i0);
     }
 }
 
@@ -580,26 +579,6 @@ static inline size_t small_smem_doubles(int d, int c, int m, int smax, int upc =
 // (spills: 0.60 / 0.57 ms against 0.51 ms on cfg4).
 // The compile-time instances run at most 256 threads per CTA (register tiles: a unit needs few threads,
 // and the tiles want more than 128 registers).
-// Direction-parallel form of the tiled instances: when a unit has exactly M times the threads one matrix
-// needs (TPU = NT * M), sub-group j of the unit's threads runs drive direction j of every per-direction op
-// at once -- the M independent product chains of the tangents and of the second-order passes side by side
-// instead of one after the other.  Every sub-group executes the same instruction sequence, so the
-// full-mask shuffles of the reductions stay converged.
-template <int D, class Ctx> struct SmDirPar {
-    static constexpr bool on = SmDims<D>::RB > 1 && Ctx::M > 0 && Ctx::TPU == SmDims<D>::NT * Ctx::M && Ctx::M > 1;
-};
-template <int D, const qcb_op *TAB, int I, class Ctx>
-__device__ __forceinline__ void sm_run_dirs(Ctx &x, const qcb_op *ctab, int m) {
-    if constexpr (SmDirPar<D, Ctx>::on) {
-        Ctx y = x;
-        y.e0 = x.e0 % SmDims<D>::NT;
-        y.j = x.e0 / SmDims<D>::NT;
-        sm_run_one<D, TAB, I, false>(y, ctab);
-    } else {
-        for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, TAB, I, false>(x, ctab); }
-    }
-}
-
 // C, M, TPU > 0: state columns, drives and threads per unit fixed at compile time (the BASELINE shapes
 // d/c/m = 4/2/2, 6/3/2, 18/9/4, 18/1/4): ncu on the generic d = 4 instance showed 60 % of the executed
 // instructions to be integer arithmetic and branches of run-time loop bounds, 8 % DFMA.
@@ -706,29 +685,30 @@ small_unit_kernel(const __grid_constant__ SmallParams p) {
     //      tangents of ALL drive directions advance in the same barrier steps ----
     x.level = 0;
     sm_run_one<D, QCB_P1, 0, false>(x, c_P1);                                           // A2
-    if (tang) sm_run_dirs<D, QCB_P5, 0>(x, c_P5, m);                                    // dA2_j
+    if (tang) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P5, 0, false>(x, c_P5); }   // dA2_j
     unit_barrier(tpu);
     sm_run_one<D, QCB_P1, 1, false>(x, c_P1);                                           // A3
     sm_run_one<D, QCB_P1, 2, false>(x, c_P1);                                           // A4
-    if (tang) {
-        sm_run_dirs<D, QCB_P5, 1>(x, c_P5, m);                                          // dA3_j
-        sm_run_dirs<D, QCB_P5, 2>(x, c_P5, m);                                          // dA4_j
+    if (tang) for (int j = 0; j < m; ++j) {
+        x.j = j;
+        sm_run_one<D, QCB_P5, 1, false>(x, c_P5);                                       // dA3_j
+        sm_run_one<D, QCB_P5, 2, false>(x, c_P5);                                       // dA4_j
     }
     unit_barrier(tpu);
     sm_run_one<D, QCB_P1, 3, false>(x, c_P1);                                           // Z2
-    if (tang) sm_run_dirs<D, QCB_P5, 3>(x, c_P5, m);                                    // dZ2_j
+    if (tang) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P5, 3, false>(x, c_P5); }   // dZ2_j
     unit_barrier(tpu);
     sm_run_one<D, QCB_P1, 4, false>(x, c_P1);                                           // Z1
-    if (tang) sm_run_dirs<D, QCB_P5, 4>(x, c_P5, m);                                    // dZ1_j
+    if (tang) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P5, 4, false>(x, c_P5); }   // dZ1_j
     unit_barrier(tpu);
     sm_run_one<D, QCB_P1, 5, false>(x, c_P1);                                           // E[0]
-    if (tang) sm_run_dirs<D, QCB_P5, 5>(x, c_P5, m);                                    // L_j
+    if (tang) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P5, 5, false>(x, c_P5); }   // L_j
     unit_barrier(tpu);
     // ---- squarings (Jacobian-only calls advance L_j in the same steps) ----
     for (int l = 0; l < s; ++l) {
         x.level = l;
         sm_run_one<D, QCB_P2, 0, false>(x, c_P2);
-        if (tang && !want_hess) sm_run_dirs<D, QCB_P7L, 0>(x, c_P7L, m);
+        if (tang && !want_hess) for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P7L, 0, false>(x, c_P7L); }
         unit_barrier(tpu);
         if (tang && !want_hess) x.lcur ^= 1;
     }
@@ -760,27 +740,12 @@ small_unit_kernel(const __grid_constant__ SmallParams p) {
         sm_run_one<D, QCB_P4, 3>(x, c_P4);                                              // AB3
         sm_run_one<D, QCB_P4, 4>(x, c_P4);                                              // AB2
         // second order at the polynomial level: fused product + contraction, nothing stored
-        if constexpr (SmDirPar<D, decltype(x)>::on) {
-            auto y = x;
-            y.e0 = x.e0 % SmDims<D>::NT;
-            const int j = x.e0 / SmDims<D>::NT;
-            sm_p6_pass<D, true>(y, j, c_P6, red, Hacc + j * m);
-        } else {
-            for (int j = 0; j < m; ++j) sm_p6_pass<D, false>(x, j, c_P6, red, Hacc + j * m);
-        }
+        for (int j = 0; j < m; ++j) sm_p6_pass<D>(x, j, c_P6, red, Hacc + j * m);
         // squaring levels: contraction against W[l+1], then all L_j advance in one step
         for (int l = 0; l < s; ++l) {
-            if constexpr (SmDirPar<D, decltype(x)>::on) {
-                auto y = x;
-                y.e0 = x.e0 % SmDims<D>::NT;
-                y.lcur = x.lcur;
-                const int j = x.e0 / SmDims<D>::NT;
-                sm_level_pass<D, true>(y, j, l, c_P7U, red, Hacc + j * m);
-            } else {
-                for (int j = 0; j < m; ++j) sm_level_pass<D, false>(x, j, l, c_P7U, red, Hacc + j * m);
-            }
+            for (int j = 0; j < m; ++j) sm_level_pass<D>(x, j, l, c_P7U, red, Hacc + j * m);
             x.level = l;
-            sm_run_dirs<D, QCB_P7L, 0>(x, c_P7L, m);
+            for (int j = 0; j < m; ++j) { x.j = j; sm_run_one<D, QCB_P7L, 0, false>(x, c_P7L); }
             unit_barrier(tpu);
             x.lcur ^= 1;
         }
