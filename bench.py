@@ -397,7 +397,7 @@ def main():
         del d_jac, d_hess               # the drivers own their result buffers
         torch.cuda.empty_cache()
         # (a smaller slab on the Ipopt rank, to make room for its assembly work, was measured slower at 2, 4 and
-        # 8 GPUs: the other ranks' compute + delivery chain is the critical path, not the root -- DESIGN.md 9)
+        # 8 GPUs: the other ranks' compute + delivery chain is the critical path, not the root -- DESIGN.md 10)
         ad = qdist.ArenaDelivery(ev, L, local)
 
         def arena_step():
