@@ -152,7 +152,10 @@ class ArenaDelivery:
     rank evaluates its own slab straight into the COO vectors and, after the barrier, assembles the
     other slabs from the delivered arenas.  S == 1 layouts on the large-d path."""
 
-    def __init__(self, evaluator, layout, device_index: int, root: int = 0, group=None):
+    def __init__(self, evaluator, layout, device_index: int, root: int = 0, group=None, buffers=None):
+        """buffers: factory `(sizes, device_index, root, group) -> object with .base, .fetch(i), .close()`
+        for the five root-side buffers (default: device memory on the root, mapped with CUDA IPC; the CPU
+        tests of the protocol inject shared host memory)."""
         import torch.distributed as dist
         if layout.S != 1:
             raise ValueError("arena delivery needs S == 1")
@@ -164,8 +167,8 @@ class ArenaDelivery:
         self.bounds = [slab_bounds(L.K, r, self.world) for r in range(self.world)]
         # [0] delta, [1] Jacobian values, [2] Hessian values (the results, on the root);
         # [3] / [4] arenas of every unit the root does not evaluate itself
-        self.buf = _RootBuffers((L.K * L.x_dim, L.K * L.jac_nnz_unit, L.K * L.hess_nnz_unit, L.K * self.JA, L.K * self.HA),
-                                device_index, root, group)
+        self.buf = (buffers or _RootBuffers)((L.K * L.x_dim, L.K * L.jac_nnz_unit, L.K * L.hess_nnz_unit, L.K * self.JA, L.K * self.HA),
+                                             device_index, root, group)
         self.k0, self.k1 = evaluator.k_begin, evaluator.k_end
         self.trace = None       # set to {} to collect host timestamps of the pipelined step's stages
 
@@ -175,7 +178,8 @@ class ArenaDelivery:
         self.dist.broadcast(Z, src=self.root, group=self.group)
         if mu is not None:
             self.dist.broadcast(mu, src=self.root, group=self.group)
-        torch.cuda.current_stream(Z.device).synchronize()     # the library runs on its own stream
+        if Z.is_cuda:
+            torch.cuda.current_stream(Z.device).synchronize()     # the library runs on its own stream
 
     def evaluate(self, dZ, dmu, pipelined: bool = True):
         """One evaluation with every value vector complete in the root's buffers on return.

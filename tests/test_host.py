@@ -126,3 +126,177 @@ def test_slab_coordinator_two_ranks_gloo(name, N, S, built_libs):
         p.join(120)
         assert p.exitcode == 0
     assert ret["err"] == 0.0        # slabs are evaluated independently: bit-identical to one pass
+
+
+# ---- the pipelined compact delivery (ArenaDelivery) as a protocol, on CPU: gloo, two ranks ----------------
+class _ShmBuffers:
+    """Stand-in for the root GPU's buffers: one shared-memory block, `base` = addresses inside it."""
+
+    def __init__(self, sizes, device_index, root, group):
+        import torch.distributed as dist
+        from multiprocessing import shared_memory
+        self.rank, self.root, self.sizes = dist.get_rank(group), root, list(sizes)
+        name = [f"qcb200_test_{os.getpid()}" if self.rank == root else None]
+        total = 8 * (sum(self.sizes) + 16)
+        if self.rank == root:
+            self.shm = shared_memory.SharedMemory(create=True, size=total, name=name[0])
+        dist.broadcast_object_list(name, src=root, group=group)
+        if self.rank != root:
+            self.shm = shared_memory.SharedMemory(name=name[0])
+            try:
+                from multiprocessing import resource_tracker
+                resource_tracker.unregister(self.shm._name, "shared_memory")
+            except Exception:
+                pass
+        self.arr = np.ndarray((total // 8,), dtype=np.float64, buffer=self.shm.buf)
+        if self.rank == root:
+            self.arr[:] = np.nan
+        dist.barrier(group=group)
+        a0 = self.arr.ctypes.data
+        self.base = [a0 + 8 * int(sum(self.sizes[:i])) for i in range(len(self.sizes))]
+
+    def view(self, addr, n):
+        off = (addr - self.arr.ctypes.data) // 8
+        return self.arr[off:off + n]
+
+    def fetch(self, i):
+        return self.view(self.base[i], self.sizes[i]).copy()
+
+    def close(self):
+        del self.arr
+        self.shm.close()
+        if self.rank == self.root:
+            self.shm.unlink()
+
+
+class _StubEvaluator:
+    """Speaks api.Evaluator's delivery interface with the C port behind it (test infrastructure): arenas and
+    COO vectors are written at raw addresses, the call order is logged."""
+
+    def __init__(self, w, k0, k1, bufs_getter):
+        self.w, self.L, self.OL = w, w.layout, oracle_layout(w.layout)
+        self.k_begin, self.k_end = k0, k1
+        self.parts, self.log, self.bufs = 3, [], bufs_getter
+        self.ji, self.js, self.hi = P.arena_codes(self.OL, 0)
+        self.JA = int(P.lib().qc_port_jac_arena(self.L.d, self.L.c, self.L.m))
+        self.HA = int(P.lib().qc_port_hess_arena(self.L.d, self.L.c, self.L.m))
+        self.e_part = self.L.d * self.L.d
+
+    def arena_doubles(self):
+        return self.JA, self.HA
+
+    def _arenas(self, Z, mu):
+        return P.evaluate_arenas(self.OL, self.w.G_drift, self.w.G_drives, Z.numpy(), None if mu is None else mu.numpy(),
+                                 k_range=(self.k_begin, self.k_end))
+
+    def _put(self, addr, values):
+        self.bufs().view(addr, len(values))[:] = values
+
+    def eval_all_device(self, Z, mu, pd, pj, ph):
+        d, ja, ha = self._arenas(Z, mu)
+        self._put(pd, d)
+        if pj is not None:
+            self._put(pj, (ja[:, self.ji] * self.js).reshape(-1))
+        if ph is not None and ha is not None:
+            self._put(ph, ha[:, self.hi].reshape(-1))
+
+    def eval_all_device_x(self, Z, mu, new_x, pd, pj, ph):
+        self.log.append(("all", bool(new_x), pj is not None, ph is not None))
+        self.eval_all_device(Z, mu, pd, pj, ph)
+
+    def eval_arenas_device(self, Z, mu, pd, aj, ah):
+        d, ja, ha = self._arenas(Z, mu)
+        self._put(pd, d)
+        nk = self.k_end - self.k_begin
+        if aj is not None:
+            dst = self.bufs().view(aj, nk * self.JA).reshape(nk, self.JA)
+            if self.parts & 1:
+                dst[:, :self.e_part] = ja[:, :self.e_part]
+            if self.parts & 2:
+                dst[:, self.e_part:] = ja[:, self.e_part:]
+        if ah is not None and ha is not None:
+            self._put(ah, ha.reshape(-1))
+
+    def eval_arenas_device_x(self, Z, mu, new_x, pd, aj, ah):
+        self.log.append(("arenas", bool(new_x), self.parts, aj is not None, ah is not None))
+        self.eval_arenas_device(Z, mu, pd, aj, ah)
+
+    def assemble_device(self, aj, ah, n, nk_src, pj, ph, parts=3):
+        self.log.append(("assemble", aj is not None, ah is not None, parts))
+        if aj is not None:
+            ja = self.bufs().view(aj, n * self.JA).reshape(n, self.JA)
+            out = self.bufs().view(pj, n * self.L.jac_nnz_unit).reshape(n, -1)
+            head = self.ji < self.e_part
+            sel = head if parts == 1 else (~head if parts == 2 else np.ones_like(head))
+            out[:, sel] = (ja[:, self.ji] * self.js)[:, sel]
+        if ah is not None:
+            ha = self.bufs().view(ah, n * self.HA).reshape(n, self.HA)
+            self.bufs().view(ph, n * self.L.hess_nnz_unit).reshape(n, -1)[:] = ha[:, self.hi]
+
+    def set_async(self, on):
+        self.log.append(("async", bool(on)))
+
+    def set_arena_parts(self, parts):
+        self.parts = parts
+
+    def wait(self, what=0):
+        self.log.append(("wait", what))
+
+
+def _arena_worker(rank, world, port, ret):
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    w = workloads.make("cfg2", N=12, jac_mode=qcb200.JAC_BLOCK_DIAG)
+    L = w.layout
+    k0, k1 = distributed.slab_bounds(L.K, rank, world)
+    holder = {}
+    ev = _StubEvaluator(w, k0, k1, lambda: holder["ad"].buf)
+    ad = holder["ad"] = distributed.ArenaDelivery(ev, L, 0, buffers=_ShmBuffers)
+    Z = torch.from_numpy(w.Z.copy()) if rank == 0 else torch.zeros(len(w.Z), dtype=torch.float64)
+    mu = torch.from_numpy(w.mu.copy()) if rank == 0 else torch.zeros(len(w.mu), dtype=torch.float64)
+    ad.broadcast(Z, mu)
+    errs = []
+    for pipelined in (True, False):
+        ev.log.clear()
+        ad.evaluate(Z, mu, pipelined=pipelined)
+        dist.barrier()
+        if rank == 0:
+            ref = P.evaluate(oracle_layout(L), w.G_drift, w.G_drives, w.Z, w.mu)
+            errs.append(max(float(np.abs(a - b).max()) for a, b in zip(ad.fetch(), ref)))
+            ad.buf.arr[:] = np.nan
+        if pipelined:
+            ret[f"log{rank}"] = list(ev.log)
+        dist.barrier()
+    if rank == 0:
+        ret["errs"] = errs
+    ad.close()
+    dist.destroy_process_group()
+
+
+def test_arena_delivery_protocol_two_ranks_gloo(built_libs):
+    """Host logic of the pipelined compact delivery on CPU: the phases are queued in order, the root
+    assembles foreign slabs part by part after the matching barriers, and the vectors that end up in the
+    root's buffers equal a single-pass evaluation bit for bit (C port behind a stub evaluator)."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    port = _free_port()
+    procs = [ctx.Process(target=_arena_worker, args=(r, 2, port, ret)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(180)
+        assert p.exitcode == 0
+    assert ret["errs"] == [0.0, 0.0]
+    root, other = ret["log0"], ret["log1"]
+    # other rank: async on, propagators (E part) with new_x = 1, then the rest of the Jacobian arena and the
+    # Hessian side with new_x = 0, waits in delivery order, async off
+    assert other[0] == ("async", True) and other[-1] == ("async", False)
+    calls = [c for c in other if c[0] == "arenas"]
+    assert calls == [("arenas", True, 1, True, False), ("arenas", False, 2, True, False), ("arenas", False, 3, False, True)]
+    assert [c[1] for c in other if c[0] == "wait"] == [1, 2, 0, 0]
+    # root: own slab straight into COO (Jacobian side first), then assembly of the foreign slab in three parts
+    assert [c for c in root if c[0] == "all"] == [("all", True, True, False), ("all", False, False, True)]
+    assert [c for c in root if c[0] == "assemble"] == [("assemble", True, False, 1), ("assemble", True, False, 2), ("assemble", False, True, 3)]
