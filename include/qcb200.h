@@ -218,8 +218,9 @@ void qcb_host_free(void *ptr);
 
 /* Host-side output formatting (no counterpart in the reference).  On the large-d path the COO
  * vectors are written into the caller's buffers by a pool of host threads from the compact arenas
- * the GPU sends.  qcb_host_threads: size of that pool -- QCB_HOST_THREADS, else OMP_NUM_THREADS,
- * else (cores this process may run on) / LOCAL_WORLD_SIZE; threads are pinned one per core
+ * the GPU sends.  qcb_host_threads: size of that pool -- QCB_HOST_THREADS, else OMP_NUM_THREADS
+ * (ignored when it is 1 and LOCAL_WORLD_SIZE is set: torch.distributed.run's default), else (cores this
+ * process may run on) / LOCAL_WORLD_SIZE; threads are pinned one per core
  * (QCB_HOST_PIN=0: not pinned).  qcb_host_stream_fill: writes `bytes` of dst with the same
  * streaming stores on the same pool and reports the wall time -- the measured host-write roofline
  * that bench.py prints beside the end-to-end number. */

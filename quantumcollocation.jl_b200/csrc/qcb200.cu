@@ -325,7 +325,7 @@ __attribute__((target("avx512f"))) void fill_run_avx512(double *dst, double v, s
 
 // Persistent worker threads for the host-side expansion (created once per process, shared by all
 // handles): run(fn) executes fn() on every worker and on the caller, returns when all are done.
-// Size: QCB_HOST_THREADS, else OMP_NUM_THREADS, else the cores this process may run on divided by
+// Size: QCB_HOST_THREADS, else OMP_NUM_THREADS (unless it is the launcher's default of 1), else the cores this process may run on divided by
 // LOCAL_WORLD_SIZE (one process per GPU on one host: N ranks must not each start a thread per core).
 // Workers are pinned one per core, rank r taking the r-th block of the allowed cores, so that the
 // ranks' streaming stores do not migrate between cores (QCB_HOST_PIN=0 disables pinning).
@@ -356,8 +356,11 @@ private:
             for (int c = 0; c < CPU_SETSIZE; ++c) if (CPU_ISSET(c, &set)) cores.push_back(c);
         if (cores.empty()) for (unsigned c = 0; c < std::max(1u, std::thread::hardware_concurrency()); ++c) cores.push_back((int)c);
         const int world = std::max(1, env_int("LOCAL_WORLD_SIZE")), rank = std::max(0, env_int("LOCAL_RANK")) % world;
+        // OMP_NUM_THREADS = 1 next to LOCAL_WORLD_SIZE is what torch.distributed.run exports by default for
+        // every rank, not a request for a serial expansion (measured: 4.4 k instead of 11 k knot-evals/s on
+        // two ranks): only an explicit QCB_HOST_THREADS, or an OMP_NUM_THREADS > 1, overrides the share of cores.
         int n = env_int("QCB_HOST_THREADS");
-        if (n <= 0) n = env_int("OMP_NUM_THREADS");
+        if (n <= 0) { n = env_int("OMP_NUM_THREADS"); if (n == 1 && getenv("LOCAL_WORLD_SIZE")) n = 0; }
         if (n <= 0) n = std::max(1, (int)cores.size() / world);
         n = std::max(1, std::min(n, (int)cores.size()));
         const char *pin_env = getenv("QCB_HOST_PIN");
