@@ -117,6 +117,15 @@ struct qcb_handle_s {
     // compact host transfer: arenas (not expanded COO vectors) cross PCIe, the host cores expand
     std::vector<uint32_t> h_jcode, h_hcode;           // host copies of the code tables [S][nnz]
     std::vector<std::vector<Seg>> jsegs, hsegs;       // per system
+    // Direct panels (host-buffer calls, S = 1): long plain-copy runs of the COO vectors whose source is used
+    // nowhere else (the u / dt blocks of the Jacobian, the (x,u) / (x,dt) blocks of the Hessian) are DMA'd from
+    // the arenas straight to their place in the caller's pinned buffer -- they neither pass through the staging
+    // buffers nor occupy the cores; the staging copy shrinks to the arena ranges the rest still needs.
+    struct Direct { int64_t dst; uint32_t src, len; };
+    std::vector<Direct> jdirect, hdirect;
+    std::vector<std::vector<Seg>> jsegs_x, hsegs_x;   // expansion lists without the direct runs
+    std::vector<std::pair<uint32_t, uint32_t>> jstage, hstage;   // arena ranges [lo, hi) still staged
+    bool direct_built = false;
     Piece *d_jpieces = nullptr, *d_hpieces = nullptr; // run-based device assembly: [S][n*pieces]
     int n_jpieces = 0, n_hpieces = 0;
     double *sc_ja2 = nullptr, *sc_ha2 = nullptr;      // second arena set (double buffering)
@@ -752,6 +761,54 @@ void ensure_compact(qcb_handle_s *h) {
     }
 }
 
+// Split a unit's run-length table into direct runs and the rest (see qcb_handle_s::Direct).
+void split_direct(const std::vector<Seg> &segs, int64_t arena_len, std::vector<qcb_handle_s::Direct> &direct,
+                  std::vector<Seg> &rest, std::vector<std::pair<uint32_t, uint32_t>> &stage) {
+    constexpr uint32_t MIN_DIRECT = 4096;       // 32 KB per unit and run: worth a DMA descriptor row
+    std::vector<uint8_t> uses((size_t)arena_len, 0);
+    for (const Seg &q : segs) {
+        const uint32_t n = (q.kind & 2u) ? 1u : q.len;
+        for (uint32_t i = 0; i < n; ++i) { uint8_t &c = uses[q.src + i]; if (c < 255) ++c; }
+    }
+    direct.clear(); rest.clear(); stage.clear();
+    std::vector<uint8_t> needed((size_t)arena_len, 0);
+    for (const Seg &q : segs) {
+        bool ok = q.kind == 0 && q.len >= MIN_DIRECT;
+        for (uint32_t i = 0; ok && i < q.len; ++i) ok = uses[q.src + i] == 1;
+        if (ok) direct.push_back({q.dst, q.src, q.len});
+        else {
+            rest.push_back(q);
+            const uint32_t n = (q.kind & 2u) ? 1u : q.len;
+            for (uint32_t i = 0; i < n; ++i) needed[q.src + i] = 1;
+        }
+    }
+    for (int64_t e = 0; e < arena_len;) {
+        if (!needed[e]) { ++e; continue; }
+        int64_t b = e;
+        while (e < arena_len && needed[e]) ++e;
+        stage.push_back({(uint32_t)b, (uint32_t)e});
+    }
+}
+
+void ensure_direct(qcb_handle_s *h) {
+    if (h->direct_built) return;
+    h->direct_built = true;
+    h->jdirect.clear(); h->hdirect.clear();
+    if (h->S != 1 || getenv("QCB_E2E_NO_DIRECT_PANELS")) return;
+    h->jsegs_x.assign(1, {}); h->hsegs_x.assign(1, {});
+    split_direct(h->jsegs[0], h->JA, h->jdirect, h->jsegs_x[0], h->jstage);
+    split_direct(h->hsegs[0], h->HA, h->hdirect, h->hsegs_x[0], h->hstage);
+    // a handful of long runs, or nothing: many short ones would turn into as many DMA calls per chunk
+    if (h->jdirect.size() > 8 || h->jstage.size() > 8) h->jdirect.clear();
+    if (h->hdirect.size() > 8 || h->hstage.size() > 8) h->hdirect.clear();
+}
+
+bool host_pinned(const void *p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
 size_t scratch_bytes_per_unit(const qcb_handle_s *h, int s_cap) {
     const size_t dd = (size_t)h->msz, pan = (size_t)h->dp * h->cp;
     size_t n = (QR_NUM_FIXED + 1 + 2 * (size_t)(s_cap + 1) + (size_t)(QCB_NUM_DSLOTS + s_cap + 1) * h->m) * dd;
@@ -873,7 +930,10 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     const int ncol = h->gcols;                       // columns of a stored matrix (dp, or dp/2 in iso mode)
     UnitGeom q = h->geom();
     const bool compact = host && host->compact && (wj || wh);
-    if (compact) ensure_compact(h);
+    if (compact) { ensure_compact(h); ensure_direct(h); }
+    // direct panels need a pinned destination (the DMA engine writes it); pageable buffers keep the staged route
+    const bool jdir = compact && wj && host->jac && !h->jdirect.empty() && h->direct_fraction == 0.0 && host_pinned(host->jac);
+    const bool hdir = compact && wh && host->hess && !h->hdirect.empty() && h->direct_fraction == 0.0 && host_pinned(host->hess);
     // chunk whose arenas are staged on the host, not yet expanded; its first prev_nd units went
     // the direct route (assembled on the device, full COO rows DMA'd) and need no expansion
     int prev_u0 = -1, prev_nu = 0, prev_nd = 0;
@@ -883,8 +943,8 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         CK(cudaEventSynchronize(h->copied[b]));
         ExpandJob jobs[2];
         int nj = 0;
-        if (wj && host->jac) jobs[nj++] = {&h->jsegs, h->stage_j[b] + (size_t)prev_nd * h->JA, h->JA, host->jac, h->jnnz_unit};
-        if (wh && host->hess) jobs[nj++] = {&h->hsegs, h->stage_h[b] + (size_t)prev_nd * h->HA, h->HA, host->hess, h->hnnz_unit};
+        if (wj && host->jac) jobs[nj++] = {jdir ? &h->jsegs_x : &h->jsegs, h->stage_j[b] + (size_t)prev_nd * h->JA, h->JA, host->jac, h->jnnz_unit};
+        if (wh && host->hess) jobs[nj++] = {hdir ? &h->hsegs_x : &h->hsegs, h->stage_h[b] + (size_t)prev_nd * h->HA, h->HA, host->hess, h->hnnz_unit};
         if (nj > 0 && prev_nu > prev_nd) expand_units(jobs, nj, h->nk, prev_u0 + prev_nd, prev_nu - prev_nd);
         prev_u0 = -1;
     };
@@ -1192,16 +1252,30 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             if (compact) {
                 // compact transfer: the value arenas (every distinct number once) cross PCIe; the
                 // host cores write the COO vectors from them while the GPU works on the next chunk
-                if (wj && host->jac && nu > nd) {
-                    CK(cudaMemcpyAsync(h->stage_j[buf] + (size_t)nd * h->JA, X.ja + (size_t)nd * h->JA,
-                                       (size_t)(nu - nd) * h->JA * 8, cudaMemcpyDeviceToHost, h->copy_stream));
-                    h->xfer[1] += (int64_t)((size_t)(nu - nd) * h->JA * 8);
-                }
-                if (wh && host->hess && nu > nd) {
-                    CK(cudaMemcpyAsync(h->stage_h[buf] + (size_t)nd * h->HA, X.ha + (size_t)nd * h->HA,
-                                       (size_t)(nu - nd) * h->HA * 8, cudaMemcpyDeviceToHost, h->copy_stream));
-                    h->xfer[1] += (int64_t)((size_t)(nu - nd) * h->HA * 8);
-                }
+                // one arena set -> host: in one piece, or (direct panels) the long plain runs straight to their
+                // place in the caller's vector and only the ranges the cores still read to the staging buffer
+                auto to_host = [&](bool direct, const double *arena, int64_t stride, double *stage, double *out, int64_t nnz,
+                                   const std::vector<qcb_handle_s::Direct> &runs, const std::vector<std::pair<uint32_t, uint32_t>> &ranges) {
+                    const size_t rows = (size_t)(nu - nd);
+                    if (!direct) {
+                        CK(cudaMemcpyAsync(stage + (size_t)nd * stride, arena + (size_t)nd * stride, rows * stride * 8,
+                                           cudaMemcpyDeviceToHost, h->copy_stream));
+                        h->xfer[1] += (int64_t)(rows * stride * 8);
+                        return;
+                    }
+                    for (const auto &r : ranges) {
+                        CK(cudaMemcpy2DAsync(stage + (size_t)nd * stride + r.first, (size_t)stride * 8, arena + (size_t)nd * stride + r.first,
+                                             (size_t)stride * 8, (size_t)(r.second - r.first) * 8, rows, cudaMemcpyDeviceToHost, h->copy_stream));
+                        h->xfer[1] += (int64_t)(rows * (r.second - r.first) * 8);
+                    }
+                    for (const auto &d : runs) {
+                        CK(cudaMemcpy2DAsync(out + (size_t)(u0 + nd) * nnz + d.dst, (size_t)nnz * 8, arena + (size_t)nd * stride + d.src,
+                                             (size_t)stride * 8, (size_t)d.len * 8, rows, cudaMemcpyDeviceToHost, h->copy_stream));
+                        h->xfer[1] += (int64_t)(rows * d.len * 8);
+                    }
+                };
+                if (wj && host->jac && nu > nd) to_host(jdir, X.ja, h->JA, h->stage_j[buf], host->jac, h->jnnz_unit, h->jdirect, h->jstage);
+                if (wh && host->hess && nu > nd) to_host(hdir, X.ha, h->HA, h->stage_h[buf], host->hess, h->hnnz_unit, h->hdirect, h->hstage);
                 CK(cudaEventRecord(h->copied[buf], h->copy_stream));
                 if (nd > 0) {
                     if (wj && host->jac) {
@@ -1844,7 +1918,7 @@ qcb_status qcb_set_structure(qcb_handle h, int64_t row_base, const int64_t *jr, 
             h->jnnz_unit = per;
             h->custom_j = true;
             h->h_jcode = codes;
-            h->jsegs.clear();
+            h->jsegs.clear(); h->direct_built = false;
             if (h->d_jpieces) { CK(cudaFree(h->d_jpieces)); h->d_jpieces = nullptr; }
             if (h->d_jac) { CK(cudaFree(h->d_jac)); h->d_jac = nullptr; }
         }
@@ -1896,7 +1970,7 @@ qcb_status qcb_set_structure(qcb_handle h, int64_t row_base, const int64_t *jr, 
             h->hnnz_unit = per;
             h->custom_h = true;
             h->h_hcode = codes;
-            h->hsegs.clear();
+            h->hsegs.clear(); h->direct_built = false;
             if (h->d_hpieces) { CK(cudaFree(h->d_hpieces)); h->d_hpieces = nullptr; }
             if (h->d_hess) { CK(cudaFree(h->d_hess)); h->d_hess = nullptr; }
         }

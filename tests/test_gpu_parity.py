@@ -695,3 +695,32 @@ def test_new_x_reuse_is_bit_identical_and_a_new_point_recomputes(storage, built_
     r = es.eval_all(ws.Z, ws.mu)
     assert np.array_equal(sj.cpu().numpy(), r[1]) and np.array_equal(sh.cpu().numpy(), r[2])
     ev.close(); fresh.close(); es.close()
+
+
+def test_host_route_with_pinned_buffers_takes_direct_panels_and_matches(built_libs, monkeypatch):
+    """Host-buffer calls on the large-d path: with pinned result buffers the long plain runs of the COO vectors
+    (u / dt blocks) are DMA'd straight into place, with pageable ones everything goes through the staging
+    buffers and the host cores; both give the same bytes, and the direct form moves fewer of them twice."""
+    import torch
+    w = workloads.make("cfg5", N=12)
+    L = w.layout
+    ev = Evaluator(L, w.G_drift, w.G_drives)
+    d0, j0, h0 = ev.eval_all(w.Z, w.mu)                              # numpy: pageable
+    staged_bytes = ev.transfer_bytes()[1]
+    pin = lambda n: torch.full((n,), float("nan"), dtype=torch.float64).pin_memory()
+    pd_, pj, ph = pin(ev.defect_dim), pin(ev.jacobian_nnz), pin(ev.hessian_nnz)
+    hZ, hmu = torch.from_numpy(w.Z).pin_memory(), torch.from_numpy(w.mu).pin_memory()
+    ev.eval_all_raw(hZ.data_ptr(), hmu.data_ptr(), pd_.data_ptr(), pj.data_ptr(), ph.data_ptr())
+    assert np.array_equal(pd_.numpy(), d0) and np.array_equal(pj.numpy(), j0) and np.array_equal(ph.numpy(), h0)
+    assert ev.transfer_bytes()[1] == staged_bytes                    # same bytes over PCIe, different destinations
+    # Jacobian only / Hessian only, and the switch that disables the direct form
+    pj.fill_(float("nan")); ph.fill_(float("nan"))
+    ev.eval_all_raw(hZ.data_ptr(), None, None, pj.data_ptr(), None)
+    ev.eval_all_raw(hZ.data_ptr(), hmu.data_ptr(), None, None, ph.data_ptr())
+    assert np.array_equal(pj.numpy(), j0) and np.array_equal(ph.numpy(), h0)
+    monkeypatch.setenv("QCB_E2E_NO_DIRECT_PANELS", "1")
+    ev2 = Evaluator(L, w.G_drift, w.G_drives)
+    pj.fill_(float("nan"))
+    ev2.eval_all_raw(hZ.data_ptr(), hmu.data_ptr(), pd_.data_ptr(), pj.data_ptr(), ph.data_ptr())
+    assert np.array_equal(pj.numpy(), j0)
+    ev.close(); ev2.close()
