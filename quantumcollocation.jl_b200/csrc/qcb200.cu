@@ -343,17 +343,25 @@ class HostPool {
 public:
     static HostPool &get() { static HostPool p; return p; }
     int size() const { return (int)workers_.size() + 1; }
-    void run(const std::function<void()> &fn) {
-        std::lock_guard<std::mutex> serial(run_m_);
+    void run(const std::function<void()> &fn) { start(fn); finish(); }
+    // start(): the workers begin fn() and the caller goes on (fn must stay alive until finish());
+    // finish(): the caller joins the work, then waits for the workers.  One job at a time per process.
+    void start(const std::function<void()> &fn) {
+        run_m_.lock();
         {
             std::lock_guard<std::mutex> lk(m_);
             fn_ = &fn; pending_ = (int)workers_.size(); ++epoch_;
         }
         cv_.notify_all();
-        fn();
-        std::unique_lock<std::mutex> lk(m_);
-        done_.wait(lk, [&] { return pending_ == 0; });
-        fn_ = nullptr;
+    }
+    void finish() {
+        (*fn_)();
+        {
+            std::unique_lock<std::mutex> lk(m_);
+            done_.wait(lk, [&] { return pending_ == 0; });
+            fn_ = nullptr;
+        }
+        run_m_.unlock();
     }
 private:
     static int env_int(const char *name) { const char *e = getenv(name); return e ? atoi(e) : 0; }
@@ -424,32 +432,57 @@ struct ExpandJob {
 };
 
 // Expand units [u0, u0 + nu) of every job: out[(u0 + u) * nnz + seg.dst ...] = +-arena[seg.src ...].
-void expand_units(const ExpandJob *jobs, int njobs, int nk, int u0, int nu) {
-    static const bool has512 = __builtin_cpu_supports("avx512f");
+// A task can run in the background: start() hands it to the pool's workers and returns, so that the calling
+// thread queues the next chunk's kernels meanwhile; finish() lets the caller help and waits for the rest.
+struct ExpandTask {
+    ExpandJob jobs[2];
+    int njobs = 0, nk = 1, u0 = 0, nu = 0;
     std::atomic<int> next{0};
-    const int total = nu * njobs;
-    std::function<void()> work = [&]() {
-        for (;;) {
-            const int w = next.fetch_add(1);
-            if (w >= total) break;
-            const ExpandJob &jb = jobs[w / nu];
-            const int u = w % nu;
-            const std::vector<Seg> &sg = (*jb.segs)[(size_t)((u0 + u) / nk)];
-            const double *ar = jb.stage + (size_t)u * jb.arena_stride;
-            double *o = jb.out + (size_t)(u0 + u) * jb.nnz;
-            for (const Seg &q : sg) {
-                const bool neg = q.kind & 1u;
-                if (q.kind & 2u) {
-                    const double v = neg ? -ar[q.src] : ar[q.src];
-                    if (has512) fill_run_avx512(o + q.dst, v, q.len);
-                    else for (uint32_t i = 0; i < q.len; ++i) o[q.dst + i] = v;
-                } else if (has512) copy_run_avx512(o + q.dst, ar + q.src, q.len, neg);
-                else copy_run_plain(o + q.dst, ar + q.src, q.len, neg);
+    std::function<void()> work;
+    bool running = false;
+    ExpandTask() {
+        work = [this]() {
+            static const bool has512 = __builtin_cpu_supports("avx512f");
+            const int total = nu * njobs;
+            for (;;) {
+                const int w = next.fetch_add(1);
+                if (w >= total) break;
+                const ExpandJob &jb = jobs[w / nu];
+                const int u = w % nu;
+                const std::vector<Seg> &sg = (*jb.segs)[(size_t)((u0 + u) / nk)];
+                const double *ar = jb.stage + (size_t)u * jb.arena_stride;
+                double *o = jb.out + (size_t)(u0 + u) * jb.nnz;
+                for (const Seg &q : sg) {
+                    const bool neg = q.kind & 1u;
+                    if (q.kind & 2u) {
+                        const double v = neg ? -ar[q.src] : ar[q.src];
+                        if (has512) fill_run_avx512(o + q.dst, v, q.len);
+                        else for (uint32_t i = 0; i < q.len; ++i) o[q.dst + i] = v;
+                    } else if (has512) copy_run_avx512(o + q.dst, ar + q.src, q.len, neg);
+                    else copy_run_plain(o + q.dst, ar + q.src, q.len, neg);
+                }
             }
-        }
-        if (has512) _mm_sfence();
-    };
-    HostPool::get().run(work);
+            if (has512) _mm_sfence();
+        };
+    }
+    void start(const ExpandJob *jb, int nj, int nk_, int u0_, int nu_) {
+        for (int i = 0; i < nj; ++i) jobs[i] = jb[i];
+        njobs = nj; nk = nk_; u0 = u0_; nu = nu_;
+        next.store(0);
+        running = true;
+        HostPool::get().start(work);
+    }
+    void finish() {
+        if (!running) return;
+        HostPool::get().finish();
+        running = false;
+    }
+    ~ExpandTask() { finish(); }     // an exception on the way out must not leave the workers with a dead job
+};
+void expand_units(const ExpandJob *jobs, int njobs, int nk, int u0, int nu) {
+    ExpandTask t;
+    t.start(jobs, njobs, nk, u0, nu);
+    t.finish();
 }
 
 void upload_codes(qcb_handle_s *h, uint32_t **dptr, const std::vector<uint32_t> &codes) {
@@ -937,6 +970,9 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     // chunk whose arenas are staged on the host, not yet expanded; its first prev_nd units went
     // the direct route (assembled on the device, full COO rows DMA'd) and need no expansion
     int prev_u0 = -1, prev_nu = 0, prev_nd = 0;
+    // The expansion of a staged chunk runs on the pool's workers in the background while this thread queues
+    // the next chunk's kernels; it is joined (the caller helps) before the staging buffer it reads is reused.
+    ExpandTask task;
     auto expand_prev = [&](size_t idx_prev) {
         if (prev_u0 < 0) return;
         const int b = (int)(idx_prev & 1);
@@ -945,7 +981,7 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         int nj = 0;
         if (wj && host->jac) jobs[nj++] = {jdir ? &h->jsegs_x : &h->jsegs, h->stage_j[b] + (size_t)prev_nd * h->JA, h->JA, host->jac, h->jnnz_unit};
         if (wh && host->hess) jobs[nj++] = {hdir ? &h->hsegs_x : &h->hsegs, h->stage_h[b] + (size_t)prev_nd * h->HA, h->HA, host->hess, h->hnnz_unit};
-        if (nj > 0 && prev_nu > prev_nd) expand_units(jobs, nj, h->nk, prev_u0 + prev_nd, prev_nu - prev_nd);
+        if (nj > 0 && prev_nu > prev_nd) task.start(jobs, nj, h->nk, prev_u0 + prev_nd, prev_nu - prev_nd);
         prev_u0 = -1;
     };
     const int chunk_step = compact ? compact_step(h) : h->chunk_units;
@@ -1274,6 +1310,7 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
                         h->xfer[1] += (int64_t)(rows * d.len * 8);
                     }
                 };
+                task.finish();      // chunk idx - 2 read the staging buffers the copies below overwrite
                 if (wj && host->jac && nu > nd) to_host(jdir, X.ja, h->JA, h->stage_j[buf], host->jac, h->jnnz_unit, h->jdirect, h->jstage);
                 if (wh && host->hess && nu > nd) to_host(hdir, X.ha, h->HA, h->stage_h[buf], host->hess, h->hnnz_unit, h->hdirect, h->hstage);
                 CK(cudaEventRecord(h->copied[buf], h->copy_stream));
@@ -1306,7 +1343,7 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
             }
         }
     }
-    if (compact) expand_prev(chunk_idx - 1);
+    if (compact) { task.finish(); expand_prev(chunk_idx - 1); task.finish(); }
     if (h->arena_out_j || h->arena_out_h) {
         for (int i = 0; i < 3; ++i) if (!h->ship_ev[i]) CK(cudaEventCreateWithFlags(&h->ship_ev[i], cudaEventDisableTiming));
         if (h->arena_out_j && (h->arena_parts & 1)) CK(cudaEventRecord(h->ship_ev[0], h->copy_stream));

