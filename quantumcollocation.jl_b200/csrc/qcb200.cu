@@ -752,15 +752,18 @@ void free_scratch(qcb_handle_s *h) {
 
 // buffers of the compact host transfer (second arena set, pinned staging, run-length tables)
 // Units per chunk of a host-complete call.  Those are bound by the host cores' expansion, not by the
-// GPU: small chunks (six full waves of per-drive CTAs) let the first arenas reach the host early, so
-// the expansion pipeline starts after a few milliseconds instead of a third of the evaluation.
+// GPU: small chunks let the first arenas reach the host early, so the expansion pipeline starts after a
+// millisecond instead of a third of the evaluation, and its last chunk is short.
 int compact_step(const qcb_handle_s *h) {
     if (getenv("QCB_E2E_BIG_CHUNKS")) return h->chunk_units;
     if (const char *e = getenv("QCB_E2E_UNITS")) return (int)std::min<long long>(h->chunk_units, std::max(1L, atol(e)));
     const long long slots = (long long)h->n_sm * (h->iso ? 2 : 1);
     const long long tiles = h->iso ? (h->dp / 128) : ((h->dp % 128 == 0) ? (long long)(h->dp / 128) * (h->dp / 128)
                                                                           : (long long)(h->dp / 64) * (h->dp / 64));
-    const long long small = std::max(1LL, 6 * slots / std::max<long long>(1, (long long)std::max(1, h->m) * std::max(1LL, tiles)));
+    // one and a half waves of per-drive CTAs.  Measured on cfg5 (e2e, knot-evals/s) with the background expansion:
+    // 16 units 6.4 k, 24: 11.9 k (the GPU side turns launch-bound), 32: 16.2 k, 40: 16.2 k, 48: 15.6 k, 80: 14.7 k,
+    // 148 (six waves, the round-1 choice): 14.5 k -- short chunks shorten the pipeline's fill and drain
+    const long long small = std::max(1LL, 3 * slots / std::max<long long>(1, 2LL * std::max(1, h->m) * std::max(1LL, tiles)));
     return (int)std::min<long long>(h->chunk_units, small);
 }
 
