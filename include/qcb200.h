@@ -215,6 +215,13 @@ qcb_status qcb_device_to_host(int32_t device, void *dst_host, const void *src_de
 /* Pinned host memory for callers that want full PCIe bandwidth on the host-buffer calls. */
 qcb_status qcb_host_alloc(void **ptr, size_t bytes);
 void qcb_host_free(void *ptr);
+/* The same for memory the caller already owns (the value arrays Ipopt / MOI allocated, a Julia Vector):
+ * page-locks [ptr, ptr + bytes) so that the host-buffer calls can DMA into it (on the large-d path the long
+ * plain runs of the COO vectors then go straight to their place instead of through staging and the host
+ * cores).  Register once per array, keep it alive and unregister before it is freed.  Already registered
+ * memory is accepted.  No counterpart in the reference. */
+qcb_status qcb_host_register(void *ptr, size_t bytes);
+void qcb_host_unregister(void *ptr);
 
 /* Host-side output formatting (no counterpart in the reference).  On the large-d path the COO
  * vectors are written into the caller's buffers by a pool of host threads from the compact arenas

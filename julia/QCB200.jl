@@ -90,6 +90,11 @@ function adopt_structure!(int::B200BilinearIntegrator, jac_rows::Vector{Int}, ja
     int.hess_nnz = ccall((:qcb_hessian_nnz, LIB), Int64, (Ptr{Cvoid},), int.handle)
 end
 
+# Page-lock the value arrays Ipopt hands to the callbacks (same arrays every iteration): the library then DMAs
+# the u / dt blocks straight into them.  Call once after the problem is built; unpin before the arrays die.
+pin!(a::Vector{Float64}) = (GC.@preserve a ccall((:qcb_host_register, LIB), Cint, (Ptr{Cvoid}, Csize_t), a, sizeof(a)); a)
+unpin!(a::Vector{Float64}) = (GC.@preserve a ccall((:qcb_host_unregister, LIB), Cvoid, (Ptr{Cvoid},), a); a)
+
 # eval_jac_g / eval_h value callbacks: write straight into Ipopt's value buffers
 function jacobian_values!(vals::AbstractVector{Float64}, int::B200BilinearIntegrator, Z::Vector{Float64})
     GC.@preserve vals Z check(int.handle, ccall((:qcb_eval_jacobian, LIB), Cint,

@@ -66,6 +66,8 @@ SYMBOLS = {
     "qcb_device_to_host": (ctypes.c_int, [ctypes.c_int32, c_vp, c_vp, ctypes.c_size_t]),
     "qcb_host_alloc": (ctypes.c_int, [ctypes.POINTER(c_vp), ctypes.c_size_t]),
     "qcb_host_free": (None, [c_vp]),
+    "qcb_host_register": (ctypes.c_int, [c_vp, ctypes.c_size_t]),
+    "qcb_host_unregister": (None, [c_vp]),
     "qcb_host_threads": (ctypes.c_int32, []),
     "qcb_host_stream_fill": (ctypes.c_int, [c_vp, ctypes.c_size_t, c_dp]),
     "qcb_kernel_launches": (ctypes.c_int64, [c_vp]),

@@ -2292,6 +2292,15 @@ qcb_status qcb_host_stream_fill(void *dst, size_t bytes, double *seconds) {
     return QCB_OK;
 }
 
+qcb_status qcb_host_register(void *ptr, size_t bytes) {
+    if (!ptr || !bytes) return QCB_ERR_ARG;
+    cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterDefault);
+    if (e == cudaErrorHostMemoryAlreadyRegistered) { cudaGetLastError(); return QCB_OK; }
+    if (e != cudaSuccess) { cudaGetLastError(); return QCB_ERR_CUDA; }
+    return QCB_OK;
+}
+void qcb_host_unregister(void *ptr) { if (ptr && cudaHostUnregister(ptr) != cudaSuccess) cudaGetLastError(); }
+
 qcb_status qcb_host_alloc(void **ptr, size_t bytes) {
     if (!ptr) return QCB_ERR_ARG;
     cudaError_t e = cudaMallocHost(ptr, bytes);

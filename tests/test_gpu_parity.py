@@ -718,6 +718,13 @@ def test_host_route_with_pinned_buffers_takes_direct_panels_and_matches(built_li
     ev.eval_all_raw(hZ.data_ptr(), None, None, pj.data_ptr(), None)
     ev.eval_all_raw(hZ.data_ptr(), hmu.data_ptr(), None, None, ph.data_ptr())
     assert np.array_equal(pj.numpy(), j0) and np.array_equal(ph.numpy(), h0)
+    # an ordinary numpy array, page-locked through the library, takes the direct form as well
+    jn = np.full(ev.jacobian_nnz, np.nan)
+    lib = _lib.load()
+    assert lib.qcb_host_register(jn.ctypes.data, jn.nbytes) == 0 and lib.qcb_host_register(jn.ctypes.data, jn.nbytes) == 0
+    ev.eval_all_raw(hZ.data_ptr(), None, None, jn.ctypes.data, None)
+    lib.qcb_host_unregister(jn.ctypes.data)
+    assert np.array_equal(jn, j0)
     monkeypatch.setenv("QCB_E2E_NO_DIRECT_PANELS", "1")
     ev2 = Evaluator(L, w.G_drift, w.G_drives)
     pj.fill_(float("nan"))
