@@ -579,6 +579,28 @@ static inline size_t small_smem_doubles(int d, int c, int m, int smax, int upc =
 // (spills: 0.60 / 0.57 ms against 0.51 ms on cfg4).
 // The compile-time instances run at most 256 threads per CTA (register tiles: a unit needs few threads,
 // and the tiles want more than 128 registers).
+// out[e] = +-arena[code[e]] for the entries e0, e0 + tpu, ... of one unit
+__device__ __forceinline__ void coo_store(const uint32_t *__restrict__ code, const double *arena, double *__restrict__ out,
+                                          long long nnz, int e0, int tpu) {
+    constexpr int U = 8;
+    long long e = e0;
+    for (; e + (long long)(U - 1) * tpu < nnz; e += (long long)U * tpu) {
+        uint32_t cc[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) cc[u] = __ldg(code + e + (long long)u * tpu);
+        double v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) v[u] = arena[cc[u] & 0x7fffffffu];
+#pragma unroll
+        for (int u = 0; u < U; ++u) out[e + (long long)u * tpu] = (cc[u] >> 31) ? -v[u] : v[u];
+    }
+    for (; e < nnz; e += tpu) {
+        const uint32_t cc = __ldg(code + e);
+        const double v = arena[cc & 0x7fffffffu];
+        out[e] = (cc >> 31) ? -v : v;
+    }
+}
+
 // C, M, TPU > 0: state columns, drives and threads per unit fixed at compile time (the BASELINE shapes
 // d/c/m = 4/2/2, 6/3/2, 18/9/4, 18/1/4): ncu on the generic d = 4 instance showed 60 % of the executed
 // instructions to be integer arithmetic and branches of run-time loop bounds, 8 % DFMA.
@@ -621,19 +643,37 @@ small_unit_kernel(const __grid_constant__ SmallParams p) {
     double *G = x.fixed + QR_G * msz, *A = x.fixed + QR_A * msz;
     const double dt = zk[p.dt_off];
 
-    // ---- load unit inputs; stage G_j in shared memory; G = G0 + sum u_j G_j ----
-    for (int e = e0; e < dc; e += tpu) {
-        X[e] = zk[p.x_off[sys] + e];
-        Xn[e] = zn[p.x_off[sys] + e];
-        Mu[e] = want_hess ? p.mu[((long long)sys * p.K + k) * dc + e] : 0.0;
+    // ---- load unit inputs; stage G_j in shared memory; G = G0 + sum u_j G_j.  Loads are issued in batches
+    //      ahead of the shared-memory stores that consume them (a unit has few warps to hide them behind) ----
+    {
+        const double *xs = zk + p.x_off[sys], *xn = zn + p.x_off[sys];
+        const double *ms = want_hess ? p.mu + ((long long)sys * p.K + k) * dc : nullptr;
+        constexpr int U = 4;
+        int e = e0;
+        for (; e + (U - 1) * tpu < dc; e += U * tpu) {
+            double a[U], b[U], c2[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) { a[u] = __ldg(xs + e + u * tpu); b[u] = __ldg(xn + e + u * tpu); c2[u] = ms ? __ldg(ms + e + u * tpu) : 0.0; }
+#pragma unroll
+            for (int u = 0; u < U; ++u) { X[e + u * tpu] = a[u]; Xn[e + u * tpu] = b[u]; Mu[e + u * tpu] = c2[u]; }
+        }
+        for (; e < dc; e += tpu) { X[e] = __ldg(xs + e); Xn[e] = __ldg(xn + e); Mu[e] = ms ? __ldg(ms + e) : 0.0; }
     }
     for (int e = e0; e < dd; e += tpu) {
         const int off = (e % d) + (e / d) * ld;
-        double v = G0[e];
-        for (int j = 0; j < m; ++j) {
-            const double gj = Gd[j * dd + e];
-            Gs[j * msz + off] = gj;
-            v = fma(zk[p.u_off + j], gj, v);
+        double v = __ldg(G0 + e);
+        if constexpr (M > 0) {
+            double gj[M];
+#pragma unroll
+            for (int j = 0; j < M; ++j) gj[j] = __ldg(Gd + j * dd + e);
+#pragma unroll
+            for (int j = 0; j < M; ++j) { Gs[j * msz + off] = gj[j]; v = fma(zk[p.u_off + j], gj[j], v); }
+        } else {
+            for (int j = 0; j < m; ++j) {
+                const double gj = __ldg(Gd + j * dd + e);
+                Gs[j * msz + off] = gj;
+                v = fma(zk[p.u_off + j], gj, v);
+            }
         }
         G[off] = v;
     }
@@ -800,25 +840,11 @@ small_unit_kernel(const __grid_constant__ SmallParams p) {
         double *o = p.ha_out + (long long)ug * p.ha_stride;
         for (int e = e0; e < (m + 1) * dc + m * m + m + 2; e += tpu) o[e] = HA[e];
     }
-    // ---- coalesced COO stores in the caller's order ----
-    if (want_jac && p.jac) {
-        const uint32_t *cd = p.jcode + (long long)sys * p.jnnz;
-        double *o = p.jac + (long long)ug * p.jnnz;
-        for (long long e = e0; e < p.jnnz; e += tpu) {
-            uint32_t cc = cd[e];
-            double v = JA[cc & 0x7fffffffu];
-            o[e] = (cc >> 31) ? -v : v;
-        }
-    }
-    if (want_hess && p.hess) {
-        const uint32_t *cd = p.hcode + (long long)sys * p.hnnz;
-        double *o = p.hess + (long long)ug * p.hnnz;
-        for (long long e = e0; e < p.hnnz; e += tpu) {
-            uint32_t cc = cd[e];
-            double v = HA[cc & 0x7fffffffu];
-            o[e] = (cc >> 31) ? -v : v;
-        }
-    }
+    // ---- coalesced COO stores in the caller's order.  The slot codes come from global memory (L1 / L2): a
+    //      batch of them is fetched before any is used, so that their latency is paid once per batch and not
+    //      once per entry (ncu: a third of the d = 4 kernel's stall samples sat on these loads) ----
+    if (want_jac && p.jac) coo_store(p.jcode + (long long)sys * p.jnnz, JA, p.jac + (long long)ug * p.jnnz, p.jnnz, e0, tpu);
+    if (want_hess && p.hess) coo_store(p.hcode + (long long)sys * p.hnnz, HA, p.hess + (long long)ug * p.hnnz, p.hnnz, e0, tpu);
 }
 
 }  // namespace qcb
