@@ -153,7 +153,7 @@ qcb_status qcb_free_phase_create(qcb_free_phase *out, int32_t n, const double *g
                                  const double *phase_map, int32_t side, int32_t device) {
     if (!out || !goal || n < 1 || n_theta < 0 || (n_theta > 0 && !phase_map) || (side != 0 && side != 1))
         return fail(nullptr, QCB_ERR_ARG, "null/bad argument");
-    if (n > 4096) return fail(nullptr, QCB_ERR_ARG, "free-phase fidelity: n > 4096 is not supported");
+    if (n > 2048) return fail(nullptr, QCB_ERR_ARG, "free-phase fidelity: n > 2048 is not supported");   // 2n doubles of shared memory
     *out = nullptr;
     qcb_free_phase_s *f = new qcb_free_phase_s();
     try {
