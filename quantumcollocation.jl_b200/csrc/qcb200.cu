@@ -150,6 +150,7 @@ struct qcb_handle_s {
     // instead of being assembled into COO vectors here; may be another GPU's memory
     double *arena_out_j = nullptr, *arena_out_h = nullptr;
     cudaEvent_t ship_ev[3] = {nullptr, nullptr, nullptr};   // last delivery of [0] the E part, [1] the rest of the Jacobian arena, [2] the Hessian arena
+    int delivery_split = 1;        // QCB_DELIVERY_SPLIT: sequential pieces per slab in a multi-GPU delivery
     int arena_parts = 3;           // qcb_set_arena_parts: 1 = propagators only (E part), 2 = the rest of the Jacobian arena, 3 = all
     // Asynchronous mode (qcb_set_async): device-pointer calls return once their work is queued; completion
     // and the range check are collected by qcb_wait.  Lets a caller queue the Jacobian and the Hessian side
@@ -987,7 +988,12 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         if (nj > 0 && prev_nu > prev_nd) task.start(jobs, nj, h->nk, prev_u0 + prev_nd, prev_nu - prev_nd);
         prev_u0 = -1;
     };
-    const int chunk_step = compact ? compact_step(h) : h->chunk_units;
+    // delivery_split > 1 (multi-GPU delivery): the slab is cut into that many sequential pieces even though the
+    // scratch holds all of it, so that the first piece's arenas cross NVLink while the next is computed
+    const int chunk_step = compact ? compact_step(h)
+                                   : ((h->delivery_split > 1 && (h->arena_out_j || h->arena_out_h) && h->chunk_units >= h->units)
+                                          ? std::max(1, (h->units + h->delivery_split - 1) / h->delivery_split)
+                                          : h->chunk_units);
     // Device-resident calls on one system: visit the units in the order of their squaring count, so
     // that a chunk never runs levels only a few of its members need (random pulses: most units sit
     // one level below the largest).  perm maps position -> unit; the kernels that touch Z, mu and
@@ -1044,7 +1050,8 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         }
         nu_next = nu;
         const long long ub = slices ? u0 : 0;                          // scratch slice of this chunk
-        cudaStream_t st = (lanes && (chunk_idx & 1)) ? h->stream2 : h->stream;
+        // lanes alternate by squaring class: the pieces of one class follow each other on their stream
+        cudaStream_t st = (lanes && (class_idx & 1)) ? h->stream2 : h->stream;
         // squarings of this chunk: what the largest ||dt G(u)||_1 among its units needs (smooth pulses
         // have slowly varying norms, so quiet stretches of the trajectory skip levels the peaks need)
         int s = s_slab;
@@ -1670,6 +1677,7 @@ qcb_status qcb_create(qcb_handle *out, const qcb_desc *desc) {
 
     qcb_handle_s *h = new qcb_handle_s();
     h->run_assembly = !getenv("QCB_GATHER_ASSEMBLY");
+    if (const char *e = getenv("QCB_DELIVERY_SPLIT")) h->delivery_split = std::max(1, atoi(e));
     try {
         int ndev = 0;
         if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
