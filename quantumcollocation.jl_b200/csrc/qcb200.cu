@@ -543,9 +543,12 @@ void launch_gemm_cfg(qcb_handle_s *h, const GemmArgs &g, int batch, cudaStream_t
 
 void launch_gemm_iso(qcb_handle_s *h, const GemmArgs &g, int units, cudaStream_t st) {
     static bool attr_set[64] = {false};
-    constexpr int ST = 3;
-    auto kern = bgemm_iso_kernel<ST>;
-    const size_t smem = GemmSmem<128, 64>::bytes(ST);
+#ifndef QCB_ISO_BK
+#define QCB_ISO_BK 16
+#endif
+    constexpr int IBK = QCB_ISO_BK, ST = IBK == 16 ? 3 : 2;      // 16-deep slabs x 3 stages (92 KB), or 32-deep x 2 (98 KB)
+    auto kern = bgemm_iso_kernel<ST, IBK>;
+    const size_t smem = GemmSmem<128, 64, IBK>::bytes(ST);
     if (!attr_set[h->device]) {
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set[h->device] = true;

@@ -48,9 +48,9 @@ __device__ __forceinline__ void dmma_16x8x4(double (&c)[4], double a0, double a1
 }
 
 constexpr int GEMM_BK = 16;
-template <int BM, int BN> struct GemmSmem {
-    static constexpr int A_ST = (GEMM_BK * (BM + 4) > BM * (GEMM_BK + 4)) ? GEMM_BK * (BM + 4) : BM * (GEMM_BK + 4);
-    static constexpr int B_ST = (GEMM_BK * (BN + 4) > BN * (GEMM_BK + 4)) ? GEMM_BK * (BN + 4) : BN * (GEMM_BK + 4);
+template <int BM, int BN, int BKT = GEMM_BK> struct GemmSmem {
+    static constexpr int A_ST = (BKT * (BM + 4) > BM * (BKT + 4)) ? BKT * (BM + 4) : BM * (BKT + 4);
+    static constexpr int B_ST = (BKT * (BN + 4) > BN * (BKT + 4)) ? BKT * (BN + 4) : BN * (BKT + 4);
     static constexpr size_t bytes(int stages) {
         size_t pipe = (size_t)stages * (A_ST + B_ST) * sizeof(double);
         size_t ctile = (size_t)BN * (BM + 2) * sizeof(double);
@@ -236,10 +236,10 @@ __device__ __forceinline__ double flip_sign(double v, unsigned mask) {
 }
 
 // one staged K slab (16 deep) of the 128 x 64 tile: fragments from shared memory, 64 DMMA per warp
-template <int TA, int TB, int MT, int NT>
+template <int TA, int TB, int MT, int NT, int BK>
 __device__ __forceinline__ void iso_slab_mma(double (&acc)[MT][NT][4], const double *as0, const double *bs0,
                                              int arow, int bcol, int tig) {
-    constexpr int BM = 128, BN = 64, BK = GEMM_BK;
+    constexpr int BM = 128, BN = 64;
     constexpr int a_rs = TA ? (BK + 4) : 1, a_ks = TA ? 1 : (BM + 4);
     constexpr int b_ks = TB ? (BN + 4) : 1, b_ns = TB ? 1 : (BK + 4);
     const double *as = as0 + arow * a_rs + tig * a_ks;
@@ -261,12 +261,14 @@ __device__ __forceinline__ void iso_slab_mma(double (&acc)[MT][NT][4], const dou
     }
 }
 
-template <int STAGES>
+template <int STAGES, int BK = GEMM_BK>
 __global__ void __launch_bounds__(256, 2)
 bgemm_iso_kernel(const __grid_constant__ GemmArgs g) {
-    constexpr int BM = 128, BN = 64, WM = 32, WN = 32, BK = GEMM_BK, NTHR = 256;
+    constexpr int BM = 128, BN = 64, WM = 32, WN = 32, NTHR = 256;
     constexpr int MT = WM / 16, NT = WN / 8;
-    constexpr int A_ST = GemmSmem<BM, BN>::A_ST, B_ST = GemmSmem<BM, BN>::B_ST;
+    constexpr int A_ST = GemmSmem<BM, BN, BK>::A_ST, B_ST = GemmSmem<BM, BN, BK>::B_ST;
+    constexpr int NA = BK / 4, NB = BK / 8;          // 16-byte chunks per thread and slab: A 128 x BK, B BK x 64
+    constexpr int KT = BK / 2;                       // threads that cover the K extent of a slab in pairs
     extern __shared__ __align__(16) double smem[];
     double *As = smem, *Bs = smem + STAGES * A_ST;
 
@@ -297,7 +299,7 @@ bgemm_iso_kernel(const __grid_constant__ GemmArgs g) {
     //      operands of the current term; advanced by a constant per slab, corrected once when the
     //      slab crosses k = n (the rotated half of the virtual full operand) ----
     const double *l_pa = nullptr, *l_pb = nullptr;
-    int offA[4], adjA[4], offB[2], stepA = 0, stepB = 0, adjB = 0;
+    int offA[NA], adjA[NA], offB[NB], stepA = 0, stepB = 0, adjB = 0;
     int sA = 0, sAstep = 0, sB = 0, sBstep = 0;     // shared-memory offsets of chunk 0 and the chunk stride
     int l_term = 0, l_slab = 0, l_stage = 0;
     auto loader_init = [&](int term) {
@@ -309,31 +311,31 @@ bgemm_iso_kernel(const __grid_constant__ GemmArgs g) {
             const int r = m0 + 2 * (tid & 63), kc = tid >> 6;
             const int rrot = (r < nh) ? r + nh : r - nh;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) { offA[i] = r + (kc + 4 * i) * lda; adjA[i] = (rrot - r) - nh * lda; }
+            for (int i = 0; i < NA; ++i) { offA[i] = r + (kc + 4 * i) * lda; adjA[i] = (rrot - r) - nh * lda; }
             stepA = BK * lda;
             sA = kc * (BM + 4) + 2 * (tid & 63); sAstep = 4 * (BM + 4);
         } else {            // X_full(k, i): i < n -> X_L(k, i);  i >= n -> +-X_L((k + n) mod d, i - n)
-            const int k2 = 2 * (tid & 7);
+            const int k2 = 2 * (tid % KT);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int irow = m0 + (tid >> 3) + 32 * i;
+            for (int i = 0; i < NA; ++i) {
+                const int irow = m0 + (tid / KT) + (NTHR / KT) * i;
                 const bool ihi = irow >= nh;
                 offA[i] = (ihi ? k2 + nh : k2) + (ihi ? irow - nh : irow) * lda;
                 adjA[i] = ihi ? -dfull : 0;
             }
             stepA = BK;
-            sA = (tid >> 3) * (BK + 4) + k2; sAstep = 32 * (BK + 4);
+            sA = (tid / KT) * (BK + 4) + k2; sAstep = (NTHR / KT) * (BK + 4);
         }
         if (!t.tb) {        // plain K x N right operand
-            const int k2 = 2 * (tid & 7);
+            const int k2 = 2 * (tid % KT);
 #pragma unroll
-            for (int i = 0; i < 2; ++i) offB[i] = k2 + (n0 + (tid >> 3) + 32 * i) * ldb;
+            for (int i = 0; i < NB; ++i) offB[i] = k2 + (n0 + (tid / KT) + (NTHR / KT) * i) * ldb;
             stepB = BK; adjB = 0;
-            sB = (tid >> 3) * (BK + 4) + k2; sBstep = 32 * (BK + 4);
+            sB = (tid / KT) * (BK + 4) + k2; sBstep = (NTHR / KT) * (BK + 4);
         } else {            // (Y^T)_L(k, c) = Y_L(c, k) (k < n) or -Y_L(c + n, k - n)
             const int n2 = 2 * (tid & 31), kc = tid >> 5;
 #pragma unroll
-            for (int i = 0; i < 2; ++i) offB[i] = (n0 + n2) + (kc + 8 * i) * ldb;
+            for (int i = 0; i < NB; ++i) offB[i] = (n0 + n2) + (kc + 8 * i) * ldb;
             stepB = BK * ldb; adjB = nh - nh * ldb;
             sB = kc * (BN + 4) + n2; sBstep = 8 * (BN + 4);
         }
@@ -341,9 +343,9 @@ bgemm_iso_kernel(const __grid_constant__ GemmArgs g) {
     auto loader_issue = [&]() {
         double *as = As + l_stage * A_ST + sA, *bs = Bs + l_stage * B_ST + sB;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) cp_async16(as + i * sAstep, l_pa + offA[i]);
+        for (int i = 0; i < NA; ++i) cp_async16(as + i * sAstep, l_pa + offA[i]);
 #pragma unroll
-        for (int i = 0; i < 2; ++i) cp_async16(bs + i * sBstep, l_pb + offB[i]);
+        for (int i = 0; i < NB; ++i) cp_async16(bs + i * sBstep, l_pb + offB[i]);
         l_stage = (l_stage + 1 == STAGES) ? 0 : l_stage + 1;
         if (++l_slab == kslabs) {
             l_slab = 0;
@@ -351,9 +353,9 @@ bgemm_iso_kernel(const __grid_constant__ GemmArgs g) {
         } else {
             const bool cross = (l_slab == half);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) offA[i] += stepA + (cross ? adjA[i] : 0);
+            for (int i = 0; i < NA; ++i) offA[i] += stepA + (cross ? adjA[i] : 0);
 #pragma unroll
-            for (int i = 0; i < 2; ++i) offB[i] += stepB + (cross ? adjB : 0);
+            for (int i = 0; i < NB; ++i) offB[i] += stepB + (cross ? adjB : 0);
         }
     };
 
@@ -396,10 +398,10 @@ bgemm_iso_kernel(const __grid_constant__ GemmArgs g) {
         }
         // four compile-time layouts of the staged tiles -> LDS with immediate offsets
         const double *as0 = As + c_stage * A_ST, *bs0 = Bs + c_stage * B_ST;
-        if (!c_ta && !c_tb) iso_slab_mma<0, 0, MT, NT>(acc, as0, bs0, wm * WM + gid, wn * WN + gid, tig);
-        else if (c_ta && !c_tb) iso_slab_mma<1, 0, MT, NT>(acc, as0, bs0, wm * WM + gid, wn * WN + gid, tig);
-        else if (!c_ta && c_tb) iso_slab_mma<0, 1, MT, NT>(acc, as0, bs0, wm * WM + gid, wn * WN + gid, tig);
-        else iso_slab_mma<1, 1, MT, NT>(acc, as0, bs0, wm * WM + gid, wn * WN + gid, tig);
+        if (!c_ta && !c_tb) iso_slab_mma<0, 0, MT, NT, BK>(acc, as0, bs0, wm * WM + gid, wn * WN + gid, tig);
+        else if (c_ta && !c_tb) iso_slab_mma<1, 0, MT, NT, BK>(acc, as0, bs0, wm * WM + gid, wn * WN + gid, tig);
+        else if (!c_ta && c_tb) iso_slab_mma<0, 1, MT, NT, BK>(acc, as0, bs0, wm * WM + gid, wn * WN + gid, tig);
+        else iso_slab_mma<1, 1, MT, NT, BK>(acc, as0, bs0, wm * WM + gid, wn * WN + gid, tig);
         c_stage = (c_stage + 1 == STAGES) ? 0 : c_stage + 1;
         if (++c_slab == kslabs) {
             c_slab = 0;
