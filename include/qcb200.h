@@ -131,6 +131,19 @@ qcb_status qcb_eval_hessian(qcb_handle h, const double *Z, const double *mu, dou
 qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu,
                         double *delta, double *jac_vals, double *hess_vals);
 
+/* The same four calls with Ipopt's `new_x` flag -- the argument Ipopt passes to eval_g / eval_jac_g / eval_h
+ * (0: "x is the point of the previous callback").  new_x != 0: identical to the calls above.  new_x == 0: the
+ * caller promises that Z holds what the previous host-buffer call on this handle was given; Z is then not
+ * uploaded again and whatever depends on Z alone (propagators, forward tangents, the Jacobian arenas) is taken
+ * from the handle's scratch, so that eval_g -> eval_jac_g -> eval_h on one iterate cost one pass; mu may
+ * differ (new_lambda).  Results are bit-identical to the recomputing calls.  Reuse needs the large-d path with
+ * the whole slab inside the scratch budget; otherwise the flag is ignored and the call recomputes. */
+qcb_status qcb_eval_defect_x(qcb_handle h, const double *Z, int32_t new_x, double *delta);
+qcb_status qcb_eval_jacobian_x(qcb_handle h, const double *Z, int32_t new_x, double *jac_vals);
+qcb_status qcb_eval_hessian_x(qcb_handle h, const double *Z, int32_t new_x, const double *mu, double *hess_vals);
+qcb_status qcb_eval_all_x(qcb_handle h, const double *Z, const double *mu, int32_t new_x,
+                          double *delta, double *jac_vals, double *hess_vals);
+
 /* ---- evaluation, device buffers (inputs/outputs already resident in HBM) ---------------
  * Same semantics; all pointers are device pointers on the handle's device; the work is
  * ordered on the handle's OWN stream (qcb_stream) and the call returns after it has completed.

@@ -106,6 +106,23 @@ function hessian_of_lagrangian_values!(vals::AbstractVector{Float64}, int::B200B
         (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}), int.handle, Z, μ, vals))
 end
 
+# The same callbacks carrying Ipopt's new_x flag (MOI passes it through eval_constraint / eval_constraint_jacobian /
+# eval_hessian_lagrangian as "x changed since the last call" [memory]): with new_x = false the library reuses what
+# the previous callback computed for this iterate.
+function evaluate!(δ::AbstractVector{Float64}, int::B200BilinearIntegrator, Z::Vector{Float64}, new_x::Bool)
+    GC.@preserve δ Z check(int.handle, ccall((:qcb_eval_defect_x, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Float64}, Int32, Ptr{Float64}), int.handle, Z, new_x, δ))
+end
+function jacobian_values!(vals::AbstractVector{Float64}, int::B200BilinearIntegrator, Z::Vector{Float64}, new_x::Bool)
+    GC.@preserve vals Z check(int.handle, ccall((:qcb_eval_jacobian_x, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Float64}, Int32, Ptr{Float64}), int.handle, Z, new_x, vals))
+end
+function hessian_of_lagrangian_values!(vals::AbstractVector{Float64}, int::B200BilinearIntegrator,
+                                       Z::Vector{Float64}, μ::Vector{Float64}, new_x::Bool)
+    GC.@preserve vals Z μ check(int.handle, ccall((:qcb_eval_hessian_x, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Float64}, Int32, Ptr{Float64}, Ptr{Float64}), int.handle, Z, new_x, μ, vals))
+end
+
 # Structure queries: what the MOI evaluator of DirectTrajOpt asks of an integrator before the solve.
 # The generic names below are [memory] (SURVEY.md 8b); the arrays are 1-based, rows relative to
 # `row_base` (the offset of this integrator's defect rows in the constraint vector).

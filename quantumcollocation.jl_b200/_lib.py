@@ -48,6 +48,10 @@ SYMBOLS = {
     "qcb_eval_jacobian": (ctypes.c_int, [c_vp, c_vp, c_vp]),
     "qcb_eval_hessian": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp]),
     "qcb_eval_all": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "qcb_eval_defect_x": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, c_vp]),
+    "qcb_eval_jacobian_x": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, c_vp]),
+    "qcb_eval_hessian_x": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, c_vp, c_vp]),
+    "qcb_eval_all_x": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int32, c_vp, c_vp, c_vp]),
     "qcb_eval_all_device": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "qcb_eval_all_device_x": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int32, c_vp, c_vp, c_vp]),
     "qcb_rollout": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp]),

@@ -154,6 +154,13 @@ class Evaluator:
         self._check(self.lib.qcb_eval_hessian(self.h, _ptr(Z), _ptr(mu), _ptr(hess)))
         return hess
 
+    def eval_all_x(self, Z, mu, new_x, delta=None, jac=None, hess=None):
+        """Host-buffer evaluation with Ipopt's new_x flag (include/qcb200.h, qcb_eval_all_x): outputs are
+        written where given (numpy arrays or raw addresses); None skips that output."""
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        mu = None if mu is None else np.ascontiguousarray(mu, dtype=np.float64)
+        self._check(self.lib.qcb_eval_all_x(self.h, _ptr(Z), _ptr(mu), 1 if new_x else 0, _ptr(delta), _ptr(jac), _ptr(hess)))
+
     # -- evaluation with device buffers (torch CUDA tensors or raw device addresses) --
     def eval_all_device(self, dZ, dmu, d_delta, d_jac, d_hess):
         """Device-resident evaluation.  The library runs on its own stream, so torch tensors are made

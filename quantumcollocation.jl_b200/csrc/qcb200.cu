@@ -145,6 +145,7 @@ struct qcb_handle_s {
     int cache_have = 0;
     int cache_s_slab = -1;
     int reuse = 0;                 // set by the *_x entry points for the call in flight
+    bool dZ_valid = false;         // the staged device copy of Z is the one the last host-buffer call uploaded
 
     // arena delivery (qcb_eval_arenas_device): where the per-unit value arenas of the slab are written
     // instead of being assembled into COO vectors here; may be another GPU's memory
@@ -1033,7 +1034,10 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     // When the scratch holds the whole slab every chunk works on its own slice (offset = its first
     // position): nothing is overwritten by a later chunk, which is what lets a new_x = 0 call find the
     // previous call's intermediates in place.
-    const bool slices = !host && !E_out && h->chunk_units >= h->units && (long long)h->m * dd >= (long long)h->dp * h->dp;
+    // (host-buffer calls included: their small chunks then work on consecutive slices, which is what lets
+    // qcb_eval_jacobian_x / qcb_eval_hessian_x with new_x = 0 reuse what an earlier callback computed)
+    const bool slices = !E_out && h->chunk_units >= h->units && (long long)h->m * dd >= (long long)h->dp * h->dp &&
+                        !(host && h->direct_fraction > 0.0);
     const bool lanes = perm && slices && !h->profiling && !getenv("QCB_NO_LANES");   // per-launch timing needs kernels that run alone
     const int reuse = slices ? (h->reuse & h->cache_have) : 0;
     h->cache_have = 0;              // re-established below once this call's launches are queued
@@ -1066,8 +1070,9 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
         LargeExec X{h, nu, u0, s};
         X.dd = dd; X.pan = pan; X.ubase = (int)ub; X.st = st;
         const int buf = compact ? (int)(chunk_idx & 1) : 0;
-        X.ja = buf ? h->sc_ja2 : h->sc_ja;
-        X.ha = buf ? h->sc_ha2 : h->sc_ha;
+        // sliced scratch: every chunk has arena rows of its own (nothing to double-buffer)
+        X.ja = (buf && !slices) ? h->sc_ja2 : h->sc_ja;
+        X.ha = (buf && !slices) ? h->sc_ha2 : h->sc_ha;
         // the D2H of chunk idx-2 read this arena set: let it finish before overwriting
         if (compact && chunk_idx >= 2) {
             CK(cudaStreamWaitEvent(st, h->copied[buf], 0));
@@ -1324,8 +1329,8 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
                     }
                 };
                 task.finish();      // chunk idx - 2 read the staging buffers the copies below overwrite
-                if (wj && host->jac && nu > nd) to_host(jdir, X.ja, h->JA, h->stage_j[buf], host->jac, h->jnnz_unit, h->jdirect, h->jstage);
-                if (wh && host->hess && nu > nd) to_host(hdir, X.ha, h->HA, h->stage_h[buf], host->hess, h->hnnz_unit, h->hdirect, h->hstage);
+                if (wj && host->jac && nu > nd) to_host(jdir, X.at(X.ja, h->JA), h->JA, h->stage_j[buf], host->jac, h->jnnz_unit, h->jdirect, h->jstage);
+                if (wh && host->hess && nu > nd) to_host(hdir, X.at(X.ha, h->HA), h->HA, h->stage_h[buf], host->hess, h->hnnz_unit, h->hdirect, h->hstage);
                 CK(cudaEventRecord(h->copied[buf], h->copy_stream));
                 if (nd > 0) {
                     if (wj && host->jac) {
@@ -1500,7 +1505,7 @@ qcb_status eval_device_inner(qcb_handle_s *h, const double *dZ, const double *dm
     const char *range_msg = "non-finite input or ||dt*G(u)||_1 beyond the supported range";
     if (h->large) {
         // new_x = 0: the norms, the squaring classes and the unit order are those of the previous call
-        const bool same_x = (h->reuse & h->cache_have & 1) && !host && !E_out && h->cache_s_slab >= 0;
+        const bool same_x = (h->reuse & h->cache_have & 1) && !E_out && h->cache_s_slab >= 0;
         const int s = same_x ? h->cache_s_slab : slab_squarings(h, dZ);
         if (!same_x) h->cache_have = 0;
         if (s < 0) { h->err = range_msg; return QCB_ERR_RANGE; }
@@ -2034,6 +2039,7 @@ qcb_status qcb_set_structure(qcb_handle h, int64_t row_base, const int64_t *jr, 
 qcb_status qcb_eval_all_device(qcb_handle h, const double *dZ, const double *dmu, double *d_delta,
                                double *d_jac, double *d_hess) {
     if (!h || !dZ) return fail(h, QCB_ERR_ARG, "null argument");
+    h->dZ_valid = false;        // what the scratch holds now belongs to the caller's dZ, not to the staged copy
     try {
         CK(cudaSetDevice(h->device));
         int want = (d_jac ? 1 : 0) | ((d_hess && dmu) ? 2 : 0);
@@ -2050,6 +2056,7 @@ qcb_status qcb_eval_arenas_device(qcb_handle h, const double *dZ, const double *
                                   double *d_jac_arenas, double *d_hess_arenas) {
     if (!h || !dZ) return fail(h, QCB_ERR_ARG, "null argument");
     if (!h->large) return fail(h, QCB_ERR_ARG, "arena delivery exists on the large-d path only (small units are cheaper to deliver assembled)");
+    h->dZ_valid = false;
     try {
         CK(cudaSetDevice(h->device));
         const int want = ((d_jac_arenas && (h->arena_parts & 2)) ? 1 : 0) | ((d_hess_arenas && dmu) ? 2 : 0);
@@ -2149,10 +2156,14 @@ qcb_status qcb_eval_all_device_x(qcb_handle h, const double *dZ, const double *d
     return st;
 }
 
-qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu, double *delta, double *jac, double *hess) {
+qcb_status qcb_eval_all_x(qcb_handle h, const double *Z, const double *mu, int32_t new_x, double *delta, double *jac,
+                          double *hess) {
     if (!h || !Z) return fail(h, QCB_ERR_ARG, "null argument");
     if (hess && !mu) return fail(h, QCB_ERR_ARG, "Hessian values need the multipliers");
     try {
+        // new_x = 0 with the previous iterate's intermediates still in place: Z is not even uploaded again
+        const bool keep_z = !new_x && h->large && (h->cache_have & 1) && h->dZ_valid;
+        h->reuse = keep_z ? 3 : 0;
         CK(cudaSetDevice(h->device));
         const size_t ezd = (size_t)h->ez();          // knot width of the caller's Z
         const size_t nz = (size_t)h->N * ezd, nmu = (size_t)h->S * h->K * h->xdim;
@@ -2169,15 +2180,17 @@ qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu, double 
         if (hess && !compact) ensure_out(h, &h->d_hess, (size_t)h->units * h->hnnz_unit);
         CK(cudaEventRecord(h->ev[0], h->stream));
         // only the knots of this slab (plus the halo knot k_end) are needed on the device
-        CK(cudaMemcpyAsync(*dZ_in + (size_t)h->k0 * ezd, Z + (size_t)h->k0 * ezd,
-                           (size_t)(h->nk + 1) * ezd * 8, cudaMemcpyHostToDevice, h->stream));
+        if (!keep_z)
+            CK(cudaMemcpyAsync(*dZ_in + (size_t)h->k0 * ezd, Z + (size_t)h->k0 * ezd,
+                               (size_t)(h->nk + 1) * ezd * 8, cudaMemcpyHostToDevice, h->stream));
+        h->dZ_valid = false;
         if (hess) {
             for (int s = 0; s < h->S; ++s) {
                 const size_t off = ((size_t)s * h->K + h->k0) * h->xdim;
                 CK(cudaMemcpyAsync(h->dmu + off, mu + off, (size_t)h->nk * h->xdim * 8, cudaMemcpyHostToDevice, h->stream));
             }
         }
-        h->xfer[0] = (int64_t)(h->nk + 1) * (int64_t)ezd * 8 + (hess ? (int64_t)h->S * h->nk * h->xdim * 8 : 0);
+        h->xfer[0] = (keep_z ? 0 : (int64_t)(h->nk + 1) * (int64_t)ezd * 8) + (hess ? (int64_t)h->S * h->nk * h->xdim * 8 : 0);
         h->xfer[1] = 0;   // counted where the device->host copies are issued
         h->xfer_compact = compact;
         CK(cudaEventRecord(h->ev[1], h->stream));
@@ -2194,10 +2207,29 @@ qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu, double 
         cudaEventElapsedTime(&a, h->ev[0], h->ev[1]);
         cudaEventElapsedTime(&b, h->ev[1], h->ev[2]);
         h->ms[0] = a; h->ms[1] = b; h->ms[2] = 0; h->ms[3] = a + b;
+        h->reuse = 0;
+        h->dZ_valid = st == QCB_OK;
         return st;
     } catch (const CudaFail &f) {
+        h->reuse = 0;
         return fail_cuda(h, f);
     }
+}
+
+qcb_status qcb_eval_all(qcb_handle h, const double *Z, const double *mu, double *delta, double *jac, double *hess) {
+    return qcb_eval_all_x(h, Z, mu, 1, delta, jac, hess);
+}
+qcb_status qcb_eval_defect_x(qcb_handle h, const double *Z, int32_t new_x, double *delta) {
+    if (!delta) return fail(h, QCB_ERR_ARG, "null output");
+    return qcb_eval_all_x(h, Z, nullptr, new_x, delta, nullptr, nullptr);
+}
+qcb_status qcb_eval_jacobian_x(qcb_handle h, const double *Z, int32_t new_x, double *jac) {
+    if (!jac) return fail(h, QCB_ERR_ARG, "null output");
+    return qcb_eval_all_x(h, Z, nullptr, new_x, nullptr, jac, nullptr);
+}
+qcb_status qcb_eval_hessian_x(qcb_handle h, const double *Z, int32_t new_x, const double *mu, double *hess) {
+    if (!hess) return fail(h, QCB_ERR_ARG, "null output");
+    return qcb_eval_all_x(h, Z, mu, new_x, nullptr, nullptr, hess);
 }
 
 qcb_status qcb_eval_defect(qcb_handle h, const double *Z, double *delta) {

@@ -731,3 +731,42 @@ def test_host_route_with_pinned_buffers_takes_direct_panels_and_matches(built_li
     ev2.eval_all_raw(hZ.data_ptr(), hmu.data_ptr(), pd_.data_ptr(), pj.data_ptr(), ph.data_ptr())
     assert np.array_equal(pj.numpy(), j0)
     ev.close(); ev2.close()
+
+
+def test_new_x_reuse_through_the_host_buffer_calls(built_libs):
+    """qcb_eval_defect_x / jacobian_x / hessian_x: Ipopt's callback order on one iterate through HOST buffers
+    (what the Julia shim calls) equals the recomputing calls bit for bit, skips the upload of Z and most of
+    the kernels, and a new iterate is recomputed."""
+    w = workloads.make("cfg5", N=9)
+    L = w.layout
+    ev = Evaluator(L, w.G_drift, w.G_drives)
+    d0, j0, h0 = ev.eval_all(w.Z, w.mu)
+    l_full = ev.kernel_launches
+    d, j, h = np.full_like(d0, np.nan), np.full_like(j0, np.nan), np.full_like(h0, np.nan)
+    ev.eval_all_x(w.Z, None, True, delta=d)
+    a = ev.kernel_launches
+    ev.eval_all_x(w.Z, None, False, jac=j)
+    assert ev.transfer_bytes()[0] == 0                                # Z stayed on the device
+    b = ev.kernel_launches
+    ev.eval_all_x(w.Z, w.mu, False, hess=h)
+    c = ev.kernel_launches
+    assert np.array_equal(d, d0) and np.array_equal(j, j0) and np.array_equal(h, h0)
+    assert (c - a) < (l_full - 0) and (b - a) > 0 and (c - b) > 0
+    # the three callbacks together launch about what one fused pass does (not three passes)
+    assert (c - l_full) < 1.35 * l_full
+    # new multipliers, same point
+    h2 = np.full_like(h0, np.nan)
+    ev.eval_all_x(w.Z, 3.0 * w.mu, False, hess=h2)
+    assert rel_err(h2, 3.0 * h0) < 1e-13
+    # a new point: new_x = 1 recomputes; a stale new_x = 0 after a device-buffer call falls back to recomputing
+    Z2 = w.Z.copy(); Z2.reshape(L.N, L.z_dim)[:, L.u_off:L.u_off + L.m] *= 0.5
+    ev.eval_all_x(Z2, w.mu, True, delta=d, jac=j, hess=h)
+    fresh = Evaluator(L, w.G_drift, w.G_drives)
+    fd, fj, fh = fresh.eval_all(Z2, w.mu)
+    assert np.array_equal(d, fd) and np.array_equal(j, fj) and np.array_equal(h, fh)
+    import torch
+    dZ = torch.from_numpy(w.Z).cuda(); dd = torch.empty(ev.defect_dim, dtype=torch.float64, device="cuda")
+    ev.eval_all_device(dZ, None, dd, None, None)                     # the scratch now belongs to another Z
+    ev.eval_all_x(Z2, None, False, jac=j)                             # promise cannot be honoured: recompute
+    assert np.array_equal(j, fj)
+    ev.close(); fresh.close()
