@@ -759,7 +759,7 @@ void free_scratch(qcb_handle_s *h) {
 // Units per chunk of a host-complete call.  Those are bound by the host cores' expansion, not by the
 // GPU: small chunks let the first arenas reach the host early, so the expansion pipeline starts after a
 // millisecond instead of a third of the evaluation, and its last chunk is short.
-int compact_step(const qcb_handle_s *h) {
+int compact_step(const qcb_handle_s *h, bool with_jacobian = true) {
     if (getenv("QCB_E2E_BIG_CHUNKS")) return h->chunk_units;
     if (const char *e = getenv("QCB_E2E_UNITS")) return (int)std::min<long long>(h->chunk_units, std::max(1L, atol(e)));
     const long long slots = (long long)h->n_sm * (h->iso ? 2 : 1);
@@ -768,12 +768,16 @@ int compact_step(const qcb_handle_s *h) {
     // one and a half waves of per-drive CTAs.  Measured on cfg5 (e2e, knot-evals/s) with the background expansion:
     // 16 units 6.4 k, 24: 11.9 k (the GPU side turns launch-bound), 32: 16.2 k, 40: 16.2 k, 48: 15.6 k, 80: 14.7 k,
     // 148 (six waves, the round-1 choice): 14.5 k -- short chunks shorten the pipeline's fill and drain
-    const long long small = std::max(1LL, 3 * slots / std::max<long long>(1, 2LL * std::max(1, h->m) * std::max(1LL, tiles)));
+    // A Hessian-only callback has a tenth of the host-side work (1.7 GB of values, most of them DMA'd straight into
+    // place): it is bound by the GPU, so its chunks are six waves long (eval_h through host buffers with new_x = 0:
+    // 62 ms with the short chunks, launch-bound).
+    const long long waves2 = with_jacobian ? 3 : 12;      // chunk length in half waves
+    const long long small = std::max(1LL, waves2 * slots / std::max<long long>(1, 2LL * std::max(1, h->m) * std::max(1LL, tiles)));
     return (int)std::min<long long>(h->chunk_units, small);
 }
 
 void ensure_compact(qcb_handle_s *h) {
-    const int step = compact_step(h);
+    const int step = std::max(compact_step(h, true), compact_step(h, false));     // staging sized for the longer chunks
     if (h->stage_units != step) {
         const size_t n = (size_t)step;
         CK(cudaMalloc(&h->sc_ja2, n * (size_t)h->JA * 8));
@@ -994,7 +998,7 @@ void eval_large(qcb_handle_s *h, const double *dZ, const double *dmu, double *d_
     };
     // delivery_split > 1 (multi-GPU delivery): the slab is cut into that many sequential pieces even though the
     // scratch holds all of it, so that the first piece's arenas cross NVLink while the next is computed
-    const int chunk_step = compact ? compact_step(h)
+    const int chunk_step = compact ? compact_step(h, wj)
                                    : ((h->delivery_split > 1 && (h->arena_out_j || h->arena_out_h) && h->chunk_units >= h->units)
                                           ? std::max(1, (h->units + h->delivery_split - 1) / h->delivery_split)
                                           : h->chunk_units);
