@@ -766,11 +766,11 @@ int compact_step(const qcb_handle_s *h, bool with_jacobian = true) {
     const long long tiles = h->iso ? (h->dp / 128) : ((h->dp % 128 == 0) ? (long long)(h->dp / 128) * (h->dp / 128)
                                                                           : (long long)(h->dp / 64) * (h->dp / 64));
     // one and a half waves of per-drive CTAs.  Measured on cfg5 (e2e, knot-evals/s) with the background expansion:
-    // 16 units 6.4 k, 24: 11.9 k (the GPU side turns launch-bound), 32: 16.2 k, 40: 16.2 k, 48: 15.6 k, 80: 14.7 k,
+    // 16 units 6.4 k, 24: 11.9 k (probably a slower box), 32: 16.2 k, 40: 16.2 k, 48: 15.6 k, 80: 14.7 k,
     // 148 (six waves, the round-1 choice): 14.5 k -- short chunks shorten the pipeline's fill and drain
     // A Hessian-only callback has a tenth of the host-side work (1.7 GB of values, most of them DMA'd straight into
     // place): it is bound by the GPU, so its chunks are six waves long (eval_h through host buffers with new_x = 0:
-    // 62 ms with the short chunks, launch-bound).
+    // 62 ms with the short chunks, 48 ms with these).
     const long long waves2 = with_jacobian ? 3 : 12;      // chunk length in half waves
     const long long small = std::max(1LL, waves2 * slots / std::max<long long>(1, 2LL * std::max(1, h->m) * std::max(1LL, tiles)));
     return (int)std::min<long long>(h->chunk_units, small);
