@@ -415,6 +415,63 @@ qcb_status qcb_aux_sensitivity_eval(qcb_aux a, const double *Z, int32_t x_off, i
                                     int32_t n_times, const int32_t *times, const double *Qs, double scale,
                                     double *objective, double *grad_vals, double *hess_vals);
 
+/* ---- one call per Ipopt callback (second half) ------------------------------
+ * The reference solves a QuantumControlProblem by handing Ipopt the five callbacks DirectTrajOpt's
+ * MOI evaluator builds over the lists a problem template assembles (src/quantum_control_problem.jl:163-164;
+ * src/problem_templates/smooth_pulse_problem.jl:139-165: objective = terminal infidelity +
+ * QuadraticRegularizers on u, du, ddu; integrators = [BilinearIntegrator, DerivativeIntegrator(u, du),
+ * DerivativeIntegrator(du, ddu)]; _problem_templates.jl:38-67 adds the timesteps-all-equal rows).
+ * A qcb_problem is that list on this side of the ABI.  It BORROWS its pieces (the caller keeps and
+ * destroys them, after the problem): integrator handles that own the whole trajectory, one qcb_aux
+ * (derivative rows, dt_t - dt_N rows, regularisers, minimum-time term) and one qcb_fidelity for
+ *     f(Z) = Q |1 - F(x_N)| + sum_terms 1/2 sum_t sum_i R_i (dt_t v_{t,i})^2 + D sum_{t<N} dt_t .
+ * Variables: Z, n = N * z_dim.  Constraint rows, in this order: every integrator's defect rows, the
+ * derivative rows, the N-1 timestep rows (m in total).  Each callback below is ONE call that writes
+ * the caller's full-length array; new_x is Ipopt's flag, passed through unchanged: the problem
+ * remembers which integrators have not yet seen the current iterate, so that
+ * eval_f(new_x = 1) -> eval_g(0) -> eval_jac_g(0) -> eval_h(0) uploads Z once per integrator and reuses
+ * the propagators and tangents between the three constraint callbacks (qcb_eval_*_x).
+ * Inequality rows (leakage constraint) and free-phase / sensitivity objectives stay separate calls. */
+typedef struct qcb_problem_s *qcb_problem;
+typedef struct {
+    int32_t struct_bytes;           /* sizeof(qcb_problem_desc) */
+    int32_t N;                      /* knots */
+    int32_t z_dim;                  /* doubles per knot */
+    int32_t n_integrators;
+    int32_t use_derivative_rows;    /* 1: aux's derivative integrators are constraint rows */
+    int32_t use_dt_equal_rows;      /* 1: append the rows dt_t - dt_N = 0 */
+    int32_t fid_hessian;            /* 1: dense upper-triangle Hessian block of the terminal term on x_N
+                                       (x_dim <= 8192); 0: left out (limited-memory runs, large states) */
+    int32_t n_reg;                  /* regulariser terms */
+    double Q;                       /* weight of the terminal infidelity */
+    double min_time_D;              /* weight of sum dt (0: none) */
+    const qcb_handle *integrators;  /* [n_integrators] */
+    qcb_aux aux;                    /* may be NULL when nothing of it is used */
+    qcb_fidelity fidelity;          /* may be NULL: no terminal term */
+    const int32_t *fid_index;       /* [x_dim of the fidelity] 0-based positions inside the LAST knot */
+    const int32_t *reg_off;         /* [n_reg] component offsets inside a knot */
+    const int32_t *reg_dim;         /* [n_reg] */
+    const double *reg_R;            /* weights, concatenated over the terms */
+} qcb_problem_desc;
+qcb_status qcb_problem_create(qcb_problem *out, const qcb_problem_desc *desc);
+void qcb_problem_destroy(qcb_problem p);
+const char *qcb_problem_last_error(qcb_problem p);   /* p may be NULL: error of the last failed create */
+/* n variables, m constraint rows, entries of the Jacobian and of the Hessian of the Lagrangian. */
+qcb_status qcb_problem_dims(qcb_problem p, int64_t *n, int64_t *m, int64_t *nnz_jac, int64_t *nnz_hess);
+/* 1-based COO structures in the order of the values (Hessian: upper triangle; an entry may occur more than
+ * once, the solver sums duplicates). */
+qcb_status qcb_problem_jacobian_structure(qcb_problem p, int64_t *rows, int64_t *cols);
+qcb_status qcb_problem_hessian_structure(qcb_problem p, int64_t *rows, int64_t *cols);
+/* Ipopt's callbacks; all buffers are host memory.  grad: n doubles, every entry written.  g: m doubles.
+ * lambda: m multipliers in the row order of eval_g; values = obj_factor * Hess f + sum lambda_i Hess g_i.
+ * |1 - F| is differentiated as the reference does (sign(1 - F), quantum_objectives.jl:199). */
+qcb_status qcb_problem_eval_f(qcb_problem p, const double *Z, int32_t new_x, double *f);
+qcb_status qcb_problem_eval_grad_f(qcb_problem p, const double *Z, int32_t new_x, double *grad);
+qcb_status qcb_problem_eval_g(qcb_problem p, const double *Z, int32_t new_x, double *g);
+qcb_status qcb_problem_eval_jac_g(qcb_problem p, const double *Z, int32_t new_x, double *jac_vals);
+qcb_status qcb_problem_eval_h(qcb_problem p, const double *Z, int32_t new_x, double obj_factor, const double *lambda,
+                              double *hess_vals);
+
 #ifdef __cplusplus
 }
 #endif

@@ -346,6 +346,97 @@ function sensitivity_objective!(grad_vals::Matrix{Float64}, a::Ptr{Cvoid}, Z::Ve
     return J[]
 end
 
+# ---- one ccall per Ipopt callback (include/qcb200.h: qcb_problem_*) -------------------------------------------
+# The whole list a problem template hands to DirectTrajOpt (smooth_pulse_problem.jl:139-165: terminal infidelity +
+# regularisers; BilinearIntegrator + two DerivativeIntegrators; the timesteps-all-equal rows of
+# _problem_templates.jl:38-67) behind five calls that write Ipopt's full-length arrays.  `new_x` is Ipopt's flag.
+struct QcbProblemDesc               # mirrors qcb_problem_desc
+    struct_bytes::Int32; N::Int32; z_dim::Int32; n_integrators::Int32
+    use_derivative_rows::Int32; use_dt_equal_rows::Int32; fid_hessian::Int32; n_reg::Int32
+    Q::Float64; min_time_D::Float64
+    integrators::Ptr{Ptr{Cvoid}}; aux::Ptr{Cvoid}; fidelity::Ptr{Cvoid}
+    fid_index::Ptr{Int32}; reg_off::Ptr{Int32}; reg_dim::Ptr{Int32}; reg_R::Ptr{Float64}
+end
+
+mutable struct B200Problem
+    handle::Ptr{Cvoid}
+    n::Int; m::Int; jac_nnz::Int; hess_nnz::Int
+    keep::Any                       # the borrowed pieces and index arrays: alive as long as the problem
+end
+
+"""
+    B200Problem(traj, integrators; aux, derivative_rows, dt_equal_rows, fidelity, state_name, Q, fid_hessian,
+                reg_names, reg_R, D)
+
+`integrators`: `B200BilinearIntegrator`s over the whole trajectory; `aux`: a `Ptr` from `qcb_aux_create` built with the
+derivative pairs (u, du), (du, ddu); `fidelity`: a `B200Fidelity` on the component `state_name` of the last knot.
+"""
+function B200Problem(traj::NamedTrajectory, integrators::Vector{B200BilinearIntegrator}; aux::Ptr{Cvoid} = C_NULL,
+                     derivative_rows::Bool = false, dt_equal_rows::Bool = false,
+                     fidelity::Union{Nothing,B200Fidelity} = nothing, state_name::Union{Nothing,Symbol} = nothing,
+                     Q::Float64 = 100.0, fid_hessian::Bool = true, reg_names::Vector{Symbol} = Symbol[],
+                     reg_R::Vector{Float64} = Float64[], D::Float64 = 0.0)
+    hs = Ptr{Cvoid}[i.handle for i in integrators]
+    fidx = isnothing(state_name) ? Int32[] : Int32.(traj.components[state_name] .- 1)
+    off = Int32[traj.components[n][1] - 1 for n in reg_names]
+    dim = Int32[length(traj.components[n]) for n in reg_names]
+    R = isempty(reg_names) ? Float64[] : vcat([fill(reg_R[i], dim[i]) for i in eachindex(reg_names)]...)
+    h = Ref{Ptr{Cvoid}}(C_NULL)
+    GC.@preserve hs fidx off dim R begin
+        desc = QcbProblemDesc(Int32(sizeof(QcbProblemDesc)), traj.N, traj.dim, length(hs), derivative_rows, dt_equal_rows,
+                              fid_hessian, length(dim), Q, D, pointer(hs), aux,
+                              isnothing(fidelity) ? C_NULL : fidelity.handle,
+                              isempty(fidx) ? C_NULL : pointer(fidx), isempty(off) ? C_NULL : pointer(off),
+                              isempty(dim) ? C_NULL : pointer(dim), isempty(R) ? C_NULL : pointer(R))
+        st = ccall((:qcb_problem_create, LIB), Cint, (Ref{Ptr{Cvoid}}, Ref{QcbProblemDesc}), h, desc)
+        st == 0 || error(unsafe_string(ccall((:qcb_problem_last_error, LIB), Cstring, (Ptr{Cvoid},), C_NULL)))
+    end
+    d = [Ref{Int64}(0) for _ in 1:4]
+    ccall((:qcb_problem_dims, LIB), Cint, (Ptr{Cvoid}, Ref{Int64}, Ref{Int64}, Ref{Int64}, Ref{Int64}), h[], d[1], d[2], d[3], d[4])
+    prob = B200Problem(h[], d[1][], d[2][], d[3][], d[4][], (integrators, fidelity, hs, fidx, off, dim, R))
+    finalizer(o -> ccall((:qcb_problem_destroy, LIB), Cvoid, (Ptr{Cvoid},), o.handle), prob)
+    return prob
+end
+
+pcheck(p::B200Problem, st) = st == 0 || error(unsafe_string(ccall((:qcb_problem_last_error, LIB), Cstring, (Ptr{Cvoid},), p.handle)))
+
+# the (row, column) lists MOI.jacobian_structure / MOI.hessian_lagrangian_structure return (1-based)
+function jacobian_structure(p::B200Problem)
+    rows = Vector{Int64}(undef, p.jac_nnz); cols = similar(rows)
+    pcheck(p, ccall((:qcb_problem_jacobian_structure, LIB), Cint, (Ptr{Cvoid}, Ptr{Int64}, Ptr{Int64}), p.handle, rows, cols))
+    return collect(zip(rows, cols))
+end
+function hessian_lagrangian_structure(p::B200Problem)
+    rows = Vector{Int64}(undef, p.hess_nnz); cols = similar(rows)
+    pcheck(p, ccall((:qcb_problem_hessian_structure, LIB), Cint, (Ptr{Cvoid}, Ptr{Int64}, Ptr{Int64}), p.handle, rows, cols))
+    return collect(zip(rows, cols))
+end
+# Ipopt's five callbacks (Ipopt.jl: eval_f(x), eval_grad_f(x, grad), eval_g(x, g), eval_jac_g(x, rows, cols, values),
+# eval_h(x, rows, cols, obj_factor, lambda, values)); MOI's AbstractNLPEvaluator methods have the same content
+function eval_f(p::B200Problem, Z::Vector{Float64}; new_x::Bool = true)
+    f = Ref{Float64}(0.0)
+    pcheck(p, ccall((:qcb_problem_eval_f, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Int32, Ref{Float64}), p.handle, Z, new_x, f))
+    return f[]
+end
+function eval_grad_f!(grad::Vector{Float64}, p::B200Problem, Z::Vector{Float64}; new_x::Bool = false)
+    pcheck(p, ccall((:qcb_problem_eval_grad_f, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Int32, Ptr{Float64}), p.handle, Z, new_x, grad))
+    return grad
+end
+function eval_g!(g::Vector{Float64}, p::B200Problem, Z::Vector{Float64}; new_x::Bool = false)
+    pcheck(p, ccall((:qcb_problem_eval_g, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Int32, Ptr{Float64}), p.handle, Z, new_x, g))
+    return g
+end
+function eval_jac_g!(vals::Vector{Float64}, p::B200Problem, Z::Vector{Float64}; new_x::Bool = false)
+    pcheck(p, ccall((:qcb_problem_eval_jac_g, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Int32, Ptr{Float64}), p.handle, Z, new_x, vals))
+    return vals
+end
+function eval_h!(vals::Vector{Float64}, p::B200Problem, Z::Vector{Float64}, obj_factor::Float64, lambda::Vector{Float64};
+                 new_x::Bool = false)
+    pcheck(p, ccall((:qcb_problem_eval_h, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Int32, Float64, Ptr{Float64}, Ptr{Float64}),
+                    p.handle, Z, new_x, obj_factor, lambda, vals))
+    return vals
+end
+
 # Old (docs / BASELINE.json) names, SURVEY.md Appendix A
 const UnitaryIntegrator = B200BilinearIntegrator
 const KetIntegrator = B200BilinearIntegrator

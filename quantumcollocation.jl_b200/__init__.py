@@ -7,5 +7,5 @@ multi-GPU time-slab driver.
 """
 from . import isomorphisms, layout, workloads, piccolo, distributed  # noqa: F401
 from .layout import KnotLayout, JAC_BLOCK_DIAG, JAC_DENSE_X  # noqa: F401
-from .api import Aux, Evaluator, Fidelity, FreePhaseFidelity  # noqa: F401
+from .api import Aux, Evaluator, Fidelity, FreePhaseFidelity, Problem  # noqa: F401
 from ._lib import QcbError, load as load_library  # noqa: F401

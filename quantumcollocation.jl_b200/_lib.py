@@ -30,6 +30,13 @@ class QcbAuxDesc(ctypes.Structure):
         ("deriv_x_off", c_ip), ("deriv_dx_off", c_ip), ("deriv_dim", c_ip), ("leak_idx", c_ip)]
 
 
+class QcbProblemDesc(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in (
+        "struct_bytes", "N", "z_dim", "n_integrators", "use_derivative_rows", "use_dt_equal_rows", "fid_hessian", "n_reg")] + [
+        ("Q", ctypes.c_double), ("min_time_D", ctypes.c_double), ("integrators", ctypes.POINTER(c_vp)), ("aux", c_vp),
+        ("fidelity", c_vp), ("fid_index", c_ip), ("reg_off", c_ip), ("reg_dim", c_ip), ("reg_R", c_dp)]
+
+
 STATUS = {0: "QCB_OK", 1: "QCB_ERR_ARG", 2: "QCB_ERR_CUDA", 3: "QCB_ERR_RANGE", 4: "QCB_ERR_STRUCTURE", 5: "QCB_ERR_NOMEM"}
 
 # every symbol include/qcb200.h declares: name -> (restype, argtypes)
@@ -104,6 +111,17 @@ SYMBOLS = {
     "qcb_aux_sensitivity_eval": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                                 c_ip, c_vp, ctypes.c_double, c_dp, c_vp, c_vp]),
     "qcb_fidelity_eval_batch_device_noalloc": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int64, c_vp, c_vp]),
+    "qcb_problem_create": (ctypes.c_int, [ctypes.POINTER(c_vp), ctypes.POINTER(QcbProblemDesc)]),
+    "qcb_problem_destroy": (None, [c_vp]),
+    "qcb_problem_last_error": (ctypes.c_char_p, [c_vp]),
+    "qcb_problem_dims": (ctypes.c_int, [c_vp, c_lp, c_lp, c_lp, c_lp]),
+    "qcb_problem_jacobian_structure": (ctypes.c_int, [c_vp, c_lp, c_lp]),
+    "qcb_problem_hessian_structure": (ctypes.c_int, [c_vp, c_lp, c_lp]),
+    "qcb_problem_eval_f": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, c_dp]),
+    "qcb_problem_eval_grad_f": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, c_vp]),
+    "qcb_problem_eval_g": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, c_vp]),
+    "qcb_problem_eval_jac_g": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, c_vp]),
+    "qcb_problem_eval_h": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, ctypes.c_double, c_vp, c_vp]),
 }
 
 _lib = None

@@ -497,3 +497,95 @@ class Aux:
             self.close()
         except Exception:
             pass
+
+
+class Problem:
+    """One call per Ipopt callback (include/qcb200.h, qcb_problem_*): the integrators, the derivative and
+    timestep rows of an `Aux`, a terminal `Fidelity` with weight Q and the quadratic regularisers, laid out in
+    Ipopt's full-length vectors.  The pieces are borrowed: keep them alive, close the problem first.
+
+    integrators: `Evaluator`s owning the whole trajectory; fid_index: 0-based positions of the fidelity's
+    state entries inside the last knot; reg_terms: [(offset in knot, dim, R scalar or [dim])]."""
+
+    def __init__(self, N: int, z_dim: int, integrators=(), aux: Optional["Aux"] = None, derivative_rows: bool = False,
+                 dt_equal_rows: bool = False, fidelity: Optional["Fidelity"] = None, fid_index=None, Q: float = 100.0,
+                 fid_hessian: bool = True, reg_terms=(), min_time_D: float = 0.0):
+        self.lib = _lib.load()
+        self._keep = (list(integrators), aux, fidelity)
+        hs = (ctypes.c_void_p * max(1, len(integrators)))(*[ev.h for ev in integrators])
+        self._fid_index = None if fid_index is None else np.ascontiguousarray(fid_index, dtype=np.int32)
+        self._off, self._dim, self._R = Aux._terms(list(reg_terms))
+        ip = lambda a: a.ctypes.data_as(_lib.c_ip) if a is not None and len(a) else None
+        desc = _lib.QcbProblemDesc(
+            struct_bytes=ctypes.sizeof(_lib.QcbProblemDesc), N=N, z_dim=z_dim, n_integrators=len(integrators),
+            use_derivative_rows=int(bool(derivative_rows)), use_dt_equal_rows=int(bool(dt_equal_rows)),
+            fid_hessian=int(bool(fid_hessian)), n_reg=len(self._dim), Q=float(Q), min_time_D=float(min_time_D),
+            integrators=ctypes.cast(hs, ctypes.POINTER(ctypes.c_void_p)), aux=aux.h if aux is not None else None,
+            fidelity=fidelity.h if fidelity is not None else None, fid_index=ip(self._fid_index),
+            reg_off=ip(self._off), reg_dim=ip(self._dim),
+            reg_R=self._R.ctypes.data_as(_lib.c_dp) if len(self._R) else None)
+        h = ctypes.c_void_p()
+        st = self.lib.qcb_problem_create(ctypes.byref(h), ctypes.byref(desc))
+        if st != 0:
+            raise _lib.QcbError(st, self.lib.qcb_problem_last_error(None).decode())
+        self.h = h
+        d = [ctypes.c_int64(0) for _ in range(4)]
+        self.lib.qcb_problem_dims(h, *[ctypes.byref(x) for x in d])
+        self.n, self.m, self.jacobian_nnz, self.hessian_nnz = (int(x.value) for x in d)
+
+    def _check(self, st):
+        if st != 0:
+            raise _lib.QcbError(st, self.lib.qcb_problem_last_error(self.h).decode())
+
+    def jacobian_structure(self):
+        rows, cols = np.empty(self.jacobian_nnz, dtype=np.int64), np.empty(self.jacobian_nnz, dtype=np.int64)
+        self._check(self.lib.qcb_problem_jacobian_structure(self.h, rows.ctypes.data_as(_lib.c_lp), cols.ctypes.data_as(_lib.c_lp)))
+        return rows, cols
+
+    def hessian_structure(self):
+        rows, cols = np.empty(self.hessian_nnz, dtype=np.int64), np.empty(self.hessian_nnz, dtype=np.int64)
+        self._check(self.lib.qcb_problem_hessian_structure(self.h, rows.ctypes.data_as(_lib.c_lp), cols.ctypes.data_as(_lib.c_lp)))
+        return rows, cols
+
+    def eval_f(self, Z, new_x: bool = True) -> float:
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        f = ctypes.c_double(0.0)
+        self._check(self.lib.qcb_problem_eval_f(self.h, _ptr(Z), 1 if new_x else 0, ctypes.byref(f)))
+        return f.value
+
+    def eval_grad_f(self, Z, new_x: bool = True, out=None):
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        out = np.empty(self.n) if out is None else out
+        self._check(self.lib.qcb_problem_eval_grad_f(self.h, _ptr(Z), 1 if new_x else 0, _ptr(out)))
+        return out
+
+    def eval_g(self, Z, new_x: bool = True, out=None):
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        out = np.empty(self.m) if out is None else out
+        self._check(self.lib.qcb_problem_eval_g(self.h, _ptr(Z), 1 if new_x else 0, _ptr(out)))
+        return out
+
+    def eval_jac_g(self, Z, new_x: bool = True, out=None):
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        out = np.empty(self.jacobian_nnz) if out is None else out
+        self._check(self.lib.qcb_problem_eval_jac_g(self.h, _ptr(Z), 1 if new_x else 0, _ptr(out)))
+        return out
+
+    def eval_h(self, Z, obj_factor: float, lam, new_x: bool = True, out=None):
+        Z = np.ascontiguousarray(Z, dtype=np.float64)
+        lam = np.ascontiguousarray(lam, dtype=np.float64)
+        assert lam.size == self.m
+        out = np.empty(self.hessian_nnz) if out is None else out
+        self._check(self.lib.qcb_problem_eval_h(self.h, _ptr(Z), 1 if new_x else 0, float(obj_factor), _ptr(lam), _ptr(out)))
+        return out
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.qcb_problem_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

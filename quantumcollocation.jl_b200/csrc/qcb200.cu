@@ -2317,24 +2317,28 @@ qcb_status qcb_rollout(qcb_handle h, const double *Z, const double *x_init, doub
 
 int32_t qcb_host_threads(void) { return HostPool::get().size(); }
 
-qcb_status qcb_host_stream_fill(void *dst, size_t bytes, double *seconds) {
-    if (!dst || bytes < 8) return QCB_ERR_ARG;
+// out[0..n) = v by the host pool with streaming stores (2 MiB pieces, handed out dynamically)
+static void host_fill_pool(double *out, size_t n, double v) {
     static const bool has512 = __builtin_cpu_supports("avx512f");
-    double *out = static_cast<double *>(dst);
-    const size_t n = bytes / 8, piece = 1u << 18;     // 2 MiB pieces, handed out dynamically
+    const size_t piece = 1u << 18;
     std::atomic<size_t> next{0};
     std::function<void()> work = [&]() {
         for (;;) {
             const size_t b = next.fetch_add(piece);
             if (b >= n) break;
             const size_t len = std::min(piece, n - b);
-            if (has512) fill_run_avx512(out + b, 1.0, len);
-            else for (size_t i = 0; i < len; ++i) out[b + i] = 1.0;
+            if (has512) fill_run_avx512(out + b, v, len);
+            else for (size_t i = 0; i < len; ++i) out[b + i] = v;
         }
         if (has512) _mm_sfence();
     };
-    const auto t0 = std::chrono::steady_clock::now();
     HostPool::get().run(work);
+}
+
+qcb_status qcb_host_stream_fill(void *dst, size_t bytes, double *seconds) {
+    if (!dst || bytes < 8) return QCB_ERR_ARG;
+    const auto t0 = std::chrono::steady_clock::now();
+    host_fill_pool(static_cast<double *>(dst), bytes / 8, 1.0);
     if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     return QCB_OK;
 }
@@ -2361,6 +2365,7 @@ void qcb_host_free(void *ptr) { if (ptr) cudaFreeHost(ptr); }
 #include "qcb_fidelity.cuh"
 #include "qcb_aux.cuh"
 #include "qcb_global.cuh"
+#include "qcb_problem.cuh"
 
 // =========================================================================================
 // Allocation-free batched fidelity (declared in include/qcb200.h next to qcb_fidelity_eval)

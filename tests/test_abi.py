@@ -43,6 +43,29 @@ def test_descriptor_struct_matches_header():
     fields = re.findall(r"\b(\w+);", body)
     assert fields == [f[0] for f in _lib.QcbDesc._fields_]
     assert ctypes.sizeof(_lib.QcbDesc) == 14 * 4 + 5 * 8
+    body = re.search(r"typedef struct \{([^{}]*)\} qcb_problem_desc;", hdr, flags=re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    assert re.findall(r"\b(\w+);", body) == [f[0] for f in _lib.QcbProblemDesc._fields_]
+    assert ctypes.sizeof(_lib.QcbProblemDesc) == 8 * 4 + 2 * 8 + 7 * 8
+
+
+def test_problem_create_checks_its_pieces_without_a_gpu(built_libs):
+    """qcb_problem_create validates the descriptor before it touches any piece."""
+    lib = _lib.load()
+    h = ctypes.c_void_p()
+    d = _lib.QcbProblemDesc(struct_bytes=ctypes.sizeof(_lib.QcbProblemDesc), N=10, z_dim=12, use_derivative_rows=1)
+    assert lib.qcb_problem_create(ctypes.byref(h), ctypes.byref(d)) == 1 and not h.value
+    assert b"qcb_aux" in lib.qcb_problem_last_error(None)
+    d = _lib.QcbProblemDesc(struct_bytes=4, N=10, z_dim=12)
+    assert lib.qcb_problem_create(ctypes.byref(h), ctypes.byref(d)) == 1
+    assert b"struct_bytes" in lib.qcb_problem_last_error(None)
+    # an empty problem is legal: n = N * z_dim variables, no rows, no entries
+    d = _lib.QcbProblemDesc(struct_bytes=ctypes.sizeof(_lib.QcbProblemDesc), N=10, z_dim=12)
+    assert lib.qcb_problem_create(ctypes.byref(h), ctypes.byref(d)) == 0
+    dims = [ctypes.c_int64(-1) for _ in range(4)]
+    assert lib.qcb_problem_dims(h, *[ctypes.byref(x) for x in dims]) == 0
+    assert [x.value for x in dims] == [120, 0, 0, 0]
+    lib.qcb_problem_destroy(h)
 
 
 def test_create_rejects_bad_descriptors_and_has_no_cpu_fallback(built_libs):

@@ -55,7 +55,7 @@ def julia_ccalls():
 
 def c_class(t):
     t = t.replace("const ", "").strip()
-    if "*" in t or "[" in t or t.endswith("handle") or t in ("qcb_handle", "qcb_fidelity", "qcb_aux", "qcb_free_phase"):
+    if "*" in t or "[" in t or t.endswith("handle") or t in ("qcb_handle", "qcb_fidelity", "qcb_aux", "qcb_free_phase", "qcb_problem"):
         return "ptr"
     t = t.split()[0]
     return {"int32_t": "i32", "int64_t": "i64", "double": "f64", "size_t": "u64", "int": "i32", "qcb_status": "i32"}.get(t, t)
@@ -116,3 +116,12 @@ def _struct_fields(src, name, julia):
 def test_mirror_structs_have_the_header_fields():
     assert _struct_fields(JL, "QcbDesc", True) == _struct_fields(HDR, "qcb_desc", False)
     assert _struct_fields(JL, "QcbAuxDesc", True) == _struct_fields(HDR, "qcb_aux_desc", False)
+    assert _struct_fields(JL, "QcbProblemDesc", True) == _struct_fields(HDR, "qcb_problem_desc", False)
+
+
+def test_shim_binds_the_five_ipopt_callbacks():
+    names = {c[0] for c in julia_ccalls()}
+    for must in ("qcb_problem_create", "qcb_problem_destroy", "qcb_problem_dims", "qcb_problem_jacobian_structure",
+                 "qcb_problem_hessian_structure", "qcb_problem_eval_f", "qcb_problem_eval_grad_f", "qcb_problem_eval_g",
+                 "qcb_problem_eval_jac_g", "qcb_problem_eval_h", "qcb_problem_last_error"):
+        assert must in names, must
