@@ -441,10 +441,32 @@ def main():
             # huge-page eligible) memory when the library writes them with the host cores
             # (large-d path, compact transfer) -- which is also what Ipopt's own arrays are
             out_pinned = args.out_mem != "pageable"      # measured: pinned is faster on both routes
+            # the whole smooth-pulse problem behind one call per Ipopt callback (qcb_problem_*): integrator +
+            # derivative rows (u, du), (du, ddu) + timestep rows; terminal infidelity + regularisers on u, du, ddu.
+            # Its vectors are the integrator's plus a few thousand entries: the result buffers below are sized
+            # for it and shared with the plain e2e calls.
+            prob = prob_pieces = None
+            extra = (0, 0, 0)
+            if (not args.no_mix and out_pinned and L.S == 1 and w.kind == "unitary" and L.z_dim >= L.u_off + 3 * L.m
+                    and ev.defect_dim == n_delta):
+                try:
+                    from qcb200 import Aux, Fidelity, Problem
+                    m_ = L.m
+                    aux_p = Aux(L.N, L.z_dim, L.dt_off, derivatives=[(L.u_off, L.u_off + m_, m_), (L.u_off + m_, L.u_off + 2 * m_, m_)],
+                                device=local)
+                    fid_p = Fidelity(Fidelity.UNITARY, w.U_goal if w.U_goal is not None else np.eye(L.c, dtype=complex), device=local)
+                    prob = Problem(L.N, L.z_dim, [ev], aux_p, derivative_rows=True, dt_equal_rows=True, fidelity=fid_p,
+                                   fid_index=np.arange(L.x_off[0], L.x_off[0] + L.x_dim), Q=100.0,
+                                   fid_hessian=L.x_dim <= 1024, reg_terms=[(L.u_off + i * m_, m_, 1e-2) for i in range(3)])
+                    prob_pieces = (aux_p, fid_p)
+                    extra = (prob.m - n_delta, prob.jacobian_nnz - n_jac, prob.hessian_nnz - n_hess)
+                except Exception as exc:
+                    prob = None
+                    print(f"# problem-level callbacks not measured: {exc}", file=sys.stderr)
             if out_pinned:
-                h_delta = torch.empty(n_delta, dtype=torch.float64, pin_memory=True)
-                h_jac = torch.empty(n_jac, dtype=torch.float64, pin_memory=True)
-                h_hess = torch.empty(n_hess, dtype=torch.float64, pin_memory=True)
+                h_delta = torch.empty(n_delta + extra[0], dtype=torch.float64, pin_memory=True)
+                h_jac = torch.empty(n_jac + extra[1], dtype=torch.float64, pin_memory=True)
+                h_hess = torch.empty(n_hess + extra[2], dtype=torch.float64, pin_memory=True)
             else:
                 h_delta = torch.from_numpy(np.zeros(n_delta))
                 h_jac = torch.from_numpy(np.zeros(n_jac))
@@ -559,6 +581,40 @@ def main():
                             "what": "host buffers, wall clock, new_x = 1 / 0 / 0 (qcb_eval_defect_x, _jacobian_x, _hessian_x)"}
             except Exception as exc:
                 host_mix = {"note": f"not measured: {exc}"[:200]}
+        # the five Ipopt callbacks of the whole problem, one C call each, in Ipopt's order on one iterate
+        problem_mix = None
+        if world == 1 and prob is not None:
+            try:
+                lam = torch.zeros(prob.m, dtype=torch.float64, pin_memory=True)
+                lam[:n_delta] = hmu
+                lam[n_delta:] = 0.5
+                grad = np.empty(prob.n)
+                import ctypes
+                lib = qcb200.load_library()
+                fval = ctypes.c_double(0.0)
+                acc = [0.0] * 5
+                for it in range(3):
+                    t = [time.perf_counter()]
+                    lib.qcb_problem_eval_f(prob.h, pZ, 1, ctypes.byref(fval)); t.append(time.perf_counter())
+                    lib.qcb_problem_eval_grad_f(prob.h, pZ, 0, grad.ctypes.data); t.append(time.perf_counter())
+                    lib.qcb_problem_eval_g(prob.h, pZ, 0, p_delta); t.append(time.perf_counter())
+                    lib.qcb_problem_eval_jac_g(prob.h, pZ, 0, p_jac); t.append(time.perf_counter())
+                    lib.qcb_problem_eval_h(prob.h, pZ, 0, 1.0, lam.data_ptr(), p_hess); t.append(time.perf_counter())
+                    if it:
+                        acc = [a + 1e3 * (t[q + 1] - t[q]) / 2 for q, a in enumerate(acc)]
+                problem_mix = {"eval_f_ms": acc[0], "eval_grad_f_ms": acc[1], "eval_g_ms": acc[2], "eval_jac_g_ms": acc[3],
+                               "eval_h_ms": acc[4],
+                               "ms_per_ipopt_iteration": (55 * acc[0] + 51 * acc[1] + 55 * acc[2] + 51 * acc[3] + 50 * acc[4]) / 50.0,
+                               "n": prob.n, "m": prob.m, "nnz_jac": prob.jacobian_nnz, "nnz_hess": prob.hessian_nnz,
+                               "what": "qcb_problem_eval_f / _grad_f / _g / _jac_g / _h: integrator + derivative rows + timestep "
+                                       "rows, terminal infidelity + regularisers on u, du, ddu; host buffers, wall clock, "
+                                       "new_x = 1 on eval_f and 0 after; mix 55 f : 51 grad f : 55 g : 51 jac : 50 hess per 50 "
+                                       "iterations (docs/literate/examples/multilevel_transmon.jl:147-153)"}
+                prob.close()
+                for p_ in prob_pieces:
+                    p_.close()
+            except Exception as exc:
+                problem_mix = {"note": f"not measured: {exc}"[:200]}
         e2e = {"value": units_total / (dt / args.steps), "unit": "knot-evals/s", "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "host_result_bytes_per_step": int(host_written),
                "result_buffers": ("shared pinned" if world > 1 else ("pinned" if out_pinned else "pageable")),
@@ -566,6 +622,8 @@ def main():
                "last_call_rank0_ms": tm}
         if host_mix:
             e2e["callback_mix_host"] = host_mix
+        if problem_mix:
+            e2e["problem_callbacks"] = problem_mix
         if host_gbs:
             e2e["host_threads"] = int(qcb200.load_library().qcb_host_threads())
             e2e["host_write_gbs"] = host_gbs

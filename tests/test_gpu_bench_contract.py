@@ -37,6 +37,9 @@ def test_bench_line_has_the_contract_keys(built_libs):
     assert c["kind"] == "port" and c["cores"] >= 1 and c["value"] > 0 and "sample" in c
     m = d["callback_mix"]
     assert m["evaluator_ms_per_ipopt_iteration"] < m["evaluator_ms_per_ipopt_iteration_recomputing"]
+    p = e["problem_callbacks"]              # the five Ipopt callbacks of the whole problem, one C call each
+    assert "note" not in p, p
+    assert p["m"] == 100 * 8192 + 100 * 24 + 100 and p["nnz_jac"] > 100 * 8192 and p["ms_per_ipopt_iteration"] > 0
 
 
 def test_reference_arm_line(built_libs):
