@@ -245,6 +245,13 @@ void qcb_host_unregister(void *ptr);
  * streaming stores on the same pool and reports the wall time -- the measured host-write roofline
  * that bench.py prints beside the end-to-end number. */
 int32_t qcb_host_threads(void);
+/* Host-buffer calls on the large-d path that deliver the Jacobian are bound by the host: its cores' streaming
+ * stores and the PCIe writes beside them share one memory system, and on some hosts fewer store threads give a
+ * faster call.  Each handle therefore times its own calls: one settling call, two calls each with all pool
+ * threads, 3/4, 1/2 and 3/8 of them, then the fastest stays (fewer threads only for a gain of at least 3 %); calls
+ * with and without the Hessian are tuned separately.  QCB_HOST_TUNE=0 or an explicit QCB_HOST_THREADS turns
+ * this off.  Returns the number of threads in use for that kind of call (the pool size until decided). */
+int32_t qcb_host_threads_in_use(qcb_handle h, int32_t with_hessian);
 qcb_status qcb_host_stream_fill(void *dst, size_t bytes, double *seconds);
 
 /* Number of kernels this handle has launched since creation, and per-phase timings of the

@@ -111,6 +111,7 @@ SYMBOLS = {
     "qcb_aux_sensitivity_eval": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                                 c_ip, c_vp, ctypes.c_double, c_dp, c_vp, c_vp]),
     "qcb_fidelity_eval_batch_device_noalloc": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int64, c_vp, c_vp]),
+    "qcb_host_threads_in_use": (ctypes.c_int32, [c_vp, ctypes.c_int32]),
     "qcb_problem_create": (ctypes.c_int, [ctypes.POINTER(c_vp), ctypes.POINTER(QcbProblemDesc)]),
     "qcb_problem_destroy": (None, [c_vp]),
     "qcb_problem_last_error": (ctypes.c_char_p, [c_vp]),

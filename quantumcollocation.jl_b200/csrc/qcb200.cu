@@ -51,6 +51,37 @@ struct Seg { int64_t dst; uint32_t src; uint32_t len; uint32_t kind; };   // kin
 
 inline int round_up(int v, int q) { return (v + q - 1) / q * q; }
 
+// Chooses the number of host threads that expand the arenas for one kind of host-buffer call on the large-d
+// path by timing the calls themselves: one settling call, then two calls with each candidate (all pool threads,
+// 3/4, 1/2 and 3/8 of them), then the fastest stays -- fewer threads only if that is at least 3 % faster.
+// Why it can pay: the cores' streaming stores and the PCIe writes share the host's DRAM write bandwidth
+// (scratch/dma_under_stores.py: D2H 57 GB/s alone, 32 GB/s beside 8 or 16 store threads, 44 GB/s beside 4), and
+// a fused call needs both to finish.
+struct HostTuner {
+    static constexpr int NC = 4;
+    int calls = 0, chosen = 0;
+    double best[NC] = {1e30, 1e30, 1e30, 1e30};
+    static int candidate(int pool, int i) {
+        const int num[NC] = {8, 6, 4, 3};
+        return i == 0 ? pool : std::max(2, pool * num[i] / 8);
+    }
+    int next(int pool) const {
+        if (chosen) return chosen;
+        if (pool < 8 || calls == 0) return pool;
+        return candidate(pool, ((calls - 1) / 2) % NC);
+    }
+    void record(int pool, double ms) {
+        if (chosen) return;
+        if (pool < 8) { chosen = pool; return; }
+        if (calls > 0) { const int i = ((calls - 1) / 2) % NC; best[i] = std::min(best[i], ms); }
+        if (++calls == 1 + 2 * NC) {
+            int b = 0;
+            for (int i = 1; i < NC; ++i) if (best[i] < 0.97 * best[0] && best[i] < best[b]) b = i;
+            chosen = candidate(pool, b);
+        }
+    }
+};
+
 }  // namespace
 
 struct qcb_handle_s {
@@ -146,6 +177,7 @@ struct qcb_handle_s {
     int cache_s_slab = -1;
     int reuse = 0;                 // set by the *_x entry points for the call in flight
     bool dZ_valid = false;         // the staged device copy of Z is the one the last host-buffer call uploaded
+    HostTuner tune[2];             // expansion threads of host-buffer calls that deliver the Jacobian: [0] without, [1] with the Hessian
 
     // arena delivery (qcb_eval_arenas_device): where the per-unit value arenas of the slab are written
     // instead of being assembled into COO vectors here; may be another GPU's memory
@@ -341,6 +373,13 @@ __attribute__((target("avx512f"))) void fill_run_avx512(double *dst, double v, s
 // Workers are pinned one per core, rank r taking the r-th block of the allowed cores, so that the
 // ranks' streaming stores do not migrate between cores (QCB_HOST_PIN=0 disables pinning).
 // run() is serialised by a mutex: handles driven from different host threads take turns.
+// Index of the calling thread inside the pool (0: the caller of run()/start(), i.e. any non-pool thread) and the
+// number of pool threads an expansion job may use (0: all).  The limit exists because on some hosts the PCIe
+// writes that run beside the expansion get starved by sixteen cores of streaming stores, and the whole call is
+// faster with fewer store threads; it is chosen per handle by measurement (HostTuner).
+thread_local int tl_pool_id = 0;
+std::atomic<int> g_expand_limit{0};
+
 class HostPool {
 public:
     static HostPool &get() { static HostPool p; return p; }
@@ -386,7 +425,7 @@ private:
         const bool pin = !(pin_env && atoi(pin_env) == 0) && (int)cores.size() >= n;
         const int first = (int)(((long long)rank * n) % (long long)cores.size());
         for (int i = 1; i < n; ++i) {
-            workers_.emplace_back([this] { loop(); });
+            workers_.emplace_back([this, i] { tl_pool_id = i; loop(); });
             if (pin) {
                 cpu_set_t one;
                 CPU_ZERO(&one);
@@ -445,6 +484,8 @@ struct ExpandTask {
     ExpandTask() {
         work = [this]() {
             static const bool has512 = __builtin_cpu_supports("avx512f");
+            const int limit = g_expand_limit.load(std::memory_order_relaxed);
+            if (limit > 0 && tl_pool_id >= limit) return;
             const int total = nu * njobs;
             for (;;) {
                 const int w = next.fetch_add(1);
@@ -2200,6 +2241,12 @@ qcb_status qcb_eval_all_x(qcb_handle h, const double *Z, const double *mu, int32
         CK(cudaEventRecord(h->ev[1], h->stream));
         HostOut ho{delta, jac, hess, compact};
         int want = (jac ? 1 : 0) | (hess ? 2 : 0);
+        // calls that deliver the Jacobian are bound by the host side: pick their store-thread count by measurement
+        static const bool tune_on = !getenv("QCB_HOST_THREADS") && !(getenv("QCB_HOST_TUNE") && atoi(getenv("QCB_HOST_TUNE")) == 0);
+        HostTuner *tn = (tune_on && h->large && compact && jac) ? &h->tune[hess ? 1 : 0] : nullptr;
+        const int pool = tn ? HostPool::get().size() : 0;
+        if (tn) { const int t = tn->next(pool); g_expand_limit.store(t >= pool ? 0 : t); }
+        const auto wall0 = std::chrono::steady_clock::now();
         // in compact mode no device COO buffer exists (the arenas travel instead): `want` alone says
         // what is evaluated
         qcb_status st = eval_device(h, *dZ_in, hess ? h->dmu : nullptr, h->d_delta,
@@ -2207,6 +2254,10 @@ qcb_status qcb_eval_all_x(qcb_handle h, const double *Z, const double *mu, int32
                                     want, &ho);
         CK(cudaEventRecord(h->ev[2], h->stream));
         CK(cudaEventSynchronize(h->ev[2]));
+        if (tn) {
+            g_expand_limit.store(0);
+            if (st == QCB_OK) tn->record(pool, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count());
+        }
         float a = 0, b = 0;
         cudaEventElapsedTime(&a, h->ev[0], h->ev[1]);
         cudaEventElapsedTime(&b, h->ev[1], h->ev[2]);
@@ -2216,6 +2267,7 @@ qcb_status qcb_eval_all_x(qcb_handle h, const double *Z, const double *mu, int32
         return st;
     } catch (const CudaFail &f) {
         h->reuse = 0;
+        g_expand_limit.store(0);
         return fail_cuda(h, f);
     }
 }
@@ -2316,6 +2368,11 @@ qcb_status qcb_rollout(qcb_handle h, const double *Z, const double *x_init, doub
 }
 
 int32_t qcb_host_threads(void) { return HostPool::get().size(); }
+int32_t qcb_host_threads_in_use(qcb_handle h, int32_t with_hessian) {
+    if (!h) return 0;
+    const HostTuner &t = h->tune[with_hessian ? 1 : 0];
+    return t.chosen ? t.chosen : HostPool::get().size();
+}
 
 // out[0..n) = v by the host pool with streaming stores (2 MiB pieces, handed out dynamically)
 static void host_fill_pool(double *out, size_t n, double v) {

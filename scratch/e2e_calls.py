@@ -34,7 +34,8 @@ def calls(n, what):
     print(tag, what, " ".join(f"{t:.1f}" for t in out), flush=True)
 
 
-calls(8, "fresh:")
+calls(16, "fresh:")
+print(tag, "threads in use (fused, jac only):", lib.qcb_host_threads_in_use(ev.h, 1), lib.qcb_host_threads_in_use(ev.h, 0), "of", lib.qcb_host_threads(), flush=True)
 if os.environ.get("E2E_QUICK"):
     print(tag, "timings", ev.timings(), flush=True)
     sys.exit(0)

@@ -770,3 +770,21 @@ def test_new_x_reuse_through_the_host_buffer_calls(built_libs):
     ev.eval_all_x(Z2, None, False, jac=j)                             # promise cannot be honoured: recompute
     assert np.array_equal(j, fj)
     ev.close(); fresh.close()
+
+
+def test_host_thread_choice_settles_and_does_not_change_results(built_libs):
+    """Large-d host-buffer calls time themselves over their first nine calls and keep the fastest number of
+    expansion threads (qcb_host_threads_in_use): every call of the exploration returns the same bits."""
+    w = workloads.make("cfg5", N=4)
+    ev = Evaluator(w.layout, w.G_drift, w.G_drives)
+    lib = qcb200.load_library()
+    pool = lib.qcb_host_threads()
+    assert lib.qcb_host_threads_in_use(ev.h, 1) == pool
+    ref = ev.eval_all(w.Z, w.mu)
+    for _ in range(9):
+        out = ev.eval_all(w.Z, w.mu)
+        assert all(np.array_equal(a, b) for a, b in zip(out, ref))
+    allowed = {pool} if pool < 8 else {pool, max(2, pool * 6 // 8), max(2, pool * 4 // 8), max(2, pool * 3 // 8)}
+    assert lib.qcb_host_threads_in_use(ev.h, 1) in allowed
+    assert lib.qcb_host_threads_in_use(ev.h, 0) == pool          # no Jacobian-only call has been made
+    ev.close()
