@@ -433,12 +433,12 @@ qcb_status qcb_aux_sensitivity_eval(qcb_aux a, const double *Z, int32_t x_off, i
  * (derivative rows, dt_t - dt_N rows, regularisers, minimum-time term) and one qcb_fidelity for
  *     f(Z) = Q |1 - F(x_N)| + sum_terms 1/2 sum_t sum_i R_i (dt_t v_{t,i})^2 + D sum_{t<N} dt_t .
  * Variables: Z, n = N * z_dim.  Constraint rows, in this order: every integrator's defect rows, the
- * derivative rows, the N-1 timestep rows (m in total).  Each callback below is ONE call that writes
+ * derivative rows, the N-1 timestep rows, the leakage rows (m in total).  Each callback below is ONE call that writes
  * the caller's full-length array; new_x is Ipopt's flag, passed through unchanged: the problem
  * remembers which integrators have not yet seen the current iterate, so that
  * eval_f(new_x = 1) -> eval_g(0) -> eval_jac_g(0) -> eval_h(0) uploads Z once per integrator and reuses
  * the propagators and tangents between the three constraint callbacks (qcb_eval_*_x).
- * Inequality rows (leakage constraint) and free-phase / sensitivity objectives stay separate calls. */
+ * Free-phase and sensitivity objectives stay separate calls. */
 typedef struct qcb_problem_s *qcb_problem;
 typedef struct {
     int32_t struct_bytes;           /* sizeof(qcb_problem_desc) */
@@ -450,8 +450,15 @@ typedef struct {
     int32_t fid_hessian;            /* 1: dense upper-triangle Hessian block of the terminal term on x_N
                                        (x_dim <= 8192); 0: left out (limited-memory runs, large states) */
     int32_t n_reg;                  /* regulariser terms */
+    int32_t use_leakage_rows;       /* 1: append the N * n_leak inequality rows x_t[i]^2 - leak_value <= 0 of aux's
+                                       leakage indices (LeakageConstraint, src/quantum_constraints.jl:156-172); the
+                                       caller gives Ipopt g_U = 0, g_L = -inf for them */
+    int32_t use_leakage_objective;  /* 1: add leak_Q * sum_t sum_i x_t[i]^2 / n_leak (LeakageObjective,
+                                       src/quantum_objectives.jl:291-307) */
     double Q;                       /* weight of the terminal infidelity */
     double min_time_D;              /* weight of sum dt (0: none) */
+    double leak_Q;                  /* weight of the leakage objective */
+    double leak_value;              /* bound of the leakage rows */
     const qcb_handle *integrators;  /* [n_integrators] */
     qcb_aux aux;                    /* may be NULL when nothing of it is used */
     qcb_fidelity fidelity;          /* may be NULL: no terminal term */

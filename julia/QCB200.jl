@@ -353,7 +353,8 @@ end
 struct QcbProblemDesc               # mirrors qcb_problem_desc
     struct_bytes::Int32; N::Int32; z_dim::Int32; n_integrators::Int32
     use_derivative_rows::Int32; use_dt_equal_rows::Int32; fid_hessian::Int32; n_reg::Int32
-    Q::Float64; min_time_D::Float64
+    use_leakage_rows::Int32; use_leakage_objective::Int32
+    Q::Float64; min_time_D::Float64; leak_Q::Float64; leak_value::Float64
     integrators::Ptr{Ptr{Cvoid}}; aux::Ptr{Cvoid}; fidelity::Ptr{Cvoid}
     fid_index::Ptr{Int32}; reg_off::Ptr{Int32}; reg_dim::Ptr{Int32}; reg_R::Ptr{Float64}
 end
@@ -375,7 +376,8 @@ function B200Problem(traj::NamedTrajectory, integrators::Vector{B200BilinearInte
                      derivative_rows::Bool = false, dt_equal_rows::Bool = false,
                      fidelity::Union{Nothing,B200Fidelity} = nothing, state_name::Union{Nothing,Symbol} = nothing,
                      Q::Float64 = 100.0, fid_hessian::Bool = true, reg_names::Vector{Symbol} = Symbol[],
-                     reg_R::Vector{Float64} = Float64[], D::Float64 = 0.0)
+                     reg_R::Vector{Float64} = Float64[], D::Float64 = 0.0, leakage_rows::Bool = false,
+                     leakage_value::Float64 = 0.0, leakage_Q::Union{Nothing,Float64} = nothing)
     hs = Ptr{Cvoid}[i.handle for i in integrators]
     fidx = isnothing(state_name) ? Int32[] : Int32.(traj.components[state_name] .- 1)
     off = Int32[traj.components[n][1] - 1 for n in reg_names]
@@ -384,7 +386,8 @@ function B200Problem(traj::NamedTrajectory, integrators::Vector{B200BilinearInte
     h = Ref{Ptr{Cvoid}}(C_NULL)
     GC.@preserve hs fidx off dim R begin
         desc = QcbProblemDesc(Int32(sizeof(QcbProblemDesc)), traj.N, traj.dim, length(hs), derivative_rows, dt_equal_rows,
-                              fid_hessian, length(dim), Q, D, pointer(hs), aux,
+                              fid_hessian, length(dim), leakage_rows, !isnothing(leakage_Q), Q, D,
+                              isnothing(leakage_Q) ? 0.0 : leakage_Q, leakage_value, pointer(hs), aux,
                               isnothing(fidelity) ? C_NULL : fidelity.handle,
                               isempty(fidx) ? C_NULL : pointer(fidx), isempty(off) ? C_NULL : pointer(off),
                               isempty(dim) ? C_NULL : pointer(dim), isempty(R) ? C_NULL : pointer(R))

@@ -505,11 +505,13 @@ class Problem:
     Ipopt's full-length vectors.  The pieces are borrowed: keep them alive, close the problem first.
 
     integrators: `Evaluator`s owning the whole trajectory; fid_index: 0-based positions of the fidelity's
-    state entries inside the last knot; reg_terms: [(offset in knot, dim, R scalar or [dim])]."""
+    state entries inside the last knot; reg_terms: [(offset in knot, dim, R scalar or [dim])]; leakage_rows /
+    leakage_Q: the inequality rows x^2 - leakage_value <= 0 and the objective term of `aux`'s leakage indices."""
 
     def __init__(self, N: int, z_dim: int, integrators=(), aux: Optional["Aux"] = None, derivative_rows: bool = False,
                  dt_equal_rows: bool = False, fidelity: Optional["Fidelity"] = None, fid_index=None, Q: float = 100.0,
-                 fid_hessian: bool = True, reg_terms=(), min_time_D: float = 0.0):
+                 fid_hessian: bool = True, reg_terms=(), min_time_D: float = 0.0, leakage_rows: bool = False,
+                 leakage_value: float = 0.0, leakage_Q: Optional[float] = None):
         self.lib = _lib.load()
         self._keep = (list(integrators), aux, fidelity)
         hs = (ctypes.c_void_p * max(1, len(integrators)))(*[ev.h for ev in integrators])
@@ -520,6 +522,8 @@ class Problem:
             struct_bytes=ctypes.sizeof(_lib.QcbProblemDesc), N=N, z_dim=z_dim, n_integrators=len(integrators),
             use_derivative_rows=int(bool(derivative_rows)), use_dt_equal_rows=int(bool(dt_equal_rows)),
             fid_hessian=int(bool(fid_hessian)), n_reg=len(self._dim), Q=float(Q), min_time_D=float(min_time_D),
+            use_leakage_rows=int(bool(leakage_rows)), use_leakage_objective=int(leakage_Q is not None),
+            leak_Q=float(leakage_Q or 0.0), leak_value=float(leakage_value),
             integrators=ctypes.cast(hs, ctypes.POINTER(ctypes.c_void_p)), aux=aux.h if aux is not None else None,
             fidelity=fidelity.h if fidelity is not None else None, fid_index=ip(self._fid_index),
             reg_off=ip(self._off), reg_dim=ip(self._dim),

@@ -31,6 +31,11 @@ struct qcb_problem_s {
     int64_t d_row0 = 0, d_jac0 = 0, d_hes0 = 0, d_rows = 0;
     int64_t t_row0 = 0, t_jac0 = 0, t_rows = 0;
     int64_t f_hes0 = 0, f_hes_n = 0, r_hes0 = 0, r_hes_n = 0, r_rows = 0;
+    // leakage (qcb_aux_leakage_eval): inequality rows x^2 - value <= 0 and / or the objective term leak_Q sum x^2 / n_leak
+    bool leak_rows = false, leak_obj = false;
+    double leak_Q = 0.0, leak_value = 0.0;
+    int64_t l_n = 0, l_row0 = 0, l_jac0 = 0, l_hes0 = 0, lo_hes0 = 0;
+    std::vector<double> lbuf;                // [3][l_n]: gradient values | constraint values or Jacobian | Hessian diagonal
     std::vector<int64_t> reg_cols;           // 1-based columns of the compact regulariser gradient
     std::vector<char> stale;                 // integrator i has not seen the current Z yet
     std::vector<double> xN, gF, HF, rg, rh;
@@ -81,7 +86,8 @@ qcb_status qcb_problem_create(qcb_problem *out, const qcb_problem_desc *d) {
         p->m += qcb_defect_dim(h); p->nnz_j += qcb_jacobian_nnz(h); p->nnz_h += qcb_hessian_nnz(h);
     }
     p->stale.assign(p->integ.size(), 1);
-    const bool want_aux = d->use_derivative_rows || d->use_dt_equal_rows || d->n_reg > 0 || d->min_time_D != 0.0;
+    const bool want_aux = d->use_derivative_rows || d->use_dt_equal_rows || d->n_reg > 0 || d->min_time_D != 0.0 ||
+                          d->use_leakage_rows || d->use_leakage_objective;
     if (want_aux) {
         if (!d->aux) return pfail(nullptr, QCB_ERR_ARG, "derivative rows, timestep rows and regularisers need a qcb_aux");
         if (d->aux->N != d->N || d->aux->z_dim != d->z_dim) return pfail(nullptr, QCB_ERR_ARG, "qcb_aux built for another trajectory shape");
@@ -98,6 +104,21 @@ qcb_status qcb_problem_create(qcb_problem *out, const qcb_problem_desc *d) {
         p->t_rows = d->N - 1;
         p->t_row0 = p->m; p->t_jac0 = p->nnz_j;
         p->m += p->t_rows; p->nnz_j += 2 * p->t_rows;
+    }
+    if (d->use_leakage_rows || d->use_leakage_objective) {
+        if (!d->aux || qcb_aux_leakage_dim(d->aux) == 0) return pfail(nullptr, QCB_ERR_ARG, "leakage terms need a qcb_aux created with leakage indices");
+        p->aux = d->aux;
+        p->l_n = qcb_aux_leakage_dim(p->aux);
+        p->lbuf.resize((size_t)3 * p->l_n);
+        if (d->use_leakage_rows) {
+            p->leak_rows = true; p->leak_value = d->leak_value;
+            p->l_row0 = p->m; p->l_jac0 = p->nnz_j; p->l_hes0 = p->nnz_h;
+            p->m += p->l_n; p->nnz_j += p->l_n; p->nnz_h += p->l_n;
+        }
+        if (d->use_leakage_objective) {
+            p->leak_obj = true; p->leak_Q = d->leak_Q;
+            p->lo_hes0 = p->nnz_h; p->nnz_h += p->l_n;
+        }
     }
     if (d->fidelity) {
         p->fid = d->fidelity;
@@ -168,6 +189,13 @@ qcb_status qcb_problem_jacobian_structure(qcb_problem p, int64_t *rows, int64_t 
         qcb_status st = qcb_aux_timesteps_equal(p->aux, nullptr, p->t_row0, nullptr, rows + p->t_jac0, cols + p->t_jac0, nullptr);
         if (st != QCB_OK) return pstep(p, st, "timestep rows", p->aux->err);
     }
+    if (p->leak_rows) {
+        const int nl = p->aux->n_leak;
+        for (int64_t e = 0; e < p->l_n; ++e) {
+            rows[p->l_jac0 + e] = p->l_row0 + e + 1;
+            cols[p->l_jac0 + e] = (e / nl) * p->z_dim + p->aux->leak[(size_t)(e % nl)] + 1;
+        }
+    }
     return QCB_OK;
 }
 
@@ -180,6 +208,14 @@ qcb_status qcb_problem_hessian_structure(qcb_problem p, int64_t *rows, int64_t *
     if (p->deriv_rows) {
         qcb_status st = qcb_aux_derivative_structure(p->aux, 0, nullptr, nullptr, rows + p->d_hes0, cols + p->d_hes0);
         if (st != QCB_OK) return pstep(p, st, "derivative rows", p->aux->err);
+    }
+    if (p->leak_rows || p->leak_obj) {
+        const int nl = p->aux->n_leak;
+        for (int64_t e = 0; e < p->l_n; ++e) {
+            const int64_t c = (e / nl) * p->z_dim + p->aux->leak[(size_t)(e % nl)] + 1;
+            if (p->leak_rows) { rows[p->l_hes0 + e] = c; cols[p->l_hes0 + e] = c; }
+            if (p->leak_obj) { rows[p->lo_hes0 + e] = c; cols[p->lo_hes0 + e] = c; }
+        }
     }
     if (p->fid_hess) {
         const int64_t xd = (int64_t)p->fid_pos.size();
@@ -217,6 +253,12 @@ qcb_status qcb_problem_eval_f(qcb_problem p, const double *Z, int32_t new_x, dou
         if (st != QCB_OK) return pstep(p, st, "regularisers", p->aux->err);
         v += J;
     }
+    if (p->leak_obj) {
+        double J = 0.0;
+        qcb_status st = qcb_aux_leakage_eval(p->aux, Z, nullptr, 0.0, nullptr, &J, nullptr, nullptr, nullptr, nullptr);
+        if (st != QCB_OK) return pstep(p, st, "leakage objective", p->aux->err);
+        v += p->leak_Q * J;
+    }
     *f = v;
     return QCB_OK;
 }
@@ -240,6 +282,12 @@ qcb_status qcb_problem_eval_grad_f(qcb_problem p, const double *Z, int32_t new_x
         if (st != QCB_OK) return pstep(p, st, "regularisers", p->aux->err);
         for (size_t e = 0; e < p->rg.size(); ++e) grad[p->reg_cols[e] - 1] += p->rg[e];
     }
+    if (p->leak_obj) {
+        qcb_status st = qcb_aux_leakage_eval(p->aux, Z, nullptr, 0.0, nullptr, nullptr, p->lbuf.data(), nullptr, nullptr, nullptr);
+        if (st != QCB_OK) return pstep(p, st, "leakage objective", p->aux->err);
+        const int nl = p->aux->n_leak;
+        for (int64_t e = 0; e < p->l_n; ++e) grad[(e / nl) * p->z_dim + p->aux->leak[(size_t)(e % nl)]] += p->leak_Q * p->lbuf[(size_t)e];
+    }
     return QCB_OK;
 }
 
@@ -259,6 +307,10 @@ qcb_status qcb_problem_eval_g(qcb_problem p, const double *Z, int32_t new_x, dou
     if (p->dt_rows) {
         qcb_status st = qcb_aux_timesteps_equal(p->aux, Z, 0, g + p->t_row0, nullptr, nullptr, nullptr);
         if (st != QCB_OK) return pstep(p, st, "timestep rows", p->aux->err);
+    }
+    if (p->leak_rows) {
+        qcb_status st = qcb_aux_leakage_eval(p->aux, Z, nullptr, p->leak_value, nullptr, nullptr, nullptr, g + p->l_row0, nullptr, nullptr);
+        if (st != QCB_OK) return pstep(p, st, "leakage rows", p->aux->err);
     }
     return QCB_OK;
 }
@@ -280,6 +332,10 @@ qcb_status qcb_problem_eval_jac_g(qcb_problem p, const double *Z, int32_t new_x,
         qcb_status st = qcb_aux_timesteps_equal(p->aux, Z, 0, nullptr, nullptr, nullptr, vals + p->t_jac0);
         if (st != QCB_OK) return pstep(p, st, "timestep rows", p->aux->err);
     }
+    if (p->leak_rows) {
+        qcb_status st = qcb_aux_leakage_eval(p->aux, Z, nullptr, p->leak_value, nullptr, nullptr, nullptr, nullptr, vals + p->l_jac0, nullptr);
+        if (st != QCB_OK) return pstep(p, st, "leakage rows", p->aux->err);
+    }
     return QCB_OK;
 }
 
@@ -297,6 +353,15 @@ qcb_status qcb_problem_eval_h(qcb_problem p, const double *Z, int32_t new_x, dou
     if (p->deriv_rows && p->d_rows) {
         qcb_status st = qcb_aux_derivative_eval(p->aux, Z, lambda + p->d_row0, nullptr, nullptr, vals + p->d_hes0);
         if (st != QCB_OK) return pstep(p, st, "derivative rows", p->aux->err);
+    }
+    if (p->leak_rows) {
+        qcb_status st = qcb_aux_leakage_eval(p->aux, Z, nullptr, p->leak_value, lambda + p->l_row0, nullptr, nullptr, nullptr, nullptr,
+                                             vals + p->l_hes0);
+        if (st != QCB_OK) return pstep(p, st, "leakage rows", p->aux->err);
+    }
+    if (p->leak_obj) {          // Hessian of leak_Q sum_t sum_i x^2 / n_leak: the constant diagonal 2 leak_Q / n_leak
+        const double v = obj_factor * 2.0 * p->leak_Q / p->aux->n_leak;
+        for (int64_t e = 0; e < p->l_n; ++e) vals[p->lo_hes0 + e] = v;
     }
     if (p->fid_hess) {
         qcb_status st;

@@ -217,3 +217,50 @@ def test_problem_on_the_large_path_reuses_the_integrator_state(built_libs):
     prob.close()
     for p in (ev, ev_ref, aux, fid):
         p.close()
+
+
+def test_problem_with_leakage_rows_and_objective(built_libs):
+    """LeakageConstraint rows (x^2 - value <= 0) and the LeakageObjective term of a 3-level transmon inside the
+    composite: values against the oracle, derivatives against central differences of the composite itself."""
+    w, L, Z, U_goal, pairs, terms, rng = _case(N=5, seed=21)
+    U = np.arange(18).reshape(3, 6).T                     # column-major (6 x 3) index map of the iso-vec
+    idx = sorted(set(U[[2, 5], :].reshape(-1)) | set(U[:, 2]))
+    ev = Evaluator(L, w.G_drift, w.G_drives)
+    aux = Aux(L.N, L.z_dim, L.dt_off, derivatives=pairs, leak_x_off=L.x_off[0], leak_idx=idx)
+    fid = Fidelity(Fidelity.UNITARY, U_goal)
+    base = dict(derivative_rows=True, dt_equal_rows=True, fidelity=fid, fid_index=np.arange(L.x_off[0], L.x_off[0] + L.x_dim),
+                Q=100.0, reg_terms=terms)
+    plain = Problem(L.N, L.z_dim, [ev], aux, **base)
+    prob = Problem(L.N, L.z_dim, [ev], aux, leakage_rows=True, leakage_value=1e-2, leakage_Q=3.0, **base)
+    nl = L.N * len(idx)
+    assert (prob.m, prob.jacobian_nnz, prob.hessian_nnz) == (plain.m + nl, plain.jacobian_nnz + nl, plain.hessian_nnz + 2 * nl)
+    obj0, grad0, con0, cjac0, _ = O.leakage(Z, L.N, L.z_dim, L.x_off[0], idx, None, 1e-2, None)
+    assert abs(prob.eval_f(Z) - (plain.eval_f(Z) + 3.0 * obj0)) < 1e-12 * abs(plain.eval_f(Z))
+    g = prob.eval_g(Z)
+    assert np.array_equal(g[:plain.m], plain.eval_g(Z)) and rel_err(g[plain.m:], con0.reshape(-1)) < 1e-14
+    n = prob.n
+    jr, jc = prob.jacobian_structure()
+    hr, hc = prob.hessian_structure()
+    assert np.all(hr <= hc) and jr.max() == prob.m
+    lam = rng.normal(size=prob.m)
+    grad = prob.eval_grad_f(Z).copy()
+    Jd = _dense(jr, jc, prob.eval_jac_g(Z), (prob.m, n))
+    Hu = _dense(hr, hc, prob.eval_h(Z, 0.9, lam), (n, n))
+    Hs = Hu + np.triu(Hu, 1).T
+
+    def lagr_grad(Zv):
+        return 0.9 * prob.eval_grad_f(Zv) + _dense(jr, jc, prob.eval_jac_g(Zv), (prob.m, n)).T @ lam
+
+    h = 1e-6
+    leak_cols = [t * L.z_dim + L.x_off[0] + i for t in (0, 3) for i in idx[:3]]
+    for v in list(rng.choice(n, size=6, replace=False)) + leak_cols:
+        Zp, Zm = Z.copy(), Z.copy()
+        Zp[v] += h; Zm[v] -= h
+        assert abs((prob.eval_f(Zp) - prob.eval_f(Zm)) / (2 * h) - grad[v]) < 1e-6 * max(1.0, abs(grad[v]))
+        assert np.abs((prob.eval_g(Zp) - prob.eval_g(Zm)) / (2 * h) - Jd[:, v]).max() < 1e-7 * max(1.0, np.abs(Jd[:, v]).max())
+        assert np.abs((lagr_grad(Zp) - lagr_grad(Zm)) / (2 * h) - Hs[:, v]).max() < 2e-6 * max(1.0, np.abs(Hs[:, v]).max())
+    with pytest.raises(qcb200._lib.QcbError) as ei:        # an aux without leakage indices cannot serve leakage rows
+        Problem(L.N, L.z_dim, [ev], Aux(L.N, L.z_dim, L.dt_off, derivatives=pairs), leakage_rows=True, **base)
+    assert "leakage" in str(ei.value)
+    for p in (prob, plain, ev, aux, fid):
+        p.close()
