@@ -431,7 +431,8 @@ qcb_status qcb_aux_sensitivity_eval(qcb_aux a, const double *Z, int32_t x_off, i
  * A qcb_problem is that list on this side of the ABI.  It BORROWS its pieces (the caller keeps and
  * destroys them, after the problem): integrator handles that own the whole trajectory, one qcb_aux
  * (derivative rows, dt_t - dt_N rows, regularisers, minimum-time term) and one qcb_fidelity for
- *     f(Z) = Q |1 - F(x_N)| + sum_terms 1/2 sum_t sum_i R_i (dt_t v_{t,i})^2 + D sum_{t<N} dt_t .
+ *     f(Z) = sum_s w_s Q |1 - F(x_N^s)| + sum_terms 1/2 sum_t sum_i R_i (dt_t v_{t,i})^2 + D sum_{t<N} dt_t
+ * (one terminal state, or one per system of a sampling problem; all states are evaluated by one batched call).
  * Variables: Z, n = N * z_dim.  Constraint rows, in this order: every integrator's defect rows, the
  * derivative rows, the N-1 timestep rows, the leakage rows (m in total).  Each callback below is ONE call that writes
  * the caller's full-length array; new_x is Ipopt's flag, passed through unchanged: the problem
@@ -455,6 +456,9 @@ typedef struct {
                                        caller gives Ipopt g_U = 0, g_L = -inf for them */
     int32_t use_leakage_objective;  /* 1: add leak_Q * sum_t sum_i x_t[i]^2 / n_leak (LeakageObjective,
                                        src/quantum_objectives.jl:291-307) */
+    int32_t n_fid_states;           /* terminal states the infidelity is summed over (0 or 1: one; S for the systems
+                                       of a sampling problem, sampling_problem.jl:139-142) */
+    int32_t reserved0;              /* 0 */
     double Q;                       /* weight of the terminal infidelity */
     double min_time_D;              /* weight of sum dt (0: none) */
     double leak_Q;                  /* weight of the leakage objective */
@@ -462,7 +466,8 @@ typedef struct {
     const qcb_handle *integrators;  /* [n_integrators] */
     qcb_aux aux;                    /* may be NULL when nothing of it is used */
     qcb_fidelity fidelity;          /* may be NULL: no terminal term */
-    const int32_t *fid_index;       /* [x_dim of the fidelity] 0-based positions inside the LAST knot */
+    const int32_t *fid_index;       /* [n_fid_states][x_dim of the fidelity] 0-based positions inside the LAST knot */
+    const double *fid_weights;      /* [n_fid_states] weights of the terminal terms, NULL = 1 */
     const int32_t *reg_off;         /* [n_reg] component offsets inside a knot */
     const int32_t *reg_dim;         /* [n_reg] */
     const double *reg_R;            /* weights, concatenated over the terms */

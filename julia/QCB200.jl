@@ -353,10 +353,10 @@ end
 struct QcbProblemDesc               # mirrors qcb_problem_desc
     struct_bytes::Int32; N::Int32; z_dim::Int32; n_integrators::Int32
     use_derivative_rows::Int32; use_dt_equal_rows::Int32; fid_hessian::Int32; n_reg::Int32
-    use_leakage_rows::Int32; use_leakage_objective::Int32
+    use_leakage_rows::Int32; use_leakage_objective::Int32; n_fid_states::Int32; reserved0::Int32
     Q::Float64; min_time_D::Float64; leak_Q::Float64; leak_value::Float64
     integrators::Ptr{Ptr{Cvoid}}; aux::Ptr{Cvoid}; fidelity::Ptr{Cvoid}
-    fid_index::Ptr{Int32}; reg_off::Ptr{Int32}; reg_dim::Ptr{Int32}; reg_R::Ptr{Float64}
+    fid_index::Ptr{Int32}; fid_weights::Ptr{Float64}; reg_off::Ptr{Int32}; reg_dim::Ptr{Int32}; reg_R::Ptr{Float64}
 end
 
 mutable struct B200Problem
@@ -375,28 +375,31 @@ derivative pairs (u, du), (du, ddu); `fidelity`: a `B200Fidelity` on the compone
 function B200Problem(traj::NamedTrajectory, integrators::Vector{B200BilinearIntegrator}; aux::Ptr{Cvoid} = C_NULL,
                      derivative_rows::Bool = false, dt_equal_rows::Bool = false,
                      fidelity::Union{Nothing,B200Fidelity} = nothing, state_name::Union{Nothing,Symbol} = nothing,
+                     state_names::Vector{Symbol} = isnothing(state_name) ? Symbol[] : [state_name],
+                     fid_weights::Vector{Float64} = Float64[],
                      Q::Float64 = 100.0, fid_hessian::Bool = true, reg_names::Vector{Symbol} = Symbol[],
                      reg_R::Vector{Float64} = Float64[], D::Float64 = 0.0, leakage_rows::Bool = false,
                      leakage_value::Float64 = 0.0, leakage_Q::Union{Nothing,Float64} = nothing)
     hs = Ptr{Cvoid}[i.handle for i in integrators]
-    fidx = isnothing(state_name) ? Int32[] : Int32.(traj.components[state_name] .- 1)
+    fidx = isempty(state_names) ? Int32[] : Int32.(vcat([traj.components[n] for n in state_names]...) .- 1)   # one state per system
     off = Int32[traj.components[n][1] - 1 for n in reg_names]
     dim = Int32[length(traj.components[n]) for n in reg_names]
     R = isempty(reg_names) ? Float64[] : vcat([fill(reg_R[i], dim[i]) for i in eachindex(reg_names)]...)
     h = Ref{Ptr{Cvoid}}(C_NULL)
-    GC.@preserve hs fidx off dim R begin
+    GC.@preserve hs fidx fid_weights off dim R begin
         desc = QcbProblemDesc(Int32(sizeof(QcbProblemDesc)), traj.N, traj.dim, length(hs), derivative_rows, dt_equal_rows,
-                              fid_hessian, length(dim), leakage_rows, !isnothing(leakage_Q), Q, D,
+                              fid_hessian, length(dim), leakage_rows, !isnothing(leakage_Q), length(state_names), 0, Q, D,
                               isnothing(leakage_Q) ? 0.0 : leakage_Q, leakage_value, pointer(hs), aux,
                               isnothing(fidelity) ? C_NULL : fidelity.handle,
-                              isempty(fidx) ? C_NULL : pointer(fidx), isempty(off) ? C_NULL : pointer(off),
+                              isempty(fidx) ? C_NULL : pointer(fidx), isempty(fid_weights) ? C_NULL : pointer(fid_weights),
+                              isempty(off) ? C_NULL : pointer(off),
                               isempty(dim) ? C_NULL : pointer(dim), isempty(R) ? C_NULL : pointer(R))
         st = ccall((:qcb_problem_create, LIB), Cint, (Ref{Ptr{Cvoid}}, Ref{QcbProblemDesc}), h, desc)
         st == 0 || error(unsafe_string(ccall((:qcb_problem_last_error, LIB), Cstring, (Ptr{Cvoid},), C_NULL)))
     end
     d = [Ref{Int64}(0) for _ in 1:4]
     ccall((:qcb_problem_dims, LIB), Cint, (Ptr{Cvoid}, Ref{Int64}, Ref{Int64}, Ref{Int64}, Ref{Int64}), h[], d[1], d[2], d[3], d[4])
-    prob = B200Problem(h[], d[1][], d[2][], d[3][], d[4][], (integrators, fidelity, hs, fidx, off, dim, R))
+    prob = B200Problem(h[], d[1][], d[2][], d[3][], d[4][], (integrators, fidelity, hs, fidx, fid_weights, off, dim, R))
     finalizer(o -> ccall((:qcb_problem_destroy, LIB), Cvoid, (Ptr{Cvoid},), o.handle), prob)
     return prob
 end

@@ -33,10 +33,10 @@ class QcbAuxDesc(ctypes.Structure):
 class QcbProblemDesc(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in (
         "struct_bytes", "N", "z_dim", "n_integrators", "use_derivative_rows", "use_dt_equal_rows", "fid_hessian", "n_reg",
-        "use_leakage_rows", "use_leakage_objective")] + [
+        "use_leakage_rows", "use_leakage_objective", "n_fid_states", "reserved0")] + [
         ("Q", ctypes.c_double), ("min_time_D", ctypes.c_double), ("leak_Q", ctypes.c_double), ("leak_value", ctypes.c_double),
         ("integrators", ctypes.POINTER(c_vp)), ("aux", c_vp),
-        ("fidelity", c_vp), ("fid_index", c_ip), ("reg_off", c_ip), ("reg_dim", c_ip), ("reg_R", c_dp)]
+        ("fidelity", c_vp), ("fid_index", c_ip), ("fid_weights", c_dp), ("reg_off", c_ip), ("reg_dim", c_ip), ("reg_R", c_dp)]
 
 
 STATUS = {0: "QCB_OK", 1: "QCB_ERR_ARG", 2: "QCB_ERR_CUDA", 3: "QCB_ERR_RANGE", 4: "QCB_ERR_STRUCTURE", 5: "QCB_ERR_NOMEM"}

@@ -505,17 +505,22 @@ class Problem:
     Ipopt's full-length vectors.  The pieces are borrowed: keep them alive, close the problem first.
 
     integrators: `Evaluator`s owning the whole trajectory; fid_index: 0-based positions of the fidelity's
-    state entries inside the last knot; reg_terms: [(offset in knot, dim, R scalar or [dim])]; leakage_rows /
+    state entries inside the last knot ([states, x_dim] for the systems of a sampling problem, fid_weights per state); reg_terms: [(offset in knot, dim, R scalar or [dim])]; leakage_rows /
     leakage_Q: the inequality rows x^2 - leakage_value <= 0 and the objective term of `aux`'s leakage indices."""
 
     def __init__(self, N: int, z_dim: int, integrators=(), aux: Optional["Aux"] = None, derivative_rows: bool = False,
                  dt_equal_rows: bool = False, fidelity: Optional["Fidelity"] = None, fid_index=None, Q: float = 100.0,
                  fid_hessian: bool = True, reg_terms=(), min_time_D: float = 0.0, leakage_rows: bool = False,
-                 leakage_value: float = 0.0, leakage_Q: Optional[float] = None):
+                 leakage_value: float = 0.0, leakage_Q: Optional[float] = None, fid_weights=None):
         self.lib = _lib.load()
         self._keep = (list(integrators), aux, fidelity)
         hs = (ctypes.c_void_p * max(1, len(integrators)))(*[ev.h for ev in integrators])
-        self._fid_index = None if fid_index is None else np.ascontiguousarray(fid_index, dtype=np.int32)
+        self._fid_index = None if fid_index is None else np.ascontiguousarray(fid_index, dtype=np.int32).reshape(-1)
+        n_states = 0
+        if fidelity is not None and self._fid_index is not None:
+            n_states = self._fid_index.size // int(self.lib.qcb_fidelity_x_dim(fidelity.h))
+        self._fid_w = None if fid_weights is None else np.ascontiguousarray(fid_weights, dtype=np.float64)
+        assert self._fid_w is None or self._fid_w.size == n_states
         self._off, self._dim, self._R = Aux._terms(list(reg_terms))
         ip = lambda a: a.ctypes.data_as(_lib.c_ip) if a is not None and len(a) else None
         desc = _lib.QcbProblemDesc(
@@ -523,7 +528,8 @@ class Problem:
             use_derivative_rows=int(bool(derivative_rows)), use_dt_equal_rows=int(bool(dt_equal_rows)),
             fid_hessian=int(bool(fid_hessian)), n_reg=len(self._dim), Q=float(Q), min_time_D=float(min_time_D),
             use_leakage_rows=int(bool(leakage_rows)), use_leakage_objective=int(leakage_Q is not None),
-            leak_Q=float(leakage_Q or 0.0), leak_value=float(leakage_value),
+            leak_Q=float(leakage_Q or 0.0), leak_value=float(leakage_value), n_fid_states=n_states,
+            fid_weights=self._fid_w.ctypes.data_as(_lib.c_dp) if self._fid_w is not None else None,
             integrators=ctypes.cast(hs, ctypes.POINTER(ctypes.c_void_p)), aux=aux.h if aux is not None else None,
             fidelity=fidelity.h if fidelity is not None else None, fid_index=ip(self._fid_index),
             reg_off=ip(self._off), reg_dim=ip(self._dim),

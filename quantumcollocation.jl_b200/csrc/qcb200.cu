@@ -2392,7 +2392,6 @@ void qcb_host_free(void *ptr) { if (ptr) cudaFreeHost(ptr); }
 #include "qcb_fidelity.cuh"
 #include "qcb_aux.cuh"
 #include "qcb_global.cuh"
-#include "qcb_problem.cuh"
 
 // =========================================================================================
 // Allocation-free batched fidelity (declared in include/qcb200.h next to qcb_fidelity_eval)
@@ -2532,3 +2531,6 @@ qcb_status qcb_device_to_host(int32_t device, void *dst_host, const void *src_de
 }
 
 }  // extern "C"
+
+// one C call per Ipopt callback over the pieces above (uses the batched fidelity entry point)
+#include "qcb_problem.cuh"

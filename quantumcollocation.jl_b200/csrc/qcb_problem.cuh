@@ -18,7 +18,10 @@ struct qcb_problem_s {
     qcb_aux aux = nullptr;
     bool deriv_rows = false, dt_rows = false;
     qcb_fidelity fid = nullptr;
-    std::vector<int64_t> fid_pos;            // 0-based positions in Z of the fidelity's state entries
+    std::vector<int64_t> fid_pos;            // [fid_states][x_dim] 0-based positions in Z of the terminal states' entries
+    int fid_states = 0;                      // terminal states the fidelity is summed over (systems of a sampling problem)
+    std::vector<double> fid_w, Fv;           // weights and values per state
+    double *dX = nullptr, *dF = nullptr, *dGr = nullptr;      // device buffers of the batched fidelity call
     double Q = 0.0;
     bool fid_hess = false;
     std::vector<int32_t> reg_off, reg_dim;
@@ -53,16 +56,31 @@ qcb_status pstep(qcb_problem_s *p, qcb_status st, const char *what, const std::s
     p->err = std::string(what) + ": " + detail;
     return st;
 }
-double prob_fidelity(qcb_problem_s *p, const double *Z, bool grad, bool hess, qcb_status *st) {
-    const size_t xd = p->fid_pos.size();
-    for (size_t i = 0; i < xd; ++i) p->xN[i] = Z[p->fid_pos[i]];
-    double F = 0.0;
-    if (grad) p->gF.resize(xd);
-    if (hess) p->HF.resize(xd * xd);
-    *st = qcb_fidelity_eval(p->fid, p->xN.data(), &F, grad ? p->gF.data() : nullptr, hess ? p->HF.data() : nullptr);
-    if (*st != QCB_OK) p->err = "terminal fidelity: " + p->fid->err;
-    return F;
+// F_s (p->Fv) and, on request, dF_s/dx (p->gF, [state][x_dim]) of every terminal state: one upload of the states, the
+// batched fidelity kernels, one read-back.  The Hessian of these losses is constant in x (p->HF, taken at create).
+qcb_status prob_fidelity(qcb_problem_s *p, const double *Z, bool grad) {
+    const size_t xd = (size_t)qcb_fidelity_x_dim(p->fid), tot = xd * p->fid_states;
+    for (size_t i = 0; i < tot; ++i) p->xN[i] = Z[p->fid_pos[i]];
+    cudaError_t e = cudaSetDevice(p->fid->device);
+    if (e == cudaSuccess) e = cudaMemcpy(p->dX, p->xN.data(), tot * 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        qcb_status st = qcb_fidelity_eval_batch_device_noalloc(p->fid, p->dX, p->fid_states, p->dF, grad ? p->dGr : nullptr);
+        if (st != QCB_OK) { p->err = "terminal fidelity: " + p->fid->err; return st; }
+        e = cudaMemcpy(p->Fv.data(), p->dF, (size_t)p->fid_states * 8, cudaMemcpyDeviceToHost);
+    }
+    if (e == cudaSuccess && grad) {
+        p->gF.resize(tot);
+        e = cudaMemcpy(p->gF.data(), p->dGr, tot * 8, cudaMemcpyDeviceToHost);
+    }
+    if (e != cudaSuccess) {
+        p->err = std::string("terminal fidelity: CUDA error '") + cudaGetErrorString(e) + "'";
+        cudaGetLastError();
+        return QCB_ERR_CUDA;
+    }
+    return QCB_OK;
 }
+// d/dF of w_s Q |1 - F_s|
+inline double prob_fid_slope(const qcb_problem_s *p, int s) { return ((1.0 - p->Fv[(size_t)s]) >= 0.0 ? -p->Q : p->Q) * p->fid_w[(size_t)s]; }
 }  // namespace
 
 extern "C" {
@@ -123,18 +141,36 @@ qcb_status qcb_problem_create(qcb_problem *out, const qcb_problem_desc *d) {
     if (d->fidelity) {
         p->fid = d->fidelity;
         const int64_t xd = qcb_fidelity_x_dim(p->fid), base = (int64_t)(d->N - 1) * d->z_dim;
+        p->fid_states = d->n_fid_states > 0 ? d->n_fid_states : 1;
         if (!d->fid_index) return pfail(nullptr, QCB_ERR_ARG, "fid_index is required with a fidelity");
-        for (int64_t i = 0; i < xd; ++i) {
+        if ((int64_t)p->fid_states * p->fid->R > QCB_NOALLOC_MAX_PROJ || p->fid_states > 65535)
+            return pfail(nullptr, QCB_ERR_ARG, "too many terminal states for the batched fidelity (states * projections <= 65536)");
+        for (int64_t i = 0; i < xd * p->fid_states; ++i) {
             if (d->fid_index[i] < 0 || d->fid_index[i] >= d->z_dim) return pfail(nullptr, QCB_ERR_ARG, "fid_index outside the knot");
             p->fid_pos.push_back(base + d->fid_index[i]);
         }
-        p->xN.resize((size_t)xd);
+        for (int s = 0; s < p->fid_states; ++s) p->fid_w.push_back(d->fid_weights ? d->fid_weights[s] : 1.0);
+        p->xN.resize((size_t)(xd * p->fid_states));
+        p->Fv.assign((size_t)p->fid_states, 0.0);
         p->Q = d->Q;
         p->fid_hess = d->fid_hessian != 0 && !p->fid->linear;
         if (p->fid_hess) {
             if (xd > 8192) return pfail(nullptr, QCB_ERR_ARG, "dense terminal Hessian block over more than 8192 state entries: set fid_hessian = 0 (qcb_fidelity_factor gives the factored form)");
-            p->f_hes0 = p->nnz_h; p->f_hes_n = xd * (xd + 1) / 2;
+            p->f_hes0 = p->nnz_h; p->f_hes_n = xd * (xd + 1) / 2 * p->fid_states;
             p->nnz_h += p->f_hes_n;
+            // quadratic forms: the Hessian does not depend on x
+            p->HF.resize((size_t)(xd * xd));
+            std::vector<double> zero((size_t)xd, 0.0);
+            if (qcb_fidelity_eval(p->fid, zero.data(), nullptr, nullptr, p->HF.data()) != QCB_OK)
+                return pfail(nullptr, QCB_ERR_CUDA, "terminal fidelity Hessian: " + p->fid->err);
+        }
+        const size_t tot = (size_t)(xd * p->fid_states);
+        if (cudaSetDevice(p->fid->device) != cudaSuccess || cudaMalloc(&p->dX, tot * 8) != cudaSuccess ||
+            cudaMalloc(&p->dGr, tot * 8) != cudaSuccess || cudaMalloc(&p->dF, (size_t)p->fid_states * 8) != cudaSuccess) {
+            cudaGetLastError();
+            if (p->dX) cudaFree(p->dX);
+            if (p->dGr) cudaFree(p->dGr);
+            return pfail(nullptr, QCB_ERR_NOMEM, "device buffers of the terminal fidelity");
         }
     }
     if (d->n_reg > 0 || d->min_time_D != 0.0) {
@@ -161,7 +197,14 @@ qcb_status qcb_problem_create(qcb_problem *out, const qcb_problem_desc *d) {
     return QCB_OK;
 }
 
-void qcb_problem_destroy(qcb_problem p) { delete p; }      // the pieces are borrowed: the caller destroys them
+void qcb_problem_destroy(qcb_problem p) {      // the pieces are borrowed: the caller destroys them (after the problem)
+    if (!p) return;
+    if (p->dX || p->dF || p->dGr) {
+        if (p->fid) cudaSetDevice(p->fid->device);
+        for (double *q : {p->dX, p->dF, p->dGr}) if (q) cudaFree(q);
+    }
+    delete p;
+}
 const char *qcb_problem_last_error(qcb_problem p) { return p ? p->err.c_str() : g_create_error.c_str(); }
 
 qcb_status qcb_problem_dims(qcb_problem p, int64_t *n, int64_t *m, int64_t *nnz_jac, int64_t *nnz_hess) {
@@ -218,13 +261,16 @@ qcb_status qcb_problem_hessian_structure(qcb_problem p, int64_t *rows, int64_t *
         }
     }
     if (p->fid_hess) {
-        const int64_t xd = (int64_t)p->fid_pos.size();
+        const int64_t xd = qcb_fidelity_x_dim(p->fid);
         int64_t e = p->f_hes0;
-        for (int64_t b = 0; b < xd; ++b)
-            for (int64_t a = 0; a <= b; ++a, ++e) {
-                rows[e] = std::min(p->fid_pos[a], p->fid_pos[b]) + 1;
-                cols[e] = std::max(p->fid_pos[a], p->fid_pos[b]) + 1;
-            }
+        for (int s = 0; s < p->fid_states; ++s) {
+            const int64_t *pos = p->fid_pos.data() + (size_t)s * xd;
+            for (int64_t b = 0; b < xd; ++b)
+                for (int64_t a = 0; a <= b; ++a, ++e) {
+                    rows[e] = std::min(pos[a], pos[b]) + 1;
+                    cols[e] = std::max(pos[a], pos[b]) + 1;
+                }
+        }
     }
     if (p->has_reg) {
         qcb_status st = qcb_aux_regularizer_structure(p->aux, (int32_t)p->reg_off.size(), p->reg_off.data(), p->reg_dim.data(),
@@ -241,10 +287,9 @@ qcb_status qcb_problem_eval_f(qcb_problem p, const double *Z, int32_t new_x, dou
     if (new_x) std::fill(p->stale.begin(), p->stale.end(), 1);
     double v = 0.0;
     if (p->fid) {
-        qcb_status st;
-        const double F = prob_fidelity(p, Z, false, false, &st);
+        qcb_status st = prob_fidelity(p, Z, false);
         if (st != QCB_OK) return st;
-        v += p->Q * std::fabs(1.0 - F);
+        for (int s = 0; s < p->fid_states; ++s) v += p->fid_w[(size_t)s] * p->Q * std::fabs(1.0 - p->Fv[(size_t)s]);
     }
     if (p->has_reg) {
         double J = 0.0;
@@ -270,11 +315,13 @@ qcb_status qcb_problem_eval_grad_f(qcb_problem p, const double *Z, int32_t new_x
     if (p->n >= (1 << 20)) host_fill_pool(grad, (size_t)p->n, 0.0);      // cfg5: 263 MB of zeros around 16 k nonzeros
     else std::memset(grad, 0, (size_t)p->n * 8);
     if (p->fid) {
-        qcb_status st;
-        const double F = prob_fidelity(p, Z, true, false, &st);
+        qcb_status st = prob_fidelity(p, Z, true);
         if (st != QCB_OK) return st;
-        const double s = (1.0 - F) >= 0.0 ? -p->Q : p->Q;           // d/dF of Q |1 - F|
-        for (size_t i = 0; i < p->fid_pos.size(); ++i) grad[p->fid_pos[i]] += s * p->gF[i];
+        const size_t xd = (size_t)qcb_fidelity_x_dim(p->fid);
+        for (int s = 0; s < p->fid_states; ++s) {
+            const double slope = prob_fid_slope(p, s);
+            for (size_t i = 0; i < xd; ++i) grad[p->fid_pos[(size_t)s * xd + i]] += slope * p->gF[(size_t)s * xd + i];
+        }
     }
     if (p->has_reg) {
         qcb_status st = qcb_aux_regularizer_eval(p->aux, Z, (int32_t)p->reg_off.size(), p->reg_off.data(), p->reg_dim.data(),
@@ -364,14 +411,15 @@ qcb_status qcb_problem_eval_h(qcb_problem p, const double *Z, int32_t new_x, dou
         for (int64_t e = 0; e < p->l_n; ++e) vals[p->lo_hes0 + e] = v;
     }
     if (p->fid_hess) {
-        qcb_status st;
-        const double F = prob_fidelity(p, Z, false, true, &st);
+        qcb_status st = prob_fidelity(p, Z, false);          // the sign of 1 - F_s at this iterate
         if (st != QCB_OK) return st;
-        const double s = obj_factor * ((1.0 - F) >= 0.0 ? -p->Q : p->Q);
-        const int64_t xd = (int64_t)p->fid_pos.size();
+        const int64_t xd = qcb_fidelity_x_dim(p->fid);
         double *o = vals + p->f_hes0;
-        for (int64_t b = 0; b < xd; ++b)
-            for (int64_t a = 0; a <= b; ++a) *o++ = s * p->HF[(size_t)(a + b * xd)];
+        for (int s = 0; s < p->fid_states; ++s) {
+            const double slope = obj_factor * prob_fid_slope(p, s);
+            for (int64_t b = 0; b < xd; ++b)
+                for (int64_t a = 0; a <= b; ++a) *o++ = slope * p->HF[(size_t)(a + b * xd)];
+        }
     }
     if (p->has_reg) {
         qcb_status st = qcb_aux_regularizer_eval(p->aux, Z, (int32_t)p->reg_off.size(), p->reg_off.data(), p->reg_dim.data(),

@@ -46,7 +46,7 @@ def test_descriptor_struct_matches_header():
     body = re.search(r"typedef struct \{([^{}]*)\} qcb_problem_desc;", hdr, flags=re.S).group(1)
     body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
     assert re.findall(r"\b(\w+);", body) == [f[0] for f in _lib.QcbProblemDesc._fields_]
-    assert ctypes.sizeof(_lib.QcbProblemDesc) == 10 * 4 + 4 * 8 + 7 * 8
+    assert ctypes.sizeof(_lib.QcbProblemDesc) == 12 * 4 + 4 * 8 + 8 * 8
 
 
 def test_problem_create_checks_its_pieces_without_a_gpu(built_libs):

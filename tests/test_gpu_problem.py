@@ -264,3 +264,57 @@ def test_problem_with_leakage_rows_and_objective(built_libs):
     assert "leakage" in str(ei.value)
     for p in (prob, plain, ev, aux, fid):
         p.close()
+
+
+def test_sampling_problem_sums_the_terminal_term_over_the_systems(built_libs):
+    """UnitarySamplingProblem shape (robust qubit, three systems sharing one pulse, sampling_problem.jl:139-142): one
+    integrator handle with S = 3, the terminal infidelity summed over the three final states with weights."""
+    w = workloads.make("cfg4", N=6, S=3)
+    L = w.layout
+    assert L.S == 3 and L.z_dim == L.u_off + L.m
+    rng = np.random.default_rng(4)
+    Z = w.Z.copy()
+    wts = np.array([1.0, 0.5, 2.0])
+    terms = [(L.u_off, L.m, 0.1)]
+    ev = Evaluator(L, w.G_drift, w.G_drives)
+    aux = Aux(L.N, L.z_dim, L.dt_off)
+    fid = Fidelity(Fidelity.UNITARY, w.U_goal)
+    fid_index = np.array([np.arange(L.x_off[s], L.x_off[s] + L.x_dim) for s in range(3)])
+    prob = Problem(L.N, L.z_dim, [ev], aux, dt_equal_rows=True, fidelity=fid, fid_index=fid_index, fid_weights=wts,
+                   Q=100.0, reg_terms=terms)
+    K, xd, n = L.N - 1, L.x_dim, L.N * L.z_dim
+    assert prob.m == 3 * K * xd + K and prob.hessian_nnz == ev.hessian_nnz + 3 * xd * (xd + 1) // 2 + L.N * (2 * L.m + 1)
+    last = Z.reshape(L.N, L.z_dim)[-1]
+    Fs = [O.unitary_fidelity(last[L.x_off[s]:L.x_off[s] + xd], w.U_goal) for s in range(3)]
+    J0, gR0, _ = O.quadratic_regularizer(Z, L.N, L.z_dim, L.dt_off, terms)
+    f = prob.eval_f(Z)
+    assert abs(f - (sum(wt * 100.0 * abs(1 - F) for wt, F in zip(wts, Fs)) + J0)) < 1e-12 * abs(f)
+    g_want = gR0.reshape(-1).copy()
+    for s in range(3):
+        _, gF, _ = O.fidelity_vgh(O.KIND_UNITARY, last[L.x_off[s]:L.x_off[s] + xd], w.U_goal)
+        b = (L.N - 1) * L.z_dim + L.x_off[s]
+        g_want[b:b + xd] += -100.0 * wts[s] * np.sign(1 - Fs[s]) * gF
+    grad = prob.eval_grad_f(Z).copy()
+    assert rel_err(grad, g_want) < 1e-13
+    d0, j0, _ = O.evaluate(oracle_layout(L), w.G_drift, w.G_drives, Z, None, want_hess=False)
+    g = prob.eval_g(Z)
+    assert rel_err(g[:ev.defect_dim], d0) < 1e-10
+    jr, jc = prob.jacobian_structure()
+    hr, hc = prob.hessian_structure()
+    lam = rng.normal(size=prob.m)
+    Hu = _dense(hr, hc, prob.eval_h(Z, 1.1, lam), (n, n))
+    Hs = Hu + np.triu(Hu, 1).T
+
+    def lagr_grad(Zv):
+        return 1.1 * prob.eval_grad_f(Zv) + _dense(jr, jc, prob.eval_jac_g(Zv), (prob.m, n)).T @ lam
+
+    h = 1e-6
+    cols = list(rng.choice(n, size=5, replace=False)) + [(L.N - 1) * L.z_dim + L.x_off[s] + 2 for s in range(3)]
+    for v in cols:
+        Zp, Zm = Z.copy(), Z.copy()
+        Zp[v] += h; Zm[v] -= h
+        assert abs((prob.eval_f(Zp) - prob.eval_f(Zm)) / (2 * h) - grad[v]) < 1e-6 * max(1.0, abs(grad[v]))
+        assert np.abs((lagr_grad(Zp) - lagr_grad(Zm)) / (2 * h) - Hs[:, v]).max() < 2e-6 * max(1.0, np.abs(Hs[:, v]).max())
+    prob.close()
+    for p in (ev, aux, fid):
+        p.close()
