@@ -91,7 +91,8 @@ qcb_status qcb_problem_create(qcb_problem *out, const qcb_problem_desc *d) {
     if (d->struct_bytes != (int32_t)sizeof(qcb_problem_desc)) return pfail(nullptr, QCB_ERR_ARG, "qcb_problem_desc.struct_bytes mismatch");
     if (d->N < 2 || d->z_dim < 1 || d->n_integrators < 0 || d->n_reg < 0 || (d->n_integrators > 0 && !d->integrators))
         return pfail(nullptr, QCB_ERR_ARG, "bad dimensions in qcb_problem_desc");
-    std::unique_ptr<qcb_problem_s> p(new qcb_problem_s());
+    // every early return below releases what was built so far, device buffers included
+    std::unique_ptr<qcb_problem_s, void (*)(qcb_problem_s *)> p(new qcb_problem_s(), qcb_problem_destroy);
     p->N = d->N; p->z_dim = d->z_dim;
     p->n = (int64_t)d->N * d->z_dim;
     for (int i = 0; i < d->n_integrators; ++i) {
@@ -168,8 +169,6 @@ qcb_status qcb_problem_create(qcb_problem *out, const qcb_problem_desc *d) {
         if (cudaSetDevice(p->fid->device) != cudaSuccess || cudaMalloc(&p->dX, tot * 8) != cudaSuccess ||
             cudaMalloc(&p->dGr, tot * 8) != cudaSuccess || cudaMalloc(&p->dF, (size_t)p->fid_states * 8) != cudaSuccess) {
             cudaGetLastError();
-            if (p->dX) cudaFree(p->dX);
-            if (p->dGr) cudaFree(p->dGr);
             return pfail(nullptr, QCB_ERR_NOMEM, "device buffers of the terminal fidelity");
         }
     }
